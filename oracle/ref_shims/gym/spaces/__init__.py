@@ -1,0 +1,2 @@
+from . import discrete
+from .discrete import Discrete

@@ -378,7 +378,8 @@ def check_room(fixed, state, H, W, num_boxes):
     assert (state == PLAYER).sum() == 1
     assert ((state == BOX) | (state == BOX_ON_TARGET)).sum() == num_boxes
     assert (state == BOX_ON_TARGET).sum() == 0
-    assert (state == TARGET).sum() == num_boxes  # every target is visible (score > 0 rule)
+    # every target is uncovered by boxes (score > 0 rule); the player jitter may park the player on one
+    assert ((state == TARGET) | ((state == PLAYER) & (fixed == TARGET))).sum() == num_boxes
     movable = (state >= 3)
     assert ((fixed != WALL) | ~movable).all()
     assert (state[~movable] == fixed[~movable]).all()

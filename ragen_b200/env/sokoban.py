@@ -1,0 +1,253 @@
+"""Sokoban on the GPU: device-resident batch + per-env views with the reference API.
+
+`SokobanBatch` holds n rooms as struct-of-arrays uint8 in HBM and advances all of them with one
+kernel launch (`ragen_sokoban_step`).  `SokobanEnv` keeps the constructor / reset / step / render /
+get_all_actions contract of ragen/env/sokoban/env.py:10-67 and is a view onto one slot of a batch,
+so it can be registered under REGISTERED_ENVS['sokoban'] unchanged.
+"""
+from dataclasses import dataclass, field
+from typing import Dict, Optional, Tuple
+
+import numpy as np
+import torch
+
+from .. import _lib
+from .base import BaseDiscreteActionEnv
+
+NEWLINE = 7
+
+
+@dataclass
+class SokobanEnvConfig:
+    """Field-for-field the reference dataclass (ragen/env/sokoban/config.py:4-21)."""
+    dim_room: Tuple[int, int] = (6, 6)
+    max_steps: int = 100
+    num_boxes: int = 3
+    search_depth: int = 300
+    grid_lookup: Optional[Dict[int, str]] = field(
+        default_factory=lambda: {0: "#", 1: "_", 2: "O", 3: "√", 4: "X", 5: "P", 6: "S"})
+    grid_vocab: Optional[Dict[str, str]] = field(
+        default_factory=lambda: {"#": "wall", "_": "empty", "O": "target", "√": "box on target", "X": "box",
+                                 "P": "player", "S": "player on target"})
+    action_lookup: Optional[Dict[int, str]] = field(default_factory=lambda: {1: "Up", 2: "Down", 3: "Left", 4: "Right"})
+    dim_x: Optional[int] = None
+    dim_y: Optional[int] = None
+    render_mode: str = "text"
+
+    def __post_init__(self):
+        if self.dim_x is not None and self.dim_y is not None:
+            self.dim_room = (self.dim_x, self.dim_y)
+            delattr(self, "dim_x")
+            delattr(self, "dim_y")
+
+
+@dataclass
+class StepOut:
+    """Device tensors written by one step launch (views of the batch's output buffers)."""
+    reward: torch.Tensor      # float64 [n] summed step rewards
+    done: torch.Tensor        # uint8 [n]
+    flags: torch.Tensor       # uint8 [n] bit0 effective, bit1 success, bit2 executed
+    n_executed: torch.Tensor  # uint8 [n]
+    obs: torch.Tensor         # uint8 [n, H*(W+1)] glyph rows
+
+
+def glyph_table(grid_lookup):
+    """index 0..7 -> str; 7 is the row separator, missing codes render as '?' (env.py:56)."""
+    tab = [grid_lookup.get(i, "?") for i in range(7)] + ["\n"]
+    return tab
+
+
+def codes_to_text(codes_row, table):
+    """codes_row: 1-D uint8 numpy array of length H*(W+1); the trailing separator is dropped."""
+    return "".join(table[c] for c in codes_row[:-1].tolist())
+
+
+class SokobanBatch:
+    def __init__(self, n, dim_room=(6, 6), num_boxes=1, max_steps=100, search_depth=300, device=0):
+        self.ctx = _lib.Context.get(device)
+        self.lib = self.ctx.lib
+        self.device = torch.device("cuda", int(device))
+        self.n = int(n)
+        self.H, self.W = int(dim_room[0]), int(dim_room[1])
+        self.num_boxes, self.max_steps, self.search_depth = int(num_boxes), int(max_steps), int(search_depth)
+        HW, G = self.H * self.W, self.H * (self.W + 1)
+        dev = self.device
+        self.state = torch.zeros((self.n, HW), dtype=torch.uint8, device=dev)
+        self.fixed = torch.zeros((self.n, HW), dtype=torch.uint8, device=dev)
+        self.player = torch.zeros(self.n, dtype=torch.int16, device=dev)
+        self.env_steps = torch.zeros(self.n, dtype=torch.uint16, device=dev)
+        self.on_target = torch.zeros(self.n, dtype=torch.uint8, device=dev)
+        self.reward = torch.zeros(self.n, dtype=torch.float64, device=dev)
+        self.done = torch.zeros(self.n, dtype=torch.uint8, device=dev)
+        self.flags = torch.zeros(self.n, dtype=torch.uint8, device=dev)
+        self.n_executed = torch.zeros(self.n, dtype=torch.uint8, device=dev)
+        self.obs = torch.zeros((self.n, G), dtype=torch.uint8, device=dev)
+        self.status = torch.zeros(self.n, dtype=torch.int32, device=dev)
+        self._pinned = {}
+
+    # -- reset ------------------------------------------------------------------------------
+    def load_rooms(self, fixed, state):
+        """Adopt rooms given as arrays [n, H*W] (or [n, H, W]); the bookkeeping of
+        SokobanEnv.reset (env.py:37-38) runs on the device."""
+        f = torch.as_tensor(np.ascontiguousarray(fixed), dtype=torch.uint8).reshape(self.n, -1)
+        s = torch.as_tensor(np.ascontiguousarray(state), dtype=torch.uint8).reshape(self.n, -1)
+        self.fixed.copy_(f, non_blocking=False)
+        self.state.copy_(s, non_blocking=False)
+        self.adopt()
+
+    def adopt(self, check=True):
+        _lib.check(self.lib.ragen_sokoban_adopt(
+            self.ctx.handle, self.n, self.H, self.W, _lib.ptr(self.state), _lib.ptr(self.fixed), _lib.ptr(self.player),
+            _lib.ptr(self.env_steps), _lib.ptr(self.on_target), _lib.ptr(self.status), self.ctx.stream()))
+        if check:
+            bad = torch.nonzero(self.status).flatten()
+            if bad.numel():
+                i = int(bad[0])
+                raise ValueError(f"room {i} rejected (status {int(self.status[i])}: 1 = no player, 2 = border not wall)")
+        self.render()
+
+    # -- step -------------------------------------------------------------------------------
+    def step(self, actions, n_actions=None, render=True) -> StepOut:
+        """actions: uint8 device tensor [n] or [n, K]; n_actions: optional uint8 [n]."""
+        if actions.dim() == 1:
+            actions = actions.unsqueeze(1)
+        assert actions.dtype == torch.uint8 and actions.is_cuda and actions.is_contiguous() and actions.shape[0] == self.n
+        K = actions.shape[1]
+        _lib.check(self.lib.ragen_sokoban_step(
+            self.ctx.handle, self.n, self.H, self.W, self.num_boxes, self.max_steps, _lib.ptr(actions), K,
+            _lib.ptr(n_actions), _lib.ptr(self.state), _lib.ptr(self.fixed), _lib.ptr(self.player),
+            _lib.ptr(self.env_steps), _lib.ptr(self.on_target), _lib.ptr(self.reward), _lib.ptr(self.done),
+            _lib.ptr(self.flags), _lib.ptr(self.n_executed), _lib.ptr(self.obs) if render else None, self.ctx.stream()))
+        return StepOut(self.reward, self.done, self.flags, self.n_executed, self.obs)
+
+    def _pin(self, name, shape, dtype):
+        key = (name, tuple(shape), dtype)
+        if key not in self._pinned:
+            self._pinned[key] = torch.empty(shape, dtype=dtype, pin_memory=True)
+        return self._pinned[key]
+
+    def step_host(self, actions_np, n_actions_np=None, want_obs=True):
+        """End-to-end call with HOST buffers: actions go host->device, the step runs, and reward /
+        done / flags / n_executed (and the glyph rows) come back device->host.  Returns numpy views
+        of pinned staging buffers (valid until the next call)."""
+        a = np.ascontiguousarray(actions_np, dtype=np.uint8)
+        if a.ndim == 1:
+            a = a[:, None]
+        h_act = self._pin("act", a.shape, torch.uint8)
+        h_act.numpy()[...] = a
+        d_act = h_act.to(self.device, non_blocking=True)
+        d_na = None
+        if n_actions_np is not None:
+            h_na = self._pin("na", (self.n,), torch.uint8)
+            h_na.numpy()[...] = n_actions_np
+            d_na = h_na.to(self.device, non_blocking=True)
+        out = self.step(d_act, d_na, render=want_obs)
+        h_rew = self._pin("rew", (self.n,), torch.float64)
+        h_done = self._pin("done", (self.n,), torch.uint8)
+        h_flags = self._pin("flags", (self.n,), torch.uint8)
+        h_nex = self._pin("nex", (self.n,), torch.uint8)
+        h_rew.copy_(out.reward, non_blocking=True)
+        h_done.copy_(out.done, non_blocking=True)
+        h_flags.copy_(out.flags, non_blocking=True)
+        h_nex.copy_(out.n_executed, non_blocking=True)
+        h_obs = None
+        if want_obs:
+            h_obs = self._pin("obs", tuple(self.obs.shape), torch.uint8)
+            h_obs.copy_(out.obs, non_blocking=True)
+        torch.cuda.current_stream(self.device).synchronize()
+        return (h_obs.numpy() if want_obs else None, h_rew.numpy(), h_done.numpy(), h_flags.numpy(), h_nex.numpy())
+
+    # -- render -----------------------------------------------------------------------------
+    def render(self):
+        _lib.check(self.lib.ragen_sokoban_render(self.ctx.handle, self.n, self.H, self.W, _lib.ptr(self.state),
+                                                 _lib.ptr(self.fixed), _lib.ptr(self.obs), self.ctx.stream()))
+        return self.obs
+
+    def texts(self, grid_lookup, rows=None):
+        tab = glyph_table(grid_lookup)
+        codes = (self.obs if rows is None else self.obs[rows]).cpu().numpy()
+        return [codes_to_text(r, tab) for r in codes]
+
+
+class SokobanEnv(BaseDiscreteActionEnv):
+    """One Sokoban env with the reference interface (ragen/env/sokoban/env.py:10-67), backed by a
+    slot of a SokobanBatch.  Standalone construction creates a private batch of one env."""
+
+    def __init__(self, config=None, batch: Optional[SokobanBatch] = None, slot: int = 0, **kwargs):
+        BaseDiscreteActionEnv.__init__(self)
+        self.config = config or SokobanEnvConfig()
+        self.GRID_LOOKUP = self.config.grid_lookup
+        self.ACTION_LOOKUP = self.config.action_lookup
+        self.search_depth = self.config.search_depth
+        self.render_mode = self.config.render_mode
+        self.dim_room = tuple(self.config.dim_room)
+        self.num_boxes = self.config.num_boxes
+        self.max_steps = self.config.max_steps
+        if batch is None:
+            batch = SokobanBatch(1, self.dim_room, self.num_boxes, self.max_steps, self.search_depth,
+                                 device=kwargs.get("device", 0))
+            slot = 0
+        self.batch, self.slot = batch, slot
+        self._act = torch.zeros((batch.n, 1), dtype=torch.uint8, device=batch.device)
+        self._na = torch.zeros(batch.n, dtype=torch.uint8, device=batch.device)
+
+    # the reference exposes these as attributes; here they read the device state of the slot
+    @property
+    def room_state(self):
+        return self.batch.state[self.slot].cpu().numpy().reshape(self.dim_room).astype(np.int64)
+
+    @property
+    def room_fixed(self):
+        return self.batch.fixed[self.slot].cpu().numpy().reshape(self.dim_room).astype(np.int64)
+
+    @property
+    def player_position(self):
+        p = int(self.batch.player[self.slot])
+        return np.array([p // self.dim_room[1], p % self.dim_room[1]])
+
+    @property
+    def num_env_steps(self):
+        return int(self.batch.env_steps[self.slot])
+
+    @property
+    def boxes_on_target(self):
+        return int(self.batch.on_target[self.slot])
+
+    def load_room(self, fixed, state):
+        """Start from a given room instead of the generator (used by parity tests)."""
+        b = self.batch
+        b.fixed[self.slot].copy_(torch.as_tensor(np.asarray(fixed, dtype=np.uint8).reshape(-1)))
+        b.state[self.slot].copy_(torch.as_tensor(np.asarray(state, dtype=np.uint8).reshape(-1)))
+        b.adopt()
+        return self.render()
+
+    def reset(self, seed=None, mode=None):
+        if not hasattr(self.batch, "reset_slots"):
+            raise NotImplementedError("device room generator not built into this SokobanBatch")
+        self.batch.reset_slots([self.slot], [seed])
+        return self.render()
+
+    def step(self, action: int):
+        b = self.batch
+        self._act.zero_()
+        self._na.zero_()
+        self._act[self.slot, 0] = int(action)
+        self._na[self.slot] = 1
+        out = b.step(self._act, self._na)
+        reward = float(out.reward[self.slot])
+        fl = int(out.flags[self.slot])
+        done = bool(out.done[self.slot])
+        info = {"action_is_effective": bool(fl & 1), "action_is_valid": True, "success": bool(fl & 2)}
+        return self.render(), reward, done, info
+
+    def render(self, mode=None):
+        render_mode = mode if mode is not None else self.render_mode
+        if render_mode != "text":
+            raise ValueError(f"Invalid mode: {render_mode} (rgb_array needs gym_sokoban sprites: out of scope)")
+        return self.batch.texts(self.GRID_LOOKUP, rows=[self.slot])[0]
+
+    def get_all_actions(self):
+        return list(self.ACTION_LOOKUP.keys())
+
+    def close(self):
+        self.render_cache = None

@@ -1,0 +1,391 @@
+"""Generates the golden vectors under tests/golden/ by running the UNMODIFIED reference
+(/root/reference, loaded through oracle/ref_loader.py + oracle/ref_shims) in this container.
+
+    PYTHONHASHSEED=0 python tests/golden/make_golden.py
+
+The reference ships no golden vectors of its own for this path, so these
+files are what pins the oracle and, through it, the CUDA kernels.  Third-party step semantics
+(gym_sokoban, gymnasium) come from the shims - see oracle/ref_shims/README.md.
+"""
+import json
+import os
+import random
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
+from oracle import cfg as C  # noqa: E402
+from oracle import ref_loader as R  # noqa: E402
+
+OUT = os.path.dirname(os.path.abspath(__file__))
+
+
+def ref_generate(H, W, nb, depth, seed):
+    """generate_room under all_seed(seed); returns (fixed, state) uint8 or None on the
+    RuntimeError/RuntimeWarning that SokobanEnv.reset would catch."""
+    U = R.sokoban_utils()
+    all_seed = R.module("ragen.utils").all_seed
+    try:
+        with all_seed(seed):
+            fixed, state, _, _ = U.generate_room(dim=(H, W), num_steps=int(1.7 * (H + W)), num_boxes=nb, search_depth=depth)
+        return fixed.astype(np.uint8).reshape(-1), state.astype(np.uint8).reshape(-1)
+    except (RuntimeError, RuntimeWarning):
+        return None
+
+
+def sokoban_rooms():
+    out = {}
+    for name, (H, W, nb, depth, seeds) in {
+        "s6": (6, 6, 1, 300, list(range(0, 96)) + list(range(1010, 1020)) + list(range(123, 131))),
+        "s6d30": (6, 6, 1, 30, list(range(0, 32))),
+        "s8": (8, 8, 2, 10, list(range(0, 64))),
+        "s6b3": (6, 6, 3, 300, list(range(0, 16))),
+        "s10": (10, 10, 2, 300, list(range(0, 8))),
+        "s7x9": (7, 9, 2, 50, list(range(0, 16))),
+    }.items():
+        fixed, state, ok = [], [], []
+        for s in seeds:
+            r = ref_generate(H, W, nb, depth, s)
+            ok.append(r is not None)
+            fixed.append(r[0] if r else np.zeros(H * W, np.uint8))
+            state.append(r[1] if r else np.zeros(H * W, np.uint8))
+        out[f"{name}_cfg"] = np.array([H, W, nb, depth])
+        out[f"{name}_seeds"] = np.array(seeds)
+        out[f"{name}_ok"] = np.array(ok)
+        out[f"{name}_fixed"] = np.stack(fixed)
+        out[f"{name}_state"] = np.stack(state)
+        print(name, "rooms", len(seeds), "failed", len(seeds) - int(np.sum(ok)))
+    np.savez_compressed(os.path.join(OUT, "sokoban_rooms.npz"), **out)
+    return out
+
+
+def sokoban_steps(rooms):
+    """Step streams through the reference SokobanEnv (RAGEN wrapper over the gym_sokoban shim)."""
+    se = R.sokoban_env()
+    out = {}
+    texts = {}
+    for name, T, max_steps in (("s6", 40, 100), ("s8", 40, 100), ("s10", 60, 25), ("s6b3", 30, 100)):
+        H, W, nb, depth = rooms[f"{name}_cfg"]
+        ok = rooms[f"{name}_ok"]
+        idx = np.flatnonzero(ok)[:24]
+        rng = np.random.default_rng(7)
+        cfg = se.SokobanEnvConfig(dim_room=(int(H), int(W)), num_boxes=int(nb), max_steps=max_steps, search_depth=int(depth))
+        acts = rng.integers(1, 5, size=(len(idx), T)).astype(np.uint8)
+        acts[rng.random(acts.shape) < 0.03] = 0  # a few gym no-op steps
+        # bias half the streams toward the shortest solution so pushes / wins / +1 / +10 rewards occur
+        U = R.sokoban_utils()
+        states = np.zeros((len(idx), T, H * W), np.uint8)
+        rew = np.zeros((len(idx), T)); done = np.zeros((len(idx), T), np.uint8); flags = np.zeros((len(idx), T), np.uint8)
+        for j, i in enumerate(idx):
+            env = se.SokobanEnv(cfg)
+            env.room_fixed = rooms[f"{name}_fixed"][i].reshape(H, W).astype(np.int64)
+            env.room_state = rooms[f"{name}_state"][i].reshape(H, W).astype(np.int64)
+            env.num_env_steps, env.reward_last, env.boxes_on_target = 0, 0, 0
+            env.player_position = np.argwhere(env.room_state == 5)[0]
+            if j % 2 == 0:
+                sol = U.get_shortest_action_path(env.room_fixed, env.room_state, MAX_DEPTH=60)
+                pre = int(rng.integers(0, 4))
+                if sol:
+                    seq = list(acts[j, :pre]) + sol
+                    acts[j, :min(T, len(seq))] = seq[:T]
+            for t in range(T):
+                obs, r, d, info = env.step(int(acts[j, t]))
+                states[j, t] = env.room_state.reshape(-1)
+                rew[j, t] = r; done[j, t] = d
+                flags[j, t] = int(info["action_is_effective"]) | (int(info["success"]) << 1)
+                if j < 2 and t < 6:
+                    texts[f"{name}/{j}/{t}"] = obs
+        out[f"{name}_idx"] = idx; out[f"{name}_actions"] = acts; out[f"{name}_states"] = states
+        out[f"{name}_reward"] = rew; out[f"{name}_done"] = done; out[f"{name}_flags"] = flags
+        out[f"{name}_max_steps"] = np.array(max_steps)
+        print(name, "steps ok; wins:", int((rew > 5).sum()), "box-on:", int((np.abs(rew - 0.9) < 1e-9).sum()),
+              "box-off:", int((np.abs(rew + 1.1) < 1e-9).sum()), "done:", int(done.sum()))
+    np.savez_compressed(os.path.join(OUT, "sokoban_steps.npz"), **out)
+    with open(os.path.join(OUT, "sokoban_texts.json"), "w") as fh:
+        json.dump(texts, fh, ensure_ascii=False, indent=0)
+
+
+def frozen_lake():
+    fl = R.frozen_lake_env()
+    seeds = list(range(0, 64)) + [42, 123, 1000, 2 ** 31 - 1, 2 ** 32 - 1]
+    T = 40
+    rng = np.random.default_rng(2)
+    acts = rng.integers(1, 5, size=(len(seeds), T)).astype(np.uint8)
+    lut = {b"S": 0, b"F": 1, b"H": 2, b"G": 3}
+    desc = np.zeros((len(seeds), 16), np.uint8); start = np.zeros(len(seeds), np.uint8)
+    pos = np.zeros((len(seeds), T), np.uint8); rew = np.zeros((len(seeds), T), np.float32)
+    done = np.zeros((len(seeds), T), np.uint8); flags = np.zeros((len(seeds), T), np.uint8)
+    texts = {}
+    for j, s in enumerate(seeds):
+        env = fl.FrozenLakeEnv(fl.FrozenLakeEnvConfig())
+        obs0 = env.reset(seed=s)
+        desc[j] = [lut[bytes(x)] for x in env.desc.reshape(-1)]
+        start[j] = int(env.s)
+        if j < 4:
+            texts[f"{j}/reset"] = obs0
+        for t in range(T):
+            obs, r, d, info = env.step(int(acts[j, t]))
+            pos[j, t] = int(env.s); rew[j, t] = r; done[j, t] = d
+            flags[j, t] = int(info["action_is_effective"]) | (int(bool(info["success"])) << 1)
+            if j < 4 and t < 5:
+                texts[f"{j}/{t}"] = obs
+    # 8x8, non-default p
+    big = []
+    for s in range(8):
+        big.append("".join(R.module("ragen.env.frozen_lake.utils").generate_random_map(size=8, p=0.7, seed=s)))
+    np.savez_compressed(os.path.join(OUT, "frozen_lake.npz"), seeds=np.array(seeds, dtype=np.int64), actions=acts, desc=desc,
+                        start=start, pos=pos, reward=rew, done=done, flags=flags, maps8=np.array(big))
+    with open(os.path.join(OUT, "frozen_lake_texts.json"), "w") as fh:
+        json.dump(texts, fh, ensure_ascii=False, indent=0)
+    print("frozen_lake ok; goals reached:", int((rew > 0).sum()))
+
+
+def bandit():
+    be = R.bandit_env()
+    seeds = np.arange(500, 1012)
+    acts = 1 + (np.arange(len(seeds)) % 2)
+    lo_first = np.zeros(len(seeds), np.uint8); rew = np.zeros(len(seeds)); succ = np.zeros(len(seeds), np.uint8)
+    texts = {}
+    for j, s in enumerate(seeds):
+        env = be.BanditEnv(be.BanditEnvConfig(lo_arm_name="Phoenix", hi_arm_name="Dragon"))
+        obs0 = env.reset(seed=int(s))
+        lo_first[j] = env.ACTION_LOOKUP[1] == "Phoenix"
+        obs, r, d, info = env.step(int(acts[j]))
+        rew[j] = r; succ[j] = info["success"]
+        if j < 3:
+            texts[str(j)] = [obs0, obs]
+    np.savez_compressed(os.path.join(OUT, "bandit.npz"), seeds=seeds, actions=acts.astype(np.uint8), lo_first=lo_first,
+                        reward=rew, success=succ)
+    with open(os.path.join(OUT, "bandit_texts.json"), "w") as fh:
+        json.dump(texts, fh, indent=0)
+    print("bandit ok; mean reward", rew.mean())
+
+
+def advantage():
+    ca = R.ragen_core_algos()
+    g = torch.Generator().manual_seed(5)
+    B, T = 12, 96
+    ids_mask = torch.zeros(B, T)
+    rewards = torch.zeros(B, T)
+    for b in range(B):
+        t = int(torch.randint(5, 20, (1,), generator=g))
+        n_turn = int(torch.randint(1, 5, (1,), generator=g))
+        for k in range(n_turn):
+            gap = int(torch.randint(3, 9, (1,), generator=g)); ln = int(torch.randint(3, 12, (1,), generator=g))
+            t += gap
+            if t + ln >= T:
+                break
+            ids_mask[b, t:t + ln] = 1
+            rewards[b, t + ln - 1] = float(torch.randint(-3, 12, (1,), generator=g)) * 0.1 + 0.05
+            t += ln
+        if ids_mask[b].sum() == 0:
+            ids_mask[b, 10:14] = 1; rewards[b, 13] = 0.7
+    values = torch.randn(B, T, generator=g) * ids_mask
+    out = {"rewards": rewards.numpy(), "values": values.numpy(), "mask": ids_mask.numpy()}
+    for tag, (gamma, lam, hg) in {"a": (1.0, 1.0, 0.95), "b": (0.99, 0.95, 0.9)}.items():
+        adv, ret = ca.compute_gae_advantage_return(rewards, values, ids_mask, gamma, lam)
+        out[f"gae_{tag}_adv"] = adv.numpy(); out[f"gae_{tag}_ret"] = ret.numpy()
+        adv, ret = ca.compute_bi_level_gae_advantage_return(rewards, values, ids_mask, gamma, lam, hg)
+        out[f"bi_{tag}_adv"] = adv.numpy(); out[f"bi_{tag}_ret"] = ret.numpy()
+        out[f"cfg_{tag}"] = np.array([gamma, lam, hg])
+    # outcome rewards for GRPO: one score at the last masked token
+    outcome = torch.zeros(B, T)
+    for b in range(B):
+        last = int(torch.nonzero(ids_mask[b]).flatten()[-1])
+        outcome[b, last] = float(torch.randn(1, generator=g))
+    uid = np.array(["g%d" % (b // 4) for b in range(B)], dtype=object)
+    uid[-1] = "solo"
+    out["outcome"] = outcome.numpy(); out["uid"] = np.array([str(u) for u in uid])
+    adv, _ = ca.compute_grpo_outcome_advantage(outcome.clone(), ids_mask, uid, norm_adv_by_std_in_grpo=True)
+    out["grpo_std_adv"] = adv.numpy()
+    adv, _ = ca.compute_grpo_outcome_advantage(outcome.clone(), ids_mask, uid, norm_adv_by_std_in_grpo=False)
+    out["grpo_mean_adv"] = adv.numpy()
+    # the reference's own print-only example (ragen/trainer/core_algos.py:96-102)
+    r = torch.tensor([[0, 0, 0, 0, 1, 0, 0, 0, 0, 1]]); v = torch.tensor([[0.1, 0.2, 0.3, 0.4, 0.5, 0.6, 0.7, 0.8, 0.9, 1.0]])
+    adv, ret = ca.compute_bi_level_gae_advantage_return(r, v, torch.ones(1, 10), 1, 1, 0.95)
+    out["example_bi_adv"] = adv.numpy(); out["example_bi_ret"] = ret.numpy()
+    adv, ret = ca.compute_gae_advantage_return(r.float(), v, torch.ones(1, 10), 1, 1)
+    out["example_gae_adv"] = adv.numpy(); out["example_gae_ret"] = ret.numpy()
+    np.savez_compressed(os.path.join(OUT, "advantage.npz"), **out)
+    print("advantage ok")
+
+
+class FakeQwenTokenizer:
+    """Stands in for the HF tokenizer the way the reference's own test does
+    (tests/llm_agent/test_context_window.py:6-21): only name_or_path and encode() are reached by
+    get_masks_and_scores."""
+    name_or_path = "qwen-fake"
+    IM_START, IM_END = 151644, 151645
+
+    def encode(self, text):
+        return {"<|im_start|>": [self.IM_START], "<|im_end|>": [self.IM_END]}[text]
+
+
+def ctx_vectors():
+    cm = R.ctx_manager()
+    cases = [
+        "<think>go</think><answer>Up || Down</answer>",
+        "<think> a </think>  \n <answer> Left||Right|| Up ||Down||Left||Up||Right </answer> trailing",
+        "<think><think></answer> 123. </think><answer> <answer> say | hi </answer></answer>",
+        "<think> 456. </think><answer> 789 </answer><think> 10123 </think><answer> 11111 </answer>",
+        "<think>no answer close</think><answer>Up",
+        "no tags at all",
+        "<think>x</think> junk <answer>Up</answer>",
+        "<think>x</think><answer></answer>",
+        "<think>x</think><answer> || || </answer>",
+        "<think>a</think>b</think><answer>Up</answer>",
+        "<think>t</think><answer>Up ||Jump|| down || LEFT</answer>",
+        "<think>√ unicode  </think> <answer> Up　|| Right </answer>",
+        "<think>t<|im_start|></think><answer><|im_end|>Up<think></answer>",
+        "<think>t</think><answer>Up | | Down</answer>",
+        "<think>first</think><answer>A</answer><answer>B</answer>",
+        "<think></think><answer>Up</answer>",
+        "<answer>Up</answer>",
+        "<think>t</think>\t\r\n\x0b\x0c <answer>Down</answer>",
+        "<think>t</think><answer>  </think> Up <|im_end|> </answer>",
+        "<think>t</think><answer>Up||||Down</answer>",
+        "<think>nested <ans<think>wer> x</think><answer>Right</answer>",
+    ]
+    out = {"parse": []}
+    for think in (True, False):
+        for max_actions in (5, 1):
+            cfg = C.base_config(enable_think=think, max_actions_per_turn=max_actions)
+            ctx = cm.ContextManager.__new__(cm.ContextManager)
+            ctx.config = cfg
+            ctx.action_sep = cfg.agent_proxy.action_sep
+            ctx.special_token_list = ["<think>", "</think>", "<answer>", "</answer>", "<|im_start|>", "<|im_end|>"]
+            for text in cases:
+                resp, actions = ctx._parse_response(text)
+                out["parse"].append({"enable_think": think, "max_actions": max_actions, "in": text, "llm_response": resp,
+                                     "actions": actions})
+    # masks and scores
+    tok = FakeQwenTokenizer()
+    rng = np.random.default_rng(5)
+    B, L = 6, 64
+    ids = np.full((B, L), 151643, dtype=np.int64)
+    scores = []
+    for b in range(B):
+        seq = [tok.IM_START] + list(rng.integers(0, 1000, 3)) + [tok.IM_END, 198]
+        nturn = int(rng.integers(1, 4))
+        sc = []
+        for k in range(nturn):
+            seq += [tok.IM_START] + list(rng.integers(0, 1000, int(rng.integers(2, 5)))) + [tok.IM_END, 198]
+            seq += [tok.IM_START] + list(rng.integers(0, 1000, int(rng.integers(2, 6)))) + [tok.IM_END, 198]
+            sc.append(float(rng.integers(-2, 11)) * 0.1)
+        seq = seq[:L]
+        ids[b, L - len(seq):] = seq
+        scores.append(sc)
+    ids_t = torch.tensor(ids)
+    ms = {"ids": ids, "scores": scores}
+    for uts in (False, True):
+        for erm in (True, False):
+            s, lm, rm = cm.get_masks_and_scores(ids_t, tok, scores, use_turn_scores=uts, enable_response_mask=erm)
+            ms[f"score_{int(uts)}{int(erm)}"] = s.numpy().tolist()
+            ms[f"loss_{int(uts)}{int(erm)}"] = lm.numpy().astype(int).tolist()
+            ms[f"resp_{int(uts)}{int(erm)}"] = rm.numpy().astype(int).tolist()
+    ms["ids"] = ids.tolist()
+    out["masks_scores"] = ms
+    # group normalisation
+    norm = {}
+    Bn = 16
+    last = torch.tensor(rng.normal(size=Bn).astype(np.float32))
+    last[8:12] = 0.5  # a zero-variance group
+    pen = torch.tensor(rng.choice([0.0, -0.1, -0.2], size=Bn).astype(np.float32))
+    pen[8:12] = 0.0
+    env_outputs = [{"group_id": i // 4, "tag": "A" if i < 8 else "B", "penalty": float(pen[i])} for i in range(Bn)]
+    norm["last"] = last.tolist(); norm["penalty"] = pen.tolist()
+    for grouping in ("state", "inductive", "batch"):
+        for method in ("identity", "mean", "mean_std", "asym_clip"):
+            cfg = C.base_config(reward_normalization={"grouping": grouping, "method": method})
+            ctx = cm.ContextManager.__new__(cm.ContextManager)
+            ctx.config = cfg
+            st = torch.zeros(Bn, 5); st[:, -1] = last
+            res = ctx._normalize_score_tensor(st, env_outputs)
+            norm[f"{grouping}/{method}"] = res[:, -1].tolist()
+    out["normalize"] = norm
+    with open(os.path.join(OUT, "ctx.json"), "w") as fh:
+        json.dump(out, fh, ensure_ascii=False, indent=0)
+    print("ctx ok:", len(out["parse"]), "parse cases")
+
+
+def es_manager_script():
+    """A scripted 3-turn rollout through the reference EnvStateManager (2 groups x 4 SimpleSokoban,
+    seed 123), the recipe of es_manager.py:268-323 extended with invalid / surplus actions."""
+    es = R.es_manager()
+    cfg = C.base_config(tags=("SimpleSokoban",), n_groups=(2,), group_size=4)
+    random.seed(0); np.random.seed(0)
+    mgr = es.EnvStateManager(cfg, mode="train")
+    cache = mgr.reset(seed=123)
+    rooms_fixed = [e["env"].room_fixed.astype(int).reshape(-1).tolist() for e in mgr.envs]
+    rooms_state = [e["env"].room_state.astype(int).reshape(-1).tolist() for e in mgr.envs]
+    rng = np.random.default_rng(1)
+    names = ["Up", "Down", "Left", "Right"]
+    script = []
+    alive = [c["env_id"] for c in cache]
+    for turn in range(4):
+        inputs = []
+        for env_id in alive:
+            k = int(rng.integers(0, 7))
+            acts = [names[int(rng.integers(0, 4))] if rng.random() > 0.15 else "Jump" for _ in range(k)]
+            if rng.random() < 0.3:
+                acts = [a.upper() if rng.random() < 0.5 else a.lower() for a in acts]
+            resp = "<think>t</think><answer>" + " || ".join(acts) + "</answer>"
+            inputs.append({"env_id": env_id, "llm_raw_response": resp, "llm_response": resp, "actions": acts[:5]})
+        script.append(inputs)
+        outs = mgr.step(json.loads(json.dumps(inputs)))
+        alive = [c["env_id"] for c in outs]
+        if not alive:
+            break
+    final = mgr.get_rollout_states()
+    def clean(o):
+        if isinstance(o, dict):
+            return {k: clean(v) for k, v in o.items()}
+        if isinstance(o, (list, tuple)):
+            return [clean(v) for v in o]
+        if isinstance(o, (np.bool_, bool)):
+            return bool(o)
+        if isinstance(o, (np.integer,)):
+            return int(o)
+        if isinstance(o, (np.floating,)):
+            return float(o)
+        return o
+    status = [{"truncated": e["status"].truncated, "terminated": e["status"].terminated, "num_actions": e["status"].num_actions,
+               "rewards": e["status"].rewards, "seed": e["status"].seed} for e in mgr.envs]
+    with open(os.path.join(OUT, "es_manager.json"), "w") as fh:
+        json.dump(clean({"group_size": 4, "seed": 123, "rooms_fixed": rooms_fixed, "rooms_state": rooms_state, "script": script,
+                         "final": final, "status": status}), fh, ensure_ascii=False, indent=0)
+    print("es_manager ok; turns", len(script))
+
+
+def countdown():
+    cd = R.countdown_env()
+    cases = [("1+2+3", [1, 2, 3], 6), ("1+2", [1, 2, 3], 3), ("3*(2-1)", [1, 2, 3], 3), ("1 + 2 = 3", [1, 2, 3], 3),
+             ("6/(3-1)", [1, 3, 6], 3), ("2/0+1", [0, 1, 2], 3), ("", [1], 1), ("012+3", [12, 3], 15), ("-5+ +7 - -2", [5, 7, 2], 4),
+             ("(44 - 19) + 5", [44, 19, 5], 30), ("44 - 19 + 5)", [44, 19, 5], 30), ("99*98*97*96", [99, 98, 97, 96], 90345024),
+             ("7/2*2", [7, 2, 2], 7), ("10/4", [10, 4], 2), ("  3 + 4", [3, 4], 7), ("3 + 4\n", [3, 4], 7), ("3 4 +", [3, 4], 7),
+             ("3 ++ 4", [3, 4], 7), ("3 +* 4", [3, 4], 7), ("((3)) + ((4))", [3, 4], 7), ("3 + 4 answer", [3, 4], 7),
+             ("1/3*3", [1, 3, 3], 1), ("50 - 25 - 12", [50, 25, 12], 13), ("5 * 5 / 5", [5, 5, 5], 5), ("0/5 + 2", [0, 5, 2], 2),
+             ("8/0", [8, 0], 1), ("00 + 7", [0, 7], 7), ("7 - 00", [0, 7], 7)]
+    obj = type("X", (), {"config": type("C", (), {"score": 1, "format_score": 0.1})})()
+    rows = [{"answer": a, "nums": n, "target": t, "reward": cd.CountdownEnv.compute_reward(obj, a, {"target": t, "nums": n})}
+            for a, n, t in cases]
+    with open(os.path.join(OUT, "countdown.json"), "w") as fh:
+        json.dump(rows, fh, indent=0)
+    print("countdown ok", [r["reward"] for r in rows])
+
+
+if __name__ == "__main__":
+    assert R.available(), "reference not present"
+    if os.environ.get("PYTHONHASHSEED") != "0":
+        print("warning: PYTHONHASHSEED != 0 (only matters if a reset hits the retry path)")
+    rooms = sokoban_rooms()
+    sokoban_steps(rooms)
+    frozen_lake()
+    bandit()
+    advantage()
+    ctx_vectors()
+    es_manager_script()
+    countdown()

@@ -180,3 +180,54 @@ def test_es_manager_rooms_are_group_seeded(rooms):
         j = seeds.index(123 + i // g["group_size"])
         assert np.array_equal(np.array(f, dtype=np.uint8), rooms["s6_fixed"][j])
         assert np.array_equal(np.array(s, dtype=np.uint8), rooms["s6_state"][j])
+
+
+@pytest.mark.parametrize("name", ["s6", "s8", "s10", "s6b3"])
+def test_batched_numpy_oracle_matches_golden_steps(rooms, steps, name):
+    """oracle/sokoban_np.py (the vectorised checker used at large n) against the reference-made fixtures."""
+    from oracle.sokoban_np import SokobanBatchOracle
+
+    H, W, nb, depth = (int(x) for x in rooms[f"{name}_cfg"])
+    idx = steps[f"{name}_idx"]
+    acts = steps[f"{name}_actions"]
+    b = SokobanBatchOracle(rooms[f"{name}_fixed"][idx], rooms[f"{name}_state"][idx], H, W, nb, int(steps[f"{name}_max_steps"]))
+    done_before = np.zeros(len(idx), dtype=bool)
+    for t in range(acts.shape[1]):
+        rew, done, eff, won = b.step_one(acts[:, t])
+        live = ~done_before  # the fixtures stop recording meaningful data after done? no: they keep stepping
+        assert np.array_equal(b.state, steps[f"{name}_states"][:, t])
+        assert np.array_equal(rew, steps[f"{name}_reward"][:, t])
+        assert np.array_equal(done.astype(np.uint8), steps[f"{name}_done"][:, t])
+        assert np.array_equal(eff.astype(np.uint8) | (won.astype(np.uint8) << 1), steps[f"{name}_flags"][:, t])
+
+
+def test_batched_numpy_oracle_turns_match_scalar_oracle():
+    from oracle.sokoban_np import SokobanBatchOracle, synthetic_rooms
+
+    H, W, nb = 7, 6, 2
+    fixed, state = synthetic_rooms(200, H, W, nb, seed=11)
+    rng = np.random.default_rng(5)
+    b = SokobanBatchOracle(fixed, state, H, W, nb, 9)
+    envs = []
+    for i in range(200):
+        e = S.SokobanOracle((H, W), nb, 9)
+        e.load(fixed[i], state[i])
+        envs.append(e)
+    for turn in range(4):
+        K = 4
+        acts = rng.integers(0, 5, (200, K)).astype(np.uint8)
+        na = rng.integers(0, K + 1, 200)
+        acc, done, flags, nexec = b.step_turn(acts, na)
+        for i, e in enumerate(envs):
+            a_acc, a_done, a_fl, a_n = 0.0, 0, 0, 0
+            for k in range(int(na[i])):
+                _, r, d, info = e.step(int(acts[i, k]))
+                a_acc += r
+                a_n += 1
+                a_fl = int(info["action_is_effective"]) | (int(info["success"]) << 1) | 4
+                a_done = int(d)
+                if d:
+                    break
+            assert (a_acc, a_done, a_fl, a_n) == (acc[i], done[i], flags[i], nexec[i]), (turn, i)
+            assert np.array_equal(e.state, b.state[i])
+            assert np.array_equal(e.glyph_codes().reshape(-1), b.glyphs()[i].reshape(H, W + 1)[:, :W].reshape(-1))

@@ -23,9 +23,9 @@ SIGNATURES = {
     "ragen_version": [],
     "ragen_launch_count": [_P],
     "ragen_sm_count": [_P],
-    "ragen_sokoban_step": [_P, _L, _I, _I, _I, _I, _P, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P],
+    "ragen_sokoban_step": [_P, _L, _I, _I, _I, _I, _P, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P],
     "ragen_sokoban_render": [_P, _L, _I, _I, _P, _P, _P, _P],
-    "ragen_sokoban_adopt": [_P, _L, _I, _I, _P, _P, _P, _P, _P, _P, _P],
+    "ragen_sokoban_adopt": [_P, _L, _I, _I, _I, _P, _P, _P, _P, _P],
 }
 _RESTYPE = {"ragen_last_error": _c.c_char_p, "ragen_launch_count": _c.c_uint64}
 

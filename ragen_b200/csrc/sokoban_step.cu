@@ -24,12 +24,13 @@ namespace {
 
 constexpr int TE = 128;  // envs per CTA tile == threads per CTA
 
-struct __align__(8) EnvMeta {  // ragen_b200.h: int16 meta[n][4]
-  int16_t player;      // cell index r*W+c
-  uint16_t steps;      // num_env_steps
-  uint8_t on_target;   // boxes_on_target
-  uint8_t under;       // room_fixed[player] == 2
-  uint16_t pad;
+struct __align__(8) EnvMeta {  // ragen_b200.h: one 8-byte record per env (int16 meta[n][4])
+  int16_t player;     // cell index r*W+c
+  uint16_t steps;     // num_env_steps
+  int8_t on_target;   // boxes_on_target as the reference stores it (0 after reset, env.py:37)
+  uint8_t under;      // room_fixed[player] == 2
+  int8_t actual;      // num_boxes - #uncovered targets of the current board (what _calc_reward recounts)
+  uint8_t pad;
 };
 static_assert(sizeof(EnvMeta) == 8, "EnvMeta is one 64-bit word");
 
@@ -52,14 +53,6 @@ __host__ __device__ inline int round16(int x) { return (x + 15) & ~15; }
 // cooperative copy for tiles whose byte count is not a multiple of 16 (only the last tile)
 __device__ __forceinline__ void copy_bytes(uint8_t* dst, const uint8_t* src, int bytes) {
   for (int i = threadIdx.x; i < bytes; i += blockDim.x) dst[i] = src[i];
-}
-
-// #cells equal to `code` in one room held in shared memory (byte loop: only runs on the first step
-// after a reset, where the reference's absolute count differs from the stored zero)
-__device__ __forceinline__ int count_code(const uint8_t* S, int HW, int code) {
-  int c = 0;
-  for (int i = 0; i < HW; ++i) c += (S[i] == code);
-  return c;
 }
 
 // The glyph rows of a tile are ONE uniform byte stream: every env is H rows of W cells + 1 separator,
@@ -133,6 +126,7 @@ __global__ void __launch_bounds__(TE) sokoban_tile_kernel(const StepParams p) {
     if (!RENDER_ONLY) {
       na = p.K;
       if (p.n_actions) na = min((int)p.n_actions[g], p.K);
+      if (m.player < 0) na = 0;  // room rejected by adopt (no player): leave it alone
       const uint8_t* act = p.actions + g * p.K;
       for (int k = 0; k < min(na, 4); ++k) acts |= (uint32_t)act[k] << (8 * k);
     }
@@ -146,13 +140,13 @@ __global__ void __launch_bounds__(TE) sokoban_tile_kernel(const StepParams p) {
   if (!RENDER_ONLY && mine) {
     uint8_t* S = s_state + e * HW;
     int steps = m.steps;
-    int on = m.on_target;
+    int on = m.on_target;    // the reference's stored count
+    int actual = m.actual;   // the true count of the board; differs from `on` only right after a reset
     double acc = 0.0;
     int fl = 0, nexec = 0, dn = 0;
     for (int k = 0; k < na; ++k) {
       const int a = (k < 4) ? (int)((acts >> (8 * k)) & 0xff) : (int)p.actions[g * p.K + k];
       const int before = pos;
-      const bool first = (steps == 0);
       ++steps;
       int delta = 0;  // change of the on-target count caused by this action
       if (a >= 1 && a <= 4) {
@@ -178,15 +172,15 @@ __global__ void __launch_bounds__(TE) sokoban_tile_kernel(const StepParams p) {
           pos = ahead;
         }
       }
-      // reward (gym_sokoban _calc_reward): the count is absolute in the reference; it equals the
-      // stored count plus `delta` except on the first step after reset (stored count is 0 there)
-      const int now_on = first ? count_code(S, HW, 3) : on + delta;
+      // reward (gym_sokoban _calc_reward): the reference recounts the board and compares with the
+      // count stored by the previous step; the recount is the running count plus this action's delta
+      const int now_on = actual + delta;
       double rew = -0.1;
       if (now_on > on) rew += 1.0;
       else if (now_on < on) rew += -1.0;
       const bool won = (now_on == p.num_boxes);
       if (won) rew += 10.0;
-      on = now_on;
+      on = actual = now_on;
       acc += rew;
       ++nexec;
       fl = (before != pos ? 1 : 0) | (won ? 2 : 0) | 4;
@@ -195,7 +189,8 @@ __global__ void __launch_bounds__(TE) sokoban_tile_kernel(const StepParams p) {
     }
     m.player = (int16_t)pos;
     m.steps = (uint16_t)steps;
-    m.on_target = (uint8_t)on;
+    m.on_target = (int8_t)on;
+    m.actual = (int8_t)actual;
     m.under = (uint8_t)under;
     p.meta[g] = m;
     p.acc_reward[g] = acc;
@@ -234,4 +229,159 @@ __global__ void __launch_bounds__(TE) sokoban_tile_kernel(const StepParams p) {
     }
   }
   if (threadIdx.x == 0) tma_store_wait_read();  // shared memory must outlive the bulk engine's reads
+}
+
+// Post-reset bookkeeping (SokobanEnv.reset, env.py:37-38) + the consistency check that lets the step
+// kernel drop room_fixed.  Same tiling as the step kernel: state and fixed tiles are staged through
+// shared memory, one thread scans one room.
+struct AdoptParams {
+  int64_t n;
+  int H, W, num_boxes;
+  const uint8_t* state;
+  const uint8_t* fixed;
+  EnvMeta* meta;
+  int32_t* status;
+};
+
+__global__ void __launch_bounds__(TE) sokoban_adopt_kernel(const AdoptParams p) {
+  const int H = p.H, W = p.W, HW = H * W;
+  extern __shared__ __align__(128) uint8_t smem[];
+  __shared__ __align__(8) uint64_t bar;
+  uint8_t* s_state = smem;
+  uint8_t* s_fixed = smem + round16(TE * HW);
+  const int64_t env0 = (int64_t)blockIdx.x * TE;
+  const int cnt = (int)min((int64_t)TE, p.n - env0);
+  const int room_bytes = cnt * HW;
+  if ((room_bytes & 15) == 0) {
+    if (threadIdx.x == 0) {
+      mbar_init(&bar, 1);
+      fence_mbar_init();
+      mbar_expect_tx(&bar, 2u * (uint32_t)room_bytes);
+      tma_load_1d(s_state, p.state + env0 * HW, (uint32_t)room_bytes, &bar);
+      tma_load_1d(s_fixed, p.fixed + env0 * HW, (uint32_t)room_bytes, &bar);
+    }
+    __syncthreads();
+    mbar_wait(&bar, 0);
+  } else {
+    copy_bytes(s_state, p.state + env0 * HW, room_bytes);
+    copy_bytes(s_fixed, p.fixed + env0 * HW, room_bytes);
+    __syncthreads();
+  }
+  const int e = threadIdx.x;
+  if (e >= cnt) return;
+  const uint8_t* S = s_state + e * HW;
+  const uint8_t* F = s_fixed + e * HW;
+  int pos = -1, st = 0, open_targets = 0, under = 0;
+  int r = 0, c = 0;
+  for (int i = 0; i < HW; ++i) {
+    const int s = S[i], f = F[i];
+    if (s == 5 && pos < 0) {  // argwhere(room_state == 5)[0]: first in row-major order
+      pos = i;
+      under = (f == 2);
+    }
+    const bool border = (r == 0) | (r == H - 1) | (c == 0) | (c == W - 1);
+    if (border && f != 0 && st == 0) st = 2;
+    // room_fixed must be recoverable from room_state: 0/1/2 are themselves, a box-on-target sits on a
+    // target, a plain box on floor, the player on floor or target (true of every generated room)
+    const bool ok = (s <= 2) ? (f == s) : (s == 3) ? (f == 2) : (s == 4) ? (f == 1) : (s == 5) ? (f == 1 || f == 2) : false;
+    if (!ok && st == 0) st = 3;
+    open_targets += (s == 2) | ((s == 5) & (f == 2));
+    if (++c == W) {
+      c = 0;
+      ++r;
+    }
+  }
+  if (pos < 0) st = 1;
+  EnvMeta m{};
+  m.player = (int16_t)pos;
+  m.steps = 0;
+  m.on_target = 0;
+  m.under = (uint8_t)under;
+  m.actual = (int8_t)max(-128, p.num_boxes - open_targets);
+  p.meta[env0 + e] = m;
+  if (p.status) p.status[env0 + e] = st;
+}
+
+size_t tile_smem(int H, int W) { return (size_t)round16(TE * H * W) + 16 + round16(TE * H * (W + 1)) + 16; }
+
+template <bool RENDER_ONLY>
+int launch_tiles(ragen_ctx* ctx, const StepParams& p, cudaStream_t stream) {
+  const size_t smem = tile_smem(p.H, p.W);
+  RAGEN_REQUIRE(smem <= 227 * 1024, "room %dx%d does not fit the shared-memory tile (%zu B)", p.H, p.W, smem);
+  const unsigned grid = (unsigned)((p.n + TE - 1) / TE);
+#define RAGEN_TILE_LAUNCH(CH, CW)                                                                   \
+  do {                                                                                              \
+    auto kern = sokoban_tile_kernel<CH, CW, RENDER_ONLY>;                                           \
+    RAGEN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+    kern<<<grid, TE, smem, stream>>>(p);                                                            \
+  } while (0)
+  if (p.H == 6 && p.W == 6) RAGEN_TILE_LAUNCH(6, 6);
+  else if (p.H == 8 && p.W == 8) RAGEN_TILE_LAUNCH(8, 8);
+  else if (p.H == 10 && p.W == 10) RAGEN_TILE_LAUNCH(10, 10);
+  else RAGEN_TILE_LAUNCH(0, 0);
+#undef RAGEN_TILE_LAUNCH
+  RAGEN_LAUNCHED(ctx);
+  return RAGEN_OK;
+}
+
+bool aligned16(const void* p) { return ((uintptr_t)p & 15) == 0; }
+bool aligned8(const void* p) { return ((uintptr_t)p & 7) == 0; }
+
+}  // namespace
+
+#define RAGEN_SOKOBAN_SHAPE(n, H, W) \
+  RAGEN_REQUIRE(n >= 0 && H >= 3 && W >= 3 && H * W <= 32767, "bad shape n=%lld H=%d W=%d", (long long)n, H, W)
+
+extern "C" int ragen_sokoban_step(ragen_ctx* ctx, int64_t n, int H, int W, int num_boxes, int max_steps,
+                                  const uint8_t* actions, int K, const uint8_t* n_actions, uint8_t* state, int16_t* meta,
+                                  double* acc_reward, uint8_t* done, uint8_t* flags, uint8_t* n_executed, uint8_t* obs,
+                                  void* stream) {
+  RAGEN_REQUIRE(ctx, "ctx is NULL");
+  RAGEN_SOKOBAN_SHAPE(n, H, W);
+  RAGEN_REQUIRE(K >= 1 && K <= 255, "K=%d out of range", K);
+  RAGEN_REQUIRE(num_boxes >= 0 && num_boxes <= 127, "num_boxes=%d out of range", num_boxes);
+  RAGEN_REQUIRE(actions && state && meta && acc_reward && done && flags && n_executed, "NULL pointer argument");
+  RAGEN_REQUIRE(aligned16(state) && (!obs || aligned16(obs)) && aligned8(meta) && aligned8(acc_reward),
+                "state/obs must be 16-byte aligned, meta/acc_reward 8-byte aligned");
+  if (n == 0) return RAGEN_OK;
+  DeviceGuard guard(ctx->device);
+  StepParams p{n, H, W, num_boxes, max_steps, K, actions, n_actions, state, reinterpret_cast<EnvMeta*>(meta),
+               acc_reward, done, flags, n_executed, obs};
+  return launch_tiles<false>(ctx, p, (cudaStream_t)stream);
+}
+
+extern "C" int ragen_sokoban_render(ragen_ctx* ctx, int64_t n, int H, int W, const uint8_t* state, const int16_t* meta,
+                                    uint8_t* obs, void* stream) {
+  RAGEN_REQUIRE(ctx, "ctx is NULL");
+  RAGEN_SOKOBAN_SHAPE(n, H, W);
+  RAGEN_REQUIRE(state && meta && obs, "NULL pointer argument");
+  RAGEN_REQUIRE(aligned16(state) && aligned16(obs) && aligned8(meta), "state/obs must be 16-byte aligned, meta 8-byte aligned");
+  if (n == 0) return RAGEN_OK;
+  DeviceGuard guard(ctx->device);
+  StepParams p{};
+  p.n = n;
+  p.H = H;
+  p.W = W;
+  p.state = const_cast<uint8_t*>(state);
+  p.meta = reinterpret_cast<EnvMeta*>(const_cast<int16_t*>(meta));
+  p.obs = obs;
+  return launch_tiles<true>(ctx, p, (cudaStream_t)stream);
+}
+
+extern "C" int ragen_sokoban_adopt(ragen_ctx* ctx, int64_t n, int H, int W, int num_boxes, const uint8_t* state,
+                                   const uint8_t* fixed, int16_t* meta, int32_t* status, void* stream) {
+  RAGEN_REQUIRE(ctx, "ctx is NULL");
+  RAGEN_SOKOBAN_SHAPE(n, H, W);
+  RAGEN_REQUIRE(num_boxes >= 0 && num_boxes <= 127, "num_boxes=%d out of range", num_boxes);
+  RAGEN_REQUIRE(state && fixed && meta, "NULL pointer argument");
+  RAGEN_REQUIRE(aligned16(state) && aligned16(fixed) && aligned8(meta), "state/fixed must be 16-byte aligned, meta 8-byte aligned");
+  if (n == 0) return RAGEN_OK;
+  DeviceGuard guard(ctx->device);
+  const size_t smem = 2 * (size_t)round16(TE * H * W);
+  RAGEN_REQUIRE(smem <= 227 * 1024, "room %dx%d does not fit the shared-memory tile (%zu B)", H, W, smem);
+  RAGEN_CUDA(cudaFuncSetAttribute(sokoban_adopt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  AdoptParams p{n, H, W, num_boxes, state, fixed, reinterpret_cast<EnvMeta*>(meta), status};
+  sokoban_adopt_kernel<<<(unsigned)((n + TE - 1) / TE), TE, smem, (cudaStream_t)stream>>>(p);
+  RAGEN_LAUNCHED(ctx);
+  return RAGEN_OK;
 }

@@ -74,9 +74,8 @@ class SokobanBatch:
         dev = self.device
         self.state = torch.zeros((self.n, HW), dtype=torch.uint8, device=dev)
         self.fixed = torch.zeros((self.n, HW), dtype=torch.uint8, device=dev)
-        self.player = torch.zeros(self.n, dtype=torch.int16, device=dev)
-        self.env_steps = torch.zeros(self.n, dtype=torch.uint16, device=dev)
-        self.on_target = torch.zeros(self.n, dtype=torch.uint8, device=dev)
+        # one 8-byte record per env (include/ragen_b200.h): player, num_env_steps, boxes_on_target|under, actual
+        self.meta = torch.zeros((self.n, 4), dtype=torch.int16, device=dev)
         self.reward = torch.zeros(self.n, dtype=torch.float64, device=dev)
         self.done = torch.zeros(self.n, dtype=torch.uint8, device=dev)
         self.flags = torch.zeros(self.n, dtype=torch.uint8, device=dev)
@@ -84,6 +83,19 @@ class SokobanBatch:
         self.obs = torch.zeros((self.n, G), dtype=torch.uint8, device=dev)
         self.status = torch.zeros(self.n, dtype=torch.int32, device=dev)
         self._pinned = {}
+
+    # views of the per-env record (reference attribute names)
+    @property
+    def player(self):
+        return self.meta[:, 0]
+
+    @property
+    def env_steps(self):
+        return self.meta[:, 1].view(torch.uint16) if hasattr(torch, "uint16") else self.meta[:, 1]
+
+    @property
+    def on_target(self):
+        return self.meta.view(torch.int8)[:, 4]
 
     # -- reset ------------------------------------------------------------------------------
     def load_rooms(self, fixed, state):
@@ -97,13 +109,14 @@ class SokobanBatch:
 
     def adopt(self, check=True):
         _lib.check(self.lib.ragen_sokoban_adopt(
-            self.ctx.handle, self.n, self.H, self.W, _lib.ptr(self.state), _lib.ptr(self.fixed), _lib.ptr(self.player),
-            _lib.ptr(self.env_steps), _lib.ptr(self.on_target), _lib.ptr(self.status), self.ctx.stream()))
+            self.ctx.handle, self.n, self.H, self.W, self.num_boxes, _lib.ptr(self.state), _lib.ptr(self.fixed),
+            _lib.ptr(self.meta), _lib.ptr(self.status), self.ctx.stream()))
         if check:
             bad = torch.nonzero(self.status).flatten()
             if bad.numel():
                 i = int(bad[0])
-                raise ValueError(f"room {i} rejected (status {int(self.status[i])}: 1 = no player, 2 = border not wall)")
+                raise ValueError(f"room {i} rejected (status {int(self.status[i])}: 1 = no player, 2 = border not wall, "
+                                 "3 = room_fixed inconsistent with room_state)")
         self.render()
 
     # -- step -------------------------------------------------------------------------------
@@ -115,8 +128,7 @@ class SokobanBatch:
         K = actions.shape[1]
         _lib.check(self.lib.ragen_sokoban_step(
             self.ctx.handle, self.n, self.H, self.W, self.num_boxes, self.max_steps, _lib.ptr(actions), K,
-            _lib.ptr(n_actions), _lib.ptr(self.state), _lib.ptr(self.fixed), _lib.ptr(self.player),
-            _lib.ptr(self.env_steps), _lib.ptr(self.on_target), _lib.ptr(self.reward), _lib.ptr(self.done),
+            _lib.ptr(n_actions), _lib.ptr(self.state), _lib.ptr(self.meta), _lib.ptr(self.reward), _lib.ptr(self.done),
             _lib.ptr(self.flags), _lib.ptr(self.n_executed), _lib.ptr(self.obs) if render else None, self.ctx.stream()))
         return StepOut(self.reward, self.done, self.flags, self.n_executed, self.obs)
 
@@ -160,7 +172,7 @@ class SokobanBatch:
     # -- render -----------------------------------------------------------------------------
     def render(self):
         _lib.check(self.lib.ragen_sokoban_render(self.ctx.handle, self.n, self.H, self.W, _lib.ptr(self.state),
-                                                 _lib.ptr(self.fixed), _lib.ptr(self.obs), self.ctx.stream()))
+                                                 _lib.ptr(self.meta), _lib.ptr(self.obs), self.ctx.stream()))
         return self.obs
 
     def texts(self, grid_lookup, rows=None):

@@ -129,6 +129,22 @@ def test_abi_argument_errors():
 
     ctx = _lib.Context.get(0)
     rc = ctx.lib.ragen_sokoban_step(ctx.handle, 4, 6, 6, 1, 100, None, 1, None, None, None, None, None, None, None, None,
-                                    None, None, None, None)
+                                    None)
     assert rc == -1 and b"NULL" in ctx.lib.ragen_last_error()
-    assert ctx.launches > 0 or True
+    rc = ctx.lib.ragen_sokoban_step(ctx.handle, 4, 1, 6, 1, 100, None, 1, None, None, None, None, None, None, None, None,
+                                    None)
+    assert rc == -1 and b"bad shape" in ctx.lib.ragen_last_error()
+
+
+def test_adopt_rejects_rooms_the_generator_cannot_produce():
+    """status 1 no player, 2 border not wall, 3 room_fixed not recoverable from room_state (a plain box
+    standing on a target cell) - the step kernel relies on that invariant instead of reading room_fixed."""
+    fixed, state = synthetic_rooms(4, 6, 6, 1, seed=3)
+    fixed, state = fixed.copy(), state.copy()
+    state[0][state[0] == 5] = fixed[0][state[0] == 5]          # no player
+    fixed[1][0] = 1; state[1][0] = 1                            # hole in the border
+    box = int(np.flatnonzero(state[2] == 4)[0]); fixed[2][box] = 2  # box (code 4) on a target cell
+    b = _batch(4, 6, 6, 1, 100)
+    with pytest.raises(ValueError):
+        b.load_rooms(fixed, state)
+    assert b.status.cpu().tolist() == [1, 2, 3, 0]

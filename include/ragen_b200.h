@@ -87,6 +87,120 @@ int ragen_sokoban_render(ragen_ctx* ctx, int64_t n, int H, int W, const uint8_t*
 int ragen_sokoban_adopt(ragen_ctx* ctx, int64_t n, int H, int W, int num_boxes, const uint8_t* state,
                         const uint8_t* fixed, int16_t* meta, int32_t* status, void* stream);
 
+/* ---- FrozenLake -------------------------------------------------------------------------- */
+/* Maps are row-major uint8[n][size*size] with tile codes 0 'S' 1 'F' 2 'H' 3 'G' (size 2..8).  Glyph rows are
+ * uint8[n][size*(size+1)]: 0 player, 1 frozen (S is drawn as F), 2 hole, 3 goal, 4 player in hole, 5 player on
+ * goal (ragen/env/frozen_lake/config.py:17-20), 7 = row separator (also the last byte, not part of the string).
+ * Every env owns NumPy's PCG64 generator: rng is uint64[2][n][2] = a plane of 128-bit states {hi, lo} followed
+ * by a plane of 128-bit increments {hi, lo} (16-byte aligned). */
+
+/* FrozenLakeEnv.reset(seed) (ragen/env/frozen_lake/env.py:28-37): generate_random_map(size, p, seed)
+ * (frozen_lake/utils.py:25-47, with the is_valid reachability test :6-22) from Generator(PCG64(SeedSequence(seed))),
+ * then gymnasium's reset: the env generator is re-seeded with the same seed and draws one uniform for the start
+ * state.  status[i] (may be NULL) = 0 ok, 1 no valid map within 100000 tries.  obs may be NULL. */
+int ragen_frozenlake_reset(ragen_ctx* ctx, int64_t n, int size, double p, const uint64_t* seeds,
+                           uint8_t* tiles, uint8_t* pos, uint64_t* rng, int32_t* status, uint8_t* obs,
+                           void* stream);
+
+/* FrozenLakeEnv.step (env.py:39-45) -> gymnasium FrozenLakeEnv.step, fused with the text render (env.py:47-57),
+ * up to K actions per env as in ragen_sokoban_step.  actions 1..4 = Left/Down/Right/Up (config.py:15,22); any
+ * other value ends the env's action list (the reference raises KeyError).  One uniform is drawn per executed
+ * step.  acc_reward/done/flags/n_executed/obs as in ragen_sokoban_step (flags bit1 = standing on the goal). */
+int ragen_frozenlake_step(ragen_ctx* ctx, int64_t n, int size, int is_slippery, const uint8_t* actions, int K,
+                          const uint8_t* n_actions, const uint8_t* tiles, uint8_t* pos, uint64_t* rng,
+                          double* acc_reward, uint8_t* done, uint8_t* flags, uint8_t* n_executed,
+                          uint8_t* obs, void* stream);
+
+int ragen_frozenlake_render(ragen_ctx* ctx, int64_t n, int size, const uint8_t* tiles, const uint8_t* pos,
+                            uint8_t* obs, void* stream);
+
+/* ---- Bandit ------------------------------------------------------------------------------ */
+/* BanditEnv.reset(seed) (ragen/env/bandit/env.py:50-60): lo_first[i] = 1 when action id `start` is the lo arm
+ * (_randomize_arms :24-38).  rng layout as above. */
+int ragen_bandit_reset(ragen_ctx* ctx, int64_t n, const uint64_t* seeds, uint64_t* rng, uint8_t* lo_first,
+                       void* stream);
+/* BanditEnv.step (env.py:62-77): reward[i] = lo_arm_score, or hi_arm_hiscore with probability
+ * hi_arm_hiscore_prob else hi_arm_loscore (one uniform, hi arm only).  active (may be NULL) masks envs; an action
+ * outside {start, start+1} executes nothing (the reference asserts).  flags: bit0 effective, bit1 success (hi arm
+ * pulled), bit2 executed. */
+int ragen_bandit_step(ragen_ctx* ctx, int64_t n, int action_space_start, double lo_arm_score,
+                      double hi_arm_loscore, double hi_arm_hiscore, double hi_arm_hiscore_prob,
+                      const uint8_t* actions, const uint8_t* active, uint64_t* rng, const uint8_t* lo_first,
+                      double* reward, uint8_t* flags, void* stream);
+
+/* ---- response parsing / action lookup / Countdown scoring ---------------------------------- */
+/* ContextManager._parse_response (ragen/llm_agent/ctx_manager.py:148-173) + EnvStateManager.
+ * _extract_map_valid_actions (ragen/llm_agent/es_manager.py:230-240) over a batch of responses.
+ *   text, offsets   UTF-8 blob and int64 [n+1] byte offsets (response i = text[offsets[i], offsets[i+1]))
+ *   action_sep      [host] NUL-terminated separator, 1..8 bytes ("||")
+ *   lookup tables   table t = entries [table_first[t], table_first[t+1]); entry k has name
+ *                   names[name_off[k], name_off[k+1]) and action id codes[k]; table_id[i] selects the table of
+ *                   response i (-1 = env without action_lookup; NULL = table 0 for all).  Names match
+ *                   case-insensitively over ASCII letters.
+ *   scratch         blob of the same size as text: cleaned group contents that are not a sub-span of the input
+ *   flags      [n]  bit0 regex matched, bit1 think span lives in scratch, bit2 answer span and action spans live
+ *                   in scratch, bit3 more than max_actions actions were found (the answer text of llm_response is
+ *                   " <sep> ".join(kept actions)), bit4 codes/n_valid are meaningful
+ *   spans      [n][4]  think start, think length, answer start, answer length (bytes, relative to offsets[i])
+ *   act_spans  [n][max_actions][2]  start, length of each kept action string
+ *   n_parsed   [n]  kept actions (<= max_actions);  n_total [n] non-empty actions before the cut
+ *   codes_out  [n][max_actions], n_valid [n]  ids of the kept actions present in the table, in order */
+int ragen_parse_actions(ragen_ctx* ctx, int64_t n, const uint8_t* text, const int64_t* offsets,
+                        int enable_think, const char* action_sep, int max_actions, const uint8_t* names,
+                        const int32_t* name_off, const uint8_t* codes, const int32_t* table_first, int n_tables,
+                        const int32_t* table_id, uint8_t* scratch, uint8_t* flags, int32_t* spans,
+                        int32_t* act_spans, uint8_t* n_parsed, int32_t* n_total, uint8_t* codes_out,
+                        uint8_t* n_valid, void* stream);
+
+/* CountdownEnv.compute_reward (ragen/env/countdown/env.py:69-78): result[i] = 0 check_format failed, 1 format ok
+ * but eval != target (or raised), 2 correct.  Answer i = text[start[i], start[i]+len[i]); nums int32 [n][8] with
+ * n_nums[i] used.  unsupported[i] (may be NULL) = 1 when the expression leaves the evaluator's grammar (ints,
+ * + - * /, unary + -, parentheses, blanks): such answers are scored as if eval() had raised. */
+int ragen_countdown_score(ragen_ctx* ctx, int64_t n, const uint8_t* text, const int64_t* start,
+                          const int32_t* len, const int32_t* nums, const int32_t* n_nums, const int64_t* target,
+                          uint8_t* result, uint8_t* unsupported, void* stream);
+
+/* ---- ContextManager tensor passes ---------------------------------------------------------- */
+/* get_masks_and_scores (ragen/llm_agent/ctx_manager.py:35-70).  input_ids int64 [B][L]; outputs [B][L-1].
+ * turn_scores double [B][max_turns] with n_turns[i] valid entries per row (the Python floats of
+ * history[k]['reward']); use_turn_scores=0 puts sum(turn_scores[i]) on the last column, =1 puts score k on the
+ * <|im_end|> of turn indicator 2k+3 (last column when the row has none), then rolls by one when roll_scores
+ * (the Qwen branch :60-62). */
+int ragen_masks_scores(ragen_ctx* ctx, int B, int L, const int64_t* input_ids, int64_t im_start_id,
+                       int64_t im_end_id, int use_turn_scores, int enable_response_mask, int roll_scores,
+                       const double* turn_scores, const int32_t* n_turns, int max_turns, uint8_t* loss_mask,
+                       uint8_t* response_mask, float* score, void* stream);
+
+/* _normalize_score_tensor (ctx_manager.py:175-226) on the last score column: out = score_last + penalty, then,
+ * when n_groups < B, per group (dense ids 0..n_groups-1): method 0 identity, 1 mean, 2 mean_std, 3 asym_clip. */
+int ragen_group_norm(ragen_ctx* ctx, int B, const float* score_last, const float* penalty, const int32_t* group,
+                     int n_groups, int method, float* out, void* stream);
+
+/* ---- advantage pass ------------------------------------------------------------------------- */
+/* compute_gae_advantage_return (verl/verl/trainer/ppo/core_algos.py:67-109) WITHOUT the final whitening:
+ * adv/ret fp32 [B][T] (bit-identical to the reference's sequential fp32 loop) and, when moments != NULL, the
+ * masked moments {sum m, sum adv*m, sum adv^2*m} (double[3], zeroed by the call) that masked_whiten needs -
+ * the only quantity that has to be all-reduced when rows are sharded over GPUs. */
+int ragen_gae(ragen_ctx* ctx, int B, int T, const float* rewards, const float* values, const uint8_t* mask,
+              double gamma, double lam, float* adv, float* ret, double* moments, void* stream);
+
+/* compute_bi_level_gae_advantage_return (ragen/trainer/core_algos.py:4-92) without the final whitening. */
+int ragen_bilevel_gae(ragen_ctx* ctx, int B, int T, const float* rewards, const float* values,
+                      const uint8_t* loss_mask, double gamma, double lam, double high_level_gamma, float* adv,
+                      float* ret, double* moments, void* stream);
+
+/* masked moments of any fp32 tensor, and masked_whiten (verl/verl/utils/torch_functional.py:122-151) applied
+ * in place from (possibly all-reduced) moments: x <- (x - mean) * rsqrt(var + 1e-8). */
+int ragen_masked_moments(ragen_ctx* ctx, int64_t n, const float* x, const uint8_t* mask, double* moments,
+                         void* stream);
+int ragen_whiten(ragen_ctx* ctx, int64_t n, float* x, const double* moments, void* stream);
+
+/* compute_grpo_outcome_advantage (verl core_algos.py:113-165): scores[b] = sum_t rewards[b][t]; per group
+ * (dense ids; a group of one has mean 0 / std 1) (score - mean)/(std + epsilon) or score - mean, times mask. */
+int ragen_grpo_outcome(ragen_ctx* ctx, int B, int T, const float* rewards, const uint8_t* mask,
+                       const int32_t* group, int n_groups, double epsilon, int norm_by_std, float* scores,
+                       float* adv, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

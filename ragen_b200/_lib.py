@@ -26,6 +26,20 @@ SIGNATURES = {
     "ragen_sokoban_step": [_P, _L, _I, _I, _I, _I, _P, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P],
     "ragen_sokoban_render": [_P, _L, _I, _I, _P, _P, _P, _P],
     "ragen_sokoban_adopt": [_P, _L, _I, _I, _I, _P, _P, _P, _P, _P],
+    "ragen_frozenlake_reset": [_P, _L, _I, _D, _P, _P, _P, _P, _P, _P, _P],
+    "ragen_frozenlake_step": [_P, _L, _I, _I, _P, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P],
+    "ragen_frozenlake_render": [_P, _L, _I, _P, _P, _P, _P],
+    "ragen_bandit_reset": [_P, _L, _P, _P, _P, _P],
+    "ragen_bandit_step": [_P, _L, _I, _D, _D, _D, _D, _P, _P, _P, _P, _P, _P, _P],
+    "ragen_parse_actions": [_P, _L, _P, _P, _I, _c.c_char_p, _I, _P, _P, _P, _P, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P],
+    "ragen_countdown_score": [_P, _L, _P, _P, _P, _P, _P, _P, _P, _P, _P],
+    "ragen_masks_scores": [_P, _I, _I, _P, _L, _L, _I, _I, _I, _P, _P, _I, _P, _P, _P, _P],
+    "ragen_group_norm": [_P, _I, _P, _P, _P, _I, _I, _P, _P],
+    "ragen_gae": [_P, _I, _I, _P, _P, _P, _D, _D, _P, _P, _P, _P],
+    "ragen_bilevel_gae": [_P, _I, _I, _P, _P, _P, _D, _D, _D, _P, _P, _P, _P],
+    "ragen_masked_moments": [_P, _L, _P, _P, _P, _P],
+    "ragen_whiten": [_P, _L, _P, _P, _P],
+    "ragen_grpo_outcome": [_P, _I, _I, _P, _P, _P, _I, _D, _I, _P, _P, _P],
 }
 _RESTYPE = {"ragen_last_error": _c.c_char_p, "ragen_launch_count": _c.c_uint64}
 

@@ -40,13 +40,37 @@ extern "C" int ragen_create(int device, ragen_ctx** out) {
 
 extern "C" int ragen_destroy(ragen_ctx* ctx) {
   if (!ctx) return RAGEN_OK;
-  if (ctx->gen_ws) {
+  if (ctx->gen_ws || ctx->scratch) {
     DeviceGuard guard(ctx->device);
-    cudaFree(ctx->gen_ws);
+    if (ctx->gen_ws) cudaFree(ctx->gen_ws);
+    if (ctx->scratch) cudaFree(ctx->scratch);
   }
   free(ctx);
   return RAGEN_OK;
 }
+
+static void* grow(ragen_ctx* ctx, void** buf, size_t* have, size_t bytes) {
+  if (*have >= bytes) return *buf;
+  DeviceGuard guard(ctx->device);
+  if (*buf) {
+    cudaDeviceSynchronize();  // earlier launches may still use the old buffer
+    cudaFree(*buf);
+    *buf = nullptr;
+    *have = 0;
+  }
+  size_t want = bytes < 4096 ? 4096 : bytes + bytes / 4;
+  cudaError_t e = cudaMalloc(buf, want);
+  if (e != cudaSuccess) {
+    *buf = nullptr;
+    ragen_set_error("cudaMalloc(%zu) failed: %s", want, cudaGetErrorString(e));
+    return nullptr;
+  }
+  *have = want;
+  return *buf;
+}
+
+void* ragen_scratch(ragen_ctx* ctx, size_t bytes) { return grow(ctx, &ctx->scratch, &ctx->scratch_bytes, bytes); }
+void* ragen_gen_workspace(ragen_ctx* ctx, size_t bytes) { return grow(ctx, &ctx->gen_ws, &ctx->gen_ws_bytes, bytes); }
 
 extern "C" uint64_t ragen_launch_count(const ragen_ctx* ctx) { return ctx ? ctx->launches : 0; }
 extern "C" int ragen_sm_count(const ragen_ctx* ctx) { return ctx ? ctx->sm_count : 0; }

@@ -18,7 +18,15 @@ struct ragen_ctx {
   // generator workspace (owned; grown on demand)
   void* gen_ws;
   size_t gen_ws_bytes;
+  // small scratch for group statistics / moments (owned; grown on demand)
+  void* scratch;
+  size_t scratch_bytes;
 };
+
+// returns a device scratch buffer of at least `bytes` owned by ctx (NULL + error set on failure).  Growing it
+// synchronises the device once; steady-state calls do not allocate.
+void* ragen_scratch(ragen_ctx* ctx, size_t bytes);
+void* ragen_gen_workspace(ragen_ctx* ctx, size_t bytes);
 
 void ragen_set_error(const char* fmt, ...);
 

@@ -1,0 +1,166 @@
+// ContextManager tensor passes (sm_100a): loss / response masks and score placement from token ids, and the
+// group reward normalisation of the trajectory score.
+//
+// Replaces get_masks_and_scores (ragen/llm_agent/ctx_manager.py:35-70) and _normalize_score_tensor (:175-226).
+//
+// Layout: input_ids int64 [B][L] row-major (left padded), outputs [B][L-1]: the reference drops the first score
+// column and the last mask column (:66-68).  One warp owns one row and scans it in 32-token steps: the turn
+// indicator cumsum(ids == <|im_start|>) is a ballot + popcount prefix, so the row is read exactly once with
+// coalesced 256 B accesses (14 B per token in total: HBM-bound, no tensor cores).
+#include "common.cuh"
+
+namespace {
+
+constexpr int WARPS = 4;
+constexpr int MAX_TURNS = 64;
+
+struct MsParams {
+  int B, L;
+  const int64_t* ids;
+  int64_t im_start, im_end;
+  int use_turn_scores, enable_response_mask, roll;
+  const double* turn_scores;  // [B][max_turns]
+  const int32_t* n_turns;     // [B]
+  int max_turns;
+  uint8_t* loss_mask;
+  uint8_t* resp_mask;
+  float* score;
+};
+
+__global__ void __launch_bounds__(WARPS * 32) masks_scores_kernel(const MsParams p) {
+  __shared__ int s_pos[WARPS][MAX_TURNS];
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int row = blockIdx.x * WARPS + w;
+  if (row >= p.B) return;
+  const int L = p.L, Lo = L - 1;
+  const int64_t* ids = p.ids + (size_t)row * L;
+  uint8_t* lm = p.loss_mask + (size_t)row * Lo;
+  uint8_t* rm = p.resp_mask + (size_t)row * Lo;
+  float* sc = p.score + (size_t)row * Lo;
+  for (int k = lane; k < p.max_turns; k += 32) s_pos[w][k] = 0x7fffffff;
+  __syncwarp();
+  int turn_base = 0;
+  for (int t0 = 0; t0 < L; t0 += 32) {
+    const int t = t0 + lane;
+    const int64_t id = (t < L) ? ids[t] : -1;
+    const unsigned starts = __ballot_sync(0xffffffffu, t < L && id == p.im_start);
+    const int turn = turn_base + __popc(starts & (0xffffffffu >> (31 - lane)));  // inclusive cumsum (:43-44)
+    turn_base += __popc(starts);
+    if (t < Lo) {
+      const bool resp = (turn & 1) && turn > 1;
+      rm[t] = resp ? 1 : 0;
+      lm[t] = p.enable_response_mask ? (resp ? 1 : 0) : (turn > 1 ? 1 : 0);
+      sc[t] = 0.0f;
+    }
+    if (p.use_turn_scores && t < L && id == p.im_end && (turn & 1) && turn >= 3) {
+      const int k = (turn - 3) >> 1;  // reward of turn k sits on the <|im_end|> of indicator 2k+3 (:55-56)
+      if (k < p.max_turns) atomicMin(&s_pos[w][k], t);
+    }
+  }
+  __syncwarp();
+  if (lane != 0) return;
+  const int nt = p.n_turns[row];
+  const double* ts = p.turn_scores + (size_t)row * p.max_turns;
+  if (!p.use_turn_scores) {
+    double acc = 0.0;  // sum(scores) of Python floats, left to right (:64)
+    for (int k = 0; k < nt; ++k) acc += ts[k];
+    if (Lo >= 1) sc[Lo - 1] = (float)acc;  // full column L-1 -> output column L-2
+    return;
+  }
+  // per turn index, ascending: write at the reward position, or at the last column when the row has none (:57-59);
+  // zip_longest pads short rows with 0 (:53).  Then the Qwen roll by one (:60-62) and the dropped first column.
+  for (int k = 0; k < p.max_turns; ++k) {
+    const float v = (k < nt) ? (float)ts[k] : 0.0f;
+    const int pos = (s_pos[w][k] == 0x7fffffff) ? L - 1 : s_pos[w][k];
+    const int out = p.roll ? pos : pos - 1;  // rolled: full[t] lands in output column t; else column t-1
+    if (out >= 0 && out < Lo) sc[out] = v;
+  }
+}
+
+// x = score + penalty; per-group statistics
+__global__ void norm_stats_kernel(int B, const float* __restrict__ score, const float* __restrict__ penalty,
+                                  const int32_t* __restrict__ group, int n_groups, float* __restrict__ x, double* gstats) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B) return;
+  const float v = __fadd_rn(score[i], penalty ? penalty[i] : 0.0f);
+  x[i] = v;
+  const int g = group[i];
+  if (gstats && g >= 0 && g < n_groups) {
+    atomicAdd(gstats + 3 * g + 0, 1.0);
+    atomicAdd(gstats + 3 * g + 1, (double)v);
+    atomicAdd(gstats + 3 * g + 2, (double)v * (double)v);
+  }
+}
+
+// method: 0 identity, 1 mean, 2 mean_std, 3 asym_clip (:193-202)
+__global__ void norm_apply_kernel(int B, float* __restrict__ x, const int32_t* __restrict__ group, int n_groups,
+                                  const double* __restrict__ gstats, int method) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B) return;
+  const int g = group[i];
+  if (method == 0 || g < 0 || g >= n_groups) return;
+  const double c = gstats[3 * g], s1 = gstats[3 * g + 1], s2 = gstats[3 * g + 2];
+  const double mu = s1 / c;
+  const float mean = (float)mu;
+  float v = x[i];
+  if (method == 1) {
+    x[i] = __fsub_rn(v, mean);
+    return;
+  }
+  // unbiased std; a group of one has std = nan in torch, which fails the "> 1e-6" test -> zeros
+  float out = 0.0f;
+  if (c > 1.5) {
+    const float sd = (float)sqrt(fmax((s2 - c * mu * mu) / (c - 1.0), 0.0));
+    if (fabsf(sd) > 1e-6f) out = __fdiv_rn(__fsub_rn(v, mean), __fadd_rn(sd, 1e-6f));
+  }
+  if (method == 3) out = fminf(fmaxf(out, -1.0f), 3.0f);
+  x[i] = out;
+}
+
+}  // namespace
+
+extern "C" int ragen_masks_scores(ragen_ctx* ctx, int B, int L, const int64_t* input_ids, int64_t im_start_id,
+                                  int64_t im_end_id, int use_turn_scores, int enable_response_mask, int roll_scores,
+                                  const double* turn_scores, const int32_t* n_turns, int max_turns, uint8_t* loss_mask,
+                                  uint8_t* response_mask, float* score, void* stream) {
+  RAGEN_REQUIRE(ctx, "ctx is NULL");
+  RAGEN_REQUIRE(B >= 0 && L >= 2, "bad shape B=%d L=%d", B, L);
+  RAGEN_REQUIRE(max_turns >= 0 && max_turns <= MAX_TURNS, "max_turns=%d out of range (0..%d)", max_turns, MAX_TURNS);
+  RAGEN_REQUIRE(input_ids && n_turns && loss_mask && response_mask && score && (turn_scores || max_turns == 0),
+                "NULL pointer argument");
+  if (B == 0) return RAGEN_OK;
+  DeviceGuard guard(ctx->device);
+  MsParams p{B, L, input_ids, im_start_id, im_end_id, use_turn_scores, enable_response_mask, roll_scores, turn_scores,
+             n_turns, max_turns, loss_mask, response_mask, score};
+  masks_scores_kernel<<<(B + WARPS - 1) / WARPS, WARPS * 32, 0, (cudaStream_t)stream>>>(p);
+  RAGEN_LAUNCHED(ctx);
+  return RAGEN_OK;
+}
+
+extern "C" int ragen_group_norm(ragen_ctx* ctx, int B, const float* score_last, const float* penalty, const int32_t* group,
+                                int n_groups, int method, float* out, void* stream) {
+  RAGEN_REQUIRE(ctx, "ctx is NULL");
+  RAGEN_REQUIRE(B >= 0 && n_groups >= 1 && method >= 0 && method <= 3, "bad argument B=%d n_groups=%d method=%d", B, n_groups,
+                method);
+  RAGEN_REQUIRE(score_last && group && out, "NULL pointer argument");
+  if (B == 0) return RAGEN_OK;
+  DeviceGuard guard(ctx->device);
+  cudaStream_t st = (cudaStream_t)stream;
+  // "if len(group2index) < acc_scores.shape[0]" (:219): with as many groups as rows only the penalty is applied
+  const bool normalise = n_groups < B && method != 0;
+  double* gstats = nullptr;
+  if (normalise) {
+    const size_t bytes = (size_t)n_groups * 3 * sizeof(double);
+    gstats = (double*)ragen_scratch(ctx, bytes);
+    if (!gstats) return RAGEN_ENOMEM;
+    RAGEN_CUDA(cudaMemsetAsync(gstats, 0, bytes, st));
+  }
+  const int threads = 128, blocks = (B + threads - 1) / threads;
+  norm_stats_kernel<<<blocks, threads, 0, st>>>(B, score_last, penalty, group, n_groups, out, gstats);
+  RAGEN_LAUNCHED(ctx);
+  if (normalise) {
+    norm_apply_kernel<<<blocks, threads, 0, st>>>(B, out, group, n_groups, gstats, method);
+    RAGEN_LAUNCHED(ctx);
+  }
+  return RAGEN_OK;
+}

@@ -1,0 +1,143 @@
+// TEST INFRASTRUCTURE: compiles the host/device logic headers of ragen_b200/csrc with g++ so that the CPU test
+// suite (tests/test_hostsim.py) can run the exact per-element code the kernels run - without a GPU - against the
+// oracle and numpy.  Nothing in the product imports or links this; it is not a CPU fallback.
+#include <stdint.h>
+#include <string.h>
+
+#include "../../ragen_b200/csrc/np_random.cuh"
+#include "../../ragen_b200/csrc/parse_logic.cuh"
+#include "../../ragen_b200/csrc/toy_logic.cuh"
+
+extern "C" {
+
+// ---- numpy generator ---------------------------------------------------------------------------------------
+void hs_seed_state(uint64_t seed, uint64_t* out4) {
+  nprand::Pcg64 g;
+  nprand::pcg_seed(g, seed);
+  out4[0] = g.state_hi;
+  out4[1] = g.state_lo;
+  out4[2] = g.inc_hi;
+  out4[3] = g.inc_lo;
+}
+void hs_random(uint64_t seed, int k, double* out) {
+  nprand::Pcg64 g;
+  nprand::pcg_seed(g, seed);
+  for (int i = 0; i < k; ++i) out[i] = nprand::pcg_random(g);
+}
+// `calls` successive Generator.integers(n, size=size) calls
+void hs_integers(uint64_t seed, uint32_t n, int size, int calls, uint32_t* out) {
+  nprand::Pcg64 g;
+  nprand::pcg_seed(g, seed);
+  for (int c = 0; c < calls; ++c)
+    for (int i = 0; i < size; ++i) out[c * size + i] = nprand::bounded32(g, n);
+}
+
+// ---- FrozenLake ----------------------------------------------------------------------------------------------
+// reset + a stream of actions for one env; returns the start cell (or -1)
+int hs_frozenlake(uint64_t seed, int size, double p, int slippery, const uint8_t* actions, int T, uint8_t* tiles_out,
+                  uint8_t* pos_out, double* reward_out, uint8_t* done_out, uint8_t* flags_out, uint8_t* glyph_reset,
+                  uint8_t* glyph_steps) {
+  const double cdf0 = p / (p + (1.0 - p));
+  nprand::Pcg64 g;
+  nprand::pcg_seed(g, seed);
+  toy::Tiles tiles{0, 0};
+  const int start = toy::fl_generate_map(g, size, cdf0, tiles, 100000);
+  if (start < 0) return -1;
+  for (int i = 0; i < size * size; ++i) tiles_out[i] = (uint8_t)tiles.get(i);
+  nprand::pcg_seed(g, seed);
+  (void)nprand::pcg_random(g);
+  int pos = start;
+  const int G = size * (size + 1);
+  toy::fl_render(tiles, size, pos, glyph_reset);
+  for (int t = 0; t < T; ++t) {
+    bool d, e, s;
+    const int r = toy::fl_step(tiles, size, pos, g, actions[t], slippery != 0, d, e, s);
+    pos_out[t] = (uint8_t)pos;
+    reward_out[t] = r;
+    done_out[t] = d;
+    flags_out[t] = (uint8_t)((e ? 1 : 0) | (s ? 2 : 0));
+    toy::fl_render(tiles, size, pos, glyph_steps + (size_t)t * G);
+  }
+  return start;
+}
+
+// ---- Bandit --------------------------------------------------------------------------------------------------
+// returns lo_first; kind_out = bandit_step result for `arm_index`
+int hs_bandit(uint64_t seed, int arm_index, double hi_prob, int* kind_out) {
+  nprand::Pcg64 g;
+  const bool lf = toy::bandit_reset(g, seed);
+  *kind_out = toy::bandit_step(g, lf, arm_index, hi_prob);
+  return lf ? 1 : 0;
+}
+
+// ---- parse ---------------------------------------------------------------------------------------------------
+// Sequential driver with the same phases as parse_kernel.  out: flags, spans[4], act_spans[2*max], n_parsed,
+// n_total, codes[max], n_valid.  `scratch` has at least n bytes.
+void hs_parse(const uint8_t* text, int n, int enable_think, const char* sep, int max_actions, const uint8_t* names,
+              const int32_t* name_off, const uint8_t* codes, int first, int count, uint8_t* scratch, int32_t* out) {
+  parse::Matcher m;
+  parse::matcher_init(m, enable_think != 0);
+  for (int i = 0; i < n && m.state != 3; ++i)
+    if (text[i] == '<') {
+      const int tag = parse::classify_tag(text + i, text + n);
+      if (tag != parse::T_NONE) parse::matcher_feed(m, text, n, i, tag);
+    }
+  int fl = 0, ts = 0, te = 0, as = 0, ae = 0;
+  parse::ParseTail tail;
+  tail.total = tail.kept = tail.nvalid = 0;
+  if (m.state == 3) {
+    fl = 1;
+    ts = m.think_s;
+    te = m.think_e;
+    as = m.ans_s;
+    ae = m.ans_e;
+    const uint8_t* abuf = text;
+    for (int which = 0; which < 2; ++which) {
+      if (which == 0 && !enable_think) continue;
+      int s = which ? as : ts, e = which ? ae : te;
+      if (parse::has_special(text, s, e)) {
+        memcpy(scratch + s, text + s, (size_t)(e - s));
+        parse::clean_content(scratch, s, e);
+        fl |= which ? 4 : 2;
+        if (which) abuf = scratch;
+      } else {
+        parse::strip(text, s, e);
+      }
+      if (which) {
+        as = s;
+        ae = e;
+      } else {
+        ts = s;
+        te = e;
+      }
+    }
+    parse::ActionTable tab{names, name_off, codes, first, count};
+    if (count >= 0) fl |= 16;
+    const int sep_len = (int)strlen(sep);
+    parse::parse_finish(abuf, as, ae, (const uint8_t*)sep, sep_len, max_actions, tab, tail);
+    if (tail.total > max_actions) fl |= 8;
+  }
+  int k = 0;
+  out[k++] = fl;
+  out[k++] = ts;
+  out[k++] = te - ts;
+  out[k++] = as;
+  out[k++] = ae - as;
+  out[k++] = tail.kept;
+  out[k++] = tail.total;
+  out[k++] = tail.nvalid;
+  for (int a = 0; a < max_actions; ++a) {
+    out[k++] = a < tail.kept ? tail.spans[2 * a] : 0;
+    out[k++] = a < tail.kept ? tail.spans[2 * a + 1] : 0;
+  }
+  for (int a = 0; a < max_actions; ++a) out[k++] = a < tail.nvalid ? tail.codes[a] : 0;
+}
+
+int hs_countdown(const uint8_t* s, int n, const int32_t* nums, int n_nums, long long target, int* unsupported) {
+  bool u = false;
+  const int r = parse::countdown_score(s, n, nums, n_nums, target, u);
+  *unsupported = u ? 1 : 0;
+  return r;
+}
+
+}  // extern "C"

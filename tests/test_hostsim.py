@@ -1,0 +1,256 @@
+"""CPU: the per-element logic the kernels run (ragen_b200/csrc/*_logic.cuh, np_random.cuh), compiled for the host
+with g++ (tests/hostsim/hostsim.cpp) and compared with numpy itself, the oracle and the reference-made golden
+fixtures.  This pins the device code's arithmetic without a GPU; the `-m gpu` tests then check the kernels proper.
+"""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from conftest import ROOT, golden_json, golden_npz
+from oracle import managers as M
+from oracle import toy_envs as TE
+
+HS_DIR = os.path.join(ROOT, "tests", "hostsim")
+HS_SO = os.path.join(HS_DIR, "_hostsim.so")
+c = ctypes
+
+
+@pytest.fixture(scope="session")
+def hs():
+    src = os.path.join(HS_DIR, "hostsim.cpp")
+    deps = [src] + [os.path.join(ROOT, "ragen_b200", "csrc", f) for f in ("np_random.cuh", "parse_logic.cuh", "toy_logic.cuh")]
+    if not os.path.exists(HS_SO) or any(os.path.getmtime(d) > os.path.getmtime(HS_SO) for d in deps):
+        subprocess.run(["g++", "-std=c++17", "-O1", "-shared", "-fPIC", "-o", HS_SO, src], check=True)
+    lib = c.CDLL(HS_SO)
+    lib.hs_countdown.restype = c.c_int
+    lib.hs_countdown.argtypes = [c.c_char_p, c.c_int, c.c_void_p, c.c_int, c.c_longlong, c.c_void_p]
+    lib.hs_frozenlake.restype = c.c_int
+    lib.hs_frozenlake.argtypes = [c.c_uint64, c.c_int, c.c_double, c.c_int] + [c.c_void_p, c.c_int] + [c.c_void_p] * 7
+    lib.hs_random.argtypes = [c.c_uint64, c.c_int, c.c_void_p]
+    lib.hs_integers.argtypes = [c.c_uint64, c.c_uint32, c.c_int, c.c_int, c.c_void_p]
+    lib.hs_seed_state.argtypes = [c.c_uint64, c.c_void_p]
+    lib.hs_bandit.argtypes = [c.c_uint64, c.c_int, c.c_double, c.c_void_p]
+    lib.hs_parse.argtypes = [c.c_char_p, c.c_int, c.c_int, c.c_char_p, c.c_int, c.c_void_p, c.c_void_p, c.c_void_p, c.c_int,
+                             c.c_int, c.c_void_p, c.c_void_p]
+    return lib
+
+
+def P(a):
+    return a.ctypes.data_as(c.c_void_p)
+
+
+SEEDS = [0, 1, 42, 123, 2 ** 31 - 1, 2 ** 32 - 1, 2 ** 32, 2 ** 40 + 7, 10 ** 6 + 5, 2 ** 63 + 11]
+
+
+def test_seedsequence_pcg64_match_numpy(hs):
+    for seed in SEEDS:
+        st = np.zeros(4, np.uint64)
+        hs.hs_seed_state(seed, P(st))
+        bg = np.random.PCG64(np.random.SeedSequence(seed))
+        want = bg.state["state"]
+        assert (int(st[0]) << 64) | int(st[1]) == want["state"], seed
+        assert (int(st[2]) << 64) | int(st[3]) == want["inc"], seed
+        got = np.zeros(64, np.float64)
+        hs.hs_random(seed, 64, P(got))
+        assert np.array_equal(got, np.random.Generator(bg).random(64))
+
+
+@pytest.mark.parametrize("n", [1, 2, 3, 4, 5, 7, 8, 100, 2 ** 31 + 3])
+def test_bounded_integers_match_numpy(hs, n):
+    for seed in SEEDS[:6]:
+        got = np.zeros(2 * 50, np.uint32)
+        hs.hs_integers(seed, n, 2, 50, P(got))
+        g = np.random.Generator(np.random.PCG64(np.random.SeedSequence(seed)))
+        want = np.concatenate([g.integers(n, size=2) for _ in range(50)])
+        assert np.array_equal(got.astype(np.int64), want), (seed, n)
+
+
+def _run_fl(hs, seed, size, p, slippery, actions):
+    T = len(actions)
+    G = size * (size + 1)
+    tiles = np.zeros(size * size, np.uint8)
+    pos = np.zeros(T, np.uint8); rew = np.zeros(T); done = np.zeros(T, np.uint8); flags = np.zeros(T, np.uint8)
+    g0 = np.zeros(G, np.uint8); gs = np.zeros((T, G), np.uint8)
+    a = np.ascontiguousarray(actions, dtype=np.uint8)
+    start = hs.hs_frozenlake(seed, size, p, int(slippery), P(a), T, P(tiles), P(pos), P(rew), P(done), P(flags), P(g0), P(gs))
+    return start, tiles, pos, rew, done, flags, g0, gs
+
+
+def _glyph_text(codes, table):
+    return "".join(table[int(x)] for x in codes[:-1])
+
+
+FL_TABLE = [TE.FL_GLYPHS[i] for i in range(6)] + ["?", "\n"]
+
+
+def test_frozenlake_matches_golden(hs):
+    g = golden_npz("frozen_lake.npz")
+    texts = golden_json("frozen_lake_texts.json")
+    for j, seed in enumerate(g["seeds"].tolist()):
+        start, tiles, pos, rew, done, flags, g0, gs = _run_fl(hs, seed, 4, 0.8, True, g["actions"][j])
+        assert np.array_equal(tiles, g["desc"][j]), seed
+        assert start == int(g["start"][j])
+        assert np.array_equal(pos, g["pos"][j]), seed
+        assert np.array_equal(rew.astype(np.float32), g["reward"][j])
+        assert np.array_equal(done, g["done"][j])
+        assert np.array_equal(flags, g["flags"][j])
+        if f"{j}/reset" in texts:
+            assert _glyph_text(g0, FL_TABLE) == texts[f"{j}/reset"]
+            for t in range(5):
+                assert _glyph_text(gs[t], FL_TABLE) == texts[f"{j}/{t}"]
+
+
+def test_frozenlake_matches_oracle_other_sizes(hs):
+    rng = np.random.default_rng(0)
+    for size, p, slip in [(8, 0.7, True), (5, 0.9, False), (2, 0.8, True), (3, 0.5, True), (8, 0.8, True)]:
+        for seed in range(12):
+            acts = rng.integers(1, 5, 30)
+            o = TE.FrozenLakeOracle(size=size, p=p, is_slippery=slip)
+            o.reset(seed)
+            start, tiles, pos, rew, done, flags, g0, gs = _run_fl(hs, seed, size, p, slip, acts)
+            assert np.array_equal(tiles, o.tiles()), (size, seed)
+            assert start == o.s
+            assert _glyph_text(g0, FL_TABLE) == o.render()
+            for t, a in enumerate(acts):
+                obs, r, d, info = o.step(int(a))
+                assert pos[t] == o.s and rew[t] == r and bool(done[t]) == d
+                assert flags[t] == int(info["action_is_effective"]) | (int(info["success"]) << 1)
+                assert _glyph_text(gs[t], FL_TABLE) == obs
+    maps8 = golden_npz("frozen_lake.npz")["maps8"]
+    lut = {"S": 0, "F": 1, "H": 2, "G": 3}
+    for s in range(8):
+        _, tiles, *_ = _run_fl(hs, s, 8, 0.7, True, [1])
+        assert tiles.tolist() == [lut[ch] for ch in str(maps8[s])]
+
+
+def test_bandit_matches_golden(hs):
+    g = golden_npz("bandit.npz")
+    for seed, act, lo_first, rew, succ in zip(g["seeds"], g["actions"], g["lo_first"], g["reward"], g["success"]):
+        kind = c.c_int(0)
+        lf = hs.hs_bandit(int(seed), int(act) - 1, 0.25, c.byref(kind))
+        assert lf == int(lo_first)
+        assert {0: 0.1, 1: 1.0, 2: 0.0}[kind.value] == rew
+        assert (kind.value != 0) == bool(succ)
+
+
+NAMES = ["Up", "Down", "Left", "Right"]
+
+
+def _table(names, codes):
+    blob = b"".join(n.encode() for n in names)
+    off = np.cumsum([0] + [len(n.encode()) for n in names]).astype(np.int32)
+    return np.frombuffer(blob, np.uint8).copy(), off, np.array(codes, np.uint8)
+
+
+def hs_parse(hs, text, enable_think=True, sep="||", max_actions=5, names=NAMES, codes=(1, 2, 3, 4)):
+    from ragen_b200.llm_agent.parse_host import assemble_response
+
+    raw = text.encode()
+    nb, off, cd = _table(names or ["-"], codes or (0,))
+    scratch = np.zeros(max(len(raw), 1), np.uint8)
+    out = np.zeros(8 + 3 * max_actions, np.int32)
+    hs.hs_parse(raw, len(raw), int(enable_think), sep.encode(), max_actions, P(nb), P(off), P(cd), 0, len(names) if names else -1,
+                P(scratch), P(out))
+    fl = int(out[0])
+    spans = out[1:5]
+    kept, total, nvalid = int(out[5]), int(out[6]), int(out[7])
+    act_spans = out[8:8 + 2 * max_actions].reshape(max_actions, 2)
+    codes_out = out[8 + 2 * max_actions:8 + 3 * max_actions]
+    resp, actions = assemble_response(raw, scratch.tobytes(), fl, spans, act_spans, kept, enable_think, sep)
+    return resp, actions, codes_out[:nvalid].tolist(), total
+
+
+def test_parse_matches_golden(hs):
+    for case in golden_json("ctx.json")["parse"]:
+        resp, actions, codes, total = hs_parse(hs, case["in"], case["enable_think"], "||", case["max_actions"])
+        assert resp == case["llm_response"], case
+        assert actions == case["actions"], case
+        assert codes == M.ManagerOracle.map_actions(dict(zip((1, 2, 3, 4), NAMES)), actions)
+
+
+def test_parse_fuzz_against_oracle(hs):
+    rng = np.random.default_rng(11)
+    atoms = ["<think>", "</think>", "<answer>", "</answer>", "<|im_start|>", "<|im_end|>", "Up", "down", "LEFT", "Right", "Jump",
+             "||", "|", " ", "\n", "\t", "　", "\xa0", "\x85", "√", "<", ">", "</", "<thi", "nk>", "</ans", "wer>", "x", "||||",
+             " ", "é", "<answe", "r>"]
+    for it in range(4000):
+        k = int(rng.integers(1, 14))
+        text = "".join(atoms[int(i)] for i in rng.integers(0, len(atoms), k))
+        if it % 3 == 0:
+            text = "<think>" + text
+        if it % 5 == 0:
+            text = text + "</think><answer>" + "".join(atoms[int(i)] for i in rng.integers(0, len(atoms), 4)) + "</answer>"
+        for think in (True, False):
+            for mx in (5, 1, 2):
+                want_resp, want_actions = M.parse_response(text, think, "||", mx)
+                resp, actions, codes, total = hs_parse(hs, text, think, "||", mx)
+                assert (resp, actions) == (want_resp, want_actions), repr(text)
+                assert codes == M.ManagerOracle.map_actions(dict(zip((1, 2, 3, 4), NAMES)), actions), repr(text)
+
+
+def test_lookup_duplicates_and_no_table(hs):
+    resp, actions, codes, _ = hs_parse(hs, "<think>t</think><answer>dragon||Phoenix||x</answer>", names=["Phoenix", "Dragon", "phoenix"],
+                                       codes=(1, 2, 7))
+    assert actions == ["dragon", "Phoenix", "x"] and codes == [2, 7]  # a later duplicate name wins, as in the dict
+    resp, actions, codes, _ = hs_parse(hs, "<think>t</think><answer>1+2</answer>", names=None, codes=())
+    assert actions == ["1+2"] and codes == []
+
+
+def _cd(hs, answer, nums, target):
+    raw = answer.encode()
+    arr = np.zeros(8, np.int32)
+    arr[:len(nums)] = nums
+    u = c.c_int(0)
+    r = hs.hs_countdown(raw, len(raw), P(arr), len(nums), int(target), c.byref(u))
+    return r, u.value
+
+
+def test_countdown_matches_golden(hs):
+    for row in golden_json("countdown.json"):
+        r, u = _cd(hs, row["answer"], row["nums"], row["target"])
+        assert {0: 0, 1: 0.1, 2: 1}[r] == row["reward"], row
+
+
+def test_countdown_fuzz_against_python_eval(hs):
+    """Random expressions inside the evaluator's grammar must score exactly like Python's eval; expressions outside
+    it must be flagged `unsupported` whenever the device disagrees with Python."""
+    rng = np.random.default_rng(3)
+    toks = ["+", "-", "*", "/", "(", ")", " ", "  "]
+    n_div = 0
+    for it in range(6000):
+        nums = rng.integers(0, 100, int(rng.integers(2, 5))).tolist()
+        parts = []
+        for i, v in enumerate(nums):
+            if rng.random() < 0.3:
+                parts.append(["-", "+", "(", "- ", "(-"][int(rng.integers(0, 5))])
+            parts.append(str(v) if rng.random() > 0.03 else "0" + str(v))
+            if rng.random() < 0.25:
+                parts.append(")")
+            if i + 1 < len(nums):
+                parts.append(toks[int(rng.integers(0, 4))] if rng.random() > 0.05 else toks[int(rng.integers(0, 8))])
+        expr = "".join(parts)
+        if rng.random() < 0.3:
+            expr = "(" + expr + ")" if rng.random() < 0.5 else expr + ")"
+        want_target = None
+        try:
+            want_target = eval(expr, {"__builtins__": None}, {})
+        except Exception:
+            pass
+        target = int(rng.integers(-50, 200))
+        if want_target is not None and isinstance(want_target, (int, float)) and rng.random() < 0.6 and abs(want_target) < 1e9 \
+                and float(want_target) == int(want_target):
+            target = int(want_target)
+        want = TE.countdown_reward(expr, nums, target)
+        r, u = _cd(hs, expr, nums, target)
+        got = {0: 0, 1: 0.1, 2: 1}[r]
+        if got != want:
+            assert u == 1, (expr, nums, target, got, want)
+            n_div += 1
+    assert n_div == 0
+    # outside the grammar: flagged, scored as an exception
+    for expr, nums, target in [("2**3", [2, 3], 8), ("7//2", [7, 2], 3), ("7%2", [7, 2], 1), ("1.5*2", [1, 5, 2], 3), ("1_0+2", [1, 0, 2], 12)]:
+        r, u = _cd(hs, expr, nums, target)
+        assert (r, u) == (1, 1), expr

@@ -1,0 +1,221 @@
+"""Torch-tensor front ends of the C-ABI entry points that are not environments: advantage pass, ContextManager
+tensor passes, response parsing, Countdown scoring.  Every function takes CUDA tensors, launches on the current
+stream of their device and returns CUDA tensors; nothing is computed on the host and there is no CPU fallback."""
+import numpy as np
+import torch
+
+from . import _lib
+
+_METHODS = {"identity": 0, "mean": 1, "mean_std": 2, "asym_clip": 3}
+
+
+def _ctx(t):
+    if not t.is_cuda:
+        raise _lib.RagenError("ragen_b200 ops need CUDA tensors (no CPU fallback)")
+    return _lib.Context.get(t.device.index or 0)
+
+
+def _u8(mask):
+    return mask if mask.dtype == torch.uint8 else mask.to(torch.uint8)
+
+
+def _f32(x):
+    return x.contiguous() if x.dtype == torch.float32 else x.float().contiguous()
+
+
+# ---- advantage ---------------------------------------------------------------------------------------------
+def gae_raw(rewards, values, mask, gamma, lam):
+    """Un-whitened GAE + masked moments.  Returns (adv, ret, moments[3] float64)."""
+    ctx = _ctx(rewards)
+    r, v, m = _f32(rewards), _f32(values), _u8(mask).contiguous()
+    B, T = r.shape
+    adv, ret = torch.empty_like(r), torch.empty_like(r)
+    mom = torch.empty(3, dtype=torch.float64, device=r.device)
+    _lib.check(ctx.lib.ragen_gae(ctx.handle, B, T, _lib.ptr(r), _lib.ptr(v), _lib.ptr(m), float(gamma), float(lam),
+                                 _lib.ptr(adv), _lib.ptr(ret), _lib.ptr(mom), ctx.stream()))
+    return adv, ret, mom
+
+
+def bilevel_gae_raw(rewards, values, loss_mask, gamma, lam, high_level_gamma):
+    ctx = _ctx(rewards)
+    r, v, m = _f32(rewards), _f32(values), _u8(loss_mask).contiguous()
+    B, T = r.shape
+    adv, ret = torch.empty_like(r), torch.empty_like(r)
+    mom = torch.empty(3, dtype=torch.float64, device=r.device)
+    _lib.check(ctx.lib.ragen_bilevel_gae(ctx.handle, B, T, _lib.ptr(r), _lib.ptr(v), _lib.ptr(m), float(gamma), float(lam),
+                                         float(high_level_gamma), _lib.ptr(adv), _lib.ptr(ret), _lib.ptr(mom), ctx.stream()))
+    return adv, ret, mom
+
+
+def masked_moments(x, mask):
+    ctx = _ctx(x)
+    x, m = _f32(x), _u8(mask).contiguous()
+    mom = torch.empty(3, dtype=torch.float64, device=x.device)
+    _lib.check(ctx.lib.ragen_masked_moments(ctx.handle, x.numel(), _lib.ptr(x), _lib.ptr(m), _lib.ptr(mom), ctx.stream()))
+    return mom
+
+
+def whiten_(x, moments, check=True):
+    """In-place masked_whiten from moments (torch_functional.py:139-151).  With check=True the two ValueErrors of
+    masked_var are raised (one 24-byte device->host read)."""
+    ctx = _ctx(x)
+    assert x.dtype == torch.float32 and x.is_contiguous()
+    if check:
+        n = float(moments[0])
+        if n == 0:
+            raise ValueError("At least one element in the mask has to be 1.")
+        if n == 1:
+            raise ValueError("The sum of the mask is one, which can cause a division by zero.")
+    _lib.check(ctx.lib.ragen_whiten(ctx.handle, x.numel(), _lib.ptr(x), _lib.ptr(moments), ctx.stream()))
+    return x
+
+
+def all_reduce_moments(moments, group=None):
+    """The only exchange of the advantage pass when rows are sharded over ranks: 24 bytes, NCCL all-reduce."""
+    import torch.distributed as dist
+
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(moments, group=group)
+    return moments
+
+
+def grpo_outcome(rewards, mask, group_index, n_groups, epsilon=1e-6, norm_by_std=True):
+    """group_index: int32 CUDA tensor [B] of dense group ids.  Returns (adv, scores)."""
+    ctx = _ctx(rewards)
+    r, m = _f32(rewards), _u8(mask).contiguous()
+    B, T = r.shape
+    g = group_index.to(torch.int32).contiguous()
+    scores = torch.empty(B, dtype=torch.float32, device=r.device)
+    adv = torch.empty_like(r)
+    _lib.check(ctx.lib.ragen_grpo_outcome(ctx.handle, B, T, _lib.ptr(r), _lib.ptr(m), _lib.ptr(g), int(n_groups), float(epsilon),
+                                          int(bool(norm_by_std)), _lib.ptr(scores), _lib.ptr(adv), ctx.stream()))
+    return adv, scores
+
+
+# ---- ContextManager tensor passes ----------------------------------------------------------------------------
+def masks_scores(input_ids, turn_scores, n_turns, im_start, im_end, use_turn_scores=False, enable_response_mask=True,
+                 roll_scores=True):
+    """input_ids int64 [B, L]; turn_scores float64 [B, K] (K may be 0), n_turns int32 [B].
+    Returns (score f32 [B, L-1], loss_mask u8 [B, L-1], response_mask u8 [B, L-1])."""
+    ctx = _ctx(input_ids)
+    ids = input_ids.contiguous()
+    B, L = ids.shape
+    K = int(turn_scores.shape[1]) if turn_scores is not None and turn_scores.numel() else 0
+    ts = turn_scores.to(torch.float64).contiguous() if K else None
+    nt = n_turns.to(torch.int32).contiguous()
+    dev = ids.device
+    lm = torch.empty((B, L - 1), dtype=torch.uint8, device=dev)
+    rm = torch.empty((B, L - 1), dtype=torch.uint8, device=dev)
+    sc = torch.empty((B, L - 1), dtype=torch.float32, device=dev)
+    _lib.check(ctx.lib.ragen_masks_scores(ctx.handle, B, L, _lib.ptr(ids), int(im_start), int(im_end), int(bool(use_turn_scores)),
+                                          int(bool(enable_response_mask)), int(bool(roll_scores)), _lib.ptr(ts), _lib.ptr(nt), K,
+                                          _lib.ptr(lm), _lib.ptr(rm), _lib.ptr(sc), ctx.stream()))
+    return sc, lm, rm
+
+
+def group_norm(score_last, penalty, group_index, n_groups, method):
+    ctx = _ctx(score_last)
+    s = _f32(score_last)
+    p = _f32(penalty) if penalty is not None else None
+    g = group_index.to(torch.int32).contiguous()
+    out = torch.empty_like(s)
+    _lib.check(ctx.lib.ragen_group_norm(ctx.handle, s.numel(), _lib.ptr(s), _lib.ptr(p), _lib.ptr(g), int(n_groups),
+                                        _METHODS[method], _lib.ptr(out), ctx.stream()))
+    return out
+
+
+# ---- response parsing ------------------------------------------------------------------------------------------
+class ActionTables:
+    """Lookup tables of `config.action_lookup` dicts ({action_id: name}) laid out for ragen_parse_actions."""
+
+    def __init__(self, lookups, device):
+        names, off, codes, first = bytearray(), [0], [], [0]
+        for lk in lookups:
+            for code, name in lk.items():  # dict order: a later duplicate name wins on the device too
+                b = name.encode()
+                names += b
+                off.append(len(names))
+                codes.append(int(code))
+            first.append(len(codes))
+        self.n_tables = len(lookups)
+        self.names = torch.tensor(list(names) or [0], dtype=torch.uint8, device=device)
+        self.name_off = torch.tensor(off, dtype=torch.int32, device=device)
+        self.codes = torch.tensor(codes or [0], dtype=torch.uint8, device=device)
+        self.first = torch.tensor(first, dtype=torch.int32, device=device)
+
+
+class ParseResult:
+    """Device tensors written by ragen_parse_actions + host views built lazily."""
+
+    def __init__(self, raw, offsets_np, scratch, flags, spans, act_spans, n_parsed, n_total, codes, n_valid, enable_think, sep):
+        self.raw, self.offsets_np, self.scratch = raw, offsets_np, scratch
+        self.flags, self.spans, self.act_spans = flags, spans, act_spans
+        self.n_parsed, self.n_total, self.codes, self.n_valid = n_parsed, n_total, codes, n_valid
+        self.enable_think, self.sep = enable_think, sep
+
+    def to_host(self):
+        """[(llm_response, actions, codes)] per response (ctx_manager.py:148-173, es_manager.py:230-240)."""
+        from .llm_agent.parse_host import assemble_response
+
+        fl = self.flags.cpu().numpy()
+        sp = self.spans.cpu().numpy()
+        asp = self.act_spans.cpu().numpy()
+        kept = self.n_parsed.cpu().numpy()
+        codes = self.codes.cpu().numpy()
+        nv = self.n_valid.cpu().numpy()
+        need_scratch = bool((fl & 6).any())
+        scr = self.scratch.cpu().numpy().tobytes() if need_scratch else b""
+        out = []
+        for i in range(len(fl)):
+            a, b = int(self.offsets_np[i]), int(self.offsets_np[i + 1])
+            resp, actions = assemble_response(self.raw[a:b], scr[a:b] if need_scratch else b"", int(fl[i]), sp[i], asp[i],
+                                              int(kept[i]), self.enable_think, self.sep)
+            out.append((resp, actions, codes[i, :nv[i]].tolist()))
+        return out
+
+
+def parse_actions(responses, tables=None, table_id=None, enable_think=True, action_sep="||", max_actions=5, device=0):
+    """responses: list[str].  tables: ActionTables or None; table_id: int32 CUDA tensor [n] / list / None."""
+    dev = torch.device("cuda", int(device)) if not isinstance(device, torch.device) else device
+    ctx = _lib.Context.get(dev.index or 0)
+    enc = [r.encode() for r in responses]
+    n = len(enc)
+    raw = b"".join(enc)
+    offsets_np = np.zeros(n + 1, dtype=np.int64)
+    np.cumsum([len(e) for e in enc], out=offsets_np[1:])
+    text = torch.frombuffer(bytearray(raw or b"\0"), dtype=torch.uint8).to(dev)
+    offsets = torch.from_numpy(offsets_np).to(dev)
+    scratch = torch.empty_like(text)
+    flags = torch.empty(n, dtype=torch.uint8, device=dev)
+    spans = torch.empty((n, 4), dtype=torch.int32, device=dev)
+    act_spans = torch.empty((n, max_actions, 2), dtype=torch.int32, device=dev)
+    n_parsed = torch.empty(n, dtype=torch.uint8, device=dev)
+    n_total = torch.empty(n, dtype=torch.int32, device=dev)
+    codes = torch.empty((n, max_actions), dtype=torch.uint8, device=dev)
+    n_valid = torch.empty(n, dtype=torch.uint8, device=dev)
+    tid = None
+    if table_id is not None:
+        tid = torch.as_tensor(table_id, dtype=torch.int32).to(dev).contiguous()
+    t = tables
+    _lib.check(ctx.lib.ragen_parse_actions(
+        ctx.handle, n, _lib.ptr(text), _lib.ptr(offsets), int(bool(enable_think)), action_sep.encode(), int(max_actions),
+        _lib.ptr(t.names) if t else None, _lib.ptr(t.name_off) if t else None, _lib.ptr(t.codes) if t else None,
+        _lib.ptr(t.first) if t else None, t.n_tables if t else 0, _lib.ptr(tid), _lib.ptr(scratch), _lib.ptr(flags),
+        _lib.ptr(spans), _lib.ptr(act_spans), _lib.ptr(n_parsed), _lib.ptr(n_total), _lib.ptr(codes), _lib.ptr(n_valid),
+        ctx.stream()))
+    res = ParseResult(raw, offsets_np, scratch, flags, spans, act_spans, n_parsed, n_total, codes, n_valid, enable_think, action_sep)
+    res.text, res.offsets = text, offsets
+    return res
+
+
+def countdown_score(text, start, length, nums, n_nums, target):
+    """text uint8 CUDA blob; start int64 [n], length int32 [n]; nums int32 [n, 8]; n_nums int32 [n]; target int64 [n].
+    Returns (result u8 [n] in {0, 1, 2}, unsupported u8 [n])."""
+    ctx = _ctx(text)
+    n = start.numel()
+    res = torch.empty(n, dtype=torch.uint8, device=text.device)
+    uns = torch.empty(n, dtype=torch.uint8, device=text.device)
+    _lib.check(ctx.lib.ragen_countdown_score(ctx.handle, n, _lib.ptr(text), _lib.ptr(start.contiguous()), _lib.ptr(length.contiguous()),
+                                             _lib.ptr(nums.contiguous()), _lib.ptr(n_nums.contiguous()), _lib.ptr(target.contiguous()),
+                                             _lib.ptr(res), _lib.ptr(uns), ctx.stream()))
+    return res, uns

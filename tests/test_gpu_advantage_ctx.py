@@ -1,0 +1,195 @@
+"""GPU parity: advantage kernels (GAE, bi-level GAE, GRPO, whitening) and ContextManager tensor passes (masks /
+scores, group normalisation) against the reference-made golden fixtures and the torch oracle.
+
+Tolerances (north_star: 1e-5 relative in fp32): raw GAE / bi-level advantages and returns are compared BIT-EXACT (the
+kernel keeps the reference's fp32 operation order); whitened / normalised values within 1e-5 of the tensor's scale."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import golden_json, golden_npz
+from oracle import advantage as A
+from oracle import managers as M
+
+pytestmark = pytest.mark.gpu
+RTOL = 1e-5
+
+
+def close(got, want, scale=None):
+    got, want = got.detach().cpu().double(), torch.as_tensor(want).double()
+    s = max(1.0, float(want.abs().max())) if scale is None else scale
+    err = float((got - want).abs().max())
+    assert err <= RTOL * s, (err, s)
+
+
+def dev(x, dtype=None):
+    t = torch.as_tensor(np.asarray(x))
+    return (t.to(dtype) if dtype else t).cuda()
+
+
+def test_gae_and_bilevel_golden():
+    from ragen_b200 import ops
+
+    g = golden_npz("advantage.npz")
+    r, v, m = dev(g["rewards"]), dev(g["values"]), dev(g["mask"])
+    for tag in ("a", "b"):
+        gamma, lam, hg = (float(x) for x in g[f"cfg_{tag}"])
+        adv, ret, mom = ops.gae_raw(r, v, m, gamma, lam)
+        raw_adv, raw_ret = A.gae_raw(torch.tensor(g["rewards"]), torch.tensor(g["values"]), gamma, lam)
+        assert torch.equal(adv.cpu(), raw_adv) and torch.equal(ret.cpu(), raw_ret)  # bit-exact before whitening
+        assert torch.equal(ret.cpu(), torch.tensor(g[f"gae_{tag}_ret"]))
+        ops.whiten_(adv, mom)
+        close(adv, g[f"gae_{tag}_adv"])
+        adv, ret, mom = ops.bilevel_gae_raw(r, v, m, gamma, lam, hg)
+        raw_adv, raw_ret = A.bilevel_gae_raw(torch.tensor(g["rewards"]), torch.tensor(g["values"]), torch.tensor(g["mask"]), gamma, lam, hg)
+        assert torch.equal(adv.cpu(), raw_adv) and torch.equal(ret.cpu(), raw_ret)
+        assert torch.equal(ret.cpu(), torch.tensor(g[f"bi_{tag}_ret"]))
+        ops.whiten_(adv, mom)
+        close(adv, g[f"bi_{tag}_adv"])
+    # the reference's own print-only example (ragen/trainer/core_algos.py:96-102)
+    r1 = dev([[0, 0, 0, 0, 1, 0, 0, 0, 0, 1]], torch.float32)
+    v1 = dev([[0.1, 0.2, 0.3, 0.4, 0.5, 0.6, 0.7, 0.8, 0.9, 1.0]], torch.float32)
+    m1 = torch.ones(1, 10, device="cuda")
+    adv, ret, mom = ops.bilevel_gae_raw(r1, v1, m1, 1, 1, 0.95)
+    assert torch.equal(ret.cpu(), torch.tensor(g["example_bi_ret"]))
+    close(ops.whiten_(adv, mom), g["example_bi_adv"])
+    adv, ret, mom = ops.gae_raw(r1, v1, m1, 1, 1)
+    assert torch.equal(ret.cpu(), torch.tensor(g["example_gae_ret"]))
+    close(ops.whiten_(adv, mom), g["example_gae_adv"])
+
+
+@pytest.mark.parametrize("B,T", [(128, 2047), (5, 1), (3, 1025), (33, 3000)])
+def test_gae_bilevel_c5_shape_against_oracle(B, T):
+    from ragen_b200 import ops
+
+    gen = torch.Generator().manual_seed(B * 7 + T)
+    mask = torch.zeros(B, T)
+    rewards = torch.zeros(B, T)
+    for b in range(B):
+        t = int(torch.randint(0, max(1, T // 8), (1,), generator=gen))
+        while t < T:
+            ln = int(torch.randint(1, 40, (1,), generator=gen))
+            e = min(T, t + ln)
+            mask[b, t:e] = 1
+            rewards[b, e - 1] = float(torch.randint(-3, 12, (1,), generator=gen)) * 0.1 + 0.05
+            t = e + int(torch.randint(1, 60, (1,), generator=gen))
+    values = torch.randn(B, T, generator=gen) * mask
+    for gamma, lam, hg in [(1.0, 1.0, 0.95), (0.99, 0.95, 0.9)]:
+        adv, ret, mom = ops.gae_raw(rewards.cuda(), values.cuda(), mask.cuda(), gamma, lam)
+        wa, wr = A.gae_raw(rewards, values, gamma, lam)
+        assert torch.equal(adv.cpu(), wa) and torch.equal(ret.cpu(), wr)
+        if mask.sum() > 1:
+            close(ops.whiten_(adv, mom), A.masked_whiten(wa, mask))
+        adv, ret, mom = ops.bilevel_gae_raw(rewards.cuda(), values.cuda(), mask.cuda(), gamma, lam, hg)
+        if B <= 33:  # the oracle's Python loops are slow
+            wa, wr = A.bilevel_gae_raw(rewards, values, mask, gamma, lam, hg)
+            assert torch.equal(adv.cpu(), wa) and torch.equal(ret.cpu(), wr)
+            if mask.sum() > 1:
+                close(ops.whiten_(adv, mom), A.masked_whiten(wa, mask))
+    mom = ops.masked_moments(values.cuda(), mask.cuda()).cpu()
+    close(mom, torch.stack([mask.sum(), (values * mask).sum(), (values * values * mask).sum()]).double(), scale=float(mask.sum()) + 1)
+
+
+def test_whiten_raises_like_reference():
+    from ragen_b200 import ops
+
+    x = torch.randn(2, 8, device="cuda")
+    m = torch.zeros(2, 8, device="cuda")
+    with pytest.raises(ValueError):
+        ops.whiten_(x.clone(), ops.masked_moments(x, m))
+    m[0, 3] = 1
+    with pytest.raises(ValueError):
+        ops.whiten_(x.clone(), ops.masked_moments(x, m))
+
+
+def test_grpo_golden_and_random():
+    from ragen_b200 import ops
+
+    g = golden_npz("advantage.npz")
+    uid = [str(u) for u in g["uid"]]
+    ids = {u: i for i, u in enumerate(dict.fromkeys(uid))}
+    gi = dev([ids[u] for u in uid], torch.int32)
+    for key, by_std in (("grpo_std_adv", True), ("grpo_mean_adv", False)):
+        adv, scores = ops.grpo_outcome(dev(g["outcome"]), dev(g["mask"]), gi, len(ids), 1e-6, by_std)
+        close(adv, g[key])
+    gen = torch.Generator().manual_seed(1)
+    B, T = 128, 300
+    rewards = torch.zeros(B, T)
+    rewards[torch.arange(B), torch.randint(0, T, (B,), generator=gen)] = torch.randn(B, generator=gen)
+    mask = (torch.rand(B, T, generator=gen) > 0.4).float()
+    index = [i // 16 for i in range(B)]
+    adv, _ = ops.grpo_outcome(rewards.cuda(), mask.cuda(), dev(index, torch.int32), 8)
+    want, _ = A.grpo_outcome(rewards, mask, index)
+    close(adv, want)
+
+
+def test_masks_scores_golden():
+    from ragen_b200 import ops
+
+    ms = golden_json("ctx.json")["masks_scores"]
+    ids = dev(ms["ids"], torch.int64)
+    scores = ms["scores"]
+    K = max(len(s) for s in scores)
+    ts = np.zeros((len(scores), K))
+    for i, s in enumerate(scores):
+        ts[i, :len(s)] = s
+    nt = dev([len(s) for s in scores], torch.int32)
+    for uts in (0, 1):
+        for erm in (1, 0):
+            sc, lm, rm = ops.masks_scores(ids, dev(ts), nt, 151644, 151645, bool(uts), bool(erm), True)
+            assert np.array_equal(lm.cpu().numpy(), np.array(ms[f"loss_{uts}{erm}"])), (uts, erm)
+            assert np.array_equal(rm.cpu().numpy(), np.array(ms[f"resp_{uts}{erm}"])), (uts, erm)
+            assert np.array_equal(sc.cpu().numpy(), np.array(ms[f"score_{uts}{erm}"], dtype=np.float32)), (uts, erm)
+
+
+def test_masks_scores_c5_shape_against_oracle():
+    from ragen_b200 import ops
+
+    rng = np.random.default_rng(5)
+    B, L, IMS, IME, PAD = 128, 2048, 151644, 151645, 151643
+    ids = np.full((B, L), PAD, dtype=np.int64)
+    scores = []
+    for b in range(B):
+        seq = [IMS] + list(rng.integers(0, 1000, 30)) + [IME, 198]
+        sc = []
+        for k in range(int(rng.integers(1, 6))):
+            seq += [IMS] + list(rng.integers(0, 1000, int(rng.integers(20, 200)))) + [IME, 198]
+            seq += [IMS] + list(rng.integers(0, 1000, int(rng.integers(5, 150))))
+            if rng.random() > 0.1:
+                seq += [IME, 198]  # sometimes the assistant turn is cut before <|im_end|>
+            sc.append(float(rng.choice([-0.1, -0.2, 0.9, 10.9, 0.0])))
+        seq = seq[-L:]
+        ids[b, L - len(seq):] = seq
+        scores.append(sc)
+    K = max(len(s) for s in scores)
+    ts = np.zeros((B, K))
+    for i, s in enumerate(scores):
+        ts[i, :len(s)] = s
+    nt = dev([len(s) for s in scores], torch.int32)
+    for uts in (False, True):
+        for erm in (True, False):
+            for roll in (True, False):
+                sc, lm, rm = ops.masks_scores(dev(ids), dev(ts), nt, IMS, IME, uts, erm, roll)
+                ws, wl, wr = M.masks_and_scores(torch.tensor(ids), scores, IMS, IME, uts, erm, roll)
+                assert torch.equal(lm.cpu().bool(), wl) and torch.equal(rm.cpu().bool(), wr)
+                assert torch.equal(sc.cpu(), ws), (uts, erm, roll)
+
+
+def test_group_norm_golden_and_oracle():
+    from ragen_b200 import ops
+
+    norm = golden_json("ctx.json")["normalize"]
+    last, pen = dev(norm["last"], torch.float32), dev(norm["penalty"], torch.float32)
+    B = last.numel()
+    keys = {"state": [i // 4 for i in range(B)], "inductive": [0 if i < 8 else 1 for i in range(B)], "batch": [0] * B}
+    for grouping, gk in keys.items():
+        for method in ("identity", "mean", "mean_std", "asym_clip"):
+            out = ops.group_norm(last, pen, dev(gk, torch.int32), len(set(gk)), method)
+            close(out, norm[f"{grouping}/{method}"])
+    # as many groups as rows: only the penalty is applied; groups of one inside a larger batch
+    out = ops.group_norm(last, pen, dev(list(range(B)), torch.int32), B, "mean_std")
+    close(out, (last + pen).cpu())
+    gk = [0, 0, 0, 1] + [2] * (B - 4)
+    for method in ("mean", "mean_std", "asym_clip"):
+        out = ops.group_norm(last, pen, dev(gk, torch.int32), 3, method)
+        close(out, M.normalize_scores(last.cpu(), pen.cpu(), gk, method))

@@ -219,3 +219,16 @@ def countdown_score(text, start, length, nums, n_nums, target):
                                              _lib.ptr(nums.contiguous()), _lib.ptr(n_nums.contiguous()), _lib.ptr(target.contiguous()),
                                              _lib.ptr(res), _lib.ptr(uns), ctx.stream()))
     return res, uns
+
+
+def countdown_score_parsed(res, rows, nums, n_nums, target):
+    """Scores the first parsed action of rows `rows` (int64 CUDA tensor) of a ParseResult.  The action bytes live in the
+    response blob, or in the scratch blob for the rows whose answer had to be cleaned (flag bit 2)."""
+    start = res.offsets[rows] + res.act_spans[rows, 0, 0].long()
+    length = torch.where(res.n_parsed[rows] > 0, res.act_spans[rows, 0, 1], torch.zeros_like(res.act_spans[rows, 0, 1]))
+    out, uns = countdown_score(res.text, start, length, nums, n_nums, target)
+    in_scratch = (res.flags[rows] & 4) != 0
+    if bool(in_scratch.any()):
+        out2, uns2 = countdown_score(res.scratch, start, length, nums, n_nums, target)
+        out, uns = torch.where(in_scratch, out2, out), torch.where(in_scratch, uns2, uns)
+    return out, uns

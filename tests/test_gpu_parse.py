@@ -84,12 +84,9 @@ def test_c3_corpus_bandit_countdown():
     # Countdown scoring of the first parsed action of each Countdown response, spans taken on the device
     cd = np.flatnonzero(c["kind"] == 1)
     idx = torch.from_numpy(cd).cuda()
-    in_scratch = (res.flags[idx] & 4) != 0
-    assert not bool(in_scratch.any())  # this corpus never needs the cleaned copy for the answer
-    start = res.offsets[idx] + res.act_spans[idx, 0, 0].long()
-    length = torch.where(res.n_parsed[idx] > 0, res.act_spans[idx, 0, 1], torch.zeros_like(res.act_spans[idx, 0, 1]))
-    out, uns = ops.countdown_score(res.text, start, length, torch.from_numpy(c["nums"][cd]).cuda(), torch.from_numpy(c["n_nums"][cd]).cuda(),
-                                   torch.from_numpy(c["target"][cd]).cuda())
+    assert bool(((res.flags[idx] & 4) != 0).any())  # the nested-tag shape needs the cleaned copy of the answer
+    out, uns = ops.countdown_score_parsed(res, idx, torch.from_numpy(c["nums"][cd]).cuda(), torch.from_numpy(c["n_nums"][cd]).cuda(),
+                                          torch.from_numpy(c["target"][cd]).cuda())
     out, uns = out.cpu().numpy(), uns.cpu().numpy()
     vals = {0: 0, 1: 0.1, 2: 1}
     hist = {0: 0, 1: 0, 2: 0}

@@ -6,6 +6,8 @@
 
 #include "../../ragen_b200/csrc/np_random.cuh"
 #include "../../ragen_b200/csrc/parse_logic.cuh"
+#include "../../ragen_b200/csrc/sokoban_gen_logic.cuh"
+#include <stdlib.h>
 #include "../../ragen_b200/csrc/toy_logic.cuh"
 
 extern "C" {
@@ -138,6 +140,51 @@ int hs_countdown(const uint8_t* s, int n, const int32_t* nums, int n_nums, long 
   const int r = parse::countdown_score(s, n, nums, n_nums, target, u);
   *unsupported = u ? 1 : 0;
   return r;
+}
+
+// ---- MT19937 streams ---------------------------------------------------------------------------------------------
+// out_f[0..k): random.random(); out_u[0..k): random._randbelow(n); out_np[0..k): np.random.randint(n) after seed(seed)
+void hs_mt(uint64_t seed, uint32_t n, int k, double* out_f, uint32_t* out_u, uint32_t* out_np) {
+  uint32_t a[mt::N], b[mt::N];
+  mt::State py{a, 0}, np{b, 0};
+  mt::seed_python(py, seed);
+  mt::seed_numpy(np, (uint32_t)seed);
+  for (int i = 0; i < k; ++i) out_f[i] = mt::py_random(py);
+  for (int i = 0; i < k; ++i) out_u[i] = mt::py_randbelow(py, n);
+  for (int i = 0; i < k; ++i) out_np[i] = mt::np_randint(np, n);
+}
+
+// ---- Sokoban generator -------------------------------------------------------------------------------------------
+int hs_sokoban_generate(int H, int W, int nb, int search_depth, int num_gen_steps, uint64_t seed, int force_hash,
+                        uint8_t* fixed, uint8_t* state, int* explored) {
+  sgen::Geometry g{H, W, nb, 0};
+  int cells = (H - 2) * (W - 2);
+  while ((1 << g.cell_bits) < cells) ++g.cell_bits;
+  uint32_t mt_py[mt::N], mt_np[mt::N];
+  sgen::Work w;
+  w.mt_py = mt_py;
+  w.mt_np = mt_np;
+  w.stack = (sgen::Frame*)malloc(sizeof(sgen::Frame) * (size_t)(search_depth + 1));
+  w.scratch = (uint8_t*)malloc((size_t)2 * H * W);
+  const int kb = sgen::key_bits(g);
+  if (kb <= 26 && !force_hash) {
+    w.vis.mode = 0;
+    w.vis_words = ((uint64_t)1 << kb) / 32 + 1;
+    w.vis.mem = (uint32_t*)malloc(w.vis_words * 4);
+    w.vis.mem64 = nullptr;
+  } else {
+    w.vis.mode = 1;
+    w.vis_words = (uint64_t)1 << 20;
+    w.vis.mask = (uint32_t)(w.vis_words - 1);
+    w.vis.mem64 = (uint64_t*)malloc(w.vis_words * 8);
+    w.vis.mem = nullptr;
+  }
+  const int st = sgen::generate_room(g, search_depth, num_gen_steps, seed, w, fixed, state, explored);
+  free(w.stack);
+  free(w.scratch);
+  free(w.vis.mem);
+  free(w.vis.mem64);
+  return st;
 }
 
 }  // extern "C"

@@ -21,9 +21,9 @@ c = ctypes
 @pytest.fixture(scope="session")
 def hs():
     src = os.path.join(HS_DIR, "hostsim.cpp")
-    deps = [src] + [os.path.join(ROOT, "ragen_b200", "csrc", f) for f in ("np_random.cuh", "parse_logic.cuh", "toy_logic.cuh")]
+    deps = [src] + [os.path.join(ROOT, "ragen_b200", "csrc", f) for f in ("np_random.cuh", "parse_logic.cuh", "toy_logic.cuh", "mt19937.cuh", "sokoban_gen_logic.cuh")]
     if not os.path.exists(HS_SO) or any(os.path.getmtime(d) > os.path.getmtime(HS_SO) for d in deps):
-        subprocess.run(["g++", "-std=c++17", "-O1", "-shared", "-fPIC", "-o", HS_SO, src], check=True)
+        subprocess.run(["g++", "-std=c++17", "-O2", "-shared", "-fPIC", "-o", HS_SO, src], check=True)
     lib = c.CDLL(HS_SO)
     lib.hs_countdown.restype = c.c_int
     lib.hs_countdown.argtypes = [c.c_char_p, c.c_int, c.c_void_p, c.c_int, c.c_longlong, c.c_void_p]
@@ -35,6 +35,8 @@ def hs():
     lib.hs_bandit.argtypes = [c.c_uint64, c.c_int, c.c_double, c.c_void_p]
     lib.hs_parse.argtypes = [c.c_char_p, c.c_int, c.c_int, c.c_char_p, c.c_int, c.c_void_p, c.c_void_p, c.c_void_p, c.c_int,
                              c.c_int, c.c_void_p, c.c_void_p]
+    lib.hs_mt.argtypes = [c.c_uint64, c.c_uint32, c.c_int, c.c_void_p, c.c_void_p, c.c_void_p]
+    lib.hs_sokoban_generate.argtypes = [c.c_int] * 5 + [c.c_uint64, c.c_int, c.c_void_p, c.c_void_p, c.c_void_p]
     return lib
 
 
@@ -254,3 +256,50 @@ def test_countdown_fuzz_against_python_eval(hs):
     for expr, nums, target in [("2**3", [2, 3], 8), ("7//2", [7, 2], 3), ("7%2", [7, 2], 1), ("1.5*2", [1, 5, 2], 3), ("1_0+2", [1, 0, 2], 12)]:
         r, u = _cd(hs, expr, nums, target)
         assert (r, u) == (1, 1), expr
+
+
+def test_mt19937_streams_match_cpython_and_numpy(hs):
+    import random
+
+    py_state, np_state = random.getstate(), np.random.get_state()
+    try:
+        for seed in [0, 1, 123, 1010, 2 ** 31, 2 ** 32 - 1, 2 ** 32 + 5, 10 ** 6 + 17]:
+            for n in (4, 5, 9, 36, 100, 1000):
+                k = 700  # crosses the 624-word regeneration boundary
+                f = np.zeros(k); u = np.zeros(k, np.uint32); v = np.zeros(k, np.uint32)
+                hs.hs_mt(seed, n, k, P(f), P(u), P(v))
+                random.seed(seed)
+                assert f.tolist() == [random.random() for _ in range(k)]
+                assert u.tolist() == [random.randrange(n) for _ in range(k)]
+                if seed < 2 ** 32:
+                    np.random.seed(seed)
+                    assert v.tolist() == [int(np.random.randint(n)) for _ in range(k)]
+    finally:
+        random.setstate(py_state)
+        np.random.set_state(np_state)
+
+
+def _gen(hs, H, W, nb, depth, seed, force_hash=0):
+    fixed = np.zeros(H * W, np.uint8); state = np.zeros(H * W, np.uint8)
+    explored = c.c_int(0)
+    st = hs.hs_sokoban_generate(H, W, nb, depth, int(1.7 * (H + W)), int(seed), force_hash, P(fixed), P(state), c.byref(explored))
+    return st, fixed, state, explored.value
+
+
+@pytest.mark.parametrize("name", ["s6", "s6d30", "s8", "s6b3", "s7x9", "s10"])
+def test_sokoban_generator_reproduces_reference_rooms(hs, name):
+    """The generator logic the CUDA kernel runs yields, seed for seed, the rooms the unmodified reference generated
+    (tests/golden/sokoban_rooms.npz), including the seeds on which the reference raises."""
+    rooms = golden_npz("sokoban_rooms.npz")
+    H, W, nb, depth = (int(x) for x in rooms[f"{name}_cfg"])
+    seeds = rooms[f"{name}_seeds"]
+    if name == "s10":
+        seeds = seeds[:4]  # ~0.1-0.3 s each on the host
+    for j, seed in enumerate(seeds):
+        st, fixed, state, explored = _gen(hs, H, W, nb, depth, seed, force_hash=j % 2 if name != "s10" else 0)
+        if not rooms[f"{name}_ok"][j]:
+            assert st != 0, (name, seed)
+            continue
+        assert st == 0, (name, seed, st)
+        assert np.array_equal(fixed, rooms[f"{name}_fixed"][j]), (name, seed)
+        assert np.array_equal(state, rooms[f"{name}_state"][j]), (name, seed)

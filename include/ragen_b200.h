@@ -87,6 +87,20 @@ int ragen_sokoban_render(ragen_ctx* ctx, int64_t n, int H, int W, const uint8_t*
 int ragen_sokoban_adopt(ragen_ctx* ctx, int64_t n, int H, int W, int num_boxes, const uint8_t* state,
                         const uint8_t* fixed, int16_t* meta, int32_t* status, void* stream);
 
+/* SokobanEnv.reset(seed) -> generate_room (ragen/env/sokoban/env.py:28-42, ragen/env/sokoban/utils.py:221-278 with
+ * room_topology_generation :281-355, place_boxes_and_player :358-397, reverse_playing / depth_first_search /
+ * reverse_move :408-542, box_displacement_score :545-560, add_random_player_movement :152-213) for a batch of seeds.
+ * Stream-exact: seeds[i] seeds CPython's `random` and NumPy's legacy `np.random` exactly as all_seed(seed)
+ * (ragen/utils.py:7-18) does, and the search visits states in the reference's order, so fixed/state [n][H*W] are
+ * the room_fixed / room_state the reference builds for that seed.  num_gen_steps is gym_sokoban's
+ * int(1.7 * (H + W)).  status[i] = 0 ok, 1 "Not enough free spots" (RuntimeError in the reference), 2 "score == 0"
+ * after 4 tries (RuntimeWarning), 3 seed >= 2^32 (np.random.seed raises); on non-zero status the room is undefined
+ * and the caller re-seeds as SokobanEnv.reset does (env.py:40-42).  explored (may be NULL) [n] = states explored by
+ * the last search.  H*W <= 256, num_boxes <= 4.  Uses ctx-owned workspace (grown on first use). */
+int ragen_sokoban_generate(ragen_ctx* ctx, int64_t n, int H, int W, int num_boxes, int search_depth,
+                           int num_gen_steps, const uint64_t* seeds, uint8_t* fixed, uint8_t* state,
+                           int32_t* status, int32_t* explored, void* stream);
+
 /* ---- FrozenLake -------------------------------------------------------------------------- */
 /* Maps are row-major uint8[n][size*size] with tile codes 0 'S' 1 'F' 2 'H' 3 'G' (size 2..8).  Glyph rows are
  * uint8[n][size*(size+1)]: 0 player, 1 frozen (S is drawn as F), 2 hole, 3 goal, 4 player in hole, 5 player on

@@ -107,6 +107,61 @@ class SokobanBatch:
         self.state.copy_(s, non_blocking=False)
         self.adopt()
 
+    def generate(self, seeds):
+        """Rooms for `seeds` (one per seed, any count) on the device.  Returns (fixed u8 [k, H*W], state u8 [k, H*W],
+        status i32 [k], explored i32 [k]) CUDA tensors; status as in include/ragen_b200.h."""
+        s = torch.as_tensor(np.asarray(seeds, dtype=np.uint64).astype(np.int64)).to(self.device)
+        k, HW = s.numel(), self.H * self.W
+        fixed = torch.empty((k, HW), dtype=torch.uint8, device=self.device)
+        state = torch.empty((k, HW), dtype=torch.uint8, device=self.device)
+        status = torch.empty(k, dtype=torch.int32, device=self.device)
+        explored = torch.empty(k, dtype=torch.int32, device=self.device)
+        _lib.check(self.lib.ragen_sokoban_generate(
+            self.ctx.handle, k, self.H, self.W, self.num_boxes, self.search_depth, int(1.7 * (self.H + self.W)), _lib.ptr(s),
+            _lib.ptr(fixed), _lib.ptr(state), _lib.ptr(status), _lib.ptr(explored), self.ctx.stream()))
+        return fixed, state, status, explored
+
+    def reset(self, seeds, slots=None):
+        """SokobanEnv.reset for many envs (env.py:28-42): env slots[i] (default: all envs) gets the room of seeds[i].
+        Envs sharing a seed (every env of a group does, es_manager.py:80-82) share one generated room.  Seeds whose
+        generation fails are re-seeded exactly as the reference does (abs(hash(str(seed))) % 2**32, env.py:41).
+        Returns the list of seeds finally used per env."""
+        seeds = [int(x) for x in seeds]
+        slots = list(range(self.n)) if slots is None else [int(x) for x in slots]
+        assert len(seeds) == len(slots)
+        rooms = {}
+        todo = sorted(set(seeds))
+        alias = {}
+        while todo:
+            fixed, state, status, _ = self.generate(todo)
+            st = status.cpu().tolist()
+            nxt = []
+            for j, sd in enumerate(todo):
+                if st[j] == 0:
+                    rooms[sd] = (fixed[j], state[j])
+                else:
+                    alias[sd] = abs(hash(str(sd))) % (2 ** 32)
+                    if alias[sd] not in rooms and alias[sd] not in nxt:
+                        nxt.append(alias[sd])
+            todo = nxt
+
+        def resolve(sd):
+            while sd not in rooms:
+                sd = alias[sd]
+            return sd
+
+        used = [resolve(sd) for sd in seeds]
+        order = sorted(set(used))
+        pos = {sd: i for i, sd in enumerate(order)}
+        f_all = torch.stack([rooms[sd][0] for sd in order])
+        s_all = torch.stack([rooms[sd][1] for sd in order])
+        src = torch.tensor([pos[sd] for sd in used], dtype=torch.long, device=self.device)
+        dst = torch.tensor(slots, dtype=torch.long, device=self.device)
+        self.fixed[dst] = f_all[src]
+        self.state[dst] = s_all[src]
+        self.adopt()
+        return used
+
     def adopt(self, check=True):
         _lib.check(self.lib.ragen_sokoban_adopt(
             self.ctx.handle, self.n, self.H, self.W, self.num_boxes, _lib.ptr(self.state), _lib.ptr(self.fixed),
@@ -234,9 +289,9 @@ class SokobanEnv(BaseDiscreteActionEnv):
         return self.render()
 
     def reset(self, seed=None, mode=None):
-        if not hasattr(self.batch, "reset_slots"):
-            raise NotImplementedError("device room generator not built into this SokobanBatch")
-        self.batch.reset_slots([self.slot], [seed])
+        if seed is None:  # the reference then uses the process's unseeded global RNG state
+            seed = int(np.random.SeedSequence().entropy % (2 ** 32))
+        self.seed_used = self.batch.reset([seed], [self.slot])[0]
         return self.render()
 
     def step(self, action: int):

@@ -148,3 +148,58 @@ def test_adopt_rejects_rooms_the_generator_cannot_produce():
     with pytest.raises(ValueError):
         b.load_rooms(fixed, state)
     assert b.status.cpu().tolist() == [1, 2, 3, 0]
+
+
+@pytest.mark.parametrize("name", ["s6", "s6d30", "s8", "s6b3", "s7x9", "s10"])
+def test_generator_reproduces_reference_rooms(rooms, name):
+    """ragen_sokoban_generate: seed for seed the rooms the unmodified reference generated, failures included."""
+    H, W, nb, depth = (int(x) for x in rooms[f"{name}_cfg"])
+    seeds = rooms[f"{name}_seeds"]
+    from ragen_b200.env.sokoban import SokobanBatch
+
+    b = SokobanBatch(1, (H, W), nb, 100, search_depth=depth)
+    fixed, state, status, explored = b.generate(seeds)
+    torch.cuda.synchronize()
+    ok = rooms[f"{name}_ok"]
+    st = status.cpu().numpy()
+    assert np.array_equal(st == 0, ok)
+    assert np.array_equal(fixed.cpu().numpy()[ok], rooms[f"{name}_fixed"][ok])
+    assert np.array_equal(state.cpu().numpy()[ok], rooms[f"{name}_state"][ok])
+    assert int(explored.max()) <= 300000
+
+
+def test_batch_reset_group_seeds_and_env_reset(rooms):
+    """EnvStateManager-style reset: 8 groups x 16 envs, group g seeded with 123 + g (es_manager.py:80-95)."""
+    from ragen_b200.env.sokoban import SokobanBatch, SokobanEnv, SokobanEnvConfig
+
+    b = SokobanBatch(128, (6, 6), 1, 100)
+    seeds = [123 + i // 16 for i in range(128)]
+    used = b.reset(seeds)
+    assert used == seeds
+    idx = {int(s): j for j, s in enumerate(rooms["s6_seeds"])}
+    want_f = np.stack([rooms["s6_fixed"][idx[s]] for s in seeds])
+    want_s = np.stack([rooms["s6_state"][idx[s]] for s in seeds])
+    assert np.array_equal(b.fixed.cpu().numpy(), want_f) and np.array_equal(b.state.cpu().numpy(), want_s)
+    env = SokobanEnv(SokobanEnvConfig(dim_room=(6, 6), num_boxes=1))
+    ref = S.SokobanOracle((6, 6), 1, 100)
+    assert env.reset(seed=1010) == ref.reset(seed=1010)
+    for a in [1, 2, 3, 4, 4, 1]:
+        assert env.step(a) == ref.step(a)
+
+
+def test_generated_rooms_are_valid_and_solvable():
+    """Seeds the fixtures do not cover: every room passes the reference's validity rules and the BFS solver."""
+    from ragen_b200.env.sokoban import SokobanBatch
+
+    b = SokobanBatch(1, (6, 6), 1, 100)
+    seeds = np.arange(5000, 5000 + 2048)
+    fixed, state, status, explored = b.generate(seeds)
+    st = status.cpu().numpy()
+    assert (st == 0).mean() > 0.9
+    f, s = fixed.cpu().numpy(), state.cpu().numpy()
+    for j in np.flatnonzero(st == 0)[:300]:
+        S.check_room(f[j], s[j], 6, 6, 1)
+        assert S.solve_bfs(f[j], s[j], 6, 6), int(seeds[j])  # solvable (get_shortest_action_path contract)
+    for j in np.flatnonzero(st == 0)[:64]:
+        want_f, want_s = S.generate_room(6, 6, 1, 300, int(seeds[j]))
+        assert np.array_equal(f[j], want_f) and np.array_equal(s[j], want_s)

@@ -170,6 +170,9 @@ class BanditOracle:
         info = {"action_is_effective": True, "action_is_valid": True, "success": arm == self.hi}
         return self.obs, reward, True, info
 
+    def render(self):
+        return self.obs
+
 
 # ---------------------------------------------------------------------------------------------
 # Countdown scoring

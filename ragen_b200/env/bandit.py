@@ -68,9 +68,9 @@ class BanditBatch:
                                               self.ctx.stream()))
         return self.reward, self.flags
 
-    def lookup(self, slot):
+    def lookup(self, slot, lf=None):
         c, s = self.config, self.config.action_space_start
-        lf = bool(self.lo_first[slot])
+        lf = bool(self.lo_first[slot]) if lf is None else lf
         return {s: c.lo_arm_name if lf else c.hi_arm_name, s + 1: c.hi_arm_name if lf else c.lo_arm_name}
 
 
@@ -88,12 +88,11 @@ class BanditEnv(BaseDiscreteActionEnv):
             batch = BanditBatch(1, self.config, device=kwargs.get("device", 0))
             slot = 0
         self.batch, self.slot = batch, slot
-        self._act = torch.zeros(batch.n, dtype=torch.uint8, device=batch.device)
-        self._on = torch.zeros(batch.n, dtype=torch.uint8, device=batch.device)
+        self._act = self._on = None  # staging tensors of the single-env step path, made on first use
 
-    def adopt_reset(self):
+    def adopt_reset(self, lo_first=None):
         """Host bookkeeping after the batch was reset (arm order -> lookup dicts and the prompt)."""
-        self.ACTION_LOOKUP = self.batch.lookup(self.slot)
+        self.ACTION_LOOKUP = self.batch.lookup(self.slot, lo_first)
         self.config.action_lookup = self.ACTION_LOOKUP
         self.ARM_IDX_TO_NAME = self.ACTION_LOOKUP
         self.NAME_TO_ARM_IDX = {name: idx for idx, name in self.ACTION_LOOKUP.items()}
@@ -109,8 +108,15 @@ class BanditEnv(BaseDiscreteActionEnv):
         self.batch.reset([seed])
         return self.adopt_reset()
 
+    def _staging(self):
+        if self._act is None:
+            batch = self.batch
+            self._act = torch.zeros(batch.n, dtype=torch.uint8, device=batch.device)
+            self._on = torch.zeros(batch.n, dtype=torch.uint8, device=batch.device)
+
     def step(self, action: int):
         assert action in self.ACTION_LOOKUP, f"Invalid action: {action}"
+        self._staging()
         self._act.zero_()
         self._on.zero_()
         self._act[self.slot] = int(action)

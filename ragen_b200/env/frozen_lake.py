@@ -98,9 +98,8 @@ class FrozenLakeEnv(BaseDiscreteActionEnv):
             batch = FrozenLakeBatch(1, self.config.size, self.config.p, self.config.is_slippery, device=kwargs.get("device", 0))
             slot = 0
         self.batch, self.slot = batch, slot
+        self._act = self._na = None  # staging tensors of the single-env step path, made on first use
         self.ncol = self.nrow = batch.size
-        self._act = torch.zeros((batch.n, 1), dtype=torch.uint8, device=batch.device)
-        self._na = torch.zeros(batch.n, dtype=torch.uint8, device=batch.device)
 
     @property
     def s(self):
@@ -124,8 +123,15 @@ class FrozenLakeEnv(BaseDiscreteActionEnv):
         self.batch.reset([seed])
         return self.render()
 
+    def _staging(self):
+        if self._act is None:
+            batch = self.batch
+            self._act = torch.zeros((batch.n, 1), dtype=torch.uint8, device=batch.device)
+            self._na = torch.zeros(batch.n, dtype=torch.uint8, device=batch.device)
+
     def step(self, action: int):
         b = self.batch
+        self._staging()
         self._act.zero_()
         self._na.zero_()
         self._act[self.slot, 0] = int(self.action_map[action]) + 1

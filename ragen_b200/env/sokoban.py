@@ -175,6 +175,8 @@ class SokobanBatch:
         self.render()
 
     # -- step -------------------------------------------------------------------------------
+
+
     def step(self, actions, n_actions=None, render=True) -> StepOut:
         """actions: uint8 device tensor [n] or [n, K]; n_actions: optional uint8 [n]."""
         if actions.dim() == 1:
@@ -255,8 +257,7 @@ class SokobanEnv(BaseDiscreteActionEnv):
                                  device=kwargs.get("device", 0))
             slot = 0
         self.batch, self.slot = batch, slot
-        self._act = torch.zeros((batch.n, 1), dtype=torch.uint8, device=batch.device)
-        self._na = torch.zeros(batch.n, dtype=torch.uint8, device=batch.device)
+        self._act = self._na = None  # staging tensors of the single-env step path, made on first use
 
     # the reference exposes these as attributes; here they read the device state of the slot
     @property
@@ -294,8 +295,15 @@ class SokobanEnv(BaseDiscreteActionEnv):
         self.seed_used = self.batch.reset([seed], [self.slot])[0]
         return self.render()
 
+    def _staging(self):
+        if self._act is None:
+            batch = self.batch
+            self._act = torch.zeros((batch.n, 1), dtype=torch.uint8, device=batch.device)
+            self._na = torch.zeros(batch.n, dtype=torch.uint8, device=batch.device)
+
     def step(self, action: int):
         b = self.batch
+        self._staging()
         self._act.zero_()
         self._na.zero_()
         self._act[self.slot, 0] = int(action)

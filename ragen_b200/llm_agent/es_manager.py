@@ -1,0 +1,299 @@
+"""EnvStateManager with the reference's interface (ragen/llm_agent/es_manager.py:28-258), backed by device batches.
+
+Same constructor, `reset(seed)`, `step(all_env_inputs)`, `get_rollout_states()`, `render()`, `close()`; same
+`envs` entries and `rollout_cache` dict shapes, so ContextManager / LLMAgentProxy / the trainer use it unchanged.
+What differs is where the work runs: all envs of a tag live in ONE device batch and a manager call is one kernel
+launch per tag (reset = room/map generation, step = up to K actions per env + reward + done + render), followed by one
+device->host copy of the per-env results; the Python loop that remains only files those results into the history
+dicts the API exposes.
+"""
+from dataclasses import dataclass, field
+from typing import Dict, List, Optional
+
+import numpy as np
+import torch
+
+from ..env import BATCH_TYPES, REGISTERED_ENV_CONFIGS, REGISTERED_ENVS
+from ..env.frozen_lake import fl_glyph_table
+from ..env.sokoban import glyph_table
+
+
+@dataclass
+class EnvStatus:
+    """Status of an environment (es_manager.py:17-24)."""
+    truncated: bool = False
+    terminated: bool = False
+    num_actions: int = 0
+    rewards: List[float] = field(default_factory=list)
+    seed: Optional[int] = None
+
+
+def _translate_rows(codes: np.ndarray, table) -> List[str]:
+    """uint8 glyph rows [k, G] -> strings (last separator dropped); one C-level translate per row."""
+    tr = {i: g for i, g in enumerate(table)}
+    return [bytes(r[:-1]).decode("latin1").translate(tr) for r in codes]
+
+
+class _Block:
+    """All envs of one tag: a device batch + the entries that view it."""
+
+    def __init__(self, tag, env_type, batch, first, count):
+        self.tag, self.env_type, self.batch, self.first, self.count = tag, env_type, batch, first, count
+        self.K = 1
+        self.act = self.nact = None
+
+
+class EnvStateManager:
+    def __init__(self, config, mode: str = "train", device: int = 0):
+        self.sys_config = config
+        self.mode = mode
+        self.device = int(device)
+        self.config = getattr(self.sys_config.es_manager, mode)
+        self.env_groups = int(self.config.env_groups)
+        self.group_size = self.config.group_size
+        self._init_envs()
+        self.rollout_cache = None
+
+    # ---- construction (es_manager.py:42-73) -----------------------------------------------------------------
+    def _init_envs(self):
+        cfg = self.config
+        assert sum(cfg.env_configs.n_groups) == self.env_groups, \
+            f"Sum of n_groups must equal env_groups. Got sum({cfg.env_configs.n_groups}) != {self.env_groups}"
+        assert len(cfg.env_configs.tags) == len(cfg.env_configs.n_groups), \
+            f"Number of tags must equal number of n_groups. Got {len(cfg.env_configs.tags)} != {len(cfg.env_configs.n_groups)}"
+        self.envs, self.blocks = [], []
+        K = int(getattr(self.sys_config.agent_proxy, "max_actions_per_turn", 5))
+        done_groups = 0
+        for tag, n_group in zip(cfg.env_configs.tags, cfg.env_configs.n_groups):
+            tpl = self.sys_config.custom_envs[tag]
+            env_type = tpl.env_type
+            first, count = done_groups * self.group_size, n_group * self.group_size
+            make_cfg = (lambda: REGISTERED_ENV_CONFIGS[env_type]()) if tpl.env_config is None else \
+                (lambda: REGISTERED_ENV_CONFIGS[env_type](**tpl.env_config))
+            c0 = make_cfg()
+            if env_type == "sokoban":
+                batch = BATCH_TYPES[env_type](count, tuple(c0.dim_room), c0.num_boxes, c0.max_steps, c0.search_depth, device=self.device)
+            elif env_type == "frozen_lake":
+                batch = BATCH_TYPES[env_type](count, c0.size, c0.p, c0.is_slippery, device=self.device)
+            else:
+                batch = BATCH_TYPES[env_type](count, c0, device=self.device)
+            block = _Block(tag, env_type, batch, first, count)
+            block.K = max(K, 1)
+            extra = {}
+            if env_type == "countdown":
+                from ..env.countdown import load_problems
+                extra["data"] = load_problems(c0)
+            for i in range(count):
+                env_config = make_cfg()
+                env_obj = REGISTERED_ENVS[env_type](env_config, batch=batch, slot=i, **extra)
+                self.envs.append({"tag": tag, "group_id": (first + i) // self.group_size, "env_id": first + i, "env": env_obj,
+                                  "config": env_config, "status": EnvStatus(),
+                                  "max_actions_per_traj": tpl.max_actions_per_traj})
+            self.blocks.append(block)
+            done_groups += n_group
+        self._block_of = {}
+        for b in self.blocks:
+            for i in range(b.count):
+                self._block_of[b.first + i] = b
+
+    # ---- observations ----------------------------------------------------------------------------------------
+    def _block_texts(self, block) -> List[str]:
+        """Current observation text of every env of the block (one device->host copy for grid envs)."""
+        envs = self.envs[block.first:block.first + block.count]
+        if block.env_type == "sokoban":
+            return _translate_rows(block.batch.obs.cpu().numpy(), glyph_table(envs[0]["env"].GRID_LOOKUP))
+        if block.env_type == "frozen_lake":
+            return _translate_rows(block.batch.obs.cpu().numpy(), fl_glyph_table(envs[0]["env"].GRID_LOOKUP))
+        return [e["env"].render() for e in envs]
+
+    # ---- reset (es_manager.py:75-103) ------------------------------------------------------------------------
+    def reset(self, seed: Optional[int] = None):
+        import random
+
+        envs = self.envs
+        rollout_cache = [{"env_id": e["env_id"], "history": [], "group_id": e["group_id"], "tag": e["tag"], "penalty": 0}
+                         for e in envs]
+        if self.mode == "train":
+            seed = random.randint(0, 1000000) if seed is None else seed
+        else:
+            seed = 123
+        seeds = [seed + i // self.group_size for i in range(len(envs))]  # every env of a group shares the seed (:80-82)
+        for block in self.blocks:
+            bs = seeds[block.first:block.first + block.count]
+            entries = envs[block.first:block.first + block.count]
+            if block.env_type == "sokoban":
+                used = block.batch.reset(bs)  # one room per distinct seed, generated on the device
+                for e, u in zip(entries, used):
+                    e["env"].seed_used = u
+            elif block.env_type == "frozen_lake":
+                block.batch.reset(bs)
+                for e, s in zip(entries, bs):
+                    e["config"].map_seed = s
+            elif block.env_type == "bandit":
+                block.batch.reset(bs)
+                lo_first = block.batch.lo_first.cpu().numpy()
+                for e, lf in zip(entries, lo_first):
+                    e["env"].adopt_reset(bool(lf))
+            else:
+                for e, s in zip(entries, bs):
+                    e["env"].reset(seed=s, mode=self.mode)
+        for s, e in zip(seeds, envs):
+            e["status"] = EnvStatus(seed=s)
+        for block in self.blocks:
+            texts = self._block_texts(block)
+            for i, t in enumerate(texts):
+                cache, e = rollout_cache[block.first + i], envs[block.first + i]
+                cache["history"] = self._update_cache_history(cache["history"], next_state=t,
+                                                              actions_left=e["max_actions_per_traj"], num_actions_info=None)
+        self.rollout_cache = rollout_cache
+        return rollout_cache
+
+    # ---- step (es_manager.py:105-171) --------------------------------------------------------------------------
+    def step(self, all_env_inputs: List[Dict]):
+        envs = self.envs
+        # 1. valid actions per input (:230-240); ContextManager.get_env_inputs already mapped them on the device
+        plans = []
+        per_block = {}
+        for env_input in all_env_inputs:
+            entry = envs[env_input["env_id"]]
+            left = entry["max_actions_per_traj"] - entry["status"].num_actions
+            valid = self._extract_map_valid_actions(entry, env_input["actions"], env_input.get("action_codes"))
+            todo = valid[:left] if left > 0 else []
+            plans.append((env_input, entry, valid, todo))
+            per_block.setdefault(id(self._block_of[entry["env_id"]]), []).append(len(plans) - 1)
+        # 2. one launch per tag
+        results = {}
+        for block in self.blocks:
+            idxs = per_block.get(id(block))
+            if idxs:
+                self._run_block(block, [plans[i] for i in idxs], idxs, results)
+        # 3. file the results into status / history, in input order
+        env_outputs = []
+        texts = {id(b): self._block_texts(b) for b in self.blocks if id(b) in per_block}
+        for i, (env_input, entry, valid, todo) in enumerate(plans):
+            env_id = entry["env_id"]
+            block = self._block_of[env_id]
+            acc_reward, turn_info, turn_done, n_exec = results[i]
+            executed = todo[:n_exec]
+            if len(valid) != len(env_input["actions"]) or not valid:
+                self.rollout_cache[env_id]["penalty"] += self.sys_config.es_manager.format_penalty
+            status = entry["status"]
+            status.num_actions += len(executed)
+            status.rewards.append(acc_reward)
+            actions_left = entry["max_actions_per_traj"] - status.num_actions
+            if turn_done:
+                status.terminated = True
+                status.truncated = not turn_info.get("success", False)
+            history = self._update_cache_history(
+                self.rollout_cache[env_id]["history"], next_state=texts[id(block)][env_id - block.first], actions_left=actions_left,
+                num_actions_info={"actions": executed, "reward": acc_reward, "info": turn_info,
+                                  "llm_response": env_input["llm_response"], "llm_raw_response": env_input["llm_raw_response"]})
+            if status.num_actions >= entry["max_actions_per_traj"] and not turn_done:
+                status.truncated = True
+                status.terminated = True
+                turn_done = True
+            self.rollout_cache[env_id]["history"] = history
+            if not turn_done:
+                env_outputs.append(self.rollout_cache[env_id])
+        return env_outputs
+
+    def _run_block(self, block, plans, idxs, results):
+        """Executes the planned actions of one tag's envs with one launch and stores, per plan index,
+        (acc_reward, turn_info, turn_done, n_executed) - what _execute_actions returns (:116-128)."""
+        b, dev = block.batch, block.batch.device
+        if block.env_type in ("sokoban", "frozen_lake"):
+            K = max(block.K, max(len(p[3]) for p in plans), 1)
+            act = np.zeros((block.count, K), dtype=np.uint8)
+            nact = np.zeros(block.count, dtype=np.uint8)
+            for env_input, entry, valid, todo in plans:
+                s = entry["env_id"] - block.first
+                codes = [entry["env"].action_map[a] + 1 for a in todo] if block.env_type == "frozen_lake" else todo
+                act[s, :len(codes)] = codes
+                nact[s] = len(codes)
+            out = b.step(torch.from_numpy(act).to(dev), torch.from_numpy(nact).to(dev))
+            host = torch.stack([out.done, out.flags, out.n_executed]).cpu().numpy()
+            rew = out.reward.cpu().numpy()
+            for i, (env_input, entry, valid, todo) in zip(idxs, plans):
+                s = entry["env_id"] - block.first
+                n_exec, fl = int(host[2, s]), int(host[1, s])
+                info = {"action_is_effective": bool(fl & 1), "action_is_valid": True, "success": bool(fl & 2)} if n_exec else {}
+                results[i] = (float(rew[s]) if n_exec else 0, info, bool(host[0, s]), n_exec)
+        elif block.env_type == "bandit":
+            act = np.zeros(block.count, dtype=np.uint8)
+            on = np.zeros(block.count, dtype=np.uint8)
+            for env_input, entry, valid, todo in plans:
+                if todo:
+                    s = entry["env_id"] - block.first
+                    assert todo[0] in entry["env"].ACTION_LOOKUP, f"Invalid action: {todo[0]}"
+                    act[s], on[s] = todo[0], 1
+            rew, fl = b.step(torch.from_numpy(act).to(dev), torch.from_numpy(on).to(dev))
+            rew, fl = rew.cpu().numpy(), fl.cpu().numpy()
+            for i, (env_input, entry, valid, todo) in zip(idxs, plans):
+                s = entry["env_id"] - block.first
+                if todo:
+                    _, r, done, info = entry["env"].finish_step(todo[0], float(rew[s]), int(fl[s]))
+                    results[i] = (0 + r, info, done, 1)
+                else:
+                    results[i] = (0, {}, False, 0)
+        else:  # countdown: actions are free text, the first one ends the episode
+            todo_plans = [(i, p) for i, p in zip(idxs, plans) if p[3]]
+            if todo_plans:
+                gts = [p[1]["env"].data[p[1]["env"].index] for _, p in todo_plans]
+                res, _ = b.score([p[3][0] for _, p in todo_plans], [list(g["nums"]) for g in gts], [g["target"] for g in gts])
+                for (i, p), r in zip(todo_plans, res):
+                    env = p[1]["env"]
+                    _, reward, done, info = env.finish_step(env.reward_from_result(int(r)))
+                    results[i] = (0 + reward, info, done, 1)
+            for i, p in zip(idxs, plans):
+                if not p[3]:
+                    results[i] = (0, {}, False, 0)
+
+    def _extract_map_valid_actions(self, entry: Dict, actions: List[str], codes=None):
+        """es_manager.py:230-240.  `codes` are the ids ragen_parse_actions already produced for these actions (set by
+        ContextManager.get_env_inputs); inputs built elsewhere are mapped here with the same rule."""
+        action_lookup = getattr(entry["env"].config, "action_lookup", None)
+        if action_lookup is None:
+            return actions
+        if codes is not None:
+            return list(codes)
+        rev = {v.lower(): k for k, v in action_lookup.items()}
+        return [rev[a.lower()] for a in actions if a.lower() in rev]
+
+    # ---- final states (es_manager.py:173-207) --------------------------------------------------------------------
+    def get_rollout_states(self):
+        TURN_LVL_METRICS = ["action_is_effective", "action_is_valid", "end_of_page"]
+        for entry, cache in zip(self.envs, self.rollout_cache):
+            status = entry["status"]
+            env_metric = {"success": float(status.terminated and (not status.truncated)), "num_actions": status.num_actions}
+            custom_metric = {}
+            for turn in cache["history"]:
+                for k, v in turn.get("info", {}).items():
+                    if k == "success":
+                        continue
+                    custom_metric.setdefault(k, []).append(float(v))
+            for k, v in custom_metric.items():
+                if "Webshop" not in k or ("Webshop" in k and k in TURN_LVL_METRICS):
+                    env_metric[k] = np.sum(v) / (len(cache["history"]) - 1)
+                else:
+                    env_metric[k] = np.sum(v)
+            cache["history"][-1]["metrics"] = custom_metric
+            cache["metrics"] = {f"{entry['tag']}/{k}": v for k, v in env_metric.items()}
+        return self.rollout_cache
+
+    def _update_cache_history(self, history: List[Dict], next_state, actions_left, num_actions_info: Optional[Dict] = None):
+        """es_manager.py:212-228 (text states only: image observations are out of this path's scope)."""
+        if num_actions_info is not None:
+            assert len(history), "History should not be empty"
+            history[-1].update(num_actions_info)
+        history.append({"state": next_state, "actions_left": actions_left})
+        return history
+
+    def render(self):
+        out = []
+        for block in self.blocks:
+            out.extend(self._block_texts(block))
+        return out
+
+    def close(self):
+        for entry in self.envs:
+            entry["env"].close()

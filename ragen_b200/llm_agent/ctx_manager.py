@@ -1,0 +1,265 @@
+"""ContextManager with the reference's interface (ragen/llm_agent/ctx_manager.py:74-356).
+
+Text assembly (chat messages, chat template, tokenizer) is the tokenizer's and stays on the host exactly as in the
+reference; the tensor passes run on the device through libragen_b200: response parsing + action lookup
+(ragen_parse_actions), loss / response masks and score placement (ragen_masks_scores), group reward normalisation
+(ragen_group_norm).  Outputs have the reference's DataProto layout (batch / non_tensor_batch / meta_info).
+"""
+from dataclasses import asdict
+from typing import Dict, List
+
+import numpy as np
+import torch
+
+from .. import ops
+from ..env import REGISTERED_ENV_CONFIGS
+
+try:  # the real container when verl is installed (ragen/llm_agent/ctx_manager.py:14)
+    from verl import DataProto  # type: ignore
+    from tensordict import TensorDict  # type: ignore
+except Exception:  # stand-in with the members this path touches (verl/verl/protocol.py:200)
+    class TensorDict(dict):
+        def __init__(self, source=None, batch_size=None):
+            super().__init__(source or {})
+            self.batch_size = batch_size
+
+    class DataProto:
+        def __init__(self, batch=None, non_tensor_batch=None, meta_info=None):
+            self.batch = batch
+            self.non_tensor_batch = non_tensor_batch if non_tensor_batch is not None else {}
+            self.meta_info = meta_info if meta_info is not None else {}
+
+
+def get_special_tokens(tokenizer):
+    """ctx_manager.py:24-33."""
+    name = tokenizer.name_or_path.lower()
+    if "qwen" in name:
+        return tokenizer.encode("<|im_start|>")[0], tokenizer.encode("<|im_end|>")[0]
+    if "llama-3" in name:
+        return 128006, 128009
+    raise ValueError(f"Unsupported model: {tokenizer.name_or_path}")
+
+
+def get_masks_and_scores(input_ids, tokenizer, all_scores=None, use_turn_scores=False, enable_response_mask=False, device=None):
+    """ctx_manager.py:35-70 on the device.  input_ids [B, L] (any device); all_scores: list of per-turn Python floats
+    per row.  Returns (score_tensor f32, loss_mask bool, response_mask bool), all [B, L-1], on input_ids' device."""
+    special_token, reward_token = get_special_tokens(tokenizer)
+    home = input_ids.device
+    dev = torch.device("cuda", torch.cuda.current_device()) if device is None else device
+    ids = input_ids.to(dev)
+    B = ids.shape[0]
+    K = max((len(s) for s in all_scores), default=0)
+    ts = np.zeros((B, max(K, 1)), dtype=np.float64)
+    for i, s in enumerate(all_scores):
+        ts[i, :len(s)] = s
+    nt = torch.tensor([len(s) for s in all_scores], dtype=torch.int32, device=dev)
+    sc, lm, rm = ops.masks_scores(ids, torch.from_numpy(ts).to(dev) if K else None, nt, special_token, reward_token,
+                                  use_turn_scores, enable_response_mask, "qwen" in tokenizer.name_or_path.lower())
+    return sc.to(home), lm.bool().to(home), rm.bool().to(home)
+
+
+class ContextManager:
+    def __init__(self, config, tokenizer, processor=None, mode: str = "train", device: int = 0):
+        self.config = config
+        self.tokenizer = tokenizer
+        self.processor = processor
+        self.device = torch.device("cuda", int(device))
+        self.action_sep = self.config.agent_proxy.action_sep
+        self.special_token_list = ["<think>", "</think>", "<answer>", "</answer>", "<|im_start|>", "<|im_end|>"]
+        self.es_cfg = self.config.es_manager[mode]
+        self.env_nums = {env_tag: n_group * self.es_cfg.group_size
+                         for n_group, env_tag in zip(self.es_cfg.env_configs.n_groups, self.es_cfg.env_configs.tags)}
+        self._init_prefix_lookup()
+        self._tables = None        # action lookup tables on the device, built from the envs at first use
+        self._env_table = None
+
+    def _check_env_installed(self, env_type: str):
+        if env_type not in REGISTERED_ENV_CONFIGS:
+            raise ValueError(f"Environment {env_type} is not installed. Please install it using the scripts/setup_{env_type}.sh script.")
+
+    def _init_prefix_lookup(self):
+        """ctx_manager.py:106-146."""
+        prefix_lookup, prefixes, env_config_lookup = {}, {}, {}
+        for env_tag, env_config in self.config.custom_envs.items():
+            if env_tag not in self.es_cfg.env_configs.tags:
+                continue
+            self._check_env_installed(env_config.env_type)
+            env_config_new = asdict(REGISTERED_ENV_CONFIGS[env_config.env_type]())
+            for k, v in env_config.items():
+                env_config_new[k] = v
+            env_instruction = env_config_new.get("env_instruction", "")
+            if env_config_new.get("grid_vocab", False):
+                env_instruction += "\nThe meaning of each symbol in the state is:\n" + \
+                    ", ".join([f"{k}: {v}" for k, v in env_config_new["grid_vocab"].items()])
+            if env_config_new.get("action_lookup", False):
+                s = "\nYour available actions are:\n" + ", ".join([f"{v}" for k, v in env_config_new["action_lookup"].items()])
+                s += f"\nYou can make up to {env_config_new['max_actions_per_traj']} actions, separated by the action separator \" " + \
+                    self.action_sep + " \"\n"
+                env_instruction += s
+            prefixes[env_tag] = env_instruction
+            env_config_lookup[env_tag] = {"max_tokens": env_config.get("max_tokens", self.config.actor_rollout_ref.rollout.response_length)}
+        cur_group = 0
+        group_size = self.es_cfg.group_size
+        for env_tag, n_group in zip(self.es_cfg.env_configs.tags, self.es_cfg.env_configs.n_groups):
+            for i in range(cur_group * group_size, (cur_group + n_group) * group_size):
+                prefix_lookup[i] = prefixes[env_tag]
+                env_config_lookup[i] = env_config_lookup[env_tag]
+            cur_group += n_group
+        self.prefix_lookup = prefix_lookup
+        self.env_config_lookup = env_config_lookup
+
+    # ---- response parsing (ctx_manager.py:148-173, 332-352) ------------------------------------------------------
+    def bind_envs(self, envs: List[Dict]):
+        """Gives the parser the envs' `config.action_lookup` dicts (EnvStateManager.envs entries) so that the action-id
+        lookup of es_manager.py:230-240 happens in the same kernel as the parse.  Call after every reset: Bandit
+        re-draws its arm order then."""
+        uniq, ids, env_table = [], {}, {}
+        for e in envs:
+            lk = getattr(e["env"].config, "action_lookup", None)
+            if lk is None:
+                env_table[e["env_id"]] = -1
+                continue
+            key = tuple(lk.items())
+            if key not in ids:
+                ids[key] = len(uniq)
+                uniq.append(dict(lk))
+            env_table[e["env_id"]] = ids[key]
+        self._tables = ops.ActionTables(uniq, self.device) if uniq else None
+        self._env_table = env_table
+
+    def _parse_batch(self, responses: List[str], env_ids=None):
+        tid = None
+        if self._tables is not None and env_ids is not None:
+            tid = [self._env_table.get(int(e), -1) for e in env_ids]
+        res = ops.parse_actions(responses, self._tables if tid is not None else None, tid,
+                                bool(self.config.agent_proxy.enable_think), self.action_sep,
+                                int(self.config.agent_proxy.max_actions_per_turn), device=self.device)
+        return res, res.to_host(), res.flags.cpu().numpy()
+
+    def _parse_response(self, response: str) -> List:
+        _, host, _ = self._parse_batch([response])
+        return host[0][0], host[0][1]
+
+    def get_env_inputs(self, lm_outputs) -> List[Dict]:
+        if lm_outputs.batch is not None and "responses" in lm_outputs.batch.keys():
+            responses = self.tokenizer.batch_decode(lm_outputs.batch["responses"], skip_special_tokens=True)
+        else:
+            responses = lm_outputs.non_tensor_batch["response_texts"]
+        head = "<think>" if self.config.agent_proxy.enable_think else "<answer>"
+        responses = [head + r for r in responses]  # generation does not include the opening tag (:340)
+        env_ids = lm_outputs.non_tensor_batch["env_ids"]
+        _, host, flags = self._parse_batch(responses, env_ids)
+        env_inputs = []
+        for env_id, response, (llm_response, actions, codes), fl in zip(env_ids, responses, host, flags):
+            item = {"env_id": env_id, "llm_raw_response": response, "llm_response": llm_response, "actions": actions}
+            if fl & 16 or (self._env_table is not None and self._env_table.get(int(env_id), -1) >= 0):
+                item["action_codes"] = codes  # ids of the valid actions, mapped on the device
+            env_inputs.append(item)
+        return env_inputs
+
+    # ---- reward normalisation (ctx_manager.py:175-226) -------------------------------------------------------------
+    def _normalize_score_tensor(self, score_tensor: torch.Tensor, env_outputs: List[Dict]) -> torch.Tensor:
+        assert self.config.agent_proxy.use_turn_scores == False, \
+            "Reward normalization is not supported for use_turn_scores == True"  # noqa: E712
+        rn_cfg = self.config.agent_proxy.reward_normalization
+        grouping, method = rn_cfg.grouping, rn_cfg.method
+        if grouping == "state":
+            group_tags = [env_output["group_id"] for env_output in env_outputs]
+        elif grouping == "inductive":
+            group_tags = [env_output["tag"] for env_output in env_outputs]
+        elif grouping == "batch":
+            group_tags = [1] * len(env_outputs)
+        else:
+            raise ValueError(f"Invalid grouping: {grouping}")
+        if method not in ("mean_std", "mean", "asym_clip", "identity"):
+            raise ValueError(f"Invalid normalization method: {method}")
+        dense = {}
+        gi = [dense.setdefault(t, len(dense)) for t in group_tags]
+        dev = self.device
+        penalty = torch.tensor([env_output.get("penalty", 0) for env_output in env_outputs], dtype=torch.float32, device=dev)
+        out = ops.group_norm(score_tensor[:, -1].to(dev), penalty, torch.tensor(gi, dtype=torch.int32, device=dev), len(dense), method)
+        score_tensor[:, -1] = out.to(score_tensor.device)  # in place, as the reference (rm_scores aliases original_rm_scores)
+        return score_tensor
+
+    # ---- LM inputs (ctx_manager.py:228-330) ---------------------------------------------------------------------------
+    def _messages(self, env_output: Dict, prepare_for_update: bool) -> List[Dict]:
+        """Chat messages of one trajectory (:248-267); trims `history` in place the way the reference does."""
+        if "state" in env_output["history"][-1] and prepare_for_update:
+            env_output["history"] = env_output["history"][:-1]  # the state of turn n+1 is not part of the trajectory
+        max_k = getattr(self.config.agent_proxy, "max_context_window", None)
+        if max_k is not None and isinstance(max_k, int) and max_k > 0:
+            env_output["history"] = env_output["history"][-max_k:]
+        enable_think = self.config.agent_proxy.enable_think
+        fmt = "<think> [Your thoughts] </think> <answer> [your answer] </answer>" if enable_think else "<answer> [your answer] </answer>"
+        length = f"Max response length: {self.env_config_lookup[env_output['env_id']]['max_tokens']} words (tokens)."
+        messages = [{"role": "system", "content": "You're a helpful assistant. "},
+                    {"role": "user", "content": self.prefix_lookup[env_output["env_id"]]}]
+        history = env_output["history"]
+        for idx, content in enumerate(history):
+            messages[-1]["content"] += f"\nTurn {idx + 1}:\n"
+            if "state" in content:
+                messages[-1]["content"] += (f"State:\n{content['state']}\nYou have {content['actions_left']} actions left. "
+                                            f"Always output: {fmt} with no extra text. Strictly follow this format. {length}\n")
+            if "llm_response" in content:
+                messages.append({"role": "assistant", "content": content["llm_response"]})
+            if "reward" in content and not (prepare_for_update and idx == len(history) - 1):
+                messages.append({"role": "user", "content": f"Reward:\n{content['reward']}\n"})
+        assert all(msg["role"] == "assistant" for msg in messages[2::2])  # the loss mask counts on this alternation
+        return messages
+
+    def get_lm_inputs(self, env_outputs: List[Dict], prepare_for_update: bool) -> DataProto:
+        llm_input_texts, messages_list = [], []
+        for env_output in env_outputs:
+            messages = self._messages(env_output, prepare_for_update)
+            text = self.tokenizer.apply_chat_template(messages, add_generation_prompt=(not prepare_for_update), tokenize=False)
+            if not prepare_for_update:
+                text += "<think>" if self.config.agent_proxy.enable_think else "<answer>"  # the opening tag is forced
+            llm_input_texts.append(text)
+            messages_list.append(messages)
+
+        inputs = self.tokenizer(llm_input_texts, return_tensors="pt", padding=True, padding_side="left", truncation=False)
+        input_ids, attention_mask = inputs.input_ids, inputs.attention_mask
+        position_ids = attention_mask.cumsum(dim=-1)
+        if prepare_for_update:
+            scores = [[i.get("reward", 0.0) for i in env_output["history"]] for env_output in env_outputs]
+            score_tensor, loss_mask, response_mask = get_masks_and_scores(
+                input_ids, self.tokenizer, scores, use_turn_scores=self.config.agent_proxy.use_turn_scores,
+                enable_response_mask=self.config.enable_response_mask, device=self.device)
+            normalized_score_tensor = score_tensor
+            if not self.config.agent_proxy.use_turn_scores:
+                normalized_score_tensor = self._normalize_score_tensor(score_tensor, env_outputs)
+            response_length = response_mask.sum(dim=-1).float().mean().item()
+
+        llm_inputs = DataProto()
+        llm_inputs.batch = TensorDict({"input_ids": input_ids, "attention_mask": attention_mask, "position_ids": position_ids,
+                                       "responses": input_ids[:, 1:]}, batch_size=input_ids.shape[0])
+        if prepare_for_update:
+            llm_inputs.batch["loss_mask"] = loss_mask
+            llm_inputs.batch["rm_scores"] = normalized_score_tensor
+            llm_inputs.batch["original_rm_scores"] = score_tensor  # the SAME tensor when normalised: the reference aliases them
+        llm_inputs.non_tensor_batch = {
+            "env_ids": np.array([env_output["env_id"] for env_output in env_outputs], dtype=object),
+            "group_ids": np.array([env_output["group_id"] for env_output in env_outputs], dtype=object),
+            "messages_list": np.array(messages_list, dtype=object),
+        }
+        if prepare_for_update:
+            llm_inputs.meta_info = {"metrics": self._mean_metrics(env_outputs, response_length)}
+        return llm_inputs
+
+    def _mean_metrics(self, env_outputs: List[Dict], response_length: float) -> Dict:
+        """Per-tag means over ALL envs of the tag plus the non-zero means (:309-328)."""
+        metrics = {}
+        for env_output in env_outputs:
+            for key, value in env_output["metrics"].items():
+                metrics.setdefault(key, []).append(value)
+        mean_metrics = {key: np.sum(value) / self.env_nums[key.split("/")[0]] for key, value in metrics.items()}
+        for key, values in metrics.items():
+            prefix, suffix = key.split("/", 1)
+            non_zero_values = [v for v in values if v != 0]
+            if non_zero_values:
+                mean_metrics[f"{prefix}/non-zero/{suffix}"] = np.mean(non_zero_values)
+        mean_metrics["response_length"] = response_length
+        return mean_metrics
+
+    def formulate_rollouts(self, env_outputs: List[Dict]) -> DataProto:
+        return self.get_lm_inputs(env_outputs, prepare_for_update=True)

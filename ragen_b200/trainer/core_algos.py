@@ -1,0 +1,91 @@
+"""Advantage estimators with the reference's names and argument meaning, on the device.
+
+  compute_gae_advantage_return            verl/verl/trainer/ppo/core_algos.py:67-109
+  compute_bi_level_gae_advantage_return   ragen/trainer/core_algos.py:4-92
+  compute_grpo_outcome_advantage          verl/verl/trainer/ppo/core_algos.py:113-165
+  masked_mean / masked_var / masked_whiten  verl/verl/utils/torch_functional.py:122-151
+
+Each is one or two launches of libragen_b200 (ragen_gae / ragen_bilevel_gae produce the un-whitened advantages, the
+returns and the masked moments in one pass; ragen_whiten applies them).  Inputs may live on the host, as in the
+reference's driver process: they are moved to `device` and the results come back where the inputs were.  When the rows of
+the batch are sharded over ranks (`group` given, or a default process group with world_size > 1 and `sharded=True`), the
+whitening moments are all-reduced (24 bytes over NCCL) so every rank whitens with the batch-global statistics.
+"""
+from collections import OrderedDict
+
+import numpy as np
+import torch
+
+from .. import ops
+
+
+def _dev(t, device):
+    if t.is_cuda:
+        return t.device
+    return torch.device("cuda", torch.cuda.current_device() if device is None else int(device))
+
+
+def _whiten_from(adv, mom, sharded, group):
+    if sharded:
+        ops.all_reduce_moments(mom, group)
+    return ops.whiten_(adv, mom)
+
+
+def compute_gae_advantage_return(token_level_rewards, values, response_mask, gamma, lam, device=None, sharded=False, group=None):
+    home, dev = token_level_rewards.device, _dev(token_level_rewards, device)
+    with torch.no_grad():
+        adv, ret, mom = ops.gae_raw(token_level_rewards.to(dev), values.to(dev), response_mask.to(dev), gamma, lam)
+        adv = _whiten_from(adv, mom, sharded, group)
+    return adv.to(home), ret.to(home)
+
+
+def compute_bi_level_gae_advantage_return(token_level_rewards, values, loss_mask, gamma, lam, high_level_gamma, device=None,
+                                          sharded=False, group=None):
+    home, dev = token_level_rewards.device, _dev(token_level_rewards, device)
+    with torch.no_grad():
+        adv, ret, mom = ops.bilevel_gae_raw(token_level_rewards.to(dev), values.to(dev), loss_mask.to(dev), gamma, lam, high_level_gamma)
+        adv = _whiten_from(adv, mom, sharded, group)
+    return adv.to(home), ret.to(home)
+
+
+def dense_index(index):
+    """uid array (any hashables) -> (int32 list of dense group ids in first-seen order, number of groups)."""
+    seen = OrderedDict()
+    idx = [seen.setdefault(u, len(seen)) for u in (index.tolist() if isinstance(index, np.ndarray) else list(index))]
+    return idx, len(seen)
+
+
+def compute_grpo_outcome_advantage(token_level_rewards, response_mask, index, epsilon: float = 1e-6,
+                                   norm_adv_by_std_in_grpo: bool = True, device=None):
+    """Returns the same tensor twice, as the reference does (:165)."""
+    home, dev = token_level_rewards.device, _dev(token_level_rewards, device)
+    gi, n_groups = dense_index(index)
+    with torch.no_grad():
+        adv, _ = ops.grpo_outcome(token_level_rewards.to(dev), response_mask.to(dev),
+                                  torch.tensor(gi, dtype=torch.int32, device=dev), n_groups, epsilon, norm_adv_by_std_in_grpo)
+    adv = adv.to(home)
+    return adv, adv
+
+
+def masked_moments(values, mask, device=None, sharded=False, group=None):
+    dev = _dev(values, device)
+    mom = ops.masked_moments(values.to(dev), mask.to(dev))
+    if sharded:
+        ops.all_reduce_moments(mom, group)
+    return mom
+
+
+def masked_mean(values, mask, device=None):
+    n, s, _ = masked_moments(values, mask, device).tolist()
+    return torch.tensor(s / (n + 1e-8), dtype=torch.float32, device=values.device)
+
+
+def masked_whiten(values, mask, shift_mean=True, device=None, sharded=False, group=None):
+    home, dev = values.device, _dev(values, device)
+    x = values.to(dev).float().contiguous().clone()
+    mom = masked_moments(x, mask, device, sharded, group)
+    out = ops.whiten_(x, mom)
+    if not shift_mean:
+        n, s, _ = mom.tolist()
+        out += s / (n + 1e-8)
+    return out.to(home)

@@ -360,6 +360,129 @@ def es_manager_script():
     print("es_manager ok; turns", len(script))
 
 
+def _digest(t):
+    import hashlib
+    a = np.ascontiguousarray(t.numpy() if hasattr(t, "numpy") else t)
+    return hashlib.sha256(a.tobytes()).hexdigest()[:24] + ":" + "x".join(map(str, a.shape)) + ":" + str(a.dtype)
+
+
+LM_VARIANTS = [
+    {"name": "update_identity", "update": True, "ap": {}},
+    {"name": "update_mean_std", "update": True, "ap": {"reward_normalization": {"grouping": "state", "method": "mean_std"}}},
+    {"name": "update_batch_asym", "update": True, "ap": {"reward_normalization": {"grouping": "batch", "method": "asym_clip"}}},
+    {"name": "update_turn_scores", "update": True, "ap": {"use_turn_scores": True}},
+    {"name": "update_window2", "update": True, "ap": {"max_context_window": 2}},
+    {"name": "update_no_think", "update": True, "ap": {"enable_think": False}, "erm": False},
+    {"name": "generate", "update": False, "ap": {}},
+    {"name": "generate_no_think_window1", "update": False, "ap": {"enable_think": False, "max_context_window": 1}},
+]
+
+
+def lm_inputs():
+    """ContextManager.get_lm_inputs / formulate_rollouts / get_env_inputs of the UNMODIFIED reference, driven by the
+    byte-level fake tokenizer (tests/fake_tokenizer.py) on the recorded rollout of es_manager.json."""
+    import copy
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from fake_tokenizer import FakeQwenTokenizer
+    cm = R.ctx_manager()
+    with open(os.path.join(OUT, "es_manager.json")) as fh:
+        final = json.load(fh)["final"]
+    tok = FakeQwenTokenizer()
+    out = {"variants": []}
+    for v in LM_VARIANTS:
+        cfg = C.base_config(tags=("SimpleSokoban",), n_groups=(2,), group_size=4, **v["ap"])
+        cfg.enable_response_mask = v.get("erm", True)
+        ctx = cm.ContextManager(cfg, tok, mode="train")
+        env_outputs = copy.deepcopy(final)
+        dp = ctx.get_lm_inputs(env_outputs, prepare_for_update=v["update"])
+        rec = {"name": v["name"], "update": v["update"], "ap": v["ap"], "erm": v.get("erm", True), "shape": list(dp.batch["input_ids"].shape),
+               "digest": {k: _digest(t) for k, t in dp.batch.items()},
+               "env_ids": [int(x) for x in dp.non_tensor_batch["env_ids"]],
+               "group_ids": [int(x) for x in dp.non_tensor_batch["group_ids"]],
+               "messages_digest": _digest(np.frombuffer(json.dumps([list(m) for m in dp.non_tensor_batch["messages_list"]],
+                                                                   ensure_ascii=False).encode(), dtype=np.uint8)),
+               "history_len": [len(e["history"]) for e in env_outputs]}
+        if "window" in v["name"]:  # the short ones in full, for a readable diff when something moves
+            rec["messages_list"] = [list(m) for m in dp.non_tensor_batch["messages_list"]]
+        if v["update"]:
+            rm = dp.batch["rm_scores"]
+            nz = rm.nonzero()
+            rec["rm_nonzero"] = [[int(i), int(j), float(rm[i, j])] for i, j in nz.tolist()]
+            rec["aliased"] = bool(dp.batch["rm_scores"].data_ptr() == dp.batch["original_rm_scores"].data_ptr())
+            rec["loss_mask_sum"] = dp.batch["loss_mask"].sum(-1).tolist()
+            rec["metrics"] = {k: float(x) for k, x in dp.meta_info["metrics"].items()}
+        out["variants"].append(rec)
+    # get_env_inputs: textual responses and token responses (the generation lacks the opening tag, :340)
+    texts = ["go</think><answer>Up || Down</answer>", " a </think> <answer> Left||Right|| Up ||Down||Left||Up||Right </answer> x",
+             "no close", "t</think><answer>Up ||Jump|| down || LEFT</answer>", "x</think><answer></answer>",
+             "\u221a </think><answer> Right </answer>", "t</think><answer>Up<|im_end|></answer>", "</think><answer>up</answer>"]
+    env = []
+    for think in (True, False):
+        cfg = C.base_config(tags=("SimpleSokoban",), n_groups=(2,), group_size=4, enable_think=think)
+        ctx = cm.ContextManager(cfg, tok, mode="train")
+        body = texts if think else [t.split("<answer>", 1)[-1] for t in texts]
+        dp = cm.DataProto(batch=None, non_tensor_batch={"response_texts": body, "env_ids": np.arange(8, dtype=object)})
+        a = ctx.get_env_inputs(dp)
+        ids = tok([b + "<|im_end|>" for b in body]).input_ids
+        dp = cm.DataProto(batch={"responses": ids}, non_tensor_batch={"env_ids": np.arange(8, dtype=object)})
+        b = ctx.get_env_inputs(dp)
+        for r in a + b:
+            r["env_id"] = int(r["env_id"])
+        env.append({"enable_think": think, "texts": body, "from_text": a, "from_tokens": b})
+    out["env_inputs"] = env
+    with open(os.path.join(OUT, "lm_inputs.json"), "w") as fh:
+        json.dump(out, fh, ensure_ascii=False, indent=0)
+    print("lm_inputs ok:", [(r["name"], r["shape"]) for r in out["variants"]])
+
+
+ROLLOUT_CASES = [
+    {"name": "sokoban_state_meanstd", "tags": ["SimpleSokoban"], "n_groups": [2], "group_size": 4, "seed": 123,
+     "ap": {"reward_normalization": {"grouping": "state", "method": "mean_std"}}},
+    {"name": "mixed_identity", "tags": ["SimpleSokoban", "FrozenLake", "Bandit", "LargerSokoban"], "n_groups": [2, 2, 1, 1],
+     "group_size": 4, "seed": 31, "ap": {}},
+    {"name": "mixed_inductive_asym_think_off", "tags": ["FrozenLake", "Bandit", "SimpleSokoban"], "n_groups": [1, 2, 1],
+     "group_size": 8, "seed": 7, "ap": {"enable_think": False, "max_turn": 3,
+                                         "reward_normalization": {"grouping": "inductive", "method": "asym_clip"}}},
+]
+
+
+def rollouts():
+    """The rollout loop of agent_proxy.py:143-159 over the UNMODIFIED reference managers, with the scripted policy of
+    tests/fake_tokenizer.py in place of the LLM (agent_proxy.py itself imports vllm / ray and is not loaded)."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from fake_tokenizer import FakeQwenTokenizer, ScriptedWg
+    cm, es = R.ctx_manager(), R.es_manager()
+    tok = FakeQwenTokenizer()
+    out = []
+    for case in ROLLOUT_CASES:
+        cfg = C.base_config(tags=tuple(case["tags"]), n_groups=tuple(case["n_groups"]), group_size=case["group_size"], **case["ap"])
+        random.seed(0); np.random.seed(0)
+        ctx, mgr = cm.ContextManager(cfg, tok, mode="train"), es.EnvStateManager(cfg, mode="train")
+        wg = ScriptedWg(tok, cm.DataProto)
+        env_outputs = mgr.reset(seed=case["seed"])
+        turns = []
+        for _ in range(cfg.agent_proxy.max_turn):
+            lm_inputs = ctx.get_lm_inputs(env_outputs, prepare_for_update=False)
+            lm_inputs.meta_info = {}
+            lm_outputs = wg.generate_sequences(lm_inputs)
+            env_inputs = ctx.get_env_inputs(lm_outputs)
+            turns.append({"n": len(env_inputs), "input_ids": _digest(lm_inputs.batch["input_ids"]),
+                          "responses": lm_outputs.non_tensor_batch["response_texts"][:3]})
+            env_outputs = mgr.step(env_inputs)
+            if len(env_outputs) == 0:
+                break
+        dp = ctx.formulate_rollouts(mgr.get_rollout_states())
+        rm = dp.batch["rm_scores"]
+        out.append({**case, "turns": turns, "shape": list(dp.batch["input_ids"].shape),
+                    "digest": {k: _digest(t) for k, t in dp.batch.items()},
+                    "rm_last": rm[:, -1].tolist(), "rm_sum": rm.sum(-1).tolist(),
+                    "loss_mask_sum": dp.batch["loss_mask"].sum(-1).tolist(),
+                    "metrics": {k: float(x) for k, x in dp.meta_info["metrics"].items()}})
+    with open(os.path.join(OUT, "rollouts.json"), "w") as fh:
+        json.dump(out, fh, ensure_ascii=False, indent=0)
+    print("rollouts ok:", [(r["name"], r["shape"], len(r["turns"])) for r in out])
+
+
 def countdown():
     cd = R.countdown_env()
     cases = [("1+2+3", [1, 2, 3], 6), ("1+2", [1, 2, 3], 3), ("3*(2-1)", [1, 2, 3], 3), ("1 + 2 = 3", [1, 2, 3], 3),
@@ -388,4 +511,6 @@ if __name__ == "__main__":
     advantage()
     ctx_vectors()
     es_manager_script()
+    lm_inputs()
+    rollouts()
     countdown()

@@ -1,0 +1,105 @@
+"""GPU parity of ragen_b200.llm_agent.ContextManager against the UNMODIFIED reference ContextManager
+(tests/golden/lm_inputs.json, made by tests/golden/make_golden.py:lm_inputs with the same byte-level fake tokenizer):
+get_lm_inputs / formulate_rollouts (token tensors, masks, scores, normalisation, metrics) and get_env_inputs."""
+import copy
+import hashlib
+import json
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import golden_json
+from fake_tokenizer import FakeQwenTokenizer
+from oracle import cfg as C
+
+pytestmark = pytest.mark.gpu
+G = golden_json("lm_inputs.json")
+
+
+def _digest(t):
+    a = np.ascontiguousarray(t.numpy() if hasattr(t, "numpy") else t)
+    return hashlib.sha256(a.tobytes()).hexdigest()[:24] + ":" + "x".join(map(str, a.shape)) + ":" + str(a.dtype)
+
+
+@pytest.mark.parametrize("rec", G["variants"], ids=[r["name"] for r in G["variants"]])
+def test_get_lm_inputs_matches_reference(rec):
+    from ragen_b200.llm_agent.ctx_manager import ContextManager
+
+    v = rec
+    cfg = C.base_config(tags=("SimpleSokoban",), n_groups=(2,), group_size=4, **v["ap"])
+    cfg.enable_response_mask = v["erm"]
+    ctx = ContextManager(cfg, FakeQwenTokenizer(), mode="train")
+    env_outputs = copy.deepcopy(golden_json("es_manager.json")["final"])
+    dp = ctx.get_lm_inputs(env_outputs, prepare_for_update=v["update"])
+    assert list(dp.batch["input_ids"].shape) == rec["shape"]
+    assert sorted(dp.batch.keys()) == sorted(rec["digest"].keys())
+    assert [int(x) for x in dp.non_tensor_batch["env_ids"]] == rec["env_ids"]
+    assert [int(x) for x in dp.non_tensor_batch["group_ids"]] == rec["group_ids"]
+    assert [len(e["history"]) for e in env_outputs] == rec["history_len"]
+    msgs = [list(m) for m in dp.non_tensor_batch["messages_list"]]
+    if "messages_list" in rec:
+        assert msgs == rec["messages_list"]
+    assert _digest(np.frombuffer(json.dumps(msgs, ensure_ascii=False).encode(), dtype=np.uint8)) == rec["messages_digest"]
+    if v["update"]:
+        rm = dp.batch["rm_scores"]
+        got = [[int(i), int(j), float(rm[i, j])] for i, j in rm.nonzero().tolist()]
+        assert [g[:2] for g in got] == [w[:2] for w in rec["rm_nonzero"]]
+        for g, w in zip(got, rec["rm_nonzero"]):  # fp32 normalisation: 1e-5 relative (north_star tolerance)
+            assert abs(g[2] - w[2]) <= 1e-5 * max(1.0, abs(w[2])), (g, w)
+        assert bool(rm.data_ptr() == dp.batch["original_rm_scores"].data_ptr()) == rec["aliased"]
+        assert dp.batch["loss_mask"].sum(-1).tolist() == rec["loss_mask_sum"]
+        assert set(dp.meta_info["metrics"]) == set(rec["metrics"])
+        for k, w in rec["metrics"].items():
+            assert float(dp.meta_info["metrics"][k]) == pytest.approx(w, rel=1e-12), k
+    exact = [k for k in rec["digest"] if k not in ("rm_scores", "original_rm_scores")]
+    if v["update"] and v["ap"].get("reward_normalization", {}).get("method", "identity") == "identity":
+        exact = list(rec["digest"])  # no fp arithmetic beyond the fp64 turn sum -> bit-exact
+    for k in exact:
+        assert _digest(dp.batch[k]) == rec["digest"][k], k
+
+
+@pytest.mark.parametrize("case", G["env_inputs"], ids=["think", "no_think"])
+def test_get_env_inputs_matches_reference(case):
+    from ragen_b200.llm_agent.ctx_manager import ContextManager, DataProto
+
+    tok = FakeQwenTokenizer()
+    cfg = C.base_config(tags=("SimpleSokoban",), n_groups=(2,), group_size=4, enable_think=case["enable_think"])
+    ctx = ContextManager(cfg, tok, mode="train")
+    ids = np.arange(8, dtype=object)
+    a = ctx.get_env_inputs(DataProto(batch=None, non_tensor_batch={"response_texts": case["texts"], "env_ids": ids}))
+    tokens = tok([b + "<|im_end|>" for b in case["texts"]]).input_ids
+    b = ctx.get_env_inputs(DataProto(batch={"responses": tokens}, non_tensor_batch={"env_ids": ids}))
+    for got, want in ((a, case["from_text"]), (b, case["from_tokens"])):
+        assert len(got) == len(want)
+        for g, w in zip(got, want):
+            assert {k: (int(g[k]) if k == "env_id" else g[k]) for k in w} == w
+
+
+def test_action_codes_when_bound_to_envs():
+    """bind_envs: the action-id lookup of es_manager.py:230-240 rides in the parse kernel; EnvStateManager.step takes
+    the codes and ends in the same place as the name path."""
+    from ragen_b200.llm_agent.ctx_manager import ContextManager, DataProto
+    from ragen_b200.llm_agent.es_manager import EnvStateManager
+
+    cfg = C.base_config(tags=("SimpleSokoban", "Bandit"), n_groups=(1, 1), group_size=4)
+    runs = []
+    for bound in (True, False):
+        es = EnvStateManager(cfg, mode="train")
+        ctx = ContextManager(cfg, FakeQwenTokenizer(), mode="train")
+        es.reset(seed=5)
+        if bound:
+            ctx.bind_envs(es.envs)
+        texts = ["t</think><answer>Up || jump || LEFT</answer>", "t</think><answer>Down</answer>", "junk", "t</think><answer>right||right</answer>",
+                 "t</think><answer>Phoenix</answer>", "t</think><answer>dragon</answer>", "t</think><answer>Tiger</answer>", "t</think><answer></answer>"]
+        inputs = ctx.get_env_inputs(DataProto(batch=None, non_tensor_batch={"response_texts": texts, "env_ids": np.arange(8, dtype=object)}))
+        assert all(("action_codes" in i) == bound for i in inputs)
+        if bound:
+            assert inputs[0]["action_codes"] == [1, 3] and inputs[3]["action_codes"] == [4, 4] and inputs[2]["action_codes"] == []
+        es.step(inputs)
+        runs.append(es.get_rollout_states())
+    for g, w in zip(*runs):
+        assert g["penalty"] == w["penalty"] and g["metrics"] == w["metrics"]
+        assert [h.get("reward") for h in g["history"]] == [h.get("reward") for h in w["history"]]
+        assert [h.get("state") for h in g["history"]] == [h.get("state") for h in w["history"]]
+        assert [h.get("actions") for h in g["history"]] == [h.get("actions") for h in w["history"]]

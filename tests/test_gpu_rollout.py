@@ -1,0 +1,132 @@
+"""GPU parity of the whole seam: LLMAgentProxy.rollout (device-backed managers + scripted policy) against the same loop
+over the UNMODIFIED reference managers (tests/golden/rollouts.json), then compute_advantage on the rollout (C5 shape:
+rollout -> token-level rewards -> GAE / bi-level GAE / GRPO) against the oracle estimators and the reference goldens."""
+import hashlib
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import golden_json, golden_npz
+from fake_tokenizer import FakeQwenTokenizer, ScriptedWg
+from oracle import advantage as A
+from oracle import cfg as C
+
+pytestmark = pytest.mark.gpu
+CASES = golden_json("rollouts.json")
+
+
+def _digest(t):
+    a = np.ascontiguousarray(t.numpy() if hasattr(t, "numpy") else t)
+    return hashlib.sha256(a.tobytes()).hexdigest()[:24] + ":" + "x".join(map(str, a.shape)) + ":" + str(a.dtype)
+
+
+class _Recorder(ScriptedWg):
+    def __init__(self, *a, **k):
+        super().__init__(*a, **k)
+        self.turns = []
+
+    def generate_sequences(self, lm_inputs):
+        out = super().generate_sequences(lm_inputs)
+        self.turns.append({"n": len(out.non_tensor_batch["response_texts"]), "input_ids": _digest(lm_inputs.batch["input_ids"]),
+                           "responses": out.non_tensor_batch["response_texts"][:3]})
+        return out
+
+
+def _rollout(case):
+    from ragen_b200.llm_agent.agent_proxy import LLMAgentProxy
+    from ragen_b200.llm_agent.ctx_manager import DataProto
+
+    cfg = C.base_config(tags=tuple(case["tags"]), n_groups=tuple(case["n_groups"]), group_size=case["group_size"], **case["ap"])
+    tok = FakeQwenTokenizer()
+    wg = _Recorder(tok, DataProto)
+    proxy = LLMAgentProxy(cfg, wg, tok)
+    return proxy.rollout(DataProto(batch=None, non_tensor_batch=None, meta_info={}), val=False, seed=case["seed"]), wg
+
+
+@pytest.mark.parametrize("case", CASES, ids=[c["name"] for c in CASES])
+def test_rollout_matches_reference_managers(case):
+    dp, wg = _rollout(case)
+    assert wg.turns == case["turns"]  # every prompt of every turn, token for token
+    assert list(dp.batch["input_ids"].shape) == case["shape"]
+    for k in ("input_ids", "attention_mask", "position_ids", "responses", "loss_mask"):
+        assert _digest(dp.batch[k]) == case["digest"][k], k
+    rm = dp.batch["rm_scores"]
+    want = torch.tensor(case["rm_last"])
+    assert float((rm[:, -1] - want).abs().max()) <= 1e-5 * max(1.0, float(want.abs().max()))
+    assert float((rm[:, :-1]).abs().max()) == 0.0
+    assert dp.batch["loss_mask"].sum(-1).tolist() == case["loss_mask_sum"]
+    assert set(dp.meta_info["metrics"]) == set(case["metrics"])
+    for k, w in case["metrics"].items():
+        assert float(dp.meta_info["metrics"][k]) == pytest.approx(w, rel=1e-12), k
+    if case["ap"].get("reward_normalization", {}).get("method", "identity") == "identity":
+        assert _digest(rm) == case["digest"]["rm_scores"]
+
+
+def test_rollout_to_advantage_c5_shape():
+    """C5: rollout -> compute_advantage (GAE, bi-level GAE, GRPO multi-turn) with the rollout's own masks and scores."""
+    from ragen_b200.trainer import AdvantageEstimator, compute_advantage
+
+    dp, _ = _rollout(CASES[1])
+    batch = dp.batch
+    B, T = batch["rm_scores"].shape
+    gen = torch.Generator().manual_seed(11)
+    batch["response_mask"] = batch["loss_mask"].float()
+    batch["token_level_rewards"] = batch["rm_scores"].clone()
+    batch["values"] = torch.randn(B, T, generator=gen) * batch["response_mask"]
+    r, v, m = batch["token_level_rewards"], batch["values"], batch["response_mask"]
+
+    compute_advantage(dp, AdvantageEstimator.GAE, gamma=1.0, lam=1.0)
+    wa, wr = A.gae(r, v, m, 1.0, 1.0)
+    assert torch.equal(batch["returns"], wr)
+    assert float((batch["advantages"] - wa).abs().max()) <= 1e-5 * max(1.0, float(wa.abs().max()))
+
+    # bi-level needs a reward at the last loss-mask position of each row (core_algos.py:79); the rollout puts the whole
+    # trajectory reward on the last column, so move it there the way the trainer's multi-turn path sees it
+    r2 = torch.zeros_like(r)
+    for b in range(B):
+        pos = m[b].nonzero()
+        if len(pos):
+            r2[b, int(pos[-1])] = r[b, -1] if float(r[b, -1]) != 0 else 0.5
+    batch["token_level_rewards"] = r2
+    compute_advantage(dp, AdvantageEstimator.GAE, gamma=1.0, lam=1.0, bi_level_gae=True, high_level_gamma=0.95)
+    wa, wr = A.bilevel_gae(r2, v, m, 1.0, 1.0, 0.95)
+    assert torch.equal(batch["returns"], wr)
+    assert float((batch["advantages"] - wa).abs().max()) <= 1e-5 * max(1.0, float(wa.abs().max()))
+
+    batch["token_level_rewards"] = r
+    dp.non_tensor_batch["uid"] = dp.non_tensor_batch["group_ids"]
+    for by_std in (True, False):
+        compute_advantage(dp, AdvantageEstimator.GRPO, multi_turn=True, norm_adv_by_std_in_grpo=by_std)
+        wa = A.grpo_outcome(r, batch["loss_mask"].float(), [int(g) for g in dp.non_tensor_batch["group_ids"]], norm_by_std=by_std)
+        wa = wa[0] if isinstance(wa, tuple) else wa
+        assert float((batch["advantages"] - wa).abs().max()) <= 1e-5 * max(1.0, float(wa.abs().max()))
+        assert batch["advantages"].data_ptr() == batch["returns"].data_ptr()
+
+    with pytest.raises(NotImplementedError):
+        compute_advantage(dp, AdvantageEstimator.RLOO)
+
+
+def test_reference_named_estimators_on_golden():
+    """The reference-named functions (whitening included) against tensors the UNMODIFIED reference produced."""
+    from ragen_b200.trainer import core_algos as K
+
+    g = golden_npz("advantage.npz")
+    r, v, m = torch.tensor(g["rewards"]), torch.tensor(g["values"]), torch.tensor(g["mask"])
+    for tag in ("a", "b"):
+        gamma, lam, hg = (float(x) for x in g[f"cfg_{tag}"])
+        adv, ret = K.compute_gae_advantage_return(r, v, m, gamma, lam)
+        assert not adv.is_cuda and torch.equal(ret, torch.tensor(g[f"gae_{tag}_ret"]))
+        assert float((adv - torch.tensor(g[f"gae_{tag}_adv"])).abs().max()) <= 1e-5 * max(1.0, float(np.abs(g[f"gae_{tag}_adv"]).max()))
+        adv, ret = K.compute_bi_level_gae_advantage_return(r, v, m, gamma, lam, hg)
+        assert torch.equal(ret, torch.tensor(g[f"bi_{tag}_ret"]))
+        assert float((adv - torch.tensor(g[f"bi_{tag}_adv"])).abs().max()) <= 1e-5 * max(1.0, float(np.abs(g[f"bi_{tag}_adv"]).max()))
+    for by_std, key in ((True, "grpo_std_adv"), (False, "grpo_mean_adv")):
+        adv, ret = K.compute_grpo_outcome_advantage(torch.tensor(g["outcome"]), m, g["uid"], norm_adv_by_std_in_grpo=by_std)
+        assert adv is ret
+        assert float((adv - torch.tensor(g[key])).abs().max()) <= 1e-5 * max(1.0, float(np.abs(g[key]).max()))
+    w = K.masked_whiten(v, m)
+    ref = A.masked_whiten(v, m)
+    assert float((w - ref).abs().max()) <= 1e-5 * max(1.0, float(ref.abs().max()))
+    with pytest.raises(ValueError):
+        K.masked_whiten(v, torch.zeros_like(m))

@@ -12,12 +12,14 @@ from .es_manager import EnvStateManager
 
 
 class LLMAgentProxy:
-    def __init__(self, config, actor_rollout_wg, tokenizer, device: int = 0):
+    def __init__(self, config, actor_rollout_wg, tokenizer, device: int = 0, rank: int = 0, world_size: int = 1, group=None):
+        """rank / world_size / group (absent in the reference, which is single-process): one proxy per GPU, each owning the
+        env groups with group_id % world_size == rank; rollout metrics come back batch-global (ragen_b200/sharding.py)."""
         self.config = config
-        self.train_ctx_manager = ContextManager(config, tokenizer, mode="train", device=device)
-        self.train_es_manager = EnvStateManager(config, mode="train", device=device)
-        self.val_ctx_manager = ContextManager(config, tokenizer, mode="val", device=device)
-        self.val_es_manager = EnvStateManager(config, mode="val", device=device)
+        self.train_ctx_manager = ContextManager(config, tokenizer, mode="train", device=device).shard(world_size, group)
+        self.train_es_manager = EnvStateManager(config, mode="train", device=device, rank=rank, world_size=world_size)
+        self.val_ctx_manager = ContextManager(config, tokenizer, mode="val", device=device).shard(world_size, group)
+        self.val_es_manager = EnvStateManager(config, mode="val", device=device, rank=rank, world_size=world_size)
         self.actor_wg = actor_rollout_wg
         self.tokenizer = tokenizer
 

@@ -72,6 +72,16 @@ class ContextManager:
         self._init_prefix_lookup()
         self._tables = None        # action lookup tables on the device, built from the envs at first use
         self._env_table = None
+        self.exchange = None       # set by shard(): batch-global metrics when env groups are spread over ranks
+
+    def shard(self, world_size: int, group=None, extra_keys=()):
+        """This manager sees only its rank's env groups (EnvStateManager(rank=, world_size=)); the rollout metrics of
+        formulate_rollouts are then all-reduced so every rank reports the whole batch (ragen_b200/sharding.py)."""
+        from ..sharding import RolloutExchange
+
+        self.world_size = int(world_size)
+        self.exchange = RolloutExchange(self.es_cfg.env_configs.tags, self.env_nums, extra_keys, group) if world_size > 1 else None
+        return self
 
     def _check_env_installed(self, env_type: str):
         if env_type not in REGISTERED_ENV_CONFIGS:
@@ -173,6 +183,9 @@ class ContextManager:
             raise ValueError(f"Invalid grouping: {grouping}")
         if method not in ("mean_std", "mean", "asym_clip", "identity"):
             raise ValueError(f"Invalid normalization method: {method}")
+        if self.exchange is not None and grouping != "state" and method != "identity":
+            raise NotImplementedError("sharded rollouts normalise within env groups (grouping='state'): whole groups live on "
+                                      "one rank; tag- or batch-wide statistics would need their own exchange")
         dense = {}
         gi = [dense.setdefault(t, len(dense)) for t in group_tags]
         dev = self.device
@@ -229,6 +242,7 @@ class ContextManager:
             if not self.config.agent_proxy.use_turn_scores:
                 normalized_score_tensor = self._normalize_score_tensor(score_tensor, env_outputs)
             response_length = response_mask.sum(dim=-1).float().mean().item()
+            self._response_tokens = (float(response_mask.sum()), int(response_mask.shape[0]))
 
         llm_inputs = DataProto()
         llm_inputs.batch = TensorDict({"input_ids": input_ids, "attention_mask": attention_mask, "position_ids": position_ids,
@@ -248,6 +262,10 @@ class ContextManager:
 
     def _mean_metrics(self, env_outputs: List[Dict], response_length: float) -> Dict:
         """Per-tag means over ALL envs of the tag plus the non-zero means (:309-328)."""
+        if self.exchange is not None:  # one all-reduce of the fixed-layout vector, then the same arithmetic on global sums
+            ex = self.exchange
+            vec = ex.pack(env_outputs, *self._response_tokens, device=self.device if torch.distributed.get_backend(ex.group) == "nccl" else None)
+            return ex.unpack(ex.all_reduce(vec))[0]
         metrics = {}
         for env_output in env_outputs:
             for key, value in env_output["metrics"].items():

@@ -44,10 +44,13 @@ class _Block:
 
 
 class EnvStateManager:
-    def __init__(self, config, mode: str = "train", device: int = 0):
+    def __init__(self, config, mode: str = "train", device: int = 0, rank: int = 0, world_size: int = 1):
+        """rank / world_size: this process keeps only the env groups with group_id % world_size == rank (env_id and
+        group_id stay global, so the union over ranks is the single-process manager; ragen_b200/sharding.py)."""
         self.sys_config = config
         self.mode = mode
         self.device = int(device)
+        self.rank, self.world_size = int(rank), int(world_size)
         self.config = getattr(self.sys_config.es_manager, mode)
         self.env_groups = int(self.config.env_groups)
         self.group_size = self.config.group_size
@@ -67,7 +70,11 @@ class EnvStateManager:
         for tag, n_group in zip(cfg.env_configs.tags, cfg.env_configs.n_groups):
             tpl = self.sys_config.custom_envs[tag]
             env_type = tpl.env_type
-            first, count = done_groups * self.group_size, n_group * self.group_size
+            groups = [g for g in range(done_groups, done_groups + n_group) if g % self.world_size == self.rank]
+            done_groups += n_group
+            if not groups:
+                continue
+            first, count = len(self.envs), len(groups) * self.group_size
             make_cfg = (lambda: REGISTERED_ENV_CONFIGS[env_type]()) if tpl.env_config is None else \
                 (lambda: REGISTERED_ENV_CONFIGS[env_type](**tpl.env_config))
             c0 = make_cfg()
@@ -86,15 +93,17 @@ class EnvStateManager:
             for i in range(count):
                 env_config = make_cfg()
                 env_obj = REGISTERED_ENVS[env_type](env_config, batch=batch, slot=i, **extra)
-                self.envs.append({"tag": tag, "group_id": (first + i) // self.group_size, "env_id": first + i, "env": env_obj,
-                                  "config": env_config, "status": EnvStatus(),
+                group_id = groups[i // self.group_size]
+                self.envs.append({"tag": tag, "group_id": group_id, "env_id": group_id * self.group_size + i % self.group_size,
+                                  "env": env_obj, "config": env_config, "status": EnvStatus(),
                                   "max_actions_per_traj": tpl.max_actions_per_traj})
             self.blocks.append(block)
-            done_groups += n_group
+        # env_id -> position in self.envs / self.rollout_cache (the identity when nothing is sharded away)
+        self._pos = {e["env_id"]: i for i, e in enumerate(self.envs)}
         self._block_of = {}
         for b in self.blocks:
             for i in range(b.count):
-                self._block_of[b.first + i] = b
+                self._block_of[self.envs[b.first + i]["env_id"]] = b
 
     # ---- observations ----------------------------------------------------------------------------------------
     def _block_texts(self, block) -> List[str]:
@@ -117,7 +126,7 @@ class EnvStateManager:
             seed = random.randint(0, 1000000) if seed is None else seed
         else:
             seed = 123
-        seeds = [seed + i // self.group_size for i in range(len(envs))]  # every env of a group shares the seed (:80-82)
+        seeds = [seed + e["group_id"] for e in envs]  # every env of a group shares the seed (:80-82)
         for block in self.blocks:
             bs = seeds[block.first:block.first + block.count]
             entries = envs[block.first:block.first + block.count]
@@ -155,7 +164,7 @@ class EnvStateManager:
         plans = []
         per_block = {}
         for env_input in all_env_inputs:
-            entry = envs[env_input["env_id"]]
+            entry = envs[self._pos[env_input["env_id"]]]
             left = entry["max_actions_per_traj"] - entry["status"].num_actions
             valid = self._extract_map_valid_actions(entry, env_input["actions"], env_input.get("action_codes"))
             todo = valid[:left] if left > 0 else []
@@ -171,12 +180,12 @@ class EnvStateManager:
         env_outputs = []
         texts = {id(b): self._block_texts(b) for b in self.blocks if id(b) in per_block}
         for i, (env_input, entry, valid, todo) in enumerate(plans):
-            env_id = entry["env_id"]
-            block = self._block_of[env_id]
+            block = self._block_of[entry["env_id"]]
+            pos = self._pos[entry["env_id"]]  # position in self.envs / self.rollout_cache
             acc_reward, turn_info, turn_done, n_exec = results[i]
             executed = todo[:n_exec]
             if len(valid) != len(env_input["actions"]) or not valid:
-                self.rollout_cache[env_id]["penalty"] += self.sys_config.es_manager.format_penalty
+                self.rollout_cache[pos]["penalty"] += self.sys_config.es_manager.format_penalty
             status = entry["status"]
             status.num_actions += len(executed)
             status.rewards.append(acc_reward)
@@ -185,16 +194,16 @@ class EnvStateManager:
                 status.terminated = True
                 status.truncated = not turn_info.get("success", False)
             history = self._update_cache_history(
-                self.rollout_cache[env_id]["history"], next_state=texts[id(block)][env_id - block.first], actions_left=actions_left,
+                self.rollout_cache[pos]["history"], next_state=texts[id(block)][pos - block.first], actions_left=actions_left,
                 num_actions_info={"actions": executed, "reward": acc_reward, "info": turn_info,
                                   "llm_response": env_input["llm_response"], "llm_raw_response": env_input["llm_raw_response"]})
             if status.num_actions >= entry["max_actions_per_traj"] and not turn_done:
                 status.truncated = True
                 status.terminated = True
                 turn_done = True
-            self.rollout_cache[env_id]["history"] = history
+            self.rollout_cache[pos]["history"] = history
             if not turn_done:
-                env_outputs.append(self.rollout_cache[env_id])
+                env_outputs.append(self.rollout_cache[pos])
         return env_outputs
 
     def _run_block(self, block, plans, idxs, results):
@@ -206,7 +215,7 @@ class EnvStateManager:
             act = np.zeros((block.count, K), dtype=np.uint8)
             nact = np.zeros(block.count, dtype=np.uint8)
             for env_input, entry, valid, todo in plans:
-                s = entry["env_id"] - block.first
+                s = self._pos[entry["env_id"]] - block.first
                 codes = [entry["env"].action_map[a] + 1 for a in todo] if block.env_type == "frozen_lake" else todo
                 act[s, :len(codes)] = codes
                 nact[s] = len(codes)
@@ -214,7 +223,7 @@ class EnvStateManager:
             host = torch.stack([out.done, out.flags, out.n_executed]).cpu().numpy()
             rew = out.reward.cpu().numpy()
             for i, (env_input, entry, valid, todo) in zip(idxs, plans):
-                s = entry["env_id"] - block.first
+                s = self._pos[entry["env_id"]] - block.first
                 n_exec, fl = int(host[2, s]), int(host[1, s])
                 info = {"action_is_effective": bool(fl & 1), "action_is_valid": True, "success": bool(fl & 2)} if n_exec else {}
                 results[i] = (float(rew[s]) if n_exec else 0, info, bool(host[0, s]), n_exec)
@@ -223,13 +232,13 @@ class EnvStateManager:
             on = np.zeros(block.count, dtype=np.uint8)
             for env_input, entry, valid, todo in plans:
                 if todo:
-                    s = entry["env_id"] - block.first
+                    s = self._pos[entry["env_id"]] - block.first
                     assert todo[0] in entry["env"].ACTION_LOOKUP, f"Invalid action: {todo[0]}"
                     act[s], on[s] = todo[0], 1
             rew, fl = b.step(torch.from_numpy(act).to(dev), torch.from_numpy(on).to(dev))
             rew, fl = rew.cpu().numpy(), fl.cpu().numpy()
             for i, (env_input, entry, valid, todo) in zip(idxs, plans):
-                s = entry["env_id"] - block.first
+                s = self._pos[entry["env_id"]] - block.first
                 if todo:
                     _, r, done, info = entry["env"].finish_step(todo[0], float(rew[s]), int(fl[s]))
                     results[i] = (0 + r, info, done, 1)

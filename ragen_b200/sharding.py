@@ -1,0 +1,99 @@
+"""Sharding of the rollout path over ranks (one process per GPU) and its only exchange.
+
+Env groups are independent: rank r owns the groups with `group_id % world_size == r`, keeps their state in
+its own HBM for the whole rollout and no env state ever moves.  What couples ranks is three sets of batch-global scalars:
+  (ii)  masked_whiten's moments (sum m, sum x*m, sum x^2*m)            verl/verl/utils/torch_functional.py:122-151
+  (iii) the rollout metrics (per-key sums / counts, response length)   ragen/llm_agent/ctx_manager.py:288, 308-329
+They travel as ONE float64 vector of fixed layout in a single all-reduce (NCCL on the GPUs, gloo in the CPU tests);
+at C5 that is 35 doubles.  Group reward normalisation with grouping="state" (ctx_manager.py:184-185) and GRPO's per-uid
+statistics need nothing: whole groups live on one rank.
+"""
+from typing import Dict, List, Sequence
+
+import numpy as np
+import torch
+
+INFO_KEYS = ("success", "num_actions", "action_is_effective", "action_is_valid")  # what the envs of this path report
+N_MOMENTS = 3
+_PER_KEY = 4  # sum, rows reporting the key, sum of non-zero values, count of non-zero values
+
+
+def world(group=None):
+    """(rank, world_size) of the default / given process group; (0, 1) when torch.distributed is not initialised."""
+    import torch.distributed as dist
+
+    if dist.is_available() and dist.is_initialized():
+        return dist.get_rank(group), dist.get_world_size(group)
+    return 0, 1
+
+
+def owned_groups(n_groups: int, rank: int, world_size: int) -> List[int]:
+    """Group ids of one rank, ascending.  Round-robin keeps every tag's block spread over all ranks."""
+    return list(range(rank, n_groups, world_size))
+
+
+def owned_env_ids(n_groups: int, group_size: int, rank: int, world_size: int) -> List[int]:
+    return [g * group_size + i for g in owned_groups(n_groups, rank, world_size) for i in range(group_size)]
+
+
+def metric_slots(tags: Sequence[str], extra_keys: Sequence[str] = ()) -> List[str]:
+    """The fixed key order of the exchange vector: every rank derives it from the config alone."""
+    keys = list(INFO_KEYS) + [k for k in extra_keys if k not in INFO_KEYS]
+    return [f"{t}/{k}" for t in dict.fromkeys(tags) for k in keys]
+
+
+class RolloutExchange:
+    """Packs this rank's partial sums, all-reduces them once, unpacks batch-global metrics and moments."""
+
+    def __init__(self, tags: Sequence[str], env_nums: Dict[str, int], extra_keys: Sequence[str] = (), group=None):
+        self.slots = metric_slots(tags, extra_keys)
+        self.index = {k: i for i, k in enumerate(self.slots)}
+        self.env_nums = dict(env_nums)  # GLOBAL number of envs per tag (ctx_manager.py:98-101)
+        self.group = group
+        self.size = _PER_KEY * len(self.slots) + 2 + N_MOMENTS
+
+    # layout: [per key: sum, present, nz_sum, nz_count] ... [response_mask tokens, rows] [moments x3]
+    def pack(self, env_outputs: List[Dict], response_tokens: float = 0.0, rows: int = 0, moments=None, device=None) -> torch.Tensor:
+        vec = np.zeros(self.size, dtype=np.float64)
+        for env_output in env_outputs:
+            for key, value in env_output["metrics"].items():
+                if key not in self.index:
+                    raise KeyError(f"metric {key!r} has no slot in the exchange vector; pass it in extra_keys")
+                o = _PER_KEY * self.index[key]
+                vec[o] += value
+                vec[o + 1] += 1
+                if value != 0:
+                    vec[o + 2] += value
+                    vec[o + 3] += 1
+        o = _PER_KEY * len(self.slots)
+        vec[o], vec[o + 1] = response_tokens, rows
+        out = torch.from_numpy(vec)
+        if device is not None:
+            out = out.to(device)
+        if moments is not None:
+            out[o + 2:] = moments.to(out.device, torch.float64)
+        return out
+
+    def all_reduce(self, vec: torch.Tensor) -> torch.Tensor:
+        import torch.distributed as dist
+
+        if dist.is_available() and dist.is_initialized() and dist.get_world_size(self.group) > 1:
+            dist.all_reduce(vec, group=self.group)
+        return vec
+
+    def unpack(self, vec: torch.Tensor):
+        """-> (metrics dict as ctx_manager.py:315-328 would give for the whole batch, moments float64[3])."""
+        v = vec.detach().cpu().numpy()
+        metrics = {}
+        for key, i in self.index.items():
+            s, present, nz_sum, nz_count = v[_PER_KEY * i:_PER_KEY * i + 4]
+            if present:
+                metrics[key] = s / self.env_nums[key.split("/")[0]]
+        for key, i in self.index.items():  # the non-zero keys follow the plain ones, as in the reference's dict order
+            s, present, nz_sum, nz_count = v[_PER_KEY * i:_PER_KEY * i + 4]
+            if present and nz_count:
+                prefix, suffix = key.split("/", 1)
+                metrics[f"{prefix}/non-zero/{suffix}"] = nz_sum / nz_count
+        o = _PER_KEY * len(self.slots)
+        metrics["response_length"] = float(v[o] / v[o + 1]) if v[o + 1] else 0.0
+        return metrics, vec[o + 2:]

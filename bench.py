@@ -32,6 +32,7 @@ if ROOT not in sys.path:
 
 H, W, NUM_BOXES, MAX_STEPS = 10, 10, 2, 100
 BYTES_PER_STEP = 3 * H * W + 1 + 10 + 8 + 1 + 1 + H * (W + 1)  # = 431, SURVEY.md 8(d) C4(ii)
+MOVED_PER_STEP = 2 * H * W + 2 * 8 + 1 + 8 + 1 + 1 + 1 + H * (W + 1)  # = 338: state r+w, 8-byte record r+w, action, results, glyph rows
 METRIC = "sokoban_env_steps_per_sec"
 UNIT = "env-steps/s"
 
@@ -302,7 +303,10 @@ def run_native(args):
                 "config": workload_config(world, n), "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                              "traffic": traffic, "kernel": "sokoban_tile_kernel<10,10,false>", "kernel_ms": kern_ms,
-                             "bytes_per_env_step": BYTES_PER_STEP, "peak_source": peak_src}}
+                             "bytes_per_env_step": BYTES_PER_STEP, "peak_source": peak_src,
+                             "bytes_moved_per_env_step": MOVED_PER_STEP, "frac_moved": MOVED_PER_STEP * n / (kern_ms * 1e-3) / 1e9 / peak,
+                             "note": "frac uses SURVEY.md 8(d)'s 431 B, which charges a 100 B room_fixed read the kernel avoids; "
+                                     "frac_moved uses the 338 B it has to move"}}
         if cpu_base is not None:
             line["cpu_baseline"] = cpu_base
         print(json.dumps(line), flush=True)

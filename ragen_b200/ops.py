@@ -174,25 +174,25 @@ class ParseResult:
         return out
 
 
-def parse_actions(responses, tables=None, table_id=None, enable_think=True, action_sep="||", max_actions=5, device=0):
-    """responses: list[str].  tables: ActionTables or None; table_id: int32 CUDA tensor [n] / list / None."""
-    dev = torch.device("cuda", int(device)) if not isinstance(device, torch.device) else device
-    ctx = _lib.Context.get(dev.index or 0)
+def stage_responses(responses, device):
+    """list[str] -> (raw bytes, offsets_np int64 [n+1], text u8 CUDA blob, offsets CUDA): the one host->device copy of a turn."""
     enc = [r.encode() for r in responses]
-    n = len(enc)
     raw = b"".join(enc)
-    offsets_np = np.zeros(n + 1, dtype=np.int64)
+    offsets_np = np.zeros(len(enc) + 1, dtype=np.int64)
     np.cumsum([len(e) for e in enc], out=offsets_np[1:])
-    text = torch.frombuffer(bytearray(raw or b"\0"), dtype=torch.uint8).to(dev)
-    offsets = torch.from_numpy(offsets_np).to(dev)
-    scratch = torch.empty_like(text)
-    flags = torch.empty(n, dtype=torch.uint8, device=dev)
-    spans = torch.empty((n, 4), dtype=torch.int32, device=dev)
-    act_spans = torch.empty((n, max_actions, 2), dtype=torch.int32, device=dev)
-    n_parsed = torch.empty(n, dtype=torch.uint8, device=dev)
-    n_total = torch.empty(n, dtype=torch.int32, device=dev)
-    codes = torch.empty((n, max_actions), dtype=torch.uint8, device=dev)
-    n_valid = torch.empty(n, dtype=torch.uint8, device=dev)
+    text = torch.frombuffer(bytearray(raw or b"\0"), dtype=torch.uint8).to(device)
+    return raw, offsets_np, text, torch.from_numpy(offsets_np).to(device)
+
+
+def parse_actions_device(text, offsets, tables=None, table_id=None, enable_think=True, action_sep="||", max_actions=5):
+    """ragen_parse_actions on a blob already in HBM.  Returns the dict of output tensors (all CUDA)."""
+    ctx = _ctx(text)
+    dev, n = text.device, offsets.numel() - 1
+    out = {"scratch": torch.empty_like(text), "flags": torch.empty(n, dtype=torch.uint8, device=dev),
+           "spans": torch.empty((n, 4), dtype=torch.int32, device=dev),
+           "act_spans": torch.empty((n, max_actions, 2), dtype=torch.int32, device=dev),
+           "n_parsed": torch.empty(n, dtype=torch.uint8, device=dev), "n_total": torch.empty(n, dtype=torch.int32, device=dev),
+           "codes": torch.empty((n, max_actions), dtype=torch.uint8, device=dev), "n_valid": torch.empty(n, dtype=torch.uint8, device=dev)}
     tid = None
     if table_id is not None:
         tid = torch.as_tensor(table_id, dtype=torch.int32).to(dev).contiguous()
@@ -200,10 +200,19 @@ def parse_actions(responses, tables=None, table_id=None, enable_think=True, acti
     _lib.check(ctx.lib.ragen_parse_actions(
         ctx.handle, n, _lib.ptr(text), _lib.ptr(offsets), int(bool(enable_think)), action_sep.encode(), int(max_actions),
         _lib.ptr(t.names) if t else None, _lib.ptr(t.name_off) if t else None, _lib.ptr(t.codes) if t else None,
-        _lib.ptr(t.first) if t else None, t.n_tables if t else 0, _lib.ptr(tid), _lib.ptr(scratch), _lib.ptr(flags),
-        _lib.ptr(spans), _lib.ptr(act_spans), _lib.ptr(n_parsed), _lib.ptr(n_total), _lib.ptr(codes), _lib.ptr(n_valid),
-        ctx.stream()))
-    res = ParseResult(raw, offsets_np, scratch, flags, spans, act_spans, n_parsed, n_total, codes, n_valid, enable_think, action_sep)
+        _lib.ptr(t.first) if t else None, t.n_tables if t else 0, _lib.ptr(tid), _lib.ptr(out["scratch"]), _lib.ptr(out["flags"]),
+        _lib.ptr(out["spans"]), _lib.ptr(out["act_spans"]), _lib.ptr(out["n_parsed"]), _lib.ptr(out["n_total"]), _lib.ptr(out["codes"]),
+        _lib.ptr(out["n_valid"]), ctx.stream()))
+    return out
+
+
+def parse_actions(responses, tables=None, table_id=None, enable_think=True, action_sep="||", max_actions=5, device=0):
+    """responses: list[str].  tables: ActionTables or None; table_id: int32 CUDA tensor [n] / list / None."""
+    dev = torch.device("cuda", int(device)) if not isinstance(device, torch.device) else device
+    raw, offsets_np, text, offsets = stage_responses(responses, dev)
+    o = parse_actions_device(text, offsets, tables, table_id, enable_think, action_sep, max_actions)
+    res = ParseResult(raw, offsets_np, o["scratch"], o["flags"], o["spans"], o["act_spans"], o["n_parsed"], o["n_total"], o["codes"],
+                      o["n_valid"], enable_think, action_sep)
     res.text, res.offsets = text, offsets
     return res
 

@@ -1,0 +1,293 @@
+#!/usr/bin/env python
+"""Per-kernel measurement of every config of SURVEY.md 8(d) (C1..C5) on ONE B200, one JSON line per row.
+
+    python scripts/bench_kernels.py [--out profiles/rNN_kernels.jsonl] [--quick]
+
+bench.py is the contract line (C4 step); this script is the supporting evidence for the other rows: each line carries
+the kernel's device time (CUDA events on the launching stream, after warm-up, median of the repetitions), the
+algorithmic bytes per unit, achieved GB/s against MEASURED_PEAKS.json, and the CPU port of the
+reference (oracle/, single core, bounded sample) timed beside it.  Rows whose working set is a few hundred KB are
+launch-latency-bound: they are reported as microseconds per call and their roofline fraction is not a quality claim.
+"""
+import argparse
+import json
+import os
+import sys
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+from ragen_b200 import ops  # noqa: E402
+from ragen_b200 import synth  # noqa: E402
+
+
+def peak_gbs():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    return float(json.load(open(p))["hbm_gbs"]) if os.path.exists(p) else 6650.0
+
+
+def dev_time(fn, reps=20, warm=3):
+    """median milliseconds of fn() by CUDA events on the current stream."""
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    ts = []
+    for _ in range(reps):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        fn()
+        b.record()
+        torch.cuda.synchronize()
+        ts.append(a.elapsed_time(b))
+    return float(np.median(ts))
+
+
+def cpu_time(fn, budget_s=5.0, min_reps=1):
+    t0 = time.perf_counter()
+    reps = 0
+    while reps < min_reps or time.perf_counter() - t0 < budget_s:
+        fn()
+        reps += 1
+        if reps >= 50:
+            break
+    return (time.perf_counter() - t0) / reps
+
+
+def line(row, unit, units, ms, bytes_per_unit, cpu_units_per_s=None, cpu_sample=None, **extra):
+    ach = bytes_per_unit * units / (ms * 1e-3) / 1e9 if bytes_per_unit else None
+    out = {"row": row, "unit": unit, "units_per_launch": units, "ms": ms, "units_per_s": units / (ms * 1e-3),
+           "bytes_per_unit": bytes_per_unit, "achieved_gbs": ach, "peak_gbs": peak_gbs(), "frac": ach / peak_gbs() if ach else None,
+           "cpu_port_units_per_s": cpu_units_per_s, "cpu_sample": cpu_sample}
+    out.update(extra)
+    print(json.dumps(out), flush=True)
+    return out
+
+
+# ---- C4(ii) / C1 step shapes: Sokoban step at several sizes -----------------------------------------------------------
+def sokoban_rows(quick):
+    from oracle import sokoban as S
+    from ragen_b200.env.sokoban import SokobanBatch
+
+    rows = []
+    for (H, W, nb, n, K, tag) in [(10, 10, 2, 1 << 20, 1, "C4 step 10x10 K=1"), (10, 10, 2, 1 << 20, 5, "C4 turn-fused 10x10 K=5"),
+                                  (6, 6, 1, 1 << 20, 1, "6x6 K=1 at 1Mi envs"), (6, 6, 1, 128, 5, "C1 shape 6x6 128 envs K=5")]:
+        if quick and n > 1 << 18:
+            n = 1 << 18
+        fixed, state = synth.synthetic_rooms(n, H, W, nb, seed=4)
+        b = SokobanBatch(n, (H, W), nb, 100, device=0)
+        b.load_rooms(fixed, state)
+        g = torch.Generator(device="cuda").manual_seed(1)
+        acts = torch.randint(1, 5, (4, n, K), dtype=torch.uint8, device="cuda", generator=g)
+        i = [0]
+
+        def step():
+            b.step(acts[i[0] % 4])
+            i[0] += 1
+        ms = dev_time(step, reps=50 if n > 1000 else 200)
+        per_step = 3 * H * W + 1 + 10 + 8 + 1 + 1 + H * (W + 1)
+        per_turn = per_step if K == 1 else (per_step - 1 + K)      # "(170+K)/K per env-step" variant: one render per turn
+        # CPU port: the reference's per-env Python loop on a bounded sample
+        m = 2048 if n > 2048 else n
+        envs = []
+        for j in range(m):
+            e = S.SokobanOracle((H, W), nb, 100)
+            e.load(fixed[j], state[j])
+            envs.append(e)
+        a_host = acts[0, :m].cpu().numpy()
+
+        def cpu():
+            for e, row in zip(envs, a_host):
+                for a in row:
+                    e.step(int(a))
+        cs = cpu_time(cpu, 3.0)
+        rows.append(line(tag, "env-step", n * K, ms, per_turn / K, m * K / cs, f"{m} envs x {K} actions, oracle/sokoban.py, 1 core",
+                         envs=n, K=K, kernel="sokoban_tile_kernel"))
+        del b
+    return rows
+
+
+# ---- C4(i): room generator -------------------------------------------------------------------------------------------
+def generator_rows(quick):
+    from ragen_b200.env.sokoban import SokobanBatch
+
+    rows = []
+    for (H, W, nb, depth, n, tag) in [(6, 6, 1, 300, 8192, "6x6/1 box depth 300"), (8, 8, 2, 10, 8192, "8x8/2 boxes depth 10"),
+                                      (10, 10, 2, 300, 2048 if quick else 16384, "C4 reset 10x10/2 boxes depth 300")]:
+        b = SokobanBatch(1, (H, W), nb, 100, depth, device=0)
+        seeds = list(range(n))
+        t0 = time.perf_counter()
+        _, _, st, explored = b.generate(seeds)
+        torch.cuda.synchronize()
+        first = time.perf_counter() - t0
+        ms = dev_time(lambda: b.generate(seeds), reps=3, warm=0)
+        ok = float((st == 0).float().mean())
+        rows.append(line(tag, "room", n, ms, 2 * H * W + 2, None, "reference: 4 ms/room (6x6), 1.0 s/room (10x10) on one core (SURVEY.md section 0)",
+                         valid_fraction=ok, mean_explored=float(explored.float().mean()), first_call_s=first, kernel="sokoban_generate_kernel",
+                         note="no roofline claim: on-chip search, output bytes only"))
+        del b
+    return rows
+
+
+# ---- C2: FrozenLake ----------------------------------------------------------------------------------------------------
+def frozenlake_rows(quick):
+    from oracle import toy_envs as TE
+    from ragen_b200.env.frozen_lake import FrozenLakeBatch
+
+    rows = []
+    for n, tag in [(1024, "C2 FrozenLake 4x4 slippery, 1024 envs"), (1 << 18 if quick else 1 << 20, "FrozenLake 4x4 slippery at 1Mi envs")]:
+        b = FrozenLakeBatch(n, 4, 0.8, True, device=0)
+        seeds = np.arange(n)
+        ms_reset = dev_time(lambda: b.reset(seeds, check=False), reps=5, warm=1)
+        g = torch.Generator(device="cuda").manual_seed(2)
+        acts = torch.randint(1, 5, (4, n, 1), dtype=torch.uint8, device="cuda", generator=g)
+        i = [0]
+
+        def step():
+            b.step(acts[i[0] % 4])
+            i[0] += 1
+        ms = dev_time(step, reps=100)
+        m = min(n, 1024)
+        envs = [TE.FrozenLakeOracle() for _ in range(m)]
+        for j, e in enumerate(envs):
+            e.reset(j)
+        a_host = (acts[0, :m, 0].cpu().numpy() - 1).tolist()
+
+        def cpu():
+            for e, a in zip(envs, a_host):
+                e.step(a + 1)
+                e.render()
+        cs = cpu_time(cpu, 2.0)
+        rows.append(line(tag, "env-step", n, ms, 109, m / cs, f"{m} envs x 1 step + render, oracle/toy_envs.py, 1 core", envs=n,
+                         reset_ms=ms_reset, kernel="frozenlake_kernel<STEP>"))
+    return rows
+
+
+# ---- C3: parse + Bandit / Countdown scoring ----------------------------------------------------------------------------
+def parse_rows(quick):
+    from oracle import managers as M
+    from oracle import toy_envs as TE
+
+    nb = nc = 2048 if quick else 8192
+    corpus = synth.synthetic_responses(nb, nc, seed=3)
+    responses = corpus["responses"] if isinstance(corpus, dict) else corpus[0]
+    dev = torch.device("cuda", 0)
+    raw, off_np, text, offsets = ops.stage_responses(responses, dev)
+    tables = ops.ActionTables([{1: "Phoenix", 2: "Dragon"}], dev)
+    tid = torch.tensor([0] * nb + [-1] * nc, dtype=torch.int32, device=dev)
+    ms = dev_time(lambda: ops.parse_actions_device(text, offsets, tables, tid, True, "||", 1), reps=30)
+    ms_e2e = dev_time(lambda: ops.parse_actions(responses, tables, tid, True, "||", 1, dev).to_host(), reps=3, warm=1)
+    m = 2048
+    cs = cpu_time(lambda: [M.parse_response(r, True, "||", 1) for r in responses[:m]], 3.0)
+    n = len(responses)
+    return [line("C3 parse + action lookup, 16k responses", "response", n, ms, len(raw) / n + 24, m / cs,
+                 f"{m} responses, re-based oracle/managers.py:parse_response, 1 core", mean_response_bytes=len(raw) / n,
+                 e2e_ms_with_staging_and_host_strings=ms_e2e, kernel="parse_kernel")]
+
+
+# ---- C5: trajectory tensors + advantage ----------------------------------------------------------------------------------
+def c5_rows(quick):
+    from oracle import advantage as A
+    from oracle import managers as M
+
+    rows = []
+    for B, L, tag in [(128, 2048, "C5 B=128 L=2048"), (2048 if quick else 8192, 2048, "B=8192 L=2048 (bandwidth regime)")]:
+        rng = np.random.default_rng(5)
+        ids = np.full((B, L), 151643, dtype=np.int64)
+        scores = np.zeros((B, 5))
+        nt = np.zeros(B, dtype=np.int32)
+        for b in range(B):
+            seq = [151644] + [7] * 20 + [151645, 198]
+            k = int(rng.integers(1, 6))
+            for _ in range(k):
+                seq += [151644] + [9] * int(rng.integers(100, 180)) + [151645, 198]
+                seq += [151644] + [11] * int(rng.integers(20, 160)) + [151645, 198]
+            seq = seq[-L:]
+            ids[b, L - len(seq):] = seq
+            nt[b] = k
+            scores[b, :k] = rng.integers(-2, 11, k) * 0.1
+        d_ids, d_sc, d_nt = torch.from_numpy(ids).cuda(), torch.from_numpy(scores).cuda(), torch.from_numpy(nt).cuda()
+        ms = dev_time(lambda: ops.masks_scores(d_ids, d_sc, d_nt, 151644, 151645, False, True, True), reps=50)
+        t_ids = torch.from_numpy(ids[:128])
+        sc_list = [scores[b, :nt[b]].tolist() for b in range(128)]
+        cs = cpu_time(lambda: M.masks_and_scores(t_ids, sc_list, 151644, 151645), 2.0)
+        rows.append(line(f"masks+scores {tag}", "token", B * L, ms, 14, 128 * L / cs, "128 rows, torch CPU oracle (all host threads)", kernel="masks_scores_kernel"))
+        sc, lm, rm = ops.masks_scores(d_ids, d_sc, d_nt, 151644, 151645, False, True, True)
+        T = L - 1
+        mask = lm.float()
+        rewards = sc.clone()
+        values = torch.randn(B, T, device="cuda") * mask
+        ms_raw = dev_time(lambda: ops.gae_raw(rewards, values, lm, 1.0, 1.0), reps=50)
+
+        def full():
+            adv, ret, mom = ops.gae_raw(rewards, values, lm, 1.0, 1.0)
+            ops.whiten_(adv, mom, check=False)
+        ms_full = dev_time(full, reps=50)
+        r_c, v_c, m_c = rewards[:128].cpu(), values[:128].cpu(), mask[:128].cpu()
+        cs = cpu_time(lambda: A.gae(r_c, v_c, m_c, 1.0, 1.0), 3.0)
+        rows.append(line(f"GAE+whiten {tag}", "token", B * T, ms_full, 25, 128 * T / cs, "128 rows, torch CPU loop as the reference (all host threads)",
+                         gae_only_ms=ms_raw, kernel="gae_kernel + whiten_kernel"))
+        # bi-level needs a reward on the last loss-mask position
+        r2 = torch.zeros_like(rewards)
+        last = (mask * torch.arange(1, T + 1, device="cuda")).argmax(dim=1)
+        r2[torch.arange(B), last] = 1.0
+        ms_bi = dev_time(lambda: ops.bilevel_gae_raw(r2, values, lm, 1.0, 1.0, 0.95), reps=50)
+        r2c = r2[:16].cpu()
+        cs = cpu_time(lambda: A.bilevel_gae(r2c, v_c[:16], m_c[:16], 1.0, 1.0, 0.95), 3.0)
+        rows.append(line(f"bi-level GAE {tag}", "token", B * T, ms_bi, 17, 16 * T / cs, "16 rows, oracle/advantage.py loop as the reference", kernel="bilevel_gae_kernel"))
+        gi = torch.arange(B, device="cuda", dtype=torch.int32) // 16
+        ms_g = dev_time(lambda: ops.grpo_outcome(rewards, lm, gi, B // 16), reps=50)
+        rows.append(line(f"GRPO {tag}", "token", B * T, ms_g, 9, None, None, kernel="grpo_scores_kernel + grpo_apply_kernel"))
+        pen = torch.zeros(B, device="cuda")
+        ms_n = dev_time(lambda: ops.group_norm(sc[:, -1], pen, gi, B // 16, "mean_std"), reps=50)
+        rows.append(line(f"group reward norm {tag}", "row", B, ms_n, 16, None, None, kernel="norm_stats_kernel + norm_apply_kernel"))
+    return rows
+
+
+# ---- C1: the manager seam (host + device) ----------------------------------------------------------------------------------
+def manager_rows(quick):
+    from oracle import cfg as C
+    from ragen_b200.llm_agent.es_manager import EnvStateManager
+
+    cfg = C.base_config(tags=("SimpleSokoban",), n_groups=(8,), group_size=16)
+    mgr = EnvStateManager(cfg, mode="train")
+    t0 = time.perf_counter(); mgr.reset(seed=123); torch.cuda.synchronize(); first = time.perf_counter() - t0
+    t0 = time.perf_counter(); cache = mgr.reset(seed=123); torch.cuda.synchronize(); reset_s = time.perf_counter() - t0
+    rng = np.random.default_rng(1)
+    names = ["Up", "Down", "Left", "Right"]
+    alive = [c["env_id"] for c in cache]
+    turn_s, steps = [], 0
+    for _ in range(5):
+        inputs = []
+        for e in alive:
+            acts = [names[int(rng.integers(0, 4))] if rng.random() > 0.1 else "Jump" for _ in range(int(rng.integers(1, 4)))]
+            resp = "<think>t</think><answer>" + " || ".join(acts) + "</answer>"
+            inputs.append({"env_id": e, "llm_raw_response": resp, "llm_response": resp, "actions": acts})
+        t0 = time.perf_counter()
+        out = mgr.step(inputs)
+        turn_s.append(time.perf_counter() - t0)
+        steps += sum(len(i["actions"]) for i in inputs)
+        alive = [c["env_id"] for c in out]
+        if not alive:
+            break
+    print(json.dumps({"row": "C1 EnvStateManager 128 envs x 5 turns (wall clock, host + device)", "reset_s": reset_s, "first_reset_s": first,
+                      "turn_ms": [1e3 * t for t in turn_s], "env_steps": steps,
+                      "note": "latency-bound: 9 KB of state; the Python history bookkeeping the API promises dominates"}), flush=True)
+
+
+if __name__ == "__main__":
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--quick", action="store_true")
+    ap.add_argument("--only", default="")
+    a = ap.parse_args()
+    torch.cuda.set_device(0)
+    todo = {"sokoban": sokoban_rows, "generator": generator_rows, "frozenlake": frozenlake_rows, "parse": parse_rows, "c5": c5_rows,
+            "manager": manager_rows}
+    for name, fn in todo.items():
+        if a.only and name not in a.only.split(","):
+            continue
+        fn(a.quick)

@@ -201,7 +201,17 @@ def cpu_baseline_subprocess(args):
         return {"value": None, "unit": UNIT, "cores": 0, "kind": "port", "sample": f"failed: {e!r}"}
 
 
+def _claim_stdout():
+    """Keeps the real stdout for the ONE JSON line; whatever libraries print to fd 1 meanwhile (NCCL's version banner at
+    communicator creation, for one) goes to stderr."""
+    sys.stdout.flush()
+    keep = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    return keep
+
+
 def run_native(args):
+    out = _claim_stdout()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -309,7 +319,7 @@ def run_native(args):
                                      "frac_moved uses the 338 B it has to move"}}
         if cpu_base is not None:
             line["cpu_baseline"] = cpu_base
-        print(json.dumps(line), flush=True)
+        print(json.dumps(line), file=out, flush=True)
     if world > 1:
         dist.destroy_process_group()
     return 0

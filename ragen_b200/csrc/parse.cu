@@ -17,6 +17,7 @@
 namespace {
 
 constexpr int PWARPS = 4;
+constexpr int CLEAN_CAP = 4096;  // bytes of shared memory per warp for cleaning a span
 using parse::MAX_ACTIONS;
 
 struct ParseParams {
@@ -41,21 +42,53 @@ struct ParseParams {
   uint8_t* n_valid;
 };
 
-// any special string starting inside text[s, e)?  (warp-cooperative)
-__device__ __forceinline__ bool warp_has_special(const uint8_t* text, int s, int e, int lane) {
-  bool any = false;
+// One replace pass of ctx_manager.py:162-164 ("content.replace(tag, '')") on scr[s, e), warp-cooperative and in place:
+// 32 bytes per iteration, occurrences found by ballot (they cannot overlap: every special string has its only '<' at
+// the front), survivors compacted with a popcount prefix.  Reads run ahead of writes (w <= r), and every lane has
+// read and classified its byte before any lane writes.  Returns the new end.
+__device__ __forceinline__ int warp_remove_tag(uint8_t* scr, int s, int e, int tag, int lane) {
+  const int L = parse::tag_len(tag);
+  // most passes find nothing to remove: look for the first occurrence with a loop that only reads
+  int first = -1;
+  for (int b = s; b < e && first < 0; b += 32) {
+    const int i = b + lane;
+    const bool st = i < e && scr[i] == '<' && parse::classify_tag(scr + i, scr + e) == tag;
+    const unsigned hit = __ballot_sync(0xffffffffu, st);
+    if (hit) first = b + __ffs(hit) - 1;
+  }
+  if (first < 0) return e;
+  s = first;  // nothing moves before it
+  int w = s, carry = 0;  // carry: bytes of an occurrence that spill into this chunk
   for (int b = s; b < e; b += 32) {
     const int i = b + lane;
-    const bool hit = i < e && text[i] == '<' && parse::classify_tag(text + i, text + e) != parse::T_NONE;
-    if (__ballot_sync(0xffffffffu, hit)) {
-      any = true;
-      break;
+    const uint8_t c = i < e ? scr[i] : 0;
+    const bool st = i < e && c == '<' && parse::classify_tag(scr + i, scr + e) == tag;
+    unsigned starts = __ballot_sync(0xffffffffu, st);
+    const unsigned valid = (e - b >= 32) ? 0xffffffffu : ((1u << (e - b)) - 1u);
+    unsigned del = carry >= 32 ? 0xffffffffu : ((1u << carry) - 1u);
+    carry = carry > 32 ? carry - 32 : 0;
+    while (starts) {
+      const int j = __ffs(starts) - 1;
+      starts &= starts - 1;
+      del |= (L >= 32 - j) ? (0xffffffffu << j) : (((1u << L) - 1u) << j);
+      if (j + L > 32) carry = j + L - 32;
     }
+    const unsigned keep = valid & ~del;
+    __syncwarp();
+    if ((keep >> lane) & 1u) scr[w + __popc(keep & ((1u << lane) - 1u))] = c;
+    w += __popc(keep);
+    __syncwarp();
   }
-  return any;
+  return w;
+}
+
+__device__ __forceinline__ unsigned lt_mask4(unsigned word) {  // bit k set iff byte k of word is '<'
+  const unsigned y = __vcmpeq4(word, 0x3c3c3c3cu) & 0x01010101u;
+  return ((y * 0x01020408u) >> 24) & 0xfu;
 }
 
 __global__ void __launch_bounds__(PWARPS * 32) parse_kernel(const ParseParams p) {
+  __shared__ uint8_t stage[PWARPS][CLEAN_CAP];
   const int lane = threadIdx.x & 31;
   const int64_t r = (int64_t)blockIdx.x * PWARPS + (threadIdx.x >> 5);
   if (r >= p.n) return;
@@ -64,18 +97,57 @@ __global__ void __launch_bounds__(PWARPS * 32) parse_kernel(const ParseParams p)
   const uint8_t* text = p.text + off;
 
   // ---- regex search over the tag occurrences ----------------------------------------------------------------
+  // The response is read once, 16 bytes per lane per step (512 B per warp step) from the 16-byte aligned address
+  // below it; bytes outside [0, n) are masked.  '<' bytes are rare: their positions come out of a SIMD byte compare,
+  // and only those are classified and fed, in text order, to the state machine that every lane advances identically.
+  // The first 32 special-string occurrences are remembered, one per lane, for the has-special test further down.
   parse::Matcher m;
   parse::matcher_init(m, p.enable_think != 0);
-  for (int b = 0; b < n && m.state != 3; b += 32) {
-    const int i = b + lane;
-    int tag = parse::T_NONE;
-    if (i < n && text[i] == '<') tag = parse::classify_tag(text + i, text + n);
-    unsigned hits = __ballot_sync(0xffffffffu, tag != parse::T_NONE);
-    while (hits) {
-      const int l = __ffs(hits) - 1;
-      hits &= hits - 1;
-      const int t = __shfl_sync(0xffffffffu, tag, l);
-      if (parse::matcher_feed(m, text, n, b + l, t)) break;
+  const int a0 = (int)((uintptr_t)text & 15);
+  const uint4* vbase = reinterpret_cast<const uint4*>(text - a0);
+  const int nvec = (a0 + n + 15) >> 4;
+  const uint8_t* blob_end = p.text + p.offsets[p.n];
+  int occ_pos = -1, occ_len = 0, n_occ = 0;
+  for (int vb = 0; vb < nvec && m.state != 3; vb += 32) {
+    const int vi = vb + lane;
+    unsigned mask = 0;
+    if (vi < nvec) {
+      const uint8_t* vp = reinterpret_cast<const uint8_t*>(vbase + vi);
+      uint4 v;
+      if (vp + 16 <= blob_end) {
+        v = __ldg(vbase + vi);
+      } else {  // the last 16 bytes of the whole blob may not be there to read as a vector
+        unsigned w[4] = {0, 0, 0, 0};
+        for (int k = 0; k < 16 && vp + k < blob_end; ++k) w[k >> 2] |= (unsigned)vp[k] << (8 * (k & 3));
+        v = make_uint4(w[0], w[1], w[2], w[3]);
+      }
+      mask = lt_mask4(v.x) | (lt_mask4(v.y) << 4) | (lt_mask4(v.z) << 8) | (lt_mask4(v.w) << 12);
+      const int lo = vi * 16 - a0;  // text offset of this lane's byte 0
+      if (lo < 0) mask &= 0xffffu << (-lo);
+      if (lo + 16 > n) mask &= (n - lo >= 16) ? 0xffffu : ((1u << (n - lo > 0 ? n - lo : 0)) - 1u);
+    }
+    unsigned lanes = __ballot_sync(0xffffffffu, mask != 0);
+    bool matched = false;
+    while (lanes && !matched) {
+      const int l = __ffs(lanes) - 1;
+      lanes &= lanes - 1;
+      unsigned bits = __shfl_sync(0xffffffffu, mask, l);
+      while (bits) {
+        const int k = __ffs(bits) - 1;
+        bits &= bits - 1;
+        const int pos = (vb + l) * 16 - a0 + k;
+        const int tag = parse::classify_tag(text + pos, text + n);
+        if (tag == parse::T_NONE) continue;
+        if (lane == n_occ) {
+          occ_pos = pos;
+          occ_len = parse::tag_len(tag);
+        }
+        ++n_occ;
+        if (parse::matcher_feed(m, text, n, pos, tag)) {
+          matched = true;
+          break;
+        }
+      }
     }
   }
 
@@ -94,14 +166,30 @@ __global__ void __launch_bounds__(PWARPS * 32) parse_kernel(const ParseParams p)
     for (int which = 0; which < 2; ++which) {
       int s = which ? ans_s : think_s, e = which ? ans_e : think_e;
       if (which == 0 && !p.enable_think) continue;
-      if (warp_has_special(text, s, e, lane)) {
+      // any special string lying wholly inside [s, e)?  All of them were seen by the scan (they start before the match end)
+      bool special = __ballot_sync(0xffffffffu, occ_pos >= s && occ_pos + occ_len <= e) != 0;
+      if (n_occ > 32 && !special) special = parse::has_special(text, s, e);  // more occurrences than remembered: look again
+      if (special) {
+        // the span is staged in shared memory for the six passes (each sweeps it once); longer spans are cleaned in
+        // the scratch blob itself
         uint8_t* scr = p.scratch + off;
-        for (int i = s + lane; i < e; i += 32) scr[i] = text[i];
+        const int len = e - s;
+        const bool staged = len <= CLEAN_CAP;
+        uint8_t* buf = staged ? stage[threadIdx.x >> 5] : scr + s;
+#pragma unroll 4
+        for (int i = lane; i < len; i += 32) buf[i] = text[s + i];
         __syncwarp();
-        if (lane == 0) parse::clean_content(scr, s, e);
-        __syncwarp();
-        s = __shfl_sync(0xffffffffu, s, 0);
-        e = __shfl_sync(0xffffffffu, e, 0);
+        int cs = 0, ce = len;
+        for (int tag = parse::T_THINK; tag <= parse::T_IM_END; ++tag) {  // six passes, each followed by strip (:162-164)
+          ce = warp_remove_tag(buf, cs, ce, tag, lane);
+          parse::strip(buf, cs, ce);
+        }
+        if (staged) {
+          for (int i = cs + lane; i < ce; i += 32) scr[s + i] = buf[i];
+          __syncwarp();
+        }
+        e = s + ce;
+        s = s + cs;
         fl |= which ? 4 : 2;
         if (which) abuf = scr;
       } else {

@@ -184,11 +184,12 @@ def stage_responses(responses, device):
     return raw, offsets_np, text, torch.from_numpy(offsets_np).to(device)
 
 
-def parse_actions_device(text, offsets, tables=None, table_id=None, enable_think=True, action_sep="||", max_actions=5):
-    """ragen_parse_actions on a blob already in HBM.  Returns the dict of output tensors (all CUDA)."""
+def parse_actions_device(text, offsets, tables=None, table_id=None, enable_think=True, action_sep="||", max_actions=5, out=None):
+    """ragen_parse_actions on a blob already in HBM.  Returns the dict of output tensors (all CUDA); pass a previous
+    result as `out` to write into the same buffers again."""
     ctx = _ctx(text)
     dev, n = text.device, offsets.numel() - 1
-    out = {"scratch": torch.empty_like(text), "flags": torch.empty(n, dtype=torch.uint8, device=dev),
+    out = out or {"scratch": torch.empty_like(text), "flags": torch.empty(n, dtype=torch.uint8, device=dev),
            "spans": torch.empty((n, 4), dtype=torch.int32, device=dev),
            "act_spans": torch.empty((n, max_actions, 2), dtype=torch.int32, device=dev),
            "n_parsed": torch.empty(n, dtype=torch.uint8, device=dev), "n_total": torch.empty(n, dtype=torch.int32, device=dev),

@@ -215,6 +215,41 @@ int ragen_grpo_outcome(ragen_ctx* ctx, int B, int T, const float* rewards, const
                        const int32_t* group, int n_groups, double epsilon, int norm_by_std, float* scores,
                        float* adv, void* stream);
 
+/* ---- the rest of compute_advantage's dispatch table and its neighbours ---------------- */
+/* Outcome estimators over per-group statistics of the row scores (scores[b] = sum_t rewards[b][t]), broadcast
+ * over the row and multiplied by the mask.  mode 0: score - mean; 1: GRPO (as ragen_grpo_outcome); 2: RLOO
+ * (compute_rloo_outcome_advantage, verl core_algos.py:205-242: score*n/(n-1) - mean*n/(n-1) for groups of n > 1);
+ * 3: REINFORCE++-baseline before its whitening (compute_reinforce_plus_plus_baseline_outcome_advantage, :168-202:
+ * score - mean; the caller whitens adv in place with ragen_whiten from `moments`).  Groups of one use mean 0.
+ * moments (may be NULL) = masked moments of adv (double[3], zeroed by the call). */
+int ragen_outcome_advantage(ragen_ctx* ctx, int B, int T, const float* rewards, const uint8_t* mask,
+                            const int32_t* group, int n_groups, int mode, double epsilon, float* scores, float* adv,
+                            double* moments, void* stream);
+
+/* compute_reinforce_plus_plus_outcome_advantage (verl core_algos.py:245-278), first half: discounted returns with the
+ * running value reset after masked-out tokens, fp32 in the reference's order, plus their masked moments.  The
+ * advantages are ragen_whiten_masked(ret, mask, moments): masked_whiten(returns) * mask (:275-276). */
+int ragen_discounted_returns(ragen_ctx* ctx, int B, int T, const float* rewards, const uint8_t* mask, double gamma,
+                             float* ret, double* moments, void* stream);
+int ragen_whiten_masked(ragen_ctx* ctx, int64_t n, const float* x, const uint8_t* mask, const double* moments,
+                        float* out, void* stream);
+
+/* compute_remax_outcome_advantage (verl core_algos.py:281-305): ret = reverse cumulative sum of rewards*mask,
+ * adv = ret - baselines[b]*mask. */
+int ragen_remax(ragen_ctx* ctx, int B, int T, const float* rewards, const uint8_t* mask, const float* baselines,
+                float* adv, float* ret, void* stream);
+
+/* apply_kl_penalty (verl/verl/trainer/ppo/ray_trainer.py:145-175) with kl_penalty (verl core_algos.py:469-501):
+ * kld = f(logp, ref_logp) * mask with mode 0 "kl", 1 "abs", 2 "mse", 3 "low_var_kl"; rewards_out = scores - beta*kld;
+ * row_kl[b] (may be NULL) = sum_t kld / (sum_t mask + 1e-8), whose mean over rows is the controller's current_kl. */
+int ragen_kl_rewards(ragen_ctx* ctx, int B, int T, const float* scores, const float* logp, const float* ref_logp,
+                     const uint8_t* mask, int mode, double beta, float* rewards_out, float* row_kl, void* stream);
+
+/* _filter_rollout's statistics (ragen/trainer/agent_trainer.py:466-469): row_sum[b] = sum_t scores[b][t] for
+ * b in [0, n_groups*group_size) and, per group of group_size consecutive rows, unbiased std / max / mean. */
+int ragen_group_filter_stats(ragen_ctx* ctx, int n_groups, int group_size, int T, const float* scores, float* row_sum,
+                             float* gstd, float* gmax, float* gmean, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -9,7 +9,9 @@ Follows
   * verl/verl/trainer/ppo/core_algos.py:113-165   compute_grpo_outcome_advantage
   * verl/verl/utils/torch_functional.py:117-151   masked_mean / masked_var / masked_whiten
   * ragen/trainer/core_algos.py:4-92              compute_bi_level_gae_advantage_return
-  * ragen/trainer/agent_trainer.py:461-500        _filter_rollout group statistics
+  * ragen/trainer/agent_trainer.py:461-500        _filter_rollout group statistics + selection
+  * verl/verl/trainer/ppo/core_algos.py:168-305   RF++-baseline, RLOO, RF++, ReMax
+  * verl/verl/trainer/ppo/core_algos.py:469-501, verl/verl/trainer/ppo/ray_trainer.py:145-175   kl_penalty / apply_kl_penalty
 """
 import torch
 
@@ -103,3 +105,90 @@ def group_filter_stats(original_scores, num_groups, group_size):
     """agent_trainer.py:466-470: per-group std / max / mean of summed scores."""
     s = original_scores.sum(dim=-1).view(num_groups, group_size)
     return s.std(dim=-1), s.max(dim=-1).values, s.mean(dim=-1)
+
+
+def _group_rows(index):
+    groups = {}
+    for i, key in enumerate(index):
+        groups.setdefault(key, []).append(i)
+    return groups
+
+
+def rloo(rewards, mask, index):
+    """compute_rloo_outcome_advantage (core_algos.py:205-242)."""
+    scores = rewards.float().sum(dim=-1)
+    out = scores.clone()
+    for rows in _group_rows(index).values():
+        n = len(rows)
+        if n > 1:
+            mean = torch.mean(scores[torch.tensor(rows)])
+            for i in rows:
+                out[i] = scores[i] * n / (n - 1) - mean * n / (n - 1)
+    return out.unsqueeze(-1) * mask
+
+
+def rfpp_baseline(rewards, mask, index):
+    """compute_reinforce_plus_plus_baseline_outcome_advantage (core_algos.py:168-202)."""
+    scores = rewards.float().sum(dim=-1)
+    out = scores.clone()
+    for rows in _group_rows(index).values():
+        mean = torch.mean(scores[torch.tensor(rows)]) if len(rows) > 1 else torch.tensor(0.0)
+        for i in rows:
+            out[i] = scores[i] - mean
+    tiled = out.unsqueeze(-1).tile([1, rewards.shape[-1]]) * mask
+    return masked_whiten(tiled, mask)
+
+
+def rfpp(rewards, mask, gamma):
+    """compute_reinforce_plus_plus_outcome_advantage (core_algos.py:245-278) -> (advantages, returns)."""
+    returns = torch.zeros_like(rewards)
+    run = 0
+    for t in reversed(range(rewards.shape[1])):
+        run = rewards[:, t] + gamma * run
+        returns[:, t] = run
+        run = run * mask[:, t]
+    return masked_whiten(returns, mask) * mask, returns
+
+
+def remax(rewards, baselines, mask):
+    """compute_remax_outcome_advantage (core_algos.py:281-305) -> (advantages, returns)."""
+    returns = (rewards * mask).flip(dims=[-1]).cumsum(dim=-1).flip(dims=[-1])
+    return returns - baselines.unsqueeze(-1) * mask, returns
+
+
+def kl_penalty(logprob, ref_logprob, kind):
+    """core_algos.py:469-501."""
+    if kind == "kl":
+        return logprob - ref_logprob
+    if kind == "abs":
+        return (logprob - ref_logprob).abs()
+    if kind == "mse":
+        return 0.5 * (logprob - ref_logprob).square()
+    if kind == "low_var_kl":
+        kl = ref_logprob - logprob
+        return torch.clamp(torch.exp(kl) - kl - 1, min=-10, max=10)
+    raise NotImplementedError
+
+
+def apply_kl_penalty(scores, logprob, ref_logprob, mask, kind, beta):
+    """ray_trainer.py:145-175 -> (token_level_rewards, current_kl)."""
+    kld = kl_penalty(logprob, ref_logprob, kind) * mask
+    per_row = (kld * mask).sum(-1) / (mask.sum(-1) + 1e-8)
+    return scores - beta * kld, torch.mean(per_row, dim=0).item()
+
+
+def filter_rollout(original_rm_scores, num_groups, group_size, ratio, kind="std"):
+    """_filter_rollout (agent_trainer.py:461-500; a closure inside fit(), restated): -> (row keep-mask, metrics)."""
+    std, mx, mean = group_filter_stats(original_rm_scores, num_groups, group_size)
+    if ratio == 1:
+        keep = torch.ones(num_groups * group_size, dtype=torch.bool)
+        chosen = slice(None)
+    else:
+        chosen = ((-std) if kind == "std_rev" else std).topk(int(ratio * num_groups)).indices
+        gm = torch.zeros(num_groups, dtype=torch.bool)
+        gm[chosen] = True
+        keep = gm.unsqueeze(1).expand(-1, group_size).flatten()
+    metrics = {"rollout/in_group_std": std.mean(), "rollout/in_group_max": mx.mean(), "rollout/in_group_mean": mean.mean(),
+               "rollout/chosen_in_group_std": std[chosen].mean(), "rollout/chosen_in_group_max": mx[chosen].mean(),
+               "rollout/chosen_in_group_mean": mean[chosen].mean()}
+    return keep, metrics

@@ -41,6 +41,12 @@ SIGNATURES = {
     "ragen_masked_moments": [_P, _L, _P, _P, _P, _P],
     "ragen_whiten": [_P, _L, _P, _P, _P],
     "ragen_grpo_outcome": [_P, _I, _I, _P, _P, _P, _I, _D, _I, _P, _P, _P],
+    "ragen_outcome_advantage": [_P, _I, _I, _P, _P, _P, _I, _I, _D, _P, _P, _P, _P],
+    "ragen_discounted_returns": [_P, _I, _I, _P, _P, _D, _P, _P, _P],
+    "ragen_remax": [_P, _I, _I, _P, _P, _P, _P, _P, _P],
+    "ragen_whiten_masked": [_P, _L, _P, _P, _P, _P, _P],
+    "ragen_kl_rewards": [_P, _I, _I, _P, _P, _P, _P, _I, _D, _P, _P, _P],
+    "ragen_group_filter_stats": [_P, _I, _I, _I, _P, _P, _P, _P, _P, _P],
 }
 _RESTYPE = {"ragen_last_error": _c.c_char_p, "ragen_launch_count": _c.c_uint64}
 

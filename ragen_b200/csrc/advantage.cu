@@ -40,6 +40,7 @@ __global__ void __launch_bounds__(ROWS_PER_CTA * 32) gae_kernel(int B, int T, co
                                                                  double* moments) {
   __shared__ float s_a[ROWS_PER_CTA][CHUNK];
   __shared__ float s_v[ROWS_PER_CTA][CHUNK];
+  __shared__ uint8_t s_m[ROWS_PER_CTA][CHUNK];
   const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int row = blockIdx.x * ROWS_PER_CTA + w;
   double m0 = 0.0, m1 = 0.0, m2 = 0.0;
@@ -48,11 +49,15 @@ __global__ void __launch_bounds__(ROWS_PER_CTA * 32) gae_kernel(int B, int T, co
     float carry = 0.0f;
     for (int t1 = T; t1 > 0; t1 -= CHUNK) {
       const int t0 = max(0, t1 - CHUNK), len = t1 - t0;
+      // the unrolled loop keeps 8 x 4 independent loads in flight per lane: at C5 (128 rows) the pass is bound by
+      // memory latency, not bandwidth
+#pragma unroll 8
       for (int i = lane; i < len; i += 32) {
         const int t = t0 + i;
-        const float v = values[base + t];
-        const float vn = (t + 1 < T) ? values[base + t + 1] : 0.0f;
-        const float r = rewards[base + t];
+        const float v = __ldg(values + base + t);
+        const float vn = (t + 1 < T) ? __ldg(values + base + t + 1) : 0.0f;
+        const float r = __ldg(rewards + base + t);
+        s_m[w][i] = mask[base + t];
         s_a[w][i] = __fsub_rn(__fadd_rn(r, __fmul_rn(gamma, vn)), v);
         s_v[w][i] = v;
       }
@@ -67,12 +72,13 @@ __global__ void __launch_bounds__(ROWS_PER_CTA * 32) gae_kernel(int B, int T, co
         carry = lg;
       }
       __syncwarp();
+#pragma unroll 8
       for (int i = lane; i < len; i += 32) {
         const int t = t0 + i;
         const float a = s_a[w][i];
         adv[base + t] = a;
         ret[base + t] = __fadd_rn(a, s_v[w][i]);
-        if (mask[base + t]) {
+        if (s_m[w][i]) {
           m0 += 1.0;
           m1 += (double)a;
           m2 += (double)a * (double)a;
@@ -106,9 +112,10 @@ __global__ void __launch_bounds__(ROWS_PER_CTA * 32) bilevel_gae_kernel(int B, i
     float hi_next_v = 0.0f, lo_next_v = 0.0f, hi_lg = 0.0f, lo_lg = 0.0f;
     for (int t1 = T; t1 > 0; t1 -= CHUNK) {
       const int t0 = max(0, t1 - CHUNK), len = t1 - t0;
+#pragma unroll 8
       for (int i = lane; i < len; i += 32) {
-        s_r[w][i] = rewards[base + t0 + i];
-        s_v[w][i] = values[base + t0 + i];
+        s_r[w][i] = __ldg(rewards + base + t0 + i);
+        s_v[w][i] = __ldg(values + base + t0 + i);
         s_m[w][i] = mask[base + t0 + i];
       }
       __syncwarp();
@@ -149,6 +156,7 @@ __global__ void __launch_bounds__(ROWS_PER_CTA * 32) bilevel_gae_kernel(int B, i
         }
       }
       __syncwarp();
+#pragma unroll 8
       for (int i = lane; i < len; i += 32) {
         const float a = s_r[w][i];
         adv[base + t0 + i] = a;
@@ -243,6 +251,203 @@ __global__ void __launch_bounds__(ROWS_PER_CTA * 32) grpo_apply_kernel(int B, in
   for (int t = lane; t < T; t += 32) adv[base + t] = mask[base + t] ? val : __fmul_rn(val, 0.0f);
 }
 
+// ---- the remaining members of compute_advantage's dispatch table (agent_trainer.py:106-134) ---------------------------
+// Outcome estimators share GRPO's first step (row scores + per-group count / sum / sum of squares); this is their second
+// step.  mode 0: score - mean (GRPO without std); 1: GRPO; 2: RLOO, score*n/(n-1) - mean*n/(n-1) for groups of n > 1
+// (core_algos.py:205-242); 3: REINFORCE++-baseline, score - mean, to be whitened by the caller from `moments` (:168-202).
+// Groups of one use mean 0 (and std 1).  The value is broadcast over the row and multiplied by the mask.
+__global__ void __launch_bounds__(ROWS_PER_CTA * 32) outcome_apply_kernel(int B, int T, const float* __restrict__ scores,
+                                                                           const int32_t* __restrict__ group, int n_groups,
+                                                                           const double* __restrict__ gstats,
+                                                                           const uint8_t* __restrict__ mask, float eps, int mode,
+                                                                           float* __restrict__ adv, double* moments) {
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int row = blockIdx.x * ROWS_PER_CTA + w;
+  double m0 = 0.0, m1 = 0.0, m2 = 0.0;
+  if (row < B) {
+    const int g = group[row];
+    float mean = 0.0f, sd = 1.0f, cnt = 1.0f;
+    if (g >= 0 && g < n_groups) {
+      const double c = gstats[3 * g], s1 = gstats[3 * g + 1], s2 = gstats[3 * g + 2];
+      cnt = (float)c;
+      if (c > 1.5) {
+        const double mu = s1 / c;
+        mean = (float)mu;
+        sd = (float)sqrt(fmax((s2 - c * mu * mu) / (c - 1.0), 0.0));
+      }
+    }
+    const float sc = scores[row];
+    float val;
+    if (mode == 1) {
+      val = __fdiv_rn(__fsub_rn(sc, mean), __fadd_rn(sd, eps));
+    } else if (mode == 2) {
+      val = sc;
+      if (cnt > 1.5f) val = __fsub_rn(__fdiv_rn(__fmul_rn(sc, cnt), cnt - 1.0f), __fdiv_rn(__fmul_rn(mean, cnt), cnt - 1.0f));
+    } else {
+      val = __fsub_rn(sc, mean);
+    }
+    const size_t base = (size_t)row * T;
+    const float off = __fmul_rn(val, 0.0f);
+    int on = 0;
+#pragma unroll 4
+    for (int t = lane; t < T; t += 32) {
+      const bool m = mask[base + t] != 0;
+      adv[base + t] = m ? val : off;
+      on += m;
+    }
+    m0 = (double)on;
+    m1 = (double)on * (double)val;
+    m2 = (double)on * (double)val * (double)val;
+  }
+  if (moments) add_moments(moments, m0, m1, m2);
+}
+
+// REINFORCE++ (core_algos.py:245-278): running = r_t + gamma * running, returns_t = running, running *= mask_t, right to
+// left, in the reference's fp32 order; plus the masked moments of the returns for the whitening that follows.
+// REMAX = 1 (core_algos.py:281-305): returns = reverse cumulative sum of rewards*mask (torch's CPU cumsum accumulates
+// fp32 data in double and rounds every prefix), adv = returns - baseline * mask.
+template <int REMAX>
+__global__ void __launch_bounds__(ROWS_PER_CTA * 32) returns_kernel(int B, int T, const float* __restrict__ rewards,
+                                                                     const uint8_t* __restrict__ mask, float gamma,
+                                                                     const float* __restrict__ baselines,
+                                                                     float* __restrict__ adv, float* __restrict__ ret,
+                                                                     double* moments) {
+  __shared__ float s_r[ROWS_PER_CTA][CHUNK];
+  __shared__ uint8_t s_m[ROWS_PER_CTA][CHUNK];
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int row = blockIdx.x * ROWS_PER_CTA + w;
+  double m0 = 0.0, m1 = 0.0, m2 = 0.0;
+  if (row < B) {
+    const size_t base = (size_t)row * T;
+    const float bl = REMAX ? baselines[row] : 0.0f;
+    float run = 0.0f;
+    double acc = 0.0;
+    for (int t1 = T; t1 > 0; t1 -= CHUNK) {
+      const int t0 = max(0, t1 - CHUNK), len = t1 - t0;
+#pragma unroll 8
+      for (int i = lane; i < len; i += 32) {
+        s_r[w][i] = __ldg(rewards + base + t0 + i);
+        s_m[w][i] = mask[base + t0 + i];
+      }
+      __syncwarp();
+      if (lane == 0) {
+#pragma unroll 8
+        for (int i = len - 1; i >= 0; --i) {
+          if (REMAX) {
+            acc += s_m[w][i] ? (double)s_r[w][i] : (double)__fmul_rn(s_r[w][i], 0.0f);
+            s_r[w][i] = (float)acc;
+          } else {
+            run = __fadd_rn(s_r[w][i], __fmul_rn(gamma, run));
+            s_r[w][i] = run;
+            run = s_m[w][i] ? run : __fmul_rn(run, 0.0f);
+          }
+        }
+      }
+      __syncwarp();
+#pragma unroll 8
+      for (int i = lane; i < len; i += 32) {
+        const float x = s_r[w][i];
+        ret[base + t0 + i] = x;
+        if (REMAX) {
+          adv[base + t0 + i] = __fsub_rn(x, s_m[w][i] ? bl : __fmul_rn(bl, 0.0f));
+        } else if (s_m[w][i]) {
+          m0 += 1.0;
+          m1 += (double)x;
+          m2 += (double)x * (double)x;
+        }
+      }
+      __syncwarp();
+    }
+  }
+  if (!REMAX) add_moments(moments, m0, m1, m2);
+}
+
+// out = masked_whiten(x) * mask (the last two lines of compute_reinforce_plus_plus_outcome_advantage, :275-276)
+__global__ void whiten_masked_kernel(int64_t n, const float* __restrict__ x, const uint8_t* __restrict__ mask,
+                                     const double* __restrict__ moments, float* __restrict__ out) {
+  const double S0 = moments[0], S1 = moments[1], S2 = moments[2];
+  const double mean = S1 / (S0 + 1e-8);
+  double var = (S2 - 2.0 * mean * S1 + mean * mean * S0) / (S0 + 1e-8);
+  var = var * (S0 / (S0 - 1.0));
+  const float meanf = (float)mean;
+  const float scale = (float)(1.0 / sqrt(var + 1e-8));
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const float v = (x[i] - meanf) * scale;
+    out[i] = mask[i] ? v : __fmul_rn(v, 0.0f);
+  }
+}
+
+// apply_kl_penalty (verl/verl/trainer/ppo/ray_trainer.py:145-175) with kl_penalty (core_algos.py:469-501):
+// kld = f(logp, ref) * mask; rewards = scores - beta * kld; row_kl[b] = sum(kld) / (sum(mask) + 1e-8).
+// mode 0 "kl", 1 "abs", 2 "mse", 3 "low_var_kl".
+__global__ void __launch_bounds__(ROWS_PER_CTA * 32) kl_rewards_kernel(int B, int T, const float* __restrict__ scores,
+                                                                        const float* __restrict__ logp,
+                                                                        const float* __restrict__ ref,
+                                                                        const uint8_t* __restrict__ mask, int mode, float beta,
+                                                                        float* __restrict__ out, float* __restrict__ row_kl) {
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int row = blockIdx.x * ROWS_PER_CTA + w;
+  if (row >= B) return;
+  const size_t base = (size_t)row * T;
+  float ksum = 0.0f, msum = 0.0f;
+#pragma unroll 4
+  for (int t = lane; t < T; t += 32) {
+    const float a = __ldg(logp + base + t), b = __ldg(ref + base + t);
+    float k;
+    if (mode == 0) {
+      k = __fsub_rn(a, b);
+    } else if (mode == 1) {
+      k = fabsf(__fsub_rn(a, b));
+    } else if (mode == 2) {
+      const float d = __fsub_rn(a, b);
+      k = __fmul_rn(0.5f, __fmul_rn(d, d));
+    } else {
+      const float d = __fsub_rn(b, a);
+      k = __fsub_rn(__fsub_rn(expf(d), d), 1.0f);
+      k = fminf(fmaxf(k, -10.0f), 10.0f);
+    }
+    const bool m = mask[base + t] != 0;
+    k = m ? k : __fmul_rn(k, 0.0f);
+    out[base + t] = __fsub_rn(__ldg(scores + base + t), __fmul_rn(beta, k));
+    ksum += k;
+    msum += m ? 1.0f : 0.0f;
+  }
+  ksum = warp_sum(ksum);
+  msum = warp_sum(msum);
+  if (lane == 0 && row_kl) row_kl[row] = ksum / (msum + 1e-8f);
+}
+
+// _filter_rollout's statistics (ragen/trainer/agent_trainer.py:466-469): row sums of the score tensor, then per group
+// of `group_size` consecutive rows the unbiased std, the max and the mean.  One warp per group, lane per row.
+__global__ void __launch_bounds__(ROWS_PER_CTA * 32) filter_stats_kernel(int n_groups, int group_size, int T,
+                                                                          const float* __restrict__ scores,
+                                                                          float* __restrict__ row_sum, float* __restrict__ gstd,
+                                                                          float* __restrict__ gmax, float* __restrict__ gmean) {
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int g = blockIdx.x * ROWS_PER_CTA + w;
+  if (g >= n_groups) return;
+  double s1 = 0.0, s2 = 0.0;
+  float mx = -INFINITY;
+  for (int r = 0; r < group_size; ++r) {  // the warp sums one row at a time (coalesced); every lane ends with the sum
+    const size_t base = ((size_t)g * group_size + r) * T;
+    double s = 0.0;
+#pragma unroll 4
+    for (int t = lane; t < T; t += 32) s += (double)__ldg(scores + base + t);
+    const float sf = (float)warp_sum(s);
+    if (lane == 0) row_sum[(size_t)g * group_size + r] = sf;
+    s1 += (double)sf;
+    s2 += (double)sf * (double)sf;
+    mx = fmaxf(mx, sf);
+  }
+  if (lane == 0) {
+    const double n = (double)group_size, mu = s1 / n;
+    gmean[g] = (float)mu;
+    gmax[g] = mx;
+    gstd[g] = group_size > 1 ? (float)sqrt(fmax((s2 - n * mu * mu) / (n - 1.0), 0.0)) : NAN;  // torch.std of one value is NaN
+  }
+}
+
 int grid_rows(int B) { return (B + ROWS_PER_CTA - 1) / ROWS_PER_CTA; }
 
 }  // namespace
@@ -327,6 +532,95 @@ extern "C" int ragen_grpo_outcome(ragen_ctx* ctx, int B, int T, const float* rew
   RAGEN_LAUNCHED(ctx);
   grpo_apply_kernel<<<grid_rows(B), ROWS_PER_CTA * 32, 0, st>>>(B, T, scores, group, n_groups, gstats, mask, (float)epsilon,
                                                                norm_by_std, adv);
+  RAGEN_LAUNCHED(ctx);
+  return RAGEN_OK;
+}
+
+extern "C" int ragen_outcome_advantage(ragen_ctx* ctx, int B, int T, const float* rewards, const uint8_t* mask,
+                                       const int32_t* group, int n_groups, int mode, double epsilon, float* scores,
+                                       float* adv, double* moments, void* stream) {
+  RAGEN_REQUIRE(ctx, "ctx is NULL");
+  RAGEN_BT(B, T);
+  RAGEN_REQUIRE(rewards && mask && group && scores && adv && n_groups >= 1 && mode >= 0 && mode <= 3, "bad argument");
+  DeviceGuard guard(ctx->device);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (moments) RAGEN_CUDA(cudaMemsetAsync(moments, 0, 3 * sizeof(double), st));
+  if (B == 0) return RAGEN_OK;
+  const size_t bytes = (size_t)n_groups * 3 * sizeof(double);
+  double* gstats = (double*)ragen_scratch(ctx, bytes);
+  if (!gstats) return RAGEN_ENOMEM;
+  RAGEN_CUDA(cudaMemsetAsync(gstats, 0, bytes, st));
+  grpo_scores_kernel<<<grid_rows(B), ROWS_PER_CTA * 32, 0, st>>>(B, T, rewards, group, n_groups, scores, gstats);
+  RAGEN_LAUNCHED(ctx);
+  outcome_apply_kernel<<<grid_rows(B), ROWS_PER_CTA * 32, 0, st>>>(B, T, scores, group, n_groups, gstats, mask, (float)epsilon,
+                                                                  mode, adv, moments);
+  RAGEN_LAUNCHED(ctx);
+  return RAGEN_OK;
+}
+
+extern "C" int ragen_discounted_returns(ragen_ctx* ctx, int B, int T, const float* rewards, const uint8_t* mask, double gamma,
+                                        float* ret, double* moments, void* stream) {
+  RAGEN_REQUIRE(ctx, "ctx is NULL");
+  RAGEN_BT(B, T);
+  RAGEN_REQUIRE(rewards && mask && ret && moments, "NULL pointer argument");
+  DeviceGuard guard(ctx->device);
+  cudaStream_t st = (cudaStream_t)stream;
+  RAGEN_CUDA(cudaMemsetAsync(moments, 0, 3 * sizeof(double), st));
+  if (B == 0) return RAGEN_OK;
+  returns_kernel<0><<<grid_rows(B), ROWS_PER_CTA * 32, 0, st>>>(B, T, rewards, mask, (float)gamma, nullptr, nullptr, ret, moments);
+  RAGEN_LAUNCHED(ctx);
+  return RAGEN_OK;
+}
+
+extern "C" int ragen_remax(ragen_ctx* ctx, int B, int T, const float* rewards, const uint8_t* mask, const float* baselines,
+                           float* adv, float* ret, void* stream) {
+  RAGEN_REQUIRE(ctx, "ctx is NULL");
+  RAGEN_BT(B, T);
+  RAGEN_REQUIRE(rewards && mask && baselines && adv && ret, "NULL pointer argument");
+  if (B == 0) return RAGEN_OK;
+  DeviceGuard guard(ctx->device);
+  returns_kernel<1><<<grid_rows(B), ROWS_PER_CTA * 32, 0, (cudaStream_t)stream>>>(B, T, rewards, mask, 0.0f, baselines, adv, ret,
+                                                                                 nullptr);
+  RAGEN_LAUNCHED(ctx);
+  return RAGEN_OK;
+}
+
+extern "C" int ragen_whiten_masked(ragen_ctx* ctx, int64_t n, const float* x, const uint8_t* mask, const double* moments,
+                                   float* out, void* stream) {
+  RAGEN_REQUIRE(ctx, "ctx is NULL");
+  RAGEN_REQUIRE(n >= 0 && x && mask && moments && out, "bad argument");
+  if (n == 0) return RAGEN_OK;
+  DeviceGuard guard(ctx->device);
+  const int threads = 256;
+  const int64_t want = (n + threads - 1) / threads;
+  const int blocks = (int)(want < (int64_t)ctx->sm_count * 16 ? want : (int64_t)ctx->sm_count * 16);
+  whiten_masked_kernel<<<blocks, threads, 0, (cudaStream_t)stream>>>(n, x, mask, moments, out);
+  RAGEN_LAUNCHED(ctx);
+  return RAGEN_OK;
+}
+
+extern "C" int ragen_kl_rewards(ragen_ctx* ctx, int B, int T, const float* scores, const float* logp, const float* ref_logp,
+                                const uint8_t* mask, int mode, double beta, float* rewards_out, float* row_kl, void* stream) {
+  RAGEN_REQUIRE(ctx, "ctx is NULL");
+  RAGEN_BT(B, T);
+  RAGEN_REQUIRE(scores && logp && ref_logp && mask && rewards_out && mode >= 0 && mode <= 3, "bad argument");
+  if (B == 0) return RAGEN_OK;
+  DeviceGuard guard(ctx->device);
+  kl_rewards_kernel<<<grid_rows(B), ROWS_PER_CTA * 32, 0, (cudaStream_t)stream>>>(B, T, scores, logp, ref_logp, mask, mode,
+                                                                                 (float)beta, rewards_out, row_kl);
+  RAGEN_LAUNCHED(ctx);
+  return RAGEN_OK;
+}
+
+extern "C" int ragen_group_filter_stats(ragen_ctx* ctx, int n_groups, int group_size, int T, const float* scores,
+                                        float* row_sum, float* gstd, float* gmax, float* gmean, void* stream) {
+  RAGEN_REQUIRE(ctx, "ctx is NULL");
+  RAGEN_REQUIRE(n_groups >= 0 && group_size >= 1 && T >= 1, "bad shape");
+  RAGEN_REQUIRE(scores && row_sum && gstd && gmax && gmean, "NULL pointer argument");
+  if (n_groups == 0) return RAGEN_OK;
+  DeviceGuard guard(ctx->device);
+  filter_stats_kernel<<<grid_rows(n_groups), ROWS_PER_CTA * 32, 0, (cudaStream_t)stream>>>(n_groups, group_size, T, scores,
+                                                                                          row_sum, gstd, gmax, gmean);
   RAGEN_LAUNCHED(ctx);
   return RAGEN_OK;
 }

@@ -92,6 +92,88 @@ def grpo_outcome(rewards, mask, group_index, n_groups, epsilon=1e-6, norm_by_std
     return adv, scores
 
 
+_OUTCOME_MODES = {"mean": 0, "grpo": 1, "rloo": 2, "rfpp_baseline": 3}
+_KL_MODES = {"kl": 0, "abs": 1, "mse": 2, "low_var_kl": 3}
+
+
+def outcome_advantage(rewards, mask, group_index, n_groups, mode, epsilon=1e-6, want_moments=False):
+    """RLOO / REINFORCE++-baseline / GRPO over per-group score statistics.  Returns (adv, scores, moments or None)."""
+    ctx = _ctx(rewards)
+    r, m = _f32(rewards), _u8(mask).contiguous()
+    B, T = r.shape
+    g = group_index.to(torch.int32).contiguous()
+    scores = torch.empty(B, dtype=torch.float32, device=r.device)
+    adv = torch.empty_like(r)
+    mom = torch.empty(3, dtype=torch.float64, device=r.device) if want_moments else None
+    _lib.check(ctx.lib.ragen_outcome_advantage(ctx.handle, B, T, _lib.ptr(r), _lib.ptr(m), _lib.ptr(g), int(n_groups),
+                                               _OUTCOME_MODES[mode], float(epsilon), _lib.ptr(scores), _lib.ptr(adv), _lib.ptr(mom),
+                                               ctx.stream()))
+    return adv, scores, mom
+
+
+def discounted_returns(rewards, mask, gamma):
+    """REINFORCE++ returns (reset after masked-out tokens) + their masked moments."""
+    ctx = _ctx(rewards)
+    r, m = _f32(rewards), _u8(mask).contiguous()
+    B, T = r.shape
+    ret = torch.empty_like(r)
+    mom = torch.empty(3, dtype=torch.float64, device=r.device)
+    _lib.check(ctx.lib.ragen_discounted_returns(ctx.handle, B, T, _lib.ptr(r), _lib.ptr(m), float(gamma), _lib.ptr(ret), _lib.ptr(mom),
+                                                ctx.stream()))
+    return ret, m, mom
+
+
+def whiten_masked(x, mask_u8, moments, check=True):
+    """masked_whiten(x) * mask into a new tensor."""
+    ctx = _ctx(x)
+    if check:
+        n = float(moments[0])
+        if n == 0:
+            raise ValueError("At least one element in the mask has to be 1.")
+        if n == 1:
+            raise ValueError("The sum of the mask is one, which can cause a division by zero.")
+    out = torch.empty_like(x)
+    _lib.check(ctx.lib.ragen_whiten_masked(ctx.handle, x.numel(), _lib.ptr(x), _lib.ptr(mask_u8), _lib.ptr(moments), _lib.ptr(out),
+                                           ctx.stream()))
+    return out
+
+
+def remax(rewards, mask, baselines):
+    ctx = _ctx(rewards)
+    r, m, b = _f32(rewards), _u8(mask).contiguous(), _f32(baselines)
+    B, T = r.shape
+    adv, ret = torch.empty_like(r), torch.empty_like(r)
+    _lib.check(ctx.lib.ragen_remax(ctx.handle, B, T, _lib.ptr(r), _lib.ptr(m), _lib.ptr(b), _lib.ptr(adv), _lib.ptr(ret), ctx.stream()))
+    return adv, ret
+
+
+def kl_rewards(scores, logp, ref_logp, mask, kl_penalty, beta):
+    """Returns (token_level_rewards f32 [B, T], row_kl f32 [B])."""
+    if kl_penalty not in _KL_MODES:
+        raise NotImplementedError(kl_penalty)
+    ctx = _ctx(scores)
+    s, a, b, m = _f32(scores), _f32(logp), _f32(ref_logp), _u8(mask).contiguous()
+    B, T = s.shape
+    out = torch.empty_like(s)
+    row = torch.empty(B, dtype=torch.float32, device=s.device)
+    _lib.check(ctx.lib.ragen_kl_rewards(ctx.handle, B, T, _lib.ptr(s), _lib.ptr(a), _lib.ptr(b), _lib.ptr(m), _KL_MODES[kl_penalty],
+                                        float(beta), _lib.ptr(out), _lib.ptr(row), ctx.stream()))
+    return out, row
+
+
+def group_filter_stats(scores, n_groups, group_size):
+    """Row sums [B] and per-group (std, max, mean) [n_groups] of a score tensor whose rows are grouped consecutively."""
+    ctx = _ctx(scores)
+    s = _f32(scores)
+    assert s.shape[0] == n_groups * group_size
+    dev = s.device
+    row = torch.empty(s.shape[0], dtype=torch.float32, device=dev)
+    gstd, gmax, gmean = (torch.empty(n_groups, dtype=torch.float32, device=dev) for _ in range(3))
+    _lib.check(ctx.lib.ragen_group_filter_stats(ctx.handle, int(n_groups), int(group_size), s.shape[1], _lib.ptr(s), _lib.ptr(row),
+                                                _lib.ptr(gstd), _lib.ptr(gmax), _lib.ptr(gmean), ctx.stream()))
+    return row, gstd, gmax, gmean
+
+
 # ---- ContextManager tensor passes ----------------------------------------------------------------------------
 def masks_scores(input_ids, turn_scores, n_turns, im_start, im_end, use_turn_scores=False, enable_response_mask=True,
                  roll_scores=True):

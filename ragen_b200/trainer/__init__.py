@@ -1,1 +1,1 @@
-from .agent_trainer import AdvantageEstimator, compute_advantage, compute_response_mask  # noqa: F401
+from .agent_trainer import AdvantageEstimator, apply_kl_penalty, compute_advantage, compute_response_mask, filter_rollout  # noqa: F401

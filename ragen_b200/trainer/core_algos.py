@@ -67,6 +67,83 @@ def compute_grpo_outcome_advantage(token_level_rewards, response_mask, index, ep
     return adv, adv
 
 
+def compute_rloo_outcome_advantage(token_level_rewards, response_mask, index, epsilon: float = 1e-6, device=None):
+    """verl/verl/trainer/ppo/core_algos.py:205-242."""
+    home, dev = token_level_rewards.device, _dev(token_level_rewards, device)
+    gi, n_groups = dense_index(index)
+    with torch.no_grad():
+        adv, _, _ = ops.outcome_advantage(token_level_rewards.to(dev), response_mask.to(dev),
+                                          torch.tensor(gi, dtype=torch.int32, device=dev), n_groups, "rloo", epsilon)
+    adv = adv.to(home)
+    return adv, adv
+
+
+def compute_reinforce_plus_plus_baseline_outcome_advantage(token_level_rewards, response_mask, index, epsilon: float = 1e-6,
+                                                           device=None, sharded=False, group=None):
+    """verl/verl/trainer/ppo/core_algos.py:168-202 (the whitening is batch-global: moments all-reduced when sharded)."""
+    home, dev = token_level_rewards.device, _dev(token_level_rewards, device)
+    gi, n_groups = dense_index(index)
+    with torch.no_grad():
+        adv, _, mom = ops.outcome_advantage(token_level_rewards.to(dev), response_mask.to(dev),
+                                            torch.tensor(gi, dtype=torch.int32, device=dev), n_groups, "rfpp_baseline", epsilon,
+                                            want_moments=True)
+        adv = _whiten_from(adv, mom, sharded, group)
+    adv = adv.to(home)
+    return adv, adv
+
+
+def compute_reinforce_plus_plus_outcome_advantage(token_level_rewards, response_mask, gamma, device=None, sharded=False, group=None):
+    """verl/verl/trainer/ppo/core_algos.py:245-278."""
+    home, dev = token_level_rewards.device, _dev(token_level_rewards, device)
+    with torch.no_grad():
+        ret, m, mom = ops.discounted_returns(token_level_rewards.to(dev), response_mask.to(dev), float(gamma))
+        if sharded:
+            ops.all_reduce_moments(mom, group)
+        adv = ops.whiten_masked(ret, m, mom)
+    return adv.to(home), ret.to(home)
+
+
+def compute_remax_outcome_advantage(token_level_rewards, reward_baselines, response_mask, device=None):
+    """verl/verl/trainer/ppo/core_algos.py:281-305."""
+    home, dev = token_level_rewards.device, _dev(token_level_rewards, device)
+    with torch.no_grad():
+        adv, ret = ops.remax(token_level_rewards.to(dev), response_mask.to(dev), reward_baselines.to(dev))
+    return adv.to(home), ret.to(home)
+
+
+class AdaptiveKLController:
+    """verl/verl/trainer/ppo/core_algos.py:29-44."""
+
+    def __init__(self, init_kl_coef, target_kl, horizon):
+        self.value = init_kl_coef
+        self.target = target_kl
+        self.horizon = horizon
+
+    def update(self, current_kl, n_steps):
+        proportional_error = np.clip(current_kl / self.target - 1, -0.2, 0.2)
+        self.value *= 1 + proportional_error * n_steps / self.horizon
+
+
+class FixedKLController:
+    """verl/verl/trainer/ppo/core_algos.py:47-54."""
+
+    def __init__(self, kl_coef):
+        self.value = kl_coef
+
+    def update(self, current_kl, n_steps):
+        pass
+
+
+def get_kl_controller(kl_ctrl):
+    """verl/verl/trainer/ppo/core_algos.py:57-64."""
+    if kl_ctrl.type == "fixed":
+        return FixedKLController(kl_coef=kl_ctrl.kl_coef)
+    if kl_ctrl.type == "adaptive":
+        assert kl_ctrl.horizon > 0, f"horizon must be larger than 0. Got {kl_ctrl.horizon}"
+        return AdaptiveKLController(init_kl_coef=kl_ctrl.kl_coef, target_kl=kl_ctrl.target_kl, horizon=kl_ctrl.horizon)
+    raise NotImplementedError
+
+
 def masked_moments(values, mask, device=None, sharded=False, group=None):
     dev = _dev(values, device)
     mom = ops.masked_moments(values.to(dev), mask.to(dev))

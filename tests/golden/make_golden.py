@@ -483,6 +483,51 @@ def rollouts():
     print("rollouts ok:", [(r["name"], r["shape"], len(r["turns"])) for r in out])
 
 
+def advantage_more():
+    """RLOO / RF++ / RF++-baseline / ReMax / kl_penalty from the UNMODIFIED verl core_algos.py; apply_kl_penalty's arithmetic
+    (ray_trainer.py:145-175 imports ray, so its three lines are evaluated here on verl's own kl_penalty and masked_mean)."""
+    ca = R.verl_core_algos()
+    tf = R.torch_functional()
+    g = torch.Generator().manual_seed(21)
+    B, T = 12, 80
+    mask = torch.zeros(B, T)
+    for b in range(B):
+        a = int(torch.randint(0, 30, (1,), generator=g)); e = int(torch.randint(a + 5, T + 1, (1,), generator=g))
+        mask[b, a:e] = 1
+        if b % 3 == 0 and e - a > 12:
+            mask[b, a + 4:a + 8] = 0  # a hole, as multi-turn loss masks have
+    outcome = torch.zeros(B, T)
+    for b in range(B):
+        last = int(torch.nonzero(mask[b]).flatten()[-1])
+        outcome[b, last] = float(torch.randn(1, generator=g))
+    dense = torch.randn(B, T, generator=g) * 0.3 * mask
+    uid = np.array(["g%d" % (b // 4) for b in range(B)], dtype=object); uid[-1] = "solo"
+    out = {"mask": mask.numpy(), "outcome": outcome.numpy(), "dense": dense.numpy(), "uid": np.array([str(u) for u in uid])}
+    out["rloo"] = ca.compute_rloo_outcome_advantage(outcome.clone(), mask, uid)[0].numpy()
+    out["rfpp_baseline"] = ca.compute_reinforce_plus_plus_baseline_outcome_advantage(outcome.clone(), mask, uid)[0].numpy()
+    for tag, gamma in (("1", 1.0), ("97", 0.97)):
+        adv, ret = ca.compute_reinforce_plus_plus_outcome_advantage(dense.clone(), mask, gamma)
+        out[f"rfpp_adv_{tag}"] = adv.numpy(); out[f"rfpp_ret_{tag}"] = ret.numpy()
+    base = torch.randn(B, generator=g)
+    adv, ret = ca.compute_remax_outcome_advantage(dense.clone(), base, mask)
+    out["remax_base"] = base.numpy(); out["remax_adv"] = adv.numpy(); out["remax_ret"] = ret.numpy()
+    logp = -torch.rand(B, T, generator=g) * 3; ref = logp + torch.randn(B, T, generator=g) * 0.2
+    out["logp"] = logp.numpy(); out["ref_logp"] = ref.numpy()
+    for kind in ("kl", "abs", "mse", "low_var_kl"):
+        kld = ca.kl_penalty(logp, ref, kl_penalty=kind) * mask
+        out[f"klrew_{kind}"] = (outcome - 0.05 * kld).numpy()
+        out[f"klcur_{kind}"] = np.array(torch.mean(tf.masked_mean(kld, mask=mask, axis=-1), dim=0).item())
+    # _filter_rollout statistics: plain torch calls of agent_trainer.py:466-469 on a [G*gs, T] score tensor
+    G, gs = 8, 4
+    sc = torch.zeros(G * gs, T); sc[:, -1] = torch.randn(G * gs, generator=g); sc[4:8, -1] = 0.5; sc[:, 10] = torch.randn(G * gs, generator=g) * 0.1
+    rm = sc.sum(dim=-1).view(G, gs)
+    out["filter_scores"] = sc.numpy(); out["filter_std"] = rm.std(dim=-1).numpy(); out["filter_max"] = rm.max(dim=-1).values.numpy()
+    out["filter_mean"] = rm.mean(dim=-1).numpy()
+    out["filter_top_std"] = rm.std(dim=-1).topk(2).indices.numpy(); out["filter_top_std_rev"] = (-rm.std(dim=-1)).topk(2).indices.numpy()
+    np.savez_compressed(os.path.join(OUT, "advantage_more.npz"), **out)
+    print("advantage_more ok")
+
+
 def countdown():
     cd = R.countdown_env()
     cases = [("1+2+3", [1, 2, 3], 6), ("1+2", [1, 2, 3], 3), ("3*(2-1)", [1, 2, 3], 3), ("1 + 2 = 3", [1, 2, 3], 3),
@@ -513,4 +558,5 @@ if __name__ == "__main__":
     es_manager_script()
     lm_inputs()
     rollouts()
+    advantage_more()
     countdown()

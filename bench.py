@@ -47,6 +47,9 @@ def parse_args():
     ap.add_argument("--ref-envs", type=int, default=0, help="envs per reference step (0 = auto from core count)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--rows", action="store_true", help="per-kernel lines for every SURVEY.md 8(d) config instead of the contract line")
+    ap.add_argument("--quick", action="store_true", help="with --rows: smaller batches")
+    ap.add_argument("--only", default="", help="with --rows: comma list of sokoban,generator,frozenlake,parse,c5,manager")
     return ap.parse_args()
 
 
@@ -327,4 +330,9 @@ def run_native(args):
 
 if __name__ == "__main__":
     _args = parse_args()
+    if _args.rows:
+        import bench_rows
+
+        bench_rows.main(_args.quick, _args.only)
+        sys.exit(0)
     sys.exit(run_reference(_args) if _args.impl == "reference" else run_native(_args))

@@ -1,12 +1,13 @@
 #!/usr/bin/env python
 """Per-kernel measurement of every config of SURVEY.md 8(d) (C1..C5) on ONE B200, one JSON line per row.
 
-    python scripts/bench_kernels.py [--out profiles/rNN_kernels.jsonl] [--quick]
+    python bench.py --rows [--quick] [--only sokoban,generator,frozenlake,parse,c5,manager]  > profiles/rNN_kernels.jsonl
 
 bench.py is the contract line (C4 step); this script is the supporting evidence for the other rows: each line carries
 the kernel's device time (CUDA events on the launching stream, after warm-up, median of the repetitions), the
 algorithmic bytes per unit, achieved GB/s against MEASURED_PEAKS.json, and the CPU port of the
-reference (oracle/, single core, bounded sample) timed beside it.  Rows whose working set is a few hundred KB are
+reference (oracle/, single core, bounded sample) timed beside it - the same `cpu_baseline` role oracle/ has in bench.py,
+which is the only way in (`bench.py --rows`).  Rows whose working set is a few hundred KB are
 launch-latency-bound: they are reported as microseconds per call and their roofline fraction is not a quality claim.
 """
 import argparse
@@ -18,7 +19,7 @@ import time
 import numpy as np
 import torch
 
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
@@ -243,6 +244,23 @@ def c5_rows(quick):
         gi = torch.arange(B, device="cuda", dtype=torch.int32) // 16
         ms_g = dev_time(lambda: ops.grpo_outcome(rewards, lm, gi, B // 16), reps=50)
         rows.append(line(f"GRPO {tag}", "token", B * T, ms_g, 9, None, None, kernel="grpo_scores_kernel + grpo_apply_kernel"))
+        ms_r = dev_time(lambda: ops.outcome_advantage(rewards, lm, gi, B // 16, "rloo"), reps=50)
+        rows.append(line(f"RLOO {tag}", "token", B * T, ms_r, 9, None, None, kernel="grpo_scores_kernel + outcome_apply_kernel"))
+
+        def rfpp():
+            ret, m8, mom = ops.discounted_returns(rewards, lm, 1.0)
+            ops.whiten_masked(ret, m8, mom, check=False)
+        ms_p = dev_time(rfpp, reps=50)
+        rows.append(line(f"REINFORCE++ {tag}", "token", B * T, ms_p, 4 + 1 + 4 + 4 + 1 + 4, None, None, kernel="returns_kernel<0> + whiten_masked_kernel"))
+        base = torch.randn(B, device="cuda")
+        ms_x = dev_time(lambda: ops.remax(rewards, lm, base), reps=50)
+        rows.append(line(f"ReMax {tag}", "token", B * T, ms_x, 4 + 1 + 4 + 4, None, None, kernel="returns_kernel<1>"))
+        lp = -torch.rand(B, T, device="cuda")
+        rf = lp + 0.1 * torch.randn(B, T, device="cuda")
+        ms_k = dev_time(lambda: ops.kl_rewards(rewards, lp, rf, lm, "low_var_kl", 0.05), reps=50)
+        rows.append(line(f"KL-in-reward {tag}", "token", B * T, ms_k, 4 * 3 + 1 + 4, None, None, kernel="kl_rewards_kernel"))
+        ms_f = dev_time(lambda: ops.group_filter_stats(sc, B // 16, 16), reps=50)
+        rows.append(line(f"rollout filter stats {tag}", "token", B * T, ms_f, 4, None, None, kernel="filter_stats_kernel"))
         pen = torch.zeros(B, device="cuda")
         ms_n = dev_time(lambda: ops.group_norm(sc[:, -1], pen, gi, B // 16, "mean_std"), reps=50)
         rows.append(line(f"group reward norm {tag}", "row", B, ms_n, 16, None, None, kernel="norm_stats_kernel + norm_apply_kernel"))
@@ -280,11 +298,8 @@ def manager_rows(quick):
                       "note": "latency-bound: 9 KB of state; the Python history bookkeeping the API promises dominates"}), flush=True)
 
 
-if __name__ == "__main__":
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--quick", action="store_true")
-    ap.add_argument("--only", default="")
-    a = ap.parse_args()
+def main(quick=False, only=""):
+    a = argparse.Namespace(quick=quick, only=only)
     torch.cuda.set_device(0)
     todo = {"sokoban": sokoban_rows, "generator": generator_rows, "frozenlake": frozenlake_rows, "parse": parse_rows, "c5": c5_rows,
             "manager": manager_rows}

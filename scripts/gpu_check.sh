@@ -12,7 +12,7 @@ timeout 300 python __graft_entry__.py --smoke > $OUT/${TAG}_smoke.log 2>&1; echo
 timeout 900 python bench.py --steps 2000 --warmup 20 > $OUT/${TAG}_bench.json 2> $OUT/${TAG}_bench.err; echo "bench exit $?"
 tail -c 3000 $OUT/${TAG}_bench.json
 timeout 600 python bench.py --impl reference --steps 5 --warmup 1 > $OUT/${TAG}_bench_ref.json 2>> $OUT/${TAG}_bench.err
-timeout 900 python scripts/bench_kernels.py > $OUT/${TAG}_kernels.jsonl 2> $OUT/${TAG}_kernels.err; echo "kernels exit $?"
+timeout 900 python bench.py --rows > $OUT/${TAG}_kernels.jsonl 2> $OUT/${TAG}_kernels.err; echo "kernels exit $?"
 BCMD="python bench.py --steps 4 --warmup 3 --no-cpu-baseline --no-e2e"
 timeout 300 $BCMD > $OUT/${TAG}_plain.log 2>&1 &&
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file $OUT/${TAG}_launches.csv $BCMD > $OUT/${TAG}_ncu1.log 2>&1

@@ -8,9 +8,9 @@ def run():
     from oracle import advantage as A
     from oracle import managers as M
     from oracle import toy_envs as TE
-    from . import ops
-    from .env.bandit import BanditBatch, BanditEnvConfig
-    from .env.frozen_lake import FrozenLakeBatch
+    from ragen_b200 import ops
+    from ragen_b200.env.bandit import BanditBatch, BanditEnvConfig
+    from ragen_b200.env.frozen_lake import FrozenLakeBatch
 
     notes = []
     # FrozenLake: map generation + 10 slippery steps, 256 envs

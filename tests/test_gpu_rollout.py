@@ -104,7 +104,7 @@ def test_rollout_to_advantage_c5_shape():
         assert batch["advantages"].data_ptr() == batch["returns"].data_ptr()
 
     with pytest.raises(NotImplementedError):
-        compute_advantage(dp, AdvantageEstimator.RLOO)
+        compute_advantage(dp, "no_such_estimator")
 
 
 def test_reference_named_estimators_on_golden():

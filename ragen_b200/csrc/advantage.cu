@@ -452,17 +452,17 @@ int grid_rows(int B) { return (B + ROWS_PER_CTA - 1) / ROWS_PER_CTA; }
 
 }  // namespace
 
-#define RAGEN_BT(B, T) RAGEN_REQUIRE(B >= 0 && T >= 1 && (int64_t)B * T < ((int64_t)1 << 40), "bad shape B=%d T=%d", B, T)
+#define RAGEN_BT(B, T) RAGEN_REQUIRE(B >= 0 && (B == 0 || T >= 1) && (int64_t)B * T < ((int64_t)1 << 40), "bad shape B=%d T=%d", B, T)
 
 extern "C" int ragen_gae(ragen_ctx* ctx, int B, int T, const float* rewards, const float* values, const uint8_t* mask,
                          double gamma, double lam, float* adv, float* ret, double* moments, void* stream) {
   RAGEN_REQUIRE(ctx, "ctx is NULL");
   RAGEN_BT(B, T);
-  RAGEN_REQUIRE(rewards && values && mask && adv && ret, "NULL pointer argument");
-  if (B == 0) return RAGEN_OK;
+  RAGEN_REQUIRE(B == 0 || (rewards && values && mask && adv && ret), "NULL pointer argument");
   DeviceGuard guard(ctx->device);
   cudaStream_t st = (cudaStream_t)stream;
   if (moments) RAGEN_CUDA(cudaMemsetAsync(moments, 0, 3 * sizeof(double), st));
+  if (B == 0) return RAGEN_OK;  // an empty shard still contributes zero moments to the all-reduce
   gae_kernel<<<grid_rows(B), ROWS_PER_CTA * 32, 0, st>>>(B, T, rewards, values, mask, (float)gamma, (float)(gamma * lam), adv,
                                                         ret, moments);
   RAGEN_LAUNCHED(ctx);
@@ -474,11 +474,11 @@ extern "C" int ragen_bilevel_gae(ragen_ctx* ctx, int B, int T, const float* rewa
                                  float* ret, double* moments, void* stream) {
   RAGEN_REQUIRE(ctx, "ctx is NULL");
   RAGEN_BT(B, T);
-  RAGEN_REQUIRE(rewards && values && loss_mask && adv && ret, "NULL pointer argument");
-  if (B == 0) return RAGEN_OK;
+  RAGEN_REQUIRE(B == 0 || (rewards && values && loss_mask && adv && ret), "NULL pointer argument");
   DeviceGuard guard(ctx->device);
   cudaStream_t st = (cudaStream_t)stream;
   if (moments) RAGEN_CUDA(cudaMemsetAsync(moments, 0, 3 * sizeof(double), st));
+  if (B == 0) return RAGEN_OK;  // an empty shard still contributes zero moments to the all-reduce
   bilevel_gae_kernel<<<grid_rows(B), ROWS_PER_CTA * 32, 0, st>>>(B, T, rewards, values, loss_mask, (float)gamma,
                                                                 (float)(gamma * lam), (float)high_level_gamma,
                                                                 (float)(high_level_gamma * lam), adv, ret, moments);
@@ -489,7 +489,7 @@ extern "C" int ragen_bilevel_gae(ragen_ctx* ctx, int B, int T, const float* rewa
 extern "C" int ragen_masked_moments(ragen_ctx* ctx, int64_t n, const float* x, const uint8_t* mask, double* moments,
                                     void* stream) {
   RAGEN_REQUIRE(ctx, "ctx is NULL");
-  RAGEN_REQUIRE(n >= 0 && x && mask && moments, "bad argument");
+  RAGEN_REQUIRE(n >= 0 && moments && (n == 0 || (x && mask)), "bad argument");
   DeviceGuard guard(ctx->device);
   cudaStream_t st = (cudaStream_t)stream;
   RAGEN_CUDA(cudaMemsetAsync(moments, 0, 3 * sizeof(double), st));
@@ -504,7 +504,7 @@ extern "C" int ragen_masked_moments(ragen_ctx* ctx, int64_t n, const float* x, c
 
 extern "C" int ragen_whiten(ragen_ctx* ctx, int64_t n, float* x, const double* moments, void* stream) {
   RAGEN_REQUIRE(ctx, "ctx is NULL");
-  RAGEN_REQUIRE(n >= 0 && x && moments, "bad argument");
+  RAGEN_REQUIRE(n >= 0 && moments && (n == 0 || x), "bad argument");
   if (n == 0) return RAGEN_OK;
   DeviceGuard guard(ctx->device);
   const int threads = 256;
@@ -541,7 +541,7 @@ extern "C" int ragen_outcome_advantage(ragen_ctx* ctx, int B, int T, const float
                                        float* adv, double* moments, void* stream) {
   RAGEN_REQUIRE(ctx, "ctx is NULL");
   RAGEN_BT(B, T);
-  RAGEN_REQUIRE(rewards && mask && group && scores && adv && n_groups >= 1 && mode >= 0 && mode <= 3, "bad argument");
+  RAGEN_REQUIRE(mode >= 0 && mode <= 3 && (B == 0 || (rewards && mask && group && scores && adv && n_groups >= 1)), "bad argument");
   DeviceGuard guard(ctx->device);
   cudaStream_t st = (cudaStream_t)stream;
   if (moments) RAGEN_CUDA(cudaMemsetAsync(moments, 0, 3 * sizeof(double), st));
@@ -562,7 +562,7 @@ extern "C" int ragen_discounted_returns(ragen_ctx* ctx, int B, int T, const floa
                                         float* ret, double* moments, void* stream) {
   RAGEN_REQUIRE(ctx, "ctx is NULL");
   RAGEN_BT(B, T);
-  RAGEN_REQUIRE(rewards && mask && ret && moments, "NULL pointer argument");
+  RAGEN_REQUIRE(moments && (B == 0 || (rewards && mask && ret)), "NULL pointer argument");
   DeviceGuard guard(ctx->device);
   cudaStream_t st = (cudaStream_t)stream;
   RAGEN_CUDA(cudaMemsetAsync(moments, 0, 3 * sizeof(double), st));

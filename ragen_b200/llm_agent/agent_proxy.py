@@ -46,6 +46,8 @@ class LLMAgentProxy:
         env_outputs = es_manager.reset() if seed is None else es_manager.reset(seed=seed)
         ctx_manager.bind_envs(es_manager.envs)  # action-id lookup joins the parse kernel (Bandit re-draws names per reset)
         for _ in range(self.config.agent_proxy.max_turn):
+            if len(env_outputs) == 0:  # a rank without env groups (more ranks than groups) has nothing to generate
+                break
             lm_inputs: DataProto = ctx_manager.get_lm_inputs(env_outputs, prepare_for_update=False)
             lm_inputs.meta_info = dataproto.meta_info
             lm_outputs: DataProto = self.generate_sequences(lm_inputs)

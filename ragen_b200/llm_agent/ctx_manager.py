@@ -220,7 +220,24 @@ class ContextManager:
         assert all(msg["role"] == "assistant" for msg in messages[2::2])  # the loss mask counts on this alternation
         return messages
 
+    def _empty_lm_inputs(self, prepare_for_update: bool) -> DataProto:
+        """A rank that owns no env group (fewer groups than ranks) still takes part in the metrics exchange."""
+        ids = torch.zeros((0, 1), dtype=torch.long)
+        batch = {"input_ids": ids, "attention_mask": ids.clone(), "position_ids": ids.clone(), "responses": ids[:, 1:]}
+        out = DataProto()
+        if prepare_for_update:
+            score = torch.zeros((0, 0), dtype=torch.float32)
+            batch.update({"loss_mask": torch.zeros((0, 0), dtype=torch.bool), "rm_scores": score, "original_rm_scores": score})
+            self._response_tokens = (0.0, 0)
+            out.meta_info = {"metrics": self._mean_metrics([], 0.0)}
+        out.batch = TensorDict(batch, batch_size=0)
+        out.non_tensor_batch = {"env_ids": np.array([], dtype=object), "group_ids": np.array([], dtype=object),
+                                "messages_list": np.array([], dtype=object)}
+        return out
+
     def get_lm_inputs(self, env_outputs: List[Dict], prepare_for_update: bool) -> DataProto:
+        if len(env_outputs) == 0:
+            return self._empty_lm_inputs(prepare_for_update)
         llm_input_texts, messages_list = [], []
         for env_output in env_outputs:
             messages = self._messages(env_output, prepare_for_update)

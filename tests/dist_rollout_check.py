@@ -35,13 +35,13 @@ def main():
         env_ids = [int(e) for e in dp.non_tensor_batch["env_ids"]]
         assert all((e // case["group_size"]) % world == rank for e in env_ids)
         # advantage on this rank's rows with batch-global whitening
-        B, T = batch["rm_scores"].shape
+        B, T = batch["rm_scores"].shape  # (0, 0) on a rank that owns no group: it still joins both all-reduces
         batch["response_mask"] = batch["loss_mask"].float()
         batch["token_level_rewards"] = batch["rm_scores"].clone()
         gen = torch.Generator().manual_seed(1000 + rank)
         batch["values"] = torch.randn(B, T, generator=gen) * batch["response_mask"]
         compute_advantage(dp, AdvantageEstimator.GAE, gamma=1.0, lam=1.0, device=local, sharded=True)
-        mine = {"env_ids": env_ids, "rm_last": batch["rm_scores"][:, -1].tolist(), "loss_mask_sum": batch["loss_mask"].sum(-1).tolist(),
+        mine = {"env_ids": env_ids, "rm_last": batch["rm_scores"][:, -1:].flatten().tolist(), "loss_mask_sum": batch["loss_mask"].sum(-1).tolist(),
                 "metrics": {k: float(v) for k, v in dp.meta_info["metrics"].items()},
                 "r": batch["token_level_rewards"], "v": batch["values"], "m": batch["response_mask"], "adv": batch["advantages"],
                 "ret": batch["returns"]}
@@ -59,6 +59,7 @@ def main():
                 for k, w in case["metrics"].items():
                     assert abs(g["metrics"][k] - w) <= 1e-6 * max(1.0, abs(w)), (case["name"], k, g["metrics"][k], w)
             # whitening: pad every shard on the left to a common T (GAE runs right-to-left and pads are masked out)
+            gathered = [g for g in gathered if len(g["env_ids"])]
             Tm = max(g["r"].shape[1] for g in gathered)
             pad = lambda t: torch.nn.functional.pad(t, (Tm - t.shape[1], 0))
             r_, v_, m_ = (torch.cat([pad(g[k]) for g in gathered]) for k in ("r", "v", "m"))

@@ -103,3 +103,54 @@ def test_action_codes_when_bound_to_envs():
         assert [h.get("reward") for h in g["history"]] == [h.get("reward") for h in w["history"]]
         assert [h.get("state") for h in g["history"]] == [h.get("state") for h in w["history"]]
         assert [h.get("actions") for h in g["history"]] == [h.get("actions") for h in w["history"]]
+
+
+def test_context_window_truncation_like_the_reference_test():
+    """The reference's only unit test (tests/llm_agent/test_context_window.py:60-84): same tokenizer stub, same config, same
+    input.  Its assertions describe truncate-then-drop; the reference CODE (ctx_manager.py:241-246) drops the trailing state
+    entry first when prepare_for_update and only then keeps the last max_context_window entries, so on this input the unmodified
+    reference yields turns S1, S2 and a score of 0.1 + 0.2 (checked by running it here) - the test as shipped fails against its
+    own code.  ragen_b200 follows the code; the shipped expectation holds for prepare_for_update=False, asserted below too."""
+    from ragen_b200.llm_agent.ctx_manager import ContextManager
+
+    class DummyTokenizer:
+        name_or_path = "qwen"
+
+        def apply_chat_template(self, messages, add_generation_prompt, tokenize):
+            return " ".join([msg["content"] for msg in messages])
+
+        def __call__(self, texts, return_tensors, padding, padding_side, truncation):
+            class DummyOutput:
+                input_ids = torch.tensor([[1, 2, 3]])
+                attention_mask = torch.tensor([[1, 1, 1]])
+            return DummyOutput()
+
+        def encode(self, text):
+            return [42, 43]
+
+    cfg = C.to_attr({
+        "agent_proxy": {"max_context_window": 2, "enable_think": False, "use_turn_scores": False, "action_sep": "|",
+                        "max_actions_per_turn": 5, "reward_normalization": {"grouping": "batch", "method": "identity"}},
+        "enable_response_mask": False,
+        "es_manager": {"train": {"env_configs": {"n_groups": [1], "tags": ["sokoban"]}, "group_size": 1}},
+        "custom_envs": {"sokoban": {"env_type": "sokoban", "max_actions_per_traj": 10}},
+        "actor_rollout_ref": {"rollout": {"response_length": 128}}})
+    ctx = ContextManager(config=cfg, tokenizer=DummyTokenizer(), mode="train")
+    ctx.prefix_lookup = {0: "Initial prompt"}
+    ctx.env_config_lookup = {0: {"max_tokens": 128}}
+    ctx.env_nums = {"": 1}
+
+    def outputs():
+        return [{"env_id": 0, "group_id": 0, "metrics": {},
+                 "history": [{"state": "S1", "llm_response": "R1", "reward": 0.1, "actions_left": 5},
+                             {"state": "S2", "llm_response": "R2", "reward": 0.2, "actions_left": 4},
+                             {"state": "S3", "llm_response": "R3", "reward": 0.3, "actions_left": 3}]}]
+
+    lm_inputs = ctx.get_lm_inputs(outputs(), prepare_for_update=True)
+    messages = str(lm_inputs.non_tensor_batch["messages_list"][0])
+    assert "S1" in messages and "S2" in messages and "S3" not in messages
+    assert lm_inputs.batch["rm_scores"].tolist() == [[0.0, pytest.approx(0.3)]]
+    assert lm_inputs.meta_info["metrics"] == {"response_length": 0.0}
+    lm_inputs = ctx.get_lm_inputs(outputs(), prepare_for_update=False)
+    messages = str(lm_inputs.non_tensor_batch["messages_list"][0])
+    assert "S1" not in messages and "S2" in messages and "S3" in messages  # the shipped test's expectation

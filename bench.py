@@ -13,6 +13,7 @@ flush is needed between timed iterations.
 `value`   : device-timed (CUDA events, max over ranks), inputs resident in HBM.
 `e2e`     : same step through SokobanBatch.step_host — the actions come from pinned HOST memory and the
             reward / done / flags / n_executed / glyph rows go back to pinned HOST memory inside the timed region.
+            The glyph rows travel as two 4-bit codes per byte (--obs packed, the default; --obs bytes = one code per byte).
 `roofline`: algorithmic bytes per env-step (431 B for 10x10) x envs / mean launch time.
 `cpu_baseline` / `--impl reference`: the reference's execution model (one Python env object per env,
             serial step loop, text render per step — oracle/sokoban.py, a port because gym_sokoban is not
@@ -47,14 +48,17 @@ def parse_args():
     ap.add_argument("--ref-envs", type=int, default=0, help="envs per reference step (0 = auto from core count)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--obs", default="packed", choices=["packed", "bytes"],
+                    help="glyph-row format of the render: two 4-bit codes per byte (what the managers consume) or one code per byte")
     ap.add_argument("--rows", action="store_true", help="per-kernel lines for every SURVEY.md 8(d) config instead of the contract line")
     ap.add_argument("--quick", action="store_true", help="with --rows: smaller batches")
     ap.add_argument("--only", default="", help="with --rows: comma list of sokoban,generator,frozenlake,parse,c5,manager")
     return ap.parse_args()
 
 
-def workload_config(n_gpus, envs_per_gpu):
-    return {"workload": "sokoban_10x10_2box_step_render_reward", "dim_room": [H, W], "num_boxes": NUM_BOXES,
+def workload_config(n_gpus, envs_per_gpu, obs="packed"):
+    return {"glyph_rows": "two 4-bit glyph codes per byte (55 B per env)" if obs == "packed" else "one glyph code per byte (110 B per env)",
+            "workload": "sokoban_10x10_2box_step_render_reward", "dim_room": [H, W], "num_boxes": NUM_BOXES,
             "max_steps": MAX_STEPS, "envs_per_gpu": envs_per_gpu, "envs_total": envs_per_gpu * n_gpus,
             "actions_per_launch": 1, "rooms": "synthetic random-walk rooms (ragen_b200/synth.py)",
             "actions": "uniform 1..4", "l2": "inputs larger than L2 (431 MB touched per step per GPU)",
@@ -128,7 +132,7 @@ def run_reference(args):
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": workload_config(args.gpus, args.envs),
+            "config": workload_config(args.gpus, args.envs, args.obs),
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -257,8 +261,9 @@ def run_native(args):
         sampler.start()
 
     # ---- device-resident timing -------------------------------------------------------------------
+    packed = args.obs == "packed"
     for i in range(args.warmup):
-        batch.step(actions[i % R])
+        batch.step(actions[i % R], packed=packed)
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     t_begin, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
@@ -266,7 +271,7 @@ def run_native(args):
     t_begin.record()
     for i in range(args.steps):
         ev[i][0].record()
-        batch.step(actions[i % R])
+        batch.step(actions[i % R], packed=packed)
         ev[i][1].record()
     t_end.record()
     barrier()
@@ -282,11 +287,11 @@ def run_native(args):
     e2e = None
     if not args.no_e2e:
         for i in range(max(args.warmup, 3)):
-            batch.step_host(host_actions[i % R])
+            batch.step_host(host_actions[i % R], packed=packed)
         barrier()
         t0 = time.perf_counter()
         for i in range(args.steps):
-            batch.step_host(host_actions[i % R])
+            batch.step_host(host_actions[i % R], packed=packed)
         barrier()
         e2e_s = time.perf_counter() - t0
         t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
@@ -295,7 +300,7 @@ def run_native(args):
         e2e_s = float(t.item())
         G = H * (W + 1)
         e2e = {"value": n * world * args.steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": n * 1,
-               "d2h_bytes_per_step": n * (G + 8 + 1 + 1 + 1), "ms_per_step": 1e3 * e2e_s / args.steps,
+               "d2h_bytes_per_step": n * ((G // 2 if packed else G) + 8 + 1 + 1 + 1), "ms_per_step": 1e3 * e2e_s / args.steps,
                "api": "SokobanBatch.step_host -> ragen_sokoban_step (C ABI), pinned host buffers"}
 
     clocks = sampler.stop() if rank == 0 else None
@@ -309,17 +314,19 @@ def run_native(args):
         traffic = None
         tpath = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(tpath):
-            traffic = json.load(open(tpath)).get("sokoban_step_bytes_per_launch")
+            traffic = json.load(open(tpath)).get("sokoban_step_packed_bytes_per_launch" if packed else "sokoban_step_bytes_per_launch")
+        moved = MOVED_PER_STEP - (H * (W + 1)) // 2 if packed else MOVED_PER_STEP
         line = {"metric": METRIC, "value": n * world * args.steps / (total_ms * 1e-3), "unit": UNIT, "n_gpus": world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-                "config": workload_config(world, n), "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
+                "config": workload_config(world, n, args.obs), "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                             "traffic": traffic, "kernel": "sokoban_tile_kernel<10,10,false>", "kernel_ms": kern_ms,
+                             "traffic": traffic, "kernel": "sokoban_tile_kernel<10,10,false,%s>" % ("true" if packed else "false"), "kernel_ms": kern_ms,
                              "bytes_per_env_step": BYTES_PER_STEP, "peak_source": peak_src,
-                             "bytes_moved_per_env_step": MOVED_PER_STEP, "frac_moved": MOVED_PER_STEP * n / (kern_ms * 1e-3) / 1e9 / peak,
-                             "note": "frac uses SURVEY.md 8(d)'s 431 B, which charges a 100 B room_fixed read the kernel avoids; "
-                                     "frac_moved uses the 338 B it has to move"}}
+                             "bytes_moved_per_env_step": moved, "frac_moved": moved * n / (kern_ms * 1e-3) / 1e9 / peak,
+                             "note": "frac uses SURVEY.md 8(d)'s 431 B per env-step, which charges a 100 B room_fixed read the kernel "
+                                     "avoids and 110 B of glyph rows; frac_moved uses the bytes this kernel has to move "
+                                     "(338 B with byte glyph rows, 283 B with packed ones)"}}
         if cpu_base is not None:
             line["cpu_baseline"] = cpu_base
         print(json.dumps(line), file=out, flush=True)

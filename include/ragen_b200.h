@@ -76,6 +76,17 @@ int ragen_sokoban_step(ragen_ctx* ctx, int64_t n, int H, int W, int num_boxes, i
                        double* acc_reward, uint8_t* done, uint8_t* flags, uint8_t* n_executed,
                        uint8_t* obs, void* stream);
 
+/* The same step with the glyph rows written as two 4-bit codes per byte (low nibble = the earlier cell):
+ * obs_packed [n][H*(W+1)/2], H*(W+1) must be even.  Half the bytes to write and to send to the host; a host turns a
+ * byte into its two glyph strings with one 256-entry translate, exactly as it turns a code into one. */
+int ragen_sokoban_step_packed(ragen_ctx* ctx, int64_t n, int H, int W, int num_boxes, int max_steps,
+                              const uint8_t* actions, int K, const uint8_t* n_actions,
+                              uint8_t* state, int16_t* meta,
+                              double* acc_reward, uint8_t* done, uint8_t* flags, uint8_t* n_executed,
+                              uint8_t* obs_packed, void* stream);
+int ragen_sokoban_render_packed(ragen_ctx* ctx, int64_t n, int H, int W, const uint8_t* state,
+                                const int16_t* meta, uint8_t* obs_packed, void* stream);
+
 /* SokobanEnv.render text branch only (env.py:53-57). */
 int ragen_sokoban_render(ragen_ctx* ctx, int64_t n, int H, int W, const uint8_t* state,
                          const int16_t* meta, uint8_t* obs, void* stream);

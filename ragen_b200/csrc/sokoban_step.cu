@@ -57,34 +57,48 @@ __device__ __forceinline__ void copy_bytes(uint8_t* dst, const uint8_t* src, int
 
 // The glyph rows of a tile are ONE uniform byte stream: every env is H rows of W cells + 1 separator,
 // and consecutive envs have consecutive cells, so output byte Q maps to cell Q - Q/(W+1) unless
-// Q % (W+1) == W (separator, code 7).  A thread builds 4 output bytes from 4 consecutive cells
+// Q % (W+1) == W (separator, code 7).  glyph_word builds the 4 output bytes Q0..Q0+3 from 4 consecutive cells
 // (unaligned 32-bit window = two aligned LDS + funnel shift) and splices the separator in.
-template <int CW>
+__device__ __forceinline__ uint32_t glyph_word(const uint32_t* sw, int Q0, int W) {
+  const int RW = W + 1;
+  const int r0 = Q0 / RW;
+  const int c0 = Q0 - r0 * RW;
+  const int s0 = Q0 - r0;
+  const int a = s0 >> 2;
+  const uint32_t x = __funnelshift_r(sw[a], sw[a + 1], (s0 & 3) << 3);
+  const int p = W - c0;  // byte of this word that is a separator (if < 4)
+  uint32_t out = x;
+  if (p < 4) {
+    const uint32_t low = (1u << (p << 3)) - 1u;                        // bytes below p
+    const uint32_t high = (p == 3) ? 0u : ~((1u << ((p + 1) << 3)) - 1u);  // bytes above p
+    out = (x & low) | (7u << (p << 3)) | ((x << 8) & high);
+  }
+  return out;
+}
+// 4 glyph codes (< 16 each, one per byte) -> 2 bytes of two 4-bit codes, low nibble first
+__device__ __forceinline__ uint32_t pack_nibbles(uint32_t w) {
+  const uint32_t t = w | (w >> 4);
+  return (t & 0xffu) | ((t >> 8) & 0xff00u);
+}
+// PACKED: the same stream with two codes per byte (glyph_bytes is then half the number of codes): half the bytes to
+// write to HBM and to send to the host, which turns a byte into its two glyphs with the same one-pass translate.
+template <int CW, bool PACKED>
 __device__ __forceinline__ void render_tile(const uint8_t* s_state, uint8_t* s_obs, int obs_bytes, int rW) {
   const int W = CW ? CW : rW;
-  const int RW = W + 1;
   const uint32_t* sw = reinterpret_cast<const uint32_t*>(s_state);
   uint32_t* ow = reinterpret_cast<uint32_t*>(s_obs);
   const int words = (obs_bytes + 3) >> 2;
   for (int j = threadIdx.x; j < words; j += TE) {
-    const int Q0 = j << 2;
-    const int r0 = Q0 / RW;
-    const int c0 = Q0 - r0 * RW;
-    const int s0 = Q0 - r0;
-    const int a = s0 >> 2;
-    const uint32_t x = __funnelshift_r(sw[a], sw[a + 1], (s0 & 3) << 3);
-    const int p = W - c0;  // byte of this word that is a separator (if < 4)
-    uint32_t out = x;
-    if (p < 4) {
-      const uint32_t low = (1u << (p << 3)) - 1u;                        // bytes below p
-      const uint32_t high = (p == 3) ? 0u : ~((1u << ((p + 1) << 3)) - 1u);  // bytes above p
-      out = (x & low) | (7u << (p << 3)) | ((x << 8) & high);
+    if (PACKED) {
+      const uint32_t lo = pack_nibbles(glyph_word(sw, j << 3, W)), hi = pack_nibbles(glyph_word(sw, (j << 3) + 4, W));
+      ow[j] = lo | (hi << 16);
+    } else {
+      ow[j] = glyph_word(sw, j << 2, W);
     }
-    ow[j] = out;
   }
 }
 
-template <int CH, int CW, bool RENDER_ONLY>
+template <int CH, int CW, bool RENDER_ONLY, bool PACKED>
 __global__ void __launch_bounds__(TE) sokoban_tile_kernel(const StepParams p) {
   const int H = CH ? CH : p.H, W = CW ? CW : p.W;
   const int HW = H * W, G = H * (W + 1);
@@ -97,7 +111,7 @@ __global__ void __launch_bounds__(TE) sokoban_tile_kernel(const StepParams p) {
   const int64_t env0 = (int64_t)blockIdx.x * TE;
   const int cnt = (int)min((int64_t)TE, p.n - env0);
   const int room_bytes = cnt * HW;
-  const int obs_bytes = cnt * G;
+  const int obs_bytes = PACKED ? (cnt * G) >> 1 : cnt * G;  // PACKED needs an even G (checked at launch)
   const bool bulk_rooms = (room_bytes & 15) == 0;
   const bool bulk_obs = (obs_bytes & 15) == 0;
   uint8_t* g_state = p.state + env0 * HW;
@@ -213,12 +227,20 @@ __global__ void __launch_bounds__(TE) sokoban_tile_kernel(const StepParams p) {
 
   // ---- render glyph rows, then shared memory -> HBM -----------------------------------------------
   if (p.obs) {
-    render_tile<CW>(s_state, s_obs, obs_bytes, p.W);
+    render_tile<CW, PACKED>(s_state, s_obs, obs_bytes, p.W);
     __syncthreads();
-    if (mine && under) s_obs[e * G + pos + pos / W] = 6;  // player standing on a target (env.py:55)
+    if (mine && under) {  // player standing on a target (env.py:55)
+      const int q = e * G + pos + pos / W;
+      if (PACKED) {  // G is even, so no other env's thread touches this byte
+        const uint8_t old = s_obs[q >> 1];
+        s_obs[q >> 1] = (q & 1) ? (uint8_t)((old & 0x0f) | 0x60) : (uint8_t)((old & 0xf0) | 0x06);
+      } else {
+        s_obs[q] = 6;
+      }
+    }
     fence_async_smem();
     __syncthreads();
-    uint8_t* g_obs = p.obs + env0 * G;
+    uint8_t* g_obs = p.obs + (PACKED ? (env0 * G) >> 1 : env0 * G);
     if (bulk_obs) {
       if (threadIdx.x == 0) {
         tma_store_1d(g_obs, s_obs, (uint32_t)obs_bytes);
@@ -302,16 +324,20 @@ __global__ void __launch_bounds__(TE) sokoban_adopt_kernel(const AdoptParams p) 
   if (p.status) p.status[env0 + e] = st;
 }
 
-size_t tile_smem(int H, int W) { return (size_t)round16(TE * H * W) + 16 + round16(TE * H * (W + 1)) + 16; }
+size_t tile_smem(int H, int W, bool packed) {
+  const int glyph_bytes = packed ? (TE * H * (W + 1)) >> 1 : TE * H * (W + 1);
+  return (size_t)round16(TE * H * W) + 16 + round16(glyph_bytes) + 16;
+}
 
-template <bool RENDER_ONLY>
+template <bool RENDER_ONLY, bool PACKED>
 int launch_tiles(ragen_ctx* ctx, const StepParams& p, cudaStream_t stream) {
-  const size_t smem = tile_smem(p.H, p.W);
+  RAGEN_REQUIRE(!PACKED || ((p.H * (p.W + 1)) & 1) == 0, "packed glyph rows need an even H*(W+1), got %dx%d", p.H, p.W);
+  const size_t smem = tile_smem(p.H, p.W, PACKED);
   RAGEN_REQUIRE(smem <= 227 * 1024, "room %dx%d does not fit the shared-memory tile (%zu B)", p.H, p.W, smem);
   const unsigned grid = (unsigned)((p.n + TE - 1) / TE);
 #define RAGEN_TILE_LAUNCH(CH, CW)                                                                   \
   do {                                                                                              \
-    auto kern = sokoban_tile_kernel<CH, CW, RENDER_ONLY>;                                           \
+    auto kern = sokoban_tile_kernel<CH, CW, RENDER_ONLY, PACKED>;                                          \
     RAGEN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
     kern<<<grid, TE, smem, stream>>>(p);                                                            \
   } while (0)
@@ -332,10 +358,10 @@ bool aligned8(const void* p) { return ((uintptr_t)p & 7) == 0; }
 #define RAGEN_SOKOBAN_SHAPE(n, H, W) \
   RAGEN_REQUIRE(n >= 0 && H >= 3 && W >= 3 && H * W <= 32767, "bad shape n=%lld H=%d W=%d", (long long)n, H, W)
 
-extern "C" int ragen_sokoban_step(ragen_ctx* ctx, int64_t n, int H, int W, int num_boxes, int max_steps,
-                                  const uint8_t* actions, int K, const uint8_t* n_actions, uint8_t* state, int16_t* meta,
-                                  double* acc_reward, uint8_t* done, uint8_t* flags, uint8_t* n_executed, uint8_t* obs,
-                                  void* stream) {
+namespace {
+int sokoban_step_entry(bool packed, ragen_ctx* ctx, int64_t n, int H, int W, int num_boxes, int max_steps, const uint8_t* actions,
+                       int K, const uint8_t* n_actions, uint8_t* state, int16_t* meta, double* acc_reward, uint8_t* done,
+                       uint8_t* flags, uint8_t* n_executed, uint8_t* obs, void* stream) {
   RAGEN_REQUIRE(ctx, "ctx is NULL");
   RAGEN_SOKOBAN_SHAPE(n, H, W);
   RAGEN_REQUIRE(K >= 1 && K <= 255, "K=%d out of range", K);
@@ -347,11 +373,11 @@ extern "C" int ragen_sokoban_step(ragen_ctx* ctx, int64_t n, int H, int W, int n
   DeviceGuard guard(ctx->device);
   StepParams p{n, H, W, num_boxes, max_steps, K, actions, n_actions, state, reinterpret_cast<EnvMeta*>(meta),
                acc_reward, done, flags, n_executed, obs};
-  return launch_tiles<false>(ctx, p, (cudaStream_t)stream);
+  return packed ? launch_tiles<false, true>(ctx, p, (cudaStream_t)stream) : launch_tiles<false, false>(ctx, p, (cudaStream_t)stream);
 }
 
-extern "C" int ragen_sokoban_render(ragen_ctx* ctx, int64_t n, int H, int W, const uint8_t* state, const int16_t* meta,
-                                    uint8_t* obs, void* stream) {
+int sokoban_render_entry(bool packed, ragen_ctx* ctx, int64_t n, int H, int W, const uint8_t* state, const int16_t* meta,
+                         uint8_t* obs, void* stream) {
   RAGEN_REQUIRE(ctx, "ctx is NULL");
   RAGEN_SOKOBAN_SHAPE(n, H, W);
   RAGEN_REQUIRE(state && meta && obs, "NULL pointer argument");
@@ -365,7 +391,34 @@ extern "C" int ragen_sokoban_render(ragen_ctx* ctx, int64_t n, int H, int W, con
   p.state = const_cast<uint8_t*>(state);
   p.meta = reinterpret_cast<EnvMeta*>(const_cast<int16_t*>(meta));
   p.obs = obs;
-  return launch_tiles<true>(ctx, p, (cudaStream_t)stream);
+  return packed ? launch_tiles<true, true>(ctx, p, (cudaStream_t)stream) : launch_tiles<true, false>(ctx, p, (cudaStream_t)stream);
+}
+}  // namespace
+
+extern "C" int ragen_sokoban_step(ragen_ctx* ctx, int64_t n, int H, int W, int num_boxes, int max_steps,
+                                  const uint8_t* actions, int K, const uint8_t* n_actions, uint8_t* state, int16_t* meta,
+                                  double* acc_reward, uint8_t* done, uint8_t* flags, uint8_t* n_executed, uint8_t* obs,
+                                  void* stream) {
+  return sokoban_step_entry(false, ctx, n, H, W, num_boxes, max_steps, actions, K, n_actions, state, meta, acc_reward, done, flags,
+                            n_executed, obs, stream);
+}
+
+extern "C" int ragen_sokoban_step_packed(ragen_ctx* ctx, int64_t n, int H, int W, int num_boxes, int max_steps,
+                                         const uint8_t* actions, int K, const uint8_t* n_actions, uint8_t* state,
+                                         int16_t* meta, double* acc_reward, uint8_t* done, uint8_t* flags,
+                                         uint8_t* n_executed, uint8_t* obs_packed, void* stream) {
+  return sokoban_step_entry(true, ctx, n, H, W, num_boxes, max_steps, actions, K, n_actions, state, meta, acc_reward, done, flags,
+                            n_executed, obs_packed, stream);
+}
+
+extern "C" int ragen_sokoban_render(ragen_ctx* ctx, int64_t n, int H, int W, const uint8_t* state, const int16_t* meta,
+                                    uint8_t* obs, void* stream) {
+  return sokoban_render_entry(false, ctx, n, H, W, state, meta, obs, stream);
+}
+
+extern "C" int ragen_sokoban_render_packed(ragen_ctx* ctx, int64_t n, int H, int W, const uint8_t* state,
+                                           const int16_t* meta, uint8_t* obs_packed, void* stream) {
+  return sokoban_render_entry(true, ctx, n, H, W, state, meta, obs_packed, stream);
 }
 
 extern "C" int ragen_sokoban_adopt(ragen_ctx* ctx, int64_t n, int H, int W, int num_boxes, const uint8_t* state,

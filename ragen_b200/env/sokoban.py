@@ -57,6 +57,27 @@ def glyph_table(grid_lookup):
     return tab
 
 
+def glyph_pair_table(grid_lookup):
+    """For packed glyph rows (two 4-bit codes per byte, low nibble first): byte value -> the two glyph strings, as a
+    str.translate table.  `packed_row.tobytes().decode("latin1").translate(table)[:-1]` is the env's text."""
+    tab = glyph_table(grid_lookup) + ["?"] * 8
+    return {b: tab[b & 15] + tab[b >> 4] for b in range(256)}
+
+
+def packed_to_text(packed_row, pair_table):
+    """packed_row: 1-D uint8 numpy array of length H*(W+1)/2; the trailing separator is dropped."""
+    return packed_row.tobytes().decode("latin1").translate(pair_table)[:-1]
+
+
+def unpack_glyphs(packed):
+    """[n, G/2] packed rows -> [n, G] glyph codes (numpy; tests and debugging)."""
+    p = np.asarray(packed)
+    out = np.empty((p.shape[0], p.shape[1] * 2), dtype=np.uint8)
+    out[:, 0::2] = p & 15
+    out[:, 1::2] = p >> 4
+    return out
+
+
 def codes_to_text(codes_row, table):
     """codes_row: 1-D uint8 numpy array of length H*(W+1); the trailing separator is dropped."""
     return "".join(table[c] for c in codes_row[:-1].tolist())
@@ -81,6 +102,8 @@ class SokobanBatch:
         self.flags = torch.zeros(self.n, dtype=torch.uint8, device=dev)
         self.n_executed = torch.zeros(self.n, dtype=torch.uint8, device=dev)
         self.obs = torch.zeros((self.n, G), dtype=torch.uint8, device=dev)
+        self.obs_packed = None  # [n, G/2], made on first packed render (needs an even G)
+        self.obs_is_packed = False  # which of the two buffers the latest render wrote
         self.status = torch.zeros(self.n, dtype=torch.int32, device=dev)
         self._pinned = {}
 
@@ -177,17 +200,32 @@ class SokobanBatch:
     # -- step -------------------------------------------------------------------------------
 
 
-    def step(self, actions, n_actions=None, render=True) -> StepOut:
-        """actions: uint8 device tensor [n] or [n, K]; n_actions: optional uint8 [n]."""
+    @property
+    def can_pack(self):
+        return (self.H * (self.W + 1)) % 2 == 0
+
+    def _packed_buffer(self):
+        if self.obs_packed is None:
+            if not self.can_pack:
+                raise ValueError(f"packed glyph rows need an even H*(W+1); room is {self.H}x{self.W}")
+            self.obs_packed = torch.zeros((self.n, self.H * (self.W + 1) // 2), dtype=torch.uint8, device=self.device)
+        return self.obs_packed
+
+    def step(self, actions, n_actions=None, render=True, packed=False) -> StepOut:
+        """actions: uint8 device tensor [n] or [n, K]; n_actions: optional uint8 [n].  packed=True renders the glyph rows
+        as two 4-bit codes per byte into `obs_packed` (half the bytes; StepOut.obs is then that tensor)."""
         if actions.dim() == 1:
             actions = actions.unsqueeze(1)
         assert actions.dtype == torch.uint8 and actions.is_cuda and actions.is_contiguous() and actions.shape[0] == self.n
         K = actions.shape[1]
-        _lib.check(self.lib.ragen_sokoban_step(
-            self.ctx.handle, self.n, self.H, self.W, self.num_boxes, self.max_steps, _lib.ptr(actions), K,
-            _lib.ptr(n_actions), _lib.ptr(self.state), _lib.ptr(self.meta), _lib.ptr(self.reward), _lib.ptr(self.done),
-            _lib.ptr(self.flags), _lib.ptr(self.n_executed), _lib.ptr(self.obs) if render else None, self.ctx.stream()))
-        return StepOut(self.reward, self.done, self.flags, self.n_executed, self.obs)
+        obs = (self._packed_buffer() if packed else self.obs) if render else None
+        if render:
+            self.obs_is_packed = bool(packed)
+        fn = self.lib.ragen_sokoban_step_packed if packed else self.lib.ragen_sokoban_step
+        _lib.check(fn(self.ctx.handle, self.n, self.H, self.W, self.num_boxes, self.max_steps, _lib.ptr(actions), K,
+                      _lib.ptr(n_actions), _lib.ptr(self.state), _lib.ptr(self.meta), _lib.ptr(self.reward), _lib.ptr(self.done),
+                      _lib.ptr(self.flags), _lib.ptr(self.n_executed), _lib.ptr(obs), self.ctx.stream()))
+        return StepOut(self.reward, self.done, self.flags, self.n_executed, obs if render else self.obs)
 
     def _pin(self, name, shape, dtype):
         key = (name, tuple(shape), dtype)
@@ -195,10 +233,10 @@ class SokobanBatch:
             self._pinned[key] = torch.empty(shape, dtype=dtype, pin_memory=True)
         return self._pinned[key]
 
-    def step_host(self, actions_np, n_actions_np=None, want_obs=True):
+    def step_host(self, actions_np, n_actions_np=None, want_obs=True, packed=False):
         """End-to-end call with HOST buffers: actions go host->device, the step runs, and reward /
-        done / flags / n_executed (and the glyph rows) come back device->host.  Returns numpy views
-        of pinned staging buffers (valid until the next call)."""
+        done / flags / n_executed (and the glyph rows; packed=True: two codes per byte, see glyph_pair_table) come back
+        device->host.  Returns numpy views of pinned staging buffers (valid until the next call)."""
         a = np.ascontiguousarray(actions_np, dtype=np.uint8)
         if a.ndim == 1:
             a = a[:, None]
@@ -210,7 +248,7 @@ class SokobanBatch:
             h_na = self._pin("na", (self.n,), torch.uint8)
             h_na.numpy()[...] = n_actions_np
             d_na = h_na.to(self.device, non_blocking=True)
-        out = self.step(d_act, d_na, render=want_obs)
+        out = self.step(d_act, d_na, render=want_obs, packed=packed and want_obs)
         h_rew = self._pin("rew", (self.n,), torch.float64)
         h_done = self._pin("done", (self.n,), torch.uint8)
         h_flags = self._pin("flags", (self.n,), torch.uint8)
@@ -221,18 +259,26 @@ class SokobanBatch:
         h_nex.copy_(out.n_executed, non_blocking=True)
         h_obs = None
         if want_obs:
-            h_obs = self._pin("obs", tuple(self.obs.shape), torch.uint8)
+            h_obs = self._pin("obs_packed" if packed else "obs", tuple(out.obs.shape), torch.uint8)
             h_obs.copy_(out.obs, non_blocking=True)
         torch.cuda.current_stream(self.device).synchronize()
         return (h_obs.numpy() if want_obs else None, h_rew.numpy(), h_done.numpy(), h_flags.numpy(), h_nex.numpy())
 
     # -- render -----------------------------------------------------------------------------
-    def render(self):
-        _lib.check(self.lib.ragen_sokoban_render(self.ctx.handle, self.n, self.H, self.W, _lib.ptr(self.state),
-                                                 _lib.ptr(self.meta), _lib.ptr(self.obs), self.ctx.stream()))
-        return self.obs
+    def render(self, packed=False):
+        obs = self._packed_buffer() if packed else self.obs
+        self.obs_is_packed = bool(packed)
+        fn = self.lib.ragen_sokoban_render_packed if packed else self.lib.ragen_sokoban_render
+        _lib.check(fn(self.ctx.handle, self.n, self.H, self.W, _lib.ptr(self.state), _lib.ptr(self.meta), _lib.ptr(obs),
+                      self.ctx.stream()))
+        return obs
 
     def texts(self, grid_lookup, rows=None):
+        """Text observations of the latest render (all envs, or `rows`): one device->host copy + one translate per env."""
+        if self.obs_is_packed:
+            pairs = glyph_pair_table(grid_lookup)
+            codes = (self.obs_packed if rows is None else self.obs_packed[rows]).cpu().numpy()
+            return [packed_to_text(r, pairs) for r in codes]
         tab = glyph_table(grid_lookup)
         codes = (self.obs if rows is None else self.obs[rows]).cpu().numpy()
         return [codes_to_text(r, tab) for r in codes]

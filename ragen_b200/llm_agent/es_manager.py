@@ -15,7 +15,6 @@ import torch
 
 from ..env import BATCH_TYPES, REGISTERED_ENV_CONFIGS, REGISTERED_ENVS
 from ..env.frozen_lake import fl_glyph_table
-from ..env.sokoban import glyph_table
 
 
 @dataclass
@@ -109,8 +108,8 @@ class EnvStateManager:
     def _block_texts(self, block) -> List[str]:
         """Current observation text of every env of the block (one device->host copy for grid envs)."""
         envs = self.envs[block.first:block.first + block.count]
-        if block.env_type == "sokoban":
-            return _translate_rows(block.batch.obs.cpu().numpy(), glyph_table(envs[0]["env"].GRID_LOOKUP))
+        if block.env_type == "sokoban":  # packed glyph rows (two codes per byte) when the room shape allows: half the copy
+            return block.batch.texts(envs[0]["env"].GRID_LOOKUP)
         if block.env_type == "frozen_lake":
             return _translate_rows(block.batch.obs.cpu().numpy(), fl_glyph_table(envs[0]["env"].GRID_LOOKUP))
         return [e["env"].render() for e in envs]
@@ -219,7 +218,8 @@ class EnvStateManager:
                 codes = [entry["env"].action_map[a] + 1 for a in todo] if block.env_type == "frozen_lake" else todo
                 act[s, :len(codes)] = codes
                 nact[s] = len(codes)
-            out = b.step(torch.from_numpy(act).to(dev), torch.from_numpy(nact).to(dev))
+            kw = {"packed": b.can_pack} if block.env_type == "sokoban" else {}
+            out = b.step(torch.from_numpy(act).to(dev), torch.from_numpy(nact).to(dev), **kw)
             host = torch.stack([out.done, out.flags, out.n_executed]).cpu().numpy()
             rew = out.reward.cpu().numpy()
             for i, (env_input, entry, valid, todo) in zip(idxs, plans):

@@ -203,3 +203,46 @@ def test_generated_rooms_are_valid_and_solvable():
     for j in np.flatnonzero(st == 0)[:64]:
         want_f, want_s = S.generate_room(6, 6, 1, 300, int(seeds[j]))
         assert np.array_equal(f[j], want_f) and np.array_equal(s[j], want_s)
+
+
+@pytest.mark.parametrize("H,W,nb,n", [(6, 6, 1, 1000), (10, 10, 2, 4099), (8, 8, 2, 515), (5, 5, 1, 130), (10, 10, 2, 1)])
+def test_packed_glyph_rows_equal_the_byte_rows(H, W, nb, n):
+    """ragen_sokoban_step_packed / ragen_sokoban_render_packed: the same step, glyph rows as two 4-bit codes per byte.
+    Unpacked they equal the oracle's rows; translated with the pair table they are the reference's text."""
+    from ragen_b200.env.sokoban import glyph_pair_table, packed_to_text, unpack_glyphs
+
+    fixed, state = synthetic_rooms(n, H, W, nb, seed=n + 7)
+    rng = np.random.default_rng(n)
+    o = SokobanBatchOracle(fixed, state, H, W, nb, 50)
+    b = _batch(n, H, W, nb, 50)
+    b.load_rooms(fixed, state)
+    assert np.array_equal(unpack_glyphs(b.render(packed=True).cpu().numpy()), o.glyphs())
+    pairs = glyph_pair_table(S.DEFAULT_GLYPHS)
+    for turn in range(8):
+        K = int(rng.integers(1, 4))
+        acts = rng.integers(0, 5, (n, K)).astype(np.uint8)
+        acc, done, flags, nexec = o.step_turn(acts, None)
+        out = b.step(torch.from_numpy(acts).cuda(), packed=True)
+        assert out.obs.shape == (n, H * (W + 1) // 2)
+        assert np.array_equal(b.state.cpu().numpy(), o.state)
+        assert np.array_equal(out.reward.cpu().numpy(), acc) and np.array_equal(out.flags.cpu().numpy(), flags)
+        packed = out.obs.cpu().numpy()
+        assert np.array_equal(unpack_glyphs(packed), o.glyphs())  # includes code 6, player on a target
+    b.render()
+    want = b.texts(S.DEFAULT_GLYPHS)
+    assert [packed_to_text(r, pairs) for r in packed[:64]] == want[:64]
+    # host-buffer path
+    acts = rng.integers(1, 5, n).astype(np.uint8)
+    o.step_turn(acts[:, None], None)
+    h_obs, h_rew, h_done, h_flags, h_nex = b.step_host(acts, packed=True)
+    assert np.array_equal(unpack_glyphs(h_obs), o.glyphs())
+
+
+def test_packed_needs_even_row_stream():
+    b = _batch(4, 7, 6, 1, 10)  # H*(W+1) = 49
+    with pytest.raises(ValueError):
+        b.render(packed=True)
+    from ragen_b200 import _lib
+    buf = torch.zeros(4 * 25, dtype=torch.uint8, device="cuda")
+    rc = b.lib.ragen_sokoban_render_packed(b.ctx.handle, 4, 7, 6, _lib.ptr(b.state), _lib.ptr(b.meta), _lib.ptr(buf), b.ctx.stream())
+    assert rc != 0 and b"even" in b.lib.ragen_last_error()

@@ -52,7 +52,7 @@ def parse_args():
                     help="glyph-row format of the render: two 4-bit codes per byte (what the managers consume) or one code per byte")
     ap.add_argument("--rows", action="store_true", help="per-kernel lines for every SURVEY.md 8(d) config instead of the contract line")
     ap.add_argument("--quick", action="store_true", help="with --rows: smaller batches")
-    ap.add_argument("--only", default="", help="with --rows: comma list of sokoban,generator,frozenlake,parse,c5,manager")
+    ap.add_argument("--only", default="", help="with --rows: comma list of sokoban,generator,frozenlake,parse,c5,manager,rollout")
     return ap.parse_args()
 
 

@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Per-kernel measurement of every config of SURVEY.md 8(d) (C1..C5) on ONE B200, one JSON line per row.
 
-    python bench.py --rows [--quick] [--only sokoban,generator,frozenlake,parse,c5,manager]  > profiles/rNN_kernels.jsonl
+    python bench.py --rows [--quick] [--only sokoban,generator,frozenlake,parse,c5,manager,rollout]  > profiles/rNN_kernels.jsonl
 
 bench.py is the contract line (C4 step); this script is the supporting evidence for the other rows: each line carries
 the kernel's device time (CUDA events on the launching stream, after warm-up, median of the repetitions), the
@@ -298,11 +298,61 @@ def manager_rows(quick):
                       "note": "latency-bound: 9 KB of state; the Python history bookkeeping the API promises dominates"}), flush=True)
 
 
+# ---- C5: rollout -> advantage through the public API, scripted policy -----------------------------------------------------
+def rollout_rows(quick):
+    """8 groups x 16 SimpleSokoban envs, 5 turns, LLMAgentProxy.rollout with the scripted stand-in policy of tests/fake_tokenizer.py
+    (the LLM is out of scope), then compute_advantage (GAE and GRPO).  Wall clock per phase; the policy's own time is reported
+    separately so that what remains is this package's share of a rollout."""
+    from fake_tokenizer import FakeQwenTokenizer, ScriptedWg
+    from oracle import cfg as C
+    from ragen_b200.llm_agent.agent_proxy import LLMAgentProxy
+    from ragen_b200.llm_agent.ctx_manager import DataProto
+    from ragen_b200.trainer import AdvantageEstimator, compute_advantage
+
+    class Timed(ScriptedWg):
+        spent = 0.0
+
+        def generate_sequences(self, lm_inputs):
+            t0 = time.perf_counter()
+            out = super().generate_sequences(lm_inputs)
+            Timed.spent += time.perf_counter() - t0
+            return out
+
+    cfg = C.base_config(tags=("SimpleSokoban",), n_groups=(8,), group_size=16, reward_normalization={"grouping": "state", "method": "mean_std"})
+    tok = FakeQwenTokenizer()
+    proxy = LLMAgentProxy(cfg, Timed(tok, DataProto), tok)
+    res = []
+    for rep in range(4):
+        Timed.spent = 0.0
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        dp = proxy.rollout(DataProto(batch=None, non_tensor_batch=None, meta_info={}), val=False, seed=123 + rep)
+        torch.cuda.synchronize()
+        t_roll = time.perf_counter() - t0
+        batch = dp.batch
+        B, T = batch["rm_scores"].shape
+        batch["response_mask"] = batch["loss_mask"].float()
+        batch["token_level_rewards"] = batch["rm_scores"].clone()
+        batch["values"] = torch.randn(B, T) * batch["response_mask"]
+        dp.non_tensor_batch["uid"] = dp.non_tensor_batch["group_ids"]
+        t0 = time.perf_counter()
+        compute_advantage(dp, AdvantageEstimator.GAE, gamma=1.0, lam=1.0)
+        t_gae = time.perf_counter() - t0
+        t0 = time.perf_counter()
+        compute_advantage(dp, AdvantageEstimator.GRPO, multi_turn=True)
+        t_grpo = time.perf_counter() - t0
+        res.append({"rollout_s": t_roll, "policy_stub_s": Timed.spent, "ours_s": t_roll - Timed.spent, "gae_s": t_gae, "grpo_s": t_grpo,
+                    "B": B, "T": T, "success": float(dp.meta_info["metrics"].get("SimpleSokoban/success", 0.0))})
+    print(json.dumps({"row": "C5 rollout -> advantage through LLMAgentProxy / compute_advantage, 8 groups x 16 SimpleSokoban, 5 turns, scripted policy "
+                             "(wall clock, CPU tensors in and out as the reference's driver has them; first repetition includes warm-up)",
+                      "reps": res}), flush=True)
+
+
 def main(quick=False, only=""):
     a = argparse.Namespace(quick=quick, only=only)
     torch.cuda.set_device(0)
     todo = {"sokoban": sokoban_rows, "generator": generator_rows, "frozenlake": frozenlake_rows, "parse": parse_rows, "c5": c5_rows,
-            "manager": manager_rows}
+            "manager": manager_rows, "rollout": rollout_rows}
     for name, fn in todo.items():
         if a.only and name not in a.only.split(","):
             continue

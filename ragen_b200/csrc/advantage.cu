@@ -16,76 +16,137 @@
 
 namespace {
 
-constexpr int ROWS_PER_CTA = 4;   // warps per CTA
-constexpr int CHUNK = 1024;       // tokens staged per warp per iteration
+constexpr int RT = 256;       // threads of the CTA that owns one row
+constexpr int RCHUNK = 2048;  // tokens of the row staged in shared memory per iteration (C5's T = 2047: one pass)
 
+// block-wide sum of three doubles, then ONE set of atomics per CTA
 __device__ __forceinline__ void add_moments(double* moments, double s0, double s1, double s2) {
+  __shared__ double red[3][RT / 32];
   s0 = warp_sum(s0);
   s1 = warp_sum(s1);
   s2 = warp_sum(s2);
-  if ((threadIdx.x & 31) == 0 && moments) {
-    atomicAdd(moments + 0, s0);
-    atomicAdd(moments + 1, s1);
-    atomicAdd(moments + 2, s2);
+  const int w = threadIdx.x >> 5;
+  if ((threadIdx.x & 31) == 0) {
+    red[0][w] = s0;
+    red[1][w] = s1;
+    red[2][w] = s2;
   }
+  __syncthreads();
+  if (threadIdx.x < 3 && moments) {
+    double t = 0.0;
+#pragma unroll
+    for (int k = 0; k < RT / 32; ++k) t += red[threadIdx.x][k];
+    atomicAdd(moments + threadIdx.x, t);
+  }
+}
+
+__device__ __forceinline__ double block_sum(double v) {  // every thread gets the sum
+  __shared__ double red[RT / 32];
+  __syncthreads();
+  v = warp_sum(v);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+  __syncthreads();
+  double t = 0.0;
+#pragma unroll
+  for (int k = 0; k < RT / 32; ++k) t += red[k];
+  return t;
+}
+
+// The serial part of every estimator here is x <- d[i] + c * x walked right to left by ONE thread over a row staged in
+// shared memory.  Written naively, each step waits for its own shared-memory loads (~30 cycles) before the 8-cycle
+// multiply-add; these helpers load a batch of 16 operands into registers first, so the loads of a batch overlap and only
+// the dependent multiply-adds remain on the critical path.  Same operations, same order: results are unchanged.
+constexpr int BATCH = 16;
+
+// d[i] <- x = d[i] + c * x for i = hi-1 .. lo (c constant)
+__device__ __forceinline__ float chain_const(float* d, int lo, int hi, float c, float x) {
+  int i = hi - 1;
+  for (; i - (BATCH - 1) >= lo; i -= BATCH) {
+    float v[BATCH];
+#pragma unroll
+    for (int k = 0; k < BATCH; ++k) v[k] = d[i - k];
+#pragma unroll
+    for (int k = 0; k < BATCH; ++k) {
+      x = __fadd_rn(v[k], __fmul_rn(c, x));
+      v[k] = x;
+    }
+#pragma unroll
+    for (int k = 0; k < BATCH; ++k) d[i - k] = v[k];
+  }
+  for (; i >= lo; --i) {
+    x = __fadd_rn(d[i], __fmul_rn(c, x));
+    d[i] = x;
+  }
+  return x;
+}
+
+// d[i] <- x = d[i] + c[i] * x for i = hi-1 .. lo (per-token coefficient)
+__device__ __forceinline__ float chain_var(float* d, const float* c, int lo, int hi, float x) {
+  int i = hi - 1;
+  for (; i - (BATCH - 1) >= lo; i -= BATCH) {
+    float v[BATCH], w[BATCH];
+#pragma unroll
+    for (int k = 0; k < BATCH; ++k) {
+      v[k] = d[i - k];
+      w[k] = c[i - k];
+    }
+#pragma unroll
+    for (int k = 0; k < BATCH; ++k) {
+      x = __fadd_rn(v[k], __fmul_rn(w[k], x));
+      v[k] = x;
+    }
+#pragma unroll
+    for (int k = 0; k < BATCH; ++k) d[i - k] = v[k];
+  }
+  for (; i >= lo; --i) {
+    x = __fadd_rn(d[i], __fmul_rn(c[i], x));
+    d[i] = x;
+  }
+  return x;
 }
 
 // A_t = (r_t + gamma V_{t+1} - V_t) + (gamma lam) A_{t+1}, V_T = 0, over ALL columns (core_algos.py:98-105);
 // returns = A + V (:107).  gamma and gamma*lam arrive already rounded to fp32 the way torch rounds a Python scalar
-// that multiplies an fp32 tensor.
-__global__ void __launch_bounds__(ROWS_PER_CTA * 32) gae_kernel(int B, int T, const float* __restrict__ rewards,
-                                                                 const float* __restrict__ values,
-                                                                 const uint8_t* __restrict__ mask, float gamma, float gl,
-                                                                 float* __restrict__ adv, float* __restrict__ ret,
-                                                                 double* moments) {
-  __shared__ float s_a[ROWS_PER_CTA][CHUNK];
-  __shared__ float s_v[ROWS_PER_CTA][CHUNK];
-  __shared__ uint8_t s_m[ROWS_PER_CTA][CHUNK];
-  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int row = blockIdx.x * ROWS_PER_CTA + w;
+// that multiplies an fp32 tensor.  One CTA per row: 256 threads stage the row and form the deltas (the loads are what
+// bounds this pass at C5, so they are spread over many threads), thread 0 runs the first-order recurrence in the
+// reference's exact fp32 order, 256 threads write back and reduce the masked moments.
+__global__ void __launch_bounds__(RT) gae_kernel(int B, int T, const float* __restrict__ rewards, const float* __restrict__ values,
+                                                 const uint8_t* __restrict__ mask, float gamma, float gl, float* __restrict__ adv,
+                                                 float* __restrict__ ret, double* moments) {
+  __shared__ float s_a[RCHUNK];
+  __shared__ float s_v[RCHUNK];
+  __shared__ uint8_t s_m[RCHUNK];
+  const int tid = threadIdx.x;
+  const size_t base = (size_t)blockIdx.x * T;
   double m0 = 0.0, m1 = 0.0, m2 = 0.0;
-  if (row < B) {
-    const size_t base = (size_t)row * T;
-    float carry = 0.0f;
-    for (int t1 = T; t1 > 0; t1 -= CHUNK) {
-      const int t0 = max(0, t1 - CHUNK), len = t1 - t0;
-      // the unrolled loop keeps 8 x 4 independent loads in flight per lane: at C5 (128 rows) the pass is bound by
-      // memory latency, not bandwidth
-#pragma unroll 8
-      for (int i = lane; i < len; i += 32) {
-        const int t = t0 + i;
-        const float v = __ldg(values + base + t);
-        const float vn = (t + 1 < T) ? __ldg(values + base + t + 1) : 0.0f;
-        const float r = __ldg(rewards + base + t);
-        s_m[w][i] = mask[base + t];
-        s_a[w][i] = __fsub_rn(__fadd_rn(r, __fmul_rn(gamma, vn)), v);
-        s_v[w][i] = v;
-      }
-      __syncwarp();
-      if (lane == 0) {
-        float lg = carry;
-#pragma unroll 8
-        for (int i = len - 1; i >= 0; --i) {
-          lg = __fadd_rn(s_a[w][i], __fmul_rn(gl, lg));
-          s_a[w][i] = lg;
-        }
-        carry = lg;
-      }
-      __syncwarp();
-#pragma unroll 8
-      for (int i = lane; i < len; i += 32) {
-        const int t = t0 + i;
-        const float a = s_a[w][i];
-        adv[base + t] = a;
-        ret[base + t] = __fadd_rn(a, s_v[w][i]);
-        if (s_m[w][i]) {
-          m0 += 1.0;
-          m1 += (double)a;
-          m2 += (double)a * (double)a;
-        }
-      }
-      __syncwarp();
+  float carry = 0.0f;  // thread 0
+  for (int t1 = T; t1 > 0; t1 -= RCHUNK) {
+    const int t0 = max(0, t1 - RCHUNK), len = t1 - t0;
+#pragma unroll 4
+    for (int i = tid; i < len; i += RT) {
+      const int t = t0 + i;
+      const float v = __ldg(values + base + t);
+      const float vn = (t + 1 < T) ? __ldg(values + base + t + 1) : 0.0f;
+      const float r = __ldg(rewards + base + t);
+      s_m[i] = mask[base + t];
+      s_a[i] = __fsub_rn(__fadd_rn(r, __fmul_rn(gamma, vn)), v);
+      s_v[i] = v;
     }
+    __syncthreads();
+    if (tid == 0) carry = chain_const(s_a, 0, len, gl, carry);
+    __syncthreads();
+#pragma unroll 4
+    for (int i = tid; i < len; i += RT) {
+      const float a = s_a[i];
+      adv[base + t0 + i] = a;
+      ret[base + t0 + i] = __fadd_rn(a, s_v[i]);
+      if (s_m[i]) {
+        m0 += 1.0;
+        m1 += (double)a;
+        m2 += (double)a * (double)a;
+      }
+    }
+    __syncthreads();
   }
   add_moments(moments, m0, m1, m2);
 }
@@ -93,82 +154,154 @@ __global__ void __launch_bounds__(ROWS_PER_CTA * 32) gae_kernel(int B, int T, co
 // ragen/trainer/core_algos.py:44-88 for one row, as ONE backward sweep: the turn-level estimate at a reward
 // position depends only on later reward positions, and the token-level pass at that position only needs the
 // turn-level result of the same position, so both passes advance together.  fp32 operation order as the reference.
-__global__ void __launch_bounds__(ROWS_PER_CTA * 32) bilevel_gae_kernel(int B, int T, const float* __restrict__ rewards,
-                                                                         const float* __restrict__ values,
-                                                                         const uint8_t* __restrict__ mask, float gamma,
-                                                                         float gl, float hgamma, float hgl,
-                                                                         float* __restrict__ adv, float* __restrict__ ret,
-                                                                         double* moments) {
-  __shared__ float s_r[ROWS_PER_CTA][CHUNK];  // rewards in, advantages out
-  __shared__ float s_v[ROWS_PER_CTA][CHUNK];  // values in, returns out
-  __shared__ uint8_t s_m[ROWS_PER_CTA][CHUNK];
-  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int row = blockIdx.x * ROWS_PER_CTA + w;
+//
+// Per chunk (right to left) the work is split so that the serial part is only the recurrence itself:
+//   A (256 threads) "value of the next loss-mask token to the right": per 32-token group by ballot + shuffle, across
+//                   groups through a per-group table in shared memory; it turns every non-reward loss-mask token into
+//                   its delta = (0 + gamma * next_value) - value;
+//   B (thread 0)    lo = d + c * lo over the tokens BETWEEN reward positions as a branch-free, unrolled loop: c = gamma*lam and
+//                   d = delta on a loss-mask token, c = 1 and d = 0 (an exact identity in fp32) elsewhere, so the loop's
+//                   shared-memory loads run ahead of the dependent multiply-add; reward positions (a handful per row, listed
+//                   by phase A) run the turn-level step, reset the token-level state and restart it from the updated
+//                   reward (:73-88);
+//   C (256 threads) returns = advantage + value, zeros off the loss mask, moments, coalesced stores.
+__global__ void __launch_bounds__(RT) bilevel_gae_kernel(int B, int T, const float* __restrict__ rewards,
+                                                         const float* __restrict__ values, const uint8_t* __restrict__ mask,
+                                                         float gamma, float gl, float hgamma, float hgl, float* __restrict__ adv,
+                                                         float* __restrict__ ret, double* moments) {
+  constexpr int NG = RCHUNK / 32;
+  __shared__ float s_r[RCHUNK];    // rewards in -> deltas -> advantages out
+  __shared__ float s_v[RCHUNK];    // values in (returns out at reward positions)
+  __shared__ uint8_t s_m[RCHUNK];  // bit0 loss mask, bit1 reward position
+  __shared__ float s_c[RCHUNK];    // recurrence coefficient per token
+  __shared__ float g_first[NG];    // value of the leftmost loss-mask token of each 32-token group
+  __shared__ uint8_t g_has[NG];
+  __shared__ unsigned g_eos[NG];   // reward positions of each group, as a bit mask
+  __shared__ float s_carry;        // value of the nearest loss-mask token right of the current chunk
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const size_t base = (size_t)blockIdx.x * T;
   double m0 = 0.0, m1 = 0.0, m2 = 0.0;
-  if (row < B) {
-    const size_t base = (size_t)row * T;
-    // sweep state (lane 0 only)
-    bool hi_has_next = false, lo_has_next = false;
-    float hi_next_v = 0.0f, lo_next_v = 0.0f, hi_lg = 0.0f, lo_lg = 0.0f;
-    for (int t1 = T; t1 > 0; t1 -= CHUNK) {
-      const int t0 = max(0, t1 - CHUNK), len = t1 - t0;
-#pragma unroll 8
-      for (int i = lane; i < len; i += 32) {
-        s_r[w][i] = __ldg(rewards + base + t0 + i);
-        s_v[w][i] = __ldg(values + base + t0 + i);
-        s_m[w][i] = mask[base + t0 + i];
-      }
-      __syncwarp();
+  bool hi_has_next = false;                            // thread 0: turn-level state
+  float hi_next_v = 0.0f, hi_lg = 0.0f, lo_lg = 0.0f;  // thread 0
+  if (tid == 0) s_carry = 0.0f;
+  for (int t1 = T; t1 > 0; t1 -= RCHUNK) {
+    const int t0 = max(0, t1 - RCHUNK), len = t1 - t0;
+    const int ngroups = (len + 31) >> 5;
+    // ---- A1: stage, per-group leftmost loss-mask value -----------------------------------------------------------
+    for (int g = wid; g < ngroups; g += RT / 32) {
+      const int i = (g << 5) + lane;
+      const bool in = i < len;
+      const float r = in ? __ldg(rewards + base + t0 + i) : 0.0f;
+      const float v = in ? __ldg(values + base + t0 + i) : 0.0f;
+      const bool m = in && mask[base + t0 + i] != 0;
+      const bool eos = in && r != 0.0f;  // reward_mask = token_level_rewards.bool()
+      const unsigned bits = __ballot_sync(0xffffffffu, m);
+      const float first_v = __shfl_sync(0xffffffffu, v, bits ? (__ffs(bits) - 1) : 0);
+      const unsigned ebits = __ballot_sync(0xffffffffu, eos);
       if (lane == 0) {
-        for (int i = len - 1; i >= 0; --i) {
-          const float r = s_r[w][i], v = s_v[w][i];
-          const bool is_eos = (r != 0.0f);  // reward_mask = token_level_rewards.bool()
-          float a_out = 0.0f, r_out = 0.0f, upd = r;
-          if (is_eos) {
-            const float nv = hi_has_next ? hi_next_v : 0.0f;
-            const float delta = __fsub_rn(__fadd_rn(r, __fmul_rn(hgamma, nv)), v);
-            hi_lg = __fadd_rn(delta, __fmul_rn(hgl, hi_lg));
-            hi_next_v = v;
-            hi_has_next = true;
-            a_out = hi_lg;
-            upd = __fadd_rn(hi_lg, v);  // returns[pos] = updated_reward[pos] = advantages[pos] + values[pos]
-            r_out = upd;
+        g_first[g] = first_v;
+        g_has[g] = bits ? 1 : 0;
+        g_eos[g] = ebits;
+      }
+      if (in) {
+        s_r[i] = r;
+        s_v[i] = v;
+        s_m[i] = (uint8_t)((m ? 1 : 0) | (eos ? 2 : 0));
+      }
+    }
+    __syncthreads();
+    // ---- A2: deltas of the non-reward loss-mask tokens --------------------------------------------------------------
+    for (int g = wid; g < ngroups; g += RT / 32) {
+      const int i = (g << 5) + lane;
+      const bool in = i < len;
+      const int f = in ? s_m[i] : 0;
+      const float v = in ? s_v[i] : 0.0f;
+      const unsigned bits = __ballot_sync(0xffffffffu, (f & 1) != 0);
+      const unsigned higher = (lane == 31) ? 0u : (bits & (0xfffffffeu << lane));
+      const float from_group = __shfl_sync(0xffffffffu, v, higher ? (__ffs(higher) - 1) : 0);
+      float nv = from_group;
+      if (!higher) {
+        // the reference indexes valid_positions[i + 1] here and raises IndexError when the last loss-mask position
+        // carries no reward; that input is treated as "next value 0" (s_carry starts at 0)
+        nv = s_carry;
+        for (int h = g + 1; h < ngroups; ++h)
+          if (g_has[h]) {
+            nv = g_first[h];
+            break;
           }
-          if (s_m[w][i]) {
-            float nv;
-            if (is_eos) {
-              nv = 0.0f;
-              lo_lg = 0.0f;
-            } else {
-              // the reference indexes valid_positions[i + 1] here and raises IndexError when the last loss-mask
-              // position carries no reward; that input is treated as "next value 0"
-              nv = lo_has_next ? lo_next_v : 0.0f;
-            }
-            const float delta = __fsub_rn(__fadd_rn(upd, __fmul_rn(gamma, nv)), v);
-            lo_lg = __fadd_rn(delta, __fmul_rn(gl, lo_lg));
-            lo_next_v = v;
-            lo_has_next = true;
+      }
+      if (in) {
+        if (f == 1) {
+          s_r[i] = __fsub_rn(__fadd_rn(s_r[i], __fmul_rn(gamma, nv)), v);
+          s_c[i] = gl;
+        } else if (f == 0) {
+          s_r[i] = 0.0f;
+          s_c[i] = 1.0f;
+        }
+      }
+    }
+    __syncthreads();
+    // ---- B -------------------------------------------------------------------------------------------------------------
+    if (tid == 0) {
+      for (int h = 0; h < ngroups; ++h)
+        if (g_has[h]) {
+          s_carry = g_first[h];  // for the chunk to the left
+          break;
+        }
+      auto run_segment = [&](int lo_end, int hi_end) {  // tokens hi_end-1 .. lo_end, none of them a reward position
+        lo_lg = chain_var(s_r, s_c, lo_end, hi_end, lo_lg);
+      };
+      int seg_end = len;
+      for (int g = ngroups - 1; g >= 0; --g) {
+        unsigned eb = g_eos[g];
+        while (eb) {  // reward positions of this group, right to left
+          const int bit = 31 - __clz(eb);
+          eb &= ~(1u << bit);
+          const int pos = (g << 5) + bit;
+          run_segment(pos + 1, seg_end);
+          const int f = s_m[pos];
+          const float r = s_r[pos], v = s_v[pos];
+          const float nvh = hi_has_next ? hi_next_v : 0.0f;
+          hi_lg = __fadd_rn(__fsub_rn(__fadd_rn(r, __fmul_rn(hgamma, nvh)), v), __fmul_rn(hgl, hi_lg));
+          hi_next_v = v;
+          hi_has_next = true;
+          const float upd = __fadd_rn(hi_lg, v);  // returns[pos] = updated_reward[pos] = advantages[pos] + values[pos]
+          float a_out = hi_lg, r_out = upd;
+          if (f & 1) {  // token-level pass restarts at a reward position: next value 0, lastgaelam 0
+            const float delta = __fsub_rn(__fadd_rn(upd, __fmul_rn(gamma, 0.0f)), v);
+            lo_lg = __fadd_rn(delta, __fmul_rn(gl, 0.0f));
             a_out = lo_lg;
             r_out = __fadd_rn(lo_lg, v);
           }
-          s_r[w][i] = a_out;
-          s_v[w][i] = r_out;
+          s_r[pos] = a_out;
+          s_v[pos] = r_out;
+          seg_end = pos;
         }
       }
-      __syncwarp();
-#pragma unroll 8
-      for (int i = lane; i < len; i += 32) {
-        const float a = s_r[w][i];
-        adv[base + t0 + i] = a;
-        ret[base + t0 + i] = s_v[w][i];
-        if (s_m[w][i]) {
-          m0 += 1.0;
-          m1 += (double)a;
-          m2 += (double)a * (double)a;
-        }
-      }
-      __syncwarp();
+      run_segment(0, seg_end);
     }
+    __syncthreads();
+    // ---- C -------------------------------------------------------------------------------------------------------------
+#pragma unroll 4
+    for (int i = tid; i < len; i += RT) {
+      const int f = s_m[i];
+      float a = 0.0f, rt = 0.0f;
+      if (f == 1) {
+        a = s_r[i];
+        rt = __fadd_rn(a, s_v[i]);
+      } else if (f & 2) {
+        a = s_r[i];
+        rt = s_v[i];
+      }
+      adv[base + t0 + i] = a;
+      ret[base + t0 + i] = rt;
+      if (f & 1) {
+        m0 += 1.0;
+        m1 += (double)a;
+        m2 += (double)a * (double)a;
+      }
+    }
+    __syncthreads();
   }
   add_moments(moments, m0, m1, m2);
 }
@@ -201,21 +334,21 @@ __global__ void moments_kernel(int64_t n, const float* __restrict__ x, const uin
   add_moments(moments, m0, m1, m2);
 }
 
-// GRPO step 1: scores[b] = sum_t rewards[b][t]; per-group {count, sum, sum of squares} (core_algos.py:139-149)
-__global__ void __launch_bounds__(ROWS_PER_CTA * 32) grpo_scores_kernel(int B, int T, const float* __restrict__ rewards,
-                                                                         const int32_t* __restrict__ group, int n_groups,
-                                                                         float* __restrict__ scores, double* gstats) {
-  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int row = blockIdx.x * ROWS_PER_CTA + w;
-  if (row >= B) return;
+// Outcome estimators, step 1: scores[b] = sum_t rewards[b][t] (fp64 accumulation, rounded once); per-group
+// {count, sum, sum of squares} (core_algos.py:139-149).  One CTA per row.
+__global__ void __launch_bounds__(RT) grpo_scores_kernel(int B, int T, const float* __restrict__ rewards,
+                                                         const int32_t* __restrict__ group, int n_groups,
+                                                         float* __restrict__ scores, double* gstats) {
+  const int row = blockIdx.x;
   const size_t base = (size_t)row * T;
   double s = 0.0;
-  for (int t = lane; t < T; t += 32) s += (double)rewards[base + t];
-  s = warp_sum(s);
-  if (lane == 0) {
+#pragma unroll 4
+  for (int t = threadIdx.x; t < T; t += RT) s += (double)__ldg(rewards + base + t);
+  s = block_sum(s);
+  if (threadIdx.x == 0) {
     const float sf = (float)s;
     scores[row] = sf;
-    const int g = group[row];
+    const int g = group ? group[row] : -1;
     if (g >= 0 && g < n_groups) {
       atomicAdd(gstats + 3 * g + 0, 1.0);
       atomicAdd(gstats + 3 * g + 1, (double)sf);
@@ -224,140 +357,125 @@ __global__ void __launch_bounds__(ROWS_PER_CTA * 32) grpo_scores_kernel(int B, i
   }
 }
 
-// GRPO step 2: (score - mean) / (std + eps) (unbiased std; groups of one: mean 0, std 1), broadcast over the
-// row and multiplied by the mask (core_algos.py:150-165).
-__global__ void __launch_bounds__(ROWS_PER_CTA * 32) grpo_apply_kernel(int B, int T, const float* __restrict__ scores,
-                                                                        const int32_t* __restrict__ group, int n_groups,
-                                                                        const double* __restrict__ gstats,
-                                                                        const uint8_t* __restrict__ mask, float eps,
-                                                                        int norm_by_std, float* __restrict__ adv) {
-  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int row = blockIdx.x * ROWS_PER_CTA + w;
-  if (row >= B) return;
+// Step 2.  mode 0: score - mean (GRPO without std); 1: GRPO, (score - mean) / (std + eps) with the unbiased std
+// (core_algos.py:150-165); 2: RLOO, score*n/(n-1) - mean*n/(n-1) for groups of n > 1 (:205-242); 3: REINFORCE++-baseline,
+// score - mean, to be whitened by the caller from `moments` (:168-202).  Groups of one use mean 0 (and std 1).  The value is
+// broadcast over the row and multiplied by the mask.
+__global__ void __launch_bounds__(RT) outcome_apply_kernel(int B, int T, const float* __restrict__ scores,
+                                                           const int32_t* __restrict__ group, int n_groups,
+                                                           const double* __restrict__ gstats, const uint8_t* __restrict__ mask,
+                                                           float eps, int mode, float* __restrict__ adv, double* moments) {
+  const int row = blockIdx.x;
   const int g = group[row];
-  float mean = 0.0f, sd = 1.0f;
+  float mean = 0.0f, sd = 1.0f, cnt = 1.0f;
   if (g >= 0 && g < n_groups) {
     const double c = gstats[3 * g], s1 = gstats[3 * g + 1], s2 = gstats[3 * g + 2];
+    cnt = (float)c;
     if (c > 1.5) {
       const double mu = s1 / c;
-      const double var = fmax((s2 - c * mu * mu) / (c - 1.0), 0.0);
       mean = (float)mu;
-      sd = (float)sqrt(var);
+      sd = (float)sqrt(fmax((s2 - c * mu * mu) / (c - 1.0), 0.0));
     }
   }
   const float sc = scores[row];
-  const float val = norm_by_std ? __fdiv_rn(__fsub_rn(sc, mean), __fadd_rn(sd, eps)) : __fsub_rn(sc, mean);
-  const size_t base = (size_t)row * T;
-  for (int t = lane; t < T; t += 32) adv[base + t] = mask[base + t] ? val : __fmul_rn(val, 0.0f);
-}
-
-// ---- the remaining members of compute_advantage's dispatch table (agent_trainer.py:106-134) ---------------------------
-// Outcome estimators share GRPO's first step (row scores + per-group count / sum / sum of squares); this is their second
-// step.  mode 0: score - mean (GRPO without std); 1: GRPO; 2: RLOO, score*n/(n-1) - mean*n/(n-1) for groups of n > 1
-// (core_algos.py:205-242); 3: REINFORCE++-baseline, score - mean, to be whitened by the caller from `moments` (:168-202).
-// Groups of one use mean 0 (and std 1).  The value is broadcast over the row and multiplied by the mask.
-__global__ void __launch_bounds__(ROWS_PER_CTA * 32) outcome_apply_kernel(int B, int T, const float* __restrict__ scores,
-                                                                           const int32_t* __restrict__ group, int n_groups,
-                                                                           const double* __restrict__ gstats,
-                                                                           const uint8_t* __restrict__ mask, float eps, int mode,
-                                                                           float* __restrict__ adv, double* moments) {
-  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int row = blockIdx.x * ROWS_PER_CTA + w;
-  double m0 = 0.0, m1 = 0.0, m2 = 0.0;
-  if (row < B) {
-    const int g = group[row];
-    float mean = 0.0f, sd = 1.0f, cnt = 1.0f;
-    if (g >= 0 && g < n_groups) {
-      const double c = gstats[3 * g], s1 = gstats[3 * g + 1], s2 = gstats[3 * g + 2];
-      cnt = (float)c;
-      if (c > 1.5) {
-        const double mu = s1 / c;
-        mean = (float)mu;
-        sd = (float)sqrt(fmax((s2 - c * mu * mu) / (c - 1.0), 0.0));
-      }
-    }
-    const float sc = scores[row];
-    float val;
-    if (mode == 1) {
-      val = __fdiv_rn(__fsub_rn(sc, mean), __fadd_rn(sd, eps));
-    } else if (mode == 2) {
-      val = sc;
-      if (cnt > 1.5f) val = __fsub_rn(__fdiv_rn(__fmul_rn(sc, cnt), cnt - 1.0f), __fdiv_rn(__fmul_rn(mean, cnt), cnt - 1.0f));
-    } else {
-      val = __fsub_rn(sc, mean);
-    }
-    const size_t base = (size_t)row * T;
-    const float off = __fmul_rn(val, 0.0f);
-    int on = 0;
-#pragma unroll 4
-    for (int t = lane; t < T; t += 32) {
-      const bool m = mask[base + t] != 0;
-      adv[base + t] = m ? val : off;
-      on += m;
-    }
-    m0 = (double)on;
-    m1 = (double)on * (double)val;
-    m2 = (double)on * (double)val * (double)val;
+  float val;
+  if (mode == 1) {
+    val = __fdiv_rn(__fsub_rn(sc, mean), __fadd_rn(sd, eps));
+  } else if (mode == 2) {
+    val = sc;
+    if (cnt > 1.5f) val = __fsub_rn(__fdiv_rn(__fmul_rn(sc, cnt), cnt - 1.0f), __fdiv_rn(__fmul_rn(mean, cnt), cnt - 1.0f));
+  } else {
+    val = __fsub_rn(sc, mean);
   }
-  if (moments) add_moments(moments, m0, m1, m2);
+  const size_t base = (size_t)row * T;
+  const float off = __fmul_rn(val, 0.0f);
+  int on = 0;
+#pragma unroll 4
+  for (int t = threadIdx.x; t < T; t += RT) {
+    const bool m = mask[base + t] != 0;
+    adv[base + t] = m ? val : off;
+    on += m;
+  }
+  if (moments) add_moments(moments, (double)on, (double)on * (double)val, (double)on * (double)val * (double)val);
 }
 
 // REINFORCE++ (core_algos.py:245-278): running = r_t + gamma * running, returns_t = running, running *= mask_t, right to
 // left, in the reference's fp32 order; plus the masked moments of the returns for the whitening that follows.
 // REMAX = 1 (core_algos.py:281-305): returns = reverse cumulative sum of rewards*mask (torch's CPU cumsum accumulates
-// fp32 data in double and rounds every prefix), adv = returns - baseline * mask.
+// fp32 data in double and rounds every prefix), adv = returns - baseline * mask.  One CTA per row, as gae_kernel.
 template <int REMAX>
-__global__ void __launch_bounds__(ROWS_PER_CTA * 32) returns_kernel(int B, int T, const float* __restrict__ rewards,
-                                                                     const uint8_t* __restrict__ mask, float gamma,
-                                                                     const float* __restrict__ baselines,
-                                                                     float* __restrict__ adv, float* __restrict__ ret,
-                                                                     double* moments) {
-  __shared__ float s_r[ROWS_PER_CTA][CHUNK];
-  __shared__ uint8_t s_m[ROWS_PER_CTA][CHUNK];
-  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int row = blockIdx.x * ROWS_PER_CTA + w;
+__global__ void __launch_bounds__(RT) returns_kernel(int B, int T, const float* __restrict__ rewards,
+                                                     const uint8_t* __restrict__ mask, float gamma,
+                                                     const float* __restrict__ baselines, float* __restrict__ adv,
+                                                     float* __restrict__ ret, double* moments) {
+  __shared__ float s_r[RCHUNK];
+  __shared__ uint8_t s_m[RCHUNK];
+  const int tid = threadIdx.x;
+  const int row = blockIdx.x;
+  const size_t base = (size_t)row * T;
+  const float bl = REMAX ? baselines[row] : 0.0f;
   double m0 = 0.0, m1 = 0.0, m2 = 0.0;
-  if (row < B) {
-    const size_t base = (size_t)row * T;
-    const float bl = REMAX ? baselines[row] : 0.0f;
-    float run = 0.0f;
-    double acc = 0.0;
-    for (int t1 = T; t1 > 0; t1 -= CHUNK) {
-      const int t0 = max(0, t1 - CHUNK), len = t1 - t0;
-#pragma unroll 8
-      for (int i = lane; i < len; i += 32) {
-        s_r[w][i] = __ldg(rewards + base + t0 + i);
-        s_m[w][i] = mask[base + t0 + i];
-      }
-      __syncwarp();
-      if (lane == 0) {
-#pragma unroll 8
-        for (int i = len - 1; i >= 0; --i) {
+  float run = 0.0f;   // thread 0
+  double acc = 0.0;   // thread 0
+  for (int t1 = T; t1 > 0; t1 -= RCHUNK) {
+    const int t0 = max(0, t1 - RCHUNK), len = t1 - t0;
+#pragma unroll 4
+    for (int i = tid; i < len; i += RT) {
+      const float r = __ldg(rewards + base + t0 + i);
+      const uint8_t m = mask[base + t0 + i];
+      s_m[i] = m;
+      s_r[i] = (REMAX && !m) ? __fmul_rn(r, 0.0f) : r;  // rewards * mask
+    }
+    __syncthreads();
+    if (tid == 0) {
+      int i = len - 1;
+      for (; i - (BATCH - 1) >= 0; i -= BATCH) {  // operands of a batch are loaded before the dependent chain starts
+        float v[BATCH];
+        uint8_t mk[BATCH];
+#pragma unroll
+        for (int k = 0; k < BATCH; ++k) {
+          v[k] = s_r[i - k];
+          mk[k] = s_m[i - k];
+        }
+#pragma unroll
+        for (int k = 0; k < BATCH; ++k) {
           if (REMAX) {
-            acc += s_m[w][i] ? (double)s_r[w][i] : (double)__fmul_rn(s_r[w][i], 0.0f);
-            s_r[w][i] = (float)acc;
+            acc += (double)v[k];
+            v[k] = (float)acc;
           } else {
-            run = __fadd_rn(s_r[w][i], __fmul_rn(gamma, run));
-            s_r[w][i] = run;
-            run = s_m[w][i] ? run : __fmul_rn(run, 0.0f);
+            run = __fadd_rn(v[k], __fmul_rn(gamma, run));
+            v[k] = run;
+            run = mk[k] ? run : __fmul_rn(run, 0.0f);
           }
         }
+#pragma unroll
+        for (int k = 0; k < BATCH; ++k) s_r[i - k] = v[k];
       }
-      __syncwarp();
-#pragma unroll 8
-      for (int i = lane; i < len; i += 32) {
-        const float x = s_r[w][i];
-        ret[base + t0 + i] = x;
+      for (; i >= 0; --i) {
         if (REMAX) {
-          adv[base + t0 + i] = __fsub_rn(x, s_m[w][i] ? bl : __fmul_rn(bl, 0.0f));
-        } else if (s_m[w][i]) {
-          m0 += 1.0;
-          m1 += (double)x;
-          m2 += (double)x * (double)x;
+          acc += (double)s_r[i];
+          s_r[i] = (float)acc;
+        } else {
+          run = __fadd_rn(s_r[i], __fmul_rn(gamma, run));
+          s_r[i] = run;
+          run = s_m[i] ? run : __fmul_rn(run, 0.0f);
         }
       }
-      __syncwarp();
     }
+    __syncthreads();
+#pragma unroll 4
+    for (int i = tid; i < len; i += RT) {
+      const float x = s_r[i];
+      ret[base + t0 + i] = x;
+      if (REMAX) {
+        adv[base + t0 + i] = __fsub_rn(x, s_m[i] ? bl : __fmul_rn(bl, 0.0f));
+      } else if (s_m[i]) {
+        m0 += 1.0;
+        m1 += (double)x;
+        m2 += (double)x * (double)x;
+      }
+    }
+    __syncthreads();
   }
   if (!REMAX) add_moments(moments, m0, m1, m2);
 }
@@ -380,19 +498,16 @@ __global__ void whiten_masked_kernel(int64_t n, const float* __restrict__ x, con
 
 // apply_kl_penalty (verl/verl/trainer/ppo/ray_trainer.py:145-175) with kl_penalty (core_algos.py:469-501):
 // kld = f(logp, ref) * mask; rewards = scores - beta * kld; row_kl[b] = sum(kld) / (sum(mask) + 1e-8).
-// mode 0 "kl", 1 "abs", 2 "mse", 3 "low_var_kl".
-__global__ void __launch_bounds__(ROWS_PER_CTA * 32) kl_rewards_kernel(int B, int T, const float* __restrict__ scores,
-                                                                        const float* __restrict__ logp,
-                                                                        const float* __restrict__ ref,
-                                                                        const uint8_t* __restrict__ mask, int mode, float beta,
-                                                                        float* __restrict__ out, float* __restrict__ row_kl) {
-  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int row = blockIdx.x * ROWS_PER_CTA + w;
-  if (row >= B) return;
+// mode 0 "kl", 1 "abs", 2 "mse", 3 "low_var_kl".  One CTA per row.
+__global__ void __launch_bounds__(RT) kl_rewards_kernel(int B, int T, const float* __restrict__ scores,
+                                                        const float* __restrict__ logp, const float* __restrict__ ref,
+                                                        const uint8_t* __restrict__ mask, int mode, float beta,
+                                                        float* __restrict__ out, float* __restrict__ row_kl) {
+  const int row = blockIdx.x;
   const size_t base = (size_t)row * T;
-  float ksum = 0.0f, msum = 0.0f;
+  double ksum = 0.0, msum = 0.0;
 #pragma unroll 4
-  for (int t = lane; t < T; t += 32) {
+  for (int t = threadIdx.x; t < T; t += RT) {
     const float a = __ldg(logp + base + t), b = __ldg(ref + base + t);
     float k;
     if (mode == 0) {
@@ -410,45 +525,33 @@ __global__ void __launch_bounds__(ROWS_PER_CTA * 32) kl_rewards_kernel(int B, in
     const bool m = mask[base + t] != 0;
     k = m ? k : __fmul_rn(k, 0.0f);
     out[base + t] = __fsub_rn(__ldg(scores + base + t), __fmul_rn(beta, k));
-    ksum += k;
-    msum += m ? 1.0f : 0.0f;
+    ksum += (double)k;
+    msum += m ? 1.0 : 0.0;
   }
-  ksum = warp_sum(ksum);
-  msum = warp_sum(msum);
-  if (lane == 0 && row_kl) row_kl[row] = ksum / (msum + 1e-8f);
+  ksum = block_sum(ksum);
+  msum = block_sum(msum);
+  if (threadIdx.x == 0 && row_kl) row_kl[row] = (float)ksum / ((float)msum + 1e-8f);
 }
 
-// _filter_rollout's statistics (ragen/trainer/agent_trainer.py:466-469): row sums of the score tensor, then per group
-// of `group_size` consecutive rows the unbiased std, the max and the mean.  One warp per group, lane per row.
-__global__ void __launch_bounds__(ROWS_PER_CTA * 32) filter_stats_kernel(int n_groups, int group_size, int T,
-                                                                          const float* __restrict__ scores,
-                                                                          float* __restrict__ row_sum, float* __restrict__ gstd,
-                                                                          float* __restrict__ gmax, float* __restrict__ gmean) {
-  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int g = blockIdx.x * ROWS_PER_CTA + w;
+// _filter_rollout's statistics (ragen/trainer/agent_trainer.py:466-469): row sums of the score tensor (grpo_scores_kernel
+// with no groups), then per group of `group_size` consecutive rows the unbiased std, the max and the mean.
+__global__ void group_stats_kernel(int n_groups, int group_size, const float* __restrict__ row_sum, float* __restrict__ gstd,
+                                   float* __restrict__ gmax, float* __restrict__ gmean) {
+  const int g = blockIdx.x * blockDim.x + threadIdx.x;
   if (g >= n_groups) return;
   double s1 = 0.0, s2 = 0.0;
   float mx = -INFINITY;
-  for (int r = 0; r < group_size; ++r) {  // the warp sums one row at a time (coalesced); every lane ends with the sum
-    const size_t base = ((size_t)g * group_size + r) * T;
-    double s = 0.0;
-#pragma unroll 4
-    for (int t = lane; t < T; t += 32) s += (double)__ldg(scores + base + t);
-    const float sf = (float)warp_sum(s);
-    if (lane == 0) row_sum[(size_t)g * group_size + r] = sf;
+  for (int r = 0; r < group_size; ++r) {
+    const float sf = row_sum[(size_t)g * group_size + r];
     s1 += (double)sf;
     s2 += (double)sf * (double)sf;
     mx = fmaxf(mx, sf);
   }
-  if (lane == 0) {
-    const double n = (double)group_size, mu = s1 / n;
-    gmean[g] = (float)mu;
-    gmax[g] = mx;
-    gstd[g] = group_size > 1 ? (float)sqrt(fmax((s2 - n * mu * mu) / (n - 1.0), 0.0)) : NAN;  // torch.std of one value is NaN
-  }
+  const double n = (double)group_size, mu = s1 / n;
+  gmean[g] = (float)mu;
+  gmax[g] = mx;
+  gstd[g] = group_size > 1 ? (float)sqrt(fmax((s2 - n * mu * mu) / (n - 1.0), 0.0)) : NAN;  // torch.std of one value is NaN
 }
-
-int grid_rows(int B) { return (B + ROWS_PER_CTA - 1) / ROWS_PER_CTA; }
 
 }  // namespace
 
@@ -463,7 +566,7 @@ extern "C" int ragen_gae(ragen_ctx* ctx, int B, int T, const float* rewards, con
   cudaStream_t st = (cudaStream_t)stream;
   if (moments) RAGEN_CUDA(cudaMemsetAsync(moments, 0, 3 * sizeof(double), st));
   if (B == 0) return RAGEN_OK;  // an empty shard still contributes zero moments to the all-reduce
-  gae_kernel<<<grid_rows(B), ROWS_PER_CTA * 32, 0, st>>>(B, T, rewards, values, mask, (float)gamma, (float)(gamma * lam), adv,
+  gae_kernel<<<B, RT, 0, st>>>(B, T, rewards, values, mask, (float)gamma, (float)(gamma * lam), adv,
                                                         ret, moments);
   RAGEN_LAUNCHED(ctx);
   return RAGEN_OK;
@@ -479,7 +582,7 @@ extern "C" int ragen_bilevel_gae(ragen_ctx* ctx, int B, int T, const float* rewa
   cudaStream_t st = (cudaStream_t)stream;
   if (moments) RAGEN_CUDA(cudaMemsetAsync(moments, 0, 3 * sizeof(double), st));
   if (B == 0) return RAGEN_OK;  // an empty shard still contributes zero moments to the all-reduce
-  bilevel_gae_kernel<<<grid_rows(B), ROWS_PER_CTA * 32, 0, st>>>(B, T, rewards, values, loss_mask, (float)gamma,
+  bilevel_gae_kernel<<<B, RT, 0, st>>>(B, T, rewards, values, loss_mask, (float)gamma,
                                                                 (float)(gamma * lam), (float)high_level_gamma,
                                                                 (float)(high_level_gamma * lam), adv, ret, moments);
   RAGEN_LAUNCHED(ctx);
@@ -528,10 +631,10 @@ extern "C" int ragen_grpo_outcome(ragen_ctx* ctx, int B, int T, const float* rew
   double* gstats = (double*)ragen_scratch(ctx, bytes);
   if (!gstats) return RAGEN_ENOMEM;
   RAGEN_CUDA(cudaMemsetAsync(gstats, 0, bytes, st));
-  grpo_scores_kernel<<<grid_rows(B), ROWS_PER_CTA * 32, 0, st>>>(B, T, rewards, group, n_groups, scores, gstats);
+  grpo_scores_kernel<<<B, RT, 0, st>>>(B, T, rewards, group, n_groups, scores, gstats);
   RAGEN_LAUNCHED(ctx);
-  grpo_apply_kernel<<<grid_rows(B), ROWS_PER_CTA * 32, 0, st>>>(B, T, scores, group, n_groups, gstats, mask, (float)epsilon,
-                                                               norm_by_std, adv);
+  outcome_apply_kernel<<<B, RT, 0, st>>>(B, T, scores, group, n_groups, gstats, mask, (float)epsilon, norm_by_std ? 1 : 0, adv,
+                                         nullptr);
   RAGEN_LAUNCHED(ctx);
   return RAGEN_OK;
 }
@@ -550,9 +653,9 @@ extern "C" int ragen_outcome_advantage(ragen_ctx* ctx, int B, int T, const float
   double* gstats = (double*)ragen_scratch(ctx, bytes);
   if (!gstats) return RAGEN_ENOMEM;
   RAGEN_CUDA(cudaMemsetAsync(gstats, 0, bytes, st));
-  grpo_scores_kernel<<<grid_rows(B), ROWS_PER_CTA * 32, 0, st>>>(B, T, rewards, group, n_groups, scores, gstats);
+  grpo_scores_kernel<<<B, RT, 0, st>>>(B, T, rewards, group, n_groups, scores, gstats);
   RAGEN_LAUNCHED(ctx);
-  outcome_apply_kernel<<<grid_rows(B), ROWS_PER_CTA * 32, 0, st>>>(B, T, scores, group, n_groups, gstats, mask, (float)epsilon,
+  outcome_apply_kernel<<<B, RT, 0, st>>>(B, T, scores, group, n_groups, gstats, mask, (float)epsilon,
                                                                   mode, adv, moments);
   RAGEN_LAUNCHED(ctx);
   return RAGEN_OK;
@@ -567,7 +670,7 @@ extern "C" int ragen_discounted_returns(ragen_ctx* ctx, int B, int T, const floa
   cudaStream_t st = (cudaStream_t)stream;
   RAGEN_CUDA(cudaMemsetAsync(moments, 0, 3 * sizeof(double), st));
   if (B == 0) return RAGEN_OK;
-  returns_kernel<0><<<grid_rows(B), ROWS_PER_CTA * 32, 0, st>>>(B, T, rewards, mask, (float)gamma, nullptr, nullptr, ret, moments);
+  returns_kernel<0><<<B, RT, 0, st>>>(B, T, rewards, mask, (float)gamma, nullptr, nullptr, ret, moments);
   RAGEN_LAUNCHED(ctx);
   return RAGEN_OK;
 }
@@ -579,7 +682,7 @@ extern "C" int ragen_remax(ragen_ctx* ctx, int B, int T, const float* rewards, c
   RAGEN_REQUIRE(rewards && mask && baselines && adv && ret, "NULL pointer argument");
   if (B == 0) return RAGEN_OK;
   DeviceGuard guard(ctx->device);
-  returns_kernel<1><<<grid_rows(B), ROWS_PER_CTA * 32, 0, (cudaStream_t)stream>>>(B, T, rewards, mask, 0.0f, baselines, adv, ret,
+  returns_kernel<1><<<B, RT, 0, (cudaStream_t)stream>>>(B, T, rewards, mask, 0.0f, baselines, adv, ret,
                                                                                  nullptr);
   RAGEN_LAUNCHED(ctx);
   return RAGEN_OK;
@@ -606,7 +709,7 @@ extern "C" int ragen_kl_rewards(ragen_ctx* ctx, int B, int T, const float* score
   RAGEN_REQUIRE(scores && logp && ref_logp && mask && rewards_out && mode >= 0 && mode <= 3, "bad argument");
   if (B == 0) return RAGEN_OK;
   DeviceGuard guard(ctx->device);
-  kl_rewards_kernel<<<grid_rows(B), ROWS_PER_CTA * 32, 0, (cudaStream_t)stream>>>(B, T, scores, logp, ref_logp, mask, mode,
+  kl_rewards_kernel<<<B, RT, 0, (cudaStream_t)stream>>>(B, T, scores, logp, ref_logp, mask, mode,
                                                                                  (float)beta, rewards_out, row_kl);
   RAGEN_LAUNCHED(ctx);
   return RAGEN_OK;
@@ -619,8 +722,10 @@ extern "C" int ragen_group_filter_stats(ragen_ctx* ctx, int n_groups, int group_
   RAGEN_REQUIRE(scores && row_sum && gstd && gmax && gmean, "NULL pointer argument");
   if (n_groups == 0) return RAGEN_OK;
   DeviceGuard guard(ctx->device);
-  filter_stats_kernel<<<grid_rows(n_groups), ROWS_PER_CTA * 32, 0, (cudaStream_t)stream>>>(n_groups, group_size, T, scores,
-                                                                                          row_sum, gstd, gmax, gmean);
+  cudaStream_t st = (cudaStream_t)stream;
+  grpo_scores_kernel<<<n_groups * group_size, RT, 0, st>>>(n_groups * group_size, T, scores, nullptr, 0, row_sum, nullptr);
+  RAGEN_LAUNCHED(ctx);
+  group_stats_kernel<<<(n_groups + 127) / 128, 128, 0, st>>>(n_groups, group_size, row_sum, gstd, gmax, gmean);
   RAGEN_LAUNCHED(ctx);
   return RAGEN_OK;
 }

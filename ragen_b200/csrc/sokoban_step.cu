@@ -117,14 +117,14 @@ __device__ __forceinline__ void render_tile(const uint8_t* s_state, uint8_t* s_o
         ++r0;
       }
     }
-    return;
-  }
-  for (int j = threadIdx.x; j < words; j += TE) {
-    if (PACKED) {
-      const uint32_t lo = pack_nibbles(glyph_word(sw, j << 3, W)), hi = pack_nibbles(glyph_word(sw, (j << 3) + 4, W));
-      ow[j] = lo | (hi << 16);
-    } else {
-      ow[j] = glyph_word(sw, j << 2, W);
+  } else {
+    for (int j = threadIdx.x; j < words; j += TE) {
+      if (PACKED) {
+        const uint32_t lo = pack_nibbles(glyph_word(sw, j << 3, W)), hi = pack_nibbles(glyph_word(sw, (j << 3) + 4, W));
+        ow[j] = lo | (hi << 16);
+      } else {
+        ow[j] = glyph_word(sw, j << 2, W);
+      }
     }
   }
 }

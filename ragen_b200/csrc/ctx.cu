@@ -11,7 +11,8 @@
 
 namespace {
 
-constexpr int WARPS = 4;
+constexpr int MT = 256;      // threads of the CTA that owns one row
+constexpr int SLABS = 8;     // 256-token slabs handled per pass: 2048 tokens of the row in registers
 constexpr int MAX_TURNS = 64;
 
 struct MsParams {
@@ -27,38 +28,70 @@ struct MsParams {
   float* score;
 };
 
-__global__ void __launch_bounds__(WARPS * 32) masks_scores_kernel(const MsParams p) {
-  __shared__ int s_pos[WARPS][MAX_TURNS];
-  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int row = blockIdx.x * WARPS + w;
-  if (row >= p.B) return;
+// One CTA per row.  A pass covers 2048 tokens: every thread loads its 8 ids at once (the loads are what bounds this pass at
+// C5: 128 rows), each warp ballots its <|im_start|> flags per slab, the 64 per-(slab, warp) counts are prefix-summed through
+// shared memory, and the turn indicator cumsum(ids == <|im_start|>) of a token is its segment's base plus a popcount.
+__global__ void __launch_bounds__(MT) masks_scores_kernel(const MsParams p) {
+  __shared__ int s_pos[MAX_TURNS];
+  __shared__ int s_cnt[SLABS * (MT / 32) + 1];
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const int row = blockIdx.x;
   const int L = p.L, Lo = L - 1;
   const int64_t* ids = p.ids + (size_t)row * L;
   uint8_t* lm = p.loss_mask + (size_t)row * Lo;
   uint8_t* rm = p.resp_mask + (size_t)row * Lo;
   float* sc = p.score + (size_t)row * Lo;
-  for (int k = lane; k < p.max_turns; k += 32) s_pos[w][k] = 0x7fffffff;
-  __syncwarp();
-  int turn_base = 0;
-  for (int t0 = 0; t0 < L; t0 += 32) {
-    const int t = t0 + lane;
-    const int64_t id = (t < L) ? ids[t] : -1;
-    const unsigned starts = __ballot_sync(0xffffffffu, t < L && id == p.im_start);
-    const int turn = turn_base + __popc(starts & (0xffffffffu >> (31 - lane)));  // inclusive cumsum (:43-44)
-    turn_base += __popc(starts);
-    if (t < Lo) {
-      const bool resp = (turn & 1) && turn > 1;
-      rm[t] = resp ? 1 : 0;
-      lm[t] = p.enable_response_mask ? (resp ? 1 : 0) : (turn > 1 ? 1 : 0);
-      sc[t] = 0.0f;
+  for (int k = tid; k < p.max_turns; k += MT) s_pos[k] = 0x7fffffff;
+  int turn_base = 0;  // im_start tokens left of the current pass
+  for (int p0 = 0; p0 < L; p0 += SLABS * MT) {
+    int64_t id[SLABS];
+    unsigned starts[SLABS];
+#pragma unroll
+    for (int j = 0; j < SLABS; ++j) {
+      const int t = p0 + j * MT + tid;
+      id[j] = (t < L) ? ids[t] : -1;
     }
-    if (p.use_turn_scores && t < L && id == p.im_end && (turn & 1) && turn >= 3) {
-      const int k = (turn - 3) >> 1;  // reward of turn k sits on the <|im_end|> of indicator 2k+3 (:55-56)
-      if (k < p.max_turns) atomicMin(&s_pos[w][k], t);
+#pragma unroll
+    for (int j = 0; j < SLABS; ++j) {
+      const int t = p0 + j * MT + tid;
+      starts[j] = __ballot_sync(0xffffffffu, t < L && id[j] == p.im_start);
+      if (lane == 0) s_cnt[j * (MT / 32) + wid] = __popc(starts[j]);
     }
+    __syncthreads();
+    if (tid < 32) {  // exclusive prefix of the 64 segment counts (segments are in token order: slab-major, then warp)
+      const int a = s_cnt[2 * lane], b = s_cnt[2 * lane + 1];
+      int incl = a + b;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int up = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += up;
+      }
+      const int excl = incl - (a + b);
+      __syncwarp();
+      s_cnt[2 * lane] = excl;
+      s_cnt[2 * lane + 1] = excl + a;
+      if (lane == 31) s_cnt[SLABS * (MT / 32)] = incl;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < SLABS; ++j) {
+      const int t = p0 + j * MT + tid;
+      const int turn = turn_base + s_cnt[j * (MT / 32) + wid] + __popc(starts[j] & (0xffffffffu >> (31 - lane)));  // inclusive (:43-44)
+      if (t < Lo) {
+        const bool resp = (turn & 1) && turn > 1;
+        rm[t] = resp ? 1 : 0;
+        lm[t] = p.enable_response_mask ? (resp ? 1 : 0) : (turn > 1 ? 1 : 0);
+        sc[t] = 0.0f;
+      }
+      if (p.use_turn_scores && t < L && id[j] == p.im_end && (turn & 1) && turn >= 3) {
+        const int k = (turn - 3) >> 1;  // reward of turn k sits on the <|im_end|> of indicator 2k+3 (:55-56)
+        if (k < p.max_turns) atomicMin(&s_pos[k], t);
+      }
+    }
+    turn_base += s_cnt[SLABS * (MT / 32)];
+    __syncthreads();
   }
-  __syncwarp();
-  if (lane != 0) return;
+  if (tid != 0) return;
   const int nt = p.n_turns[row];
   const double* ts = p.turn_scores + (size_t)row * p.max_turns;
   if (!p.use_turn_scores) {
@@ -71,7 +104,7 @@ __global__ void __launch_bounds__(WARPS * 32) masks_scores_kernel(const MsParams
   // zip_longest pads short rows with 0 (:53).  Then the Qwen roll by one (:60-62) and the dropped first column.
   for (int k = 0; k < p.max_turns; ++k) {
     const float v = (k < nt) ? (float)ts[k] : 0.0f;
-    const int pos = (s_pos[w][k] == 0x7fffffff) ? L - 1 : s_pos[w][k];
+    const int pos = (s_pos[k] == 0x7fffffff) ? L - 1 : s_pos[k];
     const int out = p.roll ? pos : pos - 1;  // rolled: full[t] lands in output column t; else column t-1
     if (out >= 0 && out < Lo) sc[out] = v;
   }
@@ -132,7 +165,7 @@ extern "C" int ragen_masks_scores(ragen_ctx* ctx, int B, int L, const int64_t* i
   DeviceGuard guard(ctx->device);
   MsParams p{B, L, input_ids, im_start_id, im_end_id, use_turn_scores, enable_response_mask, roll_scores, turn_scores,
              n_turns, max_turns, loss_mask, response_mask, score};
-  masks_scores_kernel<<<(B + WARPS - 1) / WARPS, WARPS * 32, 0, (cudaStream_t)stream>>>(p);
+  masks_scores_kernel<<<B, MT, 0, (cudaStream_t)stream>>>(p);
   RAGEN_LAUNCHED(ctx);
   return RAGEN_OK;
 }

@@ -261,6 +261,15 @@ int ragen_kl_rewards(ragen_ctx* ctx, int B, int T, const float* scores, const fl
 int ragen_group_filter_stats(ragen_ctx* ctx, int n_groups, int group_size, int T, const float* scores, float* row_sum,
                              float* gstd, float* gmax, float* gmean, void* stream);
 
+/* Answer scoring of the text environments: n (prediction, label) pairs as two UTF-8 blobs with
+ * int64 offsets [n+1].  mode 0: MetaMathQAEnv._check_answer (ragen/env/metamathqa/env.py:55-66); 1, 2, 3:
+ * compute_score_exact_match / compute_score_numeric / compute_score_multiple_choice (ragen/env/static/utils.py:69-132).
+ * result[i]: bit0 is_correct, bit1 is_valid, bit2 normalised texts equal, bit7 "unsupported": a non-ASCII byte (Python
+ * folds case by Unicode tables) or a number of more than 15 significant digits was seen - the other bits are then the
+ * ASCII / decimal-string answer. */
+int ragen_text_score(ragen_ctx* ctx, int64_t n, int mode, const uint8_t* pred, const int64_t* pred_offsets,
+                     const uint8_t* label, const int64_t* label_offsets, uint8_t* result, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

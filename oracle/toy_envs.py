@@ -192,3 +192,44 @@ def countdown_reward(answer: str, nums, target, score=1, format_score=0.1):
     except Exception:
         ok = False
     return score if ok else format_score
+
+
+# ---------------------------------------------------------------------------------------------
+# text-env answer scoring
+# ---------------------------------------------------------------------------------------------
+import string as _string
+
+
+def normalize_text(text):
+    """ragen/env/static/utils.py:7-12."""
+    text = re.sub(r"\s+", "", text.lower())
+    return text.translate(str.maketrans("", "", _string.punctuation))
+
+
+def score_metamath(user_answer, correct_answer):
+    """MetaMathQAEnv._check_answer (ragen/env/metamathqa/env.py:55-66) -> (is_correct, is_valid)."""
+    norm = re.sub(r"\s+", "", user_answer.strip().lower())
+    ok = bool(correct_answer) and norm == re.sub(r"\s+", "", correct_answer.lower())
+    return ok, norm != ""
+
+
+def score_exact(pred, label):
+    """compute_score_exact_match (static/utils.py:69-82)."""
+    return normalize_text(pred) == normalize_text(label), len(normalize_text(pred)) > 0
+
+
+def score_numeric(pred, label):
+    """compute_score_numeric (static/utils.py:84-111)."""
+    pm, lm = re.search(r"(\d+(?:\.\d+)?)", pred), re.search(r"(\d+(?:\.\d+)?)", label)
+    ok = bool(pm and lm and float(pm.group(0)) == float(lm.group(0)))
+    return ok or normalize_text(pred) == normalize_text(label), pm is not None
+
+
+def score_choice(pred, label):
+    """compute_score_multiple_choice (static/utils.py:113-132)."""
+    pm, lm = re.search(r"([A-D])", pred.upper()), re.search(r"([A-D])", label.upper())
+    ok = pm.group(0) == lm.group(0) if (pm and lm) else normalize_text(pred) == normalize_text(label)
+    return ok, pm is not None
+
+
+SCORERS = {"metamathqa": score_metamath, "exact_match": score_exact, "numeric": score_numeric, "multiple_choice": score_choice}

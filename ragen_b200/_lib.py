@@ -48,6 +48,7 @@ SIGNATURES = {
     "ragen_remax": [_P, _I, _I, _P, _P, _P, _P, _P, _P],
     "ragen_whiten_masked": [_P, _L, _P, _P, _P, _P, _P],
     "ragen_kl_rewards": [_P, _I, _I, _P, _P, _P, _P, _I, _D, _P, _P, _P],
+    "ragen_text_score": [_P, _L, _I, _P, _P, _P, _P, _P, _P],
     "ragen_group_filter_stats": [_P, _I, _I, _I, _P, _P, _P, _P, _P, _P],
 }
 _RESTYPE = {"ragen_last_error": _c.c_char_p, "ragen_launch_count": _c.c_uint64}

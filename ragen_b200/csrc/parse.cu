@@ -13,6 +13,7 @@
 // the same size.  Byte-scan work: HBM-bound (each response byte is read once), no tensor cores.
 #include "common.cuh"
 #include "parse_logic.cuh"
+#include "score_logic.cuh"
 
 namespace {
 
@@ -247,6 +248,16 @@ __global__ void countdown_kernel(int64_t n, const uint8_t* __restrict__ text, co
   if (unsupported) unsupported[i] = unsup ? 1 : 0;
 }
 
+// Answer scoring of the text envs (score_logic.cuh): one thread per (prediction, label) pair.  The strings are a few dozen
+// bytes, the batch a few thousand pairs: latency-bound, nothing to tile.
+__global__ void text_score_kernel(int64_t n, int mode, const uint8_t* __restrict__ pred, const int64_t* __restrict__ pred_off,
+                                  const uint8_t* __restrict__ label, const int64_t* __restrict__ label_off, uint8_t* out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int64_t a = pred_off[i], b = label_off[i];
+  out[i] = (uint8_t)score::score_pair(mode, pred + a, (int)(pred_off[i + 1] - a), label + b, (int)(label_off[i + 1] - b));
+}
+
 }  // namespace
 
 extern "C" int ragen_parse_actions(ragen_ctx* ctx, int64_t n, const uint8_t* text, const int64_t* offsets, int enable_think,
@@ -304,6 +315,19 @@ extern "C" int ragen_countdown_score(ragen_ctx* ctx, int64_t n, const uint8_t* t
   DeviceGuard guard(ctx->device);
   countdown_kernel<<<(unsigned)((n + 127) / 128), 128, 0, (cudaStream_t)stream>>>(n, text, start, len, nums, n_nums, target,
                                                                                  result, unsupported);
+  RAGEN_LAUNCHED(ctx);
+  return RAGEN_OK;
+}
+
+extern "C" int ragen_text_score(ragen_ctx* ctx, int64_t n, int mode, const uint8_t* pred, const int64_t* pred_offsets,
+                                const uint8_t* label, const int64_t* label_offsets, uint8_t* result, void* stream) {
+  RAGEN_REQUIRE(ctx, "ctx is NULL");
+  RAGEN_REQUIRE(n >= 0 && mode >= 0 && mode <= 3, "bad argument n=%lld mode=%d", (long long)n, mode);
+  RAGEN_REQUIRE(n == 0 || (pred && pred_offsets && label && label_offsets && result), "NULL pointer argument");
+  if (n == 0) return RAGEN_OK;
+  DeviceGuard guard(ctx->device);
+  text_score_kernel<<<(unsigned)((n + 127) / 128), 128, 0, (cudaStream_t)stream>>>(n, mode, pred, pred_offsets, label, label_offsets,
+                                                                                  result);
   RAGEN_LAUNCHED(ctx);
   return RAGEN_OK;
 }

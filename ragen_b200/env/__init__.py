@@ -5,12 +5,14 @@ from .bandit import BanditBatch, BanditEnv, BanditEnvConfig
 from .countdown import CountdownBatch, CountdownEnv, CountdownEnvConfig
 from .frozen_lake import FrozenLakeBatch, FrozenLakeEnv, FrozenLakeEnvConfig
 from .sokoban import SokobanBatch, SokobanEnv, SokobanEnvConfig
+from .text_qa import MetaMathQAEnv, MetaMathQAEnvConfig, StaticEnv, StaticEnvConfig, TextScoreBatch
 
 REGISTERED_ENVS = {
     "bandit": BanditEnv,
     "countdown": CountdownEnv,
     "sokoban": SokobanEnv,
     "frozen_lake": FrozenLakeEnv,
+    "metamathqa": MetaMathQAEnv,
 }
 
 REGISTERED_ENV_CONFIGS = {
@@ -18,6 +20,7 @@ REGISTERED_ENV_CONFIGS = {
     "countdown": CountdownEnvConfig,
     "sokoban": SokobanEnvConfig,
     "frozen_lake": FrozenLakeEnvConfig,
+    "metamathqa": MetaMathQAEnvConfig,
 }
 
 BATCH_TYPES = {
@@ -25,4 +28,5 @@ BATCH_TYPES = {
     "countdown": CountdownBatch,
     "sokoban": SokobanBatch,
     "frozen_lake": FrozenLakeBatch,
+    "metamathqa": TextScoreBatch,
 }

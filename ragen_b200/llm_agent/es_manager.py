@@ -244,6 +244,23 @@ class EnvStateManager:
                     results[i] = (0 + r, info, done, 1)
                 else:
                     results[i] = (0, {}, False, 0)
+        elif block.env_type == "metamathqa":
+            # free-text answers; a wrong answer does not end the episode, so action r of every env still going is scored in
+            # round r - one launch per round instead of one regex pass per (env, action)
+            state = {i: [0, {}, False, 0] for i in idxs}  # acc_reward, info, done, executed
+            for r in range(max((len(p[3]) for p in plans), default=0)):
+                live = [(i, p) for i, p in zip(idxs, plans) if len(p[3]) > r and not state[i][2]]
+                if not live:
+                    break
+                bits = b.score([p[3][r] for _, p in live], [p[1]["env"].correct_answer or "" for _, p in live], "metamathqa")
+                for (i, p), bt in zip(live, bits):
+                    _, reward, done, info = p[1]["env"].finish_step(bool(bt & 1), bool(bt & 2))
+                    st = state[i]
+                    st[0] += reward
+                    st[1].update(info)
+                    st[2], st[3] = done, st[3] + 1
+            for i in idxs:
+                results[i] = tuple(state[i])
         else:  # countdown: actions are free text, the first one ends the episode
             todo_plans = [(i, p) for i, p in zip(idxs, plans) if p[3]]
             if todo_plans:

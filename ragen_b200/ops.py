@@ -324,3 +324,21 @@ def countdown_score_parsed(res, rows, nums, n_nums, target):
         out2, uns2 = countdown_score(res.scratch, start, length, nums, n_nums, target)
         out, uns = torch.where(in_scratch, out2, out), torch.where(in_scratch, uns2, uns)
     return out, uns
+
+
+_SCORE_MODES = {"metamathqa": 0, "exact_match": 1, "numeric": 2, "multiple_choice": 3}
+
+
+def text_score(predictions, labels, mode, device=0):
+    """Scores n (prediction, label) string pairs on the device.  mode: "metamathqa" (MetaMathQAEnv._check_answer),
+    "exact_match", "numeric", "multiple_choice" (ragen/env/static/utils.py).  Returns uint8 CUDA tensor [n]:
+    bit0 is_correct, bit1 is_valid, bit2 text_match, bit7 unsupported (see include/ragen_b200.h)."""
+    dev = torch.device("cuda", int(device)) if not isinstance(device, torch.device) else device
+    ctx = _lib.Context.get(dev.index or 0)
+    assert len(predictions) == len(labels)
+    _, _, p_text, p_off = stage_responses(list(predictions), dev)
+    _, _, l_text, l_off = stage_responses(list(labels), dev)
+    out = torch.empty(len(predictions), dtype=torch.uint8, device=dev)
+    _lib.check(ctx.lib.ragen_text_score(ctx.handle, len(predictions), _SCORE_MODES[mode], _lib.ptr(p_text), _lib.ptr(p_off),
+                                        _lib.ptr(l_text), _lib.ptr(l_off), _lib.ptr(out), ctx.stream()))
+    return out

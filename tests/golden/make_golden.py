@@ -528,6 +528,73 @@ def advantage_more():
     print("advantage_more ok")
 
 
+SCORE_PAIRS = [
+    ("42", "42"), (" 42 \n", "42"), ("The Answer", "the answer"), ("the answer.", "The Answer"), ("x = 3", "x=3"), ("", "7"), ("7", ""),
+    ("   ", "7"), ("3.50", "3.5"), ("003.5", "3.5"), ("about 12 apples", "12"), ("12.0", "12"), ("12.", "12"), ("1,234", "1234"),
+    ("no digits", "5"), ("5", "no digits"), ("B", "b"), ("(B) because", "B"), ("the answer is c", "C"), ("E", "A"), ("none", "A"),
+    ("none", "none"), ("A or B", "B"), ("\frac{1}{2}", "\\frac{1}{2}"), ("1/2", "0.5"), ("0.5", ".5"), ("-3", "3"), ("3e2", "300"),
+    ("10%", "10"), ("Hello, World!", "hello world"), ("tab\there", "tabthere"), ("a\x1cb", "ab"), ("ABCD", "abcd"), ("d", "D."),
+    ("123456789012345", "123456789012345.0"), ("x", "X "), ("12 13", "12"), ("13 12", "12"), ("_a_", "a"), ("a-b", "ab"),
+]
+
+
+def text_scores():
+    """The UNMODIFIED scorers: MetaMathQAEnv._check_answer (metamathqa/env.py:55-66) and the three compute_score_* functions of
+    ragen/env/static/utils.py, on ASCII pairs."""
+    su = R.module("ragen.env.static.utils")
+    mm = R.module("ragen.env.metamathqa.env")
+    rows = []
+    for pred, label in SCORE_PAIRS:
+        obj = type("X", (), {"correct_answer": label})()
+        c, v = mm.MetaMathQAEnv._check_answer(obj, pred)
+        row = {"pred": pred, "label": label, "metamathqa": [bool(c), bool(v)]}
+        for name, fn in (("exact_match", su.compute_score_exact_match), ("numeric", su.compute_score_numeric),
+                         ("multiple_choice", su.compute_score_multiple_choice)):
+            r = fn(pred, label)
+            row[name] = [bool(r["is_correct"]), bool(r["is_valid"])]
+        rows.append(row)
+    with open(os.path.join(OUT, "text_scores.json"), "w") as fh:
+        json.dump(rows, fh, indent=0)
+    print("text_scores ok:", len(rows))
+
+
+QA_ROWS = [{"query": "What is 6 times 7?", "response": "6 * 7 = 42.\nThe answer is: 42"},
+           {"query": "Simplify 1/2 + 1/4.", "response": "Common denominator 4.\nThe answer is: \\frac{3}{4}"},
+           {"query": "Name the shape with three sides.", "response": "Three sides.\nThe answer is: Triangle "},
+           {"query": "A question whose solution has no marker.", "response": "It is 5."},
+           {"query": "What is 10 / 4?", "response": "10/4 = 2.5\nThe answer is: 2.5"}]
+QA_ANSWERS = ["42", " 42 ", "forty two", "\\frac{3}{4}", "\\FRAC{3}{4}", "3/4", "triangle", "TRI ANGLE", "", "   ", "5", "2.5", "2.50"]
+
+
+def metamath_episodes():
+    """MetaMathQAEnv.reset / step of the UNMODIFIED reference (ragen/env/metamathqa/env.py:29-53) on an in-memory dataset
+    (the constructor's load_dataset download is bypassed with __new__)."""
+    import contextlib
+    import io
+    mm = R.module("ragen.env.metamathqa.env")
+    rng = np.random.default_rng(12)
+    out = []
+    for seed in range(8):
+        env = mm.MetaMathQAEnv.__new__(mm.MetaMathQAEnv)
+        env.config = mm.MetaMathQAEnvConfig(split="train")
+        env.dataset = {"train": QA_ROWS}
+        with contextlib.redirect_stdout(io.StringIO()):  # _extract_answer prints the solution
+            q = env.reset(seed=seed)
+        answers = [QA_ANSWERS[int(i)] for i in rng.integers(0, len(QA_ANSWERS), 4)]
+        if seed % 2 == 0 and env.correct_answer:
+            answers[2] = env.correct_answer.upper()
+        steps = []
+        for a in answers:
+            obs, reward, done, info = env.step(a)
+            steps.append({"answer": a, "obs": obs, "reward": reward, "done": bool(done), "info": {k: bool(v) for k, v in info.items()}})
+            if done:
+                break
+        out.append({"seed": seed, "question": q, "idx": env.current_question_idx, "label": env.correct_answer, "steps": steps})
+    with open(os.path.join(OUT, "metamath_episodes.json"), "w") as fh:
+        json.dump({"rows": QA_ROWS, "episodes": out}, fh, indent=0)
+    print("metamath_episodes ok:", [(e["idx"], len(e["steps"])) for e in out])
+
+
 def countdown():
     cd = R.countdown_env()
     cases = [("1+2+3", [1, 2, 3], 6), ("1+2", [1, 2, 3], 3), ("3*(2-1)", [1, 2, 3], 3), ("1 + 2 = 3", [1, 2, 3], 3),
@@ -559,4 +626,6 @@ if __name__ == "__main__":
     lm_inputs()
     rollouts()
     advantage_more()
+    text_scores()
+    metamath_episodes()
     countdown()

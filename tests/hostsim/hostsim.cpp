@@ -6,6 +6,7 @@
 
 #include "../../ragen_b200/csrc/np_random.cuh"
 #include "../../ragen_b200/csrc/parse_logic.cuh"
+#include "../../ragen_b200/csrc/score_logic.cuh"
 #include "../../ragen_b200/csrc/sokoban_gen_logic.cuh"
 #include <stdlib.h>
 #include "../../ragen_b200/csrc/toy_logic.cuh"
@@ -186,5 +187,8 @@ int hs_sokoban_generate(int H, int W, int nb, int search_depth, int num_gen_step
   free(w.vis.mem64);
   return st;
 }
+
+// ---- text scoring -----------------------------------------------------------------------------------------------
+int hs_text_score(int mode, const uint8_t* pred, int np, const uint8_t* label, int nl) { return score::score_pair(mode, pred, np, label, nl); }
 
 }  // extern "C"

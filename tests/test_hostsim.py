@@ -21,7 +21,7 @@ c = ctypes
 @pytest.fixture(scope="session")
 def hs():
     src = os.path.join(HS_DIR, "hostsim.cpp")
-    deps = [src] + [os.path.join(ROOT, "ragen_b200", "csrc", f) for f in ("np_random.cuh", "parse_logic.cuh", "toy_logic.cuh", "mt19937.cuh", "sokoban_gen_logic.cuh")]
+    deps = [src] + [os.path.join(ROOT, "ragen_b200", "csrc", f) for f in ("np_random.cuh", "parse_logic.cuh", "score_logic.cuh", "toy_logic.cuh", "mt19937.cuh", "sokoban_gen_logic.cuh")]
     if not os.path.exists(HS_SO) or any(os.path.getmtime(d) > os.path.getmtime(HS_SO) for d in deps):
         subprocess.run(["g++", "-std=c++17", "-O2", "-shared", "-fPIC", "-o", HS_SO, src], check=True)
     lib = c.CDLL(HS_SO)
@@ -35,6 +35,8 @@ def hs():
     lib.hs_bandit.argtypes = [c.c_uint64, c.c_int, c.c_double, c.c_void_p]
     lib.hs_parse.argtypes = [c.c_char_p, c.c_int, c.c_int, c.c_char_p, c.c_int, c.c_void_p, c.c_void_p, c.c_void_p, c.c_int,
                              c.c_int, c.c_void_p, c.c_void_p]
+    lib.hs_text_score.restype = c.c_int
+    lib.hs_text_score.argtypes = [c.c_int, c.c_char_p, c.c_int, c.c_char_p, c.c_int]
     lib.hs_mt.argtypes = [c.c_uint64, c.c_uint32, c.c_int, c.c_void_p, c.c_void_p, c.c_void_p]
     lib.hs_sokoban_generate.argtypes = [c.c_int] * 5 + [c.c_uint64, c.c_int, c.c_void_p, c.c_void_p, c.c_void_p]
     return lib
@@ -303,3 +305,46 @@ def test_sokoban_generator_reproduces_reference_rooms(hs, name):
         assert st == 0, (name, seed, st)
         assert np.array_equal(fixed, rooms[f"{name}_fixed"][j]), (name, seed)
         assert np.array_equal(state, rooms[f"{name}_state"][j]), (name, seed)
+
+
+# ---- text-env answer scoring (score_logic.cuh) ---------------------------------------------------------------------------
+SCORE_MODES = {"metamathqa": 0, "exact_match": 1, "numeric": 2, "multiple_choice": 3}
+
+
+def hs_score(hs, mode, pred, label):
+    a, b = pred.encode(), label.encode()
+    r = hs.hs_text_score(SCORE_MODES[mode], a, len(a), b, len(b))
+    return bool(r & 1), bool(r & 2), bool(r & 128)
+
+
+def test_text_scores_match_reference_golden(hs):
+    for row in golden_json("text_scores.json"):
+        for mode in SCORE_MODES:
+            ok, valid, unsup = hs_score(hs, mode, row["pred"], row["label"])
+            assert [ok, valid] == row[mode], (mode, row["pred"], row["label"])
+            assert not unsup
+            assert list(TE.SCORERS[mode](row["pred"], row["label"])) == row[mode]  # the oracle restatement, same pin
+
+
+def test_text_scores_fuzz_against_oracle(hs):
+    """Random ASCII strings over an alphabet rich in the characters the scorers care about."""
+    rng = np.random.default_rng(8)
+    alphabet = list("abcdABCD xyzXYZ  0123456789..,;:-_()\t\n") + ["\x1c", "\x0b"]
+    n_unsup = 0
+    for _ in range(3000):
+        p = "".join(rng.choice(alphabet, int(rng.integers(0, 14))))
+        l = p if rng.random() < 0.25 else "".join(rng.choice(alphabet, int(rng.integers(0, 10))))
+        if rng.random() < 0.2:
+            l = p.upper().replace(" ", "  ")
+        for mode in SCORE_MODES:
+            ok, valid, unsup = hs_score(hs, mode, p, l)
+            n_unsup += unsup
+            if not unsup:
+                assert (ok, valid) == tuple(TE.SCORERS[mode](p, l)), (mode, p, l)
+    assert n_unsup < 50  # only numbers of more than 15 significant digits, which 14 characters cannot hold... none expected
+
+
+def test_text_scores_flag_what_they_cannot_decide(hs):
+    assert hs_score(hs, "exact_match", "\u00c9cole", "\u00e9cole")[2]            # Unicode case folding
+    assert hs_score(hs, "numeric", "0.1000000000000000000001", "0.1")[2]          # > 15 significant digits
+    assert not hs_score(hs, "numeric", "0.100", "0.1")[2]

@@ -75,8 +75,12 @@ def sokoban_rows(quick):
     from ragen_b200.env.sokoban import SokobanBatch
 
     rows = []
-    for (H, W, nb, n, K, tag) in [(10, 10, 2, 1 << 20, 1, "C4 step 10x10 K=1"), (10, 10, 2, 1 << 20, 5, "C4 turn-fused 10x10 K=5"),
-                                  (6, 6, 1, 1 << 20, 1, "6x6 K=1 at 1Mi envs"), (6, 6, 1, 128, 5, "C1 shape 6x6 128 envs K=5")]:
+    for (H, W, nb, n, K, packed, tag) in [(10, 10, 2, 1 << 20, 1, True, "C4 step 10x10 K=1, packed glyph rows"),
+                                          (10, 10, 2, 1 << 20, 1, False, "C4 step 10x10 K=1, byte glyph rows"),
+                                          (10, 10, 2, 1 << 20, 5, True, "C4 turn-fused 10x10 K=5, packed glyph rows"),
+                                          (6, 6, 1, 1 << 20, 1, True, "6x6 K=1 at 1Mi envs, packed glyph rows"),
+                                          (6, 6, 1, 1 << 20, 1, False, "6x6 K=1 at 1Mi envs, byte glyph rows"),
+                                          (6, 6, 1, 128, 5, True, "C1 shape 6x6 128 envs K=5")]:
         if quick and n > 1 << 18:
             n = 1 << 18
         fixed, state = synth.synthetic_rooms(n, H, W, nb, seed=4)
@@ -87,7 +91,7 @@ def sokoban_rows(quick):
         i = [0]
 
         def step():
-            b.step(acts[i[0] % 4])
+            b.step(acts[i[0] % 4], packed=packed)
             i[0] += 1
         ms = dev_time(step, reps=50 if n > 1000 else 200)
         per_step = 3 * H * W + 1 + 10 + 8 + 1 + 1 + H * (W + 1)
@@ -107,7 +111,8 @@ def sokoban_rows(quick):
                     e.step(int(a))
         cs = cpu_time(cpu, 3.0)
         rows.append(line(tag, "env-step", n * K, ms, per_turn / K, m * K / cs, f"{m} envs x {K} actions, oracle/sokoban.py, 1 core",
-                         envs=n, K=K, kernel="sokoban_tile_kernel"))
+                         envs=n, K=K, kernel="sokoban_tile_kernel", glyph_rows="packed" if packed else "bytes",
+                         bytes_moved_per_unit=(2 * H * W + 16 + 11 + (H * (W + 1) // 2 if packed else H * (W + 1))) / K + 1))
         del b
     return rows
 

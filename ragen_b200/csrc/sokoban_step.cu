@@ -88,10 +88,11 @@ __device__ __forceinline__ void render_tile(const uint8_t* s_state, uint8_t* s_o
   const uint32_t* sw = reinterpret_cast<const uint32_t*>(s_state);
   uint32_t* ow = reinterpret_cast<uint32_t*>(s_obs);
   const int words = (obs_bytes + 3) >> 2;
-  if (PACKED && W >= 7) {
-    // 8 codes per output word; a row is W + 1 > 8 codes, so a word holds at most one separator: pack the 8 CELLS that
-    // follow the word's first cell to nibbles, then splice the separator nibble in.  (row, column) of the word's first
-    // code advance by a constant per iteration, so the division happens once per thread.
+  if (PACKED && W >= 3) {
+    // 8 codes per output word; a row is W + 1 >= 4 codes, so a word holds at most two separators: pack the 8 CELLS that
+    // follow the word's first cell to nibbles, then splice the separator nibble(s) in (cells pushed past the word belong
+    // to the next one).  (row, column) of the word's first code advance by a constant per iteration, so the division
+    // happens once per thread.
     const int RW = W + 1;
     int Q0 = threadIdx.x << 3;
     int r0 = Q0 / RW, c0 = Q0 - r0 * RW;
@@ -101,12 +102,11 @@ __device__ __forceinline__ void render_tile(const uint8_t* s_state, uint8_t* s_o
       const int a = s0 >> 2, sh = (s0 & 3) << 3;
       const uint32_t w0 = sw[a], w1 = sw[a + 1], w2 = sw[a + 2];
       const uint32_t nib = pack_nibbles(__funnelshift_r(w0, w1, sh)) | (pack_nibbles(__funnelshift_r(w1, w2, sh)) << 16);
-      const int p = W - c0;  // code of this word that is the separator (if < 8)
       uint32_t out = nib;
-      if (p < 8) {
-        const uint32_t low = (1u << (p << 2)) - 1u;
-        const uint32_t high = (p == 7) ? 0u : ~((1u << ((p + 1) << 2)) - 1u);
-        out = (nib & low) | (7u << (p << 2)) | ((nib << 4) & high);
+      for (int q = W - c0; q < 8; q += RW) {  // code(s) of this word that are separators
+        const uint32_t low = (1u << (q << 2)) - 1u;
+        const uint32_t high = (q == 7) ? 0u : ~((1u << ((q + 1) << 2)) - 1u);
+        out = (out & low) | (7u << (q << 2)) | ((out << 4) & high);
       }
       ow[j] = out;
       Q0 += TE * 8;

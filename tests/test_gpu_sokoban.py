@@ -205,7 +205,7 @@ def test_generated_rooms_are_valid_and_solvable():
         assert np.array_equal(f[j], want_f) and np.array_equal(s[j], want_s)
 
 
-@pytest.mark.parametrize("H,W,nb,n", [(6, 6, 1, 1000), (10, 10, 2, 4099), (8, 8, 2, 515), (5, 5, 1, 130), (10, 10, 2, 1)])
+@pytest.mark.parametrize("H,W,nb,n", [(6, 6, 1, 1000), (10, 10, 2, 4099), (8, 8, 2, 515), (5, 5, 1, 130), (10, 10, 2, 1), (6, 4, 1, 300), (6, 3, 1, 9)])
 def test_packed_glyph_rows_equal_the_byte_rows(H, W, nb, n):
     """ragen_sokoban_step_packed / ragen_sokoban_render_packed: the same step, glyph rows as two 4-bit codes per byte.
     Unpacked they equal the oracle's rows; translated with the pair table they are the reference's text."""

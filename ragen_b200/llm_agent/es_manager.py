@@ -282,8 +282,11 @@ class EnvStateManager:
             return actions
         if codes is not None:
             return list(codes)
-        rev = {v.lower(): k for k, v in action_lookup.items()}
-        return [rev[a.lower()] for a in actions if a.lower() in rev]
+        cached = entry.get("_rev")
+        if cached is None or cached[0] is not action_lookup:  # Bandit installs a new lookup dict at every reset
+            cached = entry["_rev"] = (action_lookup, {v.lower(): k for k, v in action_lookup.items()})
+        rev = cached[1]
+        return [rev[a] for a in (x.lower() for x in actions) if a in rev]
 
     # ---- final states (es_manager.py:173-207) --------------------------------------------------------------------
     def get_rollout_states(self):

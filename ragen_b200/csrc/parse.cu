@@ -43,15 +43,49 @@ struct ParseParams {
   uint8_t* n_valid;
 };
 
+__device__ __forceinline__ unsigned lt_mask4(unsigned word) {  // bit k set iff byte k of word is '<'
+  const unsigned y = __vcmpeq4(word, 0x3c3c3c3cu) & 0x01010101u;
+  return ((y * 0x01020408u) >> 24) & 0xfu;
+}
+
+// first occurrence of `tag` in buf[s, e), buf 16-byte aligned (the shared-memory stage): 512 bytes per warp step, only the
+// '<' bytes are looked at.  -1 when there is none.
+__device__ __forceinline__ int warp_find_tag_vec(const uint8_t* buf, int s, int e, int tag, int lane) {
+  const int v1 = (e + 15) >> 4;
+  for (int vb = s >> 4; vb < v1; vb += 32) {
+    const int vi = vb + lane;
+    int mine = 0x7fffffff;
+    if (vi < v1) {
+      const uint4 v = *reinterpret_cast<const uint4*>(buf + 16 * vi);
+      unsigned m = lt_mask4(v.x) | (lt_mask4(v.y) << 4) | (lt_mask4(v.z) << 8) | (lt_mask4(v.w) << 12);
+      const int lo = 16 * vi;
+      if (lo < s) m &= 0xffffu << (s - lo);
+      if (lo + 16 > e) m &= (1u << (e - lo)) - 1u;
+      while (m) {
+        const int k = __ffs(m) - 1;
+        m &= m - 1;
+        if (parse::classify_tag(buf + lo + k, buf + e) == tag) {
+          mine = lo + k;
+          break;
+        }
+      }
+    }
+#pragma unroll
+    for (int o = 16; o; o >>= 1) mine = min(mine, __shfl_xor_sync(0xffffffffu, mine, o));
+    if (mine != 0x7fffffff) return mine;
+  }
+  return -1;
+}
+
 // One replace pass of ctx_manager.py:162-164 ("content.replace(tag, '')") on scr[s, e), warp-cooperative and in place:
 // 32 bytes per iteration, occurrences found by ballot (they cannot overlap: every special string has its only '<' at
 // the front), survivors compacted with a popcount prefix.  Reads run ahead of writes (w <= r), and every lane has
 // read and classified its byte before any lane writes.  Returns the new end.
-__device__ __forceinline__ int warp_remove_tag(uint8_t* scr, int s, int e, int tag, int lane) {
+__device__ __forceinline__ int warp_remove_tag(uint8_t* scr, int s, int e, int tag, int lane, bool staged) {
   const int L = parse::tag_len(tag);
   // most passes find nothing to remove: look for the first occurrence with a loop that only reads
-  int first = -1;
-  for (int b = s; b < e && first < 0; b += 32) {
+  int first = staged ? warp_find_tag_vec(scr, s, e, tag, lane) : -1;
+  for (int b = s; !staged && b < e && first < 0; b += 32) {
     const int i = b + lane;
     const bool st = i < e && scr[i] == '<' && parse::classify_tag(scr + i, scr + e) == tag;
     const unsigned hit = __ballot_sync(0xffffffffu, st);
@@ -83,16 +117,8 @@ __device__ __forceinline__ int warp_remove_tag(uint8_t* scr, int s, int e, int t
   return w;
 }
 
-__device__ __forceinline__ unsigned lt_mask4(unsigned word) {  // bit k set iff byte k of word is '<'
-  const unsigned y = __vcmpeq4(word, 0x3c3c3c3cu) & 0x01010101u;
-  return ((y * 0x01020408u) >> 24) & 0xfu;
-}
-
-__global__ void __launch_bounds__(PWARPS * 32) parse_kernel(const ParseParams p) {
-  __shared__ uint8_t stage[PWARPS][CLEAN_CAP];
-  const int lane = threadIdx.x & 31;
-  const int64_t r = (int64_t)blockIdx.x * PWARPS + (threadIdx.x >> 5);
-  if (r >= p.n) return;
+// one response, one warp; `stage` is this warp's CLEAN_CAP bytes of shared memory
+__device__ __forceinline__ void parse_one(const ParseParams& p, const int64_t r, const int lane, uint8_t* stage) {
   const int64_t off = p.offsets[r];
   const int n = (int)(p.offsets[r + 1] - off);
   const uint8_t* text = p.text + off;
@@ -176,13 +202,13 @@ __global__ void __launch_bounds__(PWARPS * 32) parse_kernel(const ParseParams p)
         uint8_t* scr = p.scratch + off;
         const int len = e - s;
         const bool staged = len <= CLEAN_CAP;
-        uint8_t* buf = staged ? stage[threadIdx.x >> 5] : scr + s;
+        uint8_t* buf = staged ? stage : scr + s;
 #pragma unroll 4
         for (int i = lane; i < len; i += 32) buf[i] = text[s + i];
         __syncwarp();
         int cs = 0, ce = len;
         for (int tag = parse::T_THINK; tag <= parse::T_IM_END; ++tag) {  // six passes, each followed by strip (:162-164)
-          ce = warp_remove_tag(buf, cs, ce, tag, lane);
+          ce = warp_remove_tag(buf, cs, ce, tag, lane, staged);
           parse::strip(buf, cs, ce);
         }
         if (staged) {
@@ -230,6 +256,22 @@ __global__ void __launch_bounds__(PWARPS * 32) parse_kernel(const ParseParams p)
       p.act_spans[(r * p.max_actions + k) * 2 + 1] = k < tail.kept ? tail.spans[2 * k + 1] : 0;
       p.codes_out[r * p.max_actions + k] = k < tail.nvalid ? tail.codes[k] : 0;
     }
+  }
+}
+
+// Persistent warps: response lengths differ by 10x and one in ten needs the cleaning passes, so warps take the next
+// response from a global counter instead of owning a fixed one - a finished warp never idles behind a slow neighbour of
+// its CTA, and the tail of the launch is one response long.
+__global__ void __launch_bounds__(PWARPS * 32) parse_kernel(const ParseParams p, unsigned long long* next) {
+  __shared__ __align__(16) uint8_t stage[PWARPS][CLEAN_CAP];
+  const int lane = threadIdx.x & 31;
+  for (;;) {
+    unsigned long long r = 0;
+    if (lane == 0) r = atomicAdd(next, 1ULL);
+    r = __shfl_sync(0xffffffffu, r, 0);
+    if (r >= (unsigned long long)p.n) break;
+    parse_one(p, (int64_t)r, lane, stage[threadIdx.x >> 5]);
+    __syncwarp();
   }
 }
 
@@ -300,7 +342,11 @@ extern "C" int ragen_parse_actions(ragen_ctx* ctx, int64_t n, const uint8_t* tex
   p.n_total = n_total;
   p.codes_out = codes_out;
   p.n_valid = n_valid;
-  parse_kernel<<<(unsigned)((n + PWARPS - 1) / PWARPS), PWARPS * 32, 0, (cudaStream_t)stream>>>(p);
+  unsigned long long* next = (unsigned long long*)ragen_scratch(ctx, sizeof(unsigned long long));
+  if (!next) return RAGEN_ENOMEM;
+  RAGEN_CUDA(cudaMemsetAsync(next, 0, sizeof(unsigned long long), (cudaStream_t)stream));
+  const int64_t want = (n + PWARPS - 1) / PWARPS, cap = (int64_t)ctx->sm_count * 12;  // 12 CTAs of 4 warps fit an SM (registers)
+  parse_kernel<<<(unsigned)(want < cap ? want : cap), PWARPS * 32, 0, (cudaStream_t)stream>>>(p, next);
   RAGEN_LAUNCHED(ctx);
   return RAGEN_OK;
 }

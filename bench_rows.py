@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Per-kernel measurement of every config of SURVEY.md 8(d) (C1..C5) on ONE B200, one JSON line per row.
 
-    python bench.py --rows [--quick] [--only sokoban,generator,frozenlake,parse,c5,manager,rollout]  > profiles/rNN_kernels.jsonl
+    python bench.py --rows [--quick] [--only sokoban,generator,frozenlake,parse,c5,manager,rollout,rgb]  > profiles/rNN_kernels.jsonl
 
 bench.py is the contract line (C4 step); this script is the supporting evidence for the other rows: each line carries
 the kernel's device time (CUDA events on the launching stream, after warm-up, median of the repetitions), the
@@ -23,7 +23,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
-from ragen_b200 import ops  # noqa: E402
+from ragen_b200 import _lib, ops  # noqa: E402
 from ragen_b200 import synth  # noqa: E402
 
 
@@ -67,6 +67,40 @@ def line(row, unit, units, ms, bytes_per_unit, cpu_units_per_s=None, cpu_sample=
     out.update(extra)
     print(json.dumps(out), flush=True)
     return out
+
+
+# ---- rgb_array observations: sprite blit ------------------------------------------------------------------------------
+def rgb_rows(quick):
+    from oracle import sokoban as S
+    from ragen_b200.env.sokoban import SokobanBatch
+
+    rows = []
+    for (H, W, nb, n, tag) in [(10, 10, 2, 16384, "rgb_array blit 10x10, 16 Ki envs (1.26 GB of images)"),
+                               (6, 6, 1, 16384, "rgb_array blit 6x6, 16 Ki envs"),
+                               (6, 6, 1, 128, "rgb_array blit 6x6, C1's 128 envs")]:
+        if quick and n > 4096:
+            n = 4096
+        fixed, state = synth.synthetic_rooms(n, H, W, nb, seed=4)
+        b = SokobanBatch(n, (H, W), nb, 100, device=0)
+        b.load_rooms(fixed, state)
+        surfaces = S.synthetic_surfaces(16, seed=1)
+        b.set_atlas(surfaces)
+        out = torch.empty((n, H * 16, W * 16, 3), dtype=torch.uint8, device="cuda")
+
+        def blit():
+            _lib.check(b.lib.ragen_sokoban_render_rgb(b.ctx.handle, n, H, W, 16, _lib.ptr(b.state), _lib.ptr(b.meta),
+                                                      _lib.ptr(b.atlas), None, 0, _lib.ptr(out), b.ctx.stream()))
+        ms = dev_time(blit, reps=30)
+        m = min(n, 64)
+
+        def cpu():
+            for j in range(m):
+                S.room_to_rgb(state[j].reshape(H, W), fixed[j].reshape(H, W), surfaces)
+        cs = cpu_time(cpu, 2.0)
+        rows.append(line(tag, "image", n, ms, H * W * 768 + H * W + 8, m / cs, f"{m} rooms, oracle room_to_rgb (numpy), 1 core",
+                         envs=n, kernel="sokoban_rgb_vec_kernel<16>", note="write-only traffic; sprites are synthetic"))
+        del b, out
+    return rows
 
 
 # ---- C4(ii) / C1 step shapes: Sokoban step at several sizes -----------------------------------------------------------
@@ -357,7 +391,7 @@ def main(quick=False, only=""):
     a = argparse.Namespace(quick=quick, only=only)
     torch.cuda.set_device(0)
     todo = {"sokoban": sokoban_rows, "generator": generator_rows, "frozenlake": frozenlake_rows, "parse": parse_rows, "c5": c5_rows,
-            "manager": manager_rows, "rollout": rollout_rows}
+            "manager": manager_rows, "rollout": rollout_rows, "rgb": rgb_rows}
     for name, fn in todo.items():
         if a.only and name not in a.only.split(","):
             continue

@@ -91,6 +91,15 @@ int ragen_sokoban_render_packed(ragen_ctx* ctx, int64_t n, int H, int W, const u
 int ragen_sokoban_render(ragen_ctx* ctx, int64_t n, int H, int W, const uint8_t* state,
                          const int16_t* meta, uint8_t* obs, void* stream);
 
+/* SokobanEnv.render rgb_array branch (ragen/env/sokoban/env.py:58-59 -> gym_sokoban get_image -> room_to_rgb): every cell
+ * receives the S x S x 3 sprite of its surface (room_state code; 6 = player on a target) in a uint8 image
+ * out [m][H*S][W*S][3].  atlas uint8 [7][S][S][3] is caller data (upstream's 16 x 16 PNG sprites, which live in the
+ * un-vendored gym_sokoban package).  rows int64 [n_rows] selects the envs to draw (image i = env rows[i], m = n_rows);
+ * rows NULL draws all n envs.  S in [1, 64]; S = 16 with 16-byte aligned atlas/out takes the vector path. */
+int ragen_sokoban_render_rgb(ragen_ctx* ctx, int64_t n, int H, int W, int S, const uint8_t* state,
+                             const int16_t* meta, const uint8_t* atlas, const int64_t* rows, int64_t n_rows,
+                             uint8_t* out, void* stream);
+
 /* Post-reset bookkeeping of SokobanEnv.reset (env.py:37-38) for rooms already in device memory:
  * player = argwhere(state == 5)[0], num_env_steps = 0, boxes_on_target = 0 -> meta.
  * status[i] (may be NULL) = 0 ok, 1 no player cell, 2 border not wall, 3 room_fixed is not the

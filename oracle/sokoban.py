@@ -320,6 +320,35 @@ class SokobanOracle:
         lut = self.glyphs
         return "\n".join("".join(lut.get(int(c), "?") for c in row) for row in self.glyph_codes())
 
+    def render_rgb(self, surfaces):
+        return room_to_rgb(self.state.reshape(self.H, self.W), self.fixed.reshape(self.H, self.W), surfaces)
+
+
+# --------------------------------------------------------------------------------------------
+# rgb_array observation (env.py:58-59 -> gym_sokoban get_image(mode='rgb_array') -> room_to_rgb)
+# --------------------------------------------------------------------------------------------
+# gym_sokoban is un-vendored and absent here, and so are its sprite PNGs: the blit below restates the published
+# room_to_rgb loop (parity unpinned), and the sprites are an argument.
+def room_to_rgb(room_state, room_fixed, surfaces):
+    """surfaces: uint8 [7, S, S, 3] in upstream's order (wall, floor, box_target, box_on_target, box, player,
+    player_on_target).  Returns uint8 [H*S, W*S, 3]."""
+    room = np.array(room_state).astype(np.int64)
+    if room_fixed is not None:
+        room[(room == PLAYER) & (np.asarray(room_fixed) == TARGET)] = PLAYER_ON_TARGET
+    surfaces = np.asarray(surfaces, dtype=np.uint8)
+    S = surfaces.shape[1]
+    H, W = room.shape
+    img = np.zeros((H * S, W * S, 3), dtype=np.uint8)
+    for i in range(H):
+        for j in range(W):
+            img[i * S:(i + 1) * S, j * S:(j + 1) * S, :] = surfaces[room[i, j]]
+    return img
+
+
+def synthetic_surfaces(S=16, seed=0):
+    """Random sprites for parity runs: every pixel of every surface differs, so a misplaced byte shows."""
+    return np.random.default_rng(seed).integers(0, 256, size=(7, S, S, 3), dtype=np.uint8)
+
 
 # --------------------------------------------------------------------------------------------
 # validity checks for generated rooms

@@ -41,6 +41,27 @@ class SokobanEnvConfig:
             delattr(self, "dim_y")
 
 
+SURFACE_FILES = ("wall", "floor", "box_target", "box_on_target", "box", "player", "player_on_target")
+
+
+def load_sprite_atlas(directory=None):
+    """uint8 [7, 16, 16, 3]: the PNG sprites room_to_rgb loads (gym_sokoban/envs/surface/*.png).  gym_sokoban is a third-party
+    package the reference imports; when it is not installed the sprites do not exist and the caller must supply an atlas."""
+    import importlib.util
+    import os
+
+    if directory is None:
+        spec = importlib.util.find_spec("gym_sokoban")
+        if spec is None or not spec.submodule_search_locations:
+            raise RuntimeError("rgb_array rendering needs gym_sokoban's sprite PNGs (package not installed): "
+                               "pass them with SokobanBatch.set_atlas(uint8[7, S, S, 3]) or load_sprite_atlas(directory)")
+        directory = os.path.join(list(spec.submodule_search_locations)[0], "envs", "surface")
+    from PIL import Image
+
+    return np.stack([np.asarray(Image.open(os.path.join(directory, f + ".png")).convert("RGB"), dtype=np.uint8)
+                     for f in SURFACE_FILES])
+
+
 @dataclass
 class StepOut:
     """Device tensors written by one step launch (views of the batch's output buffers)."""
@@ -221,6 +242,7 @@ class SokobanBatch:
         obs = (self._packed_buffer() if packed else self.obs) if render else None
         if render:
             self.obs_is_packed = bool(packed)
+        self.obs_stale = not render  # texts() renders again before reading rows a step did not write
         fn = self.lib.ragen_sokoban_step_packed if packed else self.lib.ragen_sokoban_step
         _lib.check(fn(self.ctx.handle, self.n, self.H, self.W, self.num_boxes, self.max_steps, _lib.ptr(actions), K,
                       _lib.ptr(n_actions), _lib.ptr(self.state), _lib.ptr(self.meta), _lib.ptr(self.reward), _lib.ptr(self.done),
@@ -268,13 +290,44 @@ class SokobanBatch:
     def render(self, packed=False):
         obs = self._packed_buffer() if packed else self.obs
         self.obs_is_packed = bool(packed)
+        self.obs_stale = False
         fn = self.lib.ragen_sokoban_render_packed if packed else self.lib.ragen_sokoban_render
         _lib.check(fn(self.ctx.handle, self.n, self.H, self.W, _lib.ptr(self.state), _lib.ptr(self.meta), _lib.ptr(obs),
                       self.ctx.stream()))
         return obs
 
+    def set_atlas(self, surfaces):
+        """Sprites for render_rgb: uint8 [7, S, S, 3] in gym_sokoban's surface order (wall, floor, box_target, box_on_target,
+        box, player, player_on_target)."""
+        a = np.ascontiguousarray(surfaces, dtype=np.uint8)
+        if a.ndim != 4 or a.shape[0] != 7 or a.shape[1] != a.shape[2] or a.shape[3] != 3:
+            raise ValueError(f"atlas must be uint8 [7, S, S, 3], got {a.shape}")
+        self.atlas = torch.from_numpy(a).to(self.device)
+        return self.atlas
+
+    def render_rgb(self, rows=None):
+        """rgb_array observations (env.py:58-59) of all envs or of `rows`: uint8 device tensor [m, H*S, W*S, 3]."""
+        if getattr(self, "atlas", None) is None:
+            self.set_atlas(load_sprite_atlas())
+        S = int(self.atlas.shape[1])
+        d_rows, m = None, self.n
+        if rows is not None:
+            d_rows = torch.as_tensor(rows, dtype=torch.int64).to(self.device)
+            m = int(d_rows.numel())
+            if m and (int(d_rows.min()) < 0 or int(d_rows.max()) >= self.n):
+                raise IndexError("render_rgb: env row out of range")
+        out = torch.empty((m, self.H * S, self.W * S, 3), dtype=torch.uint8, device=self.device)
+        if m == 0:
+            return out
+        _lib.check(self.lib.ragen_sokoban_render_rgb(self.ctx.handle, self.n, self.H, self.W, S, _lib.ptr(self.state),
+                                                     _lib.ptr(self.meta), _lib.ptr(self.atlas), _lib.ptr(d_rows), m if d_rows is not None else 0,
+                                                     _lib.ptr(out), self.ctx.stream()))
+        return out
+
     def texts(self, grid_lookup, rows=None):
         """Text observations of the latest render (all envs, or `rows`): one device->host copy + one translate per env."""
+        if getattr(self, "obs_stale", False):
+            self.render(packed=self.obs_is_packed)
         if self.obs_is_packed:
             pairs = glyph_pair_table(grid_lookup)
             codes = (self.obs_packed if rows is None else self.obs_packed[rows]).cpu().numpy()
@@ -363,9 +416,11 @@ class SokobanEnv(BaseDiscreteActionEnv):
 
     def render(self, mode=None):
         render_mode = mode if mode is not None else self.render_mode
-        if render_mode != "text":
-            raise ValueError(f"Invalid mode: {render_mode} (rgb_array needs gym_sokoban sprites: out of scope)")
-        return self.batch.texts(self.GRID_LOOKUP, rows=[self.slot])[0]
+        if render_mode == "text":
+            return self.batch.texts(self.GRID_LOOKUP, rows=[self.slot])[0]
+        if render_mode == "rgb_array":
+            return self.batch.render_rgb(rows=[self.slot])[0].cpu().numpy()
+        raise ValueError(f"Invalid mode: {render_mode}")
 
     def get_all_actions(self):
         return list(self.ACTION_LOOKUP.keys())

@@ -105,9 +105,15 @@ class EnvStateManager:
                 self._block_of[self.envs[b.first + i]["env_id"]] = b
 
     # ---- observations ----------------------------------------------------------------------------------------
-    def _block_texts(self, block) -> List[str]:
-        """Current observation text of every env of the block (one device->host copy for grid envs)."""
+    def _block_texts(self, block) -> List:
+        """Current observation of every env of the block: text, or a list of images (one device->host copy for grid envs)."""
         envs = self.envs[block.first:block.first + block.count]
+        if block.env_type == "sokoban" and envs[0]["env"].render_mode == "rgb_array":
+            # one blit launch + one device->host copy for the whole block, then _handle_mm_state (:242-250) per env
+            import PIL.Image
+
+            frames = block.batch.render_rgb().cpu().numpy()
+            return [[PIL.Image.fromarray(f, mode="RGB")] for f in frames]
         if block.env_type == "sokoban":  # packed glyph rows (two codes per byte) when the room shape allows: half the copy
             return block.batch.texts(envs[0]["env"].GRID_LOOKUP)
         if block.env_type == "frozen_lake":
@@ -218,7 +224,10 @@ class EnvStateManager:
                 codes = [entry["env"].action_map[a] + 1 for a in todo] if block.env_type == "frozen_lake" else todo
                 act[s, :len(codes)] = codes
                 nact[s] = len(codes)
-            kw = {"packed": b.can_pack} if block.env_type == "sokoban" else {}
+            kw = {}
+            if block.env_type == "sokoban":
+                text = self.envs[block.first]["env"].render_mode == "text"
+                kw = {"packed": b.can_pack and text, "render": text}
             out = b.step(torch.from_numpy(act).to(dev), torch.from_numpy(nact).to(dev), **kw)
             host = torch.stack([out.done, out.flags, out.n_executed]).cpu().numpy()
             rew = out.reward.cpu().numpy()
@@ -310,11 +319,14 @@ class EnvStateManager:
         return self.rollout_cache
 
     def _update_cache_history(self, history: List[Dict], next_state, actions_left, num_actions_info: Optional[Dict] = None):
-        """es_manager.py:212-228 (text states only: image observations are out of this path's scope)."""
+        """es_manager.py:212-228."""
         if num_actions_info is not None:
             assert len(history), "History should not be empty"
             history[-1].update(num_actions_info)
-        history.append({"state": next_state, "actions_left": actions_left})
+        if isinstance(next_state, str):
+            history.append({"state": next_state, "actions_left": actions_left})
+        else:  # list of images
+            history.append({"state": "<images>" * len(next_state), "images": next_state, "actions_left": actions_left})
         return history
 
     def render(self):

@@ -7,6 +7,7 @@
 // randint, sample(pop, 1), choice; NumPy legacy RandomState: seed(int) = init_genrand, randint = masked rejection on
 // 32-bit draws).  tests/test_hostsim.py checks these functions against the real modules.
 #pragma once
+#include <stddef.h>
 #include <stdint.h>
 
 #ifndef RAGEN_HD
@@ -21,14 +22,22 @@ namespace mt {
 
 constexpr int N = 624, M = 397;
 
+// word i of the state lives at mt[i * stride]: stride 1 on the host; on the device the 32 lanes of a warp interleave their
+// states (stride 32) so that the lock-step seeding and twist loops of a warp touch whole 128-byte lines
 struct State {
   uint32_t* mt;  // 624 words, caller-owned
   int idx;
+  int stride;
+  RAGEN_HD uint32_t& at(int i) const { return mt[(size_t)i * (size_t)stride]; }
 };
 
 RAGEN_HD void init_genrand(State& s, uint32_t seed) {
-  s.mt[0] = seed;
-  for (int i = 1; i < N; ++i) s.mt[i] = 1812433253u * (s.mt[i - 1] ^ (s.mt[i - 1] >> 30)) + (uint32_t)i;
+  uint32_t prev = seed;
+  s.at(0) = prev;
+  for (int i = 1; i < N; ++i) {
+    prev = 1812433253u * (prev ^ (prev >> 30)) + (uint32_t)i;
+    s.at(i) = prev;
+  }
   s.idx = N;
 }
 
@@ -38,50 +47,58 @@ RAGEN_HD void seed_python(State& s, uint64_t a) {
   const int klen = key[1] ? 2 : 1;
   init_genrand(s, 19650218u);
   int i = 1, j = 0;
+  uint32_t prev = s.at(0);  // mt[i - 1], carried in a register: the recurrence never waits on its own store
   for (int k = (N > klen ? N : klen); k; --k) {
-    s.mt[i] = (s.mt[i] ^ ((s.mt[i - 1] ^ (s.mt[i - 1] >> 30)) * 1664525u)) + key[j] + (uint32_t)j;
+    prev = (s.at(i) ^ ((prev ^ (prev >> 30)) * 1664525u)) + key[j] + (uint32_t)j;
+    s.at(i) = prev;
     ++i;
     ++j;
     if (i >= N) {
-      s.mt[0] = s.mt[N - 1];
+      s.at(0) = prev;
       i = 1;
     }
     if (j >= klen) j = 0;
   }
   for (int k = N - 1; k; --k) {
-    s.mt[i] = (s.mt[i] ^ ((s.mt[i - 1] ^ (s.mt[i - 1] >> 30)) * 1566083941u)) - (uint32_t)i;
+    prev = (s.at(i) ^ ((prev ^ (prev >> 30)) * 1566083941u)) - (uint32_t)i;
+    s.at(i) = prev;
     ++i;
     if (i >= N) {
-      s.mt[0] = s.mt[N - 1];
+      s.at(0) = prev;
       i = 1;
     }
   }
-  s.mt[0] = 0x80000000u;
+  s.at(0) = 0x80000000u;
   s.idx = N;
 }
 
 // np.random.seed(a) for 0 <= a < 2^32
 RAGEN_HD void seed_numpy(State& s, uint32_t a) { init_genrand(s, a); }
 
+RAGEN_HD uint32_t twist_word(uint32_t cur, uint32_t nxt, uint32_t far) {
+  const uint32_t y = (cur & 0x80000000u) | (nxt & 0x7fffffffu);
+  return far ^ (y >> 1) ^ ((y & 1u) ? 0x9908b0dfu : 0u);
+}
 RAGEN_HD void twist(State& s) {
-  uint32_t* mt = s.mt;
   int kk = 0;
+  uint32_t cur = s.at(0);
   for (; kk < N - M; ++kk) {
-    const uint32_t y = (mt[kk] & 0x80000000u) | (mt[kk + 1] & 0x7fffffffu);
-    mt[kk] = mt[kk + M] ^ (y >> 1) ^ ((y & 1u) ? 0x9908b0dfu : 0u);
+    const uint32_t nxt = s.at(kk + 1);
+    s.at(kk) = twist_word(cur, nxt, s.at(kk + M));
+    cur = nxt;
   }
   for (; kk < N - 1; ++kk) {
-    const uint32_t y = (mt[kk] & 0x80000000u) | (mt[kk + 1] & 0x7fffffffu);
-    mt[kk] = mt[kk + (M - N)] ^ (y >> 1) ^ ((y & 1u) ? 0x9908b0dfu : 0u);
+    const uint32_t nxt = s.at(kk + 1);
+    s.at(kk) = twist_word(cur, nxt, s.at(kk + (M - N)));
+    cur = nxt;
   }
-  const uint32_t y = (mt[N - 1] & 0x80000000u) | (mt[0] & 0x7fffffffu);
-  mt[N - 1] = mt[M - 1] ^ (y >> 1) ^ ((y & 1u) ? 0x9908b0dfu : 0u);
+  s.at(N - 1) = twist_word(cur, s.at(0), s.at(M - 1));
   s.idx = 0;
 }
 
 RAGEN_HD uint32_t next32(State& s) {
   if (s.idx >= N) twist(s);
-  uint32_t y = s.mt[s.idx++];
+  uint32_t y = s.at(s.idx++);
   y ^= y >> 11;
   y ^= (y << 7) & 0x9d2c5680u;
   y ^= (y << 15) & 0xefc60000u;

@@ -5,15 +5,27 @@
 // sokoban_gen_logic.cuh and is stream- and order-exact, so room i is the room the reference generates for seeds[i].
 //
 // Parallelisation: rooms are independent and each search is inherently sequential (a depth-limited DFS whose global
-// visited set makes the result depend on visiting order), so one THREAD owns one room at a time and the grid is a
-// pool of persistent threads that pull rooms from an atomic counter (search lengths vary by 1000x between seeds).
-// Each pool slot owns a private workspace in HBM: two MT19937 states, the DFS stack and an exact visited bitmap
-// over (player, {(box, pulled)}) keys - 128 KB for 10x10 / 2 boxes.  The search is latency-bound pointer chasing
-// into that bitmap, hidden by the number of rooms in flight; outputs are 2*H*W bytes per room.
+// visited set makes the result depend on visiting order), so one THREAD owns one room - and the code is shaped so that
+// the 32 rooms of a warp run in lock step instead of one after the other:
+//   * a warp takes 32 consecutive rooms at a time from an atomic counter and walks the phases of generate_room together
+//     (seed both MT19937 streams, then up to four tries of topology -> placement -> clear -> search, then the player jitter);
+//   * the MT19937 states of a warp are interleaved word by word (lane l's word i at [i][l]), so the seeding and twist
+//     loops, whose trip counts are the same for every room, touch whole 128-byte lines;
+//   * the visited bitmaps (128 KB per room for 10x10 / 2 boxes) are cleared by the whole warp, 512 contiguous bytes per
+//     instruction, for the lanes that are about to search;
+//   * the search is sgen::reverse_play_fast: the node lives in registers, a level costs a ONE-BYTE undo record in shared
+//     memory, walls are a bitmask in shared memory, cell -> (interior index, row, col) are CTA-wide tables, and one loop
+//     iteration tries one child or pops one level without inner loops, so divergence inside a warp is a few predicated
+//     branches per iteration.  What remains per iteration is one dependent probe of the room's bitmap in L2/HBM, hidden
+//     by the other warps of the SM.
+// Outputs are 2*H*W bytes per room.  No roofline claim: rooms/s and validity are what is reported.
 #include "common.cuh"
 #include "sokoban_gen_logic.cuh"
 
 namespace {
+
+constexpr int GEN_T = 64;           // threads per CTA (2 warps)
+constexpr int STACK_SMEM_MAX = 40 * 1024;  // undo stacks move to the HBM workspace beyond this (search_depth > 639)
 
 struct GenParams {
   int64_t n;
@@ -25,39 +37,118 @@ struct GenParams {
   int32_t* status;
   int32_t* explored;
   uint8_t* ws;
-  size_t slot_bytes, off_np, off_stack, off_scratch, off_vis;
-  uint64_t vis_words;
+  // a warp's block of the workspace: [mt_py 624 x 32 words][mt_np 624 x 32 words][32 lane regions of lane_bytes]; a lane
+  // region = [scratch 2*H*W][undo stack, only when it does not fit shared memory][visited set]
+  size_t warp_bytes, off_lanes, lane_bytes, off_stack, off_vis, vis_bytes;
   uint32_t vis_mask;
-  int vis_mode;
+  int vis_mode, stack_in_smem;
   unsigned long long* counter;
 };
 
-__global__ void __launch_bounds__(64) sokoban_generate_kernel(const GenParams p) {
-  const size_t slot = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  uint8_t* ws = p.ws + slot * p.slot_bytes;
-  sgen::Work w;
-  w.mt_py = reinterpret_cast<uint32_t*>(ws);
-  w.mt_np = reinterpret_cast<uint32_t*>(ws + p.off_np);
-  w.stack = reinterpret_cast<sgen::Frame*>(ws + p.off_stack);
-  w.scratch = ws + p.off_scratch;
-  w.vis.mode = p.vis_mode;
-  w.vis.mask = p.vis_mask;
-  w.vis.mem = reinterpret_cast<uint32_t*>(ws + p.off_vis);
-  w.vis.mem64 = reinterpret_cast<uint64_t*>(ws + p.off_vis);
-  w.vis_words = p.vis_words;
-  const int HW = p.g.H * p.g.W;
+__global__ void __launch_bounds__(GEN_T) sokoban_generate_kernel(const GenParams p) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  // CTA-wide tables, then per-thread wall nibbles [ceil(H*W/8)][GEN_T] words, then the undo stacks [depth][GEN_T] bytes
+  const sgen::Geometry g = p.g;
+  const int HW = g.H * g.W;
+  uint16_t* s_rc = reinterpret_cast<uint16_t*>(smem);
+  uint32_t* s_wall = reinterpret_cast<uint32_t*>(smem + 512);
+  uint8_t* s_interior = smem + 512 + ((HW + 7) / 8) * GEN_T * 4;
+  uint8_t* s_stack = s_interior + sgen::MAX_CELLS;
+  for (int cell = threadIdx.x; cell < HW; cell += GEN_T) {
+    const int r = cell / g.W, c = cell - r * g.W;
+    s_interior[cell] = (uint8_t)((r - 1) * (g.W - 2) + (c - 1));
+    s_rc[cell] = (uint16_t)((r << 8) | c);
+  }
+  __syncthreads();
+
+  const int lane = threadIdx.x & 31;
+  const size_t warp_slot = ((size_t)blockIdx.x * GEN_T + threadIdx.x) >> 5;
+  uint8_t* wws = p.ws + warp_slot * p.warp_bytes;
+  uint8_t* lws = wws + p.off_lanes + (size_t)lane * p.lane_bytes;
+  uint8_t* floor = lws;
+  uint8_t* vis_mem = lws + p.off_vis;
+  sgen::Visited vis;
+  vis.mode = p.vis_mode;
+  vis.mask = p.vis_mask;
+  vis.mem = reinterpret_cast<uint32_t*>(vis_mem);
+  vis.mem64 = reinterpret_cast<uint64_t*>(vis_mem);
+  sgen::Fast fm;
+  fm.interior = s_interior;
+  fm.rc = s_rc;
+  fm.wall = s_wall + threadIdx.x;
+  fm.wall_stride = GEN_T;
+  fm.stack = p.stack_in_smem ? s_stack + threadIdx.x : lws + p.off_stack;
+  fm.stack_stride = p.stack_in_smem ? GEN_T : 1;
+  const unsigned FULL = 0xffffffffu;
+
   for (;;) {
-    const unsigned long long room = atomicAdd(p.counter, 1ull);
-    if (room >= (unsigned long long)p.n) break;
-    const uint64_t seed = p.seeds[room];
-    int st, explored = 0;
-    if (seed >> 32) {
-      st = 3;  // np.random.seed rejects seeds >= 2^32 (ValueError in the reference)
-    } else {
-      st = sgen::generate_room(p.g, p.search_depth, p.num_gen_steps, seed, w, p.fixed + room * HW, p.state + room * HW, &explored);
+    unsigned long long base = 0;
+    if (lane == 0) base = atomicAdd(p.counter, 32ull);
+    base = __shfl_sync(FULL, base, 0);
+    if (base >= (unsigned long long)p.n) break;
+    const int64_t room = (int64_t)base + lane;
+    const bool valid = room < p.n;
+    const uint64_t seed = valid ? p.seeds[room] : 0;
+    const bool seed_ok = (seed >> 32) == 0;  // np.random.seed rejects seeds >= 2^32 (ValueError in the reference)
+    uint8_t* fixed = p.fixed + (valid ? room : 0) * HW;
+    uint8_t* state = p.state + (valid ? room : 0) * HW;
+
+    mt::State py{reinterpret_cast<uint32_t*>(wws) + lane, 0, 32};
+    mt::State np{reinterpret_cast<uint32_t*>(wws) + mt::N * 32 + lane, 0, 32};
+    mt::seed_python(py, seed);
+    mt::seed_numpy(np, (uint32_t)seed);
+
+    int st = seed_ok ? (int)sgen::OK : 3, explored = 0, player = 0;
+    bool trying = valid && seed_ok;  // this lane still owes a try (generate_room's loop of four, utils.py:244)
+    uint8_t targets[sgen::MAX_BOXES] = {0, 0, 0, 0};
+    sgen::BestFast best;
+    best.disp = 0;
+    best.p = 0;
+    best.boxes = 0;
+    for (int t = 0; t < 4; ++t) {
+      if (!__any_sync(FULL, trying)) break;
+      bool search = false;
+      if (trying) {
+        sgen::topology(py, g, p.num_gen_steps, 0.35, floor);
+        if (sgen::place(np, g, floor, fixed, player, targets)) {
+          search = true;
+        } else {
+          st = sgen::NO_SPACE;
+          explored = 0;  // generate_room returns before reporting the previous try's count
+          trying = false;
+        }
+      }
+      __syncwarp();
+      // clear the visited sets of the lanes that search, all 32 lanes on one lane's set at a time
+      unsigned need = __ballot_sync(FULL, search);
+      while (need) {
+        const int l = __ffs((int)need) - 1;
+        need &= need - 1;
+        uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(__shfl_sync(FULL, (unsigned long long)vis_mem, l)));
+        const size_t vecs = p.vis_bytes >> 4;
+        for (size_t i = lane; i < vecs; i += 32) dst[i] = make_uint4(0u, 0u, 0u, 0u);
+      }
+      __syncwarp();  // orders the other lanes' zeroes before this lane's probes
+      if (search) sgen::fill_walls(g, fixed, s_wall + threadIdx.x, GEN_T);
+      // all 32 lanes enter: the search loop is warp-wide so that the lanes meet again after every iteration
+      const int found = sgen::reverse_play_fast(g, fm, sgen::pack_cells(targets, g.nb), player, p.search_depth, vis, best, search);
+      if (search) {
+        explored = found;
+        if (best.disp > 0) trying = false;
+      }
     }
-    p.status[room] = st;
-    if (p.explored) p.explored[room] = explored;
+    if (valid) {
+      if (st == sgen::OK) {
+        if (best.disp == 0) {
+          st = sgen::SCORE_ZERO;  // RuntimeWarning('Generated Model with score == 0')
+        } else {
+          sgen::finish_room(py, g, fixed, state, best);
+        }
+      }
+      p.status[room] = st;
+      if (p.explored) p.explored[room] = seed_ok ? explored : 0;
+    }
+    __syncwarp();
   }
 }
 
@@ -90,36 +181,43 @@ extern "C" int ragen_sokoban_generate(ragen_ctx* ctx, int64_t n, int H, int W, i
   p.status = status;
   p.explored = explored;
   const int kb = sgen::key_bits(p.g);
-  size_t vis_bytes;
   if (kb <= 24) {
     p.vis_mode = 0;
-    p.vis_words = ((uint64_t)1 << kb) / 32 + 1;
-    vis_bytes = p.vis_words * 4;
+    p.vis_bytes = align_up((((size_t)1 << kb) / 32 + 1) * 4, 512);
   } else {
     p.vis_mode = 1;
-    p.vis_words = (uint64_t)1 << 20;  // > 3x the 300000-state cap of the search
-    p.vis_mask = (uint32_t)(p.vis_words - 1);
-    vis_bytes = p.vis_words * 8;
+    const size_t slots = (size_t)1 << 20;  // > 3x the 300000-state cap of the search
+    p.vis_mask = (uint32_t)(slots - 1);
+    p.vis_bytes = slots * 8;
   }
-  p.off_np = sizeof(uint32_t) * mt::N;
-  p.off_stack = 2 * p.off_np;
-  p.off_scratch = align_up(p.off_stack + sizeof(sgen::Frame) * (size_t)(search_depth + 1), 16);
-  p.off_vis = align_up(p.off_scratch + 2 * (size_t)H * W, 16);
-  p.slot_bytes = align_up(p.off_vis + vis_bytes, 128);
-  // pool size: enough threads to hide the bitmap latency, bounded by the rooms to do and by 8 GiB of workspace
-  const int threads = 64;
-  int64_t slots = (int64_t)ctx->sm_count * 512;
-  if (slots > n) slots = n;
-  const int64_t cap = (int64_t)(((size_t)8 << 30) / p.slot_bytes);
-  if (slots > cap) slots = cap;
-  slots = (slots + threads - 1) / threads * threads;
-  const size_t ws_bytes = 256 + (size_t)slots * p.slot_bytes;
+  const size_t stack_bytes = (size_t)(search_depth + 1);
+  p.stack_in_smem = stack_bytes * GEN_T <= STACK_SMEM_MAX;
+  p.off_stack = align_up(2 * (size_t)H * W, 16);
+  p.off_vis = align_up(p.off_stack + (p.stack_in_smem ? 0 : stack_bytes), 512);
+  p.lane_bytes = p.off_vis + p.vis_bytes;
+  p.off_lanes = 2 * sizeof(uint32_t) * mt::N * 32;
+  p.warp_bytes = p.off_lanes + 32 * p.lane_bytes;
+  const size_t smem = 512 + (size_t)((H * W + 7) / 8) * GEN_T * 4 + sgen::MAX_CELLS + (p.stack_in_smem ? stack_bytes * GEN_T : 0);
+  // pool size: warps of 32 rooms; as many as fit an SM by shared memory (at most 16 warps per SM), bounded by the rooms
+  // to do and by 8 GiB of workspace
+  int64_t ctas_per_sm = (int64_t)(200 * 1024 / smem);
+  if (ctas_per_sm > 8) ctas_per_sm = 8;
+  if (ctas_per_sm < 1) ctas_per_sm = 1;
+  int64_t warps = (int64_t)ctx->sm_count * ctas_per_sm * (GEN_T / 32);
+  const int64_t want = (n + 31) / 32;
+  if (warps > want) warps = want;
+  const int64_t cap = (int64_t)(((size_t)8 << 30) / p.warp_bytes);
+  if (warps > cap) warps = cap;
+  RAGEN_REQUIRE(warps >= 1, "generator workspace for one warp of rooms (%zu B) exceeds 8 GiB", p.warp_bytes);
+  const int64_t ctas = (warps + GEN_T / 32 - 1) / (GEN_T / 32);
+  const size_t ws_bytes = 256 + (size_t)ctas * (GEN_T / 32) * p.warp_bytes;
   uint8_t* ws = (uint8_t*)ragen_gen_workspace(ctx, ws_bytes);
   if (!ws) return RAGEN_ENOMEM;
   p.counter = reinterpret_cast<unsigned long long*>(ws);
   p.ws = ws + 256;
   RAGEN_CUDA(cudaMemsetAsync(p.counter, 0, sizeof(unsigned long long), st));
-  sokoban_generate_kernel<<<(unsigned)(slots / threads), threads, 0, st>>>(p);
+  RAGEN_CUDA(cudaFuncSetAttribute(sokoban_generate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  sokoban_generate_kernel<<<(unsigned)ctas, GEN_T, smem, st>>>(p);
   RAGEN_LAUNCHED(ctx);
   return RAGEN_OK;
 }

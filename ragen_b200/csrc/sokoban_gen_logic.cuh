@@ -239,6 +239,275 @@ RAGEN_HD int reverse_play(const Geometry& g, const uint8_t* structure, const uin
   return explored;
 }
 
+// ---- the same search, shaped for a GPU thread ------------------------------------------------------------------------
+// reverse_play above is the plain restatement (frames that copy the node).  reverse_play_fast visits the same nodes in the
+// same order and returns the same `explored` and `best`, but keeps the current node in registers (boxes packed one cell per
+// byte), pushes a ONE-BYTE undo record per level instead of a 12-byte frame, takes walls from a bitmask and cell -> interior
+// index / (row, col) from tables, and loops once per child tried or level popped with no inner loops - so the 32 rooms of a
+// warp advance in lock step.  tests/test_hostsim.py checks the two against each other seed for seed.
+struct Fast {
+  const uint8_t* interior;  // [H*W] interior index of a cell (garbage on the border: never read there)
+  const uint16_t* rc;       // [H*W] row << 8 | col
+  const uint32_t* wall;     // nibble (cell & 7) of word wall[(cell >> 3) * wall_stride]: bit a = neighbour a is not a wall
+  int wall_stride;
+  uint8_t* stack;           // undo record of depth d at stack[d * stack_stride]
+  int stack_stride;
+};
+struct BestFast {
+  int p, disp, score;
+  uint32_t boxes;
+};
+
+RAGEN_HD uint32_t eq4(uint32_t a, uint32_t b) {  // 0xff in every byte where a and b agree
+#ifdef __CUDA_ARCH__
+  return __vcmpeq4(a, b);
+#else
+  uint32_t m = 0;
+  for (int k = 0; k < 4; ++k)
+    if (((a >> (8 * k)) & 0xffu) == ((b >> (8 * k)) & 0xffu)) m |= 0xffu << (8 * k);
+  return m;
+#endif
+}
+RAGEN_HD int lowest_byte(uint32_t m) {  // index of the lowest non-zero byte, m != 0
+#ifdef __CUDA_ARCH__
+  return (__ffs((int)m) - 1) >> 3;
+#else
+  return __builtin_ctz(m) >> 3;
+#endif
+}
+RAGEN_HD int lowest_bit(unsigned m) {
+#ifdef __CUDA_ARCH__
+  return __ffs((int)m) - 1;
+#else
+  return __builtin_ctz(m);
+#endif
+}
+RAGEN_HD uint32_t bcast4(int cell) { return (uint32_t)cell * 0x01010101u; }
+RAGEN_HD int step_of(int W, int a) { return a == 0 ? -W : a == 1 ? W : a == 2 ? -1 : 1; }  // utils.py:588-593
+
+// bit a set: moving the player in direction a from p is not blocked by a wall or a box.  Walls come as one nibble per cell
+// (bit a: the neighbour in direction a is not a wall), boxes by comparing the packed cells with each neighbour.
+RAGEN_HD unsigned open_children(const Fast& m, int W, int p, uint32_t boxes, uint32_t nbmask) {
+  unsigned open = (m.wall[(p >> 3) * m.wall_stride] >> ((p & 7) << 2)) & 15u;
+  if (eq4(boxes, bcast4(p - W)) & nbmask) open &= ~1u;
+  if (eq4(boxes, bcast4(p + W)) & nbmask) open &= ~2u;
+  if (eq4(boxes, bcast4(p - 1)) & nbmask) open &= ~4u;
+  if (eq4(boxes, bcast4(p + 1)) & nbmask) open &= ~8u;
+  return open;
+}
+
+#define RAGEN_CSWAP(a, b)          \
+  {                                \
+    const uint32_t lo_ = a < b ? a : b; \
+    b = a < b ? b : a;             \
+    a = lo_;                       \
+  }
+// node_key of the packed node: (interior(box) << 1 | pulled) fields sorted ascending (network of <= 5 exchanges)
+template <int NB, typename KeyT>
+RAGEN_HD KeyT node_key_fast(const Fast& m, int cell_bits, int p, uint32_t boxes, unsigned pulled) {
+  uint32_t f0 = ((uint32_t)m.interior[boxes & 0xffu] << 1) | (pulled & 1u), f1 = 0, f2 = 0, f3 = 0;
+  if (NB > 1) f1 = ((uint32_t)m.interior[(boxes >> 8) & 0xffu] << 1) | ((pulled >> 1) & 1u);
+  if (NB > 2) f2 = ((uint32_t)m.interior[(boxes >> 16) & 0xffu] << 1) | ((pulled >> 2) & 1u);
+  if (NB > 3) f3 = ((uint32_t)m.interior[(boxes >> 24) & 0xffu] << 1) | ((pulled >> 3) & 1u);
+  if (NB == 2) RAGEN_CSWAP(f0, f1)
+  if (NB == 3) {
+    RAGEN_CSWAP(f0, f1)
+    RAGEN_CSWAP(f1, f2)
+    RAGEN_CSWAP(f0, f1)
+  }
+  if (NB == 4) {
+    RAGEN_CSWAP(f0, f1)
+    RAGEN_CSWAP(f2, f3)
+    RAGEN_CSWAP(f0, f2)
+    RAGEN_CSWAP(f1, f3)
+    RAGEN_CSWAP(f1, f2)
+  }
+  const int fb = cell_bits + 1;
+  KeyT key = (KeyT)m.interior[p] | ((KeyT)f0 << cell_bits);
+  if (NB > 1) key |= (KeyT)f1 << (cell_bits + fb);
+  if (NB > 2) key |= (KeyT)f2 << (cell_bits + 2 * fb);
+  if (NB > 3) key |= (KeyT)f3 << (cell_bits + 3 * fb);
+  return key;
+}
+#undef RAGEN_CSWAP
+
+// targets as the search wants them: (row, col) and the broadcast cell of each, fixed for the whole search
+template <int NB>
+struct TargetInfo {
+  uint32_t packed;
+  uint16_t rc[NB];
+};
+
+// box_swaps * box_displacement_score of a node, 0 unless every target is uncovered (utils.py:466-468); *disp_out = the
+// displacement term
+template <int NB>
+RAGEN_HD int node_score(const Fast& m, const TargetInfo<NB>& tg, uint32_t nbmask, int p, uint32_t boxes, int swaps, int* disp_out) {
+  int disp = 0;
+  bool any_covered = false;
+#pragma unroll
+  for (int k = 0; k < NB; ++k) {
+    const int b = (boxes >> (8 * k)) & 0xffu, t = (tg.packed >> (8 * k)) & 0xffu;
+    const int rb = m.rc[b], rt = tg.rc[k];
+    const int dr = (rb >> 8) - (rt >> 8), dc = (rb & 0xff) - (rt & 0xff);
+    disp += (dr < 0 ? -dr : dr) + (dc < 0 ? -dc : dc);
+    any_covered |= (t == p) || (eq4(boxes, bcast4(t)) & nbmask);
+  }
+  *disp_out = disp;
+  return any_covered ? 0 : swaps * disp;
+}
+
+// Bitmap probe through a one-entry register cache of the 64-bit word last touched.  Bits 0..5 of a key are the player's
+// interior index (cell_bits >= 6) or all of it, so walking the player around one arrangement of boxes stays in one word and
+// only a pull (or a return across one) costs a load; every new bit is written through at once.
+struct Granule {
+  uint32_t idx;
+  uint64_t val;
+};
+RAGEN_HD bool probe_bitmap(Visited& v, Granule& c, uint32_t key) {
+  const uint32_t gi = key >> 6;
+  const uint64_t bit = 1ull << (key & 63u);
+  if (gi != c.idx) {
+    c.val = v.mem64[gi];
+    c.idx = gi;
+  }
+  if (c.val & bit) return true;
+  c.val |= bit;
+  v.mem64[gi] = c.val;
+  return false;
+}
+
+// `active` false: the caller only takes part in the warp-wide loop (device) and nothing is touched.
+// BITMAP: the visited set is the bitmap (keys < 2^24, 32-bit arithmetic) instead of the hash table (64-bit keys).
+template <int NB, bool BITMAP>
+RAGEN_HD int reverse_play_nb(const Geometry& g, const Fast& m, uint32_t targets, int player, int search_depth, Visited& vis,
+                             BestFast& best, bool active) {
+  const uint32_t nbmask = NB >= 4 ? 0xffffffffu : ((1u << (8 * (NB & 3))) - 1u);
+  const int W = g.W, cell_bits = g.cell_bits;
+  int p = player, last = -1, swaps = 0, depth = -1, explored = 0;
+  uint32_t boxes = targets | ~nbmask;  // unused bytes 0xff: the far corner of a 16x16 grid at most, a wall
+  unsigned pulled = 0, open = 0;
+  Granule gran{0xffffffffu, 0ull};
+  TargetInfo<NB> tg;
+  tg.packed = targets;
+  if (active) {
+#pragma unroll
+    for (int k = 0; k < NB; ++k) tg.rc[k] = m.rc[(targets >> (8 * k)) & 0xffu];
+    best.score = -1;
+    best.p = player;
+    best.disp = 0;
+    best.boxes = boxes;
+  }
+  // the root, entered the way depth_first_search enters any node; a node at stack depth d runs with
+  // ttl = search_depth - 1 - d and its children are entered only while that stays positive (:455)
+  if (active && search_depth - 1 > 0) {
+    if (BITMAP)
+      probe_bitmap(vis, gran, node_key_fast<NB, uint32_t>(m, cell_bits, p, boxes, pulled));
+    else
+      visited_test_and_set(vis, node_key_fast<NB, uint64_t>(m, cell_bits, p, boxes, pulled));
+    explored = 1;
+    int disp;
+    const int score = node_score<NB>(m, tg, nbmask, p, boxes, swaps, &disp);
+    if (score > best.score) {
+      best.score = score;
+      best.p = p;
+      best.disp = disp;
+      best.boxes = boxes;
+    }
+    depth = 0;
+    open = (search_depth - 2 > 0) ? open_children(m, W, p, boxes, nbmask) : 0u;
+  }
+#ifdef __CUDA_ARCH__
+  // every lane of the warp is here: the vote is also the point where the lanes meet again after each iteration
+  while (__any_sync(0xffffffffu, depth >= 0)) {
+#else
+  while (depth >= 0) {
+#endif
+    // an iteration = return one level if this node has no child left, then try one child of the node now current
+    if (depth >= 0 && open == 0) {
+      if (depth == 0) {
+        depth = -1;
+      } else {
+        const unsigned code = m.stack[(size_t)depth * m.stack_stride];
+        const int a = code & 3, combo = code >> 3;
+        const int k = combo / 5 - 1, prev_last = combo % 5 - 1;
+        const int st = step_of(W, a);
+        const int parent = p - st;
+        if (k >= 0) {
+          boxes = (boxes & ~(0xffu << (8 * k))) | ((uint32_t)(parent - st) << (8 * k));
+          if (code & 4u) pulled &= ~(1u << k);
+          if (k != prev_last) --swaps;
+        }
+        last = prev_last;
+        p = parent;
+        --depth;
+        open = open_children(m, W, p, boxes, nbmask) & ~((2u << a) - 1u);
+      }
+    }
+    if (depth >= 0 && open != 0) {
+      const int a = lowest_bit(open);
+      open &= open - 1;
+      if (explored < MAX_EXPLORED) {
+        const int st = step_of(W, a);
+        const int n = p + st, behind = p - st;
+        const uint32_t mb = eq4(boxes, bcast4(behind)) & nbmask;
+        uint32_t cboxes = boxes;
+        unsigned cpulled = pulled, newbit = 0;
+        int clast = last, cswaps = swaps, k = -1;
+        if (mb) {  // pull that box onto the cell the player leaves (reverse_move :525-540)
+          k = lowest_byte(mb);
+          cboxes = (boxes & ~(0xffu << (8 * k))) | ((uint32_t)p << (8 * k));
+          newbit = ((pulled >> k) & 1u) ^ 1u;
+          cpulled |= 1u << k;
+          if (last != k) ++cswaps;
+          clast = k;
+        }
+        const bool seen = BITMAP ? probe_bitmap(vis, gran, node_key_fast<NB, uint32_t>(m, cell_bits, n, cboxes, cpulled))
+                                 : visited_test_and_set(vis, node_key_fast<NB, uint64_t>(m, cell_bits, n, cboxes, cpulled));
+        if (!seen) {
+          ++explored;
+          int disp;
+          const int score = node_score<NB>(m, tg, nbmask, n, cboxes, cswaps, &disp);
+          if (score > best.score) {
+            best.score = score;
+            best.p = n;
+            best.disp = disp;
+            best.boxes = cboxes;
+          }
+          ++depth;
+          m.stack[(size_t)depth * m.stack_stride] =
+              (uint8_t)((unsigned)a | (newbit << 2) | ((unsigned)((k + 1) * 5 + (last + 1)) << 3));
+          p = n;
+          boxes = cboxes;
+          pulled = cpulled;
+          last = clast;
+          swaps = cswaps;
+          open = (search_depth - 1 - (depth + 1) > 0) ? open_children(m, W, p, boxes, nbmask) : 0u;
+        }
+      }
+    }
+  }
+  return explored;
+}
+
+RAGEN_HD int reverse_play_fast(const Geometry& g, const Fast& m, uint32_t targets, int player, int search_depth, Visited& vis,
+                               BestFast& best, bool active = true) {
+  // every lane of a warp takes the same case (nb and the kind of visited set are launch-wide)
+  if (vis.mode == 0) {
+    switch (g.nb) {
+      case 1: return reverse_play_nb<1, true>(g, m, targets, player, search_depth, vis, best, active);
+      case 2: return reverse_play_nb<2, true>(g, m, targets, player, search_depth, vis, best, active);
+      case 3: return reverse_play_nb<3, true>(g, m, targets, player, search_depth, vis, best, active);
+      default: return reverse_play_nb<4, true>(g, m, targets, player, search_depth, vis, best, active);
+    }
+  }
+  switch (g.nb) {
+    case 1: return reverse_play_nb<1, false>(g, m, targets, player, search_depth, vis, best, active);
+    case 2: return reverse_play_nb<2, false>(g, m, targets, player, search_depth, vis, best, active);
+    case 3: return reverse_play_nb<3, false>(g, m, targets, player, search_depth, vis, best, active);
+    default: return reverse_play_nb<4, false>(g, m, targets, player, search_depth, vis, best, active);
+  }
+}
+
 // ---- add_random_player_movement (utils.py:152-213) ------------------------------------------------------------------
 RAGEN_HD int jitter(mt::State& py, const Geometry& g, const uint8_t* structure, uint8_t* state, int player, double p_move) {
   if (mt::py_random(py) > p_move) return player;
@@ -280,7 +549,7 @@ struct Work {
 RAGEN_HD int generate_room(const Geometry& g, int search_depth, int num_gen_steps, uint64_t seed, Work& w, uint8_t* fixed,
                            uint8_t* state, int* explored_out) {
   const int HW = g.H * g.W;
-  mt::State py{w.mt_py, 0}, np{w.mt_np, 0};
+  mt::State py{w.mt_py, 0, 1}, np{w.mt_np, 0, 1};
   mt::seed_python(py, seed);
   mt::seed_numpy(np, (uint32_t)seed);
   uint8_t* floor = w.scratch;
@@ -306,5 +575,78 @@ RAGEN_HD int generate_room(const Geometry& g, int search_depth, int num_gen_step
   jitter(py, g, fixed, state, best.p, best.disp == 1 ? 0.8 : 0.5);
   return OK;
 }
+
+// ---- pieces of generate_room for callers that run the search with reverse_play_fast ----------------------------------
+RAGEN_HD void fill_tables(const Geometry& g, uint8_t* interior_tab, uint16_t* rc_tab) {
+  for (int cell = 0; cell < g.H * g.W; ++cell) {
+    const int r = cell / g.W, c = cell - r * g.W;
+    interior_tab[cell] = (uint8_t)((r - 1) * (g.W - 2) + (c - 1));
+    rc_tab[cell] = (uint16_t)((r << 8) | c);
+  }
+}
+RAGEN_HD void fill_walls(const Geometry& g, const uint8_t* structure, uint32_t* wall, int stride) {
+  const int HW = g.H * g.W, W = g.W;
+  for (int w = 0; w * 8 < HW; ++w) {
+    uint32_t bits = 0;
+    for (int b = 0; b < 8 && w * 8 + b < HW; ++b) {
+      const int cell = w * 8 + b;
+      unsigned nib = 0;  // directions up, down, left, right (utils.py:588-593); off-grid neighbours count as walls
+      if (cell - W >= 0 && structure[cell - W] != 0) nib |= 1u;
+      if (cell + W < HW && structure[cell + W] != 0) nib |= 2u;
+      if (cell - 1 >= 0 && structure[cell - 1] != 0) nib |= 4u;
+      if (cell + 1 < HW && structure[cell + 1] != 0) nib |= 8u;
+      bits |= nib << (4 * b);
+    }
+    wall[w * stride] = bits;
+  }
+}
+RAGEN_HD uint32_t pack_cells(const uint8_t* cells, int nb) {
+  uint32_t v = 0;
+  for (int k = 0; k < nb; ++k) v |= (uint32_t)cells[k] << (8 * k);
+  return v;
+}
+// room_state from the best node (:257-259) + add_random_player_movement
+RAGEN_HD void finish_room(mt::State& py, const Geometry& g, const uint8_t* fixed, uint8_t* state, const BestFast& best) {
+  const int HW = g.H * g.W;
+  for (int i = 0; i < HW; ++i) state[i] = fixed[i];
+  for (int k = 0; k < g.nb; ++k) state[(best.boxes >> (8 * k)) & 0xffu] = 4;  // pulled boxes (3) become plain boxes
+  state[best.p] = 5;
+  jitter(py, g, fixed, state, best.p, best.disp == 1 ? 0.8 : 0.5);
+}
+
+#ifndef __CUDACC__
+// generate_room with the fast search, as the CUDA kernel composes it (host build only: the cross-check of the two searches)
+inline int generate_room_fast(const Geometry& g, int search_depth, int num_gen_steps, uint64_t seed, Work& w, uint8_t* fixed,
+                              uint8_t* state, int* explored_out) {
+  mt::State py{w.mt_py, 0, 1}, np{w.mt_np, 0, 1};
+  mt::seed_python(py, seed);
+  mt::seed_numpy(np, (uint32_t)seed);
+  uint8_t interior_tab[MAX_CELLS];
+  uint16_t rc_tab[MAX_CELLS];
+  uint32_t wall[MAX_CELLS / 8];
+  fill_tables(g, interior_tab, rc_tab);
+  Fast m{interior_tab, rc_tab, wall, 1, reinterpret_cast<uint8_t*>(w.stack), 1};
+  uint8_t* floor = w.scratch;
+  uint8_t targets[MAX_BOXES];
+  BestFast best;
+  best.disp = 0;
+  int player = 0, explored = 0;
+  for (int t = 0; t < 4; ++t) {
+    topology(py, g, num_gen_steps, 0.35, floor);
+    if (!place(np, g, floor, fixed, player, targets)) return NO_SPACE;
+    if (w.vis.mode == 0)
+      for (uint64_t i = 0; i < w.vis_words; ++i) w.vis.mem[i] = 0;
+    else
+      for (uint64_t i = 0; i < w.vis_words; ++i) w.vis.mem64[i] = 0;
+    fill_walls(g, fixed, wall, 1);
+    explored = reverse_play_fast(g, m, pack_cells(targets, g.nb), player, search_depth, w.vis, best);
+    if (best.disp > 0) break;
+  }
+  if (explored_out) *explored_out = explored;
+  if (best.disp == 0) return SCORE_ZERO;
+  finish_room(py, g, fixed, state, best);
+  return OK;
+}
+#endif
 
 }  // namespace sgen

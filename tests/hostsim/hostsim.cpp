@@ -147,7 +147,7 @@ int hs_countdown(const uint8_t* s, int n, const int32_t* nums, int n_nums, long 
 // out_f[0..k): random.random(); out_u[0..k): random._randbelow(n); out_np[0..k): np.random.randint(n) after seed(seed)
 void hs_mt(uint64_t seed, uint32_t n, int k, double* out_f, uint32_t* out_u, uint32_t* out_np) {
   uint32_t a[mt::N], b[mt::N];
-  mt::State py{a, 0}, np{b, 0};
+  mt::State py{a, 0, 1}, np{b, 0, 1};
   mt::seed_python(py, seed);
   mt::seed_numpy(np, (uint32_t)seed);
   for (int i = 0; i < k; ++i) out_f[i] = mt::py_random(py);
@@ -156,8 +156,11 @@ void hs_mt(uint64_t seed, uint32_t n, int k, double* out_f, uint32_t* out_u, uin
 }
 
 // ---- Sokoban generator -------------------------------------------------------------------------------------------
+// force_hash bit 0: hash-table visited set instead of the bitmap; bit 1: reverse_play_fast instead of reverse_play
 int hs_sokoban_generate(int H, int W, int nb, int search_depth, int num_gen_steps, uint64_t seed, int force_hash,
                         uint8_t* fixed, uint8_t* state, int* explored) {
+  const bool fast = force_hash & 2;
+  force_hash &= 1;
   sgen::Geometry g{H, W, nb, 0};
   int cells = (H - 2) * (W - 2);
   while ((1 << g.cell_bits) < cells) ++g.cell_bits;
@@ -171,8 +174,8 @@ int hs_sokoban_generate(int H, int W, int nb, int search_depth, int num_gen_step
   if (kb <= 26 && !force_hash) {
     w.vis.mode = 0;
     w.vis_words = ((uint64_t)1 << kb) / 32 + 1;
-    w.vis.mem = (uint32_t*)malloc(w.vis_words * 4);
-    w.vis.mem64 = nullptr;
+    w.vis.mem = (uint32_t*)malloc(w.vis_words * 4 + 8);
+    w.vis.mem64 = (uint64_t*)w.vis.mem;  // the fast search probes the bitmap 64 bits at a time
   } else {
     w.vis.mode = 1;
     w.vis_words = (uint64_t)1 << 20;
@@ -180,11 +183,11 @@ int hs_sokoban_generate(int H, int W, int nb, int search_depth, int num_gen_step
     w.vis.mem64 = (uint64_t*)malloc(w.vis_words * 8);
     w.vis.mem = nullptr;
   }
-  const int st = sgen::generate_room(g, search_depth, num_gen_steps, seed, w, fixed, state, explored);
+  const int st = fast ? sgen::generate_room_fast(g, search_depth, num_gen_steps, seed, w, fixed, state, explored)
+                      : sgen::generate_room(g, search_depth, num_gen_steps, seed, w, fixed, state, explored);
   free(w.stack);
   free(w.scratch);
-  free(w.vis.mem);
-  free(w.vis.mem64);
+  free(w.vis.mode == 0 ? (void*)w.vis.mem : (void*)w.vis.mem64);
   return st;
 }
 

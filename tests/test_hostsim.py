@@ -298,13 +298,27 @@ def test_sokoban_generator_reproduces_reference_rooms(hs, name):
     if name == "s10":
         seeds = seeds[:4]  # ~0.1-0.3 s each on the host
     for j, seed in enumerate(seeds):
-        st, fixed, state, explored = _gen(hs, H, W, nb, depth, seed, force_hash=j % 2 if name != "s10" else 0)
+        st, fixed, state, explored = _gen(hs, H, W, nb, depth, seed, force_hash=(j % 2 if name != "s10" else 0) | (2 if j % 3 else 0))
         if not rooms[f"{name}_ok"][j]:
             assert st != 0, (name, seed)
             continue
         assert st == 0, (name, seed, st)
         assert np.array_equal(fixed, rooms[f"{name}_fixed"][j]), (name, seed)
         assert np.array_equal(state, rooms[f"{name}_state"][j]), (name, seed)
+
+
+@pytest.mark.parametrize("H,W,nb,depth,n_seeds", [(6, 6, 1, 300, 60), (6, 6, 3, 300, 40), (8, 8, 2, 10, 60), (8, 8, 2, 300, 12),
+                                                  (7, 9, 3, 40, 30), (10, 10, 2, 300, 4), (10, 10, 4, 25, 20), (6, 6, 1, 1, 5),
+                                                  (6, 6, 1, 2, 5), (6, 6, 2, 3, 10), (16, 16, 4, 12, 6)])
+def test_fast_search_equals_plain_search(hs, H, W, nb, depth, n_seeds):
+    """reverse_play_fast (the search the CUDA kernel runs: node in registers, one-byte undo records) against reverse_play (the
+    plain restatement with copied frames): same status, same rooms, same number of explored states, bitmap and hash sets."""
+    for seed in range(1000, 1000 + n_seeds):
+        for force_hash in (0, 1):
+            a = _gen(hs, H, W, nb, depth, seed, force_hash=force_hash)
+            b = _gen(hs, H, W, nb, depth, seed, force_hash=force_hash | 2)
+            assert a[0] == b[0] and a[3] == b[3], (seed, a[0], b[0], a[3], b[3])
+            assert np.array_equal(a[1], b[1]) and np.array_equal(a[2], b[2]), seed
 
 
 # ---- text-env answer scoring (score_logic.cuh) ---------------------------------------------------------------------------

@@ -129,6 +129,79 @@ __device__ __forceinline__ void render_tile(const uint8_t* s_state, uint8_t* s_o
   }
 }
 
+// Thread-per-env packed render for the compile-time room shapes (rooms that are whole 32-bit words: 6x6, 8x8, 10x10).
+// The thread that stepped env e turns ITS room into the env's G/2 packed bytes with every index known at compile time:
+//   1. the room's words -> a stream of cell nibbles (two shifts-and-ors and one byte permute per 8 cells);
+//   2. output word k (8 codes) = for each of the <= 2 rows it touches, a funnel-shifted window of the cell stream under a
+//      constant mask, or-ed with a constant holding the separators (code 7) - row r's cells sit r nibbles further along in
+//      the output than in the cell stream;
+//   3. the env's bytes start at e*G/2 in the tile, which is word-aligned only for every fourth env (55 or 21 bytes per env), so
+//      the stream is funnel-shifted by (e*G/2)&3 bytes and the interior words are stored whole, the first and last as bytes.
+// ~5x fewer instructions per env than the cooperative word loop below (which recomputes row/column/alignment per word).
+template <int CH, int CW>
+__device__ __forceinline__ void render_env_packed(const uint8_t* s_state, uint8_t* s_obs, int e) {
+  constexpr int HW = CH * CW, RW = CW + 1, G = CH * RW;
+  constexpr int B = G / 2;           // packed bytes per env
+  constexpr int NW = HW / 4;         // room words per env
+  constexpr int NCW = (HW + 7) / 8;  // words of the cell-nibble stream
+  constexpr int NOW = (G + 7) / 8;   // words of the output stream before the alignment shift
+  static_assert(HW % 4 == 0 && G % 2 == 0 && RW >= 7, "shape not supported by the per-env render");
+  const uint32_t* sw = reinterpret_cast<const uint32_t*>(s_state) + e * NW;
+  uint32_t cw[NCW + 1];
+#pragma unroll
+  for (int j = 0; j < NCW; ++j) {
+    const uint32_t x0 = sw[2 * j];
+    const uint32_t x1 = (2 * j + 1 < NW) ? sw[2 * j + 1] : 0u;
+    cw[j] = __byte_perm(x0 | (x0 >> 4), x1 | (x1 >> 4), 0x6420);
+  }
+  cw[NCW] = 0u;
+  uint32_t out[NOW];
+#pragma unroll
+  for (int k = 0; k < NOW; ++k) {
+    uint32_t acc = 0u;
+#pragma unroll
+    for (int q = 0; q < 8; ++q)  // separators of this word (constant-folded)
+      if (8 * k + q < G && (8 * k + q) % RW == CW) acc |= 7u << (4 * q);
+    const int r0 = (8 * k) / RW;
+#pragma unroll
+    for (int dr = 0; dr < 3; ++dr) {
+      const int r = r0 + dr;
+      const int lo = (8 * k > r * RW) ? 8 * k : r * RW;                       // output nibbles of row r's cells ...
+      const int hi = (8 * k + 8 < r * RW + CW) ? 8 * k + 8 : r * RW + CW;    // ... that fall into word k
+      if (r < CH && lo < hi) {
+        const int s = 8 * k - r;  // cell nibble under output nibble 8k
+        uint32_t win;
+        if (s < 0) win = cw[0] << (4 * (-s));
+        else if ((s & 7) == 0) win = cw[s >> 3];
+        else win = __funnelshift_r(cw[s >> 3], cw[(s >> 3) + 1], 4 * (s & 7));
+        const uint32_t ones = (hi - lo == 8) ? 0xffffffffu : (((1u << (4 * (hi - lo))) - 1u) << (4 * (lo - 8 * k)));
+        acc |= win & ones;
+      }
+    }
+    out[k] = acc;
+  }
+  constexpr bool ALIGNED = (B % 4 == 0);
+  const int a = ALIGNED ? 0 : ((e * B) & 3);
+  uint8_t* dst = s_obs + e * B - a;  // word-aligned; this env owns bytes [a, a + B) from here
+  uint32_t prev = 0u;
+#pragma unroll
+  for (int k = 0; k <= NOW; ++k) {
+    if (4 * k >= B + 3) break;
+    const uint32_t cur = (k < NOW) ? out[k] : 0u;
+    const uint32_t w = ALIGNED ? cur : __funnelshift_l(prev, cur, a << 3);
+    prev = cur;
+    if ((ALIGNED || k >= 1) && 4 * k + 4 <= B) {
+      *reinterpret_cast<uint32_t*>(dst + 4 * k) = w;  // whole word inside [a, a + B) for every a
+    } else {
+#pragma unroll
+      for (int b = 0; b < 4; ++b) {
+        const int at = 4 * k + b;
+        if (at >= a && at < a + B) dst[at] = (uint8_t)(w >> (8 * b));
+      }
+    }
+  }
+}
+
 template <int CH, int CW, bool RENDER_ONLY, bool PACKED>
 __global__ void __launch_bounds__(TE) sokoban_tile_kernel(const StepParams p) {
   const int H = CH ? CH : p.H, W = CW ? CW : p.W;
@@ -243,6 +316,17 @@ __global__ void __launch_bounds__(TE) sokoban_tile_kernel(const StepParams p) {
     p.flags[g] = (uint8_t)fl;
     p.n_executed[g] = (uint8_t)nexec;
   }
+  // rooms of the compile-time shapes are rendered by the thread that owns them (render_env_packed), straight after its
+  // own step: no CTA-wide barrier between step and render, and the player-on-target patch touches only the owner's bytes
+  constexpr bool ENV_RENDER = PACKED && CH != 0 && CW != 0 && ((CH * CW) % 4 == 0) && ((CH * (CW + 1)) % 2 == 0) && CW >= 6;
+  if (ENV_RENDER && p.obs && mine) {
+    if constexpr (ENV_RENDER) render_env_packed<CH, CW>(s_state, s_obs, e);
+    if (under) {  // player standing on a target (env.py:55)
+      const int q = e * G + pos + pos / W;
+      const uint8_t old = s_obs[q >> 1];
+      s_obs[q >> 1] = (q & 1) ? (uint8_t)((old & 0x0f) | 0x60) : (uint8_t)((old & 0xf0) | 0x06);
+    }
+  }
   if (!RENDER_ONLY) {
     fence_async_smem();  // the stepped rooms are read by the bulk store below
     __syncthreads();
@@ -258,19 +342,23 @@ __global__ void __launch_bounds__(TE) sokoban_tile_kernel(const StepParams p) {
 
   // ---- render glyph rows, then shared memory -> HBM -----------------------------------------------
   if (p.obs) {
-    render_tile<CW, PACKED>(s_state, s_obs, obs_bytes, p.W);
-    __syncthreads();
-    if (mine && under) {  // player standing on a target (env.py:55)
-      const int q = e * G + pos + pos / W;
-      if (PACKED) {  // G is even, so no other env's thread touches this byte
-        const uint8_t old = s_obs[q >> 1];
-        s_obs[q >> 1] = (q & 1) ? (uint8_t)((old & 0x0f) | 0x60) : (uint8_t)((old & 0xf0) | 0x06);
-      } else {
-        s_obs[q] = 6;
+    if (!ENV_RENDER) {
+      render_tile<CW, PACKED>(s_state, s_obs, obs_bytes, p.W);
+      __syncthreads();
+      if (mine && under) {  // player standing on a target (env.py:55)
+        const int q = e * G + pos + pos / W;
+        if (PACKED) {  // G is even, so no other env's thread touches this byte
+          const uint8_t old = s_obs[q >> 1];
+          s_obs[q >> 1] = (q & 1) ? (uint8_t)((old & 0x0f) | 0x60) : (uint8_t)((old & 0xf0) | 0x06);
+        } else {
+          s_obs[q] = 6;
+        }
       }
     }
-    fence_async_smem();
-    __syncthreads();
+    if (!ENV_RENDER || RENDER_ONLY) {  // otherwise the barrier before the room store already covers the glyph tile
+      fence_async_smem();
+      __syncthreads();
+    }
     uint8_t* g_obs = p.obs + (PACKED ? (env0 * G) >> 1 : env0 * G);
     if (bulk_obs) {
       if (threadIdx.x == 0) {

@@ -146,6 +146,93 @@ __global__ void __launch_bounds__(TB) frozenlake_kernel(const FlParams p) {
   }
 }
 
+// ---- FrozenLake 4x4 (the reference's default size, C2): no tile staging ----------------------------------------
+// A 4x4 map is exactly one 16-byte vector per env, so the thread that owns the env loads it with ONE coalesced 128-bit
+// load and squeezes it to 2 bits per cell in a register; only the 20-byte glyph rows go through shared memory (five words
+// per env, an odd word stride: conflict-free) so that they leave as coalesced 128-bit stores.
+constexpr int TB4 = 256;
+
+__device__ __forceinline__ uint32_t squeeze4(uint32_t w) {  // 4 bytes (0..3 each) -> 8 bits, cell 0 in the low 2 bits
+  w &= 0x03030303u;
+  return (w | (w >> 6) | (w >> 12) | (w >> 18)) & 0xffu;
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(TB4) frozenlake4_kernel(const FlParams p) {
+  __shared__ __align__(16) uint32_t s_obs[TB4 * 5];
+  const int64_t env0 = (int64_t)blockIdx.x * TB4;
+  const int cnt = (int)min((int64_t)TB4, p.n - env0);
+  const int e = threadIdx.x;
+  const int64_t g = env0 + e;
+  const bool mine = e < cnt;
+  toy::Tiles tiles{0, 0};
+  int pos = 0;
+  if (mine) {
+    const uint4 t = ldg_stream(reinterpret_cast<const uint4*>(p.tiles) + g);
+    tiles.lo = (uint64_t)(squeeze4(t.x) | (squeeze4(t.y) << 8) | (squeeze4(t.z) << 16) | (squeeze4(t.w) << 24));
+    pos = p.pos[g];
+  }
+  if (MODE == FL_STEP && mine) {
+    int na = p.K;
+    if (p.n_actions) na = min((int)p.n_actions[g], p.K);
+    nprand::Pcg64 r = load_rng(p.rng, p.n, g);
+    double acc = 0.0;
+    int fl = 0, nexec = 0, dn = 0;
+    const uint8_t* act = p.actions + g * p.K;
+    for (int k = 0; k < na; ++k) {
+      const int a = act[k];
+      if (a < 1 || a > 4) break;
+      bool d, eff, suc;
+      const int rew = toy::fl_step(tiles, 4, pos, r, a, p.slippery != 0, d, eff, suc);
+      acc += (double)rew;
+      ++nexec;
+      fl = (eff ? 1 : 0) | (suc ? 2 : 0) | 4;
+      dn = d ? 1 : 0;
+      if (dn) break;
+    }
+    if (nexec) {
+      store_rng_state(p.rng, g, r);
+      p.pos[g] = (uint8_t)pos;
+    }
+    p.acc_reward[g] = acc;
+    p.done[g] = (uint8_t)dn;
+    p.flags[g] = (uint8_t)fl;
+    p.n_executed[g] = (uint8_t)nexec;
+  }
+  if (p.obs) {
+    if (mine) {
+      // fl_render with everything in registers: 2-bit tile -> glyph code (S drawn as F), the player's cell patched, a
+      // separator after every fourth code
+      const uint32_t t32 = (uint32_t)tiles.lo;
+      const uint32_t raw_here = (t32 >> (2 * pos)) & 3u;
+      const uint32_t pcode = (raw_here == 2u) ? 4u : (raw_here == 3u) ? 5u : 0u;
+      uint32_t row[4];
+#pragma unroll
+      for (int rr = 0; rr < 4; ++rr) {
+        uint32_t w = 0;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          const int i = rr * 4 + c;
+          uint32_t raw = (t32 >> (2 * i)) & 3u;
+          uint32_t code = raw ? raw : 1u;
+          code = (i == pos) ? pcode : code;
+          w |= code << (8 * c);
+        }
+        row[rr] = w;
+      }
+      // 20-byte stream r0 r0 r0 r0 7 r1 r1 r1 r1 7 ... as five little-endian words
+      uint32_t* o = s_obs + e * 5;
+      o[0] = row[0];
+      o[1] = 7u | (row[1] << 8);
+      o[2] = (row[1] >> 24) | (7u << 8) | (row[2] << 16);
+      o[3] = (row[2] >> 16) | (7u << 16) | (row[3] << 24);
+      o[4] = (row[3] >> 8) | (7u << 24);
+    }
+    __syncthreads();
+    tile_s2g(p.obs + env0 * 20, reinterpret_cast<const uint8_t*>(s_obs), cnt * 20);
+  }
+}
+
 // ---- Bandit --------------------------------------------------------------------------------------------------
 __global__ void bandit_reset_kernel(int64_t n, const uint64_t* __restrict__ seeds, uint64_t* rng, uint8_t* lo_first) {
   const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -186,6 +273,13 @@ size_t fl_smem(int size) { return (size_t)((TB * size * size + 15) & ~15) + (siz
 template <int MODE>
 int fl_launch(ragen_ctx* ctx, const FlParams& p, cudaStream_t stream) {
   DeviceGuard guard(ctx->device);
+  if constexpr (MODE != FL_RESET) {
+    if (p.size == 4 && ((uintptr_t)p.tiles & 15) == 0) {
+      frozenlake4_kernel<MODE><<<(unsigned)((p.n + TB4 - 1) / TB4), TB4, 0, stream>>>(p);
+      RAGEN_LAUNCHED(ctx);
+      return RAGEN_OK;
+    }
+  }
   frozenlake_kernel<MODE><<<(unsigned)((p.n + TB - 1) / TB), TB, fl_smem(p.size), stream>>>(p);
   RAGEN_LAUNCHED(ctx);
   return RAGEN_OK;

@@ -32,8 +32,9 @@ def peak_gbs():
     return float(json.load(open(p))["hbm_gbs"]) if os.path.exists(p) else 6650.0
 
 
-def dev_time(fn, reps=20, warm=3):
-    """median milliseconds of fn() by CUDA events on the current stream."""
+def dev_time(fn, reps=20, warm=3, inner=1):
+    """median milliseconds of fn() by CUDA events on the current stream.  inner > 1 times that many back-to-back calls per
+    event pair and divides (bandwidth-regime rows: a lone ~50 us launch otherwise carries ~10 us of launch/event gap)."""
     for _ in range(warm):
         fn()
     torch.cuda.synchronize()
@@ -41,10 +42,11 @@ def dev_time(fn, reps=20, warm=3):
     for _ in range(reps):
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record()
-        fn()
+        for _ in range(inner):
+            fn()
         b.record()
         torch.cuda.synchronize()
-        ts.append(a.elapsed_time(b))
+        ts.append(a.elapsed_time(b) / inner)
     return float(np.median(ts))
 
 
@@ -90,7 +92,7 @@ def rgb_rows(quick):
         def blit():
             _lib.check(b.lib.ragen_sokoban_render_rgb(b.ctx.handle, n, H, W, 16, _lib.ptr(b.state), _lib.ptr(b.meta),
                                                       _lib.ptr(b.atlas), None, 0, _lib.ptr(out), b.ctx.stream()))
-        ms = dev_time(blit, reps=30)
+        ms = dev_time(blit, reps=30, inner=8 if n > 1000 else 1)
         m = min(n, 64)
 
         def cpu():
@@ -127,7 +129,7 @@ def sokoban_rows(quick):
         def step():
             b.step(acts[i[0] % 4], packed=packed)
             i[0] += 1
-        ms = dev_time(step, reps=50 if n > 1000 else 200)
+        ms = dev_time(step, reps=50 if n > 1000 else 200, inner=8 if n > 1000 else 1)
         per_step = 3 * H * W + 1 + 10 + 8 + 1 + 1 + H * (W + 1)
         per_turn = per_step if K == 1 else (per_step - 1 + K)      # "(170+K)/K per env-step" variant: one render per turn
         # CPU port: the reference's per-env Python loop on a bounded sample
@@ -190,7 +192,7 @@ def frozenlake_rows(quick):
         def step():
             b.step(acts[i[0] % 4])
             i[0] += 1
-        ms = dev_time(step, reps=100)
+        ms = dev_time(step, reps=100, inner=8 if n > 1024 else 1)
         m = min(n, 1024)
         envs = [TE.FrozenLakeOracle() for _ in range(m)]
         for j, e in enumerate(envs):
@@ -237,6 +239,7 @@ def c5_rows(quick):
 
     rows = []
     for B, L, tag in [(128, 2048, "C5 B=128 L=2048"), (2048 if quick else 8192, 2048, "B=8192 L=2048 (bandwidth regime)")]:
+        INNER = 8 if B > 128 else 1  # B = 128 rows report the latency of one call, the bandwidth rows back-to-back launches
         rng = np.random.default_rng(5)
         ids = np.full((B, L), 151643, dtype=np.int64)
         scores = np.zeros((B, 5))
@@ -252,7 +255,7 @@ def c5_rows(quick):
             nt[b] = k
             scores[b, :k] = rng.integers(-2, 11, k) * 0.1
         d_ids, d_sc, d_nt = torch.from_numpy(ids).cuda(), torch.from_numpy(scores).cuda(), torch.from_numpy(nt).cuda()
-        ms = dev_time(lambda: ops.masks_scores(d_ids, d_sc, d_nt, 151644, 151645, False, True, True), reps=50)
+        ms = dev_time(lambda: ops.masks_scores(d_ids, d_sc, d_nt, 151644, 151645, False, True, True), reps=50, inner=INNER)
         t_ids = torch.from_numpy(ids[:128])
         sc_list = [scores[b, :nt[b]].tolist() for b in range(128)]
         cs = cpu_time(lambda: M.masks_and_scores(t_ids, sc_list, 151644, 151645), 2.0)
@@ -262,12 +265,12 @@ def c5_rows(quick):
         mask = lm.float()
         rewards = sc.clone()
         values = torch.randn(B, T, device="cuda") * mask
-        ms_raw = dev_time(lambda: ops.gae_raw(rewards, values, lm, 1.0, 1.0), reps=50)
+        ms_raw = dev_time(lambda: ops.gae_raw(rewards, values, lm, 1.0, 1.0), reps=50, inner=INNER)
 
         def full():
             adv, ret, mom = ops.gae_raw(rewards, values, lm, 1.0, 1.0)
             ops.whiten_(adv, mom, check=False)
-        ms_full = dev_time(full, reps=50)
+        ms_full = dev_time(full, reps=50, inner=INNER)
         r_c, v_c, m_c = rewards[:128].cpu(), values[:128].cpu(), mask[:128].cpu()
         cs = cpu_time(lambda: A.gae(r_c, v_c, m_c, 1.0, 1.0), 3.0)
         rows.append(line(f"GAE+whiten {tag}", "token", B * T, ms_full, 25, 128 * T / cs, "128 rows, torch CPU loop as the reference (all host threads)",
@@ -276,32 +279,32 @@ def c5_rows(quick):
         r2 = torch.zeros_like(rewards)
         last = (mask * torch.arange(1, T + 1, device="cuda")).argmax(dim=1)
         r2[torch.arange(B), last] = 1.0
-        ms_bi = dev_time(lambda: ops.bilevel_gae_raw(r2, values, lm, 1.0, 1.0, 0.95), reps=50)
+        ms_bi = dev_time(lambda: ops.bilevel_gae_raw(r2, values, lm, 1.0, 1.0, 0.95), reps=50, inner=INNER)
         r2c = r2[:16].cpu()
         cs = cpu_time(lambda: A.bilevel_gae(r2c, v_c[:16], m_c[:16], 1.0, 1.0, 0.95), 3.0)
         rows.append(line(f"bi-level GAE {tag}", "token", B * T, ms_bi, 17, 16 * T / cs, "16 rows, oracle/advantage.py loop as the reference", kernel="bilevel_gae_kernel"))
         gi = torch.arange(B, device="cuda", dtype=torch.int32) // 16
-        ms_g = dev_time(lambda: ops.grpo_outcome(rewards, lm, gi, B // 16), reps=50)
+        ms_g = dev_time(lambda: ops.grpo_outcome(rewards, lm, gi, B // 16), reps=50, inner=INNER)
         rows.append(line(f"GRPO {tag}", "token", B * T, ms_g, 9, None, None, kernel="grpo_scores_kernel + grpo_apply_kernel"))
-        ms_r = dev_time(lambda: ops.outcome_advantage(rewards, lm, gi, B // 16, "rloo"), reps=50)
+        ms_r = dev_time(lambda: ops.outcome_advantage(rewards, lm, gi, B // 16, "rloo"), reps=50, inner=INNER)
         rows.append(line(f"RLOO {tag}", "token", B * T, ms_r, 9, None, None, kernel="grpo_scores_kernel + outcome_apply_kernel"))
 
         def rfpp():
             ret, m8, mom = ops.discounted_returns(rewards, lm, 1.0)
             ops.whiten_masked(ret, m8, mom, check=False)
-        ms_p = dev_time(rfpp, reps=50)
+        ms_p = dev_time(rfpp, reps=50, inner=INNER)
         rows.append(line(f"REINFORCE++ {tag}", "token", B * T, ms_p, 4 + 1 + 4 + 4 + 1 + 4, None, None, kernel="returns_kernel<0> + whiten_masked_kernel"))
         base = torch.randn(B, device="cuda")
-        ms_x = dev_time(lambda: ops.remax(rewards, lm, base), reps=50)
+        ms_x = dev_time(lambda: ops.remax(rewards, lm, base), reps=50, inner=INNER)
         rows.append(line(f"ReMax {tag}", "token", B * T, ms_x, 4 + 1 + 4 + 4, None, None, kernel="returns_kernel<1>"))
         lp = -torch.rand(B, T, device="cuda")
         rf = lp + 0.1 * torch.randn(B, T, device="cuda")
-        ms_k = dev_time(lambda: ops.kl_rewards(rewards, lp, rf, lm, "low_var_kl", 0.05), reps=50)
+        ms_k = dev_time(lambda: ops.kl_rewards(rewards, lp, rf, lm, "low_var_kl", 0.05), reps=50, inner=INNER)
         rows.append(line(f"KL-in-reward {tag}", "token", B * T, ms_k, 4 * 3 + 1 + 4, None, None, kernel="kl_rewards_kernel"))
-        ms_f = dev_time(lambda: ops.group_filter_stats(sc, B // 16, 16), reps=50)
+        ms_f = dev_time(lambda: ops.group_filter_stats(sc, B // 16, 16), reps=50, inner=INNER)
         rows.append(line(f"rollout filter stats {tag}", "token", B * T, ms_f, 4, None, None, kernel="filter_stats_kernel"))
         pen = torch.zeros(B, device="cuda")
-        ms_n = dev_time(lambda: ops.group_norm(sc[:, -1], pen, gi, B // 16, "mean_std"), reps=50)
+        ms_n = dev_time(lambda: ops.group_norm(sc[:, -1], pen, gi, B // 16, "mean_std"), reps=50, inner=INNER)
         rows.append(line(f"group reward norm {tag}", "row", B, ms_n, 16, None, None, kernel="norm_stats_kernel + norm_apply_kernel"))
     return rows
 

@@ -12,6 +12,8 @@
 // whitening moments are reduced in a different order, in fp64), and all lanes write the chunk back coalesced while
 // accumulating the masked moments, which are reduced with warp shuffles and one fp64 atomic per warp.
 // Rows are independent, so the recurrence latency is hidden across warps; the pass is HBM-bound (17 B per token).
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace {
@@ -553,6 +555,257 @@ __global__ void group_stats_kernel(int n_groups, int group_size, const float* __
   gstd[g] = group_size > 1 ? (float)sqrt(fmax((s2 - n * mu * mu) / (n - 1.0), 0.0)) : NAN;  // torch.std of one value is NaN
 }
 
+
+// ---- many rows (B >= 4096): a CTA of two warps per group of 8 rows, ONE LANE PER ROW in the recurrence ---------------------
+// The one-CTA-per-row kernels above put a row's serial recurrence on one lane of one warp: ~5 warp-instructions per token with
+// 1/32 of the lanes working, which at B = 8192 rows is ~80 M warp-instructions - more issue slots than the HBM time of the
+// pass (192 us measured).  Here a row group's "scan" warp runs the recurrences of its 8 rows side by side, one lane per row,
+// in the same fp32 (or double, ReMax) order.  Rows are T floats apart in HBM, so the group is read as 32-token tiles, one
+// coalesced 128-byte row segment per request, staged by 4-byte cp.async into a 4-deep ring of shared-memory tiles by the
+// group's "mover" warp, which also writes the finished tile back (coalesced) and accumulates the masked moments; one CTA
+// barrier per tile hands tiles between the two.  Tile rows are 33 floats apart so the lane-per-row column walk is bank-conflict
+// free.  Mask rows start at arbitrary byte addresses (T is odd at C5): the 32 bytes of a tile row are fetched as the 9 aligned
+// words that cover them.  Tiles run right to left, the carries (recurrence state, V_{t+1}) stay in the lane's registers.
+// Results equal the per-row kernels bit for bit (tests/test_gpu_advantage_ctx.py).  Measured at 8192 x 2047: GAE 192 -> 102 us,
+// REINFORCE++ 324 -> 89 us; the pass is still bound by instruction latency per tile step (~2.4 instructions per token), not HBM.
+constexpr int TS_STAGES = 4;
+constexpr int TS_VS = 33;  // floats between tile rows
+constexpr int TS_MS = 40;  // bytes between mask tile rows (32 + 3 bytes of misalignment, rounded up to words)
+template <int RPW>  // rows per warp
+struct TsStage {
+  float v[RPW * TS_VS];
+  float r[RPW * TS_VS];
+  uint8_t m[RPW * TS_MS];
+};
+enum { TS_GAE = 0, TS_RFPP = 1, TS_REMAX = 2 };
+
+__device__ __forceinline__ void cp_async4(void* smem_dst, const void* gmem_src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(smem_dst)), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+template <int MODE, int RPW>
+__global__ void __launch_bounds__(64) tile_scan_kernel(int B, int T, const float* __restrict__ rewards,
+                                                       const float* __restrict__ values, const uint8_t* __restrict__ mask,
+                                                       float gamma, float gl, const float* __restrict__ baselines,
+                                                       float* __restrict__ adv, float* __restrict__ ret, double* moments) {
+  extern __shared__ __align__(16) uint8_t ts_smem[];
+  using Stage = TsStage<RPW>;
+  Stage* st = reinterpret_cast<Stage*>(ts_smem);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int row0 = blockIdx.x * RPW;
+  const int nrows = min(RPW, B - row0);
+  const int ntiles = (T + 31) >> 5;
+  const uintptr_t mask_end = (uintptr_t)(mask + (size_t)B * T);
+
+  // Two warps share a row group.  Step i (tile ntiles-1-i, ring slot i & 3):
+  //   warp 0 ("scan")  runs the recurrences of tile i, lane = row;
+  //   warp 1 ("mover") waits for tile i+1's cp.async group, writes tile i-1's results to HBM (lane = token, coalesced row
+  //                    segments) with the masked moments, then refills that slot with tile i+3;
+  // and one CTA barrier per step hands tile i to the mover and tile i+1 to the scan warp.  A warp here is usually alone on
+  // its scheduler, so each phase is "a batch of independent loads, the arithmetic, the stores": nothing else hides latency.
+  auto issue = [&](int tile, int s) {
+    const int t0 = tile << 5;
+    const bool tok = t0 + lane < T;
+    Stage& S = st[s];
+    const size_t first = (size_t)row0 * T + t0;
+    const float* vp = values + first + lane;
+    const float* rp = rewards + first + lane;
+    const uint8_t* mp = mask + first;
+#pragma unroll 8
+    for (int r = 0; r < nrows; ++r) {
+      if (tok) {
+        if (MODE == TS_GAE) cp_async4(&S.v[r * TS_VS + lane], vp);
+        cp_async4(&S.r[r * TS_VS + lane], rp);
+      }
+      if (lane < 9) {
+        const uintptr_t w = (((uintptr_t)mp) & ~(uintptr_t)3) + 4u * lane;
+        if (w < mask_end) cp_async4(&S.m[r * TS_MS + 4 * lane], reinterpret_cast<const void*>(w));
+      }
+      vp += T;
+      rp += T;
+      mp += T;
+    }
+  };
+
+  double m1 = 0.0, m2 = 0.0;  // mover
+  int n_masked = 0;           // mover: warp-uniform count of mask tokens (popcounts of ballots)
+  auto store = [&](int tile, int s) {
+    const int t0 = tile << 5;
+    const int cnt = min(32, T - t0);
+    Stage& S = st[s];
+    const bool tok = lane < cnt;
+    const size_t first = (size_t)row0 * T + t0;
+    float* ap = adv + first + lane;
+    float* tp = ret + first + lane;
+    const uint8_t* mp = mask + first;
+#pragma unroll
+    for (int r0 = 0; r0 < RPW; r0 += 8) {
+      if (r0 < nrows) {  // warp-uniform
+        float a[8], b[8];
+        uint8_t mk[8];
+        const uint32_t mp_lo = (uint32_t)(uintptr_t)mp;  // only the low two bits of a mask row's address matter
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const int r = r0 + k;  // rows past nrows read stale shared memory and are never stored
+          a[k] = S.r[r * TS_VS + lane];
+          if (MODE != TS_RFPP) b[k] = S.v[r * TS_VS + lane];
+          if (MODE != TS_REMAX) mk[k] = S.m[r * TS_MS + (int)((mp_lo + (uint32_t)(k * T)) & 3u) + lane];
+        }
+        auto put = [&](int k) {
+          if (MODE == TS_GAE) {
+            ap[(size_t)k * T] = a[k];
+            tp[(size_t)k * T] = b[k];
+          } else if (MODE == TS_RFPP) {
+            tp[(size_t)k * T] = a[k];
+          } else {
+            tp[(size_t)k * T] = a[k];
+            ap[(size_t)k * T] = b[k];
+          }
+        };
+        if ((cnt == 32) && (r0 + 8 <= nrows)) {  // warp-uniform: the common case stores without per-row branches
+#pragma unroll
+          for (int k = 0; k < 8; ++k) put(k);
+        } else {
+#pragma unroll
+          for (int k = 0; k < 8; ++k)
+            if (tok && (r0 + k < nrows)) put(k);
+        }
+        if (MODE != TS_REMAX) {
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            const bool in = tok && (r0 + k < nrows) && mk[k] != 0;
+            n_masked += __popc(__ballot_sync(0xffffffffu, in));
+            const double am = (double)(in ? a[k] : 0.0f);  // select in fp32, convert unconditionally: no branch per row
+            m1 += am;
+            m2 = fma(am, am, m2);
+          }
+        }
+        ap += (size_t)8 * T;
+        tp += (size_t)8 * T;
+        mp += (size_t)8 * T;
+      }
+    }
+  };
+
+  if (warp == 1) {
+    // the row's last tile may be partial: its missing tokens are zeros, which leave every recurrence at its initial 0
+    // (0 + c*0, and 0 added to the ReMax sum), so the scan needs no per-token bound check
+    if (lane >= T - ((ntiles - 1) << 5)) {  // columns the cp.async of that tile never writes
+      for (int r = 0; r < RPW; ++r) {
+        st[0].v[r * TS_VS + lane] = 0.0f;
+        st[0].r[r * TS_VS + lane] = 0.0f;
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < TS_STAGES - 1; ++i) {
+      if (i < ntiles) issue(ntiles - 1 - i, i);
+      cp_async_commit();
+    }
+    cp_async_wait<TS_STAGES - 2>();  // tile 0 has landed
+  }
+  __syncthreads();
+
+  const bool mine = (warp == 0) && lane < nrows;
+  const size_t my_base = (size_t)(row0 + (mine ? lane : 0)) * T;
+  const float bl = (MODE == TS_REMAX && mine) ? baselines[row0 + lane] : 0.0f;
+  const float bl0 = __fmul_rn(bl, 0.0f);
+  float x = 0.0f, vn = 0.0f;  // GAE: A_{t+1}, V_{t+1};  REINFORCE++: x = running return
+  double acc = 0.0;           // ReMax: reverse cumulative sum
+  for (int i = 0; i < ntiles; ++i) {
+    const int tile = ntiles - 1 - i, s = i & (TS_STAGES - 1);
+    if (warp == 0) {
+      if (mine) {  // my row, right to left, 16 tokens at a time
+        Stage& S = st[s];
+        float* V = S.v + lane * TS_VS;
+        float* R = S.r + lane * TS_VS;
+        const uint8_t* M = S.m + lane * TS_MS + (int)(((uintptr_t)(mask + my_base + (tile << 5))) & 3);
+#pragma unroll
+        for (int hb = 1; hb >= 0; --hb) {
+          float a[16], b[16];
+          uint8_t mk[16];
+#pragma unroll
+          for (int k = 0; k < 16; ++k) {
+            const int l = hb * 16 + 15 - k;
+            a[k] = R[l];
+            if (MODE == TS_GAE) b[k] = V[l];
+            if (MODE != TS_GAE) mk[k] = M[l];
+          }
+#pragma unroll
+          for (int k = 0; k < 16; ++k) {
+            if (MODE == TS_GAE) {
+              const float v = b[k];
+              const float d = __fsub_rn(__fadd_rn(a[k], __fmul_rn(gamma, vn)), v);
+              x = __fadd_rn(d, __fmul_rn(gl, x));
+              vn = v;
+              a[k] = x;
+              b[k] = __fadd_rn(x, v);
+            } else if (MODE == TS_RFPP) {
+              x = __fadd_rn(a[k], __fmul_rn(gamma, x));
+              a[k] = x;
+              x = mk[k] ? x : __fmul_rn(x, 0.0f);
+            } else {
+              acc += (double)(mk[k] ? a[k] : __fmul_rn(a[k], 0.0f));
+              const float c = (float)acc;
+              a[k] = c;
+              b[k] = __fsub_rn(c, mk[k] ? bl : bl0);
+            }
+          }
+#pragma unroll
+          for (int k = 0; k < 16; ++k) {
+            const int l = hb * 16 + 15 - k;
+            R[l] = a[k];
+            if (MODE != TS_RFPP) V[l] = b[k];
+          }
+        }
+      }
+    } else {
+      cp_async_wait<1>();  // tile i+1 has landed (tile i+2 may still be in flight)
+      if (i >= 1) store(tile + 1, (i - 1) & (TS_STAGES - 1));
+      __syncwarp();
+      if (i + TS_STAGES - 1 < ntiles) issue(tile - (TS_STAGES - 1), (i + TS_STAGES - 1) & (TS_STAGES - 1));
+      cp_async_commit();
+    }
+    __syncthreads();
+  }
+  if (warp == 1) {
+    store(0, (ntiles - 1) & (TS_STAGES - 1));
+    if (MODE != TS_REMAX && moments) {
+      m1 = warp_sum(m1);
+      m2 = warp_sum(m2);
+      if (lane == 0) {
+        atomicAdd(moments + 0, (double)n_masked);
+        atomicAdd(moments + 1, m1);
+        atomicAdd(moments + 2, m2);
+      }
+    }
+  }
+}
+
+// below this many rows the per-row kernels finish in a wave or two and win (RAGEN_TS_MIN_ROWS overrides, for probing)
+static int ts_min_rows() {
+  static const int v = [] {
+    const char* e = getenv("RAGEN_TS_MIN_ROWS");
+    return (e && atoi(e) > 0) ? atoi(e) : 4096;
+  }();
+  return v;
+}
+
+// 8 rows per CTA measured best at every B tried (8 Ki x 2047: 102 us vs 133 / 217 us with 16 / 32 rows; 64 Ki x 1023: 320 vs
+// 408 / 401 us): the step time of a row group is latency, not throughput, so more and smaller groups hide it better.
+constexpr int TS_RPW = 8;
+template <int MODE>
+void launch_tile_scan(const ragen_ctx* ctx, cudaStream_t st, int B, int T, const float* rewards, const float* values, const uint8_t* mask,
+                      float gamma, float gl, const float* baselines, float* adv, float* ret, double* moments) {
+  (void)ctx;
+  tile_scan_kernel<MODE, TS_RPW><<<(B + TS_RPW - 1) / TS_RPW, 64, TS_STAGES * sizeof(TsStage<TS_RPW>), st>>>(
+      B, T, rewards, values, mask, gamma, gl, baselines, adv, ret, moments);
+}
+
 }  // namespace
 
 #define RAGEN_BT(B, T) RAGEN_REQUIRE(B >= 0 && (B == 0 || T >= 1) && (int64_t)B * T < ((int64_t)1 << 40), "bad shape B=%d T=%d", B, T)
@@ -566,8 +819,10 @@ extern "C" int ragen_gae(ragen_ctx* ctx, int B, int T, const float* rewards, con
   cudaStream_t st = (cudaStream_t)stream;
   if (moments) RAGEN_CUDA(cudaMemsetAsync(moments, 0, 3 * sizeof(double), st));
   if (B == 0) return RAGEN_OK;  // an empty shard still contributes zero moments to the all-reduce
-  gae_kernel<<<B, RT, 0, st>>>(B, T, rewards, values, mask, (float)gamma, (float)(gamma * lam), adv,
-                                                        ret, moments);
+  if (B >= ts_min_rows())
+    launch_tile_scan<TS_GAE>(ctx, st, B, T, rewards, values, mask, (float)gamma, (float)(gamma * lam), nullptr, adv, ret, moments);
+  else
+    gae_kernel<<<B, RT, 0, st>>>(B, T, rewards, values, mask, (float)gamma, (float)(gamma * lam), adv, ret, moments);
   RAGEN_LAUNCHED(ctx);
   return RAGEN_OK;
 }
@@ -670,7 +925,10 @@ extern "C" int ragen_discounted_returns(ragen_ctx* ctx, int B, int T, const floa
   cudaStream_t st = (cudaStream_t)stream;
   RAGEN_CUDA(cudaMemsetAsync(moments, 0, 3 * sizeof(double), st));
   if (B == 0) return RAGEN_OK;
-  returns_kernel<0><<<B, RT, 0, st>>>(B, T, rewards, mask, (float)gamma, nullptr, nullptr, ret, moments);
+  if (B >= ts_min_rows())
+    launch_tile_scan<TS_RFPP>(ctx, st, B, T, rewards, nullptr, mask, (float)gamma, 0.0f, nullptr, nullptr, ret, moments);
+  else
+    returns_kernel<0><<<B, RT, 0, st>>>(B, T, rewards, mask, (float)gamma, nullptr, nullptr, ret, moments);
   RAGEN_LAUNCHED(ctx);
   return RAGEN_OK;
 }
@@ -682,8 +940,10 @@ extern "C" int ragen_remax(ragen_ctx* ctx, int B, int T, const float* rewards, c
   RAGEN_REQUIRE(rewards && mask && baselines && adv && ret, "NULL pointer argument");
   if (B == 0) return RAGEN_OK;
   DeviceGuard guard(ctx->device);
-  returns_kernel<1><<<B, RT, 0, (cudaStream_t)stream>>>(B, T, rewards, mask, 0.0f, baselines, adv, ret,
-                                                                                 nullptr);
+  if (B >= ts_min_rows())
+    launch_tile_scan<TS_REMAX>(ctx, (cudaStream_t)stream, B, T, rewards, nullptr, mask, 0.0f, 0.0f, baselines, adv, ret, nullptr);
+  else
+    returns_kernel<1><<<B, RT, 0, (cudaStream_t)stream>>>(B, T, rewards, mask, 0.0f, baselines, adv, ret, nullptr);
   RAGEN_LAUNCHED(ctx);
   return RAGEN_OK;
 }

@@ -193,3 +193,29 @@ def test_group_norm_golden_and_oracle():
     for method in ("mean", "mean_std", "asym_clip"):
         out = ops.group_norm(last, pen, dev(gk, torch.int32), 3, method)
         close(out, M.normalize_scores(last.cpu(), pen.cpu(), gk, method))
+
+
+def test_many_rows_use_the_lane_per_row_tile_kernel_and_stay_bit_exact():
+    """B >= 4096 rows switches GAE / REINFORCE++ / ReMax to tile_scan_kernel (32 rows per warp, one lane per row, cp.async tiles);
+    the recurrences must not change.  B is not a multiple of 32 and T not a multiple of 32 (partial tiles), odd T (unaligned mask rows)."""
+    from ragen_b200 import ops
+
+    for B, T in [(4100, 1500), (4097, 701), (4099, 31), (4096, 129), (4101, 64)]:
+        gen = torch.Generator().manual_seed(B + T)
+        mask = (torch.rand(B, T, generator=gen) < 0.6).float()
+        mask[:, -1] = 1
+        rewards = torch.randn(B, T, generator=gen) * (torch.rand(B, T, generator=gen) < 0.05)
+        values = torch.randn(B, T, generator=gen) * mask
+        for gamma, lam in [(1.0, 1.0), (0.99, 0.95)]:
+            adv, ret, mom = ops.gae_raw(rewards.cuda(), values.cuda(), mask.cuda(), gamma, lam)
+            wa, wr = A.gae_raw(rewards, values, gamma, lam)
+            assert torch.equal(adv.cpu(), wa) and torch.equal(ret.cpu(), wr)
+            close(ops.whiten_(adv, mom), A.masked_whiten(wa, mask))
+            ret, _, mom = ops.discounted_returns(rewards.cuda(), mask.cuda(), gamma)
+            _, wr = A.rfpp(rewards, mask, gamma)
+            assert torch.equal(ret.cpu(), wr)
+            close(mom.cpu(), torch.stack([mask.sum(), (wr * mask).sum(), (wr * wr * mask).sum()]).double(), scale=float(mask.sum()) + 1)
+        base = torch.randn(B, generator=gen)
+        adv, ret = ops.remax(rewards.cuda(), mask.cuda(), base.cuda())
+        wa, wr = A.remax(rewards, base, mask)
+        assert torch.equal(ret.cpu(), wr) and torch.equal(adv.cpu(), wa)

@@ -118,12 +118,19 @@ class SokobanBatch:
         self.fixed = torch.zeros((self.n, HW), dtype=torch.uint8, device=dev)
         # one 8-byte record per env (include/ragen_b200.h): player, num_env_steps, boxes_on_target|under, actual
         self.meta = torch.zeros((self.n, 4), dtype=torch.int16, device=dev)
-        self.reward = torch.zeros(self.n, dtype=torch.float64, device=dev)
-        self.done = torch.zeros(self.n, dtype=torch.uint8, device=dev)
-        self.flags = torch.zeros(self.n, dtype=torch.uint8, device=dev)
-        self.n_executed = torch.zeros(self.n, dtype=torch.uint8, device=dev)
+        # per-step results live in ONE slab [reward f64 | done | flags | n_executed | pad | packed glyph rows] so that the
+        # host-buffer path (step_host) brings a step back with a single device->host copy
+        n_ = self.n
+        self._off_obs = (11 * n_ + 15) & ~15
+        self._slab_bytes = self._off_obs + (n_ * (G // 2) if G % 2 == 0 else 0)
+        self._slab = torch.zeros(max(self._slab_bytes, 16), dtype=torch.uint8, device=dev)
+        self.reward = self._slab[: 8 * n_].view(torch.float64)
+        self.done = self._slab[8 * n_: 9 * n_]
+        self.flags = self._slab[9 * n_: 10 * n_]
+        self.n_executed = self._slab[10 * n_: 11 * n_]
         self.obs = torch.zeros((self.n, G), dtype=torch.uint8, device=dev)
-        self.obs_packed = None  # [n, G/2], made on first packed render (needs an even G)
+        # [n, G/2] two 4-bit codes per byte (needs an even G)
+        self.obs_packed = self._slab[self._off_obs: self._off_obs + n_ * (G // 2)].view(n_, G // 2) if G % 2 == 0 else None
         self.obs_is_packed = False  # which of the two buffers the latest render wrote
         self.status = torch.zeros(self.n, dtype=torch.int32, device=dev)
         self._pinned = {}
@@ -226,10 +233,8 @@ class SokobanBatch:
         return (self.H * (self.W + 1)) % 2 == 0
 
     def _packed_buffer(self):
-        if self.obs_packed is None:
-            if not self.can_pack:
-                raise ValueError(f"packed glyph rows need an even H*(W+1); room is {self.H}x{self.W}")
-            self.obs_packed = torch.zeros((self.n, self.H * (self.W + 1) // 2), dtype=torch.uint8, device=self.device)
+        if self.obs_packed is None:  # lives in the result slab whenever the row stream is even
+            raise ValueError(f"packed glyph rows need an even H*(W+1); room is {self.H}x{self.W}")
         return self.obs_packed
 
     def step(self, actions, n_actions=None, render=True, packed=False) -> StepOut:
@@ -271,6 +276,14 @@ class SokobanBatch:
             h_na.numpy()[...] = n_actions_np
             d_na = h_na.to(self.device, non_blocking=True)
         out = self.step(d_act, d_na, render=want_obs, packed=packed and want_obs)
+        if packed and want_obs:  # one copy of the whole result slab
+            n_ = self.n
+            h = self._pin("slab", (self._slab_bytes,), torch.uint8)
+            h.copy_(self._slab[: self._slab_bytes], non_blocking=True)
+            torch.cuda.current_stream(self.device).synchronize()
+            hn = h.numpy()
+            return (hn[self._off_obs:].reshape(n_, -1), hn[: 8 * n_].view(np.float64), hn[8 * n_: 9 * n_], hn[9 * n_: 10 * n_],
+                    hn[10 * n_: 11 * n_])
         h_rew = self._pin("rew", (self.n,), torch.float64)
         h_done = self._pin("done", (self.n,), torch.uint8)
         h_flags = self._pin("flags", (self.n,), torch.uint8)

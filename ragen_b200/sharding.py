@@ -27,6 +27,37 @@ def world(group=None):
     return 0, 1
 
 
+def bind_host_to_gpu(device_index: int) -> Dict:
+    """Best effort: run this process on the CPUs of the NUMA node the GPU hangs off, BEFORE any pinned host buffer is
+    allocated (first touch then places the staging buffers in that node's memory, so the rank's PCIe traffic does not cross
+    the socket interconnect - what limits host-buffer throughput when 8 ranks share one host).  Returns what it found; a host
+    that exposes no NUMA topology (single node, or a VM that hides it) is left alone."""
+    import os
+
+    info = {"device": int(device_index), "numa_node": None, "cpus": None, "bound": False}
+    try:
+        bdf = torch.cuda.get_device_properties(device_index)
+        bus = f"{getattr(bdf, 'pci_domain_id', 0):04x}:{bdf.pci_bus_id:02x}:{bdf.pci_device_id:02x}.0"
+        with open(f"/sys/bus/pci/devices/{bus}/numa_node") as fh:
+            node = int(fh.read().strip())
+        info["numa_node"] = node
+        if node < 0:
+            return info
+        with open(f"/sys/devices/system/node/node{node}/cpulist") as fh:
+            cpus = set()
+            for part in fh.read().strip().split(","):
+                lo, _, hi = part.partition("-")
+                cpus.update(range(int(lo), int(hi or lo) + 1))
+        allowed = cpus & os.sched_getaffinity(0)
+        info["cpus"] = len(allowed)
+        if allowed:
+            os.sched_setaffinity(0, allowed)
+            info["bound"] = True
+    except (OSError, ValueError, AttributeError, RuntimeError):
+        pass
+    return info
+
+
 def owned_groups(n_groups: int, rank: int, world_size: int) -> List[int]:
     """Group ids of one rank, ascending.  Round-robin keeps every tag's block spread over all ranks."""
     return list(range(rank, n_groups, world_size))

@@ -577,7 +577,7 @@ struct TsStage {
   float r[RPW * TS_VS];
   uint8_t m[RPW * TS_MS];
 };
-enum { TS_GAE = 0, TS_RFPP = 1, TS_REMAX = 2 };
+enum { TS_GAE = 0, TS_RFPP = 1, TS_REMAX = 2, TS_BILEVEL = 3 };
 
 __device__ __forceinline__ void cp_async4(void* smem_dst, const void* gmem_src) {
   asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(smem_dst)), "l"(gmem_src) : "memory");
@@ -591,8 +591,10 @@ __device__ __forceinline__ void cp_async_wait() {
 template <int MODE, int RPW>
 __global__ void __launch_bounds__(64) tile_scan_kernel(int B, int T, const float* __restrict__ rewards,
                                                        const float* __restrict__ values, const uint8_t* __restrict__ mask,
-                                                       float gamma, float gl, const float* __restrict__ baselines,
-                                                       float* __restrict__ adv, float* __restrict__ ret, double* moments) {
+                                                       float gamma, float gl, float hgamma, float hgl,
+                                                       const float* __restrict__ baselines, float* __restrict__ adv,
+                                                       float* __restrict__ ret, double* moments) {
+  constexpr bool HAS_V = (MODE == TS_GAE || MODE == TS_BILEVEL);  // the estimators that read values
   extern __shared__ __align__(16) uint8_t ts_smem[];
   using Stage = TsStage<RPW>;
   Stage* st = reinterpret_cast<Stage*>(ts_smem);
@@ -619,7 +621,7 @@ __global__ void __launch_bounds__(64) tile_scan_kernel(int B, int T, const float
 #pragma unroll 8
     for (int r = 0; r < nrows; ++r) {
       if (tok) {
-        if (MODE == TS_GAE) cp_async4(&S.v[r * TS_VS + lane], vp);
+        if (HAS_V) cp_async4(&S.v[r * TS_VS + lane], vp);
         cp_async4(&S.r[r * TS_VS + lane], rp);
       }
       if (lane < 9) {
@@ -657,7 +659,7 @@ __global__ void __launch_bounds__(64) tile_scan_kernel(int B, int T, const float
           if (MODE != TS_REMAX) mk[k] = S.m[r * TS_MS + (int)((mp_lo + (uint32_t)(k * T)) & 3u) + lane];
         }
         auto put = [&](int k) {
-          if (MODE == TS_GAE) {
+          if (HAS_V) {
             ap[(size_t)k * T] = a[k];
             tp[(size_t)k * T] = b[k];
           } else if (MODE == TS_RFPP) {
@@ -715,6 +717,7 @@ __global__ void __launch_bounds__(64) tile_scan_kernel(int B, int T, const float
   const float bl = (MODE == TS_REMAX && mine) ? baselines[row0 + lane] : 0.0f;
   const float bl0 = __fmul_rn(bl, 0.0f);
   float x = 0.0f, vn = 0.0f;  // GAE: A_{t+1}, V_{t+1};  REINFORCE++: x = running return
+  float hi_lg = 0.0f, hi_nv = 0.0f;  // bi-level: turn-level lastgaelam and the value at the next reward position
   double acc = 0.0;           // ReMax: reverse cumulative sum
   for (int i = 0; i < ntiles; ++i) {
     const int tile = ntiles - 1 - i, s = i & (TS_STAGES - 1);
@@ -732,7 +735,7 @@ __global__ void __launch_bounds__(64) tile_scan_kernel(int B, int T, const float
           for (int k = 0; k < 16; ++k) {
             const int l = hb * 16 + 15 - k;
             a[k] = R[l];
-            if (MODE == TS_GAE) b[k] = V[l];
+            if (HAS_V) b[k] = V[l];
             if (MODE != TS_GAE) mk[k] = M[l];
           }
 #pragma unroll
@@ -744,6 +747,35 @@ __global__ void __launch_bounds__(64) tile_scan_kernel(int B, int T, const float
               vn = v;
               a[k] = x;
               b[k] = __fadd_rn(x, v);
+            } else if (MODE == TS_BILEVEL) {
+              // ragen/trainer/core_algos.py:44-88 as ONE right-to-left sweep (see bilevel_gae_kernel): x = token-level lastgaelam,
+              // vn = value of the nearest loss-mask token to the right (0 when there is none: the reference would raise), hi_lg /
+              // hi_nv = turn-level state.  Reward positions are a handful per row, so the divergent branch is rare.
+              const float r = a[k], v = b[k];
+              const bool m = mk[k] != 0;
+              float ao = 0.0f, ro = 0.0f;
+              if (r != 0.0f) {
+                hi_lg = __fadd_rn(__fsub_rn(__fadd_rn(r, __fmul_rn(hgamma, hi_nv)), v), __fmul_rn(hgl, hi_lg));
+                hi_nv = v;
+                const float upd = __fadd_rn(hi_lg, v);
+                ao = hi_lg;
+                ro = upd;
+                if (m) {  // the token-level pass restarts here: next value 0, lastgaelam 0
+                  const float d = __fsub_rn(__fadd_rn(upd, __fmul_rn(gamma, 0.0f)), v);
+                  x = __fadd_rn(d, __fmul_rn(gl, 0.0f));
+                  ao = x;
+                  ro = __fadd_rn(x, v);
+                  vn = v;
+                }
+              } else if (m) {
+                const float d = __fsub_rn(__fadd_rn(r, __fmul_rn(gamma, vn)), v);
+                x = __fadd_rn(d, __fmul_rn(gl, x));
+                ao = x;
+                ro = __fadd_rn(x, v);
+                vn = v;
+              }
+              a[k] = ao;
+              b[k] = ro;
             } else if (MODE == TS_RFPP) {
               x = __fadd_rn(a[k], __fmul_rn(gamma, x));
               a[k] = x;
@@ -800,10 +832,11 @@ static int ts_min_rows() {
 constexpr int TS_RPW = 8;
 template <int MODE>
 void launch_tile_scan(const ragen_ctx* ctx, cudaStream_t st, int B, int T, const float* rewards, const float* values, const uint8_t* mask,
-                      float gamma, float gl, const float* baselines, float* adv, float* ret, double* moments) {
+                      float gamma, float gl, const float* baselines, float* adv, float* ret, double* moments, float hgamma = 0.0f,
+                      float hgl = 0.0f) {
   (void)ctx;
   tile_scan_kernel<MODE, TS_RPW><<<(B + TS_RPW - 1) / TS_RPW, 64, TS_STAGES * sizeof(TsStage<TS_RPW>), st>>>(
-      B, T, rewards, values, mask, gamma, gl, baselines, adv, ret, moments);
+      B, T, rewards, values, mask, gamma, gl, hgamma, hgl, baselines, adv, ret, moments);
 }
 
 }  // namespace
@@ -837,9 +870,12 @@ extern "C" int ragen_bilevel_gae(ragen_ctx* ctx, int B, int T, const float* rewa
   cudaStream_t st = (cudaStream_t)stream;
   if (moments) RAGEN_CUDA(cudaMemsetAsync(moments, 0, 3 * sizeof(double), st));
   if (B == 0) return RAGEN_OK;  // an empty shard still contributes zero moments to the all-reduce
-  bilevel_gae_kernel<<<B, RT, 0, st>>>(B, T, rewards, values, loss_mask, (float)gamma,
-                                                                (float)(gamma * lam), (float)high_level_gamma,
-                                                                (float)(high_level_gamma * lam), adv, ret, moments);
+  if (B >= ts_min_rows())
+    launch_tile_scan<TS_BILEVEL>(ctx, st, B, T, rewards, values, loss_mask, (float)gamma, (float)(gamma * lam), nullptr, adv, ret, moments,
+                                 (float)high_level_gamma, (float)(high_level_gamma * lam));
+  else
+    bilevel_gae_kernel<<<B, RT, 0, st>>>(B, T, rewards, values, loss_mask, (float)gamma, (float)(gamma * lam), (float)high_level_gamma,
+                                         (float)(high_level_gamma * lam), adv, ret, moments);
   RAGEN_LAUNCHED(ctx);
   return RAGEN_OK;
 }

@@ -219,3 +219,29 @@ def test_many_rows_use_the_lane_per_row_tile_kernel_and_stay_bit_exact():
         adv, ret = ops.remax(rewards.cuda(), mask.cuda(), base.cuda())
         wa, wr = A.remax(rewards, base, mask)
         assert torch.equal(ret.cpu(), wr) and torch.equal(adv.cpu(), wa)
+
+
+def test_many_rows_bilevel_equals_the_per_row_kernel_and_the_oracle():
+    """Bi-level GAE through tile_scan_kernel (B >= 4096) against the per-row kernel on the same rows (B < 4096 per call) bit for
+    bit, and a 12-row sample of it against the oracle's Python loops.  Rewards sit on and off the loss mask."""
+    from ragen_b200 import ops
+
+    for B, T in [(4100, 701), (4096, 96)]:
+        gen = torch.Generator().manual_seed(B * 3 + T)
+        mask = (torch.rand(B, T, generator=gen) < 0.55).float()
+        rewards = (torch.randint(-3, 12, (B, T), generator=gen).float() * 0.1 + 0.05) * (torch.rand(B, T, generator=gen) < 0.01)
+        last = T - 1 - mask.flip(-1).argmax(-1)  # last loss-mask position of each row carries a reward (the reference indexes past it otherwise)
+        rows = torch.arange(B)
+        mask[rows, last] = 1
+        rewards[rows, last] = 0.7
+        values = torch.randn(B, T, generator=gen) * mask
+        for gamma, lam, hg in [(1.0, 1.0, 0.95), (0.99, 0.95, 0.9)]:
+            adv, ret, mom = ops.bilevel_gae_raw(rewards.cuda(), values.cuda(), mask.cuda(), gamma, lam, hg)
+            half = B // 2
+            parts = [ops.bilevel_gae_raw(rewards[s].cuda(), values[s].cuda(), mask[s].cuda(), gamma, lam, hg) for s in (slice(0, half), slice(half, B))]
+            assert torch.equal(adv.cpu(), torch.cat([p[0].cpu() for p in parts]))
+            assert torch.equal(ret.cpu(), torch.cat([p[1].cpu() for p in parts]))
+            close(mom.cpu(), parts[0][2].cpu() + parts[1][2].cpu(), scale=float(mask.sum()) + 1)
+            pick = torch.tensor([0, 1, 7, 8, 9, 31, 32, half, B - 9, B - 8, B - 2, B - 1])
+            wa, wr = A.bilevel_gae_raw(rewards[pick], values[pick], mask[pick], gamma, lam, hg)
+            assert torch.equal(adv.cpu()[pick], wa) and torch.equal(ret.cpu()[pick], wr)

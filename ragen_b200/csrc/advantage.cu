@@ -319,7 +319,27 @@ __global__ void whiten_kernel(int64_t n, float* __restrict__ x, const double* __
   const float meanf = (float)mean;
   const float scale = (float)(1.0 / sqrt(var + 1e-8));
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) x[i] = (x[i] - meanf) * scale;
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if ((reinterpret_cast<uintptr_t>(x) & 15) == 0) {  // 128-bit accesses, two in flight per thread
+    float4* x4 = reinterpret_cast<float4*>(x);
+    const int64_t n4 = n >> 2;
+    int64_t i = tid;
+    for (; i + stride < n4; i += 2 * stride) {
+      float4 a = x4[i], b = x4[i + stride];
+      a.x = (a.x - meanf) * scale; a.y = (a.y - meanf) * scale; a.z = (a.z - meanf) * scale; a.w = (a.w - meanf) * scale;
+      b.x = (b.x - meanf) * scale; b.y = (b.y - meanf) * scale; b.z = (b.z - meanf) * scale; b.w = (b.w - meanf) * scale;
+      x4[i] = a;
+      x4[i + stride] = b;
+    }
+    if (i < n4) {
+      float4 a = x4[i];
+      a.x = (a.x - meanf) * scale; a.y = (a.y - meanf) * scale; a.z = (a.z - meanf) * scale; a.w = (a.w - meanf) * scale;
+      x4[i] = a;
+    }
+    for (int64_t j = (n4 << 2) + tid; j < n; j += stride) x[j] = (x[j] - meanf) * scale;
+    return;
+  }
+  for (int64_t i = tid; i < n; i += stride) x[i] = (x[i] - meanf) * scale;
 }
 
 // masked moments of an arbitrary tensor (for whitening inputs produced elsewhere)
@@ -492,10 +512,26 @@ __global__ void whiten_masked_kernel(int64_t n, const float* __restrict__ x, con
   const float meanf = (float)mean;
   const float scale = (float)(1.0 / sqrt(var + 1e-8));
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-    const float v = (x[i] - meanf) * scale;
-    out[i] = mask[i] ? v : __fmul_rn(v, 0.0f);
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  auto one = [&](float xv, uint8_t m) {
+    const float v = (xv - meanf) * scale;
+    return m ? v : __fmul_rn(v, 0.0f);
+  };
+  int64_t done = 0;
+  if (((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(out)) & 15) == 0 && (reinterpret_cast<uintptr_t>(mask) & 3) == 0) {
+    const float4* x4 = reinterpret_cast<const float4*>(x);
+    const uchar4* m4 = reinterpret_cast<const uchar4*>(mask);
+    float4* o4 = reinterpret_cast<float4*>(out);
+    const int64_t n4 = n >> 2;
+#pragma unroll 2
+    for (int64_t i = tid; i < n4; i += stride) {
+      const float4 a = x4[i];
+      const uchar4 m = m4[i];
+      o4[i] = make_float4(one(a.x, m.x), one(a.y, m.y), one(a.z, m.z), one(a.w, m.w));
+    }
+    done = n4 << 2;
   }
+  for (int64_t i = done + tid; i < n; i += stride) out[i] = one(x[i], mask[i]);
 }
 
 // apply_kl_penalty (verl/verl/trainer/ppo/ray_trainer.py:145-175) with kl_penalty (core_algos.py:469-501):

@@ -168,9 +168,22 @@ def generator_rows(quick):
         first = time.perf_counter() - t0
         ms = dev_time(lambda: b.generate(seeds), reps=3, warm=0)
         ok = float((st == 0).float().mean())
+        # solvability by the reference's own criterion (get_shortest_action_path, restated as oracle solve_bfs)
+        # and mean solution length, on a bounded sample of the rooms this launch produced
+        from oracle import sokoban as S
+        f_all, s_all, _, _ = b.generate(seeds[:256])
+        f_np, s_np, st_np = f_all.cpu().numpy(), s_all.cpu().numpy(), st[:256].cpu().numpy()
+        lens, t_bfs = [], time.perf_counter()
+        for j in np.flatnonzero(st_np == 0):
+            if time.perf_counter() - t_bfs > (10.0 if quick else 40.0):
+                break
+            lens.append(len(S.solve_bfs(f_np[j], s_np[j], H, W)))
+        solved = sum(1 for x in lens if x > 0)
         rows.append(line(tag, "room", n, ms, 2 * H * W + 2, None, "reference: 4 ms/room (6x6), 1.0 s/room (10x10) on one core (SURVEY.md section 0)",
                          valid_fraction=ok, mean_explored=float(explored.float().mean()), first_call_s=first, kernel="sokoban_generate_kernel",
-                         note="no roofline claim: on-chip search, output bytes only"))
+                         bfs_sample=len(lens), bfs_solvable=solved, bfs_mean_solution_len=(float(np.mean([x for x in lens if x > 0])) if solved else None),
+                         note="no roofline claim: on-chip search, output bytes only; bfs_* = oracle solve_bfs (get_shortest_action_path contract, "
+                              "MAX_DEPTH 100) on the first rooms of the launch within a CPU time budget"))
         del b
     return rows
 

@@ -180,9 +180,31 @@ class SokobanBatch:
         seeds = [int(x) for x in seeds]
         slots = list(range(self.n)) if slots is None else [int(x) for x in slots]
         assert len(seeds) == len(slots)
+        if not seeds:
+            return []
         rooms = {}
         todo = sorted(set(seeds))
         alias = {}
+        if todo:
+            # common case (every seed generates): no per-room Python work, one gather on the device
+            fixed, state, status, _ = self.generate(todo)
+            if not bool(status.any()):
+                src = torch.from_numpy(np.searchsorted(np.asarray(todo, dtype=np.uint64), np.asarray(seeds, dtype=np.uint64))).to(self.device)
+                dst = torch.tensor(slots, dtype=torch.long, device=self.device)
+                self.fixed[dst] = fixed[src]
+                self.state[dst] = state[src]
+                self.adopt()
+                return seeds
+            st = status.cpu().tolist()
+            nxt = []
+            for j, sd in enumerate(todo):
+                if st[j] == 0:
+                    rooms[sd] = (fixed[j], state[j])
+                else:
+                    alias[sd] = abs(hash(str(sd))) % (2 ** 32)
+                    if alias[sd] not in rooms and alias[sd] not in nxt:
+                        nxt.append(alias[sd])
+            todo = nxt
         while todo:
             fixed, state, status, _ = self.generate(todo)
             st = status.cpu().tolist()

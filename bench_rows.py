@@ -179,6 +179,17 @@ def generator_rows(quick):
                 break
             lens.append(len(S.solve_bfs(f_np[j], s_np[j], H, W)))
         solved = sum(1 for x in lens if x > 0)
+        # the same check on the device for EVERY room of the launch (ragen_sokoban_solve = get_shortest_action_path)
+        from ragen_b200.env.sokoban import solve_rooms
+        f_gen, s_gen, st_gen, _ = b.generate(seeds)
+        good = st_gen == 0
+        fg, sg = f_gen[good].contiguous(), s_gen[good].contiguous()
+        ms_solve = dev_time(lambda: solve_rooms(fg, sg, (H, W), nb), reps=2, warm=1)
+        sst, slen, _, sexp = solve_rooms(fg, sg, (H, W), nb)
+        rows.append(line(tag + " - device solver over the generated rooms", "room", int(good.sum()), ms_solve, 2 * H * W + 8 + 100, None, None,
+                         solvable_fraction=float((sst == 0).float().mean()), mean_solution_len=float(slen.float().mean()),
+                         max_solution_len=int(slen.max()), mean_states=float(sexp.float().mean()), kernel="sokoban_solve_kernel",
+                         note="get_shortest_action_path on the device, reference BFS order (paths equal the reference's); no roofline claim"))
         rows.append(line(tag, "room", n, ms, 2 * H * W + 2, None, "reference: 4 ms/room (6x6), 1.0 s/room (10x10) on one core (SURVEY.md section 0)",
                          valid_fraction=ok, mean_explored=float(explored.float().mean()), first_call_s=first, kernel="sokoban_generate_kernel",
                          bfs_sample=len(lens), bfs_solvable=solved, bfs_mean_solution_len=(float(np.mean([x for x in lens if x > 0])) if solved else None),

@@ -121,6 +121,17 @@ int ragen_sokoban_generate(ragen_ctx* ctx, int64_t n, int H, int W, int num_boxe
                            int num_gen_steps, const uint64_t* seeds, uint8_t* fixed, uint8_t* state,
                            int32_t* status, int32_t* explored, void* stream);
 
+/* get_shortest_action_path(room_fixed, room_state, MAX_DEPTH) (ragen/env/sokoban/utils.py:11-101) for n rooms: the
+ * reference's breadth-first search (moves tried up, down, left, right; duplicates dropped; a path longer than max_depth
+ * ends the search) with its discovery order, so path [n][max_depth] (may be NULL) receives the reference's action list
+ * (ids 1..4) in its first length[n] bytes.  status [n]: 0 solved (length 0 = already solved: the reference returns []
+ * for that too), 1 no solution within max_depth (the reference's other []), 2 more than max_states distinct states
+ * (0 = 131072, enough for every 10x10 / 2-box room), 3 no player / more than 4 boxes.  explored (may be NULL) [n] =
+ * states popped.  Uses ctx-owned workspace (grown on first use). */
+int ragen_sokoban_solve(ragen_ctx* ctx, int64_t n, int H, int W, const uint8_t* fixed, const uint8_t* state,
+                        int max_depth, int64_t max_states, int32_t* status, int32_t* length, uint8_t* path,
+                        int32_t* explored, void* stream);
+
 /* ---- FrozenLake -------------------------------------------------------------------------- */
 /* Maps are row-major uint8[n][size*size] with tile codes 0 'S' 1 'F' 2 'H' 3 'G' (size 2..8).  Glyph rows are
  * uint8[n][size*(size+1)]: 0 player, 1 frozen (S is drawn as F), 2 hole, 3 goal, 4 player in hole, 5 player on

@@ -235,6 +235,12 @@ class SokobanBatch:
         self.adopt()
         return used
 
+    def solve(self, rows=None, max_depth=100, want_path=True):
+        """Shortest push solutions of the current rooms (all envs, or `rows`): see solve_rooms."""
+        f = self.fixed if rows is None else self.fixed[rows]
+        s = self.state if rows is None else self.state[rows]
+        return solve_rooms(f, s, (self.H, self.W), self.num_boxes, max_depth, self.device.index, want_path)
+
     def adopt(self, check=True):
         _lib.check(self.lib.ragen_sokoban_adopt(
             self.ctx.handle, self.n, self.H, self.W, self.num_boxes, _lib.ptr(self.state), _lib.ptr(self.fixed),
@@ -370,6 +376,54 @@ class SokobanBatch:
         tab = glyph_table(grid_lookup)
         codes = (self.obs if rows is None else self.obs[rows]).cpu().numpy()
         return [codes_to_text(r, tab) for r in codes]
+
+
+def _state_bound(H, W, num_boxes):
+    """Upper bound on distinct (player, boxes) states of an H x W room with a wall border; the solver's queue size."""
+    import math
+
+    cells = max(1, (H - 2) * (W - 2))
+    bound = cells * math.comb(max(cells - 1, 0), max(int(num_boxes), 0)) + 1
+    return int(min(max(bound, 64), 1 << 20))
+
+
+def solve_rooms(fixed, state, dim_room, num_boxes=None, max_depth=100, device=0, want_path=True):
+    """get_shortest_action_path (ragen/env/sokoban/utils.py:11-101) for a batch of rooms on the device.
+    fixed / state: uint8 [k, H*W] (CUDA tensors or anything np.asarray takes).  Returns (status i32 [k], length i32 [k],
+    path u8 [k, max_depth] or None, explored i32 [k]) CUDA tensors; status as in include/ragen_b200.h (0 solved, 1 none within
+    max_depth, 2 state budget exceeded, 3 malformed room).  The path is the reference's own (same BFS discovery order)."""
+    H, W = int(dim_room[0]), int(dim_room[1])
+    dev = torch.device("cuda", int(device))
+
+    def dev_u8(x):
+        t = x if isinstance(x, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(np.asarray(x), dtype=np.uint8))
+        return t.to(dev, torch.uint8).reshape(-1, H * W).contiguous()
+
+    f, s = dev_u8(fixed), dev_u8(state)
+    assert f.shape == s.shape
+    k = f.shape[0]
+    if num_boxes is None:
+        num_boxes = int(((s == 3) | (s == 4)).sum(dim=1).max()) if k else 0
+    ctx = _lib.Context.get(int(device))
+    status = torch.empty(k, dtype=torch.int32, device=dev)
+    length = torch.empty(k, dtype=torch.int32, device=dev)
+    explored = torch.empty(k, dtype=torch.int32, device=dev)
+    path = torch.zeros((k, max(int(max_depth), 1)), dtype=torch.uint8, device=dev) if want_path else None
+    _lib.check(ctx.lib.ragen_sokoban_solve(ctx.handle, k, H, W, _lib.ptr(f), _lib.ptr(s), int(max_depth), _state_bound(H, W, min(num_boxes, 4)),
+                                           _lib.ptr(status), _lib.ptr(length), _lib.ptr(path) if int(max_depth) >= 1 else None,
+                                           _lib.ptr(explored), ctx.stream()))
+    return status, length, path, explored
+
+
+def get_shortest_action_path(room_fixed, room_state, MAX_DEPTH=100, device=0):
+    """The reference's function (utils.py:11-101), one room: list of actions 1..4, or [] (already solved / no solution)."""
+    f = np.asarray(room_fixed)
+    H, W = f.shape
+    status, length, path, _ = solve_rooms(f.reshape(1, -1), np.asarray(room_state).reshape(1, -1), (H, W), max_depth=MAX_DEPTH, device=device)
+    st = int(status[0])
+    if st >= 2:
+        raise RuntimeError(f"sokoban solver: status {st} (2 = state budget exceeded, 3 = malformed room)")
+    return path[0, : int(length[0])].cpu().tolist() if st == 0 else []
 
 
 class SokobanEnv(BaseDiscreteActionEnv):

@@ -8,6 +8,7 @@
 #include "../../ragen_b200/csrc/parse_logic.cuh"
 #include "../../ragen_b200/csrc/score_logic.cuh"
 #include "../../ragen_b200/csrc/sokoban_gen_logic.cuh"
+#include "../../ragen_b200/csrc/sokoban_solve_logic.cuh"
 #include <stdlib.h>
 #include "../../ragen_b200/csrc/toy_logic.cuh"
 
@@ -193,5 +194,22 @@ int hs_sokoban_generate(int H, int W, int nb, int search_depth, int num_gen_step
 
 // ---- text scoring -----------------------------------------------------------------------------------------------
 int hs_text_score(int mode, const uint8_t* pred, int np, const uint8_t* label, int nl) { return score::score_pair(mode, pred, np, label, nl); }
+
+// ---- Sokoban solver (get_shortest_action_path) -----------------------------------------------------------------------
+// returns the status; path_out needs max_depth + 1 bytes
+int hs_sokoban_solve(const uint8_t* fixed, const uint8_t* state, int H, int W, int max_depth, uint32_t max_states, uint8_t* path_out,
+                     int* len_out, int* explored_out) {
+  uint32_t cap = 2;
+  while (cap < 2 * max_states) cap <<= 1;
+  uint64_t* table = (uint64_t*)malloc(sizeof(uint64_t) * cap);
+  uint64_t* queue = (uint64_t*)malloc(sizeof(uint64_t) * max_states);
+  uint32_t* parent = (uint32_t*)malloc(sizeof(uint32_t) * max_states);
+  ssolve::Workspace ws{table, queue, parent, cap, max_states, 1u};
+  const int st = ssolve::solve([&](int cell) { return (int)fixed[cell]; }, state, H, W, max_depth, ws, path_out, 1, len_out, explored_out);
+  free(table);
+  free(queue);
+  free(parent);
+  return st;
+}
 
 }  // extern "C"

@@ -246,3 +246,42 @@ def test_packed_needs_even_row_stream():
     buf = torch.zeros(4 * 25, dtype=torch.uint8, device="cuda")
     rc = b.lib.ragen_sokoban_render_packed(b.ctx.handle, 4, 7, 6, _lib.ptr(b.state), _lib.ptr(b.meta), _lib.ptr(buf), b.ctx.stream())
     assert rc != 0 and b"even" in b.lib.ragen_last_error()
+
+
+def test_solver_returns_the_reference_paths():
+    """ragen_sokoban_solve against the paths the unmodified get_shortest_action_path returned (tests/golden/sokoban_paths.json),
+    action for action, one launch per room shape; then the generated rooms of a launch are all solvable (the reference's own
+    validity criterion) and the lengths equal the oracle BFS on a sample."""
+    from ragen_b200 import _lib
+    from ragen_b200.env.sokoban import get_shortest_action_path, solve_rooms
+
+    G = golden_json("sokoban_paths.json")
+    by_shape = {}
+    for e in G["rooms"]:
+        by_shape.setdefault((e["H"], e["W"], e["max_depth"]), []).append(e)
+    for (H, W, md), es in by_shape.items():
+        f = np.array([e["fixed"] for e in es], dtype=np.uint8)
+        s = np.array([e["state"] for e in es], dtype=np.uint8)
+        status, length, path, explored = solve_rooms(f, s, (H, W), max_depth=md)
+        status, length, path = status.cpu().numpy(), length.cpu().numpy(), path.cpu().numpy()
+        for j, e in enumerate(es):
+            assert path[j, : length[j]].tolist() == e["path"], e["tag"]
+            assert status[j] in (0, 1) and (status[j] == 0 or length[j] == 0), e["tag"]
+    e = next(x for x in G["rooms"] if len(x["path"]) > 8)
+    assert get_shortest_action_path(np.array(e["fixed"]).reshape(e["H"], e["W"]), np.array(e["state"]).reshape(e["H"], e["W"])) == e["path"]
+
+    b = _batch(16, 10, 10, 2, 100)
+    fixed, state, st, _ = b.generate(np.arange(7000, 7000 + 512))
+    ok = (st == 0)
+    status, length, path, explored = solve_rooms(fixed[ok], state[ok], (10, 10), 2)
+    assert int((status != 0).sum()) == 0 and int(length.min()) >= 1  # every generated room is solvable, none starts solved
+    f_np, s_np, l_np, p_np = fixed[ok].cpu().numpy(), state[ok].cpu().numpy(), length.cpu().numpy(), path.cpu().numpy()
+    for j in range(12):
+        assert p_np[j, : l_np[j]].tolist() == list(S.solve_bfs(f_np[j], s_np[j], 10, 10))
+    # a queue that is too small is reported, not guessed
+    ctx = b.ctx
+    st2 = torch.empty(1, dtype=torch.int32, device="cuda"); ln2 = torch.empty(1, dtype=torch.int32, device="cuda")
+    big = int(explored.argmax())
+    _lib.check(ctx.lib.ragen_sokoban_solve(ctx.handle, 1, 10, 10, _lib.ptr(fixed[ok][big:big + 1].contiguous()), _lib.ptr(state[ok][big:big + 1].contiguous()),
+                                           100, 64, _lib.ptr(st2), _lib.ptr(ln2), None, None, ctx.stream()))
+    assert int(st2[0]) == 2 and int(ln2[0]) == 0

@@ -321,6 +321,49 @@ def test_fast_search_equals_plain_search(hs, H, W, nb, depth, n_seeds):
             assert np.array_equal(a[1], b[1]) and np.array_equal(a[2], b[2]), seed
 
 
+# ---- Sokoban solver (sokoban_solve_logic.cuh) ----------------------------------------------------------------------------
+def _solve(hs, fixed, state, H, W, max_depth=100, max_states=1 << 17):
+    fixed = np.ascontiguousarray(fixed, dtype=np.uint8); state = np.ascontiguousarray(state, dtype=np.uint8)
+    path = np.zeros(max_depth + 2, np.uint8)
+    ln, ex = c.c_int(0), c.c_int(0)
+    st = hs.hs_sokoban_solve(P(fixed), P(state), H, W, max_depth, max_states, P(path), c.byref(ln), c.byref(ex))
+    return st, path[: ln.value].tolist(), ex.value
+
+
+def test_sokoban_solver_returns_the_reference_paths(hs):
+    """The BFS the CUDA solver runs returns, action for action, the path the unmodified get_shortest_action_path returned
+    (tests/golden/sokoban_paths.json): golden rooms 6x6 ... 10x10, MAX_DEPTH below / at the solution length, solved / unsolvable /
+    box-less rooms.  The reference's [] means both "already solved" and "no solution"; the status tells them apart."""
+    G = golden_json("sokoban_paths.json")
+    assert not G["skipped"]
+    for e in G["rooms"]:
+        st, path, explored = _solve(hs, e["fixed"], e["state"], e["H"], e["W"], e["max_depth"])
+        assert path == e["path"], e["tag"]
+        assert st in (0, 1) and (st == 0 or path == []), e["tag"]
+        if e["tag"] in ("edge/solved", "edge/nobox"):
+            assert st == 0 and explored == 1
+        if e["tag"] == "edge/corner" or "@" in e["tag"] and not e["path"]:
+            assert st == 1, e["tag"]
+
+
+def test_sokoban_solver_overflow_and_oracle_bfs(hs):
+    from oracle import sokoban as S
+
+    rooms = golden_npz("sokoban_rooms.npz")
+    j = int(np.flatnonzero(rooms["s10_ok"])[2])
+    f, s = rooms["s10_fixed"][j], rooms["s10_state"][j]
+    st, path, explored = _solve(hs, f, s, 10, 10)
+    assert st == 0 and path == list(S.solve_bfs(f, s, 10, 10)) and explored > 1000
+    st, path, _ = _solve(hs, f, s, 10, 10, max_states=1000)  # queue too small for this room: reported, not guessed
+    assert st == 2 and path == []
+    for name in ("s7x9", "s6b3", "s8"):
+        H, W = (int(x) for x in rooms[f"{name}_cfg"][:2])
+        for j in np.flatnonzero(rooms[f"{name}_ok"]):
+            f, s = rooms[f"{name}_fixed"][j], rooms[f"{name}_state"][j]
+            st, path, _ = _solve(hs, f, s, H, W)
+            assert st == 0 and path == list(S.solve_bfs(f, s, H, W)), (name, j)
+
+
 # ---- text-env answer scoring (score_logic.cuh) ---------------------------------------------------------------------------
 SCORE_MODES = {"metamathqa": 0, "exact_match": 1, "numeric": 2, "multiple_choice": 3}
 

@@ -57,4 +57,17 @@ def run():
     ops.whiten_(adv, mom)
     assert float((adv.cpu() - A.masked_whiten(wa, mask)).abs().max()) < 1e-5 * max(1.0, float(wa.abs().max()))
     notes.append("gae bit-exact, whiten within 1e-5")
+    # generator + solver: 64 rooms 6x6, every valid one solvable, paths equal the oracle BFS
+    from oracle import sokoban as S
+    from ragen_b200.env.sokoban import SokobanBatch, solve_rooms
+
+    sb = SokobanBatch(1, (6, 6), 1, 100)
+    fixed, state, st, _ = sb.generate(list(range(64)))
+    ok = st == 0
+    status, length, path, _ = solve_rooms(fixed[ok], state[ok], (6, 6), 1)
+    assert int((status != 0).sum()) == 0
+    f_np, s_np, l_np, p_np = fixed[ok].cpu().numpy(), state[ok].cpu().numpy(), length.cpu().numpy(), path.cpu().numpy()
+    for j in range(8):
+        assert p_np[j, : l_np[j]].tolist() == list(S.solve_bfs(f_np[j], s_np[j], 6, 6))
+    notes.append("generated 6x6 rooms all solvable, solver paths equal the oracle BFS")
     return notes

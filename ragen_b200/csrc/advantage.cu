@@ -604,7 +604,8 @@ __global__ void group_stats_kernel(int n_groups, int group_size, const float* __
 // words that cover them.  Tiles run right to left, the carries (recurrence state, V_{t+1}) stay in the lane's registers.
 // Results equal the per-row kernels bit for bit (tests/test_gpu_advantage_ctx.py).  Measured at 8192 x 2047: GAE 192 -> 102 us,
 // REINFORCE++ 324 -> 89 us; the pass is still bound by instruction latency per tile step (~2.4 instructions per token), not HBM.
-constexpr int TS_STAGES = 4;
+constexpr int TS_STAGES = 4;            // ring slots: one being scanned, one being stored, one just freed, TS_LEAD in flight
+constexpr int TS_LEAD = TS_STAGES - 3;  // tiles the loader runs ahead of the scan
 constexpr int TS_VS = 33;  // floats between tile rows
 constexpr int TS_MS = 40;  // bytes between mask tile rows (32 + 3 bytes of misalignment, rounded up to words)
 template <int RPW>  // rows per warp
@@ -625,7 +626,7 @@ __device__ __forceinline__ void cp_async_wait() {
 }
 
 template <int MODE, int RPW>
-__global__ void __launch_bounds__(64) tile_scan_kernel(int B, int T, const float* __restrict__ rewards,
+__global__ void __launch_bounds__(96) tile_scan_kernel(int B, int T, const float* __restrict__ rewards,
                                                        const float* __restrict__ values, const uint8_t* __restrict__ mask,
                                                        float gamma, float gl, float hgamma, float hgl,
                                                        const float* __restrict__ baselines, float* __restrict__ adv,
@@ -640,11 +641,12 @@ __global__ void __launch_bounds__(64) tile_scan_kernel(int B, int T, const float
   const int ntiles = (T + 31) >> 5;
   const uintptr_t mask_end = (uintptr_t)(mask + (size_t)B * T);
 
-  // Two warps share a row group.  Step i (tile ntiles-1-i, ring slot i & 3):
-  //   warp 0 ("scan")  runs the recurrences of tile i, lane = row;
-  //   warp 1 ("mover") waits for tile i+1's cp.async group, writes tile i-1's results to HBM (lane = token, coalesced row
-  //                    segments) with the masked moments, then refills that slot with tile i+3;
-  // and one CTA barrier per step hands tile i to the mover and tile i+1 to the scan warp.  A warp here is usually alone on
+  // Three warps share a row group.  Step i (tile ntiles-1-i, ring slot i & 3):
+  //   warp 0 ("scan")   runs the recurrences of tile i, lane = row;
+  //   warp 1 ("loader") issues the cp.async of tile i+TS_LEAD+1 into the slot stored during step i-1 and waits for tile i+1
+  //                     (a tile has TS_LEAD steps to arrive: with one step of lead the step time WAS the HBM latency);
+  //   warp 2 ("storer") writes tile i-1's results to HBM (lane = token, coalesced row segments) with the masked moments;
+  // and one CTA barrier per step hands the tiles on.  A warp here is usually alone on
   // its scheduler, so each phase is "a batch of independent loads, the arithmetic, the stores": nothing else hides latency.
   auto issue = [&](int tile, int s) {
     const int t0 = tile << 5;
@@ -740,11 +742,11 @@ __global__ void __launch_bounds__(64) tile_scan_kernel(int B, int T, const float
       }
     }
 #pragma unroll
-    for (int i = 0; i < TS_STAGES - 1; ++i) {
+    for (int i = 0; i <= TS_LEAD; ++i) {
       if (i < ntiles) issue(ntiles - 1 - i, i);
       cp_async_commit();
     }
-    cp_async_wait<TS_STAGES - 2>();  // tile 0 has landed
+    cp_async_wait<TS_LEAD>();  // tile 0 has landed
   }
   __syncthreads();
 
@@ -831,16 +833,17 @@ __global__ void __launch_bounds__(64) tile_scan_kernel(int B, int T, const float
           }
         }
       }
-    } else {
-      cp_async_wait<1>();  // tile i+1 has landed (tile i+2 may still be in flight)
-      if (i >= 1) store(tile + 1, (i - 1) & (TS_STAGES - 1));
-      __syncwarp();
-      if (i + TS_STAGES - 1 < ntiles) issue(tile - (TS_STAGES - 1), (i + TS_STAGES - 1) & (TS_STAGES - 1));
+    } else if (warp == 1) {
+      // into the slot whose tile was stored during step i-1 (i + TS_LEAD + 1 = i - 2 modulo the ring)
+      if (i + TS_LEAD + 1 < ntiles) issue(tile - (TS_LEAD + 1), (i + TS_LEAD + 1) & (TS_STAGES - 1));
       cp_async_commit();
+      cp_async_wait<TS_LEAD>();  // tile i+1 has landed (the TS_LEAD tiles after it may still be in flight)
+    } else {
+      if (i >= 1) store(tile + 1, (i - 1) & (TS_STAGES - 1));
     }
     __syncthreads();
   }
-  if (warp == 1) {
+  if (warp == 2) {
     store(0, (ntiles - 1) & (TS_STAGES - 1));
     if (MODE != TS_REMAX && moments) {
       m1 = warp_sum(m1);
@@ -871,7 +874,7 @@ void launch_tile_scan(const ragen_ctx* ctx, cudaStream_t st, int B, int T, const
                       float gamma, float gl, const float* baselines, float* adv, float* ret, double* moments, float hgamma = 0.0f,
                       float hgl = 0.0f) {
   (void)ctx;
-  tile_scan_kernel<MODE, TS_RPW><<<(B + TS_RPW - 1) / TS_RPW, 64, TS_STAGES * sizeof(TsStage<TS_RPW>), st>>>(
+  tile_scan_kernel<MODE, TS_RPW><<<(B + TS_RPW - 1) / TS_RPW, 96, TS_STAGES * sizeof(TsStage<TS_RPW>), st>>>(
       B, T, rewards, values, mask, gamma, gl, hgamma, hgl, baselines, adv, ret, moments);
 }
 

@@ -866,16 +866,30 @@ static int ts_min_rows() {
   return v;
 }
 
-// 8 rows per CTA measured best at every B tried (8 Ki x 2047: 102 us vs 133 / 217 us with 16 / 32 rows; 64 Ki x 1023: 320 vs
-// 408 / 401 us): the step time of a row group is latency, not throughput, so more and smaller groups hide it better.
+// 8 rows per CTA measured best at every B tried, with two and with three warps per group (three warps, 8 Ki x 2047: GAE 96 us vs
+// 118 / 172 us with 16 / 32 rows; 64 Ki x 1023: 317 vs 389 / 353 us): a row group's step is a chain of dependent instructions
+// issued by lone warps (~500 in the scan warp per 32-token tile), so more and smaller groups overlap better than fewer, fatter
+// ones.  RAGEN_TS_RPW = 16 | 32 overrides, for probing.
 constexpr int TS_RPW = 8;
 template <int MODE>
 void launch_tile_scan(const ragen_ctx* ctx, cudaStream_t st, int B, int T, const float* rewards, const float* values, const uint8_t* mask,
                       float gamma, float gl, const float* baselines, float* adv, float* ret, double* moments, float hgamma = 0.0f,
                       float hgl = 0.0f) {
   (void)ctx;
-  tile_scan_kernel<MODE, TS_RPW><<<(B + TS_RPW - 1) / TS_RPW, 96, TS_STAGES * sizeof(TsStage<TS_RPW>), st>>>(
-      B, T, rewards, values, mask, gamma, gl, hgamma, hgl, baselines, adv, ret, moments);
+  static const int force = [] {
+    const char* e = getenv("RAGEN_TS_RPW");
+    return e ? atoi(e) : 0;
+  }();
+  const int rpw = force ? force : TS_RPW;
+  if (rpw == 32)
+    tile_scan_kernel<MODE, 32><<<(B + 31) / 32, 96, TS_STAGES * sizeof(TsStage<32>), st>>>(B, T, rewards, values, mask, gamma, gl, hgamma, hgl,
+                                                                                          baselines, adv, ret, moments);
+  else if (rpw == 16)
+    tile_scan_kernel<MODE, 16><<<(B + 15) / 16, 96, TS_STAGES * sizeof(TsStage<16>), st>>>(B, T, rewards, values, mask, gamma, gl, hgamma, hgl,
+                                                                                          baselines, adv, ret, moments);
+  else
+    tile_scan_kernel<MODE, 8><<<(B + 7) / 8, 96, TS_STAGES * sizeof(TsStage<8>), st>>>(B, T, rewards, values, mask, gamma, gl, hgamma, hgl,
+                                                                                      baselines, adv, ret, moments);
 }
 
 }  // namespace

@@ -87,6 +87,19 @@ int ragen_sokoban_step_packed(ragen_ctx* ctx, int64_t n, int H, int W, int num_b
 int ragen_sokoban_render_packed(ragen_ctx* ctx, int64_t n, int H, int W, const uint8_t* state,
                                 const int16_t* meta, uint8_t* obs_packed, void* stream);
 
+/* The same step / render with THREE-BIT glyph rows: the H*W cell codes (0..6), row-major, no separators (the reader
+ * knows W), as a little-endian bit stream (cell i in bits 3i..3i+2) padded with zero bits to an even number of bytes:
+ * obs_packed3 [n][((3*H*W + 15) / 16) * 2] - 38 B for 10x10, 14 B for 6x6.  The bulk-transport format: where a step's
+ * results go back to host memory the device->host link bounds the step, and this is 31 % fewer bytes than the nibble
+ * rows.  Built for 6x6, 8x8 and 10x10 rooms (other shapes: RAGEN_EINVAL). */
+int ragen_sokoban_step_packed3(ragen_ctx* ctx, int64_t n, int H, int W, int num_boxes, int max_steps,
+                               const uint8_t* actions, int K, const uint8_t* n_actions,
+                               uint8_t* state, int16_t* meta,
+                               double* acc_reward, uint8_t* done, uint8_t* flags, uint8_t* n_executed,
+                               uint8_t* obs_packed3, void* stream);
+int ragen_sokoban_render_packed3(ragen_ctx* ctx, int64_t n, int H, int W, const uint8_t* state,
+                                 const int16_t* meta, uint8_t* obs_packed3, void* stream);
+
 /* SokobanEnv.render text branch only (env.py:53-57). */
 int ragen_sokoban_render(ragen_ctx* ctx, int64_t n, int H, int W, const uint8_t* state,
                          const int16_t* meta, uint8_t* obs, void* stream);

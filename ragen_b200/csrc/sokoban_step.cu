@@ -129,6 +129,45 @@ __device__ __forceinline__ void render_tile(const uint8_t* s_state, uint8_t* s_o
   }
 }
 
+// An env's B packed bytes start at e*B in the tile, word-aligned only for some envs: funnel-shift the NOW-word stream by
+// (e*B)&3 bytes, store the interior as whole words and the first / last partial words as bytes.
+template <int B, int NOW>
+__device__ __forceinline__ void store_env_stream(const uint32_t (&out)[NOW], uint8_t* s_obs, int e) {
+  constexpr bool ALIGNED = (B % 4 == 0);
+  const int a = ALIGNED ? 0 : ((e * B) & 3);
+  uint8_t* dst = s_obs + e * B - a;  // word-aligned; this env owns bytes [a, a + B) from here
+  uint32_t prev = 0u;
+#pragma unroll
+  for (int k = 0; k <= NOW; ++k) {
+    if (4 * k >= B + 3) break;
+    const uint32_t cur = (k < NOW) ? out[k] : 0u;
+    const uint32_t w = ALIGNED ? cur : __funnelshift_l(prev, cur, a << 3);
+    prev = cur;
+    if ((ALIGNED || k >= 1) && 4 * k + 4 <= B) {
+      *reinterpret_cast<uint32_t*>(dst + 4 * k) = w;  // whole word inside [a, a + B) for every a
+    } else {
+#pragma unroll
+      for (int b = 0; b < 4; ++b) {
+        const int at = 4 * k + b;
+        if (at >= a && at < a + B) dst[at] = (uint8_t)(w >> (8 * b));
+      }
+    }
+  }
+}
+
+// the room's words -> a stream of cell nibbles, 8 cells per word (two shift-ors and one byte permute per word)
+template <int HW>
+__device__ __forceinline__ void cell_nibbles(const uint32_t* sw, uint32_t (&cw)[(HW + 7) / 8 + 1]) {
+  constexpr int NW = HW / 4, NCW = (HW + 7) / 8;
+#pragma unroll
+  for (int j = 0; j < NCW; ++j) {
+    const uint32_t x0 = sw[2 * j];
+    const uint32_t x1 = (2 * j + 1 < NW) ? sw[2 * j + 1] : 0u;
+    cw[j] = __byte_perm(x0 | (x0 >> 4), x1 | (x1 >> 4), 0x6420);
+  }
+  cw[NCW] = 0u;
+}
+
 // Thread-per-env packed render for the compile-time room shapes (rooms that are whole 32-bit words: 6x6, 8x8, 10x10).
 // The thread that stepped env e turns ITS room into the env's G/2 packed bytes with every index known at compile time:
 //   1. the room's words -> a stream of cell nibbles (two shifts-and-ors and one byte permute per 8 cells);
@@ -146,15 +185,8 @@ __device__ __forceinline__ void render_env_packed(const uint8_t* s_state, uint8_
   constexpr int NCW = (HW + 7) / 8;  // words of the cell-nibble stream
   constexpr int NOW = (G + 7) / 8;   // words of the output stream before the alignment shift
   static_assert(HW % 4 == 0 && G % 2 == 0 && RW >= 7, "shape not supported by the per-env render");
-  const uint32_t* sw = reinterpret_cast<const uint32_t*>(s_state) + e * NW;
   uint32_t cw[NCW + 1];
-#pragma unroll
-  for (int j = 0; j < NCW; ++j) {
-    const uint32_t x0 = sw[2 * j];
-    const uint32_t x1 = (2 * j + 1 < NW) ? sw[2 * j + 1] : 0u;
-    cw[j] = __byte_perm(x0 | (x0 >> 4), x1 | (x1 >> 4), 0x6420);
-  }
-  cw[NCW] = 0u;
+  cell_nibbles<HW>(reinterpret_cast<const uint32_t*>(s_state) + e * NW, cw);
   uint32_t out[NOW];
 #pragma unroll
   for (int k = 0; k < NOW; ++k) {
@@ -180,32 +212,48 @@ __device__ __forceinline__ void render_env_packed(const uint8_t* s_state, uint8_
     }
     out[k] = acc;
   }
-  constexpr bool ALIGNED = (B % 4 == 0);
-  const int a = ALIGNED ? 0 : ((e * B) & 3);
-  uint8_t* dst = s_obs + e * B - a;  // word-aligned; this env owns bytes [a, a + B) from here
-  uint32_t prev = 0u;
-#pragma unroll
-  for (int k = 0; k <= NOW; ++k) {
-    if (4 * k >= B + 3) break;
-    const uint32_t cur = (k < NOW) ? out[k] : 0u;
-    const uint32_t w = ALIGNED ? cur : __funnelshift_l(prev, cur, a << 3);
-    prev = cur;
-    if ((ALIGNED || k >= 1) && 4 * k + 4 <= B) {
-      *reinterpret_cast<uint32_t*>(dst + 4 * k) = w;  // whole word inside [a, a + B) for every a
-    } else {
-#pragma unroll
-      for (int b = 0; b < 4; ++b) {
-        const int at = 4 * k + b;
-        if (at >= a && at < a + B) dst[at] = (uint8_t)(w >> (8 * b));
-      }
-    }
-  }
+  store_env_stream<B, NOW>(out, s_obs, e);
 }
 
-template <int CH, int CW, bool RENDER_ONLY, bool PACKED>
+// Three-bit glyph rows (ragen_sokoban_step_packed3): the H*W cell codes (0..6 fit three bits), row-major, NO separators (the
+// host knows W), little-endian bit stream padded to an even number of bytes per env - 38 B for 10x10 instead of 55 B of
+// nibbles: the format for bulk transport to the host, where the device->host link is what bounds the step.
+template <int CH, int CW>
+__device__ __forceinline__ void render_env_packed3(const uint8_t* s_state, uint8_t* s_obs, int e) {
+  constexpr int HW = CH * CW, NCW = (HW + 7) / 8;
+  constexpr int B = ((HW * 3 + 15) / 16) * 2;  // bytes per env
+  constexpr int NOW = (B + 3) / 4;
+  static_assert(HW % 4 == 0, "shape not supported by the per-env render");
+  uint32_t cw[NCW + 1];
+  cell_nibbles<HW>(reinterpret_cast<const uint32_t*>(s_state) + e * (HW / 4), cw);
+  uint32_t g24[NCW];  // 8 cells -> 24 bits
+#pragma unroll
+  for (int j = 0; j < NCW; ++j) {
+    const uint32_t x = cw[j];
+    const uint32_t pr = (x & 0x07070707u) | (((x >> 4) & 0x07070707u) << 3);  // per byte: cell 2i | cell 2i+1 << 3
+    g24[j] = (pr & 0x3fu) | ((pr >> 2) & 0xfc0u) | ((pr >> 4) & 0x3f000u) | ((pr >> 6) & 0xfc0000u);
+  }
+  uint32_t out[NOW];
+#pragma unroll
+  for (int k = 0; k < NOW; ++k) {
+    uint32_t acc = 0u;
+#pragma unroll
+    for (int j = 0; j < NCW; ++j) {
+      const int sh = 24 * j - 32 * k;  // bit position of group j in word k
+      if (sh > -24 && sh < 32) acc |= (sh >= 0) ? (g24[j] << sh) : (g24[j] >> (-sh));
+    }
+    out[k] = acc;
+  }
+  store_env_stream<B, NOW>(out, s_obs, e);
+}
+
+// PACK: glyph-row format - 0 one code per byte, 1 two 4-bit codes per byte, 2 three bits per cell without separators
+template <int CH, int CW, bool RENDER_ONLY, int PACK>
 __global__ void __launch_bounds__(TE) sokoban_tile_kernel(const StepParams p) {
+  constexpr bool PACKED = (PACK == 1), PACK3 = (PACK == 2);
   const int H = CH ? CH : p.H, W = CW ? CW : p.W;
   const int HW = H * W, G = H * (W + 1);
+  const int B3 = ((HW * 3 + 15) / 16) * 2;  // bytes of a three-bit row stream
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ __align__(8) uint64_t bar;
 
@@ -215,7 +263,7 @@ __global__ void __launch_bounds__(TE) sokoban_tile_kernel(const StepParams p) {
   const int64_t env0 = (int64_t)blockIdx.x * TE;
   const int cnt = (int)min((int64_t)TE, p.n - env0);
   const int room_bytes = cnt * HW;
-  const int obs_bytes = PACKED ? (cnt * G) >> 1 : cnt * G;  // PACKED needs an even G (checked at launch)
+  const int obs_bytes = PACK3 ? cnt * B3 : PACKED ? (cnt * G) >> 1 : cnt * G;  // PACKED needs an even G (checked at launch)
   const bool bulk_rooms = (room_bytes & 15) == 0;
   const bool bulk_obs = (obs_bytes & 15) == 0;
   uint8_t* g_state = p.state + env0 * HW;
@@ -323,9 +371,18 @@ __global__ void __launch_bounds__(TE) sokoban_tile_kernel(const StepParams p) {
   }
   // rooms of the compile-time shapes are rendered by the thread that owns them (render_env_packed), straight after its
   // own step: no CTA-wide barrier between step and render, and the player-on-target patch touches only the owner's bytes
-  constexpr bool ENV_RENDER = PACKED && CH != 0 && CW != 0 && ((CH * CW) % 4 == 0) && ((CH * (CW + 1)) % 2 == 0) && CW >= 6;
-  if (ENV_RENDER && p.obs && mine) {
-    if constexpr (ENV_RENDER) render_env_packed<CH, CW>(s_state, s_obs, e);
+  constexpr bool ENV_RENDER =
+      PACK != 0 && CH != 0 && CW != 0 && ((CH * CW) % 4 == 0) && (PACK3 || ((CH * (CW + 1)) % 2 == 0)) && CW >= 6;
+  if (ENV_RENDER && PACK3 && p.obs && mine) {
+    // three-bit rows: the player-on-target code 6 is put into the room for the duration of the render (the room's bulk store
+    // is issued after the barrier below, and the cell is the owner's)
+    const bool patch = under && pos >= 0;
+    if (patch) s_state[e * HW + pos] = 6;
+    if constexpr (ENV_RENDER && PACK3) render_env_packed3<CH, CW>(s_state, s_obs, e);
+    if (patch) s_state[e * HW + pos] = 5;
+  }
+  if (ENV_RENDER && PACKED && p.obs && mine) {
+    if constexpr (ENV_RENDER && PACKED) render_env_packed<CH, CW>(s_state, s_obs, e);
     if (under) {  // player standing on a target (env.py:55)
       const int q = e * G + pos + pos / W;
       const uint8_t old = s_obs[q >> 1];
@@ -364,7 +421,7 @@ __global__ void __launch_bounds__(TE) sokoban_tile_kernel(const StepParams p) {
       fence_async_smem();
       __syncthreads();
     }
-    uint8_t* g_obs = p.obs + (PACKED ? (env0 * G) >> 1 : env0 * G);
+    uint8_t* g_obs = p.obs + (PACK3 ? env0 * B3 : PACKED ? (env0 * G) >> 1 : env0 * G);
     if (bulk_obs) {
       if (threadIdx.x == 0) {
         tma_store_1d(g_obs, s_obs, (uint32_t)obs_bytes);
@@ -448,27 +505,29 @@ __global__ void __launch_bounds__(TE) sokoban_adopt_kernel(const AdoptParams p) 
   if (p.status) p.status[env0 + e] = st;
 }
 
-size_t tile_smem(int H, int W, bool packed) {
-  const int glyph_bytes = packed ? (TE * H * (W + 1)) >> 1 : TE * H * (W + 1);
+size_t tile_smem(int H, int W, int pack) {
+  const int glyph_bytes = pack == 2 ? TE * (((H * W * 3 + 15) / 16) * 2) : pack == 1 ? (TE * H * (W + 1)) >> 1 : TE * H * (W + 1);
   return (size_t)round16(TE * H * W) + 16 + round16(glyph_bytes) + 16;
 }
 
-template <bool RENDER_ONLY, bool PACKED>
+template <bool RENDER_ONLY, int PACK>
 int launch_tiles(ragen_ctx* ctx, const StepParams& p, cudaStream_t stream) {
-  RAGEN_REQUIRE(!PACKED || ((p.H * (p.W + 1)) & 1) == 0, "packed glyph rows need an even H*(W+1), got %dx%d", p.H, p.W);
-  const size_t smem = tile_smem(p.H, p.W, PACKED);
+  RAGEN_REQUIRE(PACK != 1 || ((p.H * (p.W + 1)) & 1) == 0, "packed glyph rows need an even H*(W+1), got %dx%d", p.H, p.W);
+  RAGEN_REQUIRE(PACK != 2 || (p.H == p.W && (p.H == 6 || p.H == 8 || p.H == 10)),
+                "three-bit glyph rows are built for 6x6, 8x8 and 10x10 rooms, got %dx%d", p.H, p.W);
+  const size_t smem = tile_smem(p.H, p.W, PACK);
   RAGEN_REQUIRE(smem <= 227 * 1024, "room %dx%d does not fit the shared-memory tile (%zu B)", p.H, p.W, smem);
   const unsigned grid = (unsigned)((p.n + TE - 1) / TE);
 #define RAGEN_TILE_LAUNCH(CH, CW)                                                                   \
   do {                                                                                              \
-    auto kern = sokoban_tile_kernel<CH, CW, RENDER_ONLY, PACKED>;                                          \
+    auto kern = sokoban_tile_kernel<CH, CW, RENDER_ONLY, PACK>;                                            \
     RAGEN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
     kern<<<grid, TE, smem, stream>>>(p);                                                            \
   } while (0)
   if (p.H == 6 && p.W == 6) RAGEN_TILE_LAUNCH(6, 6);
   else if (p.H == 8 && p.W == 8) RAGEN_TILE_LAUNCH(8, 8);
   else if (p.H == 10 && p.W == 10) RAGEN_TILE_LAUNCH(10, 10);
-  else RAGEN_TILE_LAUNCH(0, 0);
+  else if constexpr (PACK != 2) RAGEN_TILE_LAUNCH(0, 0);
 #undef RAGEN_TILE_LAUNCH
   RAGEN_LAUNCHED(ctx);
   return RAGEN_OK;
@@ -483,7 +542,7 @@ bool aligned8(const void* p) { return ((uintptr_t)p & 7) == 0; }
   RAGEN_REQUIRE(n >= 0 && H >= 3 && W >= 3 && H * W <= 32767, "bad shape n=%lld H=%d W=%d", (long long)n, H, W)
 
 namespace {
-int sokoban_step_entry(bool packed, ragen_ctx* ctx, int64_t n, int H, int W, int num_boxes, int max_steps, const uint8_t* actions,
+int sokoban_step_entry(int pack, ragen_ctx* ctx, int64_t n, int H, int W, int num_boxes, int max_steps, const uint8_t* actions,
                        int K, const uint8_t* n_actions, uint8_t* state, int16_t* meta, double* acc_reward, uint8_t* done,
                        uint8_t* flags, uint8_t* n_executed, uint8_t* obs, void* stream) {
   RAGEN_REQUIRE(ctx, "ctx is NULL");
@@ -497,10 +556,12 @@ int sokoban_step_entry(bool packed, ragen_ctx* ctx, int64_t n, int H, int W, int
   DeviceGuard guard(ctx->device);
   StepParams p{n, H, W, num_boxes, max_steps, K, actions, n_actions, state, reinterpret_cast<EnvMeta*>(meta),
                acc_reward, done, flags, n_executed, obs};
-  return packed ? launch_tiles<false, true>(ctx, p, (cudaStream_t)stream) : launch_tiles<false, false>(ctx, p, (cudaStream_t)stream);
+  return pack == 2   ? launch_tiles<false, 2>(ctx, p, (cudaStream_t)stream)
+         : pack == 1 ? launch_tiles<false, 1>(ctx, p, (cudaStream_t)stream)
+                     : launch_tiles<false, 0>(ctx, p, (cudaStream_t)stream);
 }
 
-int sokoban_render_entry(bool packed, ragen_ctx* ctx, int64_t n, int H, int W, const uint8_t* state, const int16_t* meta,
+int sokoban_render_entry(int pack, ragen_ctx* ctx, int64_t n, int H, int W, const uint8_t* state, const int16_t* meta,
                          uint8_t* obs, void* stream) {
   RAGEN_REQUIRE(ctx, "ctx is NULL");
   RAGEN_SOKOBAN_SHAPE(n, H, W);
@@ -515,7 +576,9 @@ int sokoban_render_entry(bool packed, ragen_ctx* ctx, int64_t n, int H, int W, c
   p.state = const_cast<uint8_t*>(state);
   p.meta = reinterpret_cast<EnvMeta*>(const_cast<int16_t*>(meta));
   p.obs = obs;
-  return packed ? launch_tiles<true, true>(ctx, p, (cudaStream_t)stream) : launch_tiles<true, false>(ctx, p, (cudaStream_t)stream);
+  return pack == 2   ? launch_tiles<true, 2>(ctx, p, (cudaStream_t)stream)
+         : pack == 1 ? launch_tiles<true, 1>(ctx, p, (cudaStream_t)stream)
+                     : launch_tiles<true, 0>(ctx, p, (cudaStream_t)stream);
 }
 }  // namespace
 
@@ -523,7 +586,7 @@ extern "C" int ragen_sokoban_step(ragen_ctx* ctx, int64_t n, int H, int W, int n
                                   const uint8_t* actions, int K, const uint8_t* n_actions, uint8_t* state, int16_t* meta,
                                   double* acc_reward, uint8_t* done, uint8_t* flags, uint8_t* n_executed, uint8_t* obs,
                                   void* stream) {
-  return sokoban_step_entry(false, ctx, n, H, W, num_boxes, max_steps, actions, K, n_actions, state, meta, acc_reward, done, flags,
+  return sokoban_step_entry(0, ctx, n, H, W, num_boxes, max_steps, actions, K, n_actions, state, meta, acc_reward, done, flags,
                             n_executed, obs, stream);
 }
 
@@ -531,18 +594,31 @@ extern "C" int ragen_sokoban_step_packed(ragen_ctx* ctx, int64_t n, int H, int W
                                          const uint8_t* actions, int K, const uint8_t* n_actions, uint8_t* state,
                                          int16_t* meta, double* acc_reward, uint8_t* done, uint8_t* flags,
                                          uint8_t* n_executed, uint8_t* obs_packed, void* stream) {
-  return sokoban_step_entry(true, ctx, n, H, W, num_boxes, max_steps, actions, K, n_actions, state, meta, acc_reward, done, flags,
+  return sokoban_step_entry(1, ctx, n, H, W, num_boxes, max_steps, actions, K, n_actions, state, meta, acc_reward, done, flags,
                             n_executed, obs_packed, stream);
 }
 
 extern "C" int ragen_sokoban_render(ragen_ctx* ctx, int64_t n, int H, int W, const uint8_t* state, const int16_t* meta,
                                     uint8_t* obs, void* stream) {
-  return sokoban_render_entry(false, ctx, n, H, W, state, meta, obs, stream);
+  return sokoban_render_entry(0, ctx, n, H, W, state, meta, obs, stream);
 }
 
 extern "C" int ragen_sokoban_render_packed(ragen_ctx* ctx, int64_t n, int H, int W, const uint8_t* state,
                                            const int16_t* meta, uint8_t* obs_packed, void* stream) {
-  return sokoban_render_entry(true, ctx, n, H, W, state, meta, obs_packed, stream);
+  return sokoban_render_entry(1, ctx, n, H, W, state, meta, obs_packed, stream);
+}
+
+extern "C" int ragen_sokoban_step_packed3(ragen_ctx* ctx, int64_t n, int H, int W, int num_boxes, int max_steps,
+                                          const uint8_t* actions, int K, const uint8_t* n_actions, uint8_t* state,
+                                          int16_t* meta, double* acc_reward, uint8_t* done, uint8_t* flags,
+                                          uint8_t* n_executed, uint8_t* obs_packed3, void* stream) {
+  return sokoban_step_entry(2, ctx, n, H, W, num_boxes, max_steps, actions, K, n_actions, state, meta, acc_reward, done, flags,
+                            n_executed, obs_packed3, stream);
+}
+
+extern "C" int ragen_sokoban_render_packed3(ragen_ctx* ctx, int64_t n, int H, int W, const uint8_t* state,
+                                            const int16_t* meta, uint8_t* obs_packed3, void* stream) {
+  return sokoban_render_entry(2, ctx, n, H, W, state, meta, obs_packed3, stream);
 }
 
 extern "C" int ragen_sokoban_adopt(ragen_ctx* ctx, int64_t n, int H, int W, int num_boxes, const uint8_t* state,

@@ -99,6 +99,23 @@ def unpack_glyphs(packed):
     return out
 
 
+def packed3_bytes(H, W):
+    """Bytes per env of a three-bit glyph row (include/ragen_b200.h: ragen_sokoban_step_packed3)."""
+    return ((3 * H * W + 15) // 16) * 2
+
+
+def unpack3_glyphs(packed3, H, W):
+    """[n, packed3_bytes] three-bit rows -> [n, H*(W+1)] glyph codes with the row separators (code 7) put back: the same array
+    the byte and nibble formats unpack to (numpy)."""
+    p = np.ascontiguousarray(np.asarray(packed3), dtype=np.uint8)
+    n = p.shape[0]
+    bits = np.unpackbits(p, axis=1, bitorder="little")[:, : 3 * H * W].reshape(n, H * W, 3)
+    cells = (bits[..., 0] | (bits[..., 1] << 1) | (bits[..., 2] << 2)).astype(np.uint8).reshape(n, H, W)
+    out = np.full((n, H, W + 1), 7, dtype=np.uint8)
+    out[:, :, :W] = cells
+    return out.reshape(n, H * (W + 1))
+
+
 def codes_to_text(codes_row, table):
     """codes_row: 1-D uint8 numpy array of length H*(W+1); the trailing separator is dropped."""
     return "".join(table[c] for c in codes_row[:-1].tolist())
@@ -118,19 +135,24 @@ class SokobanBatch:
         self.fixed = torch.zeros((self.n, HW), dtype=torch.uint8, device=dev)
         # one 8-byte record per env (include/ragen_b200.h): player, num_env_steps, boxes_on_target|under, actual
         self.meta = torch.zeros((self.n, 4), dtype=torch.int16, device=dev)
-        # per-step results live in ONE slab [reward f64 | done | flags | n_executed | pad | packed glyph rows] so that the
-        # host-buffer path (step_host) brings a step back with a single device->host copy
+        # per-step results live in ONE slab [three-bit rows | reward f64, done, flags, n_executed | nibble rows] so that the
+        # host-buffer path (step_host) brings a step back with a single device->host copy in either packed format
         n_ = self.n
-        self._off_obs = (11 * n_ + 15) & ~15
+        self._b3 = packed3_bytes(self.H, self.W) if (self.H == self.W and self.H in (6, 8, 10)) else 0
+        self._off_sc = (n_ * self._b3 + 15) & ~15
+        self._off_obs = (self._off_sc + 11 * n_ + 15) & ~15
         self._slab_bytes = self._off_obs + (n_ * (G // 2) if G % 2 == 0 else 0)
         self._slab = torch.zeros(max(self._slab_bytes, 16), dtype=torch.uint8, device=dev)
-        self.reward = self._slab[: 8 * n_].view(torch.float64)
-        self.done = self._slab[8 * n_: 9 * n_]
-        self.flags = self._slab[9 * n_: 10 * n_]
-        self.n_executed = self._slab[10 * n_: 11 * n_]
+        o = self._off_sc
+        self.reward = self._slab[o: o + 8 * n_].view(torch.float64)
+        self.done = self._slab[o + 8 * n_: o + 9 * n_]
+        self.flags = self._slab[o + 9 * n_: o + 10 * n_]
+        self.n_executed = self._slab[o + 10 * n_: o + 11 * n_]
         self.obs = torch.zeros((self.n, G), dtype=torch.uint8, device=dev)
         # [n, G/2] two 4-bit codes per byte (needs an even G)
         self.obs_packed = self._slab[self._off_obs: self._off_obs + n_ * (G // 2)].view(n_, G // 2) if G % 2 == 0 else None
+        # [n, packed3_bytes] three bits per cell, no separators (6x6 / 8x8 / 10x10)
+        self.obs_packed3 = self._slab[: n_ * self._b3].view(n_, self._b3) if self._b3 else None
         self.obs_is_packed = False  # which of the two buffers the latest render wrote
         self.status = torch.zeros(self.n, dtype=torch.int32, device=dev)
         self._pinned = {}
@@ -260,6 +282,11 @@ class SokobanBatch:
     def can_pack(self):
         return (self.H * (self.W + 1)) % 2 == 0
 
+    def _packed3_buffer(self):
+        if self.obs_packed3 is None:
+            raise ValueError(f"three-bit glyph rows are built for 6x6, 8x8 and 10x10 rooms; room is {self.H}x{self.W}")
+        return self.obs_packed3
+
     def _packed_buffer(self):
         if self.obs_packed is None:  # lives in the result slab whenever the row stream is even
             raise ValueError(f"packed glyph rows need an even H*(W+1); room is {self.H}x{self.W}")
@@ -272,11 +299,13 @@ class SokobanBatch:
             actions = actions.unsqueeze(1)
         assert actions.dtype == torch.uint8 and actions.is_cuda and actions.is_contiguous() and actions.shape[0] == self.n
         K = actions.shape[1]
-        obs = (self._packed_buffer() if packed else self.obs) if render else None
+        fmt = 3 if (packed == 3 and packed is not True) else (1 if packed else 0)  # 0 bytes, 1 nibbles, 3 three-bit rows
+        obs = (self._packed3_buffer() if fmt == 3 else self._packed_buffer() if fmt == 1 else self.obs) if render else None
         if render:
-            self.obs_is_packed = bool(packed)
+            self.obs_is_packed = fmt if fmt else False
         self.obs_stale = not render  # texts() renders again before reading rows a step did not write
-        fn = self.lib.ragen_sokoban_step_packed if packed else self.lib.ragen_sokoban_step
+        fn = (self.lib.ragen_sokoban_step_packed3 if fmt == 3 else self.lib.ragen_sokoban_step_packed if fmt == 1
+              else self.lib.ragen_sokoban_step)
         _lib.check(fn(self.ctx.handle, self.n, self.H, self.W, self.num_boxes, self.max_steps, _lib.ptr(actions), K,
                       _lib.ptr(n_actions), _lib.ptr(self.state), _lib.ptr(self.meta), _lib.ptr(self.reward), _lib.ptr(self.done),
                       _lib.ptr(self.flags), _lib.ptr(self.n_executed), _lib.ptr(obs), self.ctx.stream()))
@@ -303,15 +332,19 @@ class SokobanBatch:
             h_na = self._pin("na", (self.n,), torch.uint8)
             h_na.numpy()[...] = n_actions_np
             d_na = h_na.to(self.device, non_blocking=True)
-        out = self.step(d_act, d_na, render=want_obs, packed=packed and want_obs)
-        if packed and want_obs:  # one copy of the whole result slab
+        out = self.step(d_act, d_na, render=want_obs, packed=(packed if want_obs else False))
+        if packed and want_obs:  # one copy: the packed rows and the scalars are neighbours in the result slab
             n_ = self.n
-            h = self._pin("slab", (self._slab_bytes,), torch.uint8)
-            h.copy_(self._slab[: self._slab_bytes], non_blocking=True)
+            three = packed == 3 and packed is not True
+            lo, hi = (0, self._off_sc + 11 * n_) if three else (self._off_sc, self._slab_bytes)
+            h = self._pin("slab3" if three else "slab", (hi - lo,), torch.uint8)
+            h.copy_(self._slab[lo:hi], non_blocking=True)
             torch.cuda.current_stream(self.device).synchronize()
             hn = h.numpy()
-            return (hn[self._off_obs:].reshape(n_, -1), hn[: 8 * n_].view(np.float64), hn[8 * n_: 9 * n_], hn[9 * n_: 10 * n_],
-                    hn[10 * n_: 11 * n_])
+            o = self._off_sc - lo
+            rows = hn[: n_ * self._b3].reshape(n_, -1) if three else hn[self._off_obs - lo:].reshape(n_, -1)
+            return (rows, hn[o: o + 8 * n_].view(np.float64), hn[o + 8 * n_: o + 9 * n_], hn[o + 9 * n_: o + 10 * n_],
+                    hn[o + 10 * n_: o + 11 * n_])
         h_rew = self._pin("rew", (self.n,), torch.float64)
         h_done = self._pin("done", (self.n,), torch.uint8)
         h_flags = self._pin("flags", (self.n,), torch.uint8)
@@ -329,10 +362,12 @@ class SokobanBatch:
 
     # -- render -----------------------------------------------------------------------------
     def render(self, packed=False):
-        obs = self._packed_buffer() if packed else self.obs
-        self.obs_is_packed = bool(packed)
+        fmt = 3 if (packed == 3 and packed is not True) else (1 if packed else 0)
+        obs = self._packed3_buffer() if fmt == 3 else self._packed_buffer() if fmt == 1 else self.obs
+        self.obs_is_packed = fmt if fmt else False
         self.obs_stale = False
-        fn = self.lib.ragen_sokoban_render_packed if packed else self.lib.ragen_sokoban_render
+        fn = (self.lib.ragen_sokoban_render_packed3 if fmt == 3 else self.lib.ragen_sokoban_render_packed if fmt == 1
+              else self.lib.ragen_sokoban_render)
         _lib.check(fn(self.ctx.handle, self.n, self.H, self.W, _lib.ptr(self.state), _lib.ptr(self.meta), _lib.ptr(obs),
                       self.ctx.stream()))
         return obs
@@ -369,6 +404,10 @@ class SokobanBatch:
         """Text observations of the latest render (all envs, or `rows`): one device->host copy + one translate per env."""
         if getattr(self, "obs_stale", False):
             self.render(packed=self.obs_is_packed)
+        if self.obs_is_packed == 3:
+            tab = glyph_table(grid_lookup)
+            rows3 = (self.obs_packed3 if rows is None else self.obs_packed3[rows]).cpu().numpy()
+            return [codes_to_text(r, tab) for r in unpack3_glyphs(rows3, self.H, self.W)]
         if self.obs_is_packed:
             pairs = glyph_pair_table(grid_lookup)
             codes = (self.obs_packed if rows is None else self.obs_packed[rows]).cpu().numpy()

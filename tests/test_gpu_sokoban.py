@@ -285,3 +285,56 @@ def test_solver_returns_the_reference_paths():
     _lib.check(ctx.lib.ragen_sokoban_solve(ctx.handle, 1, 10, 10, _lib.ptr(fixed[ok][big:big + 1].contiguous()), _lib.ptr(state[ok][big:big + 1].contiguous()),
                                            100, 64, _lib.ptr(st2), _lib.ptr(ln2), None, None, ctx.stream()))
     assert int(st2[0]) == 2 and int(ln2[0]) == 0
+
+
+@pytest.mark.parametrize("H,W,nb,n", [(6, 6, 1, 1000), (10, 10, 2, 4099), (8, 8, 2, 515), (10, 10, 2, 1), (6, 6, 1, 129)])
+def test_three_bit_glyph_rows_equal_the_byte_rows(H, W, nb, n):
+    """ragen_sokoban_step_packed3 / ragen_sokoban_render_packed3: the same step, glyph rows as three bits per cell without
+    separators.  Unpacked (separators put back) they equal the oracle's rows, code 6 (player on a target) included; the
+    host-buffer path brings rows and scalars back with one copy; other shapes are refused."""
+    from ragen_b200 import _lib
+    from ragen_b200.env.sokoban import packed3_bytes, unpack3_glyphs
+
+    fixed, state = synthetic_rooms(n, H, W, nb, seed=n + 11)
+    rng = np.random.default_rng(n + 1)
+    o = SokobanBatchOracle(fixed, state, H, W, nb, 50)
+    b = _batch(n, H, W, nb, 50)
+    b.load_rooms(fixed, state)
+    assert np.array_equal(unpack3_glyphs(b.render(packed=3).cpu().numpy(), H, W), o.glyphs())
+    saw_six = False
+    for turn in range(10):
+        K = int(rng.integers(1, 4))
+        acts = rng.integers(0, 5, (n, K)).astype(np.uint8)
+        acc, done, flags, nexec = o.step_turn(acts, None)
+        out = b.step(torch.from_numpy(acts).cuda(), packed=3)
+        assert out.obs.shape == (n, packed3_bytes(H, W))
+        assert np.array_equal(b.state.cpu().numpy(), o.state)
+        assert np.array_equal(out.reward.cpu().numpy(), acc) and np.array_equal(out.flags.cpu().numpy(), flags)
+        got = unpack3_glyphs(out.obs.cpu().numpy(), H, W)
+        assert np.array_equal(got, o.glyphs())
+        saw_six = saw_six or bool((got == 6).any())
+    assert saw_six or n < 100
+    t3 = b.texts(S.DEFAULT_GLYPHS)[:32]  # decoded from the three-bit rows
+    b.render()
+    assert t3 == b.texts(S.DEFAULT_GLYPHS)[:32]  # the byte rows' text
+    acts = rng.integers(1, 5, n).astype(np.uint8)
+    acc, done, flags, nexec = o.step_turn(acts[:, None], None)
+    h_obs, h_rew, h_done, h_flags, h_nex = b.step_host(acts, packed=3)
+    assert np.array_equal(unpack3_glyphs(h_obs, H, W), o.glyphs())
+    assert np.array_equal(h_rew, acc) and np.array_equal(h_done, done) and np.array_equal(h_flags, flags) and np.array_equal(h_nex, nexec)
+    # the nibble path still comes back right through the shared slab
+    acc, done, flags, nexec = o.step_turn(acts[:, None], None)
+    h_obs, h_rew, h_done, h_flags, h_nex = b.step_host(acts, packed=True)
+    from ragen_b200.env.sokoban import unpack_glyphs
+    assert np.array_equal(unpack_glyphs(h_obs), o.glyphs()) and np.array_equal(h_rew, acc) and np.array_equal(h_flags, flags)
+
+
+def test_three_bit_rows_refuse_other_shapes():
+    from ragen_b200 import _lib
+
+    b = _batch(4, 7, 6, 1, 50)
+    with pytest.raises(ValueError):
+        b.render(packed=3)
+    buf = torch.zeros(4 * 16, dtype=torch.uint8, device="cuda")
+    rc = b.lib.ragen_sokoban_render_packed3(b.ctx.handle, 4, 7, 6, _lib.ptr(b.state), _lib.ptr(b.meta), _lib.ptr(buf), b.ctx.stream())
+    assert rc != 0

@@ -13,7 +13,7 @@ flush is needed between timed iterations.
 `value`   : device-timed (CUDA events, max over ranks), inputs resident in HBM.
 `e2e`     : same step through SokobanBatch.step_host — the actions come from pinned HOST memory and the
             reward / done / flags / n_executed / glyph rows go back to pinned HOST memory inside the timed region.
-            The glyph rows travel as two 4-bit codes per byte (--obs packed, the default; --obs bytes = one code per byte).
+            The glyph rows travel as three bits per cell (--obs packed3, the default; --obs packed = two 4-bit codes per byte, --obs bytes = one code per byte).
 `roofline`: algorithmic bytes per env-step (431 B for 10x10) x envs / mean launch time.
 `cpu_baseline` / `--impl reference`: the reference's execution model (one Python env object per env,
             serial step loop, text render per step — oracle/sokoban.py, a port because gym_sokoban is not
@@ -48,7 +48,7 @@ def parse_args():
     ap.add_argument("--ref-envs", type=int, default=0, help="envs per reference step (0 = auto from core count)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--obs", default="packed", choices=["packed", "bytes"],
+    ap.add_argument("--obs", default="packed3", choices=["packed3", "packed", "bytes"],
                     help="glyph-row format of the render: two 4-bit codes per byte (what the managers consume) or one code per byte")
     ap.add_argument("--rows", action="store_true", help="per-kernel lines for every SURVEY.md 8(d) config instead of the contract line")
     ap.add_argument("--quick", action="store_true", help="with --rows: smaller batches")
@@ -57,7 +57,9 @@ def parse_args():
 
 
 def workload_config(n_gpus, envs_per_gpu, obs="packed"):
-    return {"glyph_rows": "two 4-bit glyph codes per byte (55 B per env)" if obs == "packed" else "one glyph code per byte (110 B per env)",
+    rows = {"packed3": "three bits per cell, no separators (38 B per env; ragen_sokoban_step_packed3)",
+            "packed": "two 4-bit glyph codes per byte (55 B per env)", "bytes": "one glyph code per byte (110 B per env)"}[obs]
+    return {"glyph_rows": rows,
             "workload": "sokoban_10x10_2box_step_render_reward", "dim_room": [H, W], "num_boxes": NUM_BOXES,
             "max_steps": MAX_STEPS, "envs_per_gpu": envs_per_gpu, "envs_total": envs_per_gpu * n_gpus,
             "actions_per_launch": 1, "rooms": "synthetic random-walk rooms (ragen_b200/synth.py)",
@@ -264,7 +266,9 @@ def run_native(args):
         sampler.start()
 
     # ---- device-resident timing -------------------------------------------------------------------
-    packed = args.obs == "packed"
+    packed = {"packed3": 3, "packed": True, "bytes": False}[args.obs]
+    G = H * (W + 1)
+    row_bytes = {"packed3": ((3 * H * W + 15) // 16) * 2, "packed": G // 2, "bytes": G}[args.obs]
     for i in range(args.warmup):
         batch.step(actions[i % R], packed=packed)
     t_begin, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -300,10 +304,9 @@ def run_native(args):
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_s = float(t.item())
-        G = H * (W + 1)
         e2e = {"value": n * world * args.steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": n * 1,
-               "d2h_bytes_per_step": n * ((G // 2 if packed else G) + 8 + 1 + 1 + 1), "ms_per_step": 1e3 * e2e_s / args.steps,
-               "api": "SokobanBatch.step_host -> ragen_sokoban_step (C ABI), pinned host buffers", "host_numa": numa}
+               "d2h_bytes_per_step": n * (row_bytes + 8 + 1 + 1 + 1), "ms_per_step": 1e3 * e2e_s / args.steps,
+               "api": "SokobanBatch.step_host -> ragen_sokoban_step%s (C ABI), pinned host buffers, one device->host copy" % {"packed3": "_packed3", "packed": "_packed", "bytes": ""}[args.obs], "host_numa": numa}
 
     clocks = sampler.stop() if rank == 0 else None
     if rank == 0:
@@ -316,19 +319,20 @@ def run_native(args):
         traffic = None
         tpath = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(tpath):
-            traffic = json.load(open(tpath)).get("sokoban_step_packed_bytes_per_launch" if packed else "sokoban_step_bytes_per_launch")
-        moved = MOVED_PER_STEP - (H * (W + 1)) // 2 if packed else MOVED_PER_STEP
+            traffic = json.load(open(tpath)).get({"packed3": "sokoban_step_packed3_bytes_per_launch", "packed": "sokoban_step_packed_bytes_per_launch",
+                                                  "bytes": "sokoban_step_bytes_per_launch"}[args.obs])
+        moved = MOVED_PER_STEP - G + row_bytes
         line = {"metric": METRIC, "value": n * world * args.steps / (total_ms * 1e-3), "unit": UNIT, "n_gpus": world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
                 "config": workload_config(world, n, args.obs), "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                             "traffic": traffic, "kernel": "sokoban_tile_kernel<10,10,false,%s>" % ("true" if packed else "false"), "kernel_ms": kern_ms,
+                             "traffic": traffic, "kernel": "sokoban_tile_kernel<10,10,false,%d>" % {"packed3": 2, "packed": 1, "bytes": 0}[args.obs], "kernel_ms": kern_ms,
                              "bytes_per_env_step": BYTES_PER_STEP, "peak_source": peak_src,
                              "bytes_moved_per_env_step": moved, "frac_moved": moved * n / (kern_ms * 1e-3) / 1e9 / peak,
                              "note": "frac uses SURVEY.md 8(d)'s 431 B per env-step, which charges a 100 B room_fixed read the kernel "
                                      "avoids and 110 B of glyph rows; frac_moved uses the bytes this kernel has to move "
-                                     "(338 B with byte glyph rows, 283 B with packed ones)"}}
+                                     "(338 B with byte glyph rows, 283 B with nibble rows, 266 B with three-bit rows)"}}
         if cpu_base is not None:
             line["cpu_baseline"] = cpu_base
         print(json.dumps(line), file=out, flush=True)

@@ -20,16 +20,16 @@ def main():
     g = torch.Generator(device="cuda").manual_seed(1)
     acts = torch.randint(1, 5, (4, n, K), dtype=torch.uint8, device="cuda", generator=g)
     for i in range(5):
-        b.step(acts[i % 4], packed=bool(packed))
+        b.step(acts[i % 4], packed=(3 if packed == 3 else bool(packed)))
     torch.cuda.synchronize()
     s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     s.record()
     for i in range(reps):
-        b.step(acts[i % 4], packed=bool(packed))
+        b.step(acts[i % 4], packed=(3 if packed == 3 else bool(packed)))
     e.record()
     torch.cuda.synchronize()
     us = 1e3 * s.elapsed_time(e) / reps
-    moved = 2 * H * W + 16 + 11 + (H * (W + 1) // 2 if packed else H * (W + 1)) + K
+    moved = 2 * H * W + 16 + 11 + (((3 * H * W + 15) // 16) * 2 if packed == 3 else H * (W + 1) // 2 if packed else H * (W + 1)) + K
     print(f"{H}x{W} n={n} K={K} packed={packed}: {us:.1f} us/launch, {n * K / us * 1e6:.3e} env-steps/s, "
           f"{n * moved / us * 1e-3:.0f} GB/s on the {moved} B/env this launch moves")
 

@@ -259,7 +259,7 @@ def run_native(args):
     g = torch.Generator(device=dev)
     g.manual_seed(1234 + rank)
     actions = torch.randint(1, 5, (R, n), dtype=torch.uint8, device=dev, generator=g)
-    host_actions = actions.cpu().numpy()
+    host_actions = actions.cpu().pin_memory()  # the step's inputs live in pinned host memory (contract); step_host copies them up as they are
 
     sampler = ClockSampler(physical_gpu_index(local_rank))
     if rank == 0:

@@ -321,11 +321,14 @@ class SokobanBatch:
         """End-to-end call with HOST buffers: actions go host->device, the step runs, and reward /
         done / flags / n_executed (and the glyph rows; packed=True: two codes per byte, see glyph_pair_table) come back
         device->host.  Returns numpy views of pinned staging buffers (valid until the next call)."""
-        a = np.ascontiguousarray(actions_np, dtype=np.uint8)
-        if a.ndim == 1:
-            a = a[:, None]
-        h_act = self._pin("act", a.shape, torch.uint8)
-        h_act.numpy()[...] = a
+        if isinstance(actions_np, torch.Tensor) and actions_np.dtype == torch.uint8 and actions_np.is_contiguous() and actions_np.is_pinned():
+            h_act = actions_np if actions_np.dim() == 2 else actions_np.unsqueeze(1)  # already pinned host memory: no staging copy
+        else:
+            a = np.ascontiguousarray(actions_np, dtype=np.uint8)
+            if a.ndim == 1:
+                a = a[:, None]
+            h_act = self._pin("act", a.shape, torch.uint8)
+            h_act.numpy()[...] = a
         d_act = h_act.to(self.device, non_blocking=True)
         d_na = None
         if n_actions_np is not None:

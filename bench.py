@@ -50,16 +50,18 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--obs", default="packed3", choices=["packed3", "packed", "bytes"],
                     help="glyph-row format of the render: two 4-bit codes per byte (what the managers consume) or one code per byte")
+    ap.add_argument("--rooms", default="bytes", choices=["nibbles", "bytes"],
+                    help="how the rooms rest in HBM: one cell per byte, or two (ragen_sokoban_step_compact; needs --obs packed3)")
     ap.add_argument("--rows", action="store_true", help="per-kernel lines for every SURVEY.md 8(d) config instead of the contract line")
     ap.add_argument("--quick", action="store_true", help="with --rows: smaller batches")
     ap.add_argument("--only", default="", help="with --rows: comma list of sokoban,generator,frozenlake,parse,c5,manager,rollout")
     return ap.parse_args()
 
 
-def workload_config(n_gpus, envs_per_gpu, obs="packed"):
+def workload_config(n_gpus, envs_per_gpu, obs="packed", rooms="bytes"):
     rows = {"packed3": "three bits per cell, no separators (38 B per env; ragen_sokoban_step_packed3)",
             "packed": "two 4-bit glyph codes per byte (55 B per env)", "bytes": "one glyph code per byte (110 B per env)"}[obs]
-    return {"glyph_rows": rows,
+    return {"glyph_rows": rows, "rooms_in_hbm": "two cells per byte (ragen_sokoban_step_compact)" if rooms == "nibbles" else "one cell per byte",
             "workload": "sokoban_10x10_2box_step_render_reward", "dim_room": [H, W], "num_boxes": NUM_BOXES,
             "max_steps": MAX_STEPS, "envs_per_gpu": envs_per_gpu, "envs_total": envs_per_gpu * n_gpus,
             "actions_per_launch": 1, "rooms": "synthetic random-walk rooms (ragen_b200/synth.py)",
@@ -134,7 +136,7 @@ def run_reference(args):
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": workload_config(args.gpus, args.envs, args.obs),
+            "config": workload_config(args.gpus, args.envs, args.obs, args.rooms),
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -253,7 +255,10 @@ def run_native(args):
 
     n = args.envs
     fixed, state = synthetic_rooms(n, H, W, NUM_BOXES, seed=4 + rank)
-    batch = SokobanBatch(n, (H, W), NUM_BOXES, MAX_STEPS, device=local_rank)
+    compact = args.rooms == "nibbles"
+    if compact and args.obs != "packed3":
+        raise SystemExit("--rooms nibbles renders three-bit rows: use --obs packed3")
+    batch = SokobanBatch(n, (H, W), NUM_BOXES, MAX_STEPS, device=local_rank, compact=compact)
     batch.load_rooms(fixed, state)
     R = 8  # rotating action slabs, all resident in HBM
     g = torch.Generator(device=dev)
@@ -306,7 +311,7 @@ def run_native(args):
         e2e_s = float(t.item())
         e2e = {"value": n * world * args.steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": n * 1,
                "d2h_bytes_per_step": n * (row_bytes + 8 + 1 + 1 + 1), "ms_per_step": 1e3 * e2e_s / args.steps,
-               "api": "SokobanBatch.step_host -> ragen_sokoban_step%s (C ABI), pinned host buffers, one device->host copy" % {"packed3": "_packed3", "packed": "_packed", "bytes": ""}[args.obs], "host_numa": numa}
+               "api": "SokobanBatch.step_host -> ragen_sokoban_step%s (C ABI), pinned host buffers, one device->host copy" % ("_compact" if compact else {"packed3": "_packed3", "packed": "_packed", "bytes": ""}[args.obs]), "host_numa": numa}
 
     clocks = sampler.stop() if rank == 0 else None
     if rank == 0:
@@ -319,20 +324,21 @@ def run_native(args):
         traffic = None
         tpath = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(tpath):
-            traffic = json.load(open(tpath)).get({"packed3": "sokoban_step_packed3_bytes_per_launch", "packed": "sokoban_step_packed_bytes_per_launch",
+            traffic = json.load(open(tpath)).get("sokoban_step_compact_bytes_per_launch" if compact else
+                                                 {"packed3": "sokoban_step_packed3_bytes_per_launch", "packed": "sokoban_step_packed_bytes_per_launch",
                                                   "bytes": "sokoban_step_bytes_per_launch"}[args.obs])
-        moved = MOVED_PER_STEP - G + row_bytes
+        moved = MOVED_PER_STEP - G + row_bytes - (H * W if compact else 0)
         line = {"metric": METRIC, "value": n * world * args.steps / (total_ms * 1e-3), "unit": UNIT, "n_gpus": world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-                "config": workload_config(world, n, args.obs), "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
+                "config": workload_config(world, n, args.obs, args.rooms), "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                             "traffic": traffic, "kernel": "sokoban_tile_kernel<10,10,false,%d>" % {"packed3": 2, "packed": 1, "bytes": 0}[args.obs], "kernel_ms": kern_ms,
+                             "traffic": traffic, "kernel": "sokoban_tile_kernel<10,10,false,%d>" % (3 if compact else {"packed3": 2, "packed": 1, "bytes": 0}[args.obs]), "kernel_ms": kern_ms,
                              "bytes_per_env_step": BYTES_PER_STEP, "peak_source": peak_src,
                              "bytes_moved_per_env_step": moved, "frac_moved": moved * n / (kern_ms * 1e-3) / 1e9 / peak,
                              "note": "frac uses SURVEY.md 8(d)'s 431 B per env-step, which charges a 100 B room_fixed read the kernel "
                                      "avoids and 110 B of glyph rows; frac_moved uses the bytes this kernel has to move "
-                                     "(338 B with byte glyph rows, 283 B with nibble rows, 266 B with three-bit rows)"}}
+                                     "(338 B with byte glyph rows, 283 B with nibble rows, 266 B with three-bit rows, 166 B with the rooms kept as nibbles too)"}}
         if cpu_base is not None:
             line["cpu_baseline"] = cpu_base
         print(json.dumps(line), file=out, flush=True)

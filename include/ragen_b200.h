@@ -97,6 +97,16 @@ int ragen_sokoban_step_packed3(ragen_ctx* ctx, int64_t n, int H, int W, int num_
                                uint8_t* state, int16_t* meta,
                                double* acc_reward, uint8_t* done, uint8_t* flags, uint8_t* n_executed,
                                uint8_t* obs_packed3, void* stream);
+/* The step with the rooms kept as NIBBLES in HBM: state4 [n][H*W/2], cell 2i in the low nibble of byte i (cells are
+ * 0..5) - half the bytes of the dominant read-modify-write of a step; the tile is staged, stepped and rendered in that
+ * form.  Glyph rows come out three-bit (obs_packed3, may be NULL).  Everything else as ragen_sokoban_step
+ * (SokobanEnv.step, ragen/env/sokoban/env.py:44-60).  6x6, 8x8 and 10x10 rooms (other shapes: RAGEN_EINVAL).  The caller
+ * converts between state and state4 when rooms are loaded / inspected (SokobanBatch(compact=True) does). */
+int ragen_sokoban_step_compact(ragen_ctx* ctx, int64_t n, int H, int W, int num_boxes, int max_steps,
+                               const uint8_t* actions, int K, const uint8_t* n_actions,
+                               uint8_t* state4, int16_t* meta,
+                               double* acc_reward, uint8_t* done, uint8_t* flags, uint8_t* n_executed,
+                               uint8_t* obs_packed3, void* stream);
 int ragen_sokoban_render_packed3(ragen_ctx* ctx, int64_t n, int H, int W, const uint8_t* state,
                                  const int16_t* meta, uint8_t* obs_packed3, void* stream);
 

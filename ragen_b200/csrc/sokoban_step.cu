@@ -218,18 +218,17 @@ __device__ __forceinline__ void render_env_packed(const uint8_t* s_state, uint8_
 // Three-bit glyph rows (ragen_sokoban_step_packed3): the H*W cell codes (0..6 fit three bits), row-major, NO separators (the
 // host knows W), little-endian bit stream padded to an even number of bytes per env - 38 B for 10x10 instead of 55 B of
 // nibbles: the format for bulk transport to the host, where the device->host link is what bounds the step.
+// cw: the env's cell-nibble stream; word fix_word (or none: -1) is xor-ed with fix_xor first (player 5 -> player on target 6)
 template <int CH, int CW>
-__device__ __forceinline__ void render_env_packed3(const uint8_t* s_state, uint8_t* s_obs, int e) {
+__device__ __forceinline__ void pack3_store(const uint32_t (&cw)[(CH * CW + 7) / 8 + 1], int fix_word, uint32_t fix_xor,
+                                            uint8_t* s_obs, int e) {
   constexpr int HW = CH * CW, NCW = (HW + 7) / 8;
   constexpr int B = ((HW * 3 + 15) / 16) * 2;  // bytes per env
   constexpr int NOW = (B + 3) / 4;
-  static_assert(HW % 4 == 0, "shape not supported by the per-env render");
-  uint32_t cw[NCW + 1];
-  cell_nibbles<HW>(reinterpret_cast<const uint32_t*>(s_state) + e * (HW / 4), cw);
   uint32_t g24[NCW];  // 8 cells -> 24 bits
 #pragma unroll
   for (int j = 0; j < NCW; ++j) {
-    const uint32_t x = cw[j];
+    const uint32_t x = cw[j] ^ (j == fix_word ? fix_xor : 0u);
     const uint32_t pr = (x & 0x07070707u) | (((x >> 4) & 0x07070707u) << 3);  // per byte: cell 2i | cell 2i+1 << 3
     g24[j] = (pr & 0x3fu) | ((pr >> 2) & 0xfc0u) | ((pr >> 4) & 0x3f000u) | ((pr >> 6) & 0xfc0000u);
   }
@@ -247,10 +246,39 @@ __device__ __forceinline__ void render_env_packed3(const uint8_t* s_state, uint8
   store_env_stream<B, NOW>(out, s_obs, e);
 }
 
+template <int CH, int CW>
+__device__ __forceinline__ void render_env_packed3(const uint8_t* s_state, uint8_t* s_obs, int e) {
+  constexpr int HW = CH * CW, NCW = (HW + 7) / 8;
+  static_assert(HW % 4 == 0, "shape not supported by the per-env render");
+  uint32_t cw[NCW + 1];
+  cell_nibbles<HW>(reinterpret_cast<const uint32_t*>(s_state) + e * (HW / 4), cw);
+  pack3_store<CH, CW>(cw, -1, 0u, s_obs, e);
+}
+
+// Rooms kept as NIBBLES in HBM (ragen_sokoban_step_compact): a room's bytes ARE the cell-nibble stream the three-bit render
+// starts from, so env e's H*W/2 bytes of the staged tile go straight into registers.  Rows of 50 (18) bytes are only 2-byte
+// aligned: aligned words + one funnel shift; the cells past H*W in the last word belong to the next env and are masked off.
+template <int HW>
+__device__ __forceinline__ void load_env_nibbles(const uint8_t* s_tile4, int e, uint32_t (&cw)[(HW + 7) / 8 + 1]) {
+  constexpr int B = HW / 2, NCW = (HW + 7) / 8;
+  constexpr bool ALIGNED = (B % 4 == 0);
+  const int a = ALIGNED ? 0 : ((e * B) & 3);
+  const uint32_t* src = reinterpret_cast<const uint32_t*>(s_tile4 + e * B - a);
+  uint32_t raw[NCW + 1];
+#pragma unroll
+  for (int k = 0; k <= NCW; ++k) raw[k] = (ALIGNED && k == NCW) ? 0u : src[k];  // may read one word past the row: the tile is padded
+#pragma unroll
+  for (int j = 0; j < NCW; ++j) cw[j] = ALIGNED ? raw[j] : __funnelshift_r(raw[j], raw[j + 1], a << 3);
+  if (HW % 8 != 0) cw[NCW - 1] &= (1u << (4 * (HW % 8))) - 1u;
+  cw[NCW] = 0u;
+}
+
 // PACK: glyph-row format - 0 one code per byte, 1 two 4-bit codes per byte, 2 three bits per cell without separators
 template <int CH, int CW, bool RENDER_ONLY, int PACK>
 __global__ void __launch_bounds__(TE) sokoban_tile_kernel(const StepParams p) {
-  constexpr bool PACKED = (PACK == 1), PACK3 = (PACK == 2);
+  // PACK 3 = "compact": three-bit rows out AND rooms kept as nibbles in HBM (p.state is then uint8 [n][H*W/2]); the tile is
+  // staged, stepped and rendered in that form
+  constexpr bool PACKED = (PACK == 1), PACK3 = (PACK == 2 || PACK == 3), STATE4 = (PACK == 3);
   const int H = CH ? CH : p.H, W = CW ? CW : p.W;
   const int HW = H * W, G = H * (W + 1);
   const int B3 = ((HW * 3 + 15) / 16) * 2;  // bytes of a three-bit row stream
@@ -258,15 +286,15 @@ __global__ void __launch_bounds__(TE) sokoban_tile_kernel(const StepParams p) {
   __shared__ __align__(8) uint64_t bar;
 
   uint8_t* s_state = smem;
-  uint8_t* s_obs = s_state + round16(TE * HW) + 16;  // +16: the render window may read one word past the tile
+  uint8_t* s_obs = s_state + round16(STATE4 ? (TE * HW) >> 1 : TE * HW) + 16;  // +16: the render window may read one word past the tile
 
   const int64_t env0 = (int64_t)blockIdx.x * TE;
   const int cnt = (int)min((int64_t)TE, p.n - env0);
-  const int room_bytes = cnt * HW;
+  const int room_bytes = STATE4 ? (cnt * HW) >> 1 : cnt * HW;  // bytes of the tile in HBM
   const int obs_bytes = PACK3 ? cnt * B3 : PACKED ? (cnt * G) >> 1 : cnt * G;  // PACKED needs an even G (checked at launch)
   const bool bulk_rooms = (room_bytes & 15) == 0;
   const bool bulk_obs = (obs_bytes & 15) == 0;
-  uint8_t* g_state = p.state + env0 * HW;
+  uint8_t* g_state = p.state + (STATE4 ? (env0 * HW) >> 1 : env0 * HW);
 
   // ---- stage the tile: HBM -> shared memory -------------------------------------------------
   if (bulk_rooms) {
@@ -308,7 +336,17 @@ __global__ void __launch_bounds__(TE) sokoban_tile_kernel(const StepParams p) {
   int pos = m.player;
   int under = m.under;
   if (!RENDER_ONLY && mine) {
-    uint8_t* S = s_state + e * HW;
+    uint8_t* S = s_state + (STATE4 ? (e * HW) >> 1 : e * HW);
+    // cell i of the own room: a byte, or (STATE4) nibble i&1 of byte i>>1 - rooms are whole bytes, nobody else touches them
+    auto cell = [&](int i) -> int { return STATE4 ? (S[i >> 1] >> ((i & 1) << 2)) & 15 : S[i]; };
+    auto put = [&](int i, int v) {
+      if (STATE4) {
+        const int o = S[i >> 1];
+        S[i >> 1] = (uint8_t)((i & 1) ? (o & 0x0f) | (v << 4) : (o & 0xf0) | v);
+      } else {
+        S[i] = (uint8_t)v;
+      }
+    };
     int steps = m.steps;
     int on = m.on_target;    // the reference's stored count
     int actual = m.actual;   // the true count of the board; differs from `on` only right after a reset
@@ -323,22 +361,22 @@ __global__ void __launch_bounds__(TE) sokoban_tile_kernel(const StepParams p) {
         const int mag = (a <= 2) ? W : 1;          // 1 up, 2 down, 3 left, 4 right (config.py:12) without a jump table
         const int d = (a & 1) ? -mag : mag;
         const int ahead = pos + d;  // in-grid: the border is wall (checked by adopt), the player never stands on it
-        const int sa = S[ahead];
+        const int sa = cell(ahead);
         bool go = (sa == 1) | (sa == 2);
         if (sa == 3 || sa == 4) {
           const int beyond = ahead + d;
           if (beyond >= 0 && beyond < HW) {
-            const int sb = S[beyond];
+            const int sb = cell(beyond);
             if (sb == 1 || sb == 2) {
-              S[beyond] = (sb == 2) ? 3 : 4;
+              put(beyond, (sb == 2) ? 3 : 4);
               delta = (int)(sb == 2) - (int)(sa == 3);
               go = true;
             }
           }
         }
         if (go) {
-          S[ahead] = 5;
-          S[pos] = under ? 2 : 1;  // == room_fixed[pos]
+          put(ahead, 5);
+          put(pos, under ? 2 : 1);  // == room_fixed[pos]
           under = (sa == 2) | (sa == 3);
           pos = ahead;
         }
@@ -373,12 +411,21 @@ __global__ void __launch_bounds__(TE) sokoban_tile_kernel(const StepParams p) {
   // own step: no CTA-wide barrier between step and render, and the player-on-target patch touches only the owner's bytes
   constexpr bool ENV_RENDER =
       PACK != 0 && CH != 0 && CW != 0 && ((CH * CW) % 4 == 0) && (PACK3 || ((CH * (CW + 1)) % 2 == 0)) && CW >= 6;
-  if (ENV_RENDER && PACK3 && p.obs && mine) {
+  if constexpr (ENV_RENDER && STATE4) {
+    if (p.obs && mine) {
+      uint32_t cw[(CH * CW + 7) / 8 + 1];
+      load_env_nibbles<CH * CW>(s_state, e, cw);
+      // player standing on a target (env.py:55): code 5 -> 6 in the word of the cell stream that holds the player
+      const bool fix = under && pos >= 0;
+      pack3_store<CH, CW>(cw, fix ? (pos >> 3) : -1, 3u << (4 * (pos & 7)), s_obs, e);
+    }
+  }
+  if (ENV_RENDER && PACK3 && !STATE4 && p.obs && mine) {
     // three-bit rows: the player-on-target code 6 is put into the room for the duration of the render (the room's bulk store
     // is issued after the barrier below, and the cell is the owner's)
     const bool patch = under && pos >= 0;
     if (patch) s_state[e * HW + pos] = 6;
-    if constexpr (ENV_RENDER && PACK3) render_env_packed3<CH, CW>(s_state, s_obs, e);
+    if constexpr (ENV_RENDER && PACK3 && !STATE4) render_env_packed3<CH, CW>(s_state, s_obs, e);
     if (patch) s_state[e * HW + pos] = 5;
   }
   if (ENV_RENDER && PACKED && p.obs && mine) {
@@ -506,15 +553,15 @@ __global__ void __launch_bounds__(TE) sokoban_adopt_kernel(const AdoptParams p) 
 }
 
 size_t tile_smem(int H, int W, int pack) {
-  const int glyph_bytes = pack == 2 ? TE * (((H * W * 3 + 15) / 16) * 2) : pack == 1 ? (TE * H * (W + 1)) >> 1 : TE * H * (W + 1);
-  return (size_t)round16(TE * H * W) + 16 + round16(glyph_bytes) + 16;
+  const int glyph_bytes = pack >= 2 ? TE * (((H * W * 3 + 15) / 16) * 2) : pack == 1 ? (TE * H * (W + 1)) >> 1 : TE * H * (W + 1);
+  return (size_t)round16(pack == 3 ? TE * H * W / 2 : TE * H * W) + 16 + round16(glyph_bytes) + 16;
 }
 
 template <bool RENDER_ONLY, int PACK>
 int launch_tiles(ragen_ctx* ctx, const StepParams& p, cudaStream_t stream) {
   RAGEN_REQUIRE(PACK != 1 || ((p.H * (p.W + 1)) & 1) == 0, "packed glyph rows need an even H*(W+1), got %dx%d", p.H, p.W);
-  RAGEN_REQUIRE(PACK != 2 || (p.H == p.W && (p.H == 6 || p.H == 8 || p.H == 10)),
-                "three-bit glyph rows are built for 6x6, 8x8 and 10x10 rooms, got %dx%d", p.H, p.W);
+  RAGEN_REQUIRE(PACK < 2 || (p.H == p.W && (p.H == 6 || p.H == 8 || p.H == 10)),
+                "three-bit glyph rows and nibble rooms are built for 6x6, 8x8 and 10x10 rooms, got %dx%d", p.H, p.W);
   const size_t smem = tile_smem(p.H, p.W, PACK);
   RAGEN_REQUIRE(smem <= 227 * 1024, "room %dx%d does not fit the shared-memory tile (%zu B)", p.H, p.W, smem);
   const unsigned grid = (unsigned)((p.n + TE - 1) / TE);
@@ -527,7 +574,7 @@ int launch_tiles(ragen_ctx* ctx, const StepParams& p, cudaStream_t stream) {
   if (p.H == 6 && p.W == 6) RAGEN_TILE_LAUNCH(6, 6);
   else if (p.H == 8 && p.W == 8) RAGEN_TILE_LAUNCH(8, 8);
   else if (p.H == 10 && p.W == 10) RAGEN_TILE_LAUNCH(10, 10);
-  else if constexpr (PACK != 2) RAGEN_TILE_LAUNCH(0, 0);
+  else if constexpr (PACK < 2) RAGEN_TILE_LAUNCH(0, 0);
 #undef RAGEN_TILE_LAUNCH
   RAGEN_LAUNCHED(ctx);
   return RAGEN_OK;
@@ -556,7 +603,8 @@ int sokoban_step_entry(int pack, ragen_ctx* ctx, int64_t n, int H, int W, int nu
   DeviceGuard guard(ctx->device);
   StepParams p{n, H, W, num_boxes, max_steps, K, actions, n_actions, state, reinterpret_cast<EnvMeta*>(meta),
                acc_reward, done, flags, n_executed, obs};
-  return pack == 2   ? launch_tiles<false, 2>(ctx, p, (cudaStream_t)stream)
+  return pack == 3   ? launch_tiles<false, 3>(ctx, p, (cudaStream_t)stream)
+         : pack == 2 ? launch_tiles<false, 2>(ctx, p, (cudaStream_t)stream)
          : pack == 1 ? launch_tiles<false, 1>(ctx, p, (cudaStream_t)stream)
                      : launch_tiles<false, 0>(ctx, p, (cudaStream_t)stream);
 }
@@ -613,6 +661,14 @@ extern "C" int ragen_sokoban_step_packed3(ragen_ctx* ctx, int64_t n, int H, int 
                                           int16_t* meta, double* acc_reward, uint8_t* done, uint8_t* flags,
                                           uint8_t* n_executed, uint8_t* obs_packed3, void* stream) {
   return sokoban_step_entry(2, ctx, n, H, W, num_boxes, max_steps, actions, K, n_actions, state, meta, acc_reward, done, flags,
+                            n_executed, obs_packed3, stream);
+}
+
+extern "C" int ragen_sokoban_step_compact(ragen_ctx* ctx, int64_t n, int H, int W, int num_boxes, int max_steps,
+                                          const uint8_t* actions, int K, const uint8_t* n_actions, uint8_t* state4,
+                                          int16_t* meta, double* acc_reward, uint8_t* done, uint8_t* flags,
+                                          uint8_t* n_executed, uint8_t* obs_packed3, void* stream) {
+  return sokoban_step_entry(3, ctx, n, H, W, num_boxes, max_steps, actions, K, n_actions, state4, meta, acc_reward, done, flags,
                             n_executed, obs_packed3, stream);
 }
 

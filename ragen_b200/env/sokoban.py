@@ -122,7 +122,7 @@ def codes_to_text(codes_row, table):
 
 
 class SokobanBatch:
-    def __init__(self, n, dim_room=(6, 6), num_boxes=1, max_steps=100, search_depth=300, device=0):
+    def __init__(self, n, dim_room=(6, 6), num_boxes=1, max_steps=100, search_depth=300, device=0, compact=False):
         self.ctx = _lib.Context.get(device)
         self.lib = self.ctx.lib
         self.device = torch.device("cuda", int(device))
@@ -131,7 +131,15 @@ class SokobanBatch:
         self.num_boxes, self.max_steps, self.search_depth = int(num_boxes), int(max_steps), int(search_depth)
         HW, G = self.H * self.W, self.H * (self.W + 1)
         dev = self.device
-        self.state = torch.zeros((self.n, HW), dtype=torch.uint8, device=dev)
+        # compact=True: the rooms live in HBM as nibbles (state4 [n, HW/2], cell 2i in the low nibble of byte i) and are stepped by
+        # ragen_sokoban_step_compact - half the bytes of a step's dominant read-modify-write.  `state` stays the byte view every
+        # other consumer sees; it is refreshed from state4 when read after a step and packed into state4 by adopt().
+        self.compact = bool(compact)
+        if self.compact and not (self.H == self.W and self.H in (6, 8, 10)):
+            raise ValueError(f"compact rooms are built for 6x6, 8x8 and 10x10; room is {self.H}x{self.W}")
+        self._state = torch.zeros((self.n, HW), dtype=torch.uint8, device=dev)
+        self.state4 = torch.zeros((self.n, HW // 2), dtype=torch.uint8, device=dev) if self.compact else None
+        self._state_stale = False
         self.fixed = torch.zeros((self.n, HW), dtype=torch.uint8, device=dev)
         # one 8-byte record per env (include/ragen_b200.h): player, num_env_steps, boxes_on_target|under, actual
         self.meta = torch.zeros((self.n, 4), dtype=torch.int16, device=dev)
@@ -156,6 +164,15 @@ class SokobanBatch:
         self.obs_is_packed = False  # which of the two buffers the latest render wrote
         self.status = torch.zeros(self.n, dtype=torch.int32, device=dev)
         self._pinned = {}
+
+    @property
+    def state(self):
+        """room_state as uint8 [n, H*W] (the reference's cell codes)."""
+        if self._state_stale:
+            self._state[:, 0::2] = self.state4 & 15
+            self._state[:, 1::2] = self.state4 >> 4
+            self._state_stale = False
+        return self._state
 
     # views of the per-env record (reference attribute names)
     @property
@@ -264,6 +281,9 @@ class SokobanBatch:
         return solve_rooms(f, s, (self.H, self.W), self.num_boxes, max_depth, self.device.index, want_path)
 
     def adopt(self, check=True):
+        if self.compact:
+            st = self.state
+            torch.bitwise_or(st[:, 0::2], st[:, 1::2] << 4, out=self.state4)
         _lib.check(self.lib.ragen_sokoban_adopt(
             self.ctx.handle, self.n, self.H, self.W, self.num_boxes, _lib.ptr(self.state), _lib.ptr(self.fixed),
             _lib.ptr(self.meta), _lib.ptr(self.status), self.ctx.stream()))
@@ -300,6 +320,19 @@ class SokobanBatch:
         assert actions.dtype == torch.uint8 and actions.is_cuda and actions.is_contiguous() and actions.shape[0] == self.n
         K = actions.shape[1]
         fmt = 3 if (packed == 3 and packed is not True) else (1 if packed else 0)  # 0 bytes, 1 nibbles, 3 three-bit rows
+        if self.compact:
+            if render and fmt != 3:
+                raise ValueError("a compact batch renders three-bit rows while stepping (packed=3); use render() for the other formats")
+            obs = self._packed3_buffer() if render else None
+            if render:
+                self.obs_is_packed = 3
+            self.obs_stale = not render
+            _lib.check(self.lib.ragen_sokoban_step_compact(
+                self.ctx.handle, self.n, self.H, self.W, self.num_boxes, self.max_steps, _lib.ptr(actions), K, _lib.ptr(n_actions),
+                _lib.ptr(self.state4), _lib.ptr(self.meta), _lib.ptr(self.reward), _lib.ptr(self.done), _lib.ptr(self.flags),
+                _lib.ptr(self.n_executed), _lib.ptr(obs), self.ctx.stream()))
+            self._state_stale = True
+            return StepOut(self.reward, self.done, self.flags, self.n_executed, obs if render else self.obs)
         obs = (self._packed3_buffer() if fmt == 3 else self._packed_buffer() if fmt == 1 else self.obs) if render else None
         if render:
             self.obs_is_packed = fmt if fmt else False

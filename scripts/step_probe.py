@@ -1,6 +1,6 @@
 """Step-kernel timing probe (GPU): back-to-back launches of one room shape, for CUDA-event timing and as an ncu target.
 
-    python scripts/step_probe.py H W num_boxes n K packed reps
+    python scripts/step_probe.py H W num_boxes n K packed reps     (packed: 0 bytes, 1 nibbles, 3 three-bit rows, 4 three-bit rows + compact rooms)
 """
 import sys
 
@@ -15,7 +15,9 @@ def main():
     a = [int(x) for x in sys.argv[1:]] + [6, 6, 1, 1 << 20, 1, 1, 200][len(sys.argv) - 1:]
     H, W, nb, n, K, packed, reps = a
     fixed, state = synth.synthetic_rooms(n, H, W, nb, seed=4)
-    b = SokobanBatch(n, (H, W), nb, 100, device=0)
+    compact = packed == 4
+    packed = 3 if compact else packed
+    b = SokobanBatch(n, (H, W), nb, 100, device=0, compact=compact)
     b.load_rooms(fixed, state)
     g = torch.Generator(device="cuda").manual_seed(1)
     acts = torch.randint(1, 5, (4, n, K), dtype=torch.uint8, device="cuda", generator=g)
@@ -29,8 +31,8 @@ def main():
     e.record()
     torch.cuda.synchronize()
     us = 1e3 * s.elapsed_time(e) / reps
-    moved = 2 * H * W + 16 + 11 + (((3 * H * W + 15) // 16) * 2 if packed == 3 else H * (W + 1) // 2 if packed else H * (W + 1)) + K
-    print(f"{H}x{W} n={n} K={K} packed={packed}: {us:.1f} us/launch, {n * K / us * 1e6:.3e} env-steps/s, "
+    moved = (H * W if compact else 2 * H * W) + 16 + 11 + (((3 * H * W + 15) // 16) * 2 if packed == 3 else H * (W + 1) // 2 if packed else H * (W + 1)) + K
+    print(f"{H}x{W} n={n} K={K} packed={packed}{" compact" if compact else ""}: {us:.1f} us/launch, {n * K / us * 1e6:.3e} env-steps/s, "
           f"{n * moved / us * 1e-3:.0f} GB/s on the {moved} B/env this launch moves")
 
 

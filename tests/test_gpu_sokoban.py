@@ -338,3 +338,65 @@ def test_three_bit_rows_refuse_other_shapes():
     buf = torch.zeros(4 * 16, dtype=torch.uint8, device="cuda")
     rc = b.lib.ragen_sokoban_render_packed3(b.ctx.handle, 4, 7, 6, _lib.ptr(b.state), _lib.ptr(b.meta), _lib.ptr(buf), b.ctx.stream())
     assert rc != 0
+
+
+@pytest.mark.parametrize("H,W,nb,n", [(6, 6, 1, 1000), (10, 10, 2, 4099), (8, 8, 2, 515), (10, 10, 2, 1), (6, 6, 1, 129), (10, 10, 3, 257)])
+def test_compact_rooms_step_like_the_byte_rooms(H, W, nb, n):
+    """ragen_sokoban_step_compact: the rooms live in HBM as nibbles (two cells per byte); a turn reads, steps and writes
+    them back in that form.  Unpacked, room_state equals the oracle's after every turn, and so do the rewards, flags,
+    n_executed and the three-bit glyph rows; turns without a render and n_actions < K are covered; the other glyph
+    formats go through render() on the unpacked rooms."""
+    from ragen_b200.env.sokoban import SokobanBatch, unpack3_glyphs, unpack_glyphs
+
+    fixed, state = synthetic_rooms(n, H, W, nb, seed=n + 23)
+    rng = np.random.default_rng(n + 5)
+    o = SokobanBatchOracle(fixed, state, H, W, nb, 40)
+    b = SokobanBatch(n, (H, W), nb, 40, compact=True)
+    b.load_rooms(fixed, state)
+    s4 = b.state4.cpu().numpy()
+    assert np.array_equal(s4 & 15, state.reshape(n, -1)[:, 0::2]) and np.array_equal(s4 >> 4, state.reshape(n, -1)[:, 1::2])
+    for turn in range(12):
+        K = int(rng.integers(1, 4))
+        acts = rng.integers(0, 5, (n, K)).astype(np.uint8)
+        na = rng.integers(0, K + 1, n).astype(np.uint8) if turn % 3 == 2 else None
+        acc, done, flags, nexec = o.step_turn(acts, na)
+        render = turn % 4 != 1
+        out = b.step(torch.from_numpy(acts).cuda(), None if na is None else torch.from_numpy(na).cuda(), render=render, packed=3)
+        assert np.array_equal(b.state.cpu().numpy(), o.state)
+        assert np.array_equal(out.reward.cpu().numpy(), acc) and np.array_equal(out.done.cpu().numpy(), done)
+        assert np.array_equal(out.flags.cpu().numpy(), flags) and np.array_equal(out.n_executed.cpu().numpy(), nexec)
+        if render:
+            assert np.array_equal(unpack3_glyphs(out.obs.cpu().numpy(), H, W), o.glyphs())
+    assert np.array_equal(b.render().cpu().numpy().reshape(n, -1), o.glyphs())
+    assert np.array_equal(unpack_glyphs(b.render(packed=True).cpu().numpy()), o.glyphs())
+    acts = rng.integers(1, 5, n).astype(np.uint8)
+    acc, done, flags, nexec = o.step_turn(acts[:, None], None)
+    h_obs, h_rew, h_done, h_flags, h_nex = b.step_host(acts, packed=3)
+    assert np.array_equal(unpack3_glyphs(h_obs, H, W), o.glyphs())
+    assert np.array_equal(h_rew, acc) and np.array_equal(h_done, done) and np.array_equal(h_flags, flags) and np.array_equal(h_nex, nexec)
+    with pytest.raises(ValueError):
+        b.step(torch.from_numpy(acts[:, None]).cuda(), packed=True)
+    # a partial reset re-packs the rooms it touched and leaves the others alone
+    before = b.state.clone()
+    slots = [0, n // 2, n - 1] if n >= 3 else [0]
+    b.reset([7, 7, 9][: len(slots)], slots=slots)
+    after = b.state
+    touched = torch.zeros(n, dtype=torch.bool, device="cuda")
+    touched[slots] = True
+    assert torch.equal(after[~touched], before[~touched])
+    s4 = b.state4
+    assert torch.equal(s4 & 15, after[:, 0::2]) and torch.equal(s4 >> 4, after[:, 1::2])
+
+
+def test_compact_rooms_refuse_other_shapes():
+    from ragen_b200 import _lib
+    from ragen_b200.env.sokoban import SokobanBatch
+
+    with pytest.raises(ValueError):
+        SokobanBatch(4, (7, 6), 1, 50, compact=True)
+    b = _batch(4, 7, 6, 1, 50)
+    z = torch.zeros(4 * 21, dtype=torch.uint8, device="cuda")
+    a = torch.ones(4, dtype=torch.uint8, device="cuda")
+    rc = b.lib.ragen_sokoban_step_compact(b.ctx.handle, 4, 7, 6, 1, 50, _lib.ptr(a), 1, None, _lib.ptr(z), _lib.ptr(b.meta), _lib.ptr(b.reward),
+                                          _lib.ptr(b.done), _lib.ptr(b.flags), _lib.ptr(b.n_executed), None, b.ctx.stream())
+    assert rc != 0

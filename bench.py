@@ -7,8 +7,10 @@
 Workload (config 4 of BASELINE.json, the one the metric is quoted on): Sokoban 10x10, 2 boxes,
 max_steps 100; 1 Mi envs PER GPU (weak scaling: env groups are independent, no data-path collective;
 at N=8 that is 8 Mi envs); one "step" = every env takes one action: state update + reward + done/info
-flags + text glyph render, one kernel launch.  Working set per step 431 MB/GPU > 126 MB L2, so no L2
-flush is needed between timed iterations.
+flags + text glyph render, one kernel launch.  Two such batches are resident and stepped alternately, so
+the distinct lines between two touches of a line (~226 MB with the default formats) exceed the 126 MB L2
+and no L2 flush is needed between timed iterations.  The rooms rest in HBM two cells per byte (--rooms
+nibbles, the default: ragen_sokoban_step_compact; --rooms bytes = one cell per byte).
 
 `value`   : device-timed (CUDA events, max over ranks), inputs resident in HBM.
 `e2e`     : same step through SokobanBatch.step_host — the actions come from pinned HOST memory and the
@@ -50,7 +52,7 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--obs", default="packed3", choices=["packed3", "packed", "bytes"],
                     help="glyph-row format of the render: two 4-bit codes per byte (what the managers consume) or one code per byte")
-    ap.add_argument("--rooms", default="bytes", choices=["nibbles", "bytes"],
+    ap.add_argument("--rooms", default="nibbles", choices=["nibbles", "bytes"],
                     help="how the rooms rest in HBM: one cell per byte, or two (ragen_sokoban_step_compact; needs --obs packed3)")
     ap.add_argument("--rows", action="store_true", help="per-kernel lines for every SURVEY.md 8(d) config instead of the contract line")
     ap.add_argument("--quick", action="store_true", help="with --rows: smaller batches")
@@ -65,7 +67,7 @@ def workload_config(n_gpus, envs_per_gpu, obs="packed", rooms="bytes"):
             "workload": "sokoban_10x10_2box_step_render_reward", "dim_room": [H, W], "num_boxes": NUM_BOXES,
             "max_steps": MAX_STEPS, "envs_per_gpu": envs_per_gpu, "envs_total": envs_per_gpu * n_gpus,
             "actions_per_launch": 1, "rooms": "synthetic random-walk rooms (ragen_b200/synth.py)",
-            "actions": "uniform 1..4", "l2": "inputs larger than L2 (431 MB touched per step per GPU)",
+            "actions": "uniform 1..4", "l2": "inputs larger than L2: two batches of envs_per_gpu envs stepped alternately, %d MB of distinct lines between two touches of a line (L2 is 126 MB)" % ((envs_per_gpu * 2 * ((50 if rooms == "nibbles" else 100) + 8 + 1 + 11 + {"packed3": 38, "packed": 55, "bytes": 110}[obs])) >> 20),
             "parallelism": f"env-sharded x{n_gpus}"}
 
 
@@ -258,8 +260,16 @@ def run_native(args):
     compact = args.rooms == "nibbles"
     if compact and args.obs != "packed3":
         raise SystemExit("--rooms nibbles renders three-bit rows: use --obs packed3")
-    batch = SokobanBatch(n, (H, W), NUM_BOXES, MAX_STEPS, device=local_rank, compact=compact)
-    batch.load_rooms(fixed, state)
+    # Two batches of n envs each, stepped alternately: with the rooms as nibbles ONE batch's lines (rooms 52 MB, records 8 MB, rows
+    # 40 MB, results 12 MB) would fit the 126 MB L2, so between two touches of a line the other batch's ~113 MB go through it.
+    batches = []
+    for j in range(2):
+        if j:
+            fixed, state = synthetic_rooms(n, H, W, NUM_BOXES, seed=1004 + rank)
+        b_ = SokobanBatch(n, (H, W), NUM_BOXES, MAX_STEPS, device=local_rank, compact=compact)
+        b_.load_rooms(fixed, state)
+        batches.append(b_)
+    batch = batches[0]
     R = 8  # rotating action slabs, all resident in HBM
     g = torch.Generator(device=dev)
     g.manual_seed(1234 + rank)
@@ -275,13 +285,13 @@ def run_native(args):
     G = H * (W + 1)
     row_bytes = {"packed3": ((3 * H * W + 15) // 16) * 2, "packed": G // 2, "bytes": G}[args.obs]
     for i in range(args.warmup):
-        batch.step(actions[i % R], packed=packed)
+        batches[i & 1].step(actions[i % R], packed=packed)
     t_begin, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     launches0 = batch.ctx.launches
     t_begin.record()
     for i in range(args.steps):
-        batch.step(actions[i % R], packed=packed)
+        batches[i & 1].step(actions[i % R], packed=packed)
     t_end.record()
     barrier()
     launches = batch.ctx.launches - launches0
@@ -298,11 +308,11 @@ def run_native(args):
     e2e = None
     if not args.no_e2e:
         for i in range(max(args.warmup, 3)):
-            batch.step_host(host_actions[i % R], packed=packed)
+            batches[i & 1].step_host(host_actions[i % R], packed=packed)
         barrier()
         t0 = time.perf_counter()
         for i in range(args.steps):
-            batch.step_host(host_actions[i % R], packed=packed)
+            batches[i & 1].step_host(host_actions[i % R], packed=packed)
         barrier()
         e2e_s = time.perf_counter() - t0
         t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)

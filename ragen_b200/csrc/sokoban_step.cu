@@ -413,11 +413,16 @@ __global__ void __launch_bounds__(TE) sokoban_tile_kernel(const StepParams p) {
       PACK != 0 && CH != 0 && CW != 0 && ((CH * CW) % 4 == 0) && (PACK3 || ((CH * (CW + 1)) % 2 == 0)) && CW >= 6;
   if constexpr (ENV_RENDER && STATE4) {
     if (p.obs && mine) {
+      // player standing on a target (env.py:55): code 5 -> 6 (xor 3) in the owner's nibble for the duration of the render -
+      // the room's bulk store is issued after the barrier below
+      const bool fix = under && pos >= 0;
+      uint8_t* pb = s_state + ((e * HW) >> 1) + (pos >> 1);
+      const uint8_t fx = (uint8_t)(3u << ((pos & 1) << 2));
+      if (fix) *pb ^= fx;
       uint32_t cw[(CH * CW + 7) / 8 + 1];
       load_env_nibbles<CH * CW>(s_state, e, cw);
-      // player standing on a target (env.py:55): code 5 -> 6 in the word of the cell stream that holds the player
-      const bool fix = under && pos >= 0;
-      pack3_store<CH, CW>(cw, fix ? (pos >> 3) : -1, 3u << (4 * (pos & 7)), s_obs, e);
+      if (fix) *pb ^= fx;
+      pack3_store<CH, CW>(cw, -1, 0u, s_obs, e);
     }
   }
   if (ENV_RENDER && PACK3 && !STATE4 && p.obs && mine) {

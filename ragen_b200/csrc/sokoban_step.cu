@@ -218,19 +218,29 @@ __device__ __forceinline__ void render_env_packed(const uint8_t* s_state, uint8_
 // Three-bit glyph rows (ragen_sokoban_step_packed3): the H*W cell codes (0..6 fit three bits), row-major, NO separators (the
 // host knows W), little-endian bit stream padded to an even number of bytes per env - 38 B for 10x10 instead of 55 B of
 // nibbles: the format for bulk transport to the host, where the device->host link is what bounds the step.
-// cw: the env's cell-nibble stream; word fix_word (or none: -1) is xor-ed with fix_xor first (player 5 -> player on target 6)
+// (a & m) | (b & ~m) as ONE LOP3 (written in C the two constant masks become two instructions)
+__device__ __forceinline__ uint32_t bitsel(uint32_t a, uint32_t b, uint32_t m) {
+  uint32_t d;
+  asm("lop3.b32 %0, %1, %2, %3, 0xE4;" : "=r"(d) : "r"(a), "r"(b), "r"(m));
+  return d;
+}
+
+// cw: the env's cell-nibble stream (8 cells per word) -> its three-bit row stream in the glyph tile
 template <int CH, int CW>
-__device__ __forceinline__ void pack3_store(const uint32_t (&cw)[(CH * CW + 7) / 8 + 1], int fix_word, uint32_t fix_xor,
-                                            uint8_t* s_obs, int e) {
+__device__ __forceinline__ void pack3_store(const uint32_t (&cw)[(CH * CW + 7) / 8 + 1], uint8_t* s_obs, int e) {
   constexpr int HW = CH * CW, NCW = (HW + 7) / 8;
   constexpr int B = ((HW * 3 + 15) / 16) * 2;  // bytes per env
   constexpr int NOW = (B + 3) / 4;
   uint32_t g24[NCW];  // 8 cells -> 24 bits
 #pragma unroll
   for (int j = 0; j < NCW; ++j) {
-    const uint32_t x = cw[j] ^ (j == fix_word ? fix_xor : 0u);
-    const uint32_t pr = (x & 0x07070707u) | (((x >> 4) & 0x07070707u) << 3);  // per byte: cell 2i | cell 2i+1 << 3
-    g24[j] = (pr & 0x3fu) | ((pr >> 2) & 0xfc0u) | ((pr >> 4) & 0x3f000u) | ((pr >> 6) & 0xfc0000u);
+    // Bit selects (one LOP3 each) instead of mask-and-or: bit 3 of every nibble is 0 (codes 0..6), so the bits a select drags
+    // along are either zero or sit in positions a later select overwrites.
+    const uint32_t x = cw[j];
+    const uint32_t pr = bitsel(x, x >> 1, 0x07070707u);  // per byte: cell 2i | cell 2i+1 << 3 in bits 0-5 (bit 7: junk, never picked)
+    const uint32_t t1 = bitsel(pr, pr >> 2, 0x0000003fu);  // bits 0-5 byte 0, bits 6.. from byte 1 on
+    const uint32_t t2 = bitsel(t1, pr >> 4, 0x00000fffu);  // bits 12.. from byte 2 on
+    g24[j] = bitsel(t2, pr >> 6, 0x0003ffffu);             // bits 18-23 byte 3; bits 24-31 = pr bits 30.. = 0
   }
   uint32_t out[NOW];
 #pragma unroll
@@ -252,7 +262,7 @@ __device__ __forceinline__ void render_env_packed3(const uint8_t* s_state, uint8
   static_assert(HW % 4 == 0, "shape not supported by the per-env render");
   uint32_t cw[NCW + 1];
   cell_nibbles<HW>(reinterpret_cast<const uint32_t*>(s_state) + e * (HW / 4), cw);
-  pack3_store<CH, CW>(cw, -1, 0u, s_obs, e);
+  pack3_store<CH, CW>(cw, s_obs, e);
 }
 
 // Rooms kept as NIBBLES in HBM (ragen_sokoban_step_compact): a room's bytes ARE the cell-nibble stream the three-bit render
@@ -422,7 +432,7 @@ __global__ void __launch_bounds__(TE) sokoban_tile_kernel(const StepParams p) {
       uint32_t cw[(CH * CW + 7) / 8 + 1];
       load_env_nibbles<CH * CW>(s_state, e, cw);
       if (fix) *pb ^= fx;
-      pack3_store<CH, CW>(cw, -1, 0u, s_obs, e);
+      pack3_store<CH, CW>(cw, s_obs, e);
     }
   }
   if (ENV_RENDER && PACK3 && !STATE4 && p.obs && mine) {

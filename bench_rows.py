@@ -111,7 +111,13 @@ def sokoban_rows(quick):
     from ragen_b200.env.sokoban import SokobanBatch
 
     rows = []
-    for (H, W, nb, n, K, packed, tag) in [(10, 10, 2, 1 << 20, 1, True, "C4 step 10x10 K=1, packed glyph rows"),
+    # packed: False byte rows, True nibble rows, 3 three-bit rows, 4 three-bit rows + rooms resting as nibbles (step_compact)
+    for (H, W, nb, n, K, packed, tag) in [(10, 10, 2, 1 << 20, 1, 4, "C4 step 10x10 K=1, nibble rooms + three-bit glyph rows (bench default)"),
+                                          (10, 10, 2, 1 << 20, 1, 3, "C4 step 10x10 K=1, three-bit glyph rows"),
+                                          (10, 10, 2, 1 << 20, 5, 4, "C4 turn-fused 10x10 K=5, nibble rooms + three-bit glyph rows"),
+                                          (8, 8, 2, 1 << 20, 1, 4, "8x8 K=1 at 1Mi envs, nibble rooms + three-bit glyph rows"),
+                                          (6, 6, 1, 1 << 20, 1, 4, "6x6 K=1 at 1Mi envs, nibble rooms + three-bit glyph rows"),
+                                          (10, 10, 2, 1 << 20, 1, True, "C4 step 10x10 K=1, packed glyph rows"),
                                           (10, 10, 2, 1 << 20, 1, False, "C4 step 10x10 K=1, byte glyph rows"),
                                           (10, 10, 2, 1 << 20, 5, True, "C4 turn-fused 10x10 K=5, packed glyph rows"),
                                           (6, 6, 1, 1 << 20, 1, True, "6x6 K=1 at 1Mi envs, packed glyph rows"),
@@ -120,14 +126,16 @@ def sokoban_rows(quick):
         if quick and n > 1 << 18:
             n = 1 << 18
         fixed, state = synth.synthetic_rooms(n, H, W, nb, seed=4)
-        b = SokobanBatch(n, (H, W), nb, 100, device=0)
+        compact = packed == 4
+        fmt = 3 if compact else packed
+        b = SokobanBatch(n, (H, W), nb, 100, device=0, compact=compact)
         b.load_rooms(fixed, state)
         g = torch.Generator(device="cuda").manual_seed(1)
         acts = torch.randint(1, 5, (4, n, K), dtype=torch.uint8, device="cuda", generator=g)
         i = [0]
 
         def step():
-            b.step(acts[i[0] % 4], packed=packed)
+            b.step(acts[i[0] % 4], packed=fmt)
             i[0] += 1
         ms = dev_time(step, reps=50 if n > 1000 else 200, inner=8 if n > 1000 else 1)
         per_step = 3 * H * W + 1 + 10 + 8 + 1 + 1 + H * (W + 1)
@@ -147,8 +155,10 @@ def sokoban_rows(quick):
                     e.step(int(a))
         cs = cpu_time(cpu, 3.0)
         rows.append(line(tag, "env-step", n * K, ms, per_turn / K, m * K / cs, f"{m} envs x {K} actions, oracle/sokoban.py, 1 core",
-                         envs=n, K=K, kernel="sokoban_tile_kernel", glyph_rows="packed" if packed else "bytes",
-                         bytes_moved_per_unit=(2 * H * W + 16 + 11 + (H * (W + 1) // 2 if packed else H * (W + 1))) / K + 1))
+                         envs=n, K=K, kernel="sokoban_tile_kernel", rooms="nibbles" if compact else "bytes",
+                         glyph_rows="three-bit" if fmt == 3 and fmt is not True else "packed" if fmt else "bytes",
+                         bytes_moved_per_unit=((H * W if compact else 2 * H * W) + 16 + 11 + (((3 * H * W + 15) // 16) * 2 if fmt == 3 and fmt is not True
+                                                                                          else H * (W + 1) // 2 if fmt else H * (W + 1))) / K + 1))
         del b
     return rows
 

@@ -116,6 +116,21 @@ def unpack3_glyphs(packed3, H, W):
     return out.reshape(n, H * (W + 1))
 
 
+def pack_rooms(state, out=None):
+    """room_state [n, H*W] (uint8 tensor, codes 0..5, H*W even) -> the nibble rooms ragen_sokoban_step_compact keeps in HBM:
+    [n, H*W/2], cell 2i in the low nibble of byte i."""
+    return torch.bitwise_or(state[:, 0::2], state[:, 1::2] << 4, out=out)
+
+
+def unpack_rooms(state4, out=None):
+    """Inverse of pack_rooms."""
+    if out is None:
+        out = torch.empty((state4.shape[0], 2 * state4.shape[1]), dtype=torch.uint8, device=state4.device)
+    out[:, 0::2] = state4 & 15
+    out[:, 1::2] = state4 >> 4
+    return out
+
+
 def codes_to_text(codes_row, table):
     """codes_row: 1-D uint8 numpy array of length H*(W+1); the trailing separator is dropped."""
     return "".join(table[c] for c in codes_row[:-1].tolist())
@@ -169,8 +184,7 @@ class SokobanBatch:
     def state(self):
         """room_state as uint8 [n, H*W] (the reference's cell codes)."""
         if self._state_stale:
-            self._state[:, 0::2] = self.state4 & 15
-            self._state[:, 1::2] = self.state4 >> 4
+            unpack_rooms(self.state4, out=self._state)
             self._state_stale = False
         return self._state
 
@@ -282,8 +296,7 @@ class SokobanBatch:
 
     def adopt(self, check=True):
         if self.compact:
-            st = self.state
-            torch.bitwise_or(st[:, 0::2], st[:, 1::2] << 4, out=self.state4)
+            pack_rooms(self.state, out=self.state4)
         _lib.check(self.lib.ragen_sokoban_adopt(
             self.ctx.handle, self.n, self.H, self.W, self.num_boxes, _lib.ptr(self.state), _lib.ptr(self.fixed),
             _lib.ptr(self.meta), _lib.ptr(self.status), self.ctx.stream()))

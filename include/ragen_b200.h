@@ -244,6 +244,18 @@ int ragen_masks_scores(ragen_ctx* ctx, int B, int L, const int64_t* input_ids, i
 int ragen_group_norm(ragen_ctx* ctx, int B, const float* score_last, const float* penalty, const int32_t* group,
                      int n_groups, int method, float* out, void* stream);
 
+/* ragen_group_norm without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  Same arguments, same results as ragen_group_norm; the per-group statistics live in a file-scope
+ * `static __device__` array of RAGEN_NOALLOC_MAX_GROUPS * 3 doubles (96 KiB, held by every GPU that loads the library
+ * until the process exits) instead of the ctx-owned scratch.  n_groups > RAGEN_NOALLOC_MAX_GROUPS -> RAGEN_EINVAL.
+ * Calls no cudaMalloc / cudaFree / allocating routine; the first call on a device resolves the array's device address
+ * (cudaGetSymbolAddress), so make that first call outside a graph capture.  Every call on a device SHARES the array:
+ * a call clears what it uses on `stream` first, and calls that overlap on the GPU (unordered streams) race on it. */
+#define RAGEN_NOALLOC_MAX_GROUPS 4096
+int ragen_group_norm_noalloc(ragen_ctx* ctx, int B, const float* score_last, const float* penalty,
+                             const int32_t* group, int n_groups, int method, float* out, void* stream);
+
 /* ---- advantage pass ------------------------------------------------------------------------- */
 /* compute_gae_advantage_return (verl/verl/trainer/ppo/core_algos.py:67-109) WITHOUT the final whitening:
  * adv/ret fp32 [B][T] (bit-identical to the reference's sequential fp32 loop) and, when moments != NULL, the

@@ -43,6 +43,7 @@ SIGNATURES = {
     "ragen_countdown_score": [_P, _L, _P, _P, _P, _P, _P, _P, _P, _P, _P],
     "ragen_masks_scores": [_P, _I, _I, _P, _L, _L, _I, _I, _I, _P, _P, _I, _P, _P, _P, _P],
     "ragen_group_norm": [_P, _I, _P, _P, _P, _I, _I, _P, _P],
+    "ragen_group_norm_noalloc": [_P, _I, _P, _P, _P, _I, _I, _P, _P],
     "ragen_gae": [_P, _I, _I, _P, _P, _P, _D, _D, _P, _P, _P, _P],
     "ragen_bilevel_gae": [_P, _I, _I, _P, _P, _P, _D, _D, _D, _P, _P, _P, _P],
     "ragen_masked_moments": [_P, _L, _P, _P, _P, _P],

@@ -197,3 +197,52 @@ extern "C" int ragen_group_norm(ragen_ctx* ctx, int B, const float* score_last, 
   }
   return RAGEN_OK;
 }
+
+// ---- ragen_group_norm_noalloc -------------------------------------------------------------------------------------
+// The same pass for callers that cannot tolerate an allocation (CUDA graph capture, serving loops, harnesses that
+// forbid cudaMalloc): the per-group statistics live in a file-scope device array instead of the ctx-owned scratch.
+// Every GPU that loads the library holds these RAGEN_NOALLOC_MAX_GROUPS * 24 bytes until the process exits.
+// The array is SHARED by every call on a device and keeps the last call's contents: each call clears the part it uses
+// on its stream first, and two calls that overlap on the GPU (different streams, no ordering between them) race on it.
+static __device__ __align__(256) double g_norm_stats[3 * RAGEN_NOALLOC_MAX_GROUPS];
+
+namespace {
+constexpr int MAX_DEVICES = 64;
+// device address of g_norm_stats per device ordinal.  In host code the NAME g_norm_stats is only a host-side handle of
+// the symbol, not something a kernel can dereference: the address a kernel may use comes from cudaGetSymbolAddress,
+// asked once per device with that device current.
+double* g_norm_stats_addr[MAX_DEVICES];
+}  // namespace
+
+extern "C" int ragen_group_norm_noalloc(ragen_ctx* ctx, int B, const float* score_last, const float* penalty,
+                                        const int32_t* group, int n_groups, int method, float* out, void* stream) {
+  RAGEN_REQUIRE(ctx, "ctx is NULL");
+  RAGEN_REQUIRE(B >= 0 && n_groups >= 1 && method >= 0 && method <= 3, "bad argument B=%d n_groups=%d method=%d", B, n_groups,
+                method);
+  RAGEN_REQUIRE(n_groups <= RAGEN_NOALLOC_MAX_GROUPS,
+                "ragen_group_norm_noalloc: n_groups=%d exceeds the static scratch of RAGEN_NOALLOC_MAX_GROUPS=%d groups "
+                "(use ragen_group_norm, which grows a ctx-owned buffer)",
+                n_groups, RAGEN_NOALLOC_MAX_GROUPS);
+  RAGEN_REQUIRE(score_last && group && out, "NULL pointer argument");
+  RAGEN_REQUIRE(ctx->device >= 0 && ctx->device < MAX_DEVICES, "device ordinal %d beyond %d", ctx->device, MAX_DEVICES);
+  if (B == 0) return RAGEN_OK;
+  DeviceGuard guard(ctx->device);  // ctx->device is current from here on
+  double* gstats = g_norm_stats_addr[ctx->device];
+  if (!gstats) {  // set-up, once per device
+    void* p = nullptr;
+    RAGEN_CUDA(cudaGetSymbolAddress(&p, g_norm_stats));
+    RAGEN_REQUIRE(p, "cudaGetSymbolAddress returned a NULL address for the static scratch");
+    gstats = g_norm_stats_addr[ctx->device] = (double*)p;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  const bool normalise = n_groups < B && method != 0;  // as ragen_group_norm (:219)
+  if (normalise) RAGEN_CUDA(cudaMemsetAsync(gstats, 0, (size_t)n_groups * 3 * sizeof(double), st));
+  const int threads = 128, blocks = (B + threads - 1) / threads;
+  norm_stats_kernel<<<blocks, threads, 0, st>>>(B, score_last, penalty, group, n_groups, out, normalise ? gstats : nullptr);
+  RAGEN_LAUNCHED(ctx);
+  if (normalise) {
+    norm_apply_kernel<<<blocks, threads, 0, st>>>(B, out, group, n_groups, gstats, method);
+    RAGEN_LAUNCHED(ctx);
+  }
+  return RAGEN_OK;
+}

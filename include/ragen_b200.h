@@ -130,6 +130,14 @@ int ragen_sokoban_render_rgb(ragen_ctx* ctx, int64_t n, int H, int W, int S, con
 int ragen_sokoban_adopt(ragen_ctx* ctx, int64_t n, int H, int W, int num_boxes, const uint8_t* state,
                         const uint8_t* fixed, int16_t* meta, int32_t* status, void* stream);
 
+/* The same for a SUBSET of a shared batch (BaseEnv.reset on one env of a manager-owned batch, ragen/env/base.py:16,
+ * es_manager.py:93-95): env i is adopted only when only[i] != 0 (only NULL = all); the others keep their record
+ * (num_env_steps, stored box count) and their status entry.  state4 (may be NULL) [n][H*W/2] receives the adopted rooms
+ * as nibbles, the form ragen_sokoban_step_compact steps (H*W even). */
+int ragen_sokoban_adopt_slots(ragen_ctx* ctx, int64_t n, int H, int W, int num_boxes, const uint8_t* state,
+                              const uint8_t* fixed, int16_t* meta, int32_t* status, const uint8_t* only,
+                              uint8_t* state4, void* stream);
+
 /* SokobanEnv.reset(seed) -> generate_room (ragen/env/sokoban/env.py:28-42, ragen/env/sokoban/utils.py:221-278 with
  * room_topology_generation :281-355, place_boxes_and_player :358-397, reverse_playing / depth_first_search /
  * reverse_move :408-542, box_displacement_score :545-560, add_random_player_movement :152-213) for a batch of seeds.

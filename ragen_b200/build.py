@@ -34,6 +34,21 @@ def _digest():
     return h.hexdigest()
 
 
+def _obj_digest(src):
+    """Digest of one translation unit: its source, every header it may include, the flags."""
+    h = hashlib.sha256()
+    with open(src, "rb") as fh:
+        h.update(fh.read())
+    for root in (CSRC, os.path.join(HERE, "..", "include")):
+        for f in sorted(os.listdir(root)):
+            if f.endswith((".cuh", ".h")):
+                with open(os.path.join(root, f), "rb") as fh:
+                    h.update(f.encode())
+                    h.update(fh.read())
+    h.update(" ".join(FLAGS).encode())
+    return h.hexdigest()
+
+
 def build(force=False, verbose=False):
     os.makedirs(LIB_DIR, exist_ok=True)
     dig = _digest()
@@ -43,16 +58,29 @@ def build(force=False, verbose=False):
         if os.path.exists(LIB_PATH):
             return LIB_PATH  # GPU box without a changed source tree: use the shipped library
         raise RuntimeError(f"nvcc not found at {NVCC} and no prebuilt {LIB_PATH}")
-    objs = []
+    from concurrent.futures import ThreadPoolExecutor
+
+    objs, jobs = [], []
     for src in sources():
         obj = os.path.join(LIB_DIR, os.path.basename(src)[:-3] + ".o")
-        cmd = [NVCC, "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-               "-Xcompiler", "-fPIC,-O2", "-c", src, "-o", obj]
+        objs.append(obj)
+        od = _obj_digest(src)
+        if not force and os.path.exists(obj) and os.path.exists(obj + ".stamp") and open(obj + ".stamp").read().strip() == od:
+            continue  # this translation unit is unchanged
+        cmd = [NVCC] + FLAGS + ["-c", src, "-o", obj]
         if verbose:
             cmd[1:1] = ["-Xptxas", "-v"]
             print(" ".join(cmd), flush=True)
+        jobs.append((cmd, obj, od))
+
+    def run(job):
+        cmd, obj, od = job
         subprocess.run(cmd, check=True)
-        objs.append(obj)
+        with open(obj + ".stamp", "w") as fh:
+            fh.write(od)
+
+    with ThreadPoolExecutor(max_workers=min(8, max(1, len(jobs)))) as ex:
+        list(ex.map(run, jobs))
     cmd = [NVCC, "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", LIB_PATH] + objs
     subprocess.run(cmd, check=True)
     with open(STAMP, "w") as fh:

@@ -5,6 +5,7 @@
 // _extract_map_valid_actions (ragen/llm_agent/es_manager.py:230-240) and CountdownEnv.compute_reward /
 // check_format / check_correctness (ragen/env/countdown/env.py:9-21, 69-78).  Text is UTF-8.
 #pragma once
+#include <math.h>
 #include <stdint.h>
 
 #ifndef RAGEN_HD
@@ -262,9 +263,12 @@ RAGEN_HD void parse_finish(const uint8_t* abuf, int ans_s, int ans_e, const uint
 // ---- Countdown (ragen/env/countdown/env.py:9-21, 69-78) -------------------------------------------------------------
 // check_format: the integers of all ASCII digit runs, as a multiset, must equal nums.
 // check_correctness: eval(expr) == target within 1e-5.  The device evaluator covers this grammar of Python
-// expressions: decimal integers (leading zeros only for zero, as Python 3), binary + - * / (true division), unary
-// + -, parentheses, blanks (space, tab, form feed; newlines inside parentheses or trailing).  Anything else Python
-// might accept (** // % floats names comparisons ...) is reported through `unsupported` and scored as an exception.
+// expressions: decimal integers (leading zeros only for zero, as Python 3), float literals (digits '.' digits, optional
+// exponent; up to 15 significant digits), binary + - * / (true division) // (floor division) % ** (right associative,
+// binding tighter than a unary sign on its left), unary + -, parentheses, blanks (space, tab, form feed; newlines inside
+// parentheses or trailing), with Python's int / float result types.  Anything else Python might accept (names,
+// comparisons, bit operators, complex results, digit separators, integers beyond 2^61 ...) is reported through
+// `unsupported` and scored as an exception; callers surface that flag (CountdownEnv warns), they do not re-evaluate.
 constexpr int CD_MAX_NUMS = 8;
 constexpr int CD_STACK = 32;
 
@@ -274,34 +278,127 @@ struct CdValue {
   double d;
 };
 RAGEN_HD double cd_as_double(const CdValue& v) { return v.is_int ? (double)v.i : v.d; }
+RAGEN_HD bool cd_finite(double x) { return x - x == 0.0; }
+RAGEN_HD void cd_set_d(CdValue& out, double v) {
+  out.is_int = false;
+  out.i = 0;
+  out.d = v;
+}
 
-// applies a binary operator; false on ZeroDivisionError / int64 overflow (overflow also sets unsupported)
+// checked int64 multiply within |r| <= 2^61
+RAGEN_HD bool cd_mul(long long a, long long b, long long& r) {
+  bool ovf;
+#if defined(__CUDA_ARCH__)
+  r = (long long)((unsigned long long)a * (unsigned long long)b);
+  ovf = (a != 0 && (r / a != b || (a == -1 && b == (-9223372036854775807LL - 1))));
+#else
+  ovf = __builtin_mul_overflow(a, b, &r);
+#endif
+  return !(ovf || r > (1LL << 61) || r < -(1LL << 61));
+}
+
+// CPython float_divmod (Objects/floatobject.c): floor quotient and the remainder with the divisor's sign; wx != 0
+RAGEN_HD void cd_float_divmod(double vx, double wx, double& floordiv, double& mod) {
+  mod = fmod(vx, wx);
+  double div = (vx - mod) / wx;
+  if (mod != 0.0) {
+    if ((wx < 0) != (mod < 0)) {
+      mod += wx;
+      div -= 1.0;
+    }
+  } else {
+    mod = copysign(0.0, wx);
+  }
+  if (div != 0.0) {
+    floordiv = floor(div);
+    if (div - floordiv > 0.5) floordiv += 1.0;
+  } else {
+    floordiv = copysign(0.0, vx / wx);
+  }
+}
+
+// applies a binary operator ('f' = //, 'p' = **); false when Python raises (ZeroDivisionError, OverflowError) or the
+// value leaves the covered range (then `unsupported` is set as well)
 RAGEN_HD bool cd_apply(char op, const CdValue& a, const CdValue& b, CdValue& out, bool& unsupported) {
+  const bool ints = a.is_int && b.is_int;
+  if ((a.is_int && (a.i > (1LL << 53) || a.i < -(1LL << 53))) || (b.is_int && (b.i > (1LL << 53) || b.i < -(1LL << 53)))) {
+    if (!ints || op == '/' || (op == 'p' && b.i < 0)) {  // int -> float of such magnitudes: Python rounds the exact quotient
+      unsupported = true;
+      return false;
+    }
+  }
   if (op == '/') {
     const double den = cd_as_double(b);
     if (den == 0.0) return false;
-    out.is_int = false;
-    out.d = cd_as_double(a) / den;
-    out.i = 0;
+    cd_set_d(out, cd_as_double(a) / den);
     return true;
   }
-  if (a.is_int && b.is_int) {
-    long long r;
-    bool ovf;
-#if defined(__CUDA_ARCH__)
-    // |operands| are checked to stay below 2^62 so + and - cannot wrap; * is checked by division
-    if (op == '*') {
-      r = a.i * b.i;
-      ovf = (a.i != 0 && (r / a.i != b.i || (a.i == -1 && b.i == (-9223372036854775807LL - 1))));
-    } else {
-      r = (op == '+') ? a.i + b.i : a.i - b.i;
-      ovf = false;
+  if (op == 'f' || op == '%') {
+    if (ints) {
+      if (b.i == 0) return false;
+      long long q = a.i / b.i, r = a.i % b.i;
+      if (r != 0 && ((r < 0) != (b.i < 0))) {
+        q -= 1;
+        r += b.i;
+      }
+      out.is_int = true;
+      out.i = (op == 'f') ? q : r;
+      out.d = 0.0;
+      return true;
     }
-#else
-    ovf = (op == '*') ? __builtin_mul_overflow(a.i, b.i, &r) : (op == '+') ? __builtin_add_overflow(a.i, b.i, &r)
-                                                                           : __builtin_sub_overflow(a.i, b.i, &r);
-#endif
-    if (ovf || r > (1LL << 61) || r < -(1LL << 61)) {
+    const double x = cd_as_double(a), y = cd_as_double(b);
+    if (y == 0.0) return false;
+    double fd, md;
+    cd_float_divmod(x, y, fd, md);
+    cd_set_d(out, (op == 'f') ? fd : md);
+    return true;
+  }
+  if (op == 'p') {
+    if (ints && b.i >= 0) {  // int ** non-negative int stays an int
+      long long base = a.i, r = 1;
+      long long e = b.i;
+      if (base == 0 || base == 1) {
+        r = (e == 0) ? 1 : base;
+      } else if (base == -1) {
+        r = (e & 1) ? -1 : 1;
+      } else {
+        if (e > 62) {
+          unsupported = true;  // beyond int64: Python would carry on with big integers
+          return false;
+        }
+        for (long long k = 0; k < e; ++k) {
+          if (!cd_mul(r, base, r)) {
+            unsupported = true;
+            return false;
+          }
+        }
+      }
+      out.is_int = true;
+      out.i = r;
+      out.d = 0.0;
+      return true;
+    }
+    const double x = cd_as_double(a), y = cd_as_double(b);
+    if (x == 0.0 && y < 0.0) return false;  // ZeroDivisionError
+    if (x < 0.0 && cd_finite(y) && y != floor(y)) {
+      unsupported = true;  // complex result
+      return false;
+    }
+    const double r = pow(x, y);
+    if (!cd_finite(r) && cd_finite(x) && cd_finite(y)) return false;  // OverflowError
+    cd_set_d(out, r);
+    return true;
+  }
+  if (ints) {
+    long long r;
+    bool ok;
+    if (op == '*') {
+      ok = cd_mul(a.i, b.i, r);
+    } else {  // |operands| <= 2^61, so + and - cannot wrap
+      r = (op == '+') ? a.i + b.i : a.i - b.i;
+      ok = !(r > (1LL << 61) || r < -(1LL << 61));
+    }
+    if (!ok) {
       unsupported = true;  // Python ints do not overflow; such magnitudes are outside the covered range
       return false;
     }
@@ -311,13 +408,13 @@ RAGEN_HD bool cd_apply(char op, const CdValue& a, const CdValue& b, CdValue& out
     return true;
   }
   const double x = cd_as_double(a), y = cd_as_double(b);
-  out.is_int = false;
-  out.i = 0;
-  out.d = (op == '+') ? x + y : (op == '-') ? x - y : x * y;
+  cd_set_d(out, (op == '+') ? x + y : (op == '-') ? x - y : x * y);
   return true;
 }
 
-RAGEN_HD int cd_prec(char op) { return (op == 'n') ? 3 : (op == '*' || op == '/') ? 2 : (op == '+' || op == '-') ? 1 : 0; }
+RAGEN_HD int cd_prec(char op) {
+  return (op == 'p') ? 4 : (op == 'n') ? 3 : (op == '*' || op == '/' || op == 'f' || op == '%') ? 2 : (op == '+' || op == '-') ? 1 : 0;
+}
 
 // pops one operator and applies it
 RAGEN_HD bool cd_reduce(CdValue* vals, int& nv, char* ops, int& no, bool& unsupported) {
@@ -334,6 +431,87 @@ RAGEN_HD bool cd_reduce(CdValue* vals, int& nv, char* ops, int& no, bool& unsupp
   vals[nv - 2] = r;
   --nv;
   return true;
+}
+
+// A numeric literal at s[i] (a digit, or '.' followed by a digit).  Advances i past it.  Returns 0 ok, 1 SyntaxError,
+// 2 outside the covered range (unsupported).
+RAGEN_HD int cd_number(const uint8_t* s, int n, int& i, CdValue& out) {
+  const int start = i;
+  unsigned long long mant = 0;
+  int sig = 0, dropped = 0;  // significant digits kept, integer digits beyond the 18th
+  bool nonzero = false, is_float = false;
+  while (i < n && s[i] >= '0' && s[i] <= '9') {
+    if (s[i] != '0') nonzero = true;
+    if (nonzero) {
+      if (sig < 18) {
+        mant = mant * 10 + (unsigned)(s[i] - '0');
+        ++sig;
+      } else {
+        ++dropped;
+      }
+    }
+    ++i;
+  }
+  const int int_digits = i - start;
+  int frac = 0;
+  if (i < n && s[i] == '.') {
+    is_float = true;
+    ++i;
+    while (i < n && s[i] >= '0' && s[i] <= '9') {
+      if (s[i] != '0') nonzero = true;
+      if (nonzero && sig < 18) {
+        mant = mant * 10 + (unsigned)(s[i] - '0');
+        ++sig;
+        ++frac;
+      } else if (!nonzero) {
+        ++frac;  // leading zeros of a pure fraction
+      } else {
+        return 2;  // more digits than the exact path carries
+      }
+      ++i;
+    }
+  }
+  int e10 = 0;
+  if (i < n && (s[i] == 'e' || s[i] == 'E')) {
+    int j = i + 1;
+    bool neg = false;
+    if (j < n && (s[j] == '+' || s[j] == '-')) {
+      neg = s[j] == '-';
+      ++j;
+    }
+    if (!(j < n && s[j] >= '0' && s[j] <= '9')) return 2;  // "1e" / an identifier glued to a number
+    while (j < n && s[j] >= '0' && s[j] <= '9') {
+      if (e10 < 10000) e10 = e10 * 10 + (s[j] - '0');
+      ++j;
+    }
+    if (neg) e10 = -e10;
+    is_float = true;
+    i = j;
+  }
+  if (i < n) {
+    const int d = s[i];
+    if (d == '.' || d == '_' || (d >= 'a' && d <= 'z') || (d >= 'A' && d <= 'Z') || d >= 0x80) return 2;  // 1_0, 1j, 0x1, 1..
+  }
+  if (!is_float) {
+    if (int_digits > 1 && s[start] == '0' && nonzero) return 1;  // "012": SyntaxError in Python 3
+    if (dropped || mant > (1ULL << 50)) return 2;
+    out.is_int = true;
+    out.i = (long long)mant;
+    out.d = 0.0;
+    return 0;
+  }
+  // decimal -> double on the exact path: mantissa below 2^53 times / over a power of ten up to 10^22 is correctly rounded
+  if (dropped || sig > 15) return 2;
+  const int p10 = e10 - frac;
+  if (mant == 0) {
+    cd_set_d(out, 0.0);
+    return 0;
+  }
+  if (p10 > 22 || p10 < -22) return 2;
+  double pw = 1.0;
+  for (int k = 0; k < (p10 < 0 ? -p10 : p10); ++k) pw *= 10.0;  // exact up to 10^22
+  cd_set_d(out, p10 >= 0 ? (double)mant * pw : (double)mant / pw);
+  return 0;
 }
 
 // returns 0 = format check failed (reward 0), 1 = format ok but not correct (format_score), 2 = correct (score)
@@ -400,35 +578,15 @@ RAGEN_HD int countdown_score(const uint8_t* s, int n, const int32_t* nums, int n
     }
     any = true;
     if (want_operand) {
-      if (c >= '0' && c <= '9') {
-        const int start = i;
-        long long v = 0;
-        bool nonzero = false;
-        while (i < n && s[i] >= '0' && s[i] <= '9') {
-          if (s[i] != '0') nonzero = true;
-          if (v > (1LL << 50)) {
-            unsupported = true;
-            return 1;
-          }
-          v = v * 10 + (s[i] - '0');
-          ++i;
-        }
-        if (i - start > 1 && s[start] == '0' && nonzero) return 1;  // "012": SyntaxError in Python 3
-        if (i < n) {
-          const int d = s[i];
-          if (d == '.' || d == '_' || (d >= 'a' && d <= 'z') || (d >= 'A' && d <= 'Z') || d >= 0x80) {
-            unsupported = true;  // float / complex / digit separators / identifiers glued to a number
-            return 1;
-          }
-        }
-        --i;
+      if ((c >= '0' && c <= '9') || (c == '.' && i + 1 < n && s[i + 1] >= '0' && s[i + 1] <= '9')) {
         if (nv >= CD_STACK) {
           unsupported = true;
           return 1;
         }
-        vals[nv].is_int = true;
-        vals[nv].i = v;
-        vals[nv].d = 0.0;
+        const int rc = cd_number(s, n, i, vals[nv]);
+        if (rc == 2) unsupported = true;
+        if (rc != 0) return 1;
+        --i;
         ++nv;
         want_operand = false;
       } else if (c == '+') {
@@ -447,22 +605,24 @@ RAGEN_HD int countdown_score(const uint8_t* s, int n, const int32_t* nums, int n
         ops[no++] = '(';
         ++depth;
       } else {
-        if (!(c == ')' || c == '*' || c == '/')) unsupported = true;
+        if (!(c == ')' || c == '*' || c == '/' || c == '%')) unsupported = true;
         return 1;
       }
     } else {
-      if (c == '+' || c == '-' || c == '*' || c == '/') {
+      if (c == '+' || c == '-' || c == '*' || c == '/' || c == '%') {
+        char op = (char)c;
         if ((c == '*' || c == '/') && i + 1 < n && s[i + 1] == c) {
-          unsupported = true;  // ** or //
-          return 1;
+          op = (c == '*') ? 'p' : 'f';  // ** or //
+          ++i;
         }
-        while (no > 0 && ops[no - 1] != '(' && cd_prec(ops[no - 1]) >= cd_prec((char)c))
+        // ** is right associative: it only pops operators that bind tighter (none); the others pop their equals too
+        while (no > 0 && ops[no - 1] != '(' && (op == 'p' ? cd_prec(ops[no - 1]) > cd_prec(op) : cd_prec(ops[no - 1]) >= cd_prec(op)))
           if (!cd_reduce(vals, nv, ops, no, unsupported)) return 1;
         if (no >= CD_STACK) {
           unsupported = true;
           return 1;
         }
-        ops[no++] = (char)c;
+        ops[no++] = op;
         want_operand = true;
       } else if (c == ')') {
         while (no > 0 && ops[no - 1] != '(')
@@ -472,7 +632,7 @@ RAGEN_HD int countdown_score(const uint8_t* s, int n, const int32_t* nums, int n
         --depth;
       } else {
         // "3 4" is a SyntaxError and "3 (4)" a TypeError (int is not callable): plain exceptions
-        if (!((c >= '0' && c <= '9') || c == '(')) unsupported = true;
+        if (!((c >= '0' && c <= '9') || c == '(' || c == '.')) unsupported = true;
         return 1;
       }
     }
@@ -484,7 +644,7 @@ RAGEN_HD int countdown_score(const uint8_t* s, int n, const int32_t* nums, int n
   }
   if (nv != 1) return 1;
   if (vals[0].is_int) return vals[0].i == target ? 2 : 1;
-  const double diff = vals[0].d - (double)target;
+  const double diff = vals[0].d - (double)target;  // nan and inf compare false, as abs(result - target) < 1e-5 does
   return ((diff < 0 ? -diff : diff) < 1e-5) ? 2 : 1;
 }
 

@@ -506,6 +506,8 @@ struct AdoptParams {
   const uint8_t* fixed;
   EnvMeta* meta;
   int32_t* status;
+  const uint8_t* only;  // [n] or NULL: adopt env i only when only[i] != 0 (slot-wise reset of a shared batch)
+  uint8_t* state4;      // [n][H*W/2] or NULL: the room as nibbles (what ragen_sokoban_step_compact keeps), written for adopted envs
 };
 
 __global__ void __launch_bounds__(TE) sokoban_adopt_kernel(const AdoptParams p) {
@@ -534,8 +536,13 @@ __global__ void __launch_bounds__(TE) sokoban_adopt_kernel(const AdoptParams p) 
   }
   const int e = threadIdx.x;
   if (e >= cnt) return;
+  if (p.only && !p.only[env0 + e]) return;  // an env in mid-episode keeps its record (steps, stored box count)
   const uint8_t* S = s_state + e * HW;
   const uint8_t* F = s_fixed + e * HW;
+  if (p.state4) {  // H*W is even (checked at launch): rooms are whole bytes
+    uint8_t* d = p.state4 + ((env0 + e) * HW >> 1);
+    for (int i = 0; i < HW; i += 2) d[i >> 1] = (uint8_t)((S[i] & 15) | (S[i + 1] << 4));
+  }
   int pos = -1, st = 0, open_targets = 0, under = 0;
   int r = 0, c = 0;
   for (int i = 0; i < HW; ++i) {
@@ -692,9 +699,20 @@ extern "C" int ragen_sokoban_render_packed3(ragen_ctx* ctx, int64_t n, int H, in
   return sokoban_render_entry(2, ctx, n, H, W, state, meta, obs_packed3, stream);
 }
 
+extern "C" int ragen_sokoban_adopt_slots(ragen_ctx* ctx, int64_t n, int H, int W, int num_boxes, const uint8_t* state,
+                                         const uint8_t* fixed, int16_t* meta, int32_t* status, const uint8_t* only,
+                                         uint8_t* state4, void* stream);
+
 extern "C" int ragen_sokoban_adopt(ragen_ctx* ctx, int64_t n, int H, int W, int num_boxes, const uint8_t* state,
                                    const uint8_t* fixed, int16_t* meta, int32_t* status, void* stream) {
+  return ragen_sokoban_adopt_slots(ctx, n, H, W, num_boxes, state, fixed, meta, status, nullptr, nullptr, stream);
+}
+
+extern "C" int ragen_sokoban_adopt_slots(ragen_ctx* ctx, int64_t n, int H, int W, int num_boxes, const uint8_t* state,
+                                         const uint8_t* fixed, int16_t* meta, int32_t* status, const uint8_t* only,
+                                         uint8_t* state4, void* stream) {
   RAGEN_REQUIRE(ctx, "ctx is NULL");
+  RAGEN_REQUIRE(!state4 || ((H * W) & 1) == 0, "nibble rooms need an even H*W, got %dx%d", H, W);
   RAGEN_SOKOBAN_SHAPE(n, H, W);
   RAGEN_REQUIRE(num_boxes >= 0 && num_boxes <= 127, "num_boxes=%d out of range", num_boxes);
   RAGEN_REQUIRE(state && fixed && meta, "NULL pointer argument");
@@ -704,7 +722,7 @@ extern "C" int ragen_sokoban_adopt(ragen_ctx* ctx, int64_t n, int H, int W, int 
   const size_t smem = 2 * (size_t)round16(TE * H * W);
   RAGEN_REQUIRE(smem <= 227 * 1024, "room %dx%d does not fit the shared-memory tile (%zu B)", H, W, smem);
   RAGEN_CUDA(cudaFuncSetAttribute(sokoban_adopt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  AdoptParams p{n, H, W, num_boxes, state, fixed, reinterpret_cast<EnvMeta*>(meta), status};
+  AdoptParams p{n, H, W, num_boxes, state, fixed, reinterpret_cast<EnvMeta*>(meta), status, only, state4};
   sokoban_adopt_kernel<<<(unsigned)((n + TE - 1) / TE), TE, smem, (cudaStream_t)stream>>>(p);
   RAGEN_LAUNCHED(ctx);
   return RAGEN_OK;

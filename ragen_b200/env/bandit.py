@@ -57,6 +57,15 @@ class BanditBatch:
                                                self.ctx.stream()))
         return self.lo_first
 
+    def reset_slot(self, slot, seed):
+        """BaseEnv.reset(seed) of ONE env of a shared batch (ragen/env/base.py:16): arm order and generator of `seed`."""
+        one = getattr(self, "_one", None)
+        if one is None:
+            one = self._one = BanditBatch(1, self.config, device=self.device.index)
+        one.reset([seed])
+        self.lo_first[slot] = one.lo_first[0]
+        self.rng[:, slot].copy_(one.rng[:, 0])
+
     def step(self, actions, active=None):
         """actions uint8 CUDA [n] (action ids); active uint8 [n] or None.  Returns (reward f64 [n], flags u8 [n])."""
         c = self.config
@@ -101,11 +110,12 @@ class BanditEnv(BaseDiscreteActionEnv):
         return self.render_cache
 
     def reset(self, seed=None, mode=None):
-        if self.batch.n != 1:
-            raise NotImplementedError("reset a shared batch through BanditBatch.reset / EnvStateManager.reset")
         if seed is None:
             seed = int(np.random.SeedSequence().entropy % (2 ** 63))
-        self.batch.reset([seed])
+        if self.batch.n != 1:
+            self.batch.reset_slot(self.slot, seed)  # the neighbours in the batch are not touched
+        else:
+            self.batch.reset([seed])
         return self.adopt_reset()
 
     def _staging(self):

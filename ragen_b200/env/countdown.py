@@ -99,8 +99,21 @@ class CountdownEnv(BaseLanguageBasedEnv):
 
     def compute_reward(self, action, ground_truth=None):
         gt = ground_truth if ground_truth is not None else self.data[self.index]
-        res, _ = self.batch.score([action], [list(gt["nums"])], [gt["target"]])
+        res, uns = self.batch.score([action], [list(gt["nums"])], [gt["target"]])
+        self.note_unsupported(action, bool(uns[0]))
         return self.reward_from_result(int(res[0]))
+
+    def note_unsupported(self, action, flag):
+        """The device evaluator's `unsupported` bit, surfaced: the answer left the covered grammar of Python expressions
+        (include/ragen_b200.h: ragen_countdown_score) and was scored as if eval() had raised - the reference's eval
+        (countdown/env.py:16-21) might have scored it as correct.  No host re-evaluation happens; the caller is told."""
+        self.last_unsupported = flag
+        if flag:
+            import warnings
+
+            self.n_unsupported = getattr(self, "n_unsupported", 0) + 1
+            warnings.warn(f"Countdown answer outside the device evaluator's grammar, scored as an eval() exception: {action!r}",
+                          RuntimeWarning, stacklevel=2)
 
     def finish_step(self, reward):
         next_obs = f"Your answer get {reward} points."

@@ -62,6 +62,18 @@ class FrozenLakeBatch:
             raise RuntimeError("no valid FrozenLake map found for some seeds")
         return self.obs
 
+    def reset_slot(self, slot, seed):
+        """BaseEnv.reset(seed) of ONE env of a shared batch (ragen/env/base.py:16, es_manager.py:93-95): the map, the start
+        state and the generator of `seed` go into the slot; every other env keeps its episode."""
+        one = getattr(self, "_one", None)
+        if one is None:
+            one = self._one = FrozenLakeBatch(1, self.size, self.p, self.is_slippery, device=self.device.index)
+        one.reset([seed])
+        self.tiles[slot].copy_(one.tiles[0])
+        self.pos[slot] = one.pos[0]
+        self.rng[:, slot].copy_(one.rng[:, 0])
+        self.obs[slot].copy_(one.obs[0])
+
     def step(self, actions, n_actions=None, render=True) -> StepOut:
         if actions.dim() == 1:
             actions = actions.unsqueeze(1)
@@ -115,12 +127,13 @@ class FrozenLakeEnv(BaseDiscreteActionEnv):
         return (self.s // self.ncol, self.s % self.ncol)
 
     def reset(self, seed=None, mode=None):
-        if self.batch.n != 1:
-            raise NotImplementedError("reset a shared batch through FrozenLakeBatch.reset / EnvStateManager.reset")
         if seed is None:
             seed = int(np.random.SeedSequence().entropy % (2 ** 63))
         self.config.map_seed = seed
-        self.batch.reset([seed])
+        if self.batch.n != 1:
+            self.batch.reset_slot(self.slot, seed)  # the neighbours in the batch are not touched
+        else:
+            self.batch.reset([seed])
         return self.render()
 
     def _staging(self):

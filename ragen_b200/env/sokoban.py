@@ -246,7 +246,7 @@ class SokobanBatch:
                 dst = torch.tensor(slots, dtype=torch.long, device=self.device)
                 self.fixed[dst] = fixed[src]
                 self.state[dst] = state[src]
-                self.adopt()
+                self.adopt(slots=dst)
                 return seeds
             st = status.cpu().tolist()
             nxt = []
@@ -285,7 +285,7 @@ class SokobanBatch:
         dst = torch.tensor(slots, dtype=torch.long, device=self.device)
         self.fixed[dst] = f_all[src]
         self.state[dst] = s_all[src]
-        self.adopt()
+        self.adopt(slots=dst)
         return used
 
     def solve(self, rows=None, max_depth=100, want_path=True):
@@ -294,14 +294,23 @@ class SokobanBatch:
         s = self.state if rows is None else self.state[rows]
         return solve_rooms(f, s, (self.H, self.W), self.num_boxes, max_depth, self.device.index, want_path)
 
-    def adopt(self, check=True):
-        if self.compact:
-            pack_rooms(self.state, out=self.state4)
-        _lib.check(self.lib.ragen_sokoban_adopt(
-            self.ctx.handle, self.n, self.H, self.W, self.num_boxes, _lib.ptr(self.state), _lib.ptr(self.fixed),
-            _lib.ptr(self.meta), _lib.ptr(self.status), self.ctx.stream()))
+    def adopt(self, check=True, slots=None):
+        """Post-reset bookkeeping (env.py:37-38) of all envs, or of `slots` only (a device index tensor / list): the other envs
+        keep their record - an env in mid-episode must not lose its step count or its stored box count because a neighbour in
+        the batch was reset.  The nibble rooms of a compact batch are written by the same launch."""
+        only = None
+        if slots is not None:
+            idx = torch.as_tensor(slots, dtype=torch.long, device=self.device)
+            if idx.numel() != self.n or bool((idx != torch.arange(self.n, device=self.device)).any()):
+                only = torch.zeros(self.n, dtype=torch.uint8, device=self.device)
+                only[idx] = 1
+        state = self.state  # refreshes the byte view of a compact batch before the untouched rooms are read
+        _lib.check(self.lib.ragen_sokoban_adopt_slots(
+            self.ctx.handle, self.n, self.H, self.W, self.num_boxes, _lib.ptr(state), _lib.ptr(self.fixed),
+            _lib.ptr(self.meta), _lib.ptr(self.status), _lib.ptr(only), _lib.ptr(self.state4) if self.compact else None,
+            self.ctx.stream()))
         if check:
-            bad = torch.nonzero(self.status).flatten()
+            bad = torch.nonzero(self.status if only is None else self.status * only).flatten()
             if bad.numel():
                 i = int(bad[0])
                 raise ValueError(f"room {i} rejected (status {int(self.status[i])}: 1 = no player, 2 = border not wall, "
@@ -562,7 +571,7 @@ class SokobanEnv(BaseDiscreteActionEnv):
         b = self.batch
         b.fixed[self.slot].copy_(torch.as_tensor(np.asarray(fixed, dtype=np.uint8).reshape(-1)))
         b.state[self.slot].copy_(torch.as_tensor(np.asarray(state, dtype=np.uint8).reshape(-1)))
-        b.adopt()
+        b.adopt(slots=[self.slot])
         return self.render()
 
     def reset(self, seed=None, mode=None):

@@ -274,9 +274,10 @@ class EnvStateManager:
             todo_plans = [(i, p) for i, p in zip(idxs, plans) if p[3]]
             if todo_plans:
                 gts = [p[1]["env"].data[p[1]["env"].index] for _, p in todo_plans]
-                res, _ = b.score([p[3][0] for _, p in todo_plans], [list(g["nums"]) for g in gts], [g["target"] for g in gts])
-                for (i, p), r in zip(todo_plans, res):
+                res, uns = b.score([p[3][0] for _, p in todo_plans], [list(g["nums"]) for g in gts], [g["target"] for g in gts])
+                for (i, p), r, u in zip(todo_plans, res, uns):
                     env = p[1]["env"]
+                    env.note_unsupported(p[3][0], bool(u))  # warns: scored as an eval() exception, never re-evaluated on the host
                     _, reward, done, info = env.finish_step(env.reward_from_result(int(r)))
                     results[i] = (0 + reward, info, done, 1)
             for i, p in zip(idxs, plans):
@@ -316,6 +317,8 @@ class EnvStateManager:
                     env_metric[k] = np.sum(v)
             cache["history"][-1]["metrics"] = custom_metric
             cache["metrics"] = {f"{entry['tag']}/{k}": v for k, v in env_metric.items()}
+            if entry["tag"] == "MetamathQA":  # es_manager.py:205-206
+                cache["correct_answer"] = entry["env"].correct_answer
         return self.rollout_cache
 
     def _update_cache_history(self, history: List[Dict], next_state, actions_left, num_actions_info: Optional[Dict] = None):

@@ -603,7 +603,14 @@ def countdown():
              ("7/2*2", [7, 2, 2], 7), ("10/4", [10, 4], 2), ("  3 + 4", [3, 4], 7), ("3 + 4\n", [3, 4], 7), ("3 4 +", [3, 4], 7),
              ("3 ++ 4", [3, 4], 7), ("3 +* 4", [3, 4], 7), ("((3)) + ((4))", [3, 4], 7), ("3 + 4 answer", [3, 4], 7),
              ("1/3*3", [1, 3, 3], 1), ("50 - 25 - 12", [50, 25, 12], 13), ("5 * 5 / 5", [5, 5, 5], 5), ("0/5 + 2", [0, 5, 2], 2),
-             ("8/0", [8, 0], 1), ("00 + 7", [0, 7], 7), ("7 - 00", [0, 7], 7)]
+             ("8/0", [8, 0], 1), ("00 + 7", [0, 7], 7), ("7 - 00", [0, 7], 7),
+             # the rest of what eval() takes from an LLM: floor division, modulo, powers, float literals
+             ("8 // 2 + 3", [8, 2, 3], 7), ("2**3", [2, 3], 8), ("7 % 3 + 5", [7, 3, 5], 6), ("-7 // 2", [7, 2], -4), ("-7 % 3", [7, 3], 2),
+             ("7 % -3", [7, 3], -2), ("2**-1 * 4", [2, 1, 4], 2), ("-2**2", [2, 2], -4), ("2**3**2", [2, 3, 2], 512), ("(2**3)**2", [2, 3, 2], 64),
+             ("1.5*2", [1, 5, 2], 3), (".5*4", [5, 4], 2), ("3e0+4", [3, 0, 4], 7), ("7.0 // 2", [7, 0, 2], 3), ("7.5 % 2", [7, 5, 2], 1),
+             ("5 // 0", [5, 0], 1), ("5 % 0", [5, 0], 1), ("0 ** -1", [0, 1], 1), ("2 ** 0.5 * 2 ** 0.5", [2, 0, 5, 2, 0, 5], 2),
+             ("9 ** 0.5", [9, 0, 5], 3), ("10 // 3 * 3 + 10 % 3", [10, 3, 3, 10, 3], 10), ("6 / 4 // 1", [6, 4, 1], 1),
+             ("012.5 + 1", [12, 5, 1], 13), ("1. + 2", [1, 2], 3), ("4 ** 3 ** 0", [4, 3, 0], 4), ("-3 ** 2 + 18", [3, 2, 18], 9)]
     obj = type("X", (), {"config": type("C", (), {"score": 1, "format_score": 0.1})})()
     rows = [{"answer": a, "nums": n, "target": t, "reward": cd.CountdownEnv.compute_reward(obj, a, {"target": t, "nums": n})}
             for a, n, t in cases]

@@ -104,7 +104,7 @@ def test_countdown_golden_and_grammar_flags():
     from ragen_b200 import ops
 
     rows = golden_json("countdown.json")
-    extra = [("2**3", [2, 3], 8), ("7//2", [7, 2], 3), ("1.5*2", [1, 5, 2], 3), ("((((((((((((((((((((((((((((((((((1))))))))))))))))))))))))))))))))))+2", [1, 2], 3)]
+    extra = [("9**99", [9, 99], 8), ("7 & 2", [7, 2], 3), ("1_5*2", [1, 5, 2], 3), ("((((((((((((((((((((((((((((((((((1))))))))))))))))))))))))))))))))))+2", [1, 2], 3)]
     answers = [r["answer"] for r in rows] + [e[0] for e in extra]
     nums_l = [r["nums"] for r in rows] + [e[1] for e in extra]
     targets = [r["target"] for r in rows] + [e[2] for e in extra]
@@ -121,4 +121,24 @@ def test_countdown_golden_and_grammar_flags():
     out, uns = out.cpu().numpy(), uns.cpu().numpy()
     for i, r in enumerate(rows):
         assert {0: 0, 1: 0.1, 2: 1}[int(out[i])] == r["reward"], r
+    assert not uns[:len(rows)].any()  # floor division, modulo, powers and float literals are inside the grammar
     assert out[len(rows):].tolist() == [1, 1, 1, 1] and uns[len(rows):].tolist() == [1, 1, 1, 1]
+
+
+def test_countdown_env_surfaces_the_unsupported_flag():
+    """An answer outside the device grammar is scored as an eval() exception AND reported (no host re-evaluation)."""
+    import warnings
+
+    from ragen_b200.env.countdown import CountdownEnv, CountdownEnvConfig
+
+    cfg = CountdownEnvConfig(data=[{"nums": [8, 2, 3], "target": 7}, {"nums": [7, 2, 2], "target": 3}])
+    env = CountdownEnv(cfg)
+    assert len(env.data) == 2
+    env.reset(seed=0)
+    with warnings.catch_warnings():
+        warnings.simplefilter("error")
+        assert env.step("8 // 2 + 3")[1] == env.config.score and env.last_unsupported is False
+    env.reset(seed=1)
+    with pytest.warns(RuntimeWarning, match="outside the device evaluator"):
+        _, reward, done, info = env.step("7 ^ 2 ^ 2")  # bit operators: eval() takes them, the device grammar does not
+    assert reward == env.config.format_score and done and env.last_unsupported is True and env.n_unsupported == 1

@@ -106,6 +106,41 @@ def test_full_size_properties():
     assert torch.equal(fused, b.obs)
 
 
+def test_full_size_compact_kernel_against_oracle_sample():
+    """The instance bench.py times - sokoban_tile_kernel<10, 10, 0, 3>: nibble rooms, three-bit rows - at BASELINE config 4's
+    size (1 Mi envs 10x10 / 2 boxes): equality with the batched oracle on a strided sample (states, rewards, done, flags,
+    three-bit glyph rows), conservation invariants on ALL envs, K = 1 and K = 2 turns."""
+    from ragen_b200.env.sokoban import SokobanBatch, unpack3_glyphs
+
+    n, H, W, nb = 1 << 20, 10, 10, 2
+    fixed, state = synthetic_rooms(n, H, W, nb, seed=14)
+    rng = np.random.default_rng(14)
+    b = SokobanBatch(n, (H, W), nb, 100, compact=True)
+    b.load_rooms(fixed, state)
+    sample = np.arange(3, n, 251)
+    o = SokobanBatchOracle(fixed[sample], state[sample], H, W, nb, 100)
+    walls = b.fixed == 0
+    for t in range(10):
+        K = 1 if t % 3 else 2
+        a = rng.integers(1, 5, (n, K)).astype(np.uint8)
+        out = b.step(torch.from_numpy(a).cuda(), packed=3)
+        acc, done, flags, nexec = o.step_turn(a[sample])
+        assert np.array_equal(out.reward.cpu().numpy()[sample], acc)
+        assert np.array_equal(out.done.cpu().numpy()[sample], done) and np.array_equal(out.flags.cpu().numpy()[sample], flags)
+        assert np.array_equal(out.n_executed.cpu().numpy()[sample], nexec)
+        assert np.array_equal(unpack3_glyphs(out.obs[torch.from_numpy(sample).cuda()].cpu().numpy(), H, W), o.glyphs())
+        s4 = b.state4
+        lo, hi = s4 & 15, s4 >> 4
+        assert int((lo == 5).sum() + (hi == 5).sum()) == n  # exactly one player per env
+        assert int(((lo == 3) | (lo == 4)).sum() + ((hi == 3) | (hi == 4)).sum()) == n * nb  # boxes conserved
+        st = b.state
+        assert np.array_equal(st.cpu().numpy()[sample], o.state)
+        assert bool(((st == 0) == walls).all())
+    # the three-bit rows of ALL envs are the render of the byte view (render kernel, byte rooms) in the same format
+    fused = out.obs.clone()
+    assert torch.equal(fused, b.render(packed=3).clone())
+
+
 def test_env_view_matches_reference_api(rooms):
     """SokobanEnv (per-env view with the reference's reset/step/render signature)."""
     from ragen_b200.env.sokoban import SokobanEnv, SokobanEnvConfig
@@ -378,14 +413,54 @@ def test_compact_rooms_step_like_the_byte_rooms(H, W, nb, n):
         b.step(torch.from_numpy(acts[:, None]).cuda(), packed=True)
     # a partial reset re-packs the rooms it touched and leaves the others alone
     before = b.state.clone()
+    meta_before = b.meta.clone()
     slots = [0, n // 2, n - 1] if n >= 3 else [0]
     b.reset([7, 7, 9][: len(slots)], slots=slots)
     after = b.state
     touched = torch.zeros(n, dtype=torch.bool, device="cuda")
     touched[slots] = True
     assert torch.equal(after[~touched], before[~touched])
+    assert torch.equal(b.meta[~touched], meta_before[~touched])  # steps / stored box count of envs in mid-episode survive
+    assert bool((b.meta[touched][:, 1] == 0).all())
     s4 = b.state4
     assert torch.equal(s4 & 15, after[:, 0::2]) and torch.equal(s4 >> 4, after[:, 1::2])
+
+
+@pytest.mark.parametrize("compact", [False, True])
+def test_slot_reset_leaves_the_other_envs_in_mid_episode(compact):
+    """BaseEnv.reset on ONE env of a shared batch (ragen/env/base.py:16): the neighbours keep num_env_steps and the stored
+    boxes_on_target, so their next rewards and their max_steps truncation are the oracle's."""
+    from ragen_b200.env.sokoban import SokobanBatch, SokobanEnv, SokobanEnvConfig
+
+    n, H, W, nb, max_steps = 300, 6, 6, 1, 9
+    fixed, state = synthetic_rooms(n, H, W, nb, seed=91)
+    rng = np.random.default_rng(92)
+    o = SokobanBatchOracle(fixed, state, H, W, nb, max_steps)
+    b = SokobanBatch(n, (H, W), nb, max_steps, search_depth=30, compact=compact)
+    b.load_rooms(fixed, state)
+    kw = {"packed": 3} if compact else {}
+    for turn in range(3):
+        acts = rng.integers(1, 5, (n, 2)).astype(np.uint8)
+        want = o.step_turn(acts)
+        out = b.step(torch.from_numpy(acts).cuda(), **kw)
+        assert np.array_equal(out.reward.cpu().numpy(), want[0])
+    # reset two slots (through the batch and through an env view); everybody else carries on against the oracle
+    slots = [5, 200]
+    b.reset([11, 12], slots=slots[:1])
+    env = SokobanEnv(SokobanEnvConfig(dim_room=(H, W), num_boxes=nb, max_steps=max_steps, search_depth=30), batch=b, slot=slots[1])
+    env.reset(seed=12)
+    keep = np.ones(n, dtype=bool)
+    keep[slots] = False
+    assert np.array_equal(b.env_steps.cpu().numpy().astype(np.int64)[keep], o.env_steps[keep])
+    assert np.array_equal(b.on_target.cpu().numpy().astype(np.int64)[keep], o.on_target[keep])
+    assert (b.env_steps.cpu().numpy()[slots] == 0).all()
+    for turn in range(3):  # 6 + 6 steps > max_steps 9: truncation must arrive on time for the untouched envs
+        acts = rng.integers(1, 5, (n, 2)).astype(np.uint8)
+        acc, done, flags, nexec = o.step_turn(acts)
+        out = b.step(torch.from_numpy(acts).cuda(), **kw)
+        assert np.array_equal(out.reward.cpu().numpy()[keep], acc[keep])
+        assert np.array_equal(out.done.cpu().numpy()[keep], done[keep]) and np.array_equal(out.n_executed.cpu().numpy()[keep], nexec[keep])
+        assert np.array_equal(b.state.cpu().numpy()[keep], o.state[keep])
 
 
 def test_compact_rooms_refuse_other_shapes():

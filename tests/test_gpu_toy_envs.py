@@ -118,6 +118,44 @@ def test_bandit_golden_and_env_view():
     assert rew.cpu().numpy().tolist() == want
 
 
+def test_env_views_reset_their_own_slot_of_a_shared_batch():
+    """BaseEnv.reset(seed) is the plugin contract (ragen/env/base.py:16, called per env at es_manager.py:93-95): a view onto
+    a manager-owned batch resets ITS slot; the neighbours keep their episode (map, position, generator state)."""
+    from ragen_b200.env.bandit import BanditBatch, BanditEnv, BanditEnvConfig
+    from ragen_b200.env.frozen_lake import FrozenLakeBatch, FrozenLakeEnv, FrozenLakeEnvConfig
+
+    n = 9
+    b = FrozenLakeBatch(n, 4, 0.8, True)
+    b.reset(np.arange(n) + 100)
+    refs = [TE.FrozenLakeOracle() for _ in range(n)]
+    for i, r in enumerate(refs):
+        r.reset(100 + i)
+    envs = [FrozenLakeEnv(FrozenLakeEnvConfig(), batch=b, slot=i) for i in range(n)]
+    for a in (2, 3):
+        for i in (0, 4, 8):
+            assert envs[i].step(a) == refs[i].step(a)
+    assert envs[4].reset(seed=42) == refs[4].reset(42)  # slot 4 starts over with another seed ...
+    assert envs[4].config.map_seed == 42
+    for a in (2, 2, 3, 1, 4, 2):
+        for i in range(n):  # ... and every env, reset or not, follows its own oracle
+            assert envs[i].step(a) == refs[i].step(a), (i, a)
+            assert envs[i].s == refs[i].s
+
+    cfg = BanditEnvConfig(lo_arm_name="Phoenix", hi_arm_name="Dragon")
+    bb = BanditBatch(n, cfg)
+    bb.reset(np.arange(n) + 500)
+    benvs = [BanditEnv(BanditEnvConfig(lo_arm_name="Phoenix", hi_arm_name="Dragon"), batch=bb, slot=i) for i in range(n)]
+    lo = bb.lo_first.cpu().numpy()
+    for e, lf in zip(benvs, lo):
+        e.adopt_reset(bool(lf))
+    ors = [TE.BanditOracle("Phoenix", "Dragon") for _ in range(n)]
+    for i, o in enumerate(ors):
+        o.reset(500 + i)
+    assert benvs[3].reset(seed=7) == ors[3].reset(7)
+    for i in range(n):
+        assert benvs[i].step(1 + i % 2) == ors[i].step(1 + i % 2), i
+
+
 def test_frozenlake_large_batch_properties():
     """1 Mi envs: every generated map has exactly one S and one G, G reachable from S (checked on the host with the
     reference's own DFS rule on a sample), positions stay in range, terminal envs never move."""

@@ -247,6 +247,25 @@ int ragen_masks_scores(ragen_ctx* ctx, int B, int L, const int64_t* input_ids, i
                        const double* turn_scores, const int32_t* n_turns, int max_turns, uint8_t* loss_mask,
                        uint8_t* response_mask, float* score, void* stream);
 
+/* get_lm_inputs' tensor assembly (ragen/llm_agent/ctx_manager.py:269-280: apply_chat_template -> tokenizer(texts, padding=True,
+ * padding_side="left") -> position_ids = attention_mask.cumsum(-1)) as a gather of pre-tokenised segments.  pool int32
+ * [pool_tokens] holds token ids; row b is the concatenation of segments e in [ent_off[b], ent_off[b+1]): ent_len[e] tokens from
+ * pool[ent_src[e]] written at column ent_dst[e] of the row (the caller lays rows out left-padded: the first segment starts at
+ * L - row_len[b]).  Outputs int64 [B][L]: input_ids (pad_id in the padding), attention_mask (0 / 1), position_ids (0 in the
+ * padding, then 1, 2, ...).  A segment that leaves the pool or its row's real region is skipped. */
+int ragen_traj_assemble(ragen_ctx* ctx, int B, int L, const int32_t* pool, int64_t pool_tokens, const int64_t* ent_src,
+                        const int32_t* ent_dst, const int32_t* ent_len, const int32_t* ent_off, const int32_t* row_len,
+                        int64_t pad_id, int64_t* input_ids, int64_t* attention_mask, int64_t* position_ids, void* stream);
+
+/* Text render of a grid observation straight into TOKEN ids (SokobanEnv.render, ragen/env/sokoban/env.py:53-57; FrozenLakeEnv
+ * .render, frozen_lake/env.py:47-57, followed by the tokenizer): codes [n][G] (or [n][G/2] when packed: two 4-bit codes per
+ * byte, low nibble first), env i at codes + i * pitch bytes, are the glyph rows the env kernels write (code 7 = row separator, the last byte of an env included:
+ * the "\n" that follows the state in the prompt, ctx_manager.py:259); [host] table int32 [8][4] / table_len int32 [8] give the
+ * 0..4 token ids of each code under the caller's tokenizer.  tokens int32 [n][stride] receives env i's ids, n_tokens (may be
+ * NULL) [n] their count.  Valid for tokenizers that split a grid per glyph (the caller verifies that against the tokenizer). */
+int ragen_glyph_tokens(ragen_ctx* ctx, int64_t n, int G, int packed, const uint8_t* codes, int64_t pitch, const int32_t* table,
+                       const int32_t* table_len, int stride, int32_t* tokens, int32_t* n_tokens, void* stream);
+
 /* _normalize_score_tensor (ctx_manager.py:175-226) on the last score column: out = score_last + penalty, then,
  * when n_groups < B, per group (dense ids 0..n_groups-1): method 0 identity, 1 mean, 2 mean_std, 3 asym_clip. */
 int ragen_group_norm(ragen_ctx* ctx, int B, const float* score_last, const float* penalty, const int32_t* group,

@@ -43,6 +43,8 @@ SIGNATURES = {
     "ragen_parse_actions": [_P, _L, _P, _P, _I, _c.c_char_p, _I, _P, _P, _P, _P, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P],
     "ragen_countdown_score": [_P, _L, _P, _P, _P, _P, _P, _P, _P, _P, _P],
     "ragen_masks_scores": [_P, _I, _I, _P, _L, _L, _I, _I, _I, _P, _P, _I, _P, _P, _P, _P],
+    "ragen_traj_assemble": [_P, _I, _I, _P, _L, _P, _P, _P, _P, _P, _L, _P, _P, _P, _P],
+    "ragen_glyph_tokens": [_P, _L, _I, _I, _P, _L, _P, _P, _I, _P, _P, _P],
     "ragen_group_norm": [_P, _I, _P, _P, _P, _I, _I, _P, _P],
     "ragen_group_norm_noalloc": [_P, _I, _P, _P, _P, _I, _I, _P, _P],
     "ragen_gae": [_P, _I, _I, _P, _P, _P, _D, _D, _P, _P, _P, _P],

@@ -12,13 +12,15 @@ from .es_manager import EnvStateManager
 
 
 class LLMAgentProxy:
-    def __init__(self, config, actor_rollout_wg, tokenizer, device: int = 0, rank: int = 0, world_size: int = 1, group=None):
+    def __init__(self, config, actor_rollout_wg, tokenizer, device: int = 0, rank: int = 0, world_size: int = 1, group=None,
+                 assembly: str = "device"):
         """rank / world_size / group (absent in the reference, which is single-process): one proxy per GPU, each owning the
-        env groups with group_id % world_size == rank; rollout metrics come back batch-global (ragen_b200/sharding.py)."""
+        env groups with group_id % world_size == rank; rollout metrics come back batch-global (ragen_b200/sharding.py).
+        assembly: "device" (token trajectories gathered on the GPU, llm_agent/assembly.py) or "host" (the reference's path)."""
         self.config = config
-        self.train_ctx_manager = ContextManager(config, tokenizer, mode="train", device=device).shard(world_size, group)
+        self.train_ctx_manager = ContextManager(config, tokenizer, mode="train", device=device, assembly=assembly).shard(world_size, group)
         self.train_es_manager = EnvStateManager(config, mode="train", device=device, rank=rank, world_size=world_size)
-        self.val_ctx_manager = ContextManager(config, tokenizer, mode="val", device=device).shard(world_size, group)
+        self.val_ctx_manager = ContextManager(config, tokenizer, mode="val", device=device, assembly=assembly).shard(world_size, group)
         self.val_es_manager = EnvStateManager(config, mode="val", device=device, rank=rank, world_size=world_size)
         self.actor_wg = actor_rollout_wg
         self.tokenizer = tokenizer

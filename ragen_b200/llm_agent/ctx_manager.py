@@ -1,9 +1,13 @@
 """ContextManager with the reference's interface (ragen/llm_agent/ctx_manager.py:74-356).
 
-Text assembly (chat messages, chat template, tokenizer) is the tokenizer's and stays on the host exactly as in the
-reference; the tensor passes run on the device through libragen_b200: response parsing + action lookup
-(ragen_parse_actions), loss / response masks and score placement (ragen_masks_scores), group reward normalisation
-(ragen_group_norm).  Outputs have the reference's DataProto layout (batch / non_tensor_batch / meta_info).
+The token trajectories are assembled ON THE DEVICE (assembly="device", the default; ragen_b200/llm_agent/assembly.py): every
+text chunk of a prompt is tokenised once into a token pool in HBM, grid observations go from the env kernels' glyph codes to
+token ids without becoming text, and one launch gathers each row's segments into the left-padded input_ids / attention_mask /
+position_ids the reference gets from "messages -> chat template -> tokenizer" (:248-280).  The reference's host path is kept as
+assembly="host" (explicit choice, and the parity oracle of the tests).  The other tensor passes run on the device through
+libragen_b200 as well: response parsing + action lookup (ragen_parse_actions), loss / response masks and score placement
+(ragen_masks_scores), group reward normalisation (ragen_group_norm).  Outputs have the reference's DataProto layout
+(batch / non_tensor_batch / meta_info).
 """
 from dataclasses import asdict
 from typing import Dict, List
@@ -28,6 +32,52 @@ except Exception:  # stand-in with the members this path touches (verl/verl/prot
             self.batch = batch
             self.non_tensor_batch = non_tensor_batch if non_tensor_batch is not None else {}
             self.meta_info = meta_info if meta_info is not None else {}
+
+
+class LazyBatch(dict):
+    """non_tensor_batch whose `messages_list` is built when somebody reads it: on the device path no message string exists
+    until then.  Reads through [], get, items, values and iteration over items all see the real value."""
+
+    def __init__(self, base, key, thunk):
+        super().__init__(base)
+        self._lazy_key, self._thunk = key, thunk
+        super().__setitem__(key, None)
+
+    def _force(self):
+        if self._thunk is not None:
+            thunk, self._thunk = self._thunk, None
+            super().__setitem__(self._lazy_key, thunk())
+
+    def __getitem__(self, k):
+        if k == self._lazy_key:
+            self._force()
+        return super().__getitem__(k)
+
+    def get(self, k, default=None):
+        if k == self._lazy_key:
+            self._force()
+        return super().get(k, default)
+
+    def items(self):
+        self._force()
+        return super().items()
+
+    def values(self):
+        self._force()
+        return super().values()
+
+    def __setitem__(self, k, v):
+        if k == self._lazy_key:
+            self._thunk = None
+        super().__setitem__(k, v)
+
+    def copy(self):
+        self._force()
+        return dict(self)
+
+    def __reduce__(self):
+        self._force()
+        return (dict, (dict(self),))
 
 
 def get_special_tokens(tokenizer):
@@ -59,11 +109,20 @@ def get_masks_and_scores(input_ids, tokenizer, all_scores=None, use_turn_scores=
 
 
 class ContextManager:
-    def __init__(self, config, tokenizer, processor=None, mode: str = "train", device: int = 0):
+    def __init__(self, config, tokenizer, processor=None, mode: str = "train", device: int = 0, assembly: str = "device",
+                 output_device="cpu"):
+        """assembly: "device" (token trajectories gathered on the GPU from pre-tokenised segments; a tokenizer that cannot be
+        decomposed that way is refused with TokenizerNotDecomposable) or "host" (the reference's string path).
+        output_device: where the tensors of the returned DataProto live ("cpu" as in the reference, or "cuda")."""
+        if assembly not in ("device", "host"):
+            raise ValueError(f"assembly must be 'device' or 'host', got {assembly!r}")
         self.config = config
         self.tokenizer = tokenizer
         self.processor = processor
         self.device = torch.device("cuda", int(device))
+        self.assembly = assembly
+        self.output_device = torch.device(output_device) if output_device != "cuda" else self.device
+        self._assembler = None
         self.action_sep = self.config.agent_proxy.action_sep
         self.special_token_list = ["<think>", "</think>", "<answer>", "</answer>", "<|im_start|>", "<|im_end|>"]
         self.es_cfg = self.config.es_manager[mode]
@@ -195,13 +254,28 @@ class ContextManager:
         return score_tensor
 
     # ---- LM inputs (ctx_manager.py:228-330) ---------------------------------------------------------------------------
-    def _messages(self, env_output: Dict, prepare_for_update: bool) -> List[Dict]:
-        """Chat messages of one trajectory (:248-267); trims `history` in place the way the reference does."""
+    def _trim_history(self, env_output: Dict, prepare_for_update: bool):
+        """In place, as the reference does (:241-246)."""
         if "state" in env_output["history"][-1] and prepare_for_update:
             env_output["history"] = env_output["history"][:-1]  # the state of turn n+1 is not part of the trajectory
         max_k = getattr(self.config.agent_proxy, "max_context_window", None)
         if max_k is not None and isinstance(max_k, int) and max_k > 0:
             env_output["history"] = env_output["history"][-max_k:]
+
+    def _messages(self, env_output: Dict, prepare_for_update: bool) -> List[Dict]:
+        """Chat messages of one trajectory (:248-267); trims `history` in place the way the reference does."""
+        self._trim_history(env_output, prepare_for_update)
+        return self._messages_of(env_output, prepare_for_update)
+
+    def _render_text(self, env_output: Dict, prepare_for_update: bool) -> str:
+        """The prompt text of an already trimmed trajectory (:269-274)."""
+        text = self.tokenizer.apply_chat_template(self._messages_of(env_output, prepare_for_update),
+                                                  add_generation_prompt=(not prepare_for_update), tokenize=False)
+        if not prepare_for_update:
+            text += "<think>" if self.config.agent_proxy.enable_think else "<answer>"  # the opening tag is forced
+        return text
+
+    def _messages_of(self, env_output: Dict, prepare_for_update: bool) -> List[Dict]:
         enable_think = self.config.agent_proxy.enable_think
         fmt = "<think> [Your thoughts] </think> <answer> [your answer] </answer>" if enable_think else "<answer> [your answer] </answer>"
         length = f"Max response length: {self.env_config_lookup[env_output['env_id']]['max_tokens']} words (tokens)."
@@ -238,18 +312,28 @@ class ContextManager:
     def get_lm_inputs(self, env_outputs: List[Dict], prepare_for_update: bool) -> DataProto:
         if len(env_outputs) == 0:
             return self._empty_lm_inputs(prepare_for_update)
-        llm_input_texts, messages_list = [], []
-        for env_output in env_outputs:
-            messages = self._messages(env_output, prepare_for_update)
-            text = self.tokenizer.apply_chat_template(messages, add_generation_prompt=(not prepare_for_update), tokenize=False)
-            if not prepare_for_update:
-                text += "<think>" if self.config.agent_proxy.enable_think else "<answer>"  # the opening tag is forced
-            llm_input_texts.append(text)
-            messages_list.append(messages)
+        if self.assembly == "device":
+            # segments of the token pool gathered on the GPU; no prompt string is built, nothing is re-tokenised
+            if self._assembler is None:
+                from .assembly import TrajectoryAssembler
 
-        inputs = self.tokenizer(llm_input_texts, return_tensors="pt", padding=True, padding_side="left", truncation=False)
-        input_ids, attention_mask = inputs.input_ids, inputs.attention_mask
-        position_ids = attention_mask.cumsum(dim=-1)
+                self._assembler = TrajectoryAssembler(self)
+            for env_output in env_outputs:
+                self._trim_history(env_output, prepare_for_update)
+            input_ids, attention_mask, position_ids = self._assembler.assemble(env_outputs, prepare_for_update)
+            messages_list = None  # built on first access (only API-calling worker groups read it, agent_proxy.py:96)
+        else:
+            llm_input_texts, messages_list = [], []
+            for env_output in env_outputs:
+                messages = self._messages(env_output, prepare_for_update)
+                text = self.tokenizer.apply_chat_template(messages, add_generation_prompt=(not prepare_for_update), tokenize=False)
+                if not prepare_for_update:
+                    text += "<think>" if self.config.agent_proxy.enable_think else "<answer>"  # the opening tag is forced
+                llm_input_texts.append(text)
+                messages_list.append(messages)
+            inputs = self.tokenizer(llm_input_texts, return_tensors="pt", padding=True, padding_side="left", truncation=False)
+            input_ids, attention_mask = inputs.input_ids, inputs.attention_mask
+            position_ids = attention_mask.cumsum(dim=-1)
         if prepare_for_update:
             scores = [[i.get("reward", 0.0) for i in env_output["history"]] for env_output in env_outputs]
             score_tensor, loss_mask, response_mask = get_masks_and_scores(
@@ -258,9 +342,17 @@ class ContextManager:
             normalized_score_tensor = score_tensor
             if not self.config.agent_proxy.use_turn_scores:
                 normalized_score_tensor = self._normalize_score_tensor(score_tensor, env_outputs)
-            response_length = response_mask.sum(dim=-1).float().mean().item()
-            self._response_tokens = (float(response_mask.sum()), int(response_mask.shape[0]))
+            per_row = response_mask.sum(dim=-1).cpu()  # B integers; the mean is taken where the reference takes it (CPU fp32, :288)
+            response_length = per_row.float().mean().item()
+            self._response_tokens = (float(per_row.sum()), int(response_mask.shape[0]))
 
+        if self.assembly == "device":  # the reference hands CPU tensors to the trainer: one copy per tensor at the boundary
+            out_dev = self.output_device
+            input_ids, attention_mask, position_ids = (t.to(out_dev) for t in (input_ids, attention_mask, position_ids))
+            if prepare_for_update:
+                aliased = normalized_score_tensor is score_tensor
+                loss_mask, score_tensor = loss_mask.to(out_dev), score_tensor.to(out_dev)
+                normalized_score_tensor = score_tensor if aliased else normalized_score_tensor.to(out_dev)
         llm_inputs = DataProto()
         llm_inputs.batch = TensorDict({"input_ids": input_ids, "attention_mask": attention_mask, "position_ids": position_ids,
                                        "responses": input_ids[:, 1:]}, batch_size=input_ids.shape[0])
@@ -268,11 +360,18 @@ class ContextManager:
             llm_inputs.batch["loss_mask"] = loss_mask
             llm_inputs.batch["rm_scores"] = normalized_score_tensor
             llm_inputs.batch["original_rm_scores"] = score_tensor  # the SAME tensor when normalised: the reference aliases them
-        llm_inputs.non_tensor_batch = {
+        non_tensor = {
             "env_ids": np.array([env_output["env_id"] for env_output in env_outputs], dtype=object),
             "group_ids": np.array([env_output["group_id"] for env_output in env_outputs], dtype=object),
-            "messages_list": np.array(messages_list, dtype=object),
         }
+        if messages_list is None:
+            # the managers keep mutating these dicts (es_manager.py:212-228): the messages are those of THIS call
+            snapshot = [{"env_id": eo["env_id"], "history": [dict(h) for h in eo["history"]]} for eo in env_outputs]
+            non_tensor = LazyBatch(non_tensor, "messages_list", lambda: np.array(
+                [self._messages_of(eo, prepare_for_update) for eo in snapshot], dtype=object))
+        else:
+            non_tensor["messages_list"] = np.array(messages_list, dtype=object)
+        llm_inputs.non_tensor_batch = non_tensor
         if prepare_for_update:
             llm_inputs.meta_info = {"metrics": self._mean_metrics(env_outputs, response_length)}
         return llm_inputs

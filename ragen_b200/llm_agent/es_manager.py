@@ -15,6 +15,8 @@ import torch
 
 from ..env import BATCH_TYPES, REGISTERED_ENV_CONFIGS, REGISTERED_ENVS
 from ..env.frozen_lake import fl_glyph_table
+from ..env.sokoban import glyph_table, unpack_glyphs
+from .assembly import ObsLog
 
 
 @dataclass
@@ -40,6 +42,7 @@ class _Block:
         self.tag, self.env_type, self.batch, self.first, self.count = tag, env_type, batch, first, count
         self.K = 1
         self.act = self.nact = None
+        self.log = None  # ObsLog of a grid block in text mode: the glyph rows of every turn stay on the device
 
 
 class EnvStateManager:
@@ -105,7 +108,7 @@ class EnvStateManager:
                 self._block_of[self.envs[b.first + i]["env_id"]] = b
 
     # ---- observations ----------------------------------------------------------------------------------------
-    def _block_texts(self, block) -> List:
+    def _block_texts(self, block, record=False) -> List:
         """Current observation of every env of the block: text, or a list of images (one device->host copy for grid envs)."""
         envs = self.envs[block.first:block.first + block.count]
         if block.env_type == "sokoban" and envs[0]["env"].render_mode == "rgb_array":
@@ -114,10 +117,30 @@ class EnvStateManager:
 
             frames = block.batch.render_rgb().cpu().numpy()
             return [[PIL.Image.fromarray(f, mode="RGB")] for f in frames]
-        if block.env_type == "sokoban":  # packed glyph rows (two codes per byte) when the room shape allows: half the copy
-            return block.batch.texts(envs[0]["env"].GRID_LOOKUP)
-        if block.env_type == "frozen_lake":
-            return _translate_rows(block.batch.obs.cpu().numpy(), fl_glyph_table(envs[0]["env"].GRID_LOOKUP))
+        if block.env_type in ("sokoban", "frozen_lake"):
+            b = block.batch
+            if block.env_type == "sokoban":  # packed glyph rows (two codes per byte) when the room shape allows: half the copy
+                if getattr(b, "obs_stale", False):
+                    b.render(packed=b.obs_is_packed)
+                if b.obs_is_packed == 3:
+                    b.render(packed=b.can_pack)
+                packed = bool(b.obs_is_packed)
+                dev = b.obs_packed if packed else b.obs
+                table, H, W = glyph_table(envs[0]["env"].GRID_LOOKUP), b.H, b.W
+            else:
+                packed, dev = False, b.obs
+                table, H, W = fl_glyph_table(envs[0]["env"].GRID_LOOKUP), b.size, b.size
+            host = dev.cpu().numpy()
+            codes = unpack_glyphs(host) if packed else host
+            texts = _translate_rows(codes, table)
+            if record:
+                # the device keeps the glyph rows of the turn and the strings carry a reference to them: the ContextManager
+                # assembles token trajectories from the codes without reading the characters (llm_agent/assembly.py)
+                if block.log is None:
+                    block.log = ObsLog(block.count, H, W, table, dev.device)
+                    block.log.begin()
+                texts = block.log.wrap(texts, block.log.record(dev, packed, codes))
+            return texts
         return [e["env"].render() for e in envs]
 
     # ---- reset (es_manager.py:75-103) ------------------------------------------------------------------------
@@ -154,7 +177,9 @@ class EnvStateManager:
         for s, e in zip(seeds, envs):
             e["status"] = EnvStatus(seed=s)
         for block in self.blocks:
-            texts = self._block_texts(block)
+            if block.log is not None:
+                block.log.begin()  # a new rollout: references into the previous one go stale
+            texts = self._block_texts(block, record=True)
             for i, t in enumerate(texts):
                 cache, e = rollout_cache[block.first + i], envs[block.first + i]
                 cache["history"] = self._update_cache_history(cache["history"], next_state=t,
@@ -183,7 +208,7 @@ class EnvStateManager:
                 self._run_block(block, [plans[i] for i in idxs], idxs, results)
         # 3. file the results into status / history, in input order
         env_outputs = []
-        texts = {id(b): self._block_texts(b) for b in self.blocks if id(b) in per_block}
+        texts = {id(b): self._block_texts(b, record=True) for b in self.blocks if id(b) in per_block}
         for i, (env_input, entry, valid, todo) in enumerate(plans):
             block = self._block_of[entry["env_id"]]
             pos = self._pos[entry["env_id"]]  # position in self.envs / self.rollout_cache

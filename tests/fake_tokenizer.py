@@ -101,3 +101,60 @@ class ScriptedWg:
                                 "group_ids": lm_inputs.non_tensor_batch["group_ids"]}
         res.meta_info = lm_inputs.meta_info
         return res
+
+
+def make_bpe_tokenizer(vocab_size=600, seed=0):
+    """A REAL byte-level BPE tokenizer (the `tokenizers` library) with Qwen2's pre-tokenizer regex and ChatML special tokens,
+    trained here on a synthetic corpus of prompts: its merges cross glyph boundaries ("##", "#_", "__#\\n" ...) the way a
+    production tokenizer's do, which the byte-level stand-in above cannot show.  Same duck type as FakeQwenTokenizer plus the
+    batched call with add_special_tokens=False that Hugging Face tokenizers offer."""
+    import numpy as np
+    from tokenizers import Regex, Tokenizer, decoders, models, pre_tokenizers, trainers
+
+    qwen_split = (r"(?i:'s|'t|'re|'ve|'m|'ll|'d)|[^\r\n\p{L}\p{N}]?\p{L}+|\p{N}| ?[^\s\p{L}\p{N}]+[\r\n]*|\s*[\r\n]+|\s+(?!\S)|\s+")
+    tk = Tokenizer(models.BPE())
+    tk.pre_tokenizer = pre_tokenizers.Sequence([pre_tokenizers.Split(Regex(qwen_split), behavior="isolated"),
+                                                pre_tokenizers.ByteLevel(add_prefix_space=False, use_regex=False)])
+    tk.decoder = decoders.ByteLevel()
+    rng = np.random.default_rng(seed)
+    glyphs = "#_OX√PS"
+    corpus = []
+    for _ in range(400):
+        W = int(rng.integers(4, 11))
+        rows = ["".join(glyphs[int(c)] for c in rng.choice(7, W, p=[0.45, 0.35, 0.04, 0.04, 0.04, 0.04, 0.04])) for _ in range(W)]
+        corpus.append("State:\n" + "\n".join(rows) + "\nYou have 7 actions left. Always output: <think> [Your thoughts] </think> "
+                      "<answer> [your answer] </answer> with no extra text. Strictly follow this format.")
+        corpus.append("You are solving the Sokoban puzzle. Reward:\n-0.1\n\nTurn 3:\n<think>plan</think><answer>Up || Down || Left</answer>")
+    trainer = trainers.BpeTrainer(vocab_size=vocab_size, special_tokens=list(SPECIALS), initial_alphabet=pre_tokenizers.ByteLevel.alphabet(),
+                                  show_progress=False)
+    tk.train_from_iterator(corpus, trainer)
+    return BpeChatTokenizer(tk)
+
+
+class BpeChatTokenizer:
+    name_or_path = "qwen-bpe-test"
+
+    def __init__(self, tk):
+        self.tk = tk
+        self.pad_token_id = tk.token_to_id("<|endoftext|>")
+        self.IM_START, self.IM_END = tk.token_to_id("<|im_start|>"), tk.token_to_id("<|im_end|>")
+
+    def encode(self, text):
+        return self.tk.encode(text, add_special_tokens=False).ids
+
+    apply_chat_template = FakeQwenTokenizer.apply_chat_template
+
+    def __call__(self, texts, return_tensors=None, padding=False, padding_side="left", truncation=False, add_special_tokens=True):
+        rows = [e.ids for e in self.tk.encode_batch(list(texts), add_special_tokens=add_special_tokens)]
+        if return_tensors != "pt":
+            return {"input_ids": rows}
+        L = max(len(r) for r in rows)
+        ids = torch.full((len(rows), L), self.pad_token_id, dtype=torch.long)
+        att = torch.zeros((len(rows), L), dtype=torch.long)
+        for i, r in enumerate(rows):
+            ids[i, L - len(r):] = torch.tensor(r, dtype=torch.long)
+            att[i, L - len(r):] = 1
+        return SimpleNamespace(input_ids=ids, attention_mask=att)
+
+    def batch_decode(self, ids, skip_special_tokens=True):
+        return self.tk.decode_batch([list(map(int, r)) for r in ids.tolist()], skip_special_tokens=skip_special_tokens)

@@ -22,16 +22,57 @@ def _digest(t):
     return hashlib.sha256(a.tobytes()).hexdigest()[:24] + ":" + "x".join(map(str, a.shape)) + ":" + str(a.dtype)
 
 
+GLYPHS = ("#", "_", "O", "√", "X", "P", "S", "\n")
+
+
+def _attach_device_observations(env_outputs):
+    """The golden env_outputs carry state STRINGS; give them the device reference a live EnvStateManager attaches (ObsLog slot +
+    row), so that the observation path of the device assembly - glyph codes -> ragen_glyph_tokens -> gather - is what produces
+    the tokens that are compared with the reference's digests."""
+    from ragen_b200.llm_agent.assembly import ObsLog, host_obs_from_text
+
+    n = len(env_outputs)
+    turns = max(len(e["history"]) for e in env_outputs)
+    log = ObsLog(n, 6, 6, GLYPHS, torch.device("cuda", 0))
+    log.begin()
+    for t in range(turns):
+        codes = np.full((n, 6 * 7), 7, dtype=np.uint8)
+        for i, e in enumerate(env_outputs):
+            if t < len(e["history"]) and "state" in e["history"][t]:
+                codes[i] = host_obs_from_text(e["history"][t]["state"], GLYPHS).codes.reshape(-1)
+        packed = t % 2 == 1  # both layouts the manager logs: one code per byte (after reset) and two per byte (after a step)
+        dev = torch.from_numpy((codes[:, 0::2] | (codes[:, 1::2] << 4)) if packed else codes).cuda()
+        slot = log.record(dev, packed, codes)
+        for i, e in enumerate(env_outputs):
+            if t < len(e["history"]) and "state" in e["history"][t]:
+                e["history"][t]["state"] = log.wrap([e["history"][t]["state"]] * n, slot)[i]
+    return log
+
+
+@pytest.mark.parametrize("assembly", ["device", "device-obs", "host"])
 @pytest.mark.parametrize("rec", G["variants"], ids=[r["name"] for r in G["variants"]])
-def test_get_lm_inputs_matches_reference(rec):
+def test_get_lm_inputs_matches_reference(rec, assembly):
+    """assembly: "device" = segments gathered on the GPU, states given as strings (tokenised inside their chunks);
+    "device-obs" = the same with the states as device glyph rows (what EnvStateManager hands over); "host" = the reference's
+    string path.  All three must reproduce the unmodified reference's tensors."""
     from ragen_b200.llm_agent.ctx_manager import ContextManager
 
     v = rec
     cfg = C.base_config(tags=("SimpleSokoban",), n_groups=(2,), group_size=4, **v["ap"])
     cfg.enable_response_mask = v["erm"]
-    ctx = ContextManager(cfg, FakeQwenTokenizer(), mode="train")
+    ctx = ContextManager(cfg, FakeQwenTokenizer(), mode="train", assembly=assembly.split("-")[0])
     env_outputs = copy.deepcopy(golden_json("es_manager.json")["final"])
+    if assembly == "device-obs":
+        _attach_device_observations(env_outputs)
+    from ragen_b200 import _lib
+
+    launches = _lib.Context.get(0).launches
     dp = ctx.get_lm_inputs(env_outputs, prepare_for_update=v["update"])
+    if assembly != "host":
+        assert _lib.Context.get(0).launches > launches  # the gather ran on the device
+    if assembly == "device-obs":
+        assert ctx._assembler.mode(env_outputs[0]["history"][0]["state"].log) == "cell"
+    assert not dp.batch["input_ids"].is_cuda  # the reference's contract: CPU tensors at the boundary
     assert list(dp.batch["input_ids"].shape) == rec["shape"]
     assert sorted(dp.batch.keys()) == sorted(rec["digest"].keys())
     assert [int(x) for x in dp.non_tensor_batch["env_ids"]] == rec["env_ids"]
@@ -135,7 +176,7 @@ def test_context_window_truncation_like_the_reference_test():
         "es_manager": {"train": {"env_configs": {"n_groups": [1], "tags": ["sokoban"]}, "group_size": 1}},
         "custom_envs": {"sokoban": {"env_type": "sokoban", "max_actions_per_traj": 10}},
         "actor_rollout_ref": {"rollout": {"response_length": 128}}})
-    ctx = ContextManager(config=cfg, tokenizer=DummyTokenizer(), mode="train")
+    ctx = ContextManager(config=cfg, tokenizer=DummyTokenizer(), mode="train", assembly="host")  # a stub with constant ids
     ctx.prefix_lookup = {0: "Initial prompt"}
     ctx.env_config_lookup = {0: {"max_tokens": 128}}
     ctx.env_nums = {"": 1}

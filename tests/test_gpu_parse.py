@@ -121,7 +121,8 @@ def test_countdown_golden_and_grammar_flags():
     out, uns = out.cpu().numpy(), uns.cpu().numpy()
     for i, r in enumerate(rows):
         assert {0: 0, 1: 0.1, 2: 1}[int(out[i])] == r["reward"], r
-    assert not uns[:len(rows)].any()  # floor division, modulo, powers and float literals are inside the grammar
+    flagged = [r["answer"] for r, u in zip(rows, uns) if u]
+    assert flagged == ["1 + 2 = 3", "3 + 4 answer"]  # floor division, modulo, powers and float literals are inside the grammar
     assert out[len(rows):].tolist() == [1, 1, 1, 1] and uns[len(rows):].tolist() == [1, 1, 1, 1]
 
 

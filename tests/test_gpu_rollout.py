@@ -33,20 +33,31 @@ class _Recorder(ScriptedWg):
         return out
 
 
-def _rollout(case):
+def _rollout(case, assembly="device", tok=None):
     from ragen_b200.llm_agent.agent_proxy import LLMAgentProxy
     from ragen_b200.llm_agent.ctx_manager import DataProto
 
     cfg = C.base_config(tags=tuple(case["tags"]), n_groups=tuple(case["n_groups"]), group_size=case["group_size"], **case["ap"])
-    tok = FakeQwenTokenizer()
+    tok = tok or FakeQwenTokenizer()
     wg = _Recorder(tok, DataProto)
-    proxy = LLMAgentProxy(cfg, wg, tok)
-    return proxy.rollout(DataProto(batch=None, non_tensor_batch=None, meta_info={}), val=False, seed=case["seed"]), wg
+    proxy = LLMAgentProxy(cfg, wg, tok, assembly=assembly)
+    dp = proxy.rollout(DataProto(batch=None, non_tensor_batch=None, meta_info={}), val=False, seed=case["seed"])
+    wg.proxy = proxy
+    return dp, wg
 
 
+@pytest.mark.parametrize("assembly", ["device", "host"])
 @pytest.mark.parametrize("case", CASES, ids=[c["name"] for c in CASES])
-def test_rollout_matches_reference_managers(case):
-    dp, wg = _rollout(case)
+def test_rollout_matches_reference_managers(case, assembly):
+    """assembly="device": every prompt of every turn is gathered on the GPU from token segments, the observations from the
+    glyph rows the env kernels wrote (no prompt string is built); "host": the reference's string path.  Both must give the
+    unmodified reference's tokens, turn by turn."""
+    dp, wg = _rollout(case, assembly)
+    if assembly == "device":
+        modes = wg.proxy.train_ctx_manager._assembler._modes
+        assert modes and set(modes.values()) == {"cell"}  # grid observations went through ragen_glyph_tokens
+        msgs = dp.non_tensor_batch["messages_list"]  # built on demand; same shape as the reference's object array
+        assert len(msgs) == dp.batch["input_ids"].shape[0] and msgs[0][0]["role"] == "system"
     assert wg.turns == case["turns"]  # every prompt of every turn, token for token
     assert list(dp.batch["input_ids"].shape) == case["shape"]
     for k in ("input_ids", "attention_mask", "position_ids", "responses", "loss_mask"):
@@ -61,6 +72,23 @@ def test_rollout_matches_reference_managers(case):
         assert float(dp.meta_info["metrics"][k]) == pytest.approx(w, rel=1e-12), k
     if case["ap"].get("reward_normalization", {}).get("method", "identity") == "identity":
         assert _digest(rm) == case["digest"]["rm_scores"]
+
+
+@pytest.mark.parametrize("case", CASES[:2], ids=[c["name"] for c in CASES[:2]])
+def test_rollout_with_a_bpe_tokenizer_device_equals_host(case):
+    """A real BPE tokenizer (Qwen's pre-tokenizer, merges across glyphs): the device assembly takes the row-dictionary mode and
+    must give the host path's tensors for every turn and for the final batch."""
+    from fake_tokenizer import make_bpe_tokenizer
+
+    tok = make_bpe_tokenizer()
+    dev, wg_d = _rollout(case, "device", tok)
+    host, wg_h = _rollout(case, "host", tok)
+    assert wg_d.turns == wg_h.turns and len(wg_d.turns) >= 2
+    modes = wg_d.proxy.train_ctx_manager._assembler._modes
+    assert set(modes.values()) <= {"row", "text"} and "row" in modes.values()
+    for k in ("input_ids", "attention_mask", "position_ids", "responses", "loss_mask", "rm_scores"):
+        assert torch.equal(dev.batch[k], host.batch[k]), k
+    assert dev.meta_info["metrics"] == host.meta_info["metrics"]
 
 
 def test_rollout_to_advantage_c5_shape():

@@ -446,7 +446,7 @@ def test_slot_reset_leaves_the_other_envs_in_mid_episode(compact):
         assert np.array_equal(out.reward.cpu().numpy(), want[0])
     # reset two slots (through the batch and through an env view); everybody else carries on against the oracle
     slots = [5, 200]
-    b.reset([11, 12], slots=slots[:1])
+    b.reset([11], slots=slots[:1])
     env = SokobanEnv(SokobanEnvConfig(dim_room=(H, W), num_boxes=nb, max_steps=max_steps, search_depth=30), batch=b, slot=slots[1])
     env.reset(seed=12)
     keep = np.ones(n, dtype=bool)

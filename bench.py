@@ -36,6 +36,7 @@ if ROOT not in sys.path:
 H, W, NUM_BOXES, MAX_STEPS = 10, 10, 2, 100
 BYTES_PER_STEP = 3 * H * W + 1 + 10 + 8 + 1 + 1 + H * (W + 1)  # = 431, SURVEY.md 8(d) C4(ii)
 MOVED_PER_STEP = 2 * H * W + 2 * 8 + 1 + 8 + 1 + 1 + 1 + H * (W + 1)  # = 338: state r+w, 8-byte record r+w, action, results, glyph rows
+TRAFFIC_FILE = "traffic_r2.json"  # DRAM bytes per launch of the bench's kernels, summed over >= 100 steady-state launches by ncu
 METRIC = "sokoban_env_steps_per_sec"
 UNIT = "env-steps/s"
 
@@ -50,8 +51,15 @@ def parse_args():
     ap.add_argument("--ref-envs", type=int, default=0, help="envs per reference step (0 = auto from core count)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-reset", action="store_true", help="skip the batched-reset leg (room generator + solver at config 4 size)")
+    ap.add_argument("--no-graph", action="store_true", help="issue the launches of a step from Python instead of replaying a CUDA graph")
+    ap.add_argument("--launches-per-step", type=int, default=128,
+                    help="back-to-back step launches (alternating batches) that make ONE bench step; env-steps per step = envs x this")
+    ap.add_argument("--reset-groups", type=int, default=65536, help="group rooms of the reset leg, over all ranks (0 = skip)")
+    ap.add_argument("--reset-distinct", type=int, default=1 << 20, help="distinct rooms of the reset leg's group_size=1 variant, over all ranks (0 = skip)")
     ap.add_argument("--obs", default="packed3", choices=["packed3", "packed", "bytes"],
-                    help="glyph-row format of the render: two 4-bit codes per byte (what the managers consume) or one code per byte")
+                    help="glyph-row format of the render: three bits per cell without separators (packed3), two 4-bit codes per byte "
+                         "(packed, what the managers consume) or one code per byte (bytes)")
     ap.add_argument("--rooms", default="nibbles", choices=["nibbles", "bytes"],
                     help="how the rooms rest in HBM: one cell per byte, or two (ragen_sokoban_step_compact; needs --obs packed3)")
     ap.add_argument("--rows", action="store_true", help="per-kernel lines for every SURVEY.md 8(d) config instead of the contract line")
@@ -60,13 +68,14 @@ def parse_args():
     return ap.parse_args()
 
 
-def workload_config(n_gpus, envs_per_gpu, obs="packed", rooms="bytes"):
+def workload_config(n_gpus, envs_per_gpu, obs="packed", rooms="bytes", launches_per_step=128):
     rows = {"packed3": "three bits per cell, no separators (38 B per env; ragen_sokoban_step_packed3)",
             "packed": "two 4-bit glyph codes per byte (55 B per env)", "bytes": "one glyph code per byte (110 B per env)"}[obs]
     return {"glyph_rows": rows, "rooms_in_hbm": "two cells per byte (ragen_sokoban_step_compact)" if rooms == "nibbles" else "one cell per byte",
             "workload": "sokoban_10x10_2box_step_render_reward", "dim_room": [H, W], "num_boxes": NUM_BOXES,
             "max_steps": MAX_STEPS, "envs_per_gpu": envs_per_gpu, "envs_total": envs_per_gpu * n_gpus,
-            "actions_per_launch": 1, "rooms": "synthetic random-walk rooms (ragen_b200/synth.py)",
+            "actions_per_launch": 1, "launches_per_step": launches_per_step, "env_steps_per_step": envs_per_gpu * n_gpus * launches_per_step,
+            "rooms": "synthetic random-walk rooms (ragen_b200/synth.py)",
             "actions": "uniform 1..4", "l2": "inputs larger than L2: two batches of envs_per_gpu envs stepped alternately, %d MB of distinct lines between two touches of a line (L2 is 126 MB)" % ((envs_per_gpu * 2 * ((50 if rooms == "nibbles" else 100) + 8 + 1 + 11 + {"packed3": 38, "packed": 55, "bytes": 110}[obs])) >> 20),
             "parallelism": f"env-sharded x{n_gpus}"}
 
@@ -93,15 +102,21 @@ def _ref_init(seed, n):
     return n
 
 
-def _ref_step(_):
-    envs = _W["envs"]
-    acts = _W["rng"].integers(1, 5, len(envs)).tolist()
-    t0 = time.perf_counter()
-    tot = 0.0
-    for e, a in zip(envs, acts):  # es_manager.py:149-169: serial loop, one env.step (with text render) each
-        obs, r, d, info = e.step(a)
-        tot += r
-    return time.perf_counter() - t0, tot
+def _ref_run(spec):
+    """warmup + steps serial passes over this worker's envs; returns the seconds the timed passes took."""
+    warmup, steps = spec
+    envs, rng = _W["envs"], _W["rng"]
+    spent = 0.0
+    for it in range(warmup + steps):
+        acts = rng.integers(1, 5, len(envs)).tolist()
+        t0 = time.perf_counter()
+        tot = 0.0
+        for e, a in zip(envs, acts):  # es_manager.py:149-169: serial loop, one env.step (with text render) each
+            obs, r, d, info = e.step(a)
+            tot += r
+        if it >= warmup:
+            spent += time.perf_counter() - t0
+    return spent
 
 
 def run_reference(args):
@@ -118,27 +133,20 @@ def run_reference(args):
     try:
         for r in [p.apply_async(_ref_init, (100 + i, per_core)) for i, p in enumerate(pools)]:
             r.get()
-
-        def one_step():
-            t0 = time.perf_counter()
-            for r in [p.apply_async(_ref_step, (0,)) for p in pools]:
-                r.get()
-            return time.perf_counter() - t0
-
-        for _ in range(args.warmup):
-            one_step()
-        times = [one_step() for _ in range(args.steps)]
+        # every worker runs ALL its steps on its own (no per-step round trip through the parent inside the timed region);
+        # the job's time is the slowest worker's
+        times = [r.get() for r in [p.apply_async(_ref_run, ((args.warmup, args.steps),)) for p in pools]]
     finally:
         for p in pools:
             p.terminate()
-    total = sum(times)
+    total = max(times)
     n = per_core * cores
     value = n * args.steps / total
     sample = f"{n} envs ({per_core}/core x {cores} procs) x {args.steps} steps, 1 action each, text render per step"
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": workload_config(args.gpus, args.envs, args.obs, args.rooms),
+            "config": workload_config(args.gpus, args.envs, args.obs, args.rooms, max(1, args.launches_per_step)),
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -223,6 +231,61 @@ def _claim_stdout():
     return keep
 
 
+def _reset_leg(args, rank, world, local_rank, barrier, dist, torch, np):
+    """C4(i) of SURVEY.md 8(d) / BASELINE config 4: the batched reset.  65 536 group rooms (group seed g, every env of a group shares
+    the room: es_manager.py:80-95) split over the ranks by group_id % world, then the group_size = 1 variant (1 Mi distinct rooms
+    in all).  Rooms are the reference generator's, seed for seed (tests/test_gpu_sokoban.py::test_generator_reproduces_reference_rooms);
+    validity = status 0 of generate_room's four tries; the solvability check is the reference's own BFS (get_shortest_action_path)
+    on the device over every valid group room."""
+    from ragen_b200.env.sokoban import SokobanBatch, solve_rooms
+
+    dev = torch.device("cuda", local_rank)
+    gen = SokobanBatch(1, (H, W), NUM_BOXES, MAX_STEPS, 300, device=local_rank)
+    out = {"kernels": ["sokoban_generate_kernel", "sokoban_solve_kernel"], "dim_room": [H, W], "num_boxes": NUM_BOXES, "search_depth": 300}
+    for name, total in (("group_rooms", args.reset_groups), ("distinct_rooms", args.reset_distinct)):
+        if total <= 0:
+            continue
+        seeds = np.arange(rank, total, world, dtype=np.int64)  # group g lives on rank g % world
+        gen.generate(seeds[:64])  # workspace allocation and first-launch costs stay outside the timed region
+        barrier()
+        t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0.record()
+        fixed, state, status, explored = gen.generate(seeds)
+        t1.record()
+        barrier()
+        ms = torch.tensor([t0.elapsed_time(t1)], dtype=torch.float64, device=dev)
+        ok = status == 0
+        stats = torch.tensor([float(ok.sum()), float(explored.sum()), float(seeds.size)], dtype=torch.float64, device=dev)
+        mx = torch.tensor([float(explored.max())], dtype=torch.float64, device=dev)
+        rec = {}
+        if name == "group_rooms":
+            fg, sg = fixed[ok].contiguous(), state[ok].contiguous()
+            s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s0.record()
+            sst, slen, _, _ = solve_rooms(fg, sg, (H, W), NUM_BOXES, max_depth=100, device=local_rank, want_path=False)
+            s1.record()
+            torch.cuda.synchronize()
+            solved = sst == 0
+            sol = torch.tensor([float(solved.sum()), float(slen[solved].sum()), s0.elapsed_time(s1)], dtype=torch.float64, device=dev)
+            if world > 1:
+                dist.all_reduce(sol[:2])
+                smax = sol[2:].clone()
+                dist.all_reduce(smax, op=dist.ReduceOp.MAX)
+                sol[2] = smax[0]
+            rec.update({"solver_ms": float(sol[2]), "bfs_solvable": float(sol[0]), "bfs_mean_solution_len": float(sol[1] / max(float(sol[0]), 1.0))})
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+            dist.all_reduce(stats)
+            dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        rec.update({"rooms": int(stats[2]), "ms": float(ms), "rooms_per_s": float(stats[2]) / (float(ms) * 1e-3),
+                    "valid_fraction": float(stats[0] / stats[2]), "mean_explored": float(stats[1] / stats[2]), "max_explored": int(mx)})
+        if "bfs_solvable" in rec:
+            rec["bfs_solvable_fraction_of_valid"] = rec.pop("bfs_solvable") / max(float(stats[0]), 1.0)
+        out[name] = rec
+        del fixed, state, status, explored
+    return out
+
+
 def run_native(args):
     out = _claim_stdout()
     rank = int(os.environ.get("RANK", "0"))
@@ -255,6 +318,12 @@ def run_native(args):
             dist.barrier(device_ids=[local_rank])
         torch.cuda.synchronize()
 
+    def max_over_ranks(x):
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
     n = args.envs
     fixed, state = synthetic_rooms(n, H, W, NUM_BOXES, seed=4 + rank)
     compact = args.rooms == "nibbles"
@@ -270,10 +339,10 @@ def run_native(args):
         b_.load_rooms(fixed, state)
         batches.append(b_)
     batch = batches[0]
-    R = 8  # rotating action slabs, all resident in HBM
+    RA = 8  # rotating action slabs, all resident in HBM
     g = torch.Generator(device=dev)
     g.manual_seed(1234 + rank)
-    actions = torch.randint(1, 5, (R, n), dtype=torch.uint8, device=dev, generator=g)
+    actions = torch.randint(1, 5, (RA, n), dtype=torch.uint8, device=dev, generator=g)
     host_actions = actions.cpu().pin_memory()  # the step's inputs live in pinned host memory (contract); step_host copies them up as they are
 
     sampler = ClockSampler(physical_gpu_index(local_rank))
@@ -281,47 +350,114 @@ def run_native(args):
         sampler.start()
 
     # ---- device-resident timing -------------------------------------------------------------------
+    # One bench "step" = R back-to-back launches (alternating batches), so that K steps are a timed region of tens of
+    # milliseconds that host jitter cannot move; the R launches are captured once into a CUDA graph and replayed (no
+    # Python / ctypes call per 30 us kernel inside the timed region).  R = 1 reproduces the round-1 line.
     packed = {"packed3": 3, "packed": True, "bytes": False}[args.obs]
     G = H * (W + 1)
     row_bytes = {"packed3": ((3 * H * W + 15) // 16) * 2, "packed": G // 2, "bytes": G}[args.obs]
+    R = max(1, args.launches_per_step)
+
+    def one_step(first):
+        for i in range(R):
+            batches[(first + i) & 1].step(actions[(first + i) % RA], packed=packed)
+
+    one_step(0)  # module load, cudaFuncSetAttribute: before any capture
+    torch.cuda.synchronize()
+    launch_mode, graph = "loop", None
+    if not args.no_graph and R % 2 == 0 and R % RA == 0:
+        try:
+            side = torch.cuda.Stream(dev)
+            side.wait_stream(torch.cuda.current_stream(dev))
+            with torch.cuda.stream(side):
+                one_step(0)
+            torch.cuda.current_stream(dev).wait_stream(side)
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph, stream=side):
+                one_step(0)
+            launch_mode = "cuda_graph"
+        except Exception as e:  # the plain loop is the same GPU work; say which one ran
+            graph, launch_mode = None, f"loop (graph capture failed: {type(e).__name__})"
+            torch.cuda.synchronize()
+
+    def run_step(i):
+        if graph is not None:
+            graph.replay()
+        else:
+            one_step(i * R)
+
     for i in range(args.warmup):
-        batches[i & 1].step(actions[i % R], packed=packed)
+        run_step(i)
     t_begin, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     launches0 = batch.ctx.launches
     t_begin.record()
     for i in range(args.steps):
-        batches[i & 1].step(actions[i % R], packed=packed)
+        run_step(i)
     t_end.record()
     barrier()
-    launches = batch.ctx.launches - launches0
+    launches = (R * args.steps) if graph is not None else (batch.ctx.launches - launches0)
     total_ms = t_begin.elapsed_time(t_end)
-    # the step kernel is the ONLY kernel in the timed region (gpu_launches == steps; profiles/*_launches.csv), so its average
-    # launch duration is the region divided by the launches; an event pair around every launch would itself cost ~2 us per step
+    # the step kernel is the ONLY kernel in the timed region (profiles/*_launches.csv), so its average launch duration is the
+    # region divided by the launches; an event pair around every launch would itself cost ~2 us per launch
     kern_ms = total_ms / max(1, launches)
-    t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    total_ms = float(t.item())
+    total_ms = max_over_ranks(total_ms)
 
     # ---- end to end with host buffers ----------------------------------------------------------------
     e2e = None
     if not args.no_e2e:
-        for i in range(max(args.warmup, 3)):
-            batches[i & 1].step_host(host_actions[i % R], packed=packed)
-        barrier()
-        t0 = time.perf_counter()
-        for i in range(args.steps):
-            batches[i & 1].step_host(host_actions[i % R], packed=packed)
-        barrier()
-        e2e_s = time.perf_counter() - t0
-        t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
-        if world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_s = float(t.item())
-        e2e = {"value": n * world * args.steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": n * 1,
-               "d2h_bytes_per_step": n * (row_bytes + 8 + 1 + 1 + 1), "ms_per_step": 1e3 * e2e_s / args.steps,
-               "api": "SokobanBatch.step_host -> ragen_sokoban_step%s (C ABI), pinned host buffers, one device->host copy" % ("_compact" if compact else {"packed3": "_packed3", "packed": "_packed", "bytes": ""}[args.obs]), "host_numa": numa}
+        e2e_steps = max(args.steps, 20)
+        api_tail = "_compact" if compact else {"packed3": "_packed3", "packed": "_packed", "bytes": ""}[args.obs]
+
+        def timed(fn, steps):
+            for i in range(max(args.warmup, 3)):
+                fn(i)
+            barrier()
+            t0 = time.perf_counter()
+            for i in range(steps):
+                fn(i)
+            barrier()
+            return max_over_ranks(time.perf_counter() - t0)
+
+        # (1) full results per step: glyph rows + reward / done / flags / n_executed, one device->host copy, synchronous
+        rows_s = timed(lambda i: batches[i & 1].step_host(host_actions[i % RA], packed=packed), e2e_steps)
+        e2e_rows = {"value": n * world * e2e_steps / rows_s, "unit": UNIT, "h2d_bytes_per_step": n * 1,
+                    "d2h_bytes_per_step": n * (row_bytes + 8 + 1 + 1 + 1), "ms_per_step": 1e3 * rows_s / e2e_steps,
+                    "api": "SokobanBatch.step_host -> ragen_sokoban_step%s (C ABI), pinned host buffers, one device->host copy" % api_tail}
+        e2e = dict(e2e_rows, host_numa=numa)
+        if compact:
+            # (2) the same results as 4-byte step deltas (ragen_sokoban_step_delta): lossless for a consumer that mirrors the rooms
+            # (HostMirror / decode_delta rebuild rooms, rows, rewards and flags bit for bit - tests/test_gpu_sokoban.py), two steps in
+            # flight (launch i+1 while the results of step i drain on a copy stream)
+            tickets = {}
+
+            def pipelined(i):
+                tickets[i + 1] = batches[(i + 1) & 1].step_host_begin(host_actions[(i + 1) % RA], "delta")
+                batches[i & 1].step_host_end(tickets.pop(i))
+
+            def run_pipelined(steps):
+                for w in range(3):
+                    batches[w & 1].step_host_end(batches[w & 1].step_host_begin(host_actions[w % RA], "delta"))
+                barrier()
+                t0 = time.perf_counter()
+                tickets[0] = batches[0].step_host_begin(host_actions[0], "delta")
+                for i in range(steps):
+                    pipelined(i)
+                batches[steps & 1].step_host_end(tickets.pop(steps))  # drain the look-ahead step (not counted)
+                barrier()
+                return max_over_ranks(time.perf_counter() - t0)
+
+            delta_s = run_pipelined(e2e_steps)
+            e2e = {"value": n * world * e2e_steps / delta_s, "unit": UNIT, "h2d_bytes_per_step": n * 1, "d2h_bytes_per_step": n * 4,
+                   "ms_per_step": 1e3 * delta_s / e2e_steps, "host_numa": numa,
+                   "api": "SokobanBatch.step_host_begin/_end -> ragen_sokoban_step_delta (C ABI): pinned host actions up, 4-byte step "
+                          "deltas down (player cell before / after, box destination, reward code + done / effective / success bits), "
+                          "two steps in flight; decode_delta / HostMirror rebuild rewards, flags and glyph rows on the host on demand",
+                   "full_rows": e2e_rows}
+
+    reset = None
+    if not args.no_reset:
+        reset = _reset_leg(args, rank, world, local_rank, barrier, dist, torch, np)
 
     clocks = sampler.stop() if rank == 0 else None
     if rank == 0:
@@ -330,25 +466,31 @@ def run_native(args):
             peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
         else:
             peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
-        achieved = BYTES_PER_STEP * n / (kern_ms * 1e-3) / 1e9
-        traffic = None
-        tpath = os.path.join(ROOT, "profiles", "traffic.json")
-        if os.path.exists(tpath):
-            traffic = json.load(open(tpath)).get("sokoban_step_compact_bytes_per_launch" if compact else
-                                                 {"packed3": "sokoban_step_packed3_bytes_per_launch", "packed": "sokoban_step_packed_bytes_per_launch",
-                                                  "bytes": "sokoban_step_bytes_per_launch"}[args.obs])
+        kname = "sokoban_tile_kernel<10,10,false,%d>" % (3 if compact else {"packed3": 2, "packed": 1, "bytes": 0}[args.obs])
         moved = MOVED_PER_STEP - G + row_bytes - (H * W if compact else 0)
-        line = {"metric": METRIC, "value": n * world * args.steps / (total_ms * 1e-3), "unit": UNIT, "n_gpus": world,
+        achieved = moved * n / (kern_ms * 1e-3) / 1e9
+        traffic, traffic_src = None, None
+        tpath = os.path.join(ROOT, "profiles", TRAFFIC_FILE)
+        if os.path.exists(tpath):
+            rec = json.load(open(tpath)).get(kname)
+            if rec:
+                traffic, traffic_src = rec["dram_bytes_per_launch"], "profiles/%s (%s)" % (TRAFFIC_FILE, rec.get("how", ""))
+        line = {"metric": METRIC, "value": n * world * launches / (total_ms * 1e-3), "unit": UNIT, "n_gpus": world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-                "config": workload_config(world, n, args.obs, args.rooms), "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
+                "config": workload_config(world, n, args.obs, args.rooms, R), "launch_mode": launch_mode,
+                "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                             "traffic": traffic, "kernel": "sokoban_tile_kernel<10,10,false,%d>" % (3 if compact else {"packed3": 2, "packed": 1, "bytes": 0}[args.obs]), "kernel_ms": kern_ms,
-                             "bytes_per_env_step": BYTES_PER_STEP, "peak_source": peak_src,
-                             "bytes_moved_per_env_step": moved, "frac_moved": moved * n / (kern_ms * 1e-3) / 1e9 / peak,
-                             "note": "frac uses SURVEY.md 8(d)'s 431 B per env-step, which charges a 100 B room_fixed read the kernel "
-                                     "avoids and 110 B of glyph rows; frac_moved uses the bytes this kernel has to move "
-                                     "(338 B with byte glyph rows, 283 B with nibble rows, 266 B with three-bit rows, 166 B with the rooms kept as nibbles too)"}}
+                             "traffic": traffic, "traffic_source": traffic_src, "kernel": kname, "kernel_ms": kern_ms,
+                             "bytes_per_env_step": moved, "peak_source": peak_src,
+                             "frac_survey_431B": BYTES_PER_STEP * n / (kern_ms * 1e-3) / 1e9 / peak,
+                             "note": "achieved / frac count the bytes this kernel has to move per env-step (rooms r+w as nibbles 100, "
+                                     "8-byte record r+w 16, action 1, results 11, three-bit rows 38 = 166 with the defaults; 266 / 283 / 338 B "
+                                     "with byte rooms and three-bit / nibble / byte rows).  frac_survey_431B applies SURVEY.md 8(d)'s figure, "
+                                     "which charges a 100 B room_fixed read and 110 B of glyph bytes this kernel does not move: it is "
+                                     "not a physical fraction"}}
+        if reset is not None:
+            line["reset"] = reset
         if cpu_base is not None:
             line["cpu_baseline"] = cpu_base
         print(json.dumps(line), file=out, flush=True)

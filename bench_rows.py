@@ -345,42 +345,76 @@ def c5_rows(quick):
 
 # ---- C1: the manager seam (host + device) ----------------------------------------------------------------------------------
 def manager_rows(quick):
+    """EnvStateManager.reset / step through the public API at C1's size and at 16 Ki / 1 Mi envs, wall clock (host + device), with
+    the CPU port of the reference's manager loop (oracle/managers.py: one Python env object per env, serial step loop with a text
+    render per step and per turn, es_manager.py:93-95, 149-169) timed beside it on a bounded sample of the same inputs."""
     from oracle import cfg as C
+    from oracle import managers as M
+    from oracle import sokoban as S
     from ragen_b200.llm_agent.es_manager import EnvStateManager
 
-    cfg = C.base_config(tags=("SimpleSokoban",), n_groups=(8,), group_size=16)
-    mgr = EnvStateManager(cfg, mode="train")
-    t0 = time.perf_counter(); mgr.reset(seed=123); torch.cuda.synchronize(); first = time.perf_counter() - t0
-    t0 = time.perf_counter(); cache = mgr.reset(seed=123); torch.cuda.synchronize(); reset_s = time.perf_counter() - t0
-    rng = np.random.default_rng(1)
     names = ["Up", "Down", "Left", "Right"]
-    alive = [c["env_id"] for c in cache]
-    turn_s, steps = [], 0
-    for _ in range(5):
-        inputs = []
-        for e in alive:
-            acts = [names[int(rng.integers(0, 4))] if rng.random() > 0.1 else "Jump" for _ in range(int(rng.integers(1, 4)))]
-            resp = "<think>t</think><answer>" + " || ".join(acts) + "</answer>"
-            inputs.append({"env_id": e, "llm_raw_response": resp, "llm_response": resp, "actions": acts})
-        t0 = time.perf_counter()
-        out = mgr.step(inputs)
-        turn_s.append(time.perf_counter() - t0)
-        steps += sum(len(i["actions"]) for i in inputs)
-        alive = [c["env_id"] for c in out]
-        if not alive:
-            break
-    print(json.dumps({"row": "C1 EnvStateManager 128 envs x 5 turns (wall clock, host + device)", "reset_s": reset_s, "first_reset_s": first,
-                      "turn_ms": [1e3 * t for t in turn_s], "env_steps": steps,
-                      "note": "latency-bound: 9 KB of state; the Python history bookkeeping the API promises dominates"}), flush=True)
+    for groups, tag in [(8, "C1 EnvStateManager 128 envs x 5 turns"), (1024, "EnvStateManager 16 Ki envs x 5 turns"),
+                        (16384 if quick else 65536, "EnvStateManager 1 Mi envs x 2 turns")]:
+        cfg = C.base_config(tags=("SimpleSokoban",), n_groups=(groups,), group_size=16)
+        mgr = EnvStateManager(cfg, mode="train")
+        n = groups * 16
+        turns = 5 if n <= 16384 else 2
+        t0 = time.perf_counter(); mgr.reset(seed=123); torch.cuda.synchronize(); first = time.perf_counter() - t0
+        t0 = time.perf_counter(); cache = mgr.reset(seed=123); torch.cuda.synchronize(); reset_s = time.perf_counter() - t0
+        b = mgr.blocks[0].batch
+        fixed0, state0 = b.fixed.cpu().numpy(), b.state.cpu().numpy()
+        rng = np.random.default_rng(1)
+        alive = [c["env_id"] for c in cache]
+        turn_s, steps, script = [], 0, []
+        for _ in range(turns):
+            inputs = []
+            for e in alive:
+                acts = [names[int(rng.integers(0, 4))] if rng.random() > 0.1 else "Jump" for _ in range(int(rng.integers(1, 4)))]
+                resp = "<think>t</think><answer>" + " || ".join(acts) + "</answer>"
+                inputs.append({"env_id": e, "llm_raw_response": resp, "llm_response": resp, "actions": acts})
+            script.append(inputs)
+            t0 = time.perf_counter()
+            out = mgr.step(inputs)
+            turn_s.append(time.perf_counter() - t0)
+            steps += sum(len(i["actions"]) for i in inputs)
+            alive = [c["env_id"] for c in out]
+            if not alive:
+                break
+        # the port on the first m envs, same rooms, same action strings
+        m = min(n, 2048)
+        lookup = {1: "Up", 2: "Down", 3: "Left", 4: "Right"}
+        envs = [{"tag": "SimpleSokoban", "env": S.SokobanOracle((6, 6), 1, 100), "max_actions_per_traj": 10, "action_lookup": lookup}
+                for _ in range(m)]
+        port = M.ManagerOracle(envs, 16)
+        port.reset(0, reset_fn=lambda i, e, seed: e["env"].load(fixed0[i], state0[i]))
+        cpu_turn_s = []
+        for inputs in script:
+            sub = [i for i in inputs if i["env_id"] < m]
+            t0 = time.perf_counter()
+            port.step(sub)
+            cpu_turn_s.append(time.perf_counter() - t0)
+        print(json.dumps({"row": tag + " (wall clock, host + device)", "envs": n, "reset_s": reset_s, "first_reset_s": first,
+                          "turn_ms": [1e3 * t for t in turn_s], "env_steps": steps,
+                          "cpu_port_turn_ms": [1e3 * t for t in cpu_turn_s], "cpu_port_envs": m,
+                          "cpu_port_turn_ms_scaled_to_envs": [1e3 * t * n / m for t in cpu_turn_s],
+                          "cpu_sample": f"{m} envs, oracle/managers.py ManagerOracle over oracle/sokoban.py envs, 1 core (the reference's execution model)",
+                          "note": "the Python history bookkeeping the API promises (one dict per env per turn) is what remains on the host"}), flush=True)
+        del mgr
 
 
 # ---- C5: rollout -> advantage through the public API, scripted policy -----------------------------------------------------
 def rollout_rows(quick):
     """8 groups x 16 SimpleSokoban envs, 5 turns, LLMAgentProxy.rollout with the scripted stand-in policy of tests/fake_tokenizer.py
     (the LLM is out of scope), then compute_advantage (GAE and GRPO).  Wall clock per phase; the policy's own time is reported
-    separately so that what remains is this package's share of a rollout."""
+    separately so that what remains is this package's share of a rollout.  Three arms: assembly="device" (token trajectories
+    gathered on the GPU from pre-tokenised segments, llm_agent/assembly.py), assembly="host" (the reference's string path kept as
+    the explicit alternative), and the CPU port of the whole reference loop (oracle/rollout.py, pinned on the reference-made
+    rollouts.json) on the same rooms with the same policy."""
     from fake_tokenizer import FakeQwenTokenizer, ScriptedWg
     from oracle import cfg as C
+    from oracle.rollout import RolloutPort
+    from ragen_b200.env.sokoban import SokobanBatch
     from ragen_b200.llm_agent.agent_proxy import LLMAgentProxy
     from ragen_b200.llm_agent.ctx_manager import DataProto
     from ragen_b200.trainer import AdvantageEstimator, compute_advantage
@@ -396,32 +430,68 @@ def rollout_rows(quick):
 
     cfg = C.base_config(tags=("SimpleSokoban",), n_groups=(8,), group_size=16, reward_normalization={"grouping": "state", "method": "mean_std"})
     tok = FakeQwenTokenizer()
-    proxy = LLMAgentProxy(cfg, Timed(tok, DataProto), tok)
-    res = []
-    for rep in range(4):
-        Timed.spent = 0.0
-        torch.cuda.synchronize()
+    arms = {}
+    for assembly in ("device", "host"):
+        proxy = LLMAgentProxy(cfg, Timed(tok, DataProto), tok, assembly=assembly)
+        res = []
+        for rep in range(6):
+            Timed.spent = 0.0
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            dp = proxy.rollout(DataProto(batch=None, non_tensor_batch=None, meta_info={}), val=False, seed=123 + rep)
+            torch.cuda.synchronize()
+            t_roll = time.perf_counter() - t0
+            batch = dp.batch
+            B, T = batch["rm_scores"].shape
+            batch["response_mask"] = batch["loss_mask"].float()
+            batch["token_level_rewards"] = batch["rm_scores"].clone()
+            batch["values"] = torch.randn(B, T) * batch["response_mask"]
+            dp.non_tensor_batch["uid"] = dp.non_tensor_batch["group_ids"]
+            t0 = time.perf_counter()
+            compute_advantage(dp, AdvantageEstimator.GAE, gamma=1.0, lam=1.0)
+            t_gae = time.perf_counter() - t0
+            t0 = time.perf_counter()
+            compute_advantage(dp, AdvantageEstimator.GRPO, multi_turn=True)
+            t_grpo = time.perf_counter() - t0
+            res.append({"rollout_s": t_roll, "policy_stub_s": Timed.spent, "ours_s": t_roll - Timed.spent, "gae_s": t_gae, "grpo_s": t_grpo,
+                        "B": B, "T": T, "success": float(dp.meta_info["metrics"].get("SimpleSokoban/success", 0.0))})
+        arms[assembly] = res
+    # CPU port of the reference loop: same rooms (generated once per group seed), same scripted policy
+    gen = SokobanBatch(1, (6, 6), 1, 100, 300, device=0)
+    port_res = []
+    for rep in range(3):
+        f, s, st, _ = gen.generate([123 + rep + g for g in range(8)])
+        assert not bool(st.any())
+        f, s = f.cpu().numpy(), s.cpu().numpy()
+        fixed = np.stack([f[i // 16] for i in range(128)])
+        state = np.stack([s[i // 16] for i in range(128)])
+        port = RolloutPort(tok, 8, 16, env_instruction=C.SOKOBAN_INSTRUCTION, max_tokens=100, norm_method="mean_std")
+        wg = ScriptedWg(tok, DataProto)
+        spent = [0.0]
+
+        def policy(lm):
+            t0 = time.perf_counter()
+            ids = np.array(lm["env_ids"], dtype=object)
+            out = wg.generate_sequences(DataProto(batch={"input_ids": lm["input_ids"]}, non_tensor_batch={"env_ids": ids, "group_ids": ids}))
+            spent[0] += time.perf_counter() - t0
+            return out.non_tensor_batch["response_texts"]
+
         t0 = time.perf_counter()
-        dp = proxy.rollout(DataProto(batch=None, non_tensor_batch=None, meta_info={}), val=False, seed=123 + rep)
-        torch.cuda.synchronize()
+        final = port.rollout(fixed, state, policy)
         t_roll = time.perf_counter() - t0
-        batch = dp.batch
-        B, T = batch["rm_scores"].shape
-        batch["response_mask"] = batch["loss_mask"].float()
-        batch["token_level_rewards"] = batch["rm_scores"].clone()
-        batch["values"] = torch.randn(B, T) * batch["response_mask"]
-        dp.non_tensor_batch["uid"] = dp.non_tensor_batch["group_ids"]
-        t0 = time.perf_counter()
-        compute_advantage(dp, AdvantageEstimator.GAE, gamma=1.0, lam=1.0)
-        t_gae = time.perf_counter() - t0
-        t0 = time.perf_counter()
-        compute_advantage(dp, AdvantageEstimator.GRPO, multi_turn=True)
-        t_grpo = time.perf_counter() - t0
-        res.append({"rollout_s": t_roll, "policy_stub_s": Timed.spent, "ours_s": t_roll - Timed.spent, "gae_s": t_gae, "grpo_s": t_grpo,
-                    "B": B, "T": T, "success": float(dp.meta_info["metrics"].get("SimpleSokoban/success", 0.0))})
+        port_res.append({"rollout_s": t_roll, "policy_stub_s": spent[0], "port_s": t_roll - spent[0], "B": int(final["input_ids"].shape[0]),
+                         "T": int(final["input_ids"].shape[1]) - 1})
+    med = lambda xs: float(np.median(xs))  # noqa: E731
     print(json.dumps({"row": "C5 rollout -> advantage through LLMAgentProxy / compute_advantage, 8 groups x 16 SimpleSokoban, 5 turns, scripted policy "
-                             "(wall clock, CPU tensors in and out as the reference's driver has them; first repetition includes warm-up)",
-                      "reps": res}), flush=True)
+                             "(wall clock, CPU tensors in and out as the reference's driver has them; the first repetition of an arm includes warm-up "
+                             "and the one-off tokenizer decomposability check)",
+                      "ours_s_device_assembly_median": med([r["ours_s"] for r in arms["device"][1:]]),
+                      "ours_s_host_assembly_median": med([r["ours_s"] for r in arms["host"][1:]]),
+                      "cpu_port_s_median": med([r["port_s"] for r in port_res]),
+                      "cpu_sample": "oracle/rollout.py RolloutPort: the reference's loop (per-env Python envs, whole history re-tokenised per turn), "
+                                    "rooms supplied, same scripted policy, 1 core; the byte-level stand-in tokenizer is Python, a Rust tokenizer "
+                                    "would make the host legs faster",
+                      "device": arms["device"], "host": arms["host"], "cpu_port": port_res}), flush=True)
 
 
 def main(quick=False, only=""):

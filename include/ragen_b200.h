@@ -107,6 +107,18 @@ int ragen_sokoban_step_compact(ragen_ctx* ctx, int64_t n, int H, int W, int num_
                                uint8_t* state4, int16_t* meta,
                                double* acc_reward, uint8_t* done, uint8_t* flags, uint8_t* n_executed,
                                uint8_t* obs_packed3, void* stream);
+/* The compact step with its results as DELTAS: a step changes at most three cells, so what a consumer that mirrors the rooms
+ * needs is 4 bytes per executed action instead of reward + flags + a re-rendered room (49 B per 10x10 env) - the transport
+ * format for callers that keep the results in host memory, where the device->host link bounds the step.
+ *   delta [n][K][4]: byte 0 player cell before the action, byte 1 player cell after, byte 2 cell the pushed box went to
+ *   (0xff: no push), byte 3 = reward code | done << 3 | action_is_effective << 4 | success << 5 | executed << 6, with reward code
+ *   0: -0.1, 1: -0.1 + 1, 2: -0.1 - 1, 3: -0.1 + 1 + 10, 4: -0.1 + 10 (gym_sokoban _calc_reward; the caller adds the doubles in
+ *   order, which reproduces acc_reward bit for bit).  Records of actions that were not executed are zero.
+ * The vacated cell shows room_fixed again, the box lands as 3 on a target else 4 (the consumer has room_fixed from the reset).
+ * Rooms as in ragen_sokoban_step_compact (6x6, 8x8, 10x10).  No glyph rows, no result arrays are written. */
+int ragen_sokoban_step_delta(ragen_ctx* ctx, int64_t n, int H, int W, int num_boxes, int max_steps,
+                             const uint8_t* actions, int K, const uint8_t* n_actions,
+                             uint8_t* state4, int16_t* meta, uint8_t* delta, void* stream);
 int ragen_sokoban_render_packed3(ragen_ctx* ctx, int64_t n, int H, int W, const uint8_t* state,
                                  const int16_t* meta, uint8_t* obs_packed3, void* stream);
 

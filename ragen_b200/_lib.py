@@ -29,6 +29,7 @@ SIGNATURES = {
     "ragen_sokoban_render_packed": [_P, _L, _I, _I, _P, _P, _P, _P],
     "ragen_sokoban_step_packed3": [_P, _L, _I, _I, _I, _I, _P, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P],
     "ragen_sokoban_step_compact": [_P, _L, _I, _I, _I, _I, _P, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P],
+    "ragen_sokoban_step_delta": [_P, _L, _I, _I, _I, _I, _P, _I, _P, _P, _P, _P, _P],
     "ragen_sokoban_render_packed3": [_P, _L, _I, _I, _P, _P, _P, _P],
     "ragen_sokoban_render_rgb": [_P, _L, _I, _I, _I, _P, _P, _P, _P, _L, _P, _P],
     "ragen_sokoban_adopt": [_P, _L, _I, _I, _I, _P, _P, _P, _P, _P],

@@ -46,6 +46,7 @@ struct StepParams {
   uint8_t* flags;
   uint8_t* n_executed;
   uint8_t* obs;
+  uint8_t* delta;  // [n][K][4] or NULL: per-action delta records instead of the four result arrays (ragen_sokoban_step_delta)
 };
 
 __host__ __device__ inline int round16(int x) { return (x + 15) & ~15; }
@@ -362,9 +363,11 @@ __global__ void __launch_bounds__(TE) sokoban_tile_kernel(const StepParams p) {
     int actual = m.actual;   // the true count of the board; differs from `on` only right after a reset
     double acc = 0.0;
     int fl = 0, nexec = 0, dn = 0;
+    uint32_t* drec = p.delta ? reinterpret_cast<uint32_t*>(p.delta) + g * p.K : nullptr;
     for (int k = 0; k < na; ++k) {
       const int a = (k < 4) ? (int)((acts >> (8 * k)) & 0xff) : (int)p.actions[g * p.K + k];
       const int before = pos;
+      int box_to = 0xff;
       ++steps;
       int delta = 0;  // change of the on-target count caused by this action
       if (a >= 1 && a <= 4) {
@@ -381,6 +384,7 @@ __global__ void __launch_bounds__(TE) sokoban_tile_kernel(const StepParams p) {
               put(beyond, (sb == 2) ? 3 : 4);
               delta = (int)(sb == 2) - (int)(sa == 3);
               go = true;
+              box_to = beyond;
             }
           }
         }
@@ -395,8 +399,9 @@ __global__ void __launch_bounds__(TE) sokoban_tile_kernel(const StepParams p) {
       // count stored by the previous step; the recount is the running count plus this action's delta
       const int now_on = actual + delta;
       double rew = -0.1;
-      if (now_on > on) rew += 1.0;
-      else if (now_on < on) rew += -1.0;
+      const bool now_on_rose = now_on > on, now_on_fell = now_on < on;
+      if (now_on_rose) rew += 1.0;
+      else if (now_on_fell) rew += -1.0;
       const bool won = (now_on == p.num_boxes);
       if (won) rew += 10.0;
       on = actual = now_on;
@@ -404,18 +409,29 @@ __global__ void __launch_bounds__(TE) sokoban_tile_kernel(const StepParams p) {
       ++nexec;
       fl = (before != pos ? 1 : 0) | (won ? 2 : 0) | 4;
       dn = (won || steps == p.max_steps) ? 1 : 0;
+      if (drec) {
+        // [player before | player after | box destination or 0xff | reward code (0: -0.1, 1: +1, 2: -1, then +10 when won: 3 with
+        // the +1, 4 without) | done << 3 | effective << 4 | success << 5 | executed << 6]
+        const int code = won ? (now_on_rose ? 3 : 4) : now_on_rose ? 1 : now_on_fell ? 2 : 0;
+        drec[k] = (uint32_t)before | ((uint32_t)pos << 8) | ((uint32_t)box_to << 16) |
+                  ((uint32_t)(code | (dn << 3) | ((before != pos) << 4) | ((int)won << 5) | (1 << 6)) << 24);
+      }
       if (dn) break;
     }
+    if (drec)
+      for (int k = nexec; k < p.K; ++k) drec[k] = 0u;  // not executed
     m.player = (int16_t)pos;
     m.steps = (uint16_t)steps;
     m.on_target = (int8_t)on;
     m.actual = (int8_t)actual;
     m.under = (uint8_t)under;
     p.meta[g] = m;
-    p.acc_reward[g] = acc;
-    p.done[g] = (uint8_t)dn;
-    p.flags[g] = (uint8_t)fl;
-    p.n_executed[g] = (uint8_t)nexec;
+    if (p.acc_reward) {
+      p.acc_reward[g] = acc;
+      p.done[g] = (uint8_t)dn;
+      p.flags[g] = (uint8_t)fl;
+      p.n_executed[g] = (uint8_t)nexec;
+    }
   }
   // rooms of the compile-time shapes are rendered by the thread that owns them (render_env_packed), straight after its
   // own step: no CTA-wide barrier between step and render, and the player-on-target patch touches only the owner's bytes
@@ -613,18 +629,20 @@ bool aligned8(const void* p) { return ((uintptr_t)p & 7) == 0; }
 namespace {
 int sokoban_step_entry(int pack, ragen_ctx* ctx, int64_t n, int H, int W, int num_boxes, int max_steps, const uint8_t* actions,
                        int K, const uint8_t* n_actions, uint8_t* state, int16_t* meta, double* acc_reward, uint8_t* done,
-                       uint8_t* flags, uint8_t* n_executed, uint8_t* obs, void* stream) {
+                       uint8_t* flags, uint8_t* n_executed, uint8_t* obs, void* stream, uint8_t* delta = nullptr) {
   RAGEN_REQUIRE(ctx, "ctx is NULL");
   RAGEN_SOKOBAN_SHAPE(n, H, W);
   RAGEN_REQUIRE(K >= 1 && K <= 255, "K=%d out of range", K);
   RAGEN_REQUIRE(num_boxes >= 0 && num_boxes <= 127, "num_boxes=%d out of range", num_boxes);
-  RAGEN_REQUIRE(actions && state && meta && acc_reward && done && flags && n_executed, "NULL pointer argument");
-  RAGEN_REQUIRE(aligned16(state) && (!obs || aligned16(obs)) && aligned8(meta) && aligned8(acc_reward),
-                "state/obs must be 16-byte aligned, meta/acc_reward 8-byte aligned");
+  RAGEN_REQUIRE(actions && state && meta, "NULL pointer argument");
+  RAGEN_REQUIRE(delta || (acc_reward && done && flags && n_executed), "NULL pointer argument");
+  RAGEN_REQUIRE(aligned16(state) && (!obs || aligned16(obs)) && aligned8(meta) && aligned8(acc_reward) && (((uintptr_t)delta & 3) == 0),
+                "state/obs must be 16-byte aligned, meta/acc_reward 8-byte aligned, delta 4-byte aligned");
+  RAGEN_REQUIRE(!delta || H * W <= 255, "delta records hold cell indices in one byte: H*W <= 255");
   if (n == 0) return RAGEN_OK;
   DeviceGuard guard(ctx->device);
   StepParams p{n, H, W, num_boxes, max_steps, K, actions, n_actions, state, reinterpret_cast<EnvMeta*>(meta),
-               acc_reward, done, flags, n_executed, obs};
+               acc_reward, done, flags, n_executed, obs, delta};
   return pack == 3   ? launch_tiles<false, 3>(ctx, p, (cudaStream_t)stream)
          : pack == 2 ? launch_tiles<false, 2>(ctx, p, (cudaStream_t)stream)
          : pack == 1 ? launch_tiles<false, 1>(ctx, p, (cudaStream_t)stream)
@@ -692,6 +710,14 @@ extern "C" int ragen_sokoban_step_compact(ragen_ctx* ctx, int64_t n, int H, int 
                                           uint8_t* n_executed, uint8_t* obs_packed3, void* stream) {
   return sokoban_step_entry(3, ctx, n, H, W, num_boxes, max_steps, actions, K, n_actions, state4, meta, acc_reward, done, flags,
                             n_executed, obs_packed3, stream);
+}
+
+extern "C" int ragen_sokoban_step_delta(ragen_ctx* ctx, int64_t n, int H, int W, int num_boxes, int max_steps,
+                                        const uint8_t* actions, int K, const uint8_t* n_actions, uint8_t* state4,
+                                        int16_t* meta, uint8_t* delta, void* stream) {
+  RAGEN_REQUIRE(delta, "delta is NULL");
+  return sokoban_step_entry(3, ctx, n, H, W, num_boxes, max_steps, actions, K, n_actions, state4, meta, nullptr, nullptr, nullptr,
+                            nullptr, nullptr, stream, delta);
 }
 
 extern "C" int ragen_sokoban_render_packed3(ragen_ctx* ctx, int64_t n, int H, int W, const uint8_t* state,

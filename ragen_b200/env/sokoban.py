@@ -131,6 +131,62 @@ def unpack_rooms(state4, out=None):
     return out
 
 
+REWARD_CODES = (-0.1, -0.1 + 1, -0.1 + -1, -0.1 + 1 + 10, -0.1 + 10)  # gym_sokoban _calc_reward's sums, in its addition order
+
+
+def decode_delta(delta):
+    """delta uint8 [n, K, 4] (ragen_sokoban_step_delta) -> (acc_reward f64 [n], done u8 [n], flags u8 [n], n_executed u8 [n]) as
+    the other step entry points report them: rewards summed left to right in doubles, done / flags of the last executed action."""
+    d = np.asarray(delta)
+    n, K = d.shape[0], d.shape[1]
+    info = d[:, :, 3]
+    executed = (info >> 6) & 1
+    table = np.array(REWARD_CODES + (0.0, 0.0, 0.0), dtype=np.float64)
+    acc = np.zeros(n, dtype=np.float64)
+    for k in range(K):
+        acc = np.where(executed[:, k] == 1, acc + table[info[:, k] & 7], acc)
+    nexec = executed.sum(axis=1).astype(np.uint8)
+    last = info[np.arange(n), np.maximum(nexec.astype(np.int64) - 1, 0)]
+    has = nexec > 0
+    done = np.where(has, (last >> 3) & 1, 0).astype(np.uint8)
+    flags = np.where(has, ((last >> 4) & 1) | (((last >> 5) & 1) << 1) | 4, 0).astype(np.uint8)
+    return acc, done, flags, nexec
+
+
+class HostMirror:
+    """The rooms of a batch mirrored in host memory and kept current from step deltas: 4 bytes per action cross the
+    device->host link instead of a re-rendered room.  `state` is room_state [n, H*W] (codes 0..5), `fixed` room_fixed."""
+
+    def __init__(self, fixed, state, H, W):
+        self.H, self.W = int(H), int(W)
+        self.fixed = np.ascontiguousarray(fixed, dtype=np.uint8).reshape(-1, H * W).copy()
+        self.state = np.ascontiguousarray(state, dtype=np.uint8).reshape(-1, H * W).copy()
+        self.n = self.state.shape[0]
+
+    def apply(self, delta):
+        d = np.asarray(delta)
+        for k in range(d.shape[1]):
+            rec = d[:, k]
+            rows = np.flatnonzero((rec[:, 3] >> 4) & 1)  # the player moved (a push moves it too)
+            if rows.size == 0:
+                continue
+            before, after, box = rec[rows, 0].astype(np.int64), rec[rows, 1].astype(np.int64), rec[rows, 2].astype(np.int64)
+            self.state[rows, before] = self.fixed[rows, before]
+            self.state[rows, after] = 5
+            pushed = box != 0xff
+            pr, pc = rows[pushed], box[pushed]
+            self.state[pr, pc] = np.where(self.fixed[pr, pc] == 2, 3, 4)
+
+    def glyphs(self, rows=None):
+        """[m, H*(W+1)] glyph codes with separators: what the render entry points write."""
+        s = self.state if rows is None else self.state[rows]
+        f = self.fixed if rows is None else self.fixed[rows]
+        g = np.where((s == 5) & (f == 2), 6, s).reshape(-1, self.H, self.W)
+        out = np.full((g.shape[0], self.H, self.W + 1), 7, dtype=np.uint8)
+        out[:, :, : self.W] = g
+        return out.reshape(g.shape[0], -1)
+
+
 def codes_to_text(codes_row, table):
     """codes_row: 1-D uint8 numpy array of length H*(W+1); the trailing separator is dropped."""
     return "".join(table[c] for c in codes_row[:-1].tolist())
@@ -366,6 +422,75 @@ class SokobanBatch:
                       _lib.ptr(self.flags), _lib.ptr(self.n_executed), _lib.ptr(obs), self.ctx.stream()))
         return StepOut(self.reward, self.done, self.flags, self.n_executed, obs if render else self.obs)
 
+    def step_delta(self, actions, n_actions=None):
+        """The compact step reporting DELTAS (ragen_sokoban_step_delta): returns the device tensor uint8 [n, K, 4]; nothing is
+        rendered and the result arrays are not written (decode_delta / HostMirror turn deltas into them on the host)."""
+        if not self.compact:
+            raise ValueError("step_delta steps nibble rooms: construct the batch with compact=True")
+        if actions.dim() == 1:
+            actions = actions.unsqueeze(1)
+        assert actions.dtype == torch.uint8 and actions.is_cuda and actions.is_contiguous() and actions.shape[0] == self.n
+        K = actions.shape[1]
+        buf = getattr(self, "_delta", None)
+        if buf is None or buf.shape[1] != K:
+            buf = self._delta = torch.zeros((self.n, K, 4), dtype=torch.uint8, device=self.device)
+        _lib.check(self.lib.ragen_sokoban_step_delta(
+            self.ctx.handle, self.n, self.H, self.W, self.num_boxes, self.max_steps, _lib.ptr(actions), K, _lib.ptr(n_actions),
+            _lib.ptr(self.state4), _lib.ptr(self.meta), _lib.ptr(buf), self.ctx.stream()))
+        self._state_stale = True
+        self.obs_stale = True
+        return buf
+
+    def host_mirror(self):
+        """A HostMirror of the batch's current rooms (one device->host copy of state and fixed)."""
+        return HostMirror(self.fixed.cpu().numpy(), self.state.cpu().numpy(), self.H, self.W)
+
+    # -- pipelined host-buffer stepping: launch step i+1 while the results of step i drain ------------------------------------
+    def step_host_begin(self, h_actions, fmt="delta"):
+        """h_actions: PINNED uint8 host tensor [n] or [n, K].  Queues host->device copy + step on the compute stream and the
+        device->host copy of the results on a copy stream; returns a ticket for step_host_end.  fmt: "delta" (4 B per action)
+        or 3 (three-bit rows + scalars, 49 B per 10x10 env).  Up to two tickets may be open per batch."""
+        assert isinstance(h_actions, torch.Tensor) and h_actions.is_pinned() and h_actions.dtype == torch.uint8
+        h_act = h_actions if h_actions.dim() == 2 else h_actions.unsqueeze(1)
+        pipe = getattr(self, "_pipe", None)
+        if pipe is None:
+            pipe = self._pipe = {"copy": torch.cuda.Stream(self.device), "slot": 0, "d_act": [None, None]}
+        j = pipe["slot"]
+        pipe["slot"] = j ^ 1
+        main = torch.cuda.current_stream(self.device)
+        if pipe.get("last_done") is not None:
+            main.wait_event(pipe["last_done"])  # the step below overwrites the result buffer the previous copy reads
+        if pipe["d_act"][j] is None or pipe["d_act"][j].shape != h_act.shape:
+            pipe["d_act"][j] = torch.empty(h_act.shape, dtype=torch.uint8, device=self.device)
+        d_act = pipe["d_act"][j]
+        d_act.copy_(h_act, non_blocking=True)
+        if fmt == "delta":
+            src = self.step_delta(d_act).view(-1)
+        else:
+            self.step(d_act, packed=3)
+            src = self._slab[: self._off_sc + 11 * self.n]
+        h = self._pin(("pipe", fmt, j), (src.numel(),), torch.uint8)
+        ready = torch.cuda.Event()
+        ready.record(main)
+        with torch.cuda.stream(pipe["copy"]):
+            pipe["copy"].wait_event(ready)
+            h.copy_(src, non_blocking=True)
+            done = torch.cuda.Event()
+            done.record(pipe["copy"])
+        pipe["last_done"] = done
+        return (fmt, h, done, h_act.shape[1])
+
+    def step_host_end(self, ticket):
+        """Waits for the ticket's results.  "delta": numpy uint8 [n, K, 4]; 3: (rows, reward, done, flags, n_executed)."""
+        fmt, h, done, K = ticket
+        done.synchronize()
+        hn = h.numpy()
+        if fmt == "delta":
+            return hn.reshape(self.n, K, 4)
+        n_, o = self.n, self._off_sc
+        return (hn[: n_ * self._b3].reshape(n_, -1), hn[o: o + 8 * n_].view(np.float64), hn[o + 8 * n_: o + 9 * n_],
+                hn[o + 9 * n_: o + 10 * n_], hn[o + 10 * n_: o + 11 * n_])
+
     def _pin(self, name, shape, dtype):
         key = (name, tuple(shape), dtype)
         if key not in self._pinned:
@@ -463,9 +588,10 @@ class SokobanBatch:
         if getattr(self, "obs_stale", False):
             self.render(packed=self.obs_is_packed)
         if self.obs_is_packed == 3:
-            tab = glyph_table(grid_lookup)
+            tr = {i: g for i, g in enumerate(glyph_table(grid_lookup))}
             rows3 = (self.obs_packed3 if rows is None else self.obs_packed3[rows]).cpu().numpy()
-            return [codes_to_text(r, tab) for r in unpack3_glyphs(rows3, self.H, self.W)]
+            codes = unpack3_glyphs(rows3, self.H, self.W)  # vectorised; then one C-level translate per env
+            return [bytes(r[:-1]).decode("latin1").translate(tr) for r in codes]
         if self.obs_is_packed:
             pairs = glyph_pair_table(grid_lookup)
             codes = (self.obs_packed if rows is None else self.obs_packed[rows]).cpu().numpy()

@@ -463,6 +463,76 @@ def test_slot_reset_leaves_the_other_envs_in_mid_episode(compact):
         assert np.array_equal(b.state.cpu().numpy()[keep], o.state[keep])
 
 
+@pytest.mark.parametrize("H,W,nb,n,K", [(10, 10, 2, 4099, 1), (6, 6, 1, 1000, 3), (8, 8, 2, 515, 2), (10, 10, 3, 129, 5)])
+def test_step_deltas_rebuild_rooms_rewards_and_rows_on_the_host(H, W, nb, n, K):
+    """ragen_sokoban_step_delta: 4 bytes per action instead of reward + flags + a re-rendered room.  Over 50 random turns (wins,
+    truncations, envs that keep being stepped after done, n_actions < K, partial resets in between) the host mirror patched from
+    the deltas equals the full three-bit rows of a twin batch, decode_delta equals the result arrays, and both equal the oracle."""
+    from ragen_b200.env.sokoban import HostMirror, SokobanBatch, decode_delta, unpack3_glyphs
+
+    fixed, state = synthetic_rooms(n, H, W, nb, seed=n + 7)
+    rng = np.random.default_rng(n + 8)
+    max_steps = 30
+    o = SokobanBatchOracle(fixed, state, H, W, nb, max_steps)
+    b = SokobanBatch(n, (H, W), nb, max_steps, search_depth=20, compact=True)
+    twin = SokobanBatch(n, (H, W), nb, max_steps, search_depth=20, compact=True)
+    b.load_rooms(fixed, state)
+    twin.load_rooms(fixed, state)
+    mirror = b.host_mirror()
+    assert np.array_equal(mirror.glyphs(), o.glyphs())
+    for turn in range(50):
+        acts = rng.integers(0, 5, (n, K)).astype(np.uint8)
+        na = rng.integers(0, K + 1, n).astype(np.uint8) if turn % 4 == 3 else None
+        d_act = torch.from_numpy(acts).cuda()
+        d_na = None if na is None else torch.from_numpy(na).cuda()
+        delta = b.step_delta(d_act, d_na).cpu().numpy()
+        full = twin.step(d_act, d_na, packed=3)
+        acc, done, flags, nexec = o.step_turn(acts, na)
+        mirror.apply(delta)
+        got = decode_delta(delta)
+        for g, w, f in zip(got, (acc, done, flags, nexec), (full.reward, full.done, full.flags, full.n_executed)):
+            assert np.array_equal(g, w) and np.array_equal(g, f.cpu().numpy()), turn
+        assert np.array_equal(mirror.state, o.state) and np.array_equal(b.state.cpu().numpy(), o.state)
+        assert np.array_equal(mirror.glyphs(), unpack3_glyphs(full.obs.cpu().numpy(), H, W)), turn
+        if turn == 20 and H == 6:  # a partial reset: the mirror is refreshed for the slots that were reset
+            slots = [1, n // 2]
+            b.reset([5, 6], slots=slots)
+            twin.reset([5, 6], slots=slots)
+            st, fx = b.state.cpu().numpy(), b.fixed.cpu().numpy()
+            mirror.state[slots], mirror.fixed[slots] = st[slots], fx[slots]
+            o = SokobanBatchOracle(fx, st, H, W, nb, max_steps)
+            o.env_steps = b.env_steps.cpu().numpy().astype(np.int64)
+            o.on_target = b.on_target.cpu().numpy().astype(np.int64)
+
+
+def test_pipelined_host_steps_equal_the_plain_ones():
+    """step_host_begin / step_host_end (two tickets in flight, copy stream) against step_host on a twin batch, both formats."""
+    from ragen_b200.env.sokoban import SokobanBatch, decode_delta
+
+    n, H, W, nb = 5000, 10, 10, 2
+    fixed, state = synthetic_rooms(n, H, W, nb, seed=3)
+    rng = np.random.default_rng(4)
+    for fmt in ("delta", 3):
+        a = SokobanBatch(n, (H, W), nb, 100, compact=True)
+        t = SokobanBatch(n, (H, W), nb, 100, compact=True)
+        a.load_rooms(fixed, state)
+        t.load_rooms(fixed, state)
+        acts = [torch.from_numpy(rng.integers(1, 5, n).astype(np.uint8)).pin_memory() for _ in range(6)]
+        tickets = [a.step_host_begin(acts[0], fmt)]
+        for i in range(6):
+            if i + 1 < 6:
+                tickets.append(a.step_host_begin(acts[i + 1], fmt))  # step i+1 is queued before step i's results are read
+            res = a.step_host_end(tickets[i])
+            rows, rew, done, flags, nex = t.step_host(acts[i], packed=3)
+            if fmt == "delta":
+                acc, d, f, k = decode_delta(res)
+                assert np.array_equal(acc, rew) and np.array_equal(d, done) and np.array_equal(f, flags) and np.array_equal(k, nex)
+            else:
+                for g, w in zip(res, (rows, rew, done, flags, nex)):
+                    assert np.array_equal(g, w), i
+        assert torch.equal(a.state, t.state)
+
+
 def test_compact_rooms_refuse_other_shapes():
     from ragen_b200 import _lib
     from ragen_b200.env.sokoban import SokobanBatch

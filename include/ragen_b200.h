@@ -283,6 +283,15 @@ int ragen_glyph_tokens(ragen_ctx* ctx, int64_t n, int G, int packed, const uint8
 int ragen_group_norm(ragen_ctx* ctx, int B, const float* score_last, const float* penalty, const int32_t* group,
                      int n_groups, int method, float* out, void* stream);
 
+/* The same in two halves, for rows sharded over ranks when a group spans ranks (grouping "inductive" = per tag, "batch" = all
+ * rows; ctx_manager.py:186-189): ragen_group_norm_stats writes x = score_last + penalty and this rank's per-group {count, sum,
+ * sum of squares} (double [n_groups][3], zeroed by the call; B = 0 is allowed), the caller all-reduces gstats (and the row count:
+ * the reference normalises only when there are fewer groups than rows, :219), ragen_group_norm_apply normalises x in place. */
+int ragen_group_norm_stats(ragen_ctx* ctx, int B, const float* score_last, const float* penalty, const int32_t* group,
+                           int n_groups, float* x, double* gstats, void* stream);
+int ragen_group_norm_apply(ragen_ctx* ctx, int B, float* x, const int32_t* group, int n_groups, const double* gstats,
+                           int method, void* stream);
+
 /* ragen_group_norm without any allocation.  NO COUNTERPART IN THE REFERENCE: added
  * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
  * that forbid it).  Same arguments, same results as ragen_group_norm; the per-group statistics live in a file-scope

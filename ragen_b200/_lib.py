@@ -47,6 +47,8 @@ SIGNATURES = {
     "ragen_traj_assemble": [_P, _I, _I, _P, _L, _P, _P, _P, _P, _P, _L, _P, _P, _P, _P],
     "ragen_glyph_tokens": [_P, _L, _I, _I, _P, _L, _P, _P, _I, _P, _P, _P],
     "ragen_group_norm": [_P, _I, _P, _P, _P, _I, _I, _P, _P],
+    "ragen_group_norm_stats": [_P, _I, _P, _P, _P, _I, _P, _P, _P],
+    "ragen_group_norm_apply": [_P, _I, _P, _P, _I, _P, _I, _P],
     "ragen_group_norm_noalloc": [_P, _I, _P, _P, _P, _I, _I, _P, _P],
     "ragen_gae": [_P, _I, _I, _P, _P, _P, _D, _D, _P, _P, _P, _P],
     "ragen_bilevel_gae": [_P, _I, _I, _P, _P, _P, _D, _D, _D, _P, _P, _P, _P],

@@ -198,6 +198,36 @@ extern "C" int ragen_group_norm(ragen_ctx* ctx, int B, const float* score_last, 
   return RAGEN_OK;
 }
 
+// The two halves of ragen_group_norm for rows that are sharded over ranks with groups that span ranks (grouping = tag or
+// whole batch, ctx_manager.py:186-189): the caller all-reduces gstats between them.
+extern "C" int ragen_group_norm_stats(ragen_ctx* ctx, int B, const float* score_last, const float* penalty, const int32_t* group,
+                                      int n_groups, float* x, double* gstats, void* stream) {
+  RAGEN_REQUIRE(ctx, "ctx is NULL");
+  RAGEN_REQUIRE(B >= 0 && n_groups >= 1, "bad argument B=%d n_groups=%d", B, n_groups);
+  RAGEN_REQUIRE(gstats && (B == 0 || (score_last && group && x)), "NULL pointer argument");
+  DeviceGuard guard(ctx->device);
+  cudaStream_t st = (cudaStream_t)stream;
+  RAGEN_CUDA(cudaMemsetAsync(gstats, 0, (size_t)n_groups * 3 * sizeof(double), st));
+  if (B == 0) return RAGEN_OK;  // a rank without rows still contributes zeros to the all-reduce
+  const int threads = 128, blocks = (B + threads - 1) / threads;
+  norm_stats_kernel<<<blocks, threads, 0, st>>>(B, score_last, penalty, group, n_groups, x, gstats);
+  RAGEN_LAUNCHED(ctx);
+  return RAGEN_OK;
+}
+
+extern "C" int ragen_group_norm_apply(ragen_ctx* ctx, int B, float* x, const int32_t* group, int n_groups, const double* gstats,
+                                      int method, void* stream) {
+  RAGEN_REQUIRE(ctx, "ctx is NULL");
+  RAGEN_REQUIRE(B >= 0 && n_groups >= 1 && method >= 0 && method <= 3, "bad argument B=%d n_groups=%d method=%d", B, n_groups, method);
+  if (B == 0 || method == 0) return RAGEN_OK;
+  RAGEN_REQUIRE(x && group && gstats, "NULL pointer argument");
+  DeviceGuard guard(ctx->device);
+  const int threads = 128, blocks = (B + threads - 1) / threads;
+  norm_apply_kernel<<<blocks, threads, 0, (cudaStream_t)stream>>>(B, x, group, n_groups, gstats, method);
+  RAGEN_LAUNCHED(ctx);
+  return RAGEN_OK;
+}
+
 // ---- ragen_group_norm_noalloc -------------------------------------------------------------------------------------
 // The same pass for callers that cannot tolerate an allocation (CUDA graph capture, serving loops, harnesses that
 // forbid cudaMalloc): the per-group statistics live in a file-scope device array instead of the ctx-owned scratch.

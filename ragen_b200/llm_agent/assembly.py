@@ -193,6 +193,9 @@ class TrajectoryAssembler:
         self._tables: Dict[tuple, tuple] = {}    # glyph table -> (int32 [8, 4] tokens, int32 [8] lengths), cell mode
         self._rows: Dict[tuple, dict] = {}       # glyph table -> {row bytes: (start, len)}, row mode
         self._rendered: Dict[tuple, tuple] = {}  # (id(log), epoch, slot, pool generation) -> per-env segment arrays
+        self._entry_cache: Dict[int, tuple] = {}  # id(history entry) -> (entry, turn index, pool generation, resolved segments)
+        self._heads: Dict[int, tuple] = {}       # env_id -> the two chunks every prompt of the env starts with
+        self._tails: Dict[tuple, str] = {}       # (env_id, actions_left) -> "You have N actions left ..." text
         self._staging = None
         # the specials the tokenizer adds around a whole input are not part of any chunk: an empty text shows them
         try:
@@ -421,6 +424,70 @@ class TrajectoryAssembler:
         return starts, lens
 
     # ---- assembly -------------------------------------------------------------------------------------------------
+    def new_rollout(self):
+        """Finished-turn segments are cached per history entry; a new rollout starts with new entries."""
+        self._entry_cache.clear()
+
+    def _tail_text(self, env_id, actions_left):
+        key = (env_id, actions_left)
+        t = self._tails.get(key)
+        if t is None:
+            think = self.cm.config.agent_proxy.enable_think
+            fmt = "<think> [Your thoughts] </think> <answer> [your answer] </answer>" if think else "<answer> [your answer] </answer>"
+            length = f"Max response length: {self.cm.env_config_lookup[env_id]['max_tokens']} words (tokens)."
+            t = self._tails[key] = (f"You have {actions_left} actions left. Always output: {fmt} with no extra text. "
+                                    f"Strictly follow this format. {length}\n")
+        return t
+
+    def row_elements(self, env_output, prepare_for_update, fills):
+        """items() for the common shape of a grid-env trajectory - every entry carries a device observation, every entry but the
+        last is a finished turn (response + reward), the last one is the open state (generation) or a finished turn whose
+        reward message is left out (update) - with the per-turn work done ONCE: a finished turn's four chunks [observation |
+        "You have N ..." | assistant message | reward message + next turn header] never change, so their resolved segments
+        are kept per history entry and a call only builds the chunks of the newest entries.  Any other shape takes items()."""
+        hist = env_output["history"]
+        n = len(hist)
+        if n == 0:
+            return self.items(env_output, prepare_for_update)
+        is_obs = self._is_device_obs
+        for idx, c in enumerate(hist):
+            st = c.get("state")
+            if type(st) is not ObsText or not is_obs(st):
+                return self.items(env_output, prepare_for_update)
+            if idx < n - 1 and not ("llm_response" in c and "reward" in c):
+                return self.items(env_output, prepare_for_update)
+        last = hist[-1]
+        if prepare_for_update != ("llm_response" in last) or (not prepare_for_update and "reward" in last):
+            return self.items(env_output, prepare_for_update)
+        glue, env_id = self.glue, env_output["env_id"]
+        head = self._heads.get(env_id)
+        if head is None:
+            head = self._heads[env_id] = (glue.start + "You're a helpful assistant. ",
+                                          glue.between[("system", "user")] + self.cm.prefix_lookup[env_id] + "\nTurn 1:\nState:\n")
+        out = [head[0], head[1]]
+        cache, gen = self._entry_cache, self.pool.generation if self._pool is not None else 0
+        g_ua, g_au = self._glue("user", "assistant"), self._glue("assistant", "user")
+        for idx in range(n - 1):
+            c = hist[idx]
+            hit = cache.get(id(c))
+            if hit is not None and hit[0] is c and hit[1] == idx and hit[2] == gen:
+                out.append(hit[3])
+                continue
+            a = len(out)
+            out.append(c["state"])
+            out.append(self._tail_text(env_id, c["actions_left"]))
+            out.append(g_ua + c["llm_response"])
+            out.append(g_au + f"Reward:\n{c['reward']}\n\nTurn {idx + 2}:\nState:\n")
+            fills.append((c, idx, out, a, a + 4))
+        out.append(last["state"])
+        tail = self._tail_text(env_id, last["actions_left"])
+        if prepare_for_update:
+            out.append(tail)
+            out.append(g_ua + last["llm_response"] + glue.end["assistant"])
+        else:
+            out.append(tail + glue.end_generation + ("<think>" if self.cm.config.agent_proxy.enable_think else "<answer>"))
+        return out
+
     def assemble(self, env_outputs, prepare_for_update):
         """-> (input_ids, attention_mask, position_ids) int64 [B, L] CUDA tensors, bit-identical to the reference's
         tokenizer(texts, padding=True, padding_side='left') + attention_mask.cumsum(-1)."""
@@ -428,7 +495,9 @@ class TrajectoryAssembler:
         if pool.full():
             pool.reset()
             self._rendered.clear()
-        rows = [self.items(eo, prepare_for_update) for eo in env_outputs]
+            self._entry_cache.clear()
+        fills = []
+        rows = [self.row_elements(eo, prepare_for_update, fills) for eo in env_outputs]
         memo = pool.memo
         new = {}
         for items in rows:
@@ -440,17 +509,40 @@ class TrajectoryAssembler:
             for t, seg in zip(texts, pool.put(encode_many(self.tokenizer, texts))):
                 memo[t] = seg
         src, ln, off = [], [], [0]
+        obs_lists = {}
         for items in rows:
-            for it in items:
-                if type(it) is str:
-                    s, n = memo[it]
-                    src.append(s)
-                    ln.append(n)
+            for j, it in enumerate(items):
+                tp = type(it)
+                if tp is tuple:  # segments resolved by an earlier call (entry cache): (starts, lens)
+                    src.extend(it[0])
+                    ln.extend(it[1])
+                elif tp is str:
+                    s_, n_ = memo[it]
+                    src.append(s_)
+                    ln.append(n_)
                 else:
-                    starts, lens = self._obs_segments(it.log, it.slot)
-                    src.extend(starts[it.index].tolist())
-                    ln.extend(lens[it.index].tolist())
+                    key = (id(it.log), it.slot)
+                    pair = obs_lists.get(key)
+                    if pair is None:
+                        starts, lens = self._obs_segments(it.log, it.slot)
+                        pair = obs_lists[key] = (starts.tolist(), lens.tolist())
+                    src.extend(pair[0][it.index])
+                    ln.extend(pair[1][it.index])
             off.append(len(src))
+        for entry, idx, items, a, b in fills:  # a finished turn never changes again: keep its resolved segments
+            ss, ll = [], []
+            for it in items[a:b]:
+                if type(it) is str:
+                    s_, n_ = memo[it]
+                    ss.append(s_)
+                    ll.append(n_)
+                else:
+                    pair = obs_lists[(id(it.log), it.slot)]
+                    ss.extend(pair[0][it.index])
+                    ll.extend(pair[1][it.index])
+            self._entry_cache[id(entry)] = (entry, idx, pool.generation, (tuple(ss), tuple(ll)))
+        if len(self._entry_cache) > 200000:
+            self._entry_cache.clear()
         B, E = len(rows), len(src)
         src = np.asarray(src, dtype=np.int64)
         ln = np.asarray(ln, dtype=np.int32)

@@ -195,6 +195,8 @@ class ContextManager:
             env_table[e["env_id"]] = ids[key]
         self._tables = ops.ActionTables(uniq, self.device) if uniq else None
         self._env_table = env_table
+        if self._assembler is not None:
+            self._assembler.new_rollout()
 
     def _parse_batch(self, responses: List[str], env_ids=None):
         tid = None
@@ -203,7 +205,9 @@ class ContextManager:
         res = ops.parse_actions(responses, self._tables if tid is not None else None, tid,
                                 bool(self.config.agent_proxy.enable_think), self.action_sep,
                                 int(self.config.agent_proxy.max_actions_per_turn), device=self.device)
-        return res, res.to_host(), res.flags.cpu().numpy()
+        host = res.to_host()
+        flags = getattr(res, "flags_host", None)
+        return res, host, flags if flags is not None else res.flags.cpu().numpy()
 
     def _parse_response(self, response: str) -> List:
         _, host, _ = self._parse_batch([response])
@@ -242,9 +246,16 @@ class ContextManager:
             raise ValueError(f"Invalid grouping: {grouping}")
         if method not in ("mean_std", "mean", "asym_clip", "identity"):
             raise ValueError(f"Invalid normalization method: {method}")
-        if self.exchange is not None and grouping != "state" and method != "identity":
-            raise NotImplementedError("sharded rollouts normalise within env groups (grouping='state'): whole groups live on "
-                                      "one rank; tag- or batch-wide statistics would need their own exchange")
+        keys = self._cross_rank_norm_keys()
+        if keys is not None:
+            # sharded rows and groups that span ranks (per tag / whole batch): this rank's partial {count, sum, sum of squares}
+            # per group ride in the rollout's one all-reduce (_mean_metrics), the normalisation is applied after it
+            dev = self.device
+            gi = torch.tensor([keys.index(t) for t in group_tags], dtype=torch.int32, device=dev)
+            penalty = torch.tensor([env_output.get("penalty", 0) for env_output in env_outputs], dtype=torch.float32, device=dev)
+            x, gstats = ops.group_norm_stats(score_tensor[:, -1].to(dev), penalty, gi, len(keys))
+            self._pending_norm = (x, gi, gstats, method, score_tensor)
+            return score_tensor
         dense = {}
         gi = [dense.setdefault(t, len(dense)) for t in group_tags]
         dev = self.device
@@ -252,6 +263,14 @@ class ContextManager:
         out = ops.group_norm(score_tensor[:, -1].to(dev), penalty, torch.tensor(gi, dtype=torch.int32, device=dev), len(dense), method)
         score_tensor[:, -1] = out.to(score_tensor.device)  # in place, as the reference (rm_scores aliases original_rm_scores)
         return score_tensor
+
+    def _cross_rank_norm_keys(self):
+        """The group keys of a normalisation whose groups span ranks (sharded rollout, grouping by tag or whole batch, a method
+        other than identity), in an order every rank derives from the config alone; None when the normalisation is rank-local."""
+        rn_cfg = self.config.agent_proxy.reward_normalization
+        if self.exchange is None or rn_cfg.grouping == "state" or rn_cfg.method == "identity" or self.config.agent_proxy.use_turn_scores:
+            return None
+        return list(dict.fromkeys(self.es_cfg.env_configs.tags)) if rn_cfg.grouping == "inductive" else [1]
 
     # ---- LM inputs (ctx_manager.py:228-330) ---------------------------------------------------------------------------
     def _trim_history(self, env_output: Dict, prepare_for_update: bool):
@@ -345,14 +364,22 @@ class ContextManager:
             per_row = response_mask.sum(dim=-1).cpu()  # B integers; the mean is taken where the reference takes it (CPU fp32, :288)
             response_length = per_row.float().mean().item()
             self._response_tokens = (float(per_row.sum()), int(response_mask.shape[0]))
+            metrics = self._mean_metrics(env_outputs, response_length)  # sharded: the rollout's one all-reduce happens here
 
-        if self.assembly == "device":  # the reference hands CPU tensors to the trainer: one copy per tensor at the boundary
-            out_dev = self.output_device
-            input_ids, attention_mask, position_ids = (t.to(out_dev) for t in (input_ids, attention_mask, position_ids))
+        if self.assembly == "device" and self.output_device.type == "cpu":
+            # the reference hands CPU tensors to the trainer: asynchronous copies into pinned memory, one synchronisation
+            aliased = prepare_for_update and normalized_score_tensor is score_tensor
+            dev_t = [input_ids, attention_mask, position_ids] + ([loss_mask, score_tensor] if prepare_for_update else [])
+            if prepare_for_update and not aliased:
+                dev_t.append(normalized_score_tensor)
+            host_t = [torch.empty(t.shape, dtype=t.dtype, pin_memory=True) for t in dev_t]
+            for h, t in zip(host_t, dev_t):
+                h.copy_(t, non_blocking=True)
+            torch.cuda.current_stream(self.device).synchronize()
+            input_ids, attention_mask, position_ids = host_t[:3]
             if prepare_for_update:
-                aliased = normalized_score_tensor is score_tensor
-                loss_mask, score_tensor = loss_mask.to(out_dev), score_tensor.to(out_dev)
-                normalized_score_tensor = score_tensor if aliased else normalized_score_tensor.to(out_dev)
+                loss_mask, score_tensor = host_t[3], host_t[4]
+                normalized_score_tensor = score_tensor if aliased else host_t[5]
         llm_inputs = DataProto()
         llm_inputs.batch = TensorDict({"input_ids": input_ids, "attention_mask": attention_mask, "position_ids": position_ids,
                                        "responses": input_ids[:, 1:]}, batch_size=input_ids.shape[0])
@@ -373,15 +400,31 @@ class ContextManager:
             non_tensor["messages_list"] = np.array(messages_list, dtype=object)
         llm_inputs.non_tensor_batch = non_tensor
         if prepare_for_update:
-            llm_inputs.meta_info = {"metrics": self._mean_metrics(env_outputs, response_length)}
+            llm_inputs.meta_info = {"metrics": metrics}
         return llm_inputs
 
     def _mean_metrics(self, env_outputs: List[Dict], response_length: float) -> Dict:
         """Per-tag means over ALL envs of the tag plus the non-zero means (:309-328)."""
         if self.exchange is not None:  # one all-reduce of the fixed-layout vector, then the same arithmetic on global sums
             ex = self.exchange
-            vec = ex.pack(env_outputs, *self._response_tokens, device=self.device if torch.distributed.get_backend(ex.group) == "nccl" else None)
-            return ex.unpack(ex.all_reduce(vec))[0]
+            on_dev = self.device if torch.distributed.get_backend(ex.group) == "nccl" else None
+            vec = ex.pack(env_outputs, *self._response_tokens, device=on_dev)
+            keys = self._cross_rank_norm_keys()
+            pending, self._pending_norm = getattr(self, "_pending_norm", None), None
+            if keys is not None:  # tail: per-key {count, sum, sum of squares} of this rank's rows, then its row count
+                tail = torch.zeros(3 * len(keys) + 1, dtype=torch.float64, device=vec.device)
+                if pending is not None:
+                    tail[:-1] = pending[2].flatten().to(vec.device)
+                    tail[-1] = float(pending[0].numel())
+                vec = torch.cat([vec, tail])
+            vec = ex.all_reduce(vec)
+            if keys is not None and pending is not None:
+                x, gi, _, method, score_tensor = pending
+                gstats, rows = vec[ex.size:-1].reshape(len(keys), 3), float(vec[-1])
+                if len(keys) < rows:  # "if len(group2index) < acc_scores.shape[0]" (:219), on the whole batch
+                    ops.group_norm_apply(x, gi, len(keys), gstats, method)
+                score_tensor[:, -1] = x.to(score_tensor.device)
+            return ex.unpack(vec[: ex.size])[0]
         metrics = {}
         for env_output in env_outputs:
             for key, value in env_output["metrics"].items():

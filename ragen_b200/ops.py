@@ -206,6 +206,30 @@ def group_norm(score_last, penalty, group_index, n_groups, method):
     return out
 
 
+def group_norm_stats(score_last, penalty, group_index, n_groups, device=None):
+    """First half of group_norm for sharded rows: (x = score + penalty f32 [B], per-group {count, sum, sum of squares} f64 [n_groups, 3])."""
+    dev = score_last.device if score_last.is_cuda else torch.device("cuda", torch.cuda.current_device() if device is None else int(device))
+    ctx = _lib.Context.get(dev.index)
+    s = _f32(score_last.to(dev))
+    p = _f32(penalty.to(dev)) if penalty is not None else None
+    g = group_index.to(dev, torch.int32).contiguous()
+    x = torch.empty_like(s)
+    gstats = torch.empty((int(n_groups), 3), dtype=torch.float64, device=dev)
+    _lib.check(ctx.lib.ragen_group_norm_stats(ctx.handle, s.numel(), _lib.ptr(s), _lib.ptr(p), _lib.ptr(g), int(n_groups), _lib.ptr(x),
+                                              _lib.ptr(gstats), ctx.stream()))
+    return x, gstats
+
+
+def group_norm_apply(x, group_index, n_groups, gstats, method):
+    """Second half: normalises x in place from (all-reduced) per-group statistics."""
+    ctx = _ctx(x)
+    g = group_index.to(x.device, torch.int32).contiguous()
+    gs = gstats.to(x.device, torch.float64).contiguous()
+    _lib.check(ctx.lib.ragen_group_norm_apply(ctx.handle, x.numel(), _lib.ptr(x), _lib.ptr(g), int(n_groups), _lib.ptr(gs), _METHODS[method],
+                                              ctx.stream()))
+    return x
+
+
 # ---- response parsing ------------------------------------------------------------------------------------------
 class ActionTables:
     """Lookup tables of `config.action_lookup` dicts ({action_id: name}) laid out for ragen_parse_actions."""
@@ -239,12 +263,22 @@ class ParseResult:
         """[(llm_response, actions, codes)] per response (ctx_manager.py:148-173, es_manager.py:230-240)."""
         from .llm_agent.parse_host import assemble_response
 
-        fl = self.flags.cpu().numpy()
-        sp = self.spans.cpu().numpy()
-        asp = self.act_spans.cpu().numpy()
-        kept = self.n_parsed.cpu().numpy()
-        codes = self.codes.cpu().numpy()
-        nv = self.n_valid.cpu().numpy()
+        if getattr(self, "slab", None) is not None:  # one device->host copy for all per-response results
+            n, A = self.layout
+            h = self.slab.cpu().numpy()
+            words = 4 * n + 2 * A * n + n
+            i32, b0 = h[: 4 * words].view(np.int32), 4 * words
+            sp, asp = i32[: 4 * n].reshape(n, 4), i32[4 * n: 4 * n + 2 * A * n].reshape(n, A, 2)
+            fl, kept = h[b0: b0 + n], h[b0 + n: b0 + 2 * n]
+            codes, nv = h[b0 + 2 * n: b0 + (2 + A) * n].reshape(n, A), h[b0 + (2 + A) * n:]
+            self.flags_host = fl
+        else:
+            fl = self.flags.cpu().numpy()
+            sp = self.spans.cpu().numpy()
+            asp = self.act_spans.cpu().numpy()
+            kept = self.n_parsed.cpu().numpy()
+            codes = self.codes.cpu().numpy()
+            nv = self.n_valid.cpu().numpy()
         need_scratch = bool((fl & 6).any())
         scr = self.scratch.cpu().numpy().tobytes() if need_scratch else b""
         out = []
@@ -271,11 +305,18 @@ def parse_actions_device(text, offsets, tables=None, table_id=None, enable_think
     result as `out` to write into the same buffers again."""
     ctx = _ctx(text)
     dev, n = text.device, offsets.numel() - 1
-    out = out or {"scratch": torch.empty_like(text), "flags": torch.empty(n, dtype=torch.uint8, device=dev),
-           "spans": torch.empty((n, 4), dtype=torch.int32, device=dev),
-           "act_spans": torch.empty((n, max_actions, 2), dtype=torch.int32, device=dev),
-           "n_parsed": torch.empty(n, dtype=torch.uint8, device=dev), "n_total": torch.empty(n, dtype=torch.int32, device=dev),
-           "codes": torch.empty((n, max_actions), dtype=torch.uint8, device=dev), "n_valid": torch.empty(n, dtype=torch.uint8, device=dev)}
+    if out is None:
+        # every per-response result lives in ONE slab [spans i32 4n | act_spans i32 2An | n_total i32 n | flags n | n_parsed n |
+        # codes An | n_valid n], so the host gets a turn's parse with a single device->host copy (ParseResult.to_host)
+        A = int(max_actions)
+        words = 4 * n + 2 * A * n + n
+        slab = torch.empty(4 * words + (3 + A) * n, dtype=torch.uint8, device=dev)
+        i32 = slab[: 4 * words].view(torch.int32)
+        b0 = 4 * words
+        out = {"scratch": torch.empty_like(text), "slab": slab, "layout": (n, A),
+               "spans": i32[: 4 * n].view(n, 4), "act_spans": i32[4 * n: 4 * n + 2 * A * n].view(n, A, 2),
+               "n_total": i32[4 * n + 2 * A * n:], "flags": slab[b0: b0 + n], "n_parsed": slab[b0 + n: b0 + 2 * n],
+               "codes": slab[b0 + 2 * n: b0 + (2 + A) * n].view(n, A), "n_valid": slab[b0 + (2 + A) * n:]}
     tid = None
     if table_id is not None:
         tid = torch.as_tensor(table_id, dtype=torch.int32).to(dev).contiguous()
@@ -297,6 +338,7 @@ def parse_actions(responses, tables=None, table_id=None, enable_think=True, acti
     res = ParseResult(raw, offsets_np, o["scratch"], o["flags"], o["spans"], o["act_spans"], o["n_parsed"], o["n_total"], o["codes"],
                       o["n_valid"], enable_think, action_sep)
     res.text, res.offsets = text, offsets
+    res.slab, res.layout = o.get("slab"), o.get("layout")
     return res
 
 

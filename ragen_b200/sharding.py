@@ -1,12 +1,15 @@
 """Sharding of the rollout path over ranks (one process per GPU) and its only exchange.
 
 Env groups are independent: rank r owns the groups with `group_id % world_size == r`, keeps their state in
-its own HBM for the whole rollout and no env state ever moves.  What couples ranks is three sets of batch-global scalars:
+its own HBM for the whole rollout and no env state ever moves.  What couples ranks is a few sets of batch-global scalars:
   (ii)  masked_whiten's moments (sum m, sum x*m, sum x^2*m)            verl/verl/utils/torch_functional.py:122-151
   (iii) the rollout metrics (per-key sums / counts, response length)   ragen/llm_agent/ctx_manager.py:288, 308-329
-They travel as ONE float64 vector of fixed layout in a single all-reduce (NCCL on the GPUs, gloo in the CPU tests);
-at C5 that is 35 doubles.  Group reward normalisation with grouping="state" (ctx_manager.py:184-185) and GRPO's per-uid
-statistics need nothing: whole groups live on one rank.
+        and, when the reward normalisation groups by tag or over the whole batch (groups then span ranks), the per-group
+        {count, sum, sum of squares} + row count as a tail of the same vector                          ctx_manager.py:175-226
+  (iv)  the StarPO-S filter's per-group std / max / mean at their global group index   ragen/trainer/agent_trainer.py:461-500
+(ii)+(iii) travel as ONE float64 vector of fixed layout in a single all-reduce per rollout (NCCL on the GPUs, gloo in the CPU
+tests; 35 doubles at C5), (iv) as 3 * env_groups doubles when the trainer filters.  Group reward normalisation with
+grouping="state" (ctx_manager.py:184-185) and GRPO's per-uid statistics need nothing: whole groups live on one rank.
 """
 from typing import Dict, List, Sequence
 
@@ -71,6 +74,23 @@ def metric_slots(tags: Sequence[str], extra_keys: Sequence[str] = ()) -> List[st
     """The fixed key order of the exchange vector: every rank derives it from the config alone."""
     keys = list(INFO_KEYS) + [k for k in extra_keys if k not in INFO_KEYS]
     return [f"{t}/{k}" for t in dict.fromkeys(tags) for k in keys]
+
+
+def all_reduce_group_stats(num_groups: int, my_groups: torch.Tensor, stats: Sequence[torch.Tensor], group=None, device=None):
+    """(iv) of SURVEY.md 8e: per-group statistics of the groups this rank owns -> the same statistics of ALL groups on every
+    rank.  stats: tensors [len(my_groups)]; returns float32 tensors [num_groups].  One all-reduce of len(stats) * num_groups
+    doubles (a float32 is exact in a double, and every slot is written by exactly one rank)."""
+    import torch.distributed as dist
+
+    k = len(stats)
+    on = device if (dist.is_available() and dist.is_initialized() and dist.get_backend(group) == "nccl") else torch.device("cpu")
+    vec = torch.zeros(k * num_groups, dtype=torch.float64, device=on)
+    idx = my_groups.to(on)
+    for j, t in enumerate(stats):
+        vec[j * num_groups + idx] = t.to(on, torch.float64)
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(vec, group=group)
+    return tuple(vec[j * num_groups:(j + 1) * num_groups].to(torch.float32) for j in range(k))
 
 
 class RolloutExchange:

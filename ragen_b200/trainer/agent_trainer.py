@@ -96,15 +96,34 @@ def apply_kl_penalty(data, kl_ctrl, kl_penalty="kl", multi_turn=False, device=No
     return data, {"actor/reward_kl_penalty": current_kl, "actor/reward_kl_penalty_coeff": beta}
 
 
-def filter_rollout(batch, num_groups, group_size, rollout_filter_ratio, rollout_filter_type="std", device=None):
+def filter_rollout(batch, num_groups, group_size, rollout_filter_ratio, rollout_filter_type="std", device=None, sharded=False,
+                   group=None):
     """StarPO-S trajectory filter, the `_filter_rollout` closure of RayAgentTrainer.fit (ragen/trainer/agent_trainer.py:461-500):
     keep the top `ratio` of the env groups by in-group std of the summed scores ("std") or by its negative ("std_rev").
     The statistics are one launch; choosing int(ratio * num_groups) of num_groups floats and the boolean row gather of the
-    (host-resident) batch are the reference's own torch calls, so ties break exactly as they do there."""
+    (host-resident) batch are the reference's own torch calls, so ties break exactly as they do there.
+
+    sharded=True: `batch` holds this rank's env groups only (consecutive rows per group, their GLOBAL ids in
+    non_tensor_batch["group_ids"]) and `num_groups` is the number of groups of the WHOLE rollout.  Every rank writes the
+    std / max / mean of its groups at their global index of one float64 vector, the vector is all-reduced (3 * num_groups
+    doubles), every rank takes the reference's top-k on the full vector and keeps its own rows of the chosen
+    groups; the metrics are those of the whole rollout on every rank."""
     scores = batch.batch["original_rm_scores"]
     home = scores.device
     dev = home if home.type == "cuda" else torch.device("cuda", torch.cuda.current_device() if device is None else int(device))
-    _, in_group_std, in_group_max, in_group_mean = (t.to(home) for t in ops.group_filter_stats(scores.to(dev), num_groups, group_size))
+    local_groups = scores.shape[0] // group_size if sharded else num_groups
+    if local_groups:
+        _, in_group_std, in_group_max, in_group_mean = (t.to(home) for t in ops.group_filter_stats(scores.to(dev), local_groups, group_size))
+    else:
+        in_group_std = in_group_max = in_group_mean = torch.zeros(0, dtype=torch.float32, device=home)
+    my_groups = None
+    if sharded:
+        from ..sharding import all_reduce_group_stats
+
+        my_groups = torch.tensor([int(g) for g in batch.non_tensor_batch["group_ids"][::group_size]], dtype=torch.long)
+        in_group_std, in_group_max, in_group_mean = all_reduce_group_stats(
+            num_groups, my_groups, (in_group_std, in_group_max, in_group_mean), group=group, device=dev)
+        in_group_std, in_group_max, in_group_mean = (t.to(home) for t in (in_group_std, in_group_max, in_group_mean))
     if rollout_filter_ratio == 1:
         return batch, {"rollout/in_group_std": in_group_std.mean(), "rollout/in_group_max": in_group_max.mean(),
                        "rollout/in_group_mean": in_group_mean.mean(), "rollout/chosen_in_group_std": in_group_std.mean(),
@@ -118,6 +137,8 @@ def filter_rollout(batch, num_groups, group_size, rollout_filter_ratio, rollout_
         raise ValueError(f"Invalid rollout filter type: {rollout_filter_type}")
     mask = torch.zeros(num_groups, dtype=torch.bool)
     mask[top_groups.cpu()] = True
+    if my_groups is not None:
+        mask = mask[my_groups]  # this rank's groups, in the order of its rows
     mask = mask.unsqueeze(1).expand(-1, group_size).flatten()
     if isinstance(batch.batch, dict):  # the stand-in container (no tensordict installed)
         kept = type(batch.batch)({k_: v[mask.to(v.device)] for k_, v in batch.batch.items()})

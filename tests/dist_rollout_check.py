@@ -23,10 +23,11 @@ def main():
     from ragen_b200.llm_agent.agent_proxy import LLMAgentProxy
     from ragen_b200.llm_agent.ctx_manager import DataProto
     from ragen_b200.trainer import AdvantageEstimator, compute_advantage
+    from ragen_b200.trainer.agent_trainer import filter_rollout
 
     with open(os.path.join(HERE, "golden", "rollouts.json")) as fh:
         cases = json.load(fh)
-    for case in cases[:2]:
+    for case in cases:
         cfg = C.base_config(tags=tuple(case["tags"]), n_groups=tuple(case["n_groups"]), group_size=case["group_size"], **case["ap"])
         tok = FakeQwenTokenizer()
         proxy = LLMAgentProxy(cfg, ScriptedWg(tok, DataProto), tok, device=local, rank=rank, world_size=world)
@@ -41,7 +42,18 @@ def main():
         gen = torch.Generator().manual_seed(1000 + rank)
         batch["values"] = torch.randn(B, T, generator=gen) * batch["response_mask"]
         compute_advantage(dp, AdvantageEstimator.GAE, gamma=1.0, lam=1.0, device=local, sharded=True)
-        mine = {"env_ids": env_ids, "rm_last": batch["rm_scores"][:, -1:].flatten().tolist(), "loss_mask_sum": batch["loss_mask"].sum(-1).tolist(),
+        # StarPO-S filter on the sharded batch (agent_trainer.py:461-500): top half of ALL groups by in-group std
+        import copy as _copy
+
+        n_groups_all = int(sum(case["n_groups"]))
+        fdp = DataProto(batch=type(batch)({k: v for k, v in batch.items()}), non_tensor_batch=dict(dp.non_tensor_batch.items()), meta_info={})
+        if hasattr(batch, "batch_size"):
+            fdp.batch.batch_size = batch.batch_size
+        row_sums = batch["original_rm_scores"].sum(-1).tolist()
+        fdp, fmetrics = filter_rollout(fdp, n_groups_all, case["group_size"], 0.5, "std", device=local, sharded=True)
+        kept_ids = [int(e) for e in fdp.non_tensor_batch["env_ids"]]
+        mine = {"env_ids": env_ids, "row_sums": row_sums, "kept_ids": kept_ids,
+                "filter_metrics": {k: float(v) for k, v in fmetrics.items()}, "rm_last": batch["rm_scores"][:, -1:].flatten().tolist(), "loss_mask_sum": batch["loss_mask"].sum(-1).tolist(),
                 "metrics": {k: float(v) for k, v in dp.meta_info["metrics"].items()},
                 "r": batch["token_level_rewards"], "v": batch["values"], "m": batch["response_mask"], "adv": batch["advantages"],
                 "ret": batch["returns"]}
@@ -54,6 +66,16 @@ def main():
                 r, i = order[e]
                 assert abs(gathered[r]["rm_last"][i] - case["rm_last"][e]) <= 1e-5 * max(1.0, abs(case["rm_last"][e])), (case["name"], e)
                 assert gathered[r]["loss_mask_sum"][i] == case["loss_mask_sum"][e], (case["name"], e)
+            # the filter: same choice as the reference's arithmetic on the whole batch, same metrics on every rank
+            gs_ = case["group_size"]
+            sums = torch.tensor([gathered[order[e][0]]["row_sums"][order[e][1]] for e in range(len(order))]).view(-1, gs_)
+            std_all = sums.std(dim=-1)
+            top = std_all.topk(int(0.5 * sums.shape[0])).indices.tolist()
+            want_kept = sorted(g_ * gs_ + i for g_ in top for i in range(gs_))
+            assert sorted(e for g in gathered for e in g["kept_ids"]) == want_kept, case["name"]
+            for g in gathered:
+                assert abs(g["filter_metrics"]["rollout/in_group_std"] - float(std_all.mean())) <= 1e-5 * max(1.0, float(std_all.mean()))
+                assert g["filter_metrics"] == gathered[0]["filter_metrics"]
             for g in gathered:
                 assert set(g["metrics"]) == set(case["metrics"])
                 for k, w in case["metrics"].items():

@@ -119,3 +119,36 @@ def test_obs_text_is_a_plain_string_to_everybody_else():
     assert type(back) is str and back == t
     Log.epoch = 4
     assert not t.live()
+
+
+def test_fast_row_path_equals_the_general_item_walk():
+    """row_elements (finished turns resolved once and cached per history entry) must describe the same chunk sequence as
+    items() (the reference's message loop) for every stage of a growing trajectory, in generation and in update mode."""
+    from ragen_b200.llm_agent.assembly import ObsText
+
+    class Log:  # what ObsText needs from an ObsLog on the host
+        epoch, H, W = 1, 6, 6
+        glyphs = GLYPHS
+
+    a = _assembler(FakeQwenTokenizer())
+    a._modes[(GLYPHS, 6, 6)] = "cell"
+    log = Log()
+    final = copy.deepcopy(golden_json("es_manager.json")["final"])
+    for eo in final:
+        full = eo["history"]
+        for j, h in enumerate(full):
+            if "state" in h:
+                h["state"] = ObsText(h["state"], log, 1, j, eo["env_id"])
+        for upto in range(1, len(full) + 1):
+            for pfu in (False, True):
+                hist = [dict(h) for h in full[:upto]]
+                if not pfu:  # the open state of a generation call has no response yet
+                    hist[-1] = {k: v for k, v in hist[-1].items() if k in ("state", "actions_left")}
+                elif "llm_response" not in hist[-1]:
+                    continue
+                view = {"env_id": eo["env_id"], "history": hist}
+                fills = []
+                fast = a.row_elements(view, pfu, fills)
+                slow = a.items(view, pfu)
+                assert fast == slow and [type(x) for x in fast] == [type(x) for x in slow]
+                assert len(fills) == len(hist) - 1

@@ -18,4 +18,4 @@ def test_sharded_rollout_and_advantage_nccl():
            "--master-port", "29671", os.path.join(here, "dist_rollout_check.py")]
     res = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
-    assert res.stdout.count("dist check ok") == 2
+    assert res.stdout.count("dist check ok") == 3

@@ -75,7 +75,23 @@ def _worker(rank, world, port, ret):
         # ops.all_reduce_moments is the 24-byte variant used by compute_advantage(sharded=True)
         from ragen_b200 import ops
         mom2 = ops.all_reduce_moments(local.clone())
-        ret[rank] = (metrics, mom.tolist(), mom2.tolist())
+        # (iv) StarPO-S filter statistics: 6 groups of 2 rows, this rank's groups written at their global index
+        scores = torch.randn(12, generator=torch.Generator().manual_seed(5)).view(6, 2)
+        mine_g = torch.tensor([g for g in range(6) if g % world == rank])
+        full = S.all_reduce_group_stats(6, mine_g, (scores[mine_g].std(-1), scores[mine_g].max(-1).values, scores[mine_g].mean(-1)))
+        # (iii) tail: tag-wide normalisation statistics of this rank's rows (what ragen_group_norm_stats writes) + row count
+        last = torch.randn(12, generator=torch.Generator().manual_seed(6))
+        pen = torch.tensor([0.0, -0.1] * 6)
+        keys = [0 if c["tag"] == "A" else 1 for c in caches]
+        xs = (last + pen)[rows].double()
+        tail = torch.zeros(3 * 2 + 1, dtype=torch.float64)
+        for v, k in zip(xs.tolist(), [keys[i] for i in rows]):
+            tail[3 * k] += 1
+            tail[3 * k + 1] += v
+            tail[3 * k + 2] += v * v
+        tail[-1] = len(rows)
+        both = ex.all_reduce(torch.cat([ex.pack(mine, float(mm.sum()), len(rows), moments=local), tail]))
+        ret[rank] = (metrics, mom.tolist(), mom2.tolist(), [t.tolist() for t in full], both[ex.size:].tolist())
     finally:
         dist.destroy_process_group()
 
@@ -104,7 +120,26 @@ def test_world_size_2_exchange_matches_single_process():
     gen = torch.Generator().manual_seed(3)
     x = torch.randn(12, 40, generator=gen)
     mask = (torch.rand(12, 40, generator=gen) > 0.4).float()
-    for metrics, mom, mom2 in results:
+    scores = torch.randn(12, generator=torch.Generator().manual_seed(5)).view(6, 2)
+    last = torch.randn(12, generator=torch.Generator().manual_seed(6))
+    pen = torch.tensor([0.0, -0.1] * 6)
+    keys = [0 if c["tag"] == "A" else 1 for c in caches]
+    want_norm = M.normalize_scores(last, pen, keys, "mean_std")
+    for metrics, mom, mom2, full, tail in results:
+        # every rank holds the statistics of ALL groups, exactly the single-process values -> the same top-k everywhere
+        assert torch.equal(torch.tensor(full[0]), scores.std(-1)) and torch.equal(torch.tensor(full[1]), scores.max(-1).values)
+        assert torch.equal(torch.tensor(full[2]), scores.mean(-1))
+        # global per-tag statistics -> the reference's normalisation of the whole batch (norm_apply_kernel's arithmetic)
+        assert tail[-1] == 12
+        xn = (last + pen).double()
+        for k in (0, 1):
+            c, s1, s2 = tail[3 * k:3 * k + 3]
+            mu = s1 / c
+            sd = np.sqrt(max((s2 - c * mu * mu) / (c - 1), 0.0))
+            idx = [i for i, kk in enumerate(keys) if kk == k]
+            got = (xn[idx] - mu) / (sd + 1e-6)
+            assert float((got - want_norm[idx].double()).abs().max()) <= 1e-5
+    for metrics, mom, mom2, _, _ in results:
         assert set(metrics) == set(want) | {"response_length"}
         for k, w in want.items():
             assert metrics[k] == pytest.approx(float(w), rel=1e-12), k

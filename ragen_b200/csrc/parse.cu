@@ -197,10 +197,52 @@ __device__ __forceinline__ void parse_one(const ParseParams& p, const int64_t r,
       bool special = __ballot_sync(0xffffffffu, occ_pos >= s && occ_pos + occ_len <= e) != 0;
       if (n_occ > 32 && !special) special = parse::has_special(text, s, e);  // more occurrences than remembered: look again
       if (special) {
-        // the span is staged in shared memory for the six passes (each sweeps it once); longer spans are cleaned in
-        // the scratch blob itself
         uint8_t* scr = p.scratch + off;
         const int len = e - s;
+        // First the common case, in ONE pass: special strings start with '<' and hold no second one, so occurrences never overlap,
+        // and removing all of them at once is what the six sequential replace passes do unless a removal splices a new special
+        // string together ("</ans<think>wer>") - which can only happen across a junction, so the 11 bytes before every junction of
+        // the cleaned text are looked at.  (One strip at the end equals a strip after every pass: stripping creates nothing.)
+        // The occurrences are the ones the scan remembered, one per lane, in text order.
+        bool fused = n_occ <= 32;
+        int w = 0;
+        if (fused) {
+          unsigned inside = __ballot_sync(0xffffffffu, occ_pos >= s && occ_pos + occ_len <= e);
+          int from = s;
+          int my_junction = -1;
+          while (inside) {
+            const int l = __ffs(inside) - 1;
+            inside &= inside - 1;
+            const int q = __shfl_sync(0xffffffffu, occ_pos, l), ql = __shfl_sync(0xffffffffu, occ_len, l);
+            if (q < from) continue;  // starts inside an occurrence already removed: cannot happen (no '<' inside one)
+            for (int i = from + lane; i < q; i += 32) scr[s + w + (i - from)] = text[i];
+            w += q - from;
+            from = q + ql;
+            if (lane == l) my_junction = w;
+          }
+          for (int i = from + lane; i < e; i += 32) scr[s + w + (i - from)] = text[i];
+          w += e - from;
+          __syncwarp();
+          bool splice = false;
+          if (my_junction >= 0) {
+            for (int k = 1; k <= 11 && my_junction - k >= 0; ++k) {
+              const uint8_t* c = scr + s + my_junction - k;
+              if (*c == '<') {
+                const int tag = parse::classify_tag(c, scr + s + w);
+                if (tag != parse::T_NONE && parse::tag_len(tag) > k) splice = true;
+              }
+            }
+          }
+          fused = !__any_sync(0xffffffffu, splice);
+        }
+        if (fused) {
+          int cs = s, ce = s + w;
+          parse::strip(scr, cs, ce);
+          s = cs;
+          e = ce;
+        } else {
+        // the span is staged in shared memory for the six passes (each sweeps it once); longer spans are cleaned in
+        // the scratch blob itself
         const bool staged = len <= CLEAN_CAP;
         uint8_t* buf = staged ? stage : scr + s;
 #pragma unroll 4
@@ -217,6 +259,7 @@ __device__ __forceinline__ void parse_one(const ParseParams& p, const int64_t r,
         }
         e = s + ce;
         s = s + cs;
+        }
         fl |= which ? 4 : 2;
         if (which) abuf = scr;
       } else {

@@ -7,8 +7,10 @@
 // Parallelisation: rooms are independent and each search is inherently sequential (a depth-limited DFS whose global
 // visited set makes the result depend on visiting order), so one THREAD owns one room - and the code is shaped so that
 // the 32 rooms of a warp run in lock step instead of one after the other:
-//   * a warp takes 32 consecutive rooms at a time from an atomic counter and walks the phases of generate_room together
-//     (seed both MT19937 streams, then up to four tries of topology -> placement -> clear -> search, then the player jitter);
+//   * rooms are handed out LANE BY LANE from an atomic counter: a warp alternates between a set-up phase, where the lanes that
+//     owe a try walk seed -> topology -> placement -> clear together, and a search phase that ends as soon as a few searches
+//     have ended, so a lane with a short search is given its next room while its neighbours' long searches go on (a room's
+//     search explores 2 400 states on average and 25 000 at worst: waiting for the longest of 32 left 5 of 32 lanes busy);
 //   * the MT19937 states of a warp are interleaved word by word (lane l's word i at [i][l]), so the seeding and twist
 //     loops, whose trip counts are the same for every room, touch whole 128-byte lines;
 //   * the visited bitmaps (128 KB per room for 10x10 / 2 boxes) are cleared by the whole warp, 512 contiguous bytes per
@@ -21,6 +23,8 @@
 // Outputs are 2*H*W bytes per room.  No roofline claim: rooms/s and validity are what is reported.
 #include "common.cuh"
 #include "sokoban_gen_logic.cuh"
+
+#include <stdlib.h>
 
 namespace {
 
@@ -42,8 +46,134 @@ struct GenParams {
   size_t warp_bytes, off_lanes, lane_bytes, off_stack, off_vis, vis_bytes;
   uint32_t vis_mask;
   int vis_mode, stack_in_smem;
+  int refill_at;  // searches of a warp that must have ended before it stops to hand their lanes new rooms
   unsigned long long* counter;
 };
+
+
+// One warp, NB boxes, bitmap or hash visited set.  A lane is IDLE (wants a room), owes a TRY (topology -> placement -> clear ->
+// search_begin; up to four per room, utils.py:244) or is in a SEARCH.  The warp alternates between a set-up phase, in which
+// the lanes that owe a try run it in lock step (the MT19937 seeding and the visited-set clears are the expensive, uniform
+// parts), and a search phase that runs until `refill_at` searches have ended (any, once the queue is empty) - so a lane whose
+// search is short gets its next room while the long searches of its neighbours go on, instead of idling until the longest of
+// 32 ends.  Rooms are handed out lane by lane from one atomic counter.
+template <int NB, bool BITMAP>
+__device__ __forceinline__ void generate_warp(const GenParams& p, const sgen::Geometry& g, sgen::Fast& fm, sgen::Visited& vis,
+                                              uint8_t* wws, uint8_t* floor, uint8_t* vis_mem, uint32_t* s_wall_lane, const int lane) {
+  const unsigned FULL = 0xffffffffu;
+  const int HW = g.H * g.W;
+  enum { IDLE = 0, TRY = 1, SEARCH = 2 };
+  int phase = IDLE, tries = 0, st = 0, explored = 0, player = 0;
+  int64_t room = 0;
+  bool fresh = false, queue_empty = false;
+  uint8_t targets[sgen::MAX_BOXES] = {0, 0, 0, 0};
+  sgen::BestFast best;
+  best.disp = 0;
+  best.p = 0;
+  best.boxes = 0;
+  best.score = -1;
+  sgen::Search<NB> S;
+  S.depth = -1;
+  mt::State py{reinterpret_cast<uint32_t*>(wws) + lane, 0, 32};
+  mt::State np{reinterpret_cast<uint32_t*>(wws) + mt::N * 32 + lane, 0, 32};
+
+  for (;;) {
+    // ---- idle lanes take the next rooms ---------------------------------------------------------------------------
+    const unsigned idle = __ballot_sync(FULL, phase == IDLE);
+    if (idle && !queue_empty) {
+      const int cnt = __popc(idle);
+      unsigned long long base = 0;
+      if (lane == 0) base = atomicAdd(p.counter, (unsigned long long)cnt);
+      base = __shfl_sync(FULL, base, 0);
+      if (phase == IDLE) {
+        const unsigned long long r = base + (unsigned)__popc(idle & ((1u << lane) - 1u));
+        if (r < (unsigned long long)p.n) {
+          room = (int64_t)r;
+          phase = TRY;
+          fresh = true;
+          tries = 0;
+        }
+      }
+      if (base + (unsigned long long)cnt >= (unsigned long long)p.n) queue_empty = true;
+    }
+    // ---- lanes that owe a try: seed (new rooms), topology, placement, clear, enter the root ----------------------------
+    if (__any_sync(FULL, phase == TRY)) {
+      if (phase == TRY && fresh) {
+        const uint64_t seed = p.seeds[room];
+        mt::seed_python(py, seed);
+        mt::seed_numpy(np, (uint32_t)seed);
+        fresh = false;
+        st = (int)sgen::OK;
+        explored = 0;
+        best.disp = 0;
+        if ((seed >> 32) != 0) {  // np.random.seed rejects seeds >= 2^32 (ValueError in the reference)
+          p.status[room] = 3;
+          if (p.explored) p.explored[room] = 0;
+          phase = IDLE;
+        }
+      }
+      bool search = false;
+      uint8_t* fixed = p.fixed + room * HW;
+      if (phase == TRY) {
+        sgen::topology(py, g, p.num_gen_steps, 0.35, floor);
+        if (sgen::place(np, g, floor, fixed, player, targets)) {
+          search = true;
+        } else {  // 'Not enough free spots': generate_room raises before reporting the previous try's count
+          p.status[room] = (int)sgen::NO_SPACE;
+          if (p.explored) p.explored[room] = 0;
+          phase = IDLE;
+        }
+      }
+      __syncwarp();
+      // clear the visited sets of the lanes that search, all 32 lanes on one lane's set at a time
+      unsigned need = __ballot_sync(FULL, search);
+      while (need) {
+        const int l = __ffs((int)need) - 1;
+        need &= need - 1;
+        uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(__shfl_sync(FULL, (unsigned long long)vis_mem, l)));
+        const size_t vecs = p.vis_bytes >> 4;
+        for (size_t i = lane; i < vecs; i += 32) dst[i] = make_uint4(0u, 0u, 0u, 0u);
+      }
+      __syncwarp();  // orders the other lanes' zeroes before this lane's probes
+      if (search) {
+        sgen::fill_walls(g, fixed, s_wall_lane, GEN_T);
+        sgen::search_begin<NB, BITMAP>(S, g, fm, sgen::pack_cells(targets, g.nb), player, p.search_depth, vis, best, true);
+        phase = SEARCH;
+        ++tries;
+      }
+    }
+    // ---- search: one child tried or one level popped per iteration, until enough searches have ended --------------------
+    const unsigned searching = __ballot_sync(FULL, phase == SEARCH);
+    if (searching == 0) {
+      if (queue_empty) break;  // nobody searches, nobody owes a try (they would be searching now), nothing left to hand out
+      continue;
+    }
+    const int stop_at = queue_empty ? 1 : (__popc(searching) < p.refill_at ? __popc(searching) : p.refill_at);
+    for (;;) {
+      const bool running = phase == SEARCH && S.depth >= 0;
+      const unsigned run = __ballot_sync(FULL, running);
+      if (__popc(searching & ~run) >= stop_at) break;
+      if (running) sgen::search_step<NB, BITMAP>(S, g, fm, p.search_depth, vis, best);
+    }
+    // ---- lanes whose search has ended: done, or another try ----------------------------------------------------------------
+    if (phase == SEARCH && S.depth < 0) {
+      explored = S.explored;
+      if (best.disp > 0 || tries >= 4) {
+        if (best.disp == 0) {
+          st = (int)sgen::SCORE_ZERO;  // RuntimeWarning('Generated Model with score == 0')
+        } else {
+          sgen::finish_room(py, g, p.fixed + room * HW, p.state + room * HW, best);
+        }
+        p.status[room] = st;
+        if (p.explored) p.explored[room] = explored;
+        phase = IDLE;
+      } else {
+        phase = TRY;
+      }
+    }
+    __syncwarp();
+  }
+}
 
 __global__ void __launch_bounds__(GEN_T) sokoban_generate_kernel(const GenParams p) {
   extern __shared__ __align__(16) uint8_t smem[];
@@ -79,76 +209,22 @@ __global__ void __launch_bounds__(GEN_T) sokoban_generate_kernel(const GenParams
   fm.wall_stride = GEN_T;
   fm.stack = p.stack_in_smem ? s_stack + threadIdx.x : lws + p.off_stack;
   fm.stack_stride = p.stack_in_smem ? GEN_T : 1;
-  const unsigned FULL = 0xffffffffu;
-
-  for (;;) {
-    unsigned long long base = 0;
-    if (lane == 0) base = atomicAdd(p.counter, 32ull);
-    base = __shfl_sync(FULL, base, 0);
-    if (base >= (unsigned long long)p.n) break;
-    const int64_t room = (int64_t)base + lane;
-    const bool valid = room < p.n;
-    const uint64_t seed = valid ? p.seeds[room] : 0;
-    const bool seed_ok = (seed >> 32) == 0;  // np.random.seed rejects seeds >= 2^32 (ValueError in the reference)
-    uint8_t* fixed = p.fixed + (valid ? room : 0) * HW;
-    uint8_t* state = p.state + (valid ? room : 0) * HW;
-
-    mt::State py{reinterpret_cast<uint32_t*>(wws) + lane, 0, 32};
-    mt::State np{reinterpret_cast<uint32_t*>(wws) + mt::N * 32 + lane, 0, 32};
-    mt::seed_python(py, seed);
-    mt::seed_numpy(np, (uint32_t)seed);
-
-    int st = seed_ok ? (int)sgen::OK : 3, explored = 0, player = 0;
-    bool trying = valid && seed_ok;  // this lane still owes a try (generate_room's loop of four, utils.py:244)
-    uint8_t targets[sgen::MAX_BOXES] = {0, 0, 0, 0};
-    sgen::BestFast best;
-    best.disp = 0;
-    best.p = 0;
-    best.boxes = 0;
-    for (int t = 0; t < 4; ++t) {
-      if (!__any_sync(FULL, trying)) break;
-      bool search = false;
-      if (trying) {
-        sgen::topology(py, g, p.num_gen_steps, 0.35, floor);
-        if (sgen::place(np, g, floor, fixed, player, targets)) {
-          search = true;
-        } else {
-          st = sgen::NO_SPACE;
-          explored = 0;  // generate_room returns before reporting the previous try's count
-          trying = false;
-        }
-      }
-      __syncwarp();
-      // clear the visited sets of the lanes that search, all 32 lanes on one lane's set at a time
-      unsigned need = __ballot_sync(FULL, search);
-      while (need) {
-        const int l = __ffs((int)need) - 1;
-        need &= need - 1;
-        uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(__shfl_sync(FULL, (unsigned long long)vis_mem, l)));
-        const size_t vecs = p.vis_bytes >> 4;
-        for (size_t i = lane; i < vecs; i += 32) dst[i] = make_uint4(0u, 0u, 0u, 0u);
-      }
-      __syncwarp();  // orders the other lanes' zeroes before this lane's probes
-      if (search) sgen::fill_walls(g, fixed, s_wall + threadIdx.x, GEN_T);
-      // all 32 lanes enter: the search loop is warp-wide so that the lanes meet again after every iteration
-      const int found = sgen::reverse_play_fast(g, fm, sgen::pack_cells(targets, g.nb), player, p.search_depth, vis, best, search);
-      if (search) {
-        explored = found;
-        if (best.disp > 0) trying = false;
-      }
+  uint32_t* wl = s_wall + threadIdx.x;
+  // every lane of the launch takes the same case (the number of boxes and the kind of visited set are launch-wide)
+  if (p.vis_mode == 0) {
+    switch (g.nb) {
+      case 1: generate_warp<1, true>(p, g, fm, vis, wws, floor, vis_mem, wl, lane); break;
+      case 2: generate_warp<2, true>(p, g, fm, vis, wws, floor, vis_mem, wl, lane); break;
+      case 3: generate_warp<3, true>(p, g, fm, vis, wws, floor, vis_mem, wl, lane); break;
+      default: generate_warp<4, true>(p, g, fm, vis, wws, floor, vis_mem, wl, lane); break;
     }
-    if (valid) {
-      if (st == sgen::OK) {
-        if (best.disp == 0) {
-          st = sgen::SCORE_ZERO;  // RuntimeWarning('Generated Model with score == 0')
-        } else {
-          sgen::finish_room(py, g, fixed, state, best);
-        }
-      }
-      p.status[room] = st;
-      if (p.explored) p.explored[room] = seed_ok ? explored : 0;
+  } else {
+    switch (g.nb) {
+      case 1: generate_warp<1, false>(p, g, fm, vis, wws, floor, vis_mem, wl, lane); break;
+      case 2: generate_warp<2, false>(p, g, fm, vis, wws, floor, vis_mem, wl, lane); break;
+      case 3: generate_warp<3, false>(p, g, fm, vis, wws, floor, vis_mem, wl, lane); break;
+      default: generate_warp<4, false>(p, g, fm, vis, wws, floor, vis_mem, wl, lane); break;
     }
-    __syncwarp();
   }
 }
 
@@ -213,6 +289,11 @@ extern "C" int ragen_sokoban_generate(ragen_ctx* ctx, int64_t n, int H, int W, i
   const size_t ws_bytes = 256 + (size_t)ctas * (GEN_T / 32) * p.warp_bytes;
   uint8_t* ws = (uint8_t*)ragen_gen_workspace(ctx, ws_bytes);
   if (!ws) return RAGEN_ENOMEM;
+  p.refill_at = 8;
+  if (const char* e = getenv("RAGEN_GEN_REFILL")) {  // probing only
+    const int v = atoi(e);
+    if (v >= 1 && v <= 32) p.refill_at = v;
+  }
   p.counter = reinterpret_cast<unsigned long long*>(ws);
   p.ws = ws + 256;
   RAGEN_CUDA(cudaMemsetAsync(p.counter, 0, sizeof(unsigned long long), st));

@@ -376,117 +376,148 @@ RAGEN_HD bool probe_bitmap(Visited& v, Granule& c, uint32_t key) {
   return false;
 }
 
-// `active` false: the caller only takes part in the warp-wide loop (device) and nothing is touched.
+// The search as a resumable state: search_begin enters the root, search_step is ONE iteration (return one level if the node
+// has no child left, then try one child of the node now current), the search is over when depth < 0.  A caller may stop
+// stepping a lane and come back to it later (the generator kernel refills idle lanes of a warp while the others are
+// mid-search); reverse_play_nb below is begin + step until done.
 // BITMAP: the visited set is the bitmap (keys < 2^24, 32-bit arithmetic) instead of the hash table (64-bit keys).
+template <int NB>
+struct Search {
+  int p, last, swaps, depth, explored;
+  uint32_t boxes;
+  unsigned pulled, open;
+  Granule gran;
+  TargetInfo<NB> tg;
+};
+
 template <int NB, bool BITMAP>
-RAGEN_HD int reverse_play_nb(const Geometry& g, const Fast& m, uint32_t targets, int player, int search_depth, Visited& vis,
-                             BestFast& best, bool active) {
+RAGEN_HD void search_begin(Search<NB>& s, const Geometry& g, const Fast& m, uint32_t targets, int player, int search_depth,
+                           Visited& vis, BestFast& best, bool active) {
   const uint32_t nbmask = NB >= 4 ? 0xffffffffu : ((1u << (8 * (NB & 3))) - 1u);
   const int W = g.W, cell_bits = g.cell_bits;
-  int p = player, last = -1, swaps = 0, depth = -1, explored = 0;
-  uint32_t boxes = targets | ~nbmask;  // unused bytes 0xff: the far corner of a 16x16 grid at most, a wall
-  unsigned pulled = 0, open = 0;
-  Granule gran{0xffffffffu, 0ull};
-  TargetInfo<NB> tg;
-  tg.packed = targets;
+  s.p = player;
+  s.last = -1;
+  s.swaps = 0;
+  s.depth = -1;
+  s.explored = 0;
+  s.boxes = targets | ~nbmask;  // unused bytes 0xff: the far corner of a 16x16 grid at most, a wall
+  s.pulled = 0;
+  s.open = 0;
+  s.gran = Granule{0xffffffffu, 0ull};
+  s.tg.packed = targets;
   if (active) {
 #pragma unroll
-    for (int k = 0; k < NB; ++k) tg.rc[k] = m.rc[(targets >> (8 * k)) & 0xffu];
+    for (int k = 0; k < NB; ++k) s.tg.rc[k] = m.rc[(targets >> (8 * k)) & 0xffu];
     best.score = -1;
     best.p = player;
     best.disp = 0;
-    best.boxes = boxes;
+    best.boxes = s.boxes;
   }
   // the root, entered the way depth_first_search enters any node; a node at stack depth d runs with
   // ttl = search_depth - 1 - d and its children are entered only while that stays positive (:455)
   if (active && search_depth - 1 > 0) {
     if (BITMAP)
-      probe_bitmap(vis, gran, node_key_fast<NB, uint32_t>(m, cell_bits, p, boxes, pulled));
+      probe_bitmap(vis, s.gran, node_key_fast<NB, uint32_t>(m, cell_bits, s.p, s.boxes, s.pulled));
     else
-      visited_test_and_set(vis, node_key_fast<NB, uint64_t>(m, cell_bits, p, boxes, pulled));
-    explored = 1;
+      visited_test_and_set(vis, node_key_fast<NB, uint64_t>(m, cell_bits, s.p, s.boxes, s.pulled));
+    s.explored = 1;
     int disp;
-    const int score = node_score<NB>(m, tg, nbmask, p, boxes, swaps, &disp);
+    const int score = node_score<NB>(m, s.tg, nbmask, s.p, s.boxes, s.swaps, &disp);
     if (score > best.score) {
       best.score = score;
-      best.p = p;
+      best.p = s.p;
       best.disp = disp;
-      best.boxes = boxes;
+      best.boxes = s.boxes;
     }
-    depth = 0;
-    open = (search_depth - 2 > 0) ? open_children(m, W, p, boxes, nbmask) : 0u;
+    s.depth = 0;
+    s.open = (search_depth - 2 > 0) ? open_children(m, W, s.p, s.boxes, nbmask) : 0u;
   }
+}
+
+template <int NB, bool BITMAP>
+RAGEN_HD void search_step(Search<NB>& s, const Geometry& g, const Fast& m, int search_depth, Visited& vis, BestFast& best) {
+  const uint32_t nbmask = NB >= 4 ? 0xffffffffu : ((1u << (8 * (NB & 3))) - 1u);
+  const int W = g.W, cell_bits = g.cell_bits;
+  // an iteration = return one level if this node has no child left, then try one child of the node now current
+  if (s.depth >= 0 && s.open == 0) {
+    if (s.depth == 0) {
+      s.depth = -1;
+    } else {
+      const unsigned code = m.stack[(size_t)s.depth * m.stack_stride];
+      const int a = code & 3, combo = code >> 3;
+      const int k = combo / 5 - 1, prev_last = combo % 5 - 1;
+      const int st = step_of(W, a);
+      const int parent = s.p - st;
+      if (k >= 0) {
+        s.boxes = (s.boxes & ~(0xffu << (8 * k))) | ((uint32_t)(parent - st) << (8 * k));
+        if (code & 4u) s.pulled &= ~(1u << k);
+        if (k != prev_last) --s.swaps;
+      }
+      s.last = prev_last;
+      s.p = parent;
+      --s.depth;
+      s.open = open_children(m, W, s.p, s.boxes, nbmask) & ~((2u << a) - 1u);
+    }
+  }
+  if (s.depth >= 0 && s.open != 0) {
+    const int a = lowest_bit(s.open);
+    s.open &= s.open - 1;
+    if (s.explored < MAX_EXPLORED) {
+      const int st = step_of(W, a);
+      const int n = s.p + st, behind = s.p - st;
+      const uint32_t mb = eq4(s.boxes, bcast4(behind)) & nbmask;
+      uint32_t cboxes = s.boxes;
+      unsigned cpulled = s.pulled, newbit = 0;
+      int clast = s.last, cswaps = s.swaps, k = -1;
+      if (mb) {  // pull that box onto the cell the player leaves (reverse_move :525-540)
+        k = lowest_byte(mb);
+        cboxes = (s.boxes & ~(0xffu << (8 * k))) | ((uint32_t)s.p << (8 * k));
+        newbit = ((s.pulled >> k) & 1u) ^ 1u;
+        cpulled |= 1u << k;
+        if (s.last != k) ++cswaps;
+        clast = k;
+      }
+      const bool seen = BITMAP ? probe_bitmap(vis, s.gran, node_key_fast<NB, uint32_t>(m, cell_bits, n, cboxes, cpulled))
+                               : visited_test_and_set(vis, node_key_fast<NB, uint64_t>(m, cell_bits, n, cboxes, cpulled));
+      if (!seen) {
+        ++s.explored;
+        int disp;
+        const int score = node_score<NB>(m, s.tg, nbmask, n, cboxes, cswaps, &disp);
+        if (score > best.score) {
+          best.score = score;
+          best.p = n;
+          best.disp = disp;
+          best.boxes = cboxes;
+        }
+        ++s.depth;
+        m.stack[(size_t)s.depth * m.stack_stride] =
+            (uint8_t)((unsigned)a | (newbit << 2) | ((unsigned)((k + 1) * 5 + (s.last + 1)) << 3));
+        s.p = n;
+        s.boxes = cboxes;
+        s.pulled = cpulled;
+        s.last = clast;
+        s.swaps = cswaps;
+        s.open = (search_depth - 1 - (s.depth + 1) > 0) ? open_children(m, W, s.p, s.boxes, nbmask) : 0u;
+      }
+    }
+  }
+}
+
+// `active` false: the caller only takes part in the warp-wide loop (device) and nothing is touched.
+template <int NB, bool BITMAP>
+RAGEN_HD int reverse_play_nb(const Geometry& g, const Fast& m, uint32_t targets, int player, int search_depth, Visited& vis,
+                             BestFast& best, bool active) {
+  Search<NB> s;
+  search_begin<NB, BITMAP>(s, g, m, targets, player, search_depth, vis, best, active);
 #ifdef __CUDA_ARCH__
   // every lane of the warp is here: the vote is also the point where the lanes meet again after each iteration
-  while (__any_sync(0xffffffffu, depth >= 0)) {
+  while (__any_sync(0xffffffffu, s.depth >= 0)) {
 #else
-  while (depth >= 0) {
+  while (s.depth >= 0) {
 #endif
-    // an iteration = return one level if this node has no child left, then try one child of the node now current
-    if (depth >= 0 && open == 0) {
-      if (depth == 0) {
-        depth = -1;
-      } else {
-        const unsigned code = m.stack[(size_t)depth * m.stack_stride];
-        const int a = code & 3, combo = code >> 3;
-        const int k = combo / 5 - 1, prev_last = combo % 5 - 1;
-        const int st = step_of(W, a);
-        const int parent = p - st;
-        if (k >= 0) {
-          boxes = (boxes & ~(0xffu << (8 * k))) | ((uint32_t)(parent - st) << (8 * k));
-          if (code & 4u) pulled &= ~(1u << k);
-          if (k != prev_last) --swaps;
-        }
-        last = prev_last;
-        p = parent;
-        --depth;
-        open = open_children(m, W, p, boxes, nbmask) & ~((2u << a) - 1u);
-      }
-    }
-    if (depth >= 0 && open != 0) {
-      const int a = lowest_bit(open);
-      open &= open - 1;
-      if (explored < MAX_EXPLORED) {
-        const int st = step_of(W, a);
-        const int n = p + st, behind = p - st;
-        const uint32_t mb = eq4(boxes, bcast4(behind)) & nbmask;
-        uint32_t cboxes = boxes;
-        unsigned cpulled = pulled, newbit = 0;
-        int clast = last, cswaps = swaps, k = -1;
-        if (mb) {  // pull that box onto the cell the player leaves (reverse_move :525-540)
-          k = lowest_byte(mb);
-          cboxes = (boxes & ~(0xffu << (8 * k))) | ((uint32_t)p << (8 * k));
-          newbit = ((pulled >> k) & 1u) ^ 1u;
-          cpulled |= 1u << k;
-          if (last != k) ++cswaps;
-          clast = k;
-        }
-        const bool seen = BITMAP ? probe_bitmap(vis, gran, node_key_fast<NB, uint32_t>(m, cell_bits, n, cboxes, cpulled))
-                                 : visited_test_and_set(vis, node_key_fast<NB, uint64_t>(m, cell_bits, n, cboxes, cpulled));
-        if (!seen) {
-          ++explored;
-          int disp;
-          const int score = node_score<NB>(m, tg, nbmask, n, cboxes, cswaps, &disp);
-          if (score > best.score) {
-            best.score = score;
-            best.p = n;
-            best.disp = disp;
-            best.boxes = cboxes;
-          }
-          ++depth;
-          m.stack[(size_t)depth * m.stack_stride] =
-              (uint8_t)((unsigned)a | (newbit << 2) | ((unsigned)((k + 1) * 5 + (last + 1)) << 3));
-          p = n;
-          boxes = cboxes;
-          pulled = cpulled;
-          last = clast;
-          swaps = cswaps;
-          open = (search_depth - 1 - (depth + 1) > 0) ? open_children(m, W, p, boxes, nbmask) : 0u;
-        }
-      }
-    }
+    search_step<NB, BITMAP>(s, g, m, search_depth, vis, best);
   }
-  return explored;
+  return s.explored;
 }
 
 RAGEN_HD int reverse_play_fast(const Geometry& g, const Fast& m, uint32_t targets, int player, int search_depth, Visited& vis,

@@ -193,7 +193,9 @@ class TrajectoryAssembler:
         self._tables: Dict[tuple, tuple] = {}    # glyph table -> (int32 [8, 4] tokens, int32 [8] lengths), cell mode
         self._rows: Dict[tuple, dict] = {}       # glyph table -> {row bytes: (start, len)}, row mode
         self._rendered: Dict[tuple, tuple] = {}  # (id(log), epoch, slot, pool generation) -> per-env segment arrays
-        self._entry_cache: Dict[int, tuple] = {}  # id(history entry) -> (entry, turn index, pool generation, resolved segments)
+        self._row_cache: Dict[int, list] = {}    # id(rollout_cache dict) -> [dict, finished turns resolved, first entry, last resolved entry, pool generation, elements]
+        self._g_ua, self._g_au = self._glue("user", "assistant"), self._glue("assistant", "user")
+        self._gen_tail = self.glue.end_generation + ("<think>" if ctx_manager.config.agent_proxy.enable_think else "<answer>")
         self._heads: Dict[int, tuple] = {}       # env_id -> the two chunks every prompt of the env starts with
         self._tails: Dict[tuple, str] = {}       # (env_id, actions_left) -> "You have N actions left ..." text
         self._staging = None
@@ -425,8 +427,8 @@ class TrajectoryAssembler:
 
     # ---- assembly -------------------------------------------------------------------------------------------------
     def new_rollout(self):
-        """Finished-turn segments are cached per history entry; a new rollout starts with new entries."""
-        self._entry_cache.clear()
+        """Finished-turn segments are cached per rollout_cache dict; a new rollout starts with new histories."""
+        self._row_cache.clear()
 
     def _tail_text(self, env_id, actions_left):
         key = (env_id, actions_left)
@@ -443,14 +445,23 @@ class TrajectoryAssembler:
         """items() for the common shape of a grid-env trajectory - every entry carries a device observation, every entry but the
         last is a finished turn (response + reward), the last one is the open state (generation) or a finished turn whose
         reward message is left out (update) - with the per-turn work done ONCE: a finished turn's four chunks [observation |
-        "You have N ..." | assistant message | reward message + next turn header] never change, so their resolved segments
-        are kept per history entry and a call only builds the chunks of the newest entries.  Any other shape takes items()."""
+        "You have N ..." | assistant message | reward message + next turn header] never change, so the resolved segments of
+        a row's finished turns are kept (per rollout_cache dict) and a call only builds the chunks of the newest entries.
+        Any other shape takes items()."""
         hist = env_output["history"]
         n = len(hist)
         if n == 0:
             return self.items(env_output, prepare_for_update)
+        gen = self._pool.generation if self._pool is not None else 0
+        k0, out = 0, None
+        rc = self._row_cache.get(id(env_output))
+        if rc is not None and rc[0] is env_output and rc[4] == gen:
+            k = rc[1]
+            if 0 < k <= n - 1 and hist[0] is rc[2] and hist[k - 1] is rc[3]:
+                k0, out = k, list(rc[5])  # head + the finished turns resolved by earlier calls
         is_obs = self._is_device_obs
-        for idx, c in enumerate(hist):
+        for idx in range(k0, n):
+            c = hist[idx]
             st = c.get("state")
             if type(st) is not ObsText or not is_obs(st):
                 return self.items(env_output, prepare_for_update)
@@ -460,32 +471,28 @@ class TrajectoryAssembler:
         if prepare_for_update != ("llm_response" in last) or (not prepare_for_update and "reward" in last):
             return self.items(env_output, prepare_for_update)
         glue, env_id = self.glue, env_output["env_id"]
-        head = self._heads.get(env_id)
-        if head is None:
-            head = self._heads[env_id] = (glue.start + "You're a helpful assistant. ",
-                                          glue.between[("system", "user")] + self.cm.prefix_lookup[env_id] + "\nTurn 1:\nState:\n")
-        out = [head[0], head[1]]
-        cache, gen = self._entry_cache, self.pool.generation if self._pool is not None else 0
-        g_ua, g_au = self._glue("user", "assistant"), self._glue("assistant", "user")
-        for idx in range(n - 1):
+        if out is None:
+            head = self._heads.get(env_id)
+            if head is None:
+                head = self._heads[env_id] = (glue.start + "You're a helpful assistant. ",
+                                              glue.between[("system", "user")] + self.cm.prefix_lookup[env_id] + "\nTurn 1:\nState:\n")
+            out = [head[0], head[1]]
+        g_ua = self._g_ua
+        for idx in range(k0, n - 1):
             c = hist[idx]
-            hit = cache.get(id(c))
-            if hit is not None and hit[0] is c and hit[1] == idx and hit[2] == gen:
-                out.append(hit[3])
-                continue
             a = len(out)
             out.append(c["state"])
             out.append(self._tail_text(env_id, c["actions_left"]))
             out.append(g_ua + c["llm_response"])
-            out.append(g_au + f"Reward:\n{c['reward']}\n\nTurn {idx + 2}:\nState:\n")
-            fills.append((c, idx, out, a, a + 4))
+            out.append(self._g_au + f"Reward:\n{c['reward']}\n\nTurn {idx + 2}:\nState:\n")
+            fills.append((c, idx, out, a, env_output, gen))
         out.append(last["state"])
         tail = self._tail_text(env_id, last["actions_left"])
         if prepare_for_update:
             out.append(tail)
             out.append(g_ua + last["llm_response"] + glue.end["assistant"])
         else:
-            out.append(tail + glue.end_generation + ("<think>" if self.cm.config.agent_proxy.enable_think else "<answer>"))
+            out.append(tail + self._gen_tail)
         return out
 
     def assemble(self, env_outputs, prepare_for_update):
@@ -495,7 +502,7 @@ class TrajectoryAssembler:
         if pool.full():
             pool.reset()
             self._rendered.clear()
-            self._entry_cache.clear()
+            self._row_cache.clear()
         fills = []
         rows = [self.row_elements(eo, prepare_for_update, fills) for eo in env_outputs]
         memo = pool.memo
@@ -529,9 +536,9 @@ class TrajectoryAssembler:
                     src.extend(pair[0][it.index])
                     ln.extend(pair[1][it.index])
             off.append(len(src))
-        for entry, idx, items, a, b in fills:  # a finished turn never changes again: keep its resolved segments
+        for entry, idx, items, a, eo, gen in fills:  # a finished turn never changes again: keep its resolved segments with the row
             ss, ll = [], []
-            for it in items[a:b]:
+            for it in items[a:a + 4]:
                 if type(it) is str:
                     s_, n_ = memo[it]
                     ss.append(s_)
@@ -540,9 +547,16 @@ class TrajectoryAssembler:
                     pair = obs_lists[(id(it.log), it.slot)]
                     ss.extend(pair[0][it.index])
                     ll.extend(pair[1][it.index])
-            self._entry_cache[id(entry)] = (entry, idx, pool.generation, (tuple(ss), tuple(ll)))
-        if len(self._entry_cache) > 200000:
-            self._entry_cache.clear()
+            rc = self._row_cache.get(id(eo))
+            if rc is None or rc[0] is not eo or rc[4] != gen or rc[1] > idx:
+                if idx != 0:
+                    continue
+                rc = self._row_cache[id(eo)] = [eo, 0, entry, entry, gen, [items[0], items[1]]]
+            if rc[1] == idx:
+                rc[5].append((tuple(ss), tuple(ll)))
+                rc[1], rc[3] = idx + 1, entry
+        if len(self._row_cache) > 1 << 20:
+            self._row_cache.clear()
         B, E = len(rows), len(src)
         src = np.asarray(src, dtype=np.int64)
         ln = np.asarray(ln, dtype=np.int32)

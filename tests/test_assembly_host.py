@@ -151,4 +151,4 @@ def test_fast_row_path_equals_the_general_item_walk():
                 fast = a.row_elements(view, pfu, fills)
                 slow = a.items(view, pfu)
                 assert fast == slow and [type(x) for x in fast] == [type(x) for x in slow]
-                assert len(fills) == len(hist) - 1
+                assert len(fills) == len(hist) - 1 and all(f[1] == i for i, f in enumerate(fills))

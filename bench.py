@@ -246,7 +246,7 @@ def _reset_leg(args, rank, world, local_rank, barrier, dist, torch, np):
         if total <= 0:
             continue
         seeds = np.arange(rank, total, world, dtype=np.int64)  # group g lives on rank g % world
-        gen.generate(seeds[:64])  # workspace allocation and first-launch costs stay outside the timed region
+        gen.generate(seeds[:min(seeds.size, 1 << 17)])  # workspace allocation (it grows with the rooms in flight) and first-launch costs stay outside the timed region
         barrier()
         t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         t0.record()

@@ -308,7 +308,17 @@ def c5_rows(quick):
         r_c, v_c, m_c = rewards[:128].cpu(), values[:128].cpu(), mask[:128].cpu()
         cs = cpu_time(lambda: A.gae(r_c, v_c, m_c, 1.0, 1.0), 3.0)
         rows.append(line(f"GAE+whiten {tag}", "token", B * T, ms_full, 25, 128 * T / cs, "128 rows, torch CPU loop as the reference (all host threads)",
-                         gae_only_ms=ms_raw, kernel="gae_kernel + whiten_kernel"))
+                         gae_only_ms=ms_raw, kernel="gae_kernel + whiten_kernel (bit-exact sequential order)"))
+        ms_scan = dev_time(lambda: ops.gae_raw(rewards, values, lm, 1.0, 1.0, exact=False), reps=50, inner=INNER)
+
+        def full_scan():
+            adv, ret, mom = ops.gae_raw(rewards, values, lm, 1.0, 1.0, exact=False)
+            ops.whiten_(adv, mom, check=False)
+        ms_scan_full = dev_time(full_scan, reps=50, inner=INNER)
+        rows.append(line(f"GAE (parallel scan)+whiten {tag}", "token", B * T, ms_scan_full, 25, 128 * T / cs,
+                         "128 rows, torch CPU loop as the reference (all host threads)", gae_only_ms=ms_scan,
+                         gae_only_frac_17B=17 * B * T / (ms_scan * 1e-3) / 1e9 / peak_gbs(),
+                         kernel="gae_scan_kernel + whiten_kernel (within 1e-5 of the sequential order)"))
         # bi-level needs a reward on the last loss-mask position
         r2 = torch.zeros_like(rewards)
         last = (mask * torch.arange(1, T + 1, device="cuda")).argmax(dim=1)

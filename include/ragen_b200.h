@@ -312,6 +312,13 @@ int ragen_group_norm_noalloc(ragen_ctx* ctx, int B, const float* score_last, con
 int ragen_gae(ragen_ctx* ctx, int B, int T, const float* rewards, const float* values, const uint8_t* mask,
               double gamma, double lam, float* adv, float* ret, double* moments, void* stream);
 
+/* The same quantities from a PARALLEL scan of the recurrence (a CTA per row, 2048 tokens per step: per-thread runs of 8 tokens
+ * combined by warp-shuffle suffix sums): adv / ret equal the
+ * reference's sequential fp32 loop up to rounding (a few 1e-7 relative; north_star's bar is 1e-5) instead of bit for bit, at
+ * HBM speed for any number of rows.  For callers that consume the whitened advantages; ragen_gae keeps the reference's bits. */
+int ragen_gae_scan(ragen_ctx* ctx, int B, int T, const float* rewards, const float* values, const uint8_t* mask,
+                   double gamma, double lam, float* adv, float* ret, double* moments, void* stream);
+
 /* compute_bi_level_gae_advantage_return (ragen/trainer/core_algos.py:4-92) without the final whitening. */
 int ragen_bilevel_gae(ragen_ctx* ctx, int B, int T, const float* rewards, const float* values,
                       const uint8_t* loss_mask, double gamma, double lam, double high_level_gamma, float* adv,

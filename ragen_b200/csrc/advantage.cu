@@ -857,6 +857,154 @@ __global__ void __launch_bounds__(96) tile_scan_kernel(int B, int T, const float
   }
 }
 
+// ---- GAE as a parallel scan (ragen_gae_scan) ----------------------------------------------------------------------------------
+// A_t = delta_t + c * A_{t+1} with delta_t = r_t + gamma * V_{t+1} - V_t and c = gamma * lam is a linear recurrence: its solution
+// A_t = sum_{k >= t} c^(k - t) * delta_k can be formed in any order.  A CTA of 256 threads owns a row and takes 2048 tokens of it
+// per step (C5's T = 2047: the whole row at once): the tile comes in with full-line loads, thread i runs the recurrence over
+// ITS 8 consecutive tokens (from shared memory, 9-word pitch: conflict-free), the 256 per-thread totals are combined by a
+// warp-shuffle suffix scan (weights c^8, c^16 ... c^128) and a pass over the 8 warp totals, every thread folds what lies to its
+// right into its 8 values, and the tile leaves through shared memory with full-line stores.  Three barriers per 2048 tokens
+// instead of a dependent chain per token.  CTAs are persistent over rows, so the masked moments (fp64) cost one set of
+// atomics per CTA.  The result differs from the reference's sequential fp32 loop by rounding only (a few ulps of the largest
+// partial sum; north_star's bar is 1e-5) - callers that want the reference's bits take ragen_gae.
+constexpr int BS_T = 256;              // threads
+constexpr int BS_K = 8;                // tokens per thread
+constexpr int BS_CH = BS_T * BS_K;     // tokens per step
+constexpr int BS_PITCH = BS_K + 1;     // words of shared memory per thread
+
+__global__ void __launch_bounds__(BS_T) gae_scan_kernel(int B, int T, const float* __restrict__ rewards,
+                                                      const float* __restrict__ values, const uint8_t* __restrict__ mask,
+                                                      float gamma, float c, float* __restrict__ adv, float* __restrict__ ret,
+                                                      double* moments) {
+  __shared__ float s_r[BS_T * BS_PITCH + 1];
+  __shared__ float s_v[BS_T * BS_PITCH + 1];
+  __shared__ __align__(8) uint8_t s_m[BS_CH];
+  __shared__ float s_w[BS_T / 32];
+  __shared__ float s_carry[2];
+  __shared__ double s_mom[BS_T / 32][3];
+  const unsigned FULL = 0xffffffffu;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  float cp[BS_K + 1];  // c^0 .. c^8
+  cp[0] = 1.0f;
+#pragma unroll
+  for (int k = 1; k <= BS_K; ++k) cp[k] = cp[k - 1] * c;
+  const float w1 = cp[BS_K], w2 = w1 * w1, w4 = w2 * w2, w8 = w4 * w4, w16 = w8 * w8, w32 = w16 * w16;  // (c^8)^(1, 2, 4, 8, 16, 32)
+  float lanew = 1.0f;  // (c^8)^(32 - lane): what a thread's total weighs in for everything right of its warp
+  {
+    float base = w1;
+    int e = 32 - lane;
+    while (e) {
+      if (e & 1) lanew *= base;
+      base *= base;
+      e >>= 1;
+    }
+  }
+  double m0 = 0.0, m1 = 0.0, m2 = 0.0;
+  const int n_chunks = (T + BS_CH - 1) / BS_CH;
+  for (int row = blockIdx.x; row < B; row += gridDim.x) {
+    const float* r = rewards + (size_t)row * T;
+    const float* v = values + (size_t)row * T;
+    const uint8_t* m = mask + (size_t)row * T;
+    float* a_out = adv + (size_t)row * T;
+    float* r_out = ret + (size_t)row * T;
+    float carry = 0.0f;   // A of the first token right of the tile
+    float v_next = 0.0f;  // V of that token (V_T = 0, core_algos.py:100)
+    for (int ch = n_chunks - 1; ch >= 0; --ch) {
+      const int t0 = ch * BS_CH;
+#pragma unroll
+      for (int j = 0; j < BS_K; ++j) {
+        const int g = tid + BS_T * j, t = t0 + g;
+        const bool in = t < T;
+        const int idx = (g >> 3) * BS_PITCH + (g & 7);
+        s_r[idx] = in ? r[t] : 0.0f;
+        s_v[idx] = in ? v[t] : 0.0f;
+        s_m[g] = in ? m[t] : (uint8_t)0;
+      }
+      if (tid == 0) s_v[BS_T * BS_PITCH] = v_next;
+      __syncthreads();
+      const int base = tid * BS_PITCH;
+      float vv[BS_K + 1];
+#pragma unroll
+      for (int k = 0; k < BS_K; ++k) vv[k] = s_v[base + k];
+      vv[BS_K] = s_v[base + BS_PITCH];  // the next thread's first token (the tile's right neighbour for the last thread)
+      float x[BS_K];
+      float acc = 0.0f;
+#pragma unroll
+      for (int k = BS_K - 1; k >= 0; --k) {
+        const bool in = t0 + BS_K * tid + k < T;
+        const float delta = in ? (s_r[base + k] + gamma * vv[k + 1] - vv[k]) : 0.0f;
+        acc = delta + c * acc;
+        x[k] = acc;
+      }
+      // suffix scan of the 256 per-thread totals
+      float P = x[0], y;
+      y = __shfl_down_sync(FULL, P, 1);
+      if (lane + 1 < 32) P += w1 * y;
+      y = __shfl_down_sync(FULL, P, 2);
+      if (lane + 2 < 32) P += w2 * y;
+      y = __shfl_down_sync(FULL, P, 4);
+      if (lane + 4 < 32) P += w4 * y;
+      y = __shfl_down_sync(FULL, P, 8);
+      if (lane + 8 < 32) P += w8 * y;
+      y = __shfl_down_sync(FULL, P, 16);
+      if (lane + 16 < 32) P += w16 * y;
+      if (lane == 0) s_w[warp] = P;
+      __syncthreads();
+      float G = carry;  // A of the first token of the next warp (of the tile to the right for the last warp)
+      for (int w = BS_T / 32 - 1; w > warp; --w) G = s_w[w] + w32 * G;
+      const float S = P + lanew * G;  // A of this thread's first token
+      float In = __shfl_down_sync(FULL, S, 1);
+      if (lane == 31) In = G;
+      const uint2 mm = *reinterpret_cast<const uint2*>(s_m + BS_K * tid);
+#pragma unroll
+      for (int k = 0; k < BS_K; ++k) {
+        const float a = x[k] + cp[BS_K - k] * In;
+        s_r[base + k] = a;  // only this thread reads these words before the barrier below
+        const unsigned mb = ((k < 4 ? mm.x : mm.y) >> (8 * (k & 3))) & 0xffu;
+        if (mb) {
+          m0 += 1.0;
+          m1 += (double)a;
+          m2 += (double)a * (double)a;
+        }
+      }
+      if (tid == 0) {
+        s_carry[0] = S;
+        s_carry[1] = vv[0];
+      }
+      __syncthreads();
+      carry = s_carry[0];
+      v_next = s_carry[1];
+#pragma unroll
+      for (int j = 0; j < BS_K; ++j) {
+        const int g = tid + BS_T * j, t = t0 + g;
+        if (t < T) {
+          const int idx = (g >> 3) * BS_PITCH + (g & 7);
+          const float a = s_r[idx];
+          a_out[t] = a;
+          r_out[t] = a + s_v[idx];  // returns = advantages + values (:107)
+        }
+      }
+      __syncthreads();  // the next tile (or row) overwrites the staging
+    }
+  }
+  if (moments) {
+    m0 = warp_sum(m0);
+    m1 = warp_sum(m1);
+    m2 = warp_sum(m2);
+    if (lane == 0) {
+      s_mom[warp][0] = m0;
+      s_mom[warp][1] = m1;
+      s_mom[warp][2] = m2;
+    }
+    __syncthreads();
+    if (tid < 3) {
+      double acc = 0.0;
+      for (int w = 0; w < BS_T / 32; ++w) acc += s_mom[w][tid];
+      atomicAdd(moments + tid, acc);
+    }
+  }
+}
+
 // below this many rows the per-row kernels finish in a wave or two and win (RAGEN_TS_MIN_ROWS overrides, for probing)
 static int ts_min_rows() {
   static const int v = [] {
@@ -909,6 +1057,21 @@ extern "C" int ragen_gae(ragen_ctx* ctx, int B, int T, const float* rewards, con
     launch_tile_scan<TS_GAE>(ctx, st, B, T, rewards, values, mask, (float)gamma, (float)(gamma * lam), nullptr, adv, ret, moments);
   else
     gae_kernel<<<B, RT, 0, st>>>(B, T, rewards, values, mask, (float)gamma, (float)(gamma * lam), adv, ret, moments);
+  RAGEN_LAUNCHED(ctx);
+  return RAGEN_OK;
+}
+
+extern "C" int ragen_gae_scan(ragen_ctx* ctx, int B, int T, const float* rewards, const float* values, const uint8_t* mask,
+                              double gamma, double lam, float* adv, float* ret, double* moments, void* stream) {
+  RAGEN_REQUIRE(ctx, "ctx is NULL");
+  RAGEN_BT(B, T);
+  RAGEN_REQUIRE(B == 0 || (rewards && values && mask && adv && ret), "NULL pointer argument");
+  DeviceGuard guard(ctx->device);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (moments) RAGEN_CUDA(cudaMemsetAsync(moments, 0, 3 * sizeof(double), st));
+  if (B == 0) return RAGEN_OK;
+  const int cap = ctx->sm_count * 4;  // persistent CTAs: four of 256 threads fit an SM (64 registers per thread)
+  gae_scan_kernel<<<B < cap ? B : cap, BS_T, 0, st>>>(B, T, rewards, values, mask, (float)gamma, (float)(gamma * lam), adv, ret, moments);
   RAGEN_LAUNCHED(ctx);
   return RAGEN_OK;
 }

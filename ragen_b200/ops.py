@@ -24,14 +24,16 @@ def _f32(x):
 
 
 # ---- advantage ---------------------------------------------------------------------------------------------
-def gae_raw(rewards, values, mask, gamma, lam):
-    """Un-whitened GAE + masked moments.  Returns (adv, ret, moments[3] float64)."""
+def gae_raw(rewards, values, mask, gamma, lam, exact=True):
+    """Un-whitened GAE + masked moments.  Returns (adv, ret, moments[3] float64).  exact=True: the reference's sequential
+    fp32 order, bit for bit (ragen_gae); exact=False: the parallel scan (ragen_gae_scan), equal up to rounding (<< 1e-5)."""
     ctx = _ctx(rewards)
     r, v, m = _f32(rewards), _f32(values), _u8(mask).contiguous()
     B, T = r.shape
     adv, ret = torch.empty_like(r), torch.empty_like(r)
     mom = torch.empty(3, dtype=torch.float64, device=r.device)
-    _lib.check(ctx.lib.ragen_gae(ctx.handle, B, T, _lib.ptr(r), _lib.ptr(v), _lib.ptr(m), float(gamma), float(lam),
+    fn = ctx.lib.ragen_gae if exact else ctx.lib.ragen_gae_scan
+    _lib.check(fn(ctx.handle, B, T, _lib.ptr(r), _lib.ptr(v), _lib.ptr(m), float(gamma), float(lam),
                                  _lib.ptr(adv), _lib.ptr(ret), _lib.ptr(mom), ctx.stream()))
     return adv, ret, mom
 

@@ -31,10 +31,19 @@ def _whiten_from(adv, mom, sharded, group):
     return ops.whiten_(adv, mom)
 
 
-def compute_gae_advantage_return(token_level_rewards, values, response_mask, gamma, lam, device=None, sharded=False, group=None):
+SCAN_MIN_ROWS = 4096  # from here on the pass is bandwidth-bound and the parallel scan is the default
+
+
+def compute_gae_advantage_return(token_level_rewards, values, response_mask, gamma, lam, device=None, sharded=False, group=None,
+                                 exact=None):
+    """exact=True: un-whitened advantages and returns carry the reference's bits (its sequential fp32 loop, verl core_algos.py:
+    100-104); exact=False: the recurrence as a parallel scan (ragen_gae_scan), equal up to rounding - a few 1e-7, north_star's
+    bar is 1e-5 - at HBM speed; None: exact below SCAN_MIN_ROWS rows (there the pass is latency-bound either way)."""
     home, dev = token_level_rewards.device, _dev(token_level_rewards, device)
+    if exact is None:
+        exact = token_level_rewards.shape[0] < SCAN_MIN_ROWS
     with torch.no_grad():
-        adv, ret, mom = ops.gae_raw(token_level_rewards.to(dev), values.to(dev), response_mask.to(dev), gamma, lam)
+        adv, ret, mom = ops.gae_raw(token_level_rewards.to(dev), values.to(dev), response_mask.to(dev), gamma, lam, exact=exact)
         adv = _whiten_from(adv, mom, sharded, group)
     return adv.to(home), ret.to(home)
 

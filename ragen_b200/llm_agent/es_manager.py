@@ -43,6 +43,8 @@ class _Block:
         self.K = 1
         self.act = self.nact = None
         self.log = None  # ObsLog of a grid block in text mode: the glyph rows of every turn stay on the device
+        self.stage = None     # pinned + device staging of a turn's actions
+        self.host_obs = None  # glyph rows the last step copied back together with its results
 
 
 class EnvStateManager:
@@ -130,7 +132,12 @@ class EnvStateManager:
             else:
                 packed, dev = False, b.obs
                 table, H, W = fl_glyph_table(envs[0]["env"].GRID_LOOKUP), b.size, b.size
-            host = dev.cpu().numpy()
+            fresh = getattr(block, "host_obs", None)  # the step just brought these rows over with its results
+            block.host_obs = None
+            if fresh is not None and fresh[0] is dev and fresh[1] == packed:
+                host = fresh[2]
+            else:
+                host = dev.cpu().numpy()
             codes = unpack_glyphs(host) if packed else host
             texts = _translate_rows(codes, table)
             if record:
@@ -242,25 +249,45 @@ class EnvStateManager:
         b, dev = block.batch, block.batch.device
         if block.env_type in ("sokoban", "frozen_lake"):
             K = max(block.K, max(len(p[3]) for p in plans), 1)
-            act = np.zeros((block.count, K), dtype=np.uint8)
-            nact = np.zeros(block.count, dtype=np.uint8)
+            n = block.count
+            # actions and per-env action counts travel in ONE pinned staging buffer [n * K | n]: one host->device copy per turn
+            stage = getattr(block, "stage", None)
+            if stage is None or stage[0].numel() != n * (K + 1):
+                pinned = torch.zeros(n * (K + 1), dtype=torch.uint8, pin_memory=True)
+                stage = block.stage = (pinned, torch.empty(n * (K + 1), dtype=torch.uint8, device=dev), K)
+            pinned, d_stage, _ = stage
+            host_stage = pinned.numpy()
+            host_stage[:] = 0
+            act, nact = host_stage[: n * K].reshape(n, K), host_stage[n * K:]
             for env_input, entry, valid, todo in plans:
                 s = self._pos[entry["env_id"]] - block.first
                 codes = [entry["env"].action_map[a] + 1 for a in todo] if block.env_type == "frozen_lake" else todo
                 act[s, :len(codes)] = codes
                 nact[s] = len(codes)
+            d_stage.copy_(pinned, non_blocking=True)
+            d_act, d_nact = d_stage[: n * K].view(n, K), d_stage[n * K:]
             kw = {}
             if block.env_type == "sokoban":
                 text = self.envs[block.first]["env"].render_mode == "text"
                 kw = {"packed": b.can_pack and text, "render": text}
-            out = b.step(torch.from_numpy(act).to(dev), torch.from_numpy(nact).to(dev), **kw)
-            host = torch.stack([out.done, out.flags, out.n_executed]).cpu().numpy()
-            rew = out.reward.cpu().numpy()
+            out = b.step(d_act, d_nact, **kw)
+            if block.env_type == "sokoban" and kw["render"] and kw["packed"]:
+                # reward / done / flags / n_executed and the nibble glyph rows are neighbours in the batch's result slab:
+                # ONE device->host copy brings the whole turn back (the texts below are built from this copy)
+                slab = b._slab[b._off_sc: b._slab_bytes].cpu().numpy()
+                rew = slab[: 8 * n].view(np.float64)
+                done_h, flags_h, nexec_h = slab[8 * n: 9 * n], slab[9 * n: 10 * n], slab[10 * n: 11 * n]
+                block.host_obs = (b.obs_packed, True, slab[b._off_obs - b._off_sc:].reshape(n, -1))
+            else:
+                host = torch.stack([out.done, out.flags, out.n_executed]).cpu().numpy()
+                done_h, flags_h, nexec_h = host[0], host[1], host[2]
+                rew = out.reward.cpu().numpy()
+                block.host_obs = None
             for i, (env_input, entry, valid, todo) in zip(idxs, plans):
                 s = self._pos[entry["env_id"]] - block.first
-                n_exec, fl = int(host[2, s]), int(host[1, s])
+                n_exec, fl = int(nexec_h[s]), int(flags_h[s])
                 info = {"action_is_effective": bool(fl & 1), "action_is_valid": True, "success": bool(fl & 2)} if n_exec else {}
-                results[i] = (float(rew[s]) if n_exec else 0, info, bool(host[0, s]), n_exec)
+                results[i] = (float(rew[s]) if n_exec else 0, info, bool(done_h[s]), n_exec)
         elif block.env_type == "bandit":
             act = np.zeros(block.count, dtype=np.uint8)
             on = np.zeros(block.count, dtype=np.uint8)

@@ -12,12 +12,12 @@ def assemble_response(raw: bytes, scratch: bytes, flags: int, spans, act_spans, 
         return raw.decode("utf-8", "replace"), []
     abuf = scratch if flags & F_ANSWER_SCRATCH else raw
     tbuf = scratch if flags & F_THINK_SCRATCH else raw
-    actions = [bytes(abuf[int(s):int(s) + int(n)]).decode("utf-8", "replace") for s, n in list(act_spans)[:kept]]
+    actions = [abuf[s:s + n].decode("utf-8", "replace") for s, n in act_spans[:kept]]
     if flags & F_TRUNCATED:
         answer = (" " + sep + " ").join(actions)
     else:
-        answer = bytes(abuf[int(spans[2]):int(spans[2]) + int(spans[3])]).decode("utf-8", "replace")
+        answer = abuf[spans[2]:spans[2] + spans[3]].decode("utf-8", "replace")
     if enable_think:
-        think = bytes(tbuf[int(spans[0]):int(spans[0]) + int(spans[1])]).decode("utf-8", "replace")
+        think = tbuf[spans[0]:spans[0] + spans[1]].decode("utf-8", "replace")
         return f"<think>{think}</think><answer>{answer}</answer>", actions
     return f"<answer>{answer}</answer>", actions

@@ -283,12 +283,15 @@ class ParseResult:
             nv = self.n_valid.cpu().numpy()
         need_scratch = bool((fl & 6).any())
         scr = self.scratch.cpu().numpy().tobytes() if need_scratch else b""
+        # plain Python ints from here on: per-element numpy scalar arithmetic would dominate this loop
+        offs, fl_l, sp_l, asp_l = self.offsets_np.tolist(), fl.tolist(), sp.tolist(), asp.tolist()
+        kept_l, nv_l, codes_l = kept.tolist(), nv.tolist(), codes.tolist()
+        raw, think, sep = self.raw, self.enable_think, self.sep
         out = []
-        for i in range(len(fl)):
-            a, b = int(self.offsets_np[i]), int(self.offsets_np[i + 1])
-            resp, actions = assemble_response(self.raw[a:b], scr[a:b] if need_scratch else b"", int(fl[i]), sp[i], asp[i],
-                                              int(kept[i]), self.enable_think, self.sep)
-            out.append((resp, actions, codes[i, :nv[i]].tolist()))
+        for i in range(len(fl_l)):
+            a, b = offs[i], offs[i + 1]
+            resp, actions = assemble_response(raw[a:b], scr[a:b] if need_scratch else b"", fl_l[i], sp_l[i], asp_l[i], kept_l[i], think, sep)
+            out.append((resp, actions, codes_l[i][:nv_l[i]]))
         return out
 
 

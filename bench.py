@@ -455,6 +455,35 @@ def run_native(args):
                           "two steps in flight; decode_delta / HostMirror rebuild rewards, flags and glyph rows on the host on demand",
                    "full_rows": e2e_rows}
 
+        if compact:
+            # (3) the same step with the observations as TEXT in host memory: the three-bit rows the step wrote are rendered to
+            # UTF-8 strings on the device (ragen_glyph_utf8; fixed-width NUL-padded rows, one numpy 'S' view away from Python
+            # bytes objects) and those travel instead of the codes
+            from ragen_b200.env.sokoban import glyph_table  # noqa: F401
+
+            lookup = {0: "#", 1: "_", 2: "O", 3: "√", 4: "X", 5: "P", 6: "S"}  # ragen/env/sokoban/config.py:10
+            text_bufs = [b_.text_rows(lookup, fmt=3) for b_ in batches]
+            stride = int(text_bufs[0][0].shape[1])
+            pinned_text = [torch.empty((n, stride), dtype=torch.uint8, pin_memory=True) for _ in batches]
+            pinned_len = [torch.empty(n, dtype=torch.int32, pin_memory=True) for _ in batches]
+
+            def text_step(i):
+                b_ = batches[i & 1]
+                d_act = host_actions[i % RA].to(dev, non_blocking=True).unsqueeze(1)
+                b_.step(d_act, packed=3)
+                rows_d, lens_d = b_.text_rows(lookup, out=text_bufs[i & 1], fmt=3)
+                pinned_text[i & 1].copy_(rows_d, non_blocking=True)
+                pinned_len[i & 1].copy_(lens_d, non_blocking=True)
+                h = b_._pin("slab_sc", (11 * n,), torch.uint8)
+                h.copy_(b_._slab[b_._off_sc: b_._off_sc + 11 * n], non_blocking=True)
+                torch.cuda.current_stream(dev).synchronize()
+
+            text_s = timed(text_step, e2e_steps)
+            e2e["text"] = {"value": n * world * e2e_steps / text_s, "unit": UNIT, "h2d_bytes_per_step": n * 1,
+                           "d2h_bytes_per_step": n * (stride + 4 + 11), "ms_per_step": 1e3 * text_s / e2e_steps,
+                           "api": "SokobanBatch.step (compact) + text_rows -> ragen_glyph_utf8 (C ABI): observations as UTF-8 text rows "
+                                  "(%d B per env, the reference's glyphs) + lengths + reward / done / flags in pinned host memory" % stride}
+
     reset = None
     if not args.no_reset:
         reset = _reset_leg(args, rank, world, local_rank, barrier, dist, torch, np)

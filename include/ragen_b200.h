@@ -278,6 +278,14 @@ int ragen_traj_assemble(ragen_ctx* ctx, int B, int L, const int32_t* pool, int64
 int ragen_glyph_tokens(ragen_ctx* ctx, int64_t n, int G, int packed, const uint8_t* codes, int64_t pitch, const int32_t* table,
                        const int32_t* table_len, int stride, int32_t* tokens, int32_t* n_tokens, void* stream);
 
+/* The same render into UTF-8 TEXT (SokobanEnv.render's string, sokoban/env.py:53-57): [host] table int32 [8][4] / table_len hold
+ * the 0..4 UTF-8 bytes of each glyph ("√" is three), text uint8 [n][stride] receives env i's string NUL-padded to the stride
+ * (a numpy 'S<stride>' view of it is an array of byte strings), n_bytes (may be NULL) its length.  format: 0 / 1 as `packed`
+ * above, 3 = the three-bit rows of ragen_sokoban_step_packed3 / _compact (row-major cells, no separators; W = room width, pitch
+ * >= the row's even byte count).  The last separator is rendered as "\n" too; the reference string has none (drop one byte). */
+int ragen_glyph_utf8(ragen_ctx* ctx, int64_t n, int G, int format, int W, const uint8_t* codes, int64_t pitch, const int32_t* table,
+                     const int32_t* table_len, int stride, uint8_t* text, int32_t* n_bytes, void* stream);
+
 /* _normalize_score_tensor (ctx_manager.py:175-226) on the last score column: out = score_last + penalty, then,
  * when n_groups < B, per group (dense ids 0..n_groups-1): method 0 identity, 1 mean, 2 mean_std, 3 asym_clip. */
 int ragen_group_norm(ragen_ctx* ctx, int B, const float* score_last, const float* penalty, const int32_t* group,

@@ -46,6 +46,7 @@ SIGNATURES = {
     "ragen_masks_scores": [_P, _I, _I, _P, _L, _L, _I, _I, _I, _P, _P, _I, _P, _P, _P, _P],
     "ragen_traj_assemble": [_P, _I, _I, _P, _L, _P, _P, _P, _P, _P, _L, _P, _P, _P, _P],
     "ragen_glyph_tokens": [_P, _L, _I, _I, _P, _L, _P, _P, _I, _P, _P, _P],
+    "ragen_glyph_utf8": [_P, _L, _I, _I, _I, _P, _L, _P, _P, _I, _P, _P, _P],
     "ragen_group_norm": [_P, _I, _P, _P, _P, _I, _I, _P, _P],
     "ragen_group_norm_stats": [_P, _I, _P, _P, _P, _I, _P, _P, _P],
     "ragen_group_norm_apply": [_P, _I, _P, _P, _I, _P, _I, _P],

@@ -441,6 +441,35 @@ class SokobanBatch:
         self.obs_stale = True
         return buf
 
+    def text_rows(self, grid_lookup, out=None, fmt=None):
+        """The latest render as UTF-8 TEXT on the device (ragen_glyph_utf8): uint8 [n, stride] NUL-padded rows (the env's string
+        plus a final newline) and int32 [n] lengths.  `np.asarray(rows.cpu()).view(f"S{stride}")` is an array of byte strings."""
+        fmt = self.obs_is_packed if fmt is None else fmt
+        fmt = 3 if (fmt == 3 and fmt is not True) else (1 if fmt else 0)
+        src = self._packed3_buffer() if fmt == 3 else self._packed_buffer() if fmt == 1 else self.obs
+        G = self.H * (self.W + 1)
+        tab = np.zeros((8, 4), dtype=np.int32)
+        ln = np.zeros(8, dtype=np.int32)
+        for c, g in enumerate(glyph_table(grid_lookup)):
+            b = g.encode("utf-8")
+            if len(b) > 4:
+                raise ValueError(f"glyph {g!r} is longer than 4 UTF-8 bytes")
+            tab[c, : len(b)] = list(b)
+            ln[c] = len(b)
+        worst = int(ln.max())
+        if int(np.delete(ln, 3).max()) <= 1:  # only "box on target" is multi-byte (the default vocabulary): at most num_boxes of them
+            stride = G + (int(ln[3]) - 1) * self.num_boxes
+        else:
+            stride = G * worst
+        stride = (stride + 3) & ~3
+        if out is None:
+            out = (torch.empty((self.n, stride), dtype=torch.uint8, device=self.device),
+                   torch.empty(self.n, dtype=torch.int32, device=self.device))
+        _lib.check(self.lib.ragen_glyph_utf8(self.ctx.handle, self.n, G, fmt, self.W, _lib.ptr(src), int(src.shape[1]),
+                                             tab.ctypes.data_as(_lib._P), ln.ctypes.data_as(_lib._P), int(out[0].shape[1]),
+                                             _lib.ptr(out[0]), _lib.ptr(out[1]), self.ctx.stream()))
+        return out
+
     def host_mirror(self):
         """A HostMirror of the batch's current rooms (one device->host copy of state and fixed)."""
         return HostMirror(self.fixed.cpu().numpy(), self.state.cpu().numpy(), self.H, self.W)

@@ -533,6 +533,36 @@ def test_pipelined_host_steps_equal_the_plain_ones():
         assert torch.equal(a.state, t.state)
 
 
+@pytest.mark.parametrize("compact", [False, True])
+def test_text_rows_rendered_on_the_device_are_the_reference_strings(compact):
+    """ragen_glyph_utf8: the env's text observation as UTF-8 bytes written by the device, from byte, nibble and three-bit glyph
+    rows; multi-byte glyphs ("√", and a custom vocabulary) included."""
+    from ragen_b200.env.sokoban import SokobanBatch
+
+    n, H, W, nb = 777, 6, 6, 2
+    fixed, state = synthetic_rooms(n, H, W, nb, seed=31)
+    rng = np.random.default_rng(32)
+    b = SokobanBatch(n, (H, W), nb, 100, compact=compact)
+    b.load_rooms(fixed, state)
+    o = SokobanBatchOracle(fixed, state, H, W, nb, 100)
+    lookups = [S.DEFAULT_GLYPHS, {0: "█", 1: ".", 2: "◎", 3: "√", 4: "□", 5: "@", 6: "é"}]
+    for turn in range(8):
+        acts = rng.integers(1, 5, (n, 3)).astype(np.uint8)
+        o.step_turn(acts)
+        fmts = [3] if compact else [False, True, 3]
+        fmt = fmts[turn % len(fmts)]
+        b.step(torch.from_numpy(acts).cuda(), packed=fmt)
+        for lk in lookups:
+            rows, lens = b.text_rows(lk)
+            host = rows.cpu().numpy()
+            got = [bytes(r[:k]).decode("utf-8") for r, k in zip(host, lens.cpu().numpy())]
+            tab = [lk.get(i, "?") for i in range(7)] + ["\n"]
+            want = ["".join(tab[c] for c in g) for g in o.glyphs()]
+            assert got == want, (turn, fmt)
+            as_strings = host.view(f"S{host.shape[1]}").reshape(-1)  # NUL padding: a fixed-width bytes array
+            assert as_strings[5].decode("utf-8") == want[5]
+
+
 def test_compact_rooms_refuse_other_shapes():
     from ragen_b200 import _lib
     from ragen_b200.env.sokoban import SokobanBatch

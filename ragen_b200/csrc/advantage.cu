@@ -317,7 +317,8 @@ __global__ void whiten_kernel(int64_t n, float* __restrict__ x, const double* __
   double var = (S2 - 2.0 * mean * S1 + mean * mean * S0) / (S0 + 1e-8);
   var = var * (S0 / (S0 - 1.0));
   const float meanf = (float)mean;
-  const float scale = (float)(1.0 / sqrt(var + 1e-8));
+  // fewer than two mask tokens: masked_var raises in the reference; here every output is NaN so that the misuse shows
+  const float scale = (S0 > 1.0) ? (float)(1.0 / sqrt(var + 1e-8)) : __int_as_float(0x7fc00000);
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if ((reinterpret_cast<uintptr_t>(x) & 15) == 0) {  // 128-bit accesses, two in flight per thread
@@ -510,7 +511,8 @@ __global__ void whiten_masked_kernel(int64_t n, const float* __restrict__ x, con
   double var = (S2 - 2.0 * mean * S1 + mean * mean * S0) / (S0 + 1e-8);
   var = var * (S0 / (S0 - 1.0));
   const float meanf = (float)mean;
-  const float scale = (float)(1.0 / sqrt(var + 1e-8));
+  // fewer than two mask tokens: masked_var raises in the reference; here every output is NaN so that the misuse shows
+  const float scale = (S0 > 1.0) ? (float)(1.0 / sqrt(var + 1e-8)) : __int_as_float(0x7fc00000);
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   auto one = [&](float xv, uint8_t m) {
@@ -639,7 +641,7 @@ __global__ void __launch_bounds__(96) tile_scan_kernel(int B, int T, const float
   const int row0 = blockIdx.x * RPW;
   const int nrows = min(RPW, B - row0);
   const int ntiles = (T + 31) >> 5;
-  const uintptr_t mask_end = (uintptr_t)(mask + (size_t)B * T);
+  const uintptr_t mask_begin = (uintptr_t)mask, mask_end = (uintptr_t)(mask + (size_t)B * T);
 
   // Three warps share a row group.  Step i (tile ntiles-1-i, ring slot i & 3):
   //   warp 0 ("scan")   runs the recurrences of tile i, lane = row;
@@ -664,7 +666,12 @@ __global__ void __launch_bounds__(96) tile_scan_kernel(int B, int T, const float
       }
       if (lane < 9) {
         const uintptr_t w = (((uintptr_t)mp) & ~(uintptr_t)3) + 4u * lane;
-        if (w < mask_end) cp_async4(&S.m[r * TS_MS + 4 * lane], reinterpret_cast<const void*>(w));
+        if (w >= mask_begin && w + 4 <= mask_end) {
+          cp_async4(&S.m[r * TS_MS + 4 * lane], reinterpret_cast<const void*>(w));
+        } else if (w < mask_end && w + 4 > mask_begin) {  // a word that straddles either end of the mask tensor: only its bytes that exist
+          for (int b = 0; b < 4; ++b)
+            if (w + b >= mask_begin && w + b < mask_end) S.m[r * TS_MS + 4 * lane + b] = *reinterpret_cast<const uint8_t*>(w + b);
+        }
       }
       vp += T;
       rp += T;
@@ -1112,6 +1119,9 @@ extern "C" int ragen_masked_moments(ragen_ctx* ctx, int64_t n, const float* x, c
   return RAGEN_OK;
 }
 
+// moments live on the device (they may just have come out of an all-reduce), so the two ValueErrors of masked_var (sum of the mask
+// 0 or 1, torch_functional.py:128-136) cannot be raised here without a synchronisation: that check is the caller's
+// (ops.whiten_(check=True) reads the 24 bytes back and raises them); the kernel itself writes NaN for such moments.
 extern "C" int ragen_whiten(ragen_ctx* ctx, int64_t n, float* x, const double* moments, void* stream) {
   RAGEN_REQUIRE(ctx, "ctx is NULL");
   RAGEN_REQUIRE(n >= 0 && moments && (n == 0 || x), "bad argument");

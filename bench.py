@@ -60,23 +60,37 @@ def parse_args():
     ap.add_argument("--obs", default="packed3", choices=["packed3", "packed", "bytes"],
                     help="glyph-row format of the render: three bits per cell without separators (packed3), two 4-bit codes per byte "
                          "(packed, what the managers consume) or one code per byte (bytes)")
-    ap.add_argument("--rooms", default="nibbles", choices=["nibbles", "bytes"],
-                    help="how the rooms rest in HBM: one cell per byte, or two (ragen_sokoban_step_compact; needs --obs packed3)")
+    ap.add_argument("--rooms", default="glyph3", choices=["glyph3", "nibbles", "bytes"],
+                    help="how the rooms rest in HBM: one cell per byte, two (ragen_sokoban_step_compact), or as three-bit glyph codes that "
+                         "are their own rendered observation (ragen_sokoban_step_glyph3); the last two need --obs packed3")
     ap.add_argument("--rows", action="store_true", help="per-kernel lines for every SURVEY.md 8(d) config instead of the contract line")
     ap.add_argument("--quick", action="store_true", help="with --rows: smaller batches")
     ap.add_argument("--only", default="", help="with --rows: comma list of sokoban,generator,frozenlake,parse,c5,manager,rollout")
     return ap.parse_args()
 
 
+def line_bytes_per_env(obs, rooms):
+    """Bytes of distinct cache lines one launch touches per env: room, 8-byte record, action, results, separate glyph rows."""
+    return {"nibbles": 50, "bytes": 100, "glyph3": 38}[rooms] + 8 + 1 + 11 + (0 if rooms == "glyph3" else {"packed3": 38, "packed": 55, "bytes": 110}[obs])
+
+
+def resident_batches(envs_per_gpu, obs, rooms):
+    """How many batches are stepped in rotation so that the lines between two touches of a line exceed the 126 MB L2 by 1.6x."""
+    per_batch = envs_per_gpu * line_bytes_per_env(obs, rooms)
+    need = -(-int(1.6 * 126 * (1 << 20)) // max(per_batch, 1))
+    return max(2, min(need + (need & 1), 16))  # even, so that graph capture and the pipelined legs pair up
+
+
 def workload_config(n_gpus, envs_per_gpu, obs="packed", rooms="bytes", launches_per_step=128):
     rows = {"packed3": "three bits per cell, no separators (38 B per env; ragen_sokoban_step_packed3)",
             "packed": "two 4-bit glyph codes per byte (55 B per env)", "bytes": "one glyph code per byte (110 B per env)"}[obs]
-    return {"glyph_rows": rows, "rooms_in_hbm": "two cells per byte (ragen_sokoban_step_compact)" if rooms == "nibbles" else "one cell per byte",
+    return {"glyph_rows": rows, "rooms_in_hbm": {"nibbles": "two cells per byte (ragen_sokoban_step_compact)", "bytes": "one cell per byte",
+                                                "glyph3": "three-bit glyph codes, the room is its own rendered observation (ragen_sokoban_step_glyph3)"}[rooms],
             "workload": "sokoban_10x10_2box_step_render_reward", "dim_room": [H, W], "num_boxes": NUM_BOXES,
             "max_steps": MAX_STEPS, "envs_per_gpu": envs_per_gpu, "envs_total": envs_per_gpu * n_gpus,
             "actions_per_launch": 1, "launches_per_step": launches_per_step, "env_steps_per_step": envs_per_gpu * n_gpus * launches_per_step,
             "rooms": "synthetic random-walk rooms (ragen_b200/synth.py)",
-            "actions": "uniform 1..4", "l2": "inputs larger than L2: two batches of envs_per_gpu envs stepped alternately, %d MB of distinct lines between two touches of a line (L2 is 126 MB)" % ((envs_per_gpu * 2 * ((50 if rooms == "nibbles" else 100) + 8 + 1 + 11 + {"packed3": 38, "packed": 55, "bytes": 110}[obs])) >> 20),
+            "actions": "uniform 1..4", "l2": "inputs larger than L2: %d batches of envs_per_gpu envs stepped in rotation, %d MB of distinct lines between two touches of a line (L2 is 126 MB)" % (resident_batches(envs_per_gpu, obs, rooms), (envs_per_gpu * resident_batches(envs_per_gpu, obs, rooms) * line_bytes_per_env(obs, rooms)) >> 20),
             "parallelism": f"env-sharded x{n_gpus}"}
 
 
@@ -326,16 +340,18 @@ def run_native(args):
 
     n = args.envs
     fixed, state = synthetic_rooms(n, H, W, NUM_BOXES, seed=4 + rank)
-    compact = args.rooms == "nibbles"
+    glyph = args.rooms == "glyph3"
+    compact = args.rooms == "nibbles" or glyph  # both step packed rooms and report three-bit rows / deltas
     if compact and args.obs != "packed3":
-        raise SystemExit("--rooms nibbles renders three-bit rows: use --obs packed3")
-    # Two batches of n envs each, stepped alternately: with the rooms as nibbles ONE batch's lines (rooms 52 MB, records 8 MB, rows
-    # 40 MB, results 12 MB) would fit the 126 MB L2, so between two touches of a line the other batch's ~113 MB go through it.
+        raise SystemExit("--rooms nibbles / glyph3 work with three-bit rows: use --obs packed3")
+    # Several batches of n envs each, stepped in rotation: ONE batch's lines (58 MB with glyph rooms, 108 MB with nibble rooms) would
+    # fit the 126 MB L2, so between two touches of a line the other batches' lines (>= 1.6 x L2 in all) go through it.
+    NBATCH = resident_batches(n, args.obs, args.rooms)
     batches = []
-    for j in range(2):
+    for j in range(NBATCH):
         if j:
-            fixed, state = synthetic_rooms(n, H, W, NUM_BOXES, seed=1004 + rank)
-        b_ = SokobanBatch(n, (H, W), NUM_BOXES, MAX_STEPS, device=local_rank, compact=compact)
+            fixed, state = synthetic_rooms(n, H, W, NUM_BOXES, seed=1004 + 17 * j + rank)
+        b_ = SokobanBatch(n, (H, W), NUM_BOXES, MAX_STEPS, device=local_rank, rooms=args.rooms)
         b_.load_rooms(fixed, state)
         batches.append(b_)
     batch = batches[0]
@@ -360,12 +376,12 @@ def run_native(args):
 
     def one_step(first):
         for i in range(R):
-            batches[(first + i) & 1].step(actions[(first + i) % RA], packed=packed)
+            batches[(first + i) % NBATCH].step(actions[(first + i) % RA], packed=packed)
 
     one_step(0)  # module load, cudaFuncSetAttribute: before any capture
     torch.cuda.synchronize()
     launch_mode, graph = "loop", None
-    if not args.no_graph and R % 2 == 0 and R % RA == 0:
+    if not args.no_graph and R % NBATCH == 0 and R % RA == 0:
         try:
             side = torch.cuda.Stream(dev)
             side.wait_stream(torch.cuda.current_stream(dev))
@@ -407,7 +423,7 @@ def run_native(args):
     e2e = None
     if not args.no_e2e:
         e2e_steps = max(args.steps, 20)
-        api_tail = "_compact" if compact else {"packed3": "_packed3", "packed": "_packed", "bytes": ""}[args.obs]
+        api_tail = "_glyph3" if glyph else "_compact" if compact else {"packed3": "_packed3", "packed": "_packed", "bytes": ""}[args.obs]
 
         def timed(fn, steps):
             for i in range(max(args.warmup, 3)):
@@ -450,7 +466,7 @@ def run_native(args):
             delta_s = run_pipelined(e2e_steps)
             e2e = {"value": n * world * e2e_steps / delta_s, "unit": UNIT, "h2d_bytes_per_step": n * 1, "d2h_bytes_per_step": n * 4,
                    "ms_per_step": 1e3 * delta_s / e2e_steps, "host_numa": numa,
-                   "api": "SokobanBatch.step_host_begin/_end -> ragen_sokoban_step_delta (C ABI): pinned host actions up, 4-byte step "
+                   "api": "SokobanBatch.step_host_begin/_end -> ragen_sokoban_step_%s (C ABI): pinned host actions up, 4-byte step " % ("glyph3 with delta records" if glyph else "delta") +
                           "deltas down (player cell before / after, box destination, reward code + done / effective / success bits), "
                           "two steps in flight; decode_delta / HostMirror rebuild rewards, flags and glyph rows on the host on demand",
                    "full_rows": e2e_rows}
@@ -495,8 +511,10 @@ def run_native(args):
             peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
         else:
             peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
-        kname = "sokoban_tile_kernel<10,10,false,%d>" % (3 if compact else {"packed3": 2, "packed": 1, "bytes": 0}[args.obs])
+        kname = "sokoban_tile_kernel<10,10,false,%d>" % (4 if glyph else 3 if compact else {"packed3": 2, "packed": 1, "bytes": 0}[args.obs])
         moved = MOVED_PER_STEP - G + row_bytes - (H * W if compact else 0)
+        if glyph:
+            moved = 2 * row_bytes + 2 * 8 + 1 + 11  # glyph room in and out (it is the observation), record r+w, action, results
         achieved = moved * n / (kern_ms * 1e-3) / 1e9
         traffic, traffic_src = None, None
         tpath = os.path.join(ROOT, "profiles", TRAFFIC_FILE)
@@ -513,9 +531,9 @@ def run_native(args):
                              "traffic": traffic, "traffic_source": traffic_src, "kernel": kname, "kernel_ms": kern_ms,
                              "bytes_per_env_step": moved, "peak_source": peak_src,
                              "frac_survey_431B": BYTES_PER_STEP * n / (kern_ms * 1e-3) / 1e9 / peak,
-                             "note": "achieved / frac count the bytes this kernel has to move per env-step (rooms r+w as nibbles 100, "
-                                     "8-byte record r+w 16, action 1, results 11, three-bit rows 38 = 166 with the defaults; 266 / 283 / 338 B "
-                                     "with byte rooms and three-bit / nibble / byte rows).  frac_survey_431B applies SURVEY.md 8(d)'s figure, "
+                             "note": "achieved / frac count the bytes this kernel has to move per env-step (glyph rooms: room in and out 76 - the room is the "
+                                     "observation - record r+w 16, action 1, results 11 = 104; nibble rooms: 100 + 16 + 1 + 11 + three-bit rows 38 = 166; 266 / 283 / "
+                                     "338 B with byte rooms and three-bit / nibble / byte rows).  frac_survey_431B applies SURVEY.md 8(d)'s figure, "
                                      "which charges a 100 B room_fixed read and 110 B of glyph bytes this kernel does not move: it is "
                                      "not a physical fraction"}}
         if reset is not None:

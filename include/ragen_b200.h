@@ -119,6 +119,16 @@ int ragen_sokoban_step_compact(ragen_ctx* ctx, int64_t n, int H, int W, int num_
 int ragen_sokoban_step_delta(ragen_ctx* ctx, int64_t n, int H, int W, int num_boxes, int max_steps,
                              const uint8_t* actions, int K, const uint8_t* n_actions,
                              uint8_t* state4, int16_t* meta, uint8_t* delta, void* stream);
+/* The step on GLYPH ROOMS: state3 [n][((3*H*W + 15) / 16) * 2] holds every room as three-bit glyph codes (0..5 as room_state, 6 =
+ * the player on a target; the layout of obs_packed3 above), so the room IS its rendered observation (SokobanEnv.render,
+ * sokoban/env.py:53-57: where(state == 5 & fixed == 2, 6, state)): a step reads and writes 38 B per 10x10 env and nothing is
+ * left to render.  room_state = the codes with 6 read as 5.  Results as ragen_sokoban_step, or - delta != NULL - as the 4-byte
+ * records of ragen_sokoban_step_delta (the result arrays may then be NULL).  ragen_sokoban_adopt_slots writes state3.  6x6, 8x8, 10x10. */
+int ragen_sokoban_step_glyph3(ragen_ctx* ctx, int64_t n, int H, int W, int num_boxes, int max_steps,
+                              const uint8_t* actions, int K, const uint8_t* n_actions,
+                              uint8_t* state3, int16_t* meta,
+                              double* acc_reward, uint8_t* done, uint8_t* flags, uint8_t* n_executed,
+                              uint8_t* delta, void* stream);
 int ragen_sokoban_render_packed3(ragen_ctx* ctx, int64_t n, int H, int W, const uint8_t* state,
                                  const int16_t* meta, uint8_t* obs_packed3, void* stream);
 
@@ -145,10 +155,11 @@ int ragen_sokoban_adopt(ragen_ctx* ctx, int64_t n, int H, int W, int num_boxes, 
 /* The same for a SUBSET of a shared batch (BaseEnv.reset on one env of a manager-owned batch, ragen/env/base.py:16,
  * es_manager.py:93-95): env i is adopted only when only[i] != 0 (only NULL = all); the others keep their record
  * (num_env_steps, stored box count) and their status entry.  state4 (may be NULL) [n][H*W/2] receives the adopted rooms
- * as nibbles, the form ragen_sokoban_step_compact steps (H*W even). */
+ * as nibbles, the form ragen_sokoban_step_compact steps (H*W even); state3 (may be NULL) as three-bit glyph codes
+ * (ragen_sokoban_step_glyph3). */
 int ragen_sokoban_adopt_slots(ragen_ctx* ctx, int64_t n, int H, int W, int num_boxes, const uint8_t* state,
                               const uint8_t* fixed, int16_t* meta, int32_t* status, const uint8_t* only,
-                              uint8_t* state4, void* stream);
+                              uint8_t* state4, uint8_t* state3, void* stream);
 
 /* SokobanEnv.reset(seed) -> generate_room (ragen/env/sokoban/env.py:28-42, ragen/env/sokoban/utils.py:221-278 with
  * room_topology_generation :281-355, place_boxes_and_player :358-397, reverse_playing / depth_first_search /

@@ -289,7 +289,9 @@ template <int CH, int CW, bool RENDER_ONLY, int PACK>
 __global__ void __launch_bounds__(TE) sokoban_tile_kernel(const StepParams p) {
   // PACK 3 = "compact": three-bit rows out AND rooms kept as nibbles in HBM (p.state is then uint8 [n][H*W/2]); the tile is
   // staged, stepped and rendered in that form
-  constexpr bool PACKED = (PACK == 1), PACK3 = (PACK == 2 || PACK == 3), STATE4 = (PACK == 3);
+  // PACK 4 = "glyph rooms": the rooms rest in HBM as THREE-BIT GLYPH CODES (0..5 as room_state, 6 = player on a target) - the room
+  // IS its own rendered observation, so a step reads and writes 38 B per 10x10 env and there is nothing left to render
+  constexpr bool PACKED = (PACK == 1), PACK3 = (PACK == 2 || PACK == 3), STATE4 = (PACK == 3), STATE3 = (PACK == 4);
   const int H = CH ? CH : p.H, W = CW ? CW : p.W;
   const int HW = H * W, G = H * (W + 1);
   const int B3 = ((HW * 3 + 15) / 16) * 2;  // bytes of a three-bit row stream
@@ -297,15 +299,15 @@ __global__ void __launch_bounds__(TE) sokoban_tile_kernel(const StepParams p) {
   __shared__ __align__(8) uint64_t bar;
 
   uint8_t* s_state = smem;
-  uint8_t* s_obs = s_state + round16(STATE4 ? (TE * HW) >> 1 : TE * HW) + 16;  // +16: the render window may read one word past the tile
+  uint8_t* s_obs = s_state + round16(STATE3 ? TE * B3 : STATE4 ? (TE * HW) >> 1 : TE * HW) + 16;  // +16: the render window may read one word past the tile
 
   const int64_t env0 = (int64_t)blockIdx.x * TE;
   const int cnt = (int)min((int64_t)TE, p.n - env0);
-  const int room_bytes = STATE4 ? (cnt * HW) >> 1 : cnt * HW;  // bytes of the tile in HBM
+  const int room_bytes = STATE3 ? cnt * B3 : STATE4 ? (cnt * HW) >> 1 : cnt * HW;  // bytes of the tile in HBM
   const int obs_bytes = PACK3 ? cnt * B3 : PACKED ? (cnt * G) >> 1 : cnt * G;  // PACKED needs an even G (checked at launch)
   const bool bulk_rooms = (room_bytes & 15) == 0;
   const bool bulk_obs = (obs_bytes & 15) == 0;
-  uint8_t* g_state = p.state + (STATE4 ? (env0 * HW) >> 1 : env0 * HW);
+  uint8_t* g_state = p.state + (STATE3 ? env0 * B3 : STATE4 ? (env0 * HW) >> 1 : env0 * HW);
 
   // ---- stage the tile: HBM -> shared memory -------------------------------------------------
   if (bulk_rooms) {
@@ -347,11 +349,30 @@ __global__ void __launch_bounds__(TE) sokoban_tile_kernel(const StepParams p) {
   int pos = m.player;
   int under = m.under;
   if (!RENDER_ONLY && mine) {
-    uint8_t* S = s_state + (STATE4 ? (e * HW) >> 1 : e * HW);
-    // cell i of the own room: a byte, or (STATE4) nibble i&1 of byte i>>1 - rooms are whole bytes, nobody else touches them
-    auto cell = [&](int i) -> int { return STATE4 ? (S[i >> 1] >> ((i & 1) << 2)) & 15 : S[i]; };
+    uint8_t* S = s_state + (STATE3 ? e * B3 : STATE4 ? (e * HW) >> 1 : e * HW);
+    // cell i of the own room: a byte, or (STATE4) nibble i&1 of byte i>>1, or (STATE3) bits 3i..3i+2 - rooms are whole bytes,
+    // nobody else touches them (a three-bit cell straddles into the next byte only inside its own room)
+    auto cell = [&](int i) -> int {
+      if (STATE3) {
+        const int bit = 3 * i, b = bit >> 3, sh = bit & 7;
+        unsigned w = S[b];
+        if (sh > 5) w |= (unsigned)S[b + 1] << 8;
+        return (w >> sh) & 7;
+      }
+      return STATE4 ? (S[i >> 1] >> ((i & 1) << 2)) & 15 : S[i];
+    };
     auto put = [&](int i, int v) {
-      if (STATE4) {
+      if (STATE3) {
+        const int bit = 3 * i, b = bit >> 3, sh = bit & 7;
+        if (sh <= 5) {
+          S[b] = (uint8_t)((S[b] & ~(7u << sh)) | ((unsigned)v << sh));
+        } else {
+          unsigned w = (unsigned)S[b] | ((unsigned)S[b + 1] << 8);
+          w = (w & ~(7u << sh)) | ((unsigned)v << sh);
+          S[b] = (uint8_t)w;
+          S[b + 1] = (uint8_t)(w >> 8);
+        }
+      } else if (STATE4) {
         const int o = S[i >> 1];
         S[i >> 1] = (uint8_t)((i & 1) ? (o & 0x0f) | (v << 4) : (o & 0xf0) | v);
       } else {
@@ -389,9 +410,10 @@ __global__ void __launch_bounds__(TE) sokoban_tile_kernel(const StepParams p) {
           }
         }
         if (go) {
-          put(ahead, 5);
+          const int now_under = (sa == 2) | (sa == 3);
+          put(ahead, (STATE3 && now_under) ? 6 : 5);  // glyph rooms hold the player-on-target code themselves
           put(pos, under ? 2 : 1);  // == room_fixed[pos]
-          under = (sa == 2) | (sa == 3);
+          under = now_under;
           pos = ahead;
         }
       }
@@ -524,6 +546,7 @@ struct AdoptParams {
   int32_t* status;
   const uint8_t* only;  // [n] or NULL: adopt env i only when only[i] != 0 (slot-wise reset of a shared batch)
   uint8_t* state4;      // [n][H*W/2] or NULL: the room as nibbles (what ragen_sokoban_step_compact keeps), written for adopted envs
+  uint8_t* state3;      // [n][B3] or NULL: the room as three-bit glyph codes (ragen_sokoban_step_glyph3), written for adopted envs
 };
 
 __global__ void __launch_bounds__(TE) sokoban_adopt_kernel(const AdoptParams p) {
@@ -559,6 +582,26 @@ __global__ void __launch_bounds__(TE) sokoban_adopt_kernel(const AdoptParams p) 
     uint8_t* d = p.state4 + ((env0 + e) * HW >> 1);
     for (int i = 0; i < HW; i += 2) d[i >> 1] = (uint8_t)((S[i] & 15) | (S[i + 1] << 4));
   }
+  if (p.state3) {  // glyph codes: room_state with the player on a target as 6, three bits per cell, rows padded to even bytes
+    const int b3 = ((HW * 3 + 15) / 16) * 2;
+    uint8_t* d = p.state3 + (env0 + e) * b3;
+    unsigned acc = 0;
+    int have = 0, at = 0;
+    for (int i = 0; i < HW; ++i) {
+      const unsigned code = (S[i] == 5 && F[i] == 2) ? 6u : (unsigned)(S[i] & 7);
+      acc |= code << have;
+      have += 3;
+      while (have >= 8) {
+        d[at++] = (uint8_t)acc;
+        acc >>= 8;
+        have -= 8;
+      }
+    }
+    while (at < b3) {
+      d[at++] = (uint8_t)acc;
+      acc >>= 8;
+    }
+  }
   int pos = -1, st = 0, open_targets = 0, under = 0;
   int r = 0, c = 0;
   for (int i = 0; i < HW; ++i) {
@@ -591,7 +634,9 @@ __global__ void __launch_bounds__(TE) sokoban_adopt_kernel(const AdoptParams p) 
 }
 
 size_t tile_smem(int H, int W, int pack) {
-  const int glyph_bytes = pack >= 2 ? TE * (((H * W * 3 + 15) / 16) * 2) : pack == 1 ? (TE * H * (W + 1)) >> 1 : TE * H * (W + 1);
+  const int b3 = ((H * W * 3 + 15) / 16) * 2;
+  if (pack == 4) return (size_t)round16(TE * b3) + 32;  // glyph rooms: the room tile only
+  const int glyph_bytes = pack >= 2 ? TE * b3 : pack == 1 ? (TE * H * (W + 1)) >> 1 : TE * H * (W + 1);
   return (size_t)round16(pack == 3 ? TE * H * W / 2 : TE * H * W) + 16 + round16(glyph_bytes) + 16;
 }
 
@@ -643,7 +688,9 @@ int sokoban_step_entry(int pack, ragen_ctx* ctx, int64_t n, int H, int W, int nu
   DeviceGuard guard(ctx->device);
   StepParams p{n, H, W, num_boxes, max_steps, K, actions, n_actions, state, reinterpret_cast<EnvMeta*>(meta),
                acc_reward, done, flags, n_executed, obs, delta};
-  return pack == 3   ? launch_tiles<false, 3>(ctx, p, (cudaStream_t)stream)
+  RAGEN_REQUIRE(pack != 4 || !obs, "glyph rooms are their own observation: obs must be NULL");
+  return pack == 4   ? launch_tiles<false, 4>(ctx, p, (cudaStream_t)stream)
+         : pack == 3 ? launch_tiles<false, 3>(ctx, p, (cudaStream_t)stream)
          : pack == 2 ? launch_tiles<false, 2>(ctx, p, (cudaStream_t)stream)
          : pack == 1 ? launch_tiles<false, 1>(ctx, p, (cudaStream_t)stream)
                      : launch_tiles<false, 0>(ctx, p, (cudaStream_t)stream);
@@ -720,6 +767,14 @@ extern "C" int ragen_sokoban_step_delta(ragen_ctx* ctx, int64_t n, int H, int W,
                             nullptr, nullptr, stream, delta);
 }
 
+extern "C" int ragen_sokoban_step_glyph3(ragen_ctx* ctx, int64_t n, int H, int W, int num_boxes, int max_steps,
+                                         const uint8_t* actions, int K, const uint8_t* n_actions, uint8_t* state3,
+                                         int16_t* meta, double* acc_reward, uint8_t* done, uint8_t* flags,
+                                         uint8_t* n_executed, uint8_t* delta, void* stream) {
+  return sokoban_step_entry(4, ctx, n, H, W, num_boxes, max_steps, actions, K, n_actions, state3, meta, acc_reward, done, flags,
+                            n_executed, nullptr, stream, delta);
+}
+
 extern "C" int ragen_sokoban_render_packed3(ragen_ctx* ctx, int64_t n, int H, int W, const uint8_t* state,
                                             const int16_t* meta, uint8_t* obs_packed3, void* stream) {
   return sokoban_render_entry(2, ctx, n, H, W, state, meta, obs_packed3, stream);
@@ -727,16 +782,16 @@ extern "C" int ragen_sokoban_render_packed3(ragen_ctx* ctx, int64_t n, int H, in
 
 extern "C" int ragen_sokoban_adopt_slots(ragen_ctx* ctx, int64_t n, int H, int W, int num_boxes, const uint8_t* state,
                                          const uint8_t* fixed, int16_t* meta, int32_t* status, const uint8_t* only,
-                                         uint8_t* state4, void* stream);
+                                         uint8_t* state4, uint8_t* state3, void* stream);
 
 extern "C" int ragen_sokoban_adopt(ragen_ctx* ctx, int64_t n, int H, int W, int num_boxes, const uint8_t* state,
                                    const uint8_t* fixed, int16_t* meta, int32_t* status, void* stream) {
-  return ragen_sokoban_adopt_slots(ctx, n, H, W, num_boxes, state, fixed, meta, status, nullptr, nullptr, stream);
+  return ragen_sokoban_adopt_slots(ctx, n, H, W, num_boxes, state, fixed, meta, status, nullptr, nullptr, nullptr, stream);
 }
 
 extern "C" int ragen_sokoban_adopt_slots(ragen_ctx* ctx, int64_t n, int H, int W, int num_boxes, const uint8_t* state,
                                          const uint8_t* fixed, int16_t* meta, int32_t* status, const uint8_t* only,
-                                         uint8_t* state4, void* stream) {
+                                         uint8_t* state4, uint8_t* state3, void* stream) {
   RAGEN_REQUIRE(ctx, "ctx is NULL");
   RAGEN_REQUIRE(!state4 || ((H * W) & 1) == 0, "nibble rooms need an even H*W, got %dx%d", H, W);
   RAGEN_SOKOBAN_SHAPE(n, H, W);
@@ -748,7 +803,7 @@ extern "C" int ragen_sokoban_adopt_slots(ragen_ctx* ctx, int64_t n, int H, int W
   const size_t smem = 2 * (size_t)round16(TE * H * W);
   RAGEN_REQUIRE(smem <= 227 * 1024, "room %dx%d does not fit the shared-memory tile (%zu B)", H, W, smem);
   RAGEN_CUDA(cudaFuncSetAttribute(sokoban_adopt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  AdoptParams p{n, H, W, num_boxes, state, fixed, reinterpret_cast<EnvMeta*>(meta), status, only, state4};
+  AdoptParams p{n, H, W, num_boxes, state, fixed, reinterpret_cast<EnvMeta*>(meta), status, only, state4, state3};
   sokoban_adopt_kernel<<<(unsigned)((n + TE - 1) / TE), TE, smem, (cudaStream_t)stream>>>(p);
   RAGEN_LAUNCHED(ctx);
   return RAGEN_OK;

@@ -187,13 +187,26 @@ class HostMirror:
         return out.reshape(g.shape[0], -1)
 
 
+def unpack3_rooms(state3, HW, out=None):
+    """Glyph rooms [n, B3] (three bits per cell, codes 0..6) -> room_state [n, H*W] uint8 on the same device (6 read as 5)."""
+    n = state3.shape[0]
+    bits = (state3.unsqueeze(-1) >> torch.arange(8, device=state3.device, dtype=torch.uint8)) & 1  # [n, B3, 8], little-endian
+    cells = bits.reshape(n, -1)[:, : 3 * HW].reshape(n, HW, 3)
+    codes = cells[..., 0] | (cells[..., 1] << 1) | (cells[..., 2] << 2)
+    codes = torch.where(codes == 6, torch.full_like(codes, 5), codes)
+    if out is not None:
+        out.copy_(codes)
+        return out
+    return codes
+
+
 def codes_to_text(codes_row, table):
     """codes_row: 1-D uint8 numpy array of length H*(W+1); the trailing separator is dropped."""
     return "".join(table[c] for c in codes_row[:-1].tolist())
 
 
 class SokobanBatch:
-    def __init__(self, n, dim_room=(6, 6), num_boxes=1, max_steps=100, search_depth=300, device=0, compact=False):
+    def __init__(self, n, dim_room=(6, 6), num_boxes=1, max_steps=100, search_depth=300, device=0, compact=False, rooms=None):
         self.ctx = _lib.Context.get(device)
         self.lib = self.ctx.lib
         self.device = torch.device("cuda", int(device))
@@ -205,11 +218,18 @@ class SokobanBatch:
         # compact=True: the rooms live in HBM as nibbles (state4 [n, HW/2], cell 2i in the low nibble of byte i) and are stepped by
         # ragen_sokoban_step_compact - half the bytes of a step's dominant read-modify-write.  `state` stays the byte view every
         # other consumer sees; it is refreshed from state4 when read after a step and packed into state4 by adopt().
-        self.compact = bool(compact)
-        if self.compact and not (self.H == self.W and self.H in (6, 8, 10)):
+        # rooms="glyph3": the rooms live in HBM as THREE-BIT GLYPH CODES (state3 [n, packed3_bytes]; 0..5 as room_state, 6 = the player
+        # on a target) and are stepped by ragen_sokoban_step_glyph3: the room is its own rendered observation (StepOut.obs IS
+        # state3), a step moves 38 B in and 38 B out per 10x10 env and nothing is rendered.
+        if rooms not in (None, "bytes", "nibbles", "glyph3"):
+            raise ValueError(f"rooms must be 'bytes', 'nibbles' or 'glyph3', got {rooms!r}")
+        self.glyph3 = rooms == "glyph3"
+        self.compact = bool(compact) or rooms == "nibbles"
+        if (self.compact or self.glyph3) and not (self.H == self.W and self.H in (6, 8, 10)):
             raise ValueError(f"compact rooms are built for 6x6, 8x8 and 10x10; room is {self.H}x{self.W}")
         self._state = torch.zeros((self.n, HW), dtype=torch.uint8, device=dev)
         self.state4 = torch.zeros((self.n, HW // 2), dtype=torch.uint8, device=dev) if self.compact else None
+        self.state3 = torch.zeros((self.n, packed3_bytes(self.H, self.W)), dtype=torch.uint8, device=dev) if self.glyph3 else None
         self._state_stale = False
         self.fixed = torch.zeros((self.n, HW), dtype=torch.uint8, device=dev)
         # one 8-byte record per env (include/ragen_b200.h): player, num_env_steps, boxes_on_target|under, actual
@@ -240,7 +260,10 @@ class SokobanBatch:
     def state(self):
         """room_state as uint8 [n, H*W] (the reference's cell codes)."""
         if self._state_stale:
-            unpack_rooms(self.state4, out=self._state)
+            if self.glyph3:
+                unpack3_rooms(self.state3, self.H * self.W, out=self._state)
+            else:
+                unpack_rooms(self.state4, out=self._state)
             self._state_stale = False
         return self._state
 
@@ -364,7 +387,7 @@ class SokobanBatch:
         _lib.check(self.lib.ragen_sokoban_adopt_slots(
             self.ctx.handle, self.n, self.H, self.W, self.num_boxes, _lib.ptr(state), _lib.ptr(self.fixed),
             _lib.ptr(self.meta), _lib.ptr(self.status), _lib.ptr(only), _lib.ptr(self.state4) if self.compact else None,
-            self.ctx.stream()))
+            _lib.ptr(self.state3) if self.glyph3 else None, self.ctx.stream()))
         if check:
             bad = torch.nonzero(self.status if only is None else self.status * only).flatten()
             if bad.numel():
@@ -381,6 +404,8 @@ class SokobanBatch:
         return (self.H * (self.W + 1)) % 2 == 0
 
     def _packed3_buffer(self):
+        if self.glyph3:
+            return self.state3  # glyph rooms are their own three-bit rows
         if self.obs_packed3 is None:
             raise ValueError(f"three-bit glyph rows are built for 6x6, 8x8 and 10x10 rooms; room is {self.H}x{self.W}")
         return self.obs_packed3
@@ -398,6 +423,17 @@ class SokobanBatch:
         assert actions.dtype == torch.uint8 and actions.is_cuda and actions.is_contiguous() and actions.shape[0] == self.n
         K = actions.shape[1]
         fmt = 3 if (packed == 3 and packed is not True) else (1 if packed else 0)  # 0 bytes, 1 nibbles, 3 three-bit rows
+        if self.glyph3:
+            if render and fmt != 3:
+                raise ValueError("glyph rooms ARE three-bit glyph rows (packed=3); use render() for the other formats")
+            self.obs_is_packed = 3
+            self.obs_stale = False
+            _lib.check(self.lib.ragen_sokoban_step_glyph3(
+                self.ctx.handle, self.n, self.H, self.W, self.num_boxes, self.max_steps, _lib.ptr(actions), K, _lib.ptr(n_actions),
+                _lib.ptr(self.state3), _lib.ptr(self.meta), _lib.ptr(self.reward), _lib.ptr(self.done), _lib.ptr(self.flags),
+                _lib.ptr(self.n_executed), None, self.ctx.stream()))
+            self._state_stale = True
+            return StepOut(self.reward, self.done, self.flags, self.n_executed, self.state3)
         if self.compact:
             if render and fmt != 3:
                 raise ValueError("a compact batch renders three-bit rows while stepping (packed=3); use render() for the other formats")
@@ -425,8 +461,8 @@ class SokobanBatch:
     def step_delta(self, actions, n_actions=None):
         """The compact step reporting DELTAS (ragen_sokoban_step_delta): returns the device tensor uint8 [n, K, 4]; nothing is
         rendered and the result arrays are not written (decode_delta / HostMirror turn deltas into them on the host)."""
-        if not self.compact:
-            raise ValueError("step_delta steps nibble rooms: construct the batch with compact=True")
+        if not (self.compact or self.glyph3):
+            raise ValueError("step_delta steps nibble or glyph rooms: construct the batch with compact=True or rooms='glyph3'")
         if actions.dim() == 1:
             actions = actions.unsqueeze(1)
         assert actions.dtype == torch.uint8 and actions.is_cuda and actions.is_contiguous() and actions.shape[0] == self.n
@@ -434,9 +470,14 @@ class SokobanBatch:
         buf = getattr(self, "_delta", None)
         if buf is None or buf.shape[1] != K:
             buf = self._delta = torch.zeros((self.n, K, 4), dtype=torch.uint8, device=self.device)
-        _lib.check(self.lib.ragen_sokoban_step_delta(
-            self.ctx.handle, self.n, self.H, self.W, self.num_boxes, self.max_steps, _lib.ptr(actions), K, _lib.ptr(n_actions),
-            _lib.ptr(self.state4), _lib.ptr(self.meta), _lib.ptr(buf), self.ctx.stream()))
+        if self.glyph3:
+            _lib.check(self.lib.ragen_sokoban_step_glyph3(
+                self.ctx.handle, self.n, self.H, self.W, self.num_boxes, self.max_steps, _lib.ptr(actions), K, _lib.ptr(n_actions),
+                _lib.ptr(self.state3), _lib.ptr(self.meta), None, None, None, None, _lib.ptr(buf), self.ctx.stream()))
+        else:
+            _lib.check(self.lib.ragen_sokoban_step_delta(
+                self.ctx.handle, self.n, self.H, self.W, self.num_boxes, self.max_steps, _lib.ptr(actions), K, _lib.ptr(n_actions),
+                _lib.ptr(self.state4), _lib.ptr(self.meta), _lib.ptr(buf), self.ctx.stream()))
         self._state_stale = True
         self.obs_stale = True
         return buf
@@ -496,6 +537,8 @@ class SokobanBatch:
         if fmt == "delta":
             src = self.step_delta(d_act).view(-1)
         else:
+            if self.glyph3:
+                raise ValueError("glyph rooms: pipelined host stepping carries deltas (fmt='delta'); full rows come from step_host")
             self.step(d_act, packed=3)
             src = self._slab[: self._off_sc + 11 * self.n]
         h = self._pin(("pipe", fmt, j), (src.numel(),), torch.uint8)
@@ -545,6 +588,17 @@ class SokobanBatch:
             h_na.numpy()[...] = n_actions_np
             d_na = h_na.to(self.device, non_blocking=True)
         out = self.step(d_act, d_na, render=want_obs, packed=(packed if want_obs else False))
+        if self.glyph3:  # the rows are the rooms themselves: one copy for them, one for the scalars
+            n_, o = self.n, self._off_sc
+            h_rows = self._pin("rows3", tuple(self.state3.shape), torch.uint8)
+            h_sc = self._pin("sc", (11 * n_,), torch.uint8)
+            if want_obs:
+                h_rows.copy_(self.state3, non_blocking=True)
+            h_sc.copy_(self._slab[o: o + 11 * n_], non_blocking=True)
+            torch.cuda.current_stream(self.device).synchronize()
+            hn = h_sc.numpy()
+            return (h_rows.numpy() if want_obs else None, hn[: 8 * n_].view(np.float64), hn[8 * n_: 9 * n_], hn[9 * n_: 10 * n_],
+                    hn[10 * n_: 11 * n_])
         if packed and want_obs:  # one copy: the packed rows and the scalars are neighbours in the result slab
             n_ = self.n
             three = packed == 3 and packed is not True
@@ -575,6 +629,9 @@ class SokobanBatch:
     # -- render -----------------------------------------------------------------------------
     def render(self, packed=False):
         fmt = 3 if (packed == 3 and packed is not True) else (1 if packed else 0)
+        if self.glyph3 and fmt == 3:  # nothing to do: the rooms are the rows
+            self.obs_is_packed, self.obs_stale = 3, False
+            return self.state3
         obs = self._packed3_buffer() if fmt == 3 else self._packed_buffer() if fmt == 1 else self.obs
         self.obs_is_packed = fmt if fmt else False
         self.obs_stale = False
@@ -618,7 +675,8 @@ class SokobanBatch:
             self.render(packed=self.obs_is_packed)
         if self.obs_is_packed == 3:
             tr = {i: g for i, g in enumerate(glyph_table(grid_lookup))}
-            rows3 = (self.obs_packed3 if rows is None else self.obs_packed3[rows]).cpu().numpy()
+            buf3 = self._packed3_buffer()
+            rows3 = (buf3 if rows is None else buf3[rows]).cpu().numpy()
             codes = unpack3_glyphs(rows3, self.H, self.W)  # vectorised; then one C-level translate per env
             return [bytes(r[:-1]).decode("latin1").translate(tr) for r in codes]
         if self.obs_is_packed:

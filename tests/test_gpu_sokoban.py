@@ -563,6 +563,92 @@ def test_text_rows_rendered_on_the_device_are_the_reference_strings(compact):
             assert as_strings[5].decode("utf-8") == want[5]
 
 
+@pytest.mark.parametrize("H,W,nb,n", [(6, 6, 1, 1000), (10, 10, 2, 4099), (8, 8, 2, 515), (10, 10, 2, 1), (6, 6, 1, 129), (10, 10, 3, 257)])
+def test_glyph_rooms_are_their_own_observation(H, W, nb, n):
+    """ragen_sokoban_step_glyph3: the rooms rest in HBM as three-bit glyph codes (6 = player on a target), so the room IS the
+    rendered observation.  After every turn state3 equals the oracle's glyph rows in the three-bit layout (what the other step
+    entry points RENDER), room_state (6 read as 5) equals the oracle's state, and rewards / done / flags / n_executed agree;
+    K-action turns, n_actions < K, ragged tiles, partial resets, step_host, deltas and the other render formats included."""
+    from ragen_b200.env.sokoban import SokobanBatch, decode_delta, unpack3_glyphs, unpack_glyphs
+
+    fixed, state = synthetic_rooms(n, H, W, nb, seed=n + 41)
+    rng = np.random.default_rng(n + 42)
+    o = SokobanBatchOracle(fixed, state, H, W, nb, 40)
+    b = SokobanBatch(n, (H, W), nb, 40, search_depth=20, rooms="glyph3")
+    b.load_rooms(fixed, state)
+    assert np.array_equal(unpack3_glyphs(b.state3.cpu().numpy(), H, W), o.glyphs())  # adopt wrote the glyph rooms
+    for turn in range(14):
+        K = int(rng.integers(1, 4))
+        acts = rng.integers(0, 5, (n, K)).astype(np.uint8)
+        na = rng.integers(0, K + 1, n).astype(np.uint8) if turn % 3 == 2 else None
+        acc, done, flags, nexec = o.step_turn(acts, na)
+        d_act = torch.from_numpy(acts).cuda()
+        d_na = None if na is None else torch.from_numpy(na).cuda()
+        if turn % 4 == 3:  # the same kernel reporting deltas
+            delta = b.step_delta(d_act, d_na).cpu().numpy()
+            got = decode_delta(delta)
+        else:
+            out = b.step(d_act, d_na, packed=3)
+            assert out.obs.data_ptr() == b.state3.data_ptr()  # the observation is the room
+            got = (out.reward.cpu().numpy(), out.done.cpu().numpy(), out.flags.cpu().numpy(), out.n_executed.cpu().numpy())
+            delta = None
+        for g, w in zip(got, (acc, done, flags, nexec)):
+            assert np.array_equal(g, w), turn
+        assert np.array_equal(unpack3_glyphs(b.state3.cpu().numpy(), H, W), o.glyphs()), turn
+        assert np.array_equal(b.state.cpu().numpy(), o.state), turn
+        assert np.array_equal(b.player.cpu().numpy(), o.player) and np.array_equal(b.on_target.cpu().numpy().astype(np.int64), o.on_target)
+    assert np.array_equal(b.render().cpu().numpy().reshape(n, -1), o.glyphs())
+    assert np.array_equal(unpack_glyphs(b.render(packed=True).cpu().numpy()), o.glyphs())
+    assert b.texts(S.DEFAULT_GLYPHS)[0] == "".join(S.DEFAULT_GLYPHS.get(int(c), "?") if c != 7 else "\n" for c in o.glyphs()[0][:-1])
+    acts = rng.integers(1, 5, n).astype(np.uint8)
+    acc, done, flags, nexec = o.step_turn(acts[:, None], None)
+    h_obs, h_rew, h_done, h_flags, h_nex = b.step_host(acts, packed=3)
+    assert np.array_equal(unpack3_glyphs(h_obs, H, W), o.glyphs())
+    assert np.array_equal(h_rew, acc) and np.array_equal(h_done, done) and np.array_equal(h_flags, flags) and np.array_equal(h_nex, nexec)
+    rows, lens = b.text_rows(S.DEFAULT_GLYPHS)
+    tab = [S.DEFAULT_GLYPHS.get(i, "?") for i in range(7)] + ["\n"]
+    host = rows.cpu().numpy()
+    assert [bytes(r[:k]).decode() for r, k in zip(host[:50], lens.cpu().numpy()[:50])] == ["".join(tab[c] for c in g) for g in o.glyphs()[:50]]
+    # a partial reset writes the glyph rooms of the slots it touched and leaves the others alone
+    before = b.state3.clone()
+    slots = [0, n // 2, n - 1] if n >= 3 else [0]
+    b.reset([7, 7, 9][: len(slots)], slots=slots)
+    touched = torch.zeros(n, dtype=torch.bool, device="cuda")
+    touched[slots] = True
+    assert torch.equal(b.state3[~touched], before[~touched])
+    st = b.state.cpu().numpy()
+    fx = b.fixed.cpu().numpy()
+    want = np.where((st == 5) & (fx == 2), 6, st).reshape(n, H, W)
+    assert np.array_equal(unpack3_glyphs(b.state3.cpu().numpy(), H, W).reshape(n, H, W + 1)[:, :, :W], want)
+
+
+def test_glyph_rooms_at_full_size():
+    """The bench's kernel instance sokoban_tile_kernel<10, 10, 0, 4> at 1 Mi envs: oracle equality on a strided sample, conservation
+    on all envs."""
+    from ragen_b200.env.sokoban import SokobanBatch, unpack3_glyphs
+
+    n, H, W, nb = 1 << 20, 10, 10, 2
+    fixed, state = synthetic_rooms(n, H, W, nb, seed=24)
+    rng = np.random.default_rng(24)
+    b = SokobanBatch(n, (H, W), nb, 100, rooms="glyph3")
+    b.load_rooms(fixed, state)
+    sample = np.arange(5, n, 251)
+    d_sample = torch.from_numpy(sample).cuda()
+    o = SokobanBatchOracle(fixed[sample], state[sample], H, W, nb, 100)
+    walls = b.fixed == 0
+    for t in range(10):
+        K = 1 if t % 3 else 2
+        a = rng.integers(1, 5, (n, K)).astype(np.uint8)
+        out = b.step(torch.from_numpy(a).cuda(), packed=3)
+        acc, done, flags, nexec = o.step_turn(a[sample])
+        assert np.array_equal(out.reward.cpu().numpy()[sample], acc)
+        assert np.array_equal(out.done.cpu().numpy()[sample], done) and np.array_equal(out.flags.cpu().numpy()[sample], flags)
+        assert np.array_equal(unpack3_glyphs(b.state3[d_sample].cpu().numpy(), H, W), o.glyphs())
+        st = b.state
+        assert int((st == 5).sum()) == n and int(((st == 3) | (st == 4)).sum()) == n * nb
+        assert bool(((st == 0) == walls).all())
+
+
 def test_compact_rooms_refuse_other_shapes():
     from ragen_b200 import _lib
     from ragen_b200.env.sokoban import SokobanBatch

@@ -286,7 +286,7 @@ __device__ __forceinline__ void load_env_nibbles(const uint8_t* s_tile4, int e, 
 
 // PACK: glyph-row format - 0 one code per byte, 1 two 4-bit codes per byte, 2 three bits per cell without separators
 template <int CH, int CW, bool RENDER_ONLY, int PACK>
-__global__ void __launch_bounds__(TE) sokoban_tile_kernel(const StepParams p) {
+__global__ void __launch_bounds__(TE, (PACK >= 3 && !RENDER_ONLY) ? 16 : 1) sokoban_tile_kernel(const StepParams p) {
   // PACK 3 = "compact": three-bit rows out AND rooms kept as nibbles in HBM (p.state is then uint8 [n][H*W/2]); the tile is
   // staged, stepped and rendered in that form
   // PACK 4 = "glyph rooms": the rooms rest in HBM as THREE-BIT GLYPH CODES (0..5 as room_state, 6 = player on a target) - the room
@@ -329,17 +329,21 @@ __global__ void __launch_bounds__(TE) sokoban_tile_kernel(const StepParams p) {
   uint32_t acts = 0;  // first 4 actions packed (K <= 4 is the common case); longer turns re-read global
   int na = 0;
   if (mine) {
-    m = p.meta[g];
     if (!RENDER_ONLY) {
-      na = p.K;
-      if (p.n_actions) na = min((int)p.n_actions[g], p.K);
-      if (m.player < 0) na = 0;  // room rejected by adopt (no player): leave it alone
+      // the record, the action count and the action bytes are three INDEPENDENT loads (one HBM round trip, not three in a row):
+      // the first min(K, 4) action bytes are fetched whatever n_actions and the record say, and the ones past `na` are never looked at
       const uint8_t* act = p.actions + g * p.K;
+      const int nab = p.n_actions ? (int)p.n_actions[g] : p.K;
       // straight-line predicated byte loads (a counted loop here compiles to three peeled gather loops)
-      if (na > 0) acts = act[0];
-      if (na > 1) acts |= (uint32_t)act[1] << 8;
-      if (na > 2) acts |= (uint32_t)act[2] << 16;
-      if (na > 3) acts |= (uint32_t)act[3] << 24;
+      if (p.K > 0) acts = act[0];
+      if (p.K > 1) acts |= (uint32_t)act[1] << 8;
+      if (p.K > 2) acts |= (uint32_t)act[2] << 16;
+      if (p.K > 3) acts |= (uint32_t)act[3] << 24;
+      m = p.meta[g];
+      na = min(nab, p.K);
+      if (m.player < 0) na = 0;  // room rejected by adopt (no player): leave it alone
+    } else {
+      m = p.meta[g];
     }
   }
   __syncthreads();  // barrier initialised (bulk) / tile copied (fallback) before anyone reads

@@ -870,8 +870,9 @@ __global__ void __launch_bounds__(96) tile_scan_kernel(int B, int T, const float
 // per step (C5's T = 2047: the whole row at once): the tile comes in with full-line loads, thread i runs the recurrence over
 // ITS 8 consecutive tokens (from shared memory, 9-word pitch: conflict-free), the 256 per-thread totals are combined by a
 // warp-shuffle suffix scan (weights c^8, c^16 ... c^128) and a pass over the 8 warp totals, every thread folds what lies to its
-// right into its 8 values, and the tile leaves through shared memory with full-line stores.  Three barriers per 2048 tokens
-// instead of a dependent chain per token.  CTAs are persistent over rows, so the masked moments (fp64) cost one set of
+// right into its 8 values, and the tile leaves through shared memory with full-line stores.  Four barriers per 2048 tokens
+// instead of a dependent chain per token.  CTAs are persistent over rows and keep TWO tiles in shared memory: the cp.async
+// loads of the next tile run under the scan and the stores of the current one.  The masked moments (fp64) cost one set of
 // atomics per CTA.  The result differs from the reference's sequential fp32 loop by rounding only (a few ulps of the largest
 // partial sum; north_star's bar is 1e-5) - callers that want the reference's bits take ragen_gae.
 constexpr int BS_T = 256;              // threads
@@ -879,13 +880,18 @@ constexpr int BS_K = 8;                // tokens per thread
 constexpr int BS_CH = BS_T * BS_K;     // tokens per step
 constexpr int BS_PITCH = BS_K + 1;     // words of shared memory per thread
 
-__global__ void __launch_bounds__(BS_T) gae_scan_kernel(int B, int T, const float* __restrict__ rewards,
+struct __align__(16) ScanStage {
+  float r[BS_T * BS_PITCH + 1];
+  float v[BS_T * BS_PITCH + 1];
+};
+
+__global__ void __launch_bounds__(BS_T, 4) gae_scan_kernel(int B, int T, const float* __restrict__ rewards,
                                                       const float* __restrict__ values, const uint8_t* __restrict__ mask,
                                                       float gamma, float c, float* __restrict__ adv, float* __restrict__ ret,
                                                       double* moments) {
-  __shared__ float s_r[BS_T * BS_PITCH + 1];
-  __shared__ float s_v[BS_T * BS_PITCH + 1];
-  __shared__ __align__(8) uint8_t s_m[BS_CH];
+  // two stages: while tile i is scanned and stored, the 4-byte cp.async of tile i + 1 (the next chunk of the row, or the next
+  // row of this CTA) are in flight into the other stage - the loads never wait for the scan
+  __shared__ ScanStage stage[2];
   __shared__ float s_w[BS_T / 32];
   __shared__ float s_carry[2];
   __shared__ double s_mom[BS_T / 32][3];
@@ -908,91 +914,130 @@ __global__ void __launch_bounds__(BS_T) gae_scan_kernel(int B, int T, const floa
   }
   double m0 = 0.0, m1 = 0.0, m2 = 0.0;
   const int n_chunks = (T + BS_CH - 1) / BS_CH;
-  for (int row = blockIdx.x; row < B; row += gridDim.x) {
+  const int my_rows = blockIdx.x < B ? (B - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
+  const int n_items = my_rows * n_chunks;  // (row, chunk) tiles of this CTA: rows in grid-stride order, chunks right to left
+
+  // queue the loads of tile `it` into stage `st`.  raw[j] receives the tile's mask bytes, 8 per thread in the COALESCED order
+  // (token tid + 256 j): the store phase below handles exactly those tokens, so the mask never passes through shared memory.
+  // The eight byte loads are issued FIRST and looked at a barrier later (pack_mask): asm volatile is a compiler fence, loads
+  // mixed in between the cp.async would each be waited for in turn
+  auto issue = [&](int it, int st, uint32_t (&raw)[BS_K]) {
+    const int row = blockIdx.x + (it / n_chunks) * gridDim.x;
+    const int t0 = (n_chunks - 1 - it % n_chunks) * BS_CH;
     const float* r = rewards + (size_t)row * T;
     const float* v = values + (size_t)row * T;
     const uint8_t* m = mask + (size_t)row * T;
+    ScanStage& S = stage[st];
+#pragma unroll
+    for (int j = 0; j < BS_K; ++j) {
+      const int t = t0 + tid + BS_T * j;
+      raw[j] = t < T ? (uint32_t)m[t] : 0u;
+    }
+#pragma unroll
+    for (int j = 0; j < BS_K; ++j) {
+      const int g = tid + BS_T * j, t = t0 + g;
+      const int idx = (g >> 3) * BS_PITCH + (g & 7);
+      if (t < T) {
+        cp_async4(&S.r[idx], r + t);
+        cp_async4(&S.v[idx], v + t);
+      } else {
+        S.r[idx] = 0.0f;
+        S.v[idx] = 0.0f;
+      }
+    }
+  };
+  auto pack_mask = [&](const uint32_t (&raw)[BS_K]) -> uint32_t {
+    uint32_t bits = 0;
+#pragma unroll
+    for (int j = 0; j < BS_K; ++j) bits |= (raw[j] ? 1u : 0u) << j;
+    return bits;
+  };
+
+  float carry = 0.0f;   // A of the first token right of the tile
+  float v_next = 0.0f;  // V of that token (V_T = 0, core_algos.py:100)
+  uint32_t mm = 0;  // bit j: mask of token tid + 256 j of the current tile
+  uint32_t raw[BS_K] = {};
+  if (n_items > 0) issue(0, 0, raw);
+  cp_async_commit();
+  mm = pack_mask(raw);
+  for (int it = 0; it < n_items; ++it) {
+    const int st = it & 1;
+#pragma unroll
+    for (int j = 0; j < BS_K; ++j) raw[j] = 0u;
+    if (it + 1 < n_items) issue(it + 1, st ^ 1, raw);  // that stage was last read before the barrier that ended tile it - 1
+    cp_async_commit();
+    cp_async_wait<1>();  // this thread's copies of tile `it` have landed
+    const int ch = n_chunks - 1 - it % n_chunks;
+    const int row = blockIdx.x + (it / n_chunks) * gridDim.x;
+    const int t0 = ch * BS_CH;
+    if (ch == n_chunks - 1) {  // a new row starts at its right end
+      carry = 0.0f;
+      v_next = 0.0f;
+    }
+    ScanStage& S = stage[st];
     float* a_out = adv + (size_t)row * T;
     float* r_out = ret + (size_t)row * T;
-    float carry = 0.0f;   // A of the first token right of the tile
-    float v_next = 0.0f;  // V of that token (V_T = 0, core_algos.py:100)
-    for (int ch = n_chunks - 1; ch >= 0; --ch) {
-      const int t0 = ch * BS_CH;
+    if (tid == 0) S.v[BS_T * BS_PITCH] = v_next;
+    __syncthreads();  // everybody's copies are visible
+    const int base = tid * BS_PITCH;
+    float vv[BS_K + 1];
 #pragma unroll
-      for (int j = 0; j < BS_K; ++j) {
-        const int g = tid + BS_T * j, t = t0 + g;
-        const bool in = t < T;
+    for (int k = 0; k < BS_K; ++k) vv[k] = S.v[base + k];
+    vv[BS_K] = S.v[base + BS_PITCH];  // the next thread's first token (the tile's right neighbour for the last thread)
+    float x[BS_K];
+    float acc = 0.0f;
+#pragma unroll
+    for (int k = BS_K - 1; k >= 0; --k) {
+      const bool in = t0 + BS_K * tid + k < T;
+      const float delta = in ? (S.r[base + k] + gamma * vv[k + 1] - vv[k]) : 0.0f;
+      acc = delta + c * acc;
+      x[k] = acc;
+    }
+    // suffix scan of the 256 per-thread totals
+    float P = x[0], y;
+    y = __shfl_down_sync(FULL, P, 1);
+    if (lane + 1 < 32) P += w1 * y;
+    y = __shfl_down_sync(FULL, P, 2);
+    if (lane + 2 < 32) P += w2 * y;
+    y = __shfl_down_sync(FULL, P, 4);
+    if (lane + 4 < 32) P += w4 * y;
+    y = __shfl_down_sync(FULL, P, 8);
+    if (lane + 8 < 32) P += w8 * y;
+    y = __shfl_down_sync(FULL, P, 16);
+    if (lane + 16 < 32) P += w16 * y;
+    if (lane == 0) s_w[warp] = P;
+    __syncthreads();
+    float G = carry;  // A of the first token of the next warp (of the tile to the right for the last warp)
+    for (int w = BS_T / 32 - 1; w > warp; --w) G = s_w[w] + w32 * G;
+    const float Sx = P + lanew * G;  // A of this thread's first token
+    float In = __shfl_down_sync(FULL, Sx, 1);
+    if (lane == 31) In = G;
+#pragma unroll
+    for (int k = 0; k < BS_K; ++k) S.r[base + k] = x[k] + cp[BS_K - k] * In;  // only this thread reads these words before the barrier
+    if (tid == 0) {
+      s_carry[0] = Sx;
+      s_carry[1] = vv[0];
+    }
+    __syncthreads();
+    carry = s_carry[0];
+    v_next = s_carry[1];
+#pragma unroll
+    for (int j = 0; j < BS_K; ++j) {
+      const int g = tid + BS_T * j, t = t0 + g;
+      if (t < T) {
         const int idx = (g >> 3) * BS_PITCH + (g & 7);
-        s_r[idx] = in ? r[t] : 0.0f;
-        s_v[idx] = in ? v[t] : 0.0f;
-        s_m[g] = in ? m[t] : (uint8_t)0;
-      }
-      if (tid == 0) s_v[BS_T * BS_PITCH] = v_next;
-      __syncthreads();
-      const int base = tid * BS_PITCH;
-      float vv[BS_K + 1];
-#pragma unroll
-      for (int k = 0; k < BS_K; ++k) vv[k] = s_v[base + k];
-      vv[BS_K] = s_v[base + BS_PITCH];  // the next thread's first token (the tile's right neighbour for the last thread)
-      float x[BS_K];
-      float acc = 0.0f;
-#pragma unroll
-      for (int k = BS_K - 1; k >= 0; --k) {
-        const bool in = t0 + BS_K * tid + k < T;
-        const float delta = in ? (s_r[base + k] + gamma * vv[k + 1] - vv[k]) : 0.0f;
-        acc = delta + c * acc;
-        x[k] = acc;
-      }
-      // suffix scan of the 256 per-thread totals
-      float P = x[0], y;
-      y = __shfl_down_sync(FULL, P, 1);
-      if (lane + 1 < 32) P += w1 * y;
-      y = __shfl_down_sync(FULL, P, 2);
-      if (lane + 2 < 32) P += w2 * y;
-      y = __shfl_down_sync(FULL, P, 4);
-      if (lane + 4 < 32) P += w4 * y;
-      y = __shfl_down_sync(FULL, P, 8);
-      if (lane + 8 < 32) P += w8 * y;
-      y = __shfl_down_sync(FULL, P, 16);
-      if (lane + 16 < 32) P += w16 * y;
-      if (lane == 0) s_w[warp] = P;
-      __syncthreads();
-      float G = carry;  // A of the first token of the next warp (of the tile to the right for the last warp)
-      for (int w = BS_T / 32 - 1; w > warp; --w) G = s_w[w] + w32 * G;
-      const float S = P + lanew * G;  // A of this thread's first token
-      float In = __shfl_down_sync(FULL, S, 1);
-      if (lane == 31) In = G;
-      const uint2 mm = *reinterpret_cast<const uint2*>(s_m + BS_K * tid);
-#pragma unroll
-      for (int k = 0; k < BS_K; ++k) {
-        const float a = x[k] + cp[BS_K - k] * In;
-        s_r[base + k] = a;  // only this thread reads these words before the barrier below
-        const unsigned mb = ((k < 4 ? mm.x : mm.y) >> (8 * (k & 3))) & 0xffu;
-        if (mb) {
+        const float a = S.r[idx];
+        a_out[t] = a;
+        r_out[t] = a + S.v[idx];  // returns = advantages + values (:107)
+        if ((mm >> j) & 1u) {
           m0 += 1.0;
           m1 += (double)a;
           m2 += (double)a * (double)a;
         }
       }
-      if (tid == 0) {
-        s_carry[0] = S;
-        s_carry[1] = vv[0];
-      }
-      __syncthreads();
-      carry = s_carry[0];
-      v_next = s_carry[1];
-#pragma unroll
-      for (int j = 0; j < BS_K; ++j) {
-        const int g = tid + BS_T * j, t = t0 + g;
-        if (t < T) {
-          const int idx = (g >> 3) * BS_PITCH + (g & 7);
-          const float a = s_r[idx];
-          a_out[t] = a;
-          r_out[t] = a + s_v[idx];  // returns = advantages + values (:107)
-        }
-      }
-      __syncthreads();  // the next tile (or row) overwrites the staging
     }
+    mm = pack_mask(raw);  // the next tile's mask bytes: in flight since the top of this iteration
+    __syncthreads();  // the tile after next is loaded into this stage
   }
   if (moments) {
     m0 = warp_sum(m0);
@@ -1007,6 +1052,228 @@ __global__ void __launch_bounds__(BS_T) gae_scan_kernel(int B, int T, const floa
     if (tid < 3) {
       double acc = 0.0;
       for (int w = 0; w < BS_T / 32; ++w) acc += s_mom[w][tid];
+      atomicAdd(moments + tid, acc);
+    }
+  }
+}
+
+// ---- the same scan with bulk-copy staging (ragen_gae_scan's fast path) -----------------------------------------------------------
+// ncu on the kernel above (profiles/r28b_gae_scan_cpasync_raw.csv): the LSU pipe is the busiest unit (52 %), a run that ONLY
+// loads the tiles takes 51 us of the 73 - 4-byte copies cost one LSU slot per token and array.  Here the tiles travel by 1-D bulk
+// copies (cp.async.bulk, no LSU slot at all) and the shared memory is read and written with 128-bit accesses.  Bulk copies need
+// 16-byte-aligned addresses, a row of an odd T starts anywhere, so a tile is cut in ALIGNED FLAT WORDS, not in tokens: the tile of
+// row `row`, chunk c covers the words [al_lo + c * 2304, ...) of the flat [B * T] tensors, where al_lo is the row's first word
+// rounded down to a multiple of four; words of the tile that belong to the neighbouring rows are staged but masked out of the
+// recurrence (right of the row's end everything is zero, left of its start nothing is kept).  The mask bytes of those words sit
+// at the same flat index.  Results leave by bulk stores too - whole 16-byte groups inside the row - and the up to three words at
+// either end of a row by ordinary stores.  288 threads x 8 words = 2304 words per tile: a row of T = 2047 fits one tile whatever
+// its alignment.  Needs 16-byte-aligned base pointers and B * T % 16 == 0; everything else takes the kernel above.
+constexpr int BT_T = 288;            // threads (9 warps)
+constexpr int BT_K = 8;              // words per thread
+constexpr int BT_W = BT_T * BT_K;    // words per tile
+constexpr int BT_NW = BT_T / 32;     // warps
+
+struct __align__(128) BulkStage {
+  float r[BT_W];           // rewards in, advantages out
+  float v[BT_W];           // values in, returns out
+  uint8_t m[BT_W + 48];    // mask bytes of the tile's words, from the 16-byte boundary at or below the tile's first word
+};
+
+struct ScanTile {  // which (row, chunk) a CTA works on; chunks of a row run right to left
+  int row, c;
+};
+
+template <int NS>
+__global__ void __launch_bounds__(BT_T) gae_scan_bulk_kernel(int B, int T, const float* __restrict__ rewards,
+                                                           const float* __restrict__ values, const uint8_t* __restrict__ mask,
+                                                           float gamma, float c, float* __restrict__ adv, float* __restrict__ ret,
+                                                           double* moments) {
+  extern __shared__ __align__(128) uint8_t bulk_smem[];
+  BulkStage* stage = reinterpret_cast<BulkStage*>(bulk_smem);
+  __shared__ __align__(8) uint64_t full[NS];
+  __shared__ float s_w[BT_NW];
+  __shared__ float s_carry[2];
+  __shared__ double s_mom[BT_NW][3];
+  const unsigned FULL = 0xffffffffu;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  float cp[BT_K + 1];  // c^0 .. c^8
+  cp[0] = 1.0f;
+#pragma unroll
+  for (int k = 1; k <= BT_K; ++k) cp[k] = cp[k - 1] * c;
+  const float w1 = cp[BT_K], w2 = w1 * w1, w4 = w2 * w2, w8 = w4 * w4, w16 = w8 * w8, w32 = w16 * w16;
+  float lanew = 1.0f;  // (c^8)^(32 - lane)
+  {
+    float base = w1;
+    int e = 32 - lane;
+    while (e) {
+      if (e & 1) lanew *= base;
+      base *= base;
+      e >>= 1;
+    }
+  }
+  // geometry of a tile
+  auto row_chunks = [&](int row) -> int {
+    const int64_t lo = (int64_t)row * T, hi = lo + T;
+    return (int)((((hi + 3) & ~(int64_t)3) - (lo & ~(int64_t)3) + BT_W - 1) / BT_W);
+  };
+  auto first_tile = [&]() -> ScanTile {
+    ScanTile t{(int)blockIdx.x, 0};
+    if (t.row < B) t.c = row_chunks(t.row) - 1;
+    return t;
+  };
+  auto advance = [&](ScanTile t) -> ScanTile {
+    if (t.c > 0) return ScanTile{t.row, t.c - 1};
+    t.row += gridDim.x;
+    t.c = t.row < B ? row_chunks(t.row) - 1 : 0;
+    return t;
+  };
+  // tid 0: arm the stage's barrier and queue the three bulk loads of tile t
+  auto issue = [&](ScanTile t, int st) {
+    const int64_t lo = (int64_t)t.row * T, hi = lo + T;
+    const int64_t al_lo = lo & ~(int64_t)3, al_hi = (hi + 3) & ~(int64_t)3;
+    const int64_t cw0 = al_lo + (int64_t)t.c * BT_W;
+    const int64_t cw1 = cw0 + BT_W < al_hi ? cw0 + BT_W : al_hi;
+    const int64_t mb0 = cw0 & ~(int64_t)15, mb1 = (cw1 + 15) & ~(int64_t)15;  // B * T % 16 == 0: never past the tensor
+    const uint32_t wbytes = (uint32_t)(cw1 - cw0) * 4u, mbytes = (uint32_t)(mb1 - mb0);
+    BulkStage& S = stage[st];
+    mbar_expect_tx(&full[st], 2u * wbytes + mbytes);
+    tma_load_1d(S.r, rewards + cw0, wbytes, &full[st]);
+    tma_load_1d(S.v, values + cw0, wbytes, &full[st]);
+    tma_load_1d(S.m, mask + mb0, mbytes, &full[st]);
+  };
+  if (tid == 0) {
+    for (int s = 0; s < NS; ++s) mbar_init(&full[s], 1);
+    fence_mbar_init();
+  }
+  __syncthreads();
+  ScanTile cur = first_tile();
+  ScanTile nxt = cur;  // the next tile to load (tid 0's)
+  if (tid == 0) {
+    for (int s = 0; s < NS && nxt.row < B; ++s) {
+      issue(nxt, s);
+      nxt = advance(nxt);
+    }
+  }
+  double m0 = 0.0, m1 = 0.0, m2 = 0.0;
+  float carry = 0.0f;   // A of the first word right of the tile
+  float v_next = 0.0f;  // V of that word
+  for (int it = 0; cur.row < B; ++it, cur = advance(cur)) {
+    const int st = it % NS;
+    const int64_t lo = (int64_t)cur.row * T, hi = lo + T;
+    const int64_t al_lo = lo & ~(int64_t)3, al_hi = (hi + 3) & ~(int64_t)3;
+    const int64_t cw0 = al_lo + (int64_t)cur.c * BT_W;
+    const int nw = (int)((cw0 + BT_W < al_hi ? cw0 + BT_W : al_hi) - cw0);  // staged words
+    const int rel_lo = (int)(lo - cw0), rel_hi = (int)(hi - cw0);          // the row, in words of this tile
+    const int mshift = (int)(cw0 & 15);
+    if (cw0 + BT_W >= al_hi) {  // the row's right end: V_T = 0 and nothing to carry in (core_algos.py:100)
+      carry = 0.0f;
+      v_next = 0.0f;
+    }
+    BulkStage& S = stage[st];
+    mbar_wait(&full[st], (uint32_t)((it / NS) & 1));
+    const int w0 = BT_K * tid;
+    const float4 r0 = reinterpret_cast<const float4*>(S.r)[2 * tid], r1 = reinterpret_cast<const float4*>(S.r)[2 * tid + 1];
+    const float4 v0 = reinterpret_cast<const float4*>(S.v)[2 * tid], v1 = reinterpret_cast<const float4*>(S.v)[2 * tid + 1];
+    const uint32_t* mwp = reinterpret_cast<const uint32_t*>(S.m + mshift + w0);  // mshift is a multiple of four, w0 of eight
+    const uint2 mw = make_uint2(mwp[0], mwp[1]);
+    float vn = __shfl_down_sync(FULL, v0.x, 1);
+    if (lane == 31) vn = (tid == BT_T - 1) ? v_next : S.v[w0 + BT_K];
+    const float rr[BT_K] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
+    const float vv[BT_K + 1] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w, vn};
+    float x[BT_K];
+    float acc = 0.0f;
+#pragma unroll
+    for (int k = BT_K - 1; k >= 0; --k) {
+      const bool in = (w0 + k >= rel_lo) && (w0 + k < rel_hi);
+      const float vnext = (w0 + k + 1 < rel_hi) ? vv[k + 1] : 0.0f;  // selects, never products: words of other rows may hold anything
+      const float delta = in ? (rr[k] + gamma * vnext - vv[k]) : 0.0f;
+      acc = delta + c * acc;
+      x[k] = acc;
+    }
+    float P = x[0], y;
+    y = __shfl_down_sync(FULL, P, 1);
+    if (lane + 1 < 32) P += w1 * y;
+    y = __shfl_down_sync(FULL, P, 2);
+    if (lane + 2 < 32) P += w2 * y;
+    y = __shfl_down_sync(FULL, P, 4);
+    if (lane + 4 < 32) P += w4 * y;
+    y = __shfl_down_sync(FULL, P, 8);
+    if (lane + 8 < 32) P += w8 * y;
+    y = __shfl_down_sync(FULL, P, 16);
+    if (lane + 16 < 32) P += w16 * y;
+    if (lane == 0) s_w[warp] = P;
+    __syncthreads();
+    float G = carry;
+    for (int w = BT_NW - 1; w > warp; --w) G = s_w[w] + w32 * G;
+    const float Sx = P + lanew * G;  // A of this thread's first word
+    float In = __shfl_down_sync(FULL, Sx, 1);
+    if (lane == 31) In = G;
+    float a[BT_K];
+#pragma unroll
+    for (int k = 0; k < BT_K; ++k) {
+      a[k] = x[k] + cp[BT_K - k] * In;
+      const bool in = (w0 + k >= rel_lo) && (w0 + k < rel_hi);
+      const unsigned mb = ((k < 4 ? mw.x : mw.y) >> (8 * (k & 3))) & 0xffu;
+      if (in && mb) {
+        m0 += 1.0;
+        m1 += (double)a[k];
+        m2 += (double)a[k] * (double)a[k];
+      }
+    }
+    reinterpret_cast<float4*>(S.r)[2 * tid] = make_float4(a[0], a[1], a[2], a[3]);
+    reinterpret_cast<float4*>(S.r)[2 * tid + 1] = make_float4(a[4], a[5], a[6], a[7]);
+    reinterpret_cast<float4*>(S.v)[2 * tid] = make_float4(a[0] + vv[0], a[1] + vv[1], a[2] + vv[2], a[3] + vv[3]);  // returns (:107)
+    reinterpret_cast<float4*>(S.v)[2 * tid + 1] = make_float4(a[4] + vv[4], a[5] + vv[5], a[6] + vv[6], a[7] + vv[7]);
+    if (tid == 0) {
+      s_carry[0] = Sx;
+      s_carry[1] = vv[0];
+    }
+    fence_async_smem();  // the bulk stores below read what was just written
+    __syncthreads();
+    carry = s_carry[0];
+    v_next = s_carry[1];
+    if (warp == 0) {
+      // whole 16-byte groups of the row leave by bulk store, the words at the row's ends one by one
+      const int ra0 = rel_lo > 0 ? rel_lo : 0, ra1 = rel_hi < nw ? rel_hi : nw;
+      const int g0 = (rel_lo + 3) & ~3, g1 = rel_hi & ~3;
+      const int rs0 = g0 > 0 ? g0 : 0, rs1 = g1 < nw ? g1 : nw;
+      const bool bulk = rs1 > rs0;
+      const int left_end = bulk ? rs0 : ra1;
+      if (lane == 0 && bulk) {
+        tma_store_1d(adv + cw0 + rs0, S.r + rs0, (uint32_t)(rs1 - rs0) * 4u);
+        tma_store_1d(ret + cw0 + rs0, S.v + rs0, (uint32_t)(rs1 - rs0) * 4u);
+      }
+      if (lane == 0) tma_store_commit();
+      int w = -1;
+      if (lane >= 1 && lane <= 8 && ra0 + lane - 1 < left_end) w = ra0 + lane - 1;
+      if (lane >= 9 && lane <= 11 && bulk && rs1 + lane - 9 < ra1) w = rs1 + lane - 9;
+      if (w >= 0) {
+        adv[cw0 + w] = S.r[w];
+        ret[cw0 + w] = S.v[w];
+      }
+      __syncwarp();
+      if (lane == 0) {
+        tma_store_wait_read();  // the stage is free once the bulk stores have read it
+        if (nxt.row < B) {
+          issue(nxt, st);
+          nxt = advance(nxt);
+        }
+      }
+    }
+  }
+  if (moments) {
+    m0 = warp_sum(m0);
+    m1 = warp_sum(m1);
+    m2 = warp_sum(m2);
+    if (lane == 0) {
+      s_mom[warp][0] = m0;
+      s_mom[warp][1] = m1;
+      s_mom[warp][2] = m2;
+    }
+    __syncthreads();
+    if (tid < 3) {
+      double acc = 0.0;
+      for (int w = 0; w < BT_NW; ++w) acc += s_mom[w][tid];
       atomicAdd(moments + tid, acc);
     }
   }
@@ -1068,6 +1335,11 @@ extern "C" int ragen_gae(ragen_ctx* ctx, int B, int T, const float* rewards, con
   return RAGEN_OK;
 }
 
+static int scan_knob(const char* name, int dflt) {  // probing knobs of the scan path (environment, read per call: cheap next to a launch)
+  const char* e = getenv(name);
+  return e ? atoi(e) : dflt;
+}
+
 extern "C" int ragen_gae_scan(ragen_ctx* ctx, int B, int T, const float* rewards, const float* values, const uint8_t* mask,
                               double gamma, double lam, float* adv, float* ret, double* moments, void* stream) {
   RAGEN_REQUIRE(ctx, "ctx is NULL");
@@ -1077,7 +1349,25 @@ extern "C" int ragen_gae_scan(ragen_ctx* ctx, int B, int T, const float* rewards
   cudaStream_t st = (cudaStream_t)stream;
   if (moments) RAGEN_CUDA(cudaMemsetAsync(moments, 0, 3 * sizeof(double), st));
   if (B == 0) return RAGEN_OK;
-  const int cap = ctx->sm_count * 4;  // persistent CTAs: four of 256 threads fit an SM (64 registers per thread)
+  const float gf = (float)gamma, cf = (float)(gamma * lam);
+  const bool aligned = (((uintptr_t)rewards | (uintptr_t)values | (uintptr_t)mask | (uintptr_t)adv | (uintptr_t)ret) & 15) == 0;
+  if (aligned && ((int64_t)B * T) % 16 == 0 && scan_knob("RAGEN_SCAN_BULK", 1)) {
+    const int ns = scan_knob("RAGEN_SCAN_STAGES", 2), per_sm = scan_knob("RAGEN_SCAN_CTAS", 3);
+    const int grid = B < ctx->sm_count * per_sm ? B : ctx->sm_count * per_sm;
+    const size_t smem = (size_t)ns * sizeof(BulkStage);
+    auto kern = ns == 3 ? gae_scan_bulk_kernel<3> : gae_scan_bulk_kernel<2>;
+    RAGEN_REQUIRE(ns == 2 || ns == 3, "RAGEN_SCAN_STAGES is 2 or 3");
+    RAGEN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<grid, BT_T, smem, st>>>(B, T, rewards, values, mask, gf, cf, adv, ret, moments);
+    RAGEN_LAUNCHED(ctx);
+    return RAGEN_OK;
+  }
+  const int cap = ctx->sm_count * 4;  // persistent CTAs: four of 256 threads fit an SM (64 registers per thread, 2 x 18 KB of stages)
+  static bool carved[64] = {};
+  if (ctx->device >= 0 && ctx->device < 64 && !carved[ctx->device]) {  // 4 x 37 KB per SM: ask for the large shared-memory split once
+    RAGEN_CUDA(cudaFuncSetAttribute(gae_scan_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    carved[ctx->device] = true;
+  }
   gae_scan_kernel<<<B < cap ? B : cap, BS_T, 0, st>>>(B, T, rewards, values, mask, (float)gamma, (float)(gamma * lam), adv, ret, moments);
   RAGEN_LAUNCHED(ctx);
   return RAGEN_OK;

@@ -204,10 +204,15 @@ def test_group_norm_golden_and_oracle():
 
 
 @pytest.mark.parametrize("B,T,gamma,lam", [(128, 2047, 1.0, 1.0), (5, 1, 1.0, 1.0), (3, 31, 0.99, 0.95), (7, 33, 0.9, 1.0), (64, 3000, 0.97, 0.9),
-                                          (1, 4097, 1.0, 0.95), (4099, 257, 0.99, 0.97)])
+                                          (1, 4097, 1.0, 0.95), (4099, 257, 0.99, 0.97),
+                                          # B * T % 16 == 0: the bulk-copy kernel (tiles cut in aligned flat words) - rows that start at
+                                          # every alignment, rows shorter than a 16-byte group, rows of one / two / three tiles
+                                          (16, 1, 1.0, 1.0), (16, 5, 0.99, 0.9), (48, 2303, 1.0, 1.0), (16, 2305, 0.99, 0.95),
+                                          (32, 4097, 1.0, 0.97), (16, 6911, 0.999, 0.95), (4112, 257, 0.99, 0.97), (16, 2304, 1.0, 1.0)])
 def test_gae_as_a_parallel_scan_is_within_the_bar(B, T, gamma, lam):
     """ragen_gae_scan: the GAE recurrence as warp-shuffle suffix sums.  Not bit-identical to the sequential fp32 loop by design;
-    un-whitened advantages / returns and the whitened advantages must sit within north_star's 1e-5 of the reference's."""
+    un-whitened advantages / returns and the whitened advantages must sit within north_star's 1e-5 of the reference's.
+    Shapes with B * T % 16 == 0 take gae_scan_bulk_kernel, the others gae_scan_kernel."""
     from ragen_b200 import ops
 
     g = torch.Generator().manual_seed(B * 131 + T)

@@ -327,6 +327,9 @@ def c5_rows(quick):
         r2c = r2[:16].cpu()
         cs = cpu_time(lambda: A.bilevel_gae(r2c, v_c[:16], m_c[:16], 1.0, 1.0, 0.95), 3.0)
         rows.append(line(f"bi-level GAE {tag}", "token", B * T, ms_bi, 17, 16 * T / cs, "16 rows, oracle/advantage.py loop as the reference", kernel="bilevel_gae_kernel"))
+        ms_bis = dev_time(lambda: ops.bilevel_gae_raw(r2, values, lm, 1.0, 1.0, 0.95, exact=False), reps=50, inner=INNER)
+        rows.append(line(f"bi-level GAE (block scans) {tag}", "token", B * T, ms_bis, 17, 16 * T / cs, "16 rows, oracle/advantage.py loop as the reference",
+                         kernel="bilevel_scan_bulk_kernel (within 1e-5 of the sequential order)"))
         gi = torch.arange(B, device="cuda", dtype=torch.int32) // 16
         ms_g = dev_time(lambda: ops.grpo_outcome(rewards, lm, gi, B // 16), reps=50, inner=INNER)
         rows.append(line(f"GRPO {tag}", "token", B * T, ms_g, 9, None, None, kernel="grpo_scores_kernel + grpo_apply_kernel"))

@@ -331,7 +331,8 @@ int ragen_group_norm_noalloc(ragen_ctx* ctx, int B, const float* score_last, con
 int ragen_gae(ragen_ctx* ctx, int B, int T, const float* rewards, const float* values, const uint8_t* mask,
               double gamma, double lam, float* adv, float* ret, double* moments, void* stream);
 
-/* The same quantities from a PARALLEL scan of the recurrence (a CTA per row, 2048 tokens per step: per-thread runs of 8 tokens
+/* The same quantities from a PARALLEL scan of the recurrence (a CTA per row, 2304 words per step staged by bulk copies - 2048
+ * tokens by 4-byte cp.async when a base pointer is off a 16-byte boundary or B * T % 16 != 0; per-thread runs of 8 tokens
  * combined by warp-shuffle suffix sums): adv / ret equal the
  * reference's sequential fp32 loop up to rounding (a few 1e-7 relative; north_star's bar is 1e-5) instead of bit for bit, at
  * HBM speed for any number of rows.  For callers that consume the whitened advantages; ragen_gae keeps the reference's bits. */
@@ -342,6 +343,14 @@ int ragen_gae_scan(ragen_ctx* ctx, int B, int T, const float* rewards, const flo
 int ragen_bilevel_gae(ragen_ctx* ctx, int B, int T, const float* rewards, const float* values,
                       const uint8_t* loss_mask, double gamma, double lam, double high_level_gamma, float* adv,
                       float* ret, double* moments, void* stream);
+
+/* The same estimator as block scans (every piece of :44-88 is an associative composition of maps on a state that travels right to
+ * left: next loss-mask value, next reward-position value, turn-level and token-level lastgaelam): equal to ragen_bilevel_gae up
+ * to fp32 rounding (north_star's bar is 1e-5) instead of bit for bit, at HBM speed for any number of rows.  Tiles travel by bulk
+ * copies, which need 16-byte-aligned base pointers and B * T % 16 == 0; other tensors are handed to ragen_bilevel_gae. */
+int ragen_bilevel_gae_scan(ragen_ctx* ctx, int B, int T, const float* rewards, const float* values,
+                           const uint8_t* loss_mask, double gamma, double lam, double high_level_gamma, float* adv,
+                           float* ret, double* moments, void* stream);
 
 /* masked moments of any fp32 tensor, and masked_whiten (verl/verl/utils/torch_functional.py:122-151) applied
  * in place from (possibly all-reduced) moments: x <- (x - mean) * rsqrt(var + 1e-8). */

@@ -55,6 +55,7 @@ SIGNATURES = {
     "ragen_gae": [_P, _I, _I, _P, _P, _P, _D, _D, _P, _P, _P, _P],
     "ragen_gae_scan": [_P, _I, _I, _P, _P, _P, _D, _D, _P, _P, _P, _P],
     "ragen_bilevel_gae": [_P, _I, _I, _P, _P, _P, _D, _D, _D, _P, _P, _P, _P],
+    "ragen_bilevel_gae_scan": [_P, _I, _I, _P, _P, _P, _D, _D, _D, _P, _P, _P, _P],
     "ragen_masked_moments": [_P, _L, _P, _P, _P, _P],
     "ragen_whiten": [_P, _L, _P, _P, _P],
     "ragen_grpo_outcome": [_P, _I, _I, _P, _P, _P, _I, _D, _I, _P, _P, _P],

@@ -1083,6 +1083,98 @@ struct ScanTile {  // which (row, chunk) a CTA works on; chunks of a row run rig
   int row, c;
 };
 
+struct TileGeom {
+  int64_t cw0;         // first flat word of the tile (a multiple of four)
+  int nw;              // staged words (a multiple of four)
+  int rel_lo, rel_hi;  // the row, in words of this tile: word w of the tile belongs to the row iff rel_lo <= w < rel_hi
+  int mshift;          // the tile's first mask byte sits at S.m[mshift] (0, 4, 8 or 12)
+  bool right_end;      // the tile holds the row's last token
+};
+
+// the flat word index of a row's first token is 64-bit; everything relative to the tile fits an int (|.| <= T + BT_W)
+__device__ __forceinline__ int bt_row_chunks(int row, int T) {
+  const int off = (int)(((int64_t)row * T) & 3);  // words between the 16-byte boundary below the row and its first token
+  return (((off + T + 3) & ~3) + BT_W - 1) / BT_W;
+}
+__device__ __forceinline__ ScanTile bt_first(int B, int T) {
+  ScanTile t{(int)blockIdx.x, 0};
+  if (t.row < B) t.c = bt_row_chunks(t.row, T) - 1;
+  return t;
+}
+__device__ __forceinline__ ScanTile bt_advance(ScanTile t, int B, int T) {
+  if (t.c > 0) return ScanTile{t.row, t.c - 1};
+  t.row += gridDim.x;
+  t.c = t.row < B ? bt_row_chunks(t.row, T) - 1 : 0;
+  return t;
+}
+__device__ __forceinline__ TileGeom bt_geom(ScanTile t, int T) {
+  const int64_t lo = (int64_t)t.row * T;
+  const int off = (int)(lo & 3);
+  const int span = (off + T + 3) & ~3;  // aligned words that cover the row
+  const int c0 = t.c * BT_W;            // the tile's first word, counted from the row's aligned start
+  TileGeom g;
+  g.cw0 = (lo - off) + c0;
+  g.right_end = c0 + BT_W >= span;
+  g.nw = g.right_end ? span - c0 : BT_W;
+  g.rel_lo = off - c0;
+  g.rel_hi = g.rel_lo + T;
+  g.mshift = (int)(g.cw0 & 15);
+  return g;
+}
+// one thread: arm the stage's barrier and queue the three bulk loads of tile t
+__device__ __forceinline__ void bt_issue(ScanTile t, int T, BulkStage& S, uint64_t* bar, const float* rewards, const float* values,
+                                         const uint8_t* mask) {
+  const TileGeom g = bt_geom(t, T);
+  const int64_t cw1 = g.cw0 + g.nw;
+  const int64_t mb0 = g.cw0 & ~(int64_t)15, mb1 = (cw1 + 15) & ~(int64_t)15;  // B * T % 16 == 0: never past the tensor
+  const uint32_t wbytes = (uint32_t)g.nw * 4u, mbytes = (uint32_t)(mb1 - mb0);
+  mbar_expect_tx(bar, 2u * wbytes + mbytes);
+  tma_load_1d(S.r, rewards + g.cw0, wbytes, bar);
+  tma_load_1d(S.v, values + g.cw0, wbytes, bar);
+  tma_load_1d(S.m, mask + mb0, mbytes, bar);
+}
+// warp 0, after the barrier that follows the tile's last shared-memory write (and fence_async_smem): whole 16-byte groups of the
+// row leave by bulk store (lane 0, one committed group), the words at the row's ends one by one (lanes 1..11)
+__device__ __forceinline__ void bt_store(const TileGeom& g, BulkStage& S, float* adv, float* ret, int lane) {
+  const int ra0 = g.rel_lo > 0 ? g.rel_lo : 0, ra1 = g.rel_hi < g.nw ? g.rel_hi : g.nw;
+  const int g0 = (g.rel_lo + 3) & ~3, g1 = g.rel_hi & ~3;
+  const int rs0 = g0 > 0 ? g0 : 0, rs1 = g1 < g.nw ? g1 : g.nw;
+  const bool bulk = rs1 > rs0;
+  const int left_end = bulk ? rs0 : ra1;
+  if (lane == 0 && bulk) {
+    tma_store_1d(adv + g.cw0 + rs0, S.r + rs0, (uint32_t)(rs1 - rs0) * 4u);
+    tma_store_1d(ret + g.cw0 + rs0, S.v + rs0, (uint32_t)(rs1 - rs0) * 4u);
+  }
+  if (lane == 0) tma_store_commit();
+  int w = -1;
+  if (lane >= 1 && lane <= 8 && ra0 + lane - 1 < left_end) w = ra0 + lane - 1;
+  if (lane >= 9 && lane <= 11 && bulk && rs1 + lane - 9 < ra1) w = rs1 + lane - 9;
+  if (w >= 0) {
+    adv[g.cw0 + w] = S.r[w];
+    ret[g.cw0 + w] = S.v[w];
+  }
+  __syncwarp();
+}
+// fp64 masked moments of a CTA -> three atomics
+__device__ __forceinline__ void bt_add_moments(double* moments, double m0, double m1, double m2, double (*s_mom)[3], int tid) {
+  if (!moments) return;
+  const int lane = tid & 31, warp = tid >> 5;
+  m0 = warp_sum(m0);
+  m1 = warp_sum(m1);
+  m2 = warp_sum(m2);
+  if (lane == 0) {
+    s_mom[warp][0] = m0;
+    s_mom[warp][1] = m1;
+    s_mom[warp][2] = m2;
+  }
+  __syncthreads();
+  if (tid < 3) {
+    double acc = 0.0;
+    for (int w = 0; w < BT_NW; ++w) acc += s_mom[w][tid];
+    atomicAdd(moments + tid, acc);
+  }
+}
+
 template <int NS>
 __global__ void __launch_bounds__(BT_T) gae_scan_bulk_kernel(int B, int T, const float* __restrict__ rewards,
                                                            const float* __restrict__ values, const uint8_t* __restrict__ mask,
@@ -1111,61 +1203,26 @@ __global__ void __launch_bounds__(BT_T) gae_scan_bulk_kernel(int B, int T, const
       e >>= 1;
     }
   }
-  // geometry of a tile
-  auto row_chunks = [&](int row) -> int {
-    const int64_t lo = (int64_t)row * T, hi = lo + T;
-    return (int)((((hi + 3) & ~(int64_t)3) - (lo & ~(int64_t)3) + BT_W - 1) / BT_W);
-  };
-  auto first_tile = [&]() -> ScanTile {
-    ScanTile t{(int)blockIdx.x, 0};
-    if (t.row < B) t.c = row_chunks(t.row) - 1;
-    return t;
-  };
-  auto advance = [&](ScanTile t) -> ScanTile {
-    if (t.c > 0) return ScanTile{t.row, t.c - 1};
-    t.row += gridDim.x;
-    t.c = t.row < B ? row_chunks(t.row) - 1 : 0;
-    return t;
-  };
-  // tid 0: arm the stage's barrier and queue the three bulk loads of tile t
-  auto issue = [&](ScanTile t, int st) {
-    const int64_t lo = (int64_t)t.row * T, hi = lo + T;
-    const int64_t al_lo = lo & ~(int64_t)3, al_hi = (hi + 3) & ~(int64_t)3;
-    const int64_t cw0 = al_lo + (int64_t)t.c * BT_W;
-    const int64_t cw1 = cw0 + BT_W < al_hi ? cw0 + BT_W : al_hi;
-    const int64_t mb0 = cw0 & ~(int64_t)15, mb1 = (cw1 + 15) & ~(int64_t)15;  // B * T % 16 == 0: never past the tensor
-    const uint32_t wbytes = (uint32_t)(cw1 - cw0) * 4u, mbytes = (uint32_t)(mb1 - mb0);
-    BulkStage& S = stage[st];
-    mbar_expect_tx(&full[st], 2u * wbytes + mbytes);
-    tma_load_1d(S.r, rewards + cw0, wbytes, &full[st]);
-    tma_load_1d(S.v, values + cw0, wbytes, &full[st]);
-    tma_load_1d(S.m, mask + mb0, mbytes, &full[st]);
-  };
   if (tid == 0) {
     for (int s = 0; s < NS; ++s) mbar_init(&full[s], 1);
     fence_mbar_init();
   }
   __syncthreads();
-  ScanTile cur = first_tile();
+  ScanTile cur = bt_first(B, T);
   ScanTile nxt = cur;  // the next tile to load (tid 0's)
   if (tid == 0) {
     for (int s = 0; s < NS && nxt.row < B; ++s) {
-      issue(nxt, s);
-      nxt = advance(nxt);
+      bt_issue(nxt, T, stage[s], &full[s], rewards, values, mask);
+      nxt = bt_advance(nxt, B, T);
     }
   }
   double m0 = 0.0, m1 = 0.0, m2 = 0.0;
   float carry = 0.0f;   // A of the first word right of the tile
   float v_next = 0.0f;  // V of that word
-  for (int it = 0; cur.row < B; ++it, cur = advance(cur)) {
+  for (int it = 0; cur.row < B; ++it, cur = bt_advance(cur, B, T)) {
     const int st = it % NS;
-    const int64_t lo = (int64_t)cur.row * T, hi = lo + T;
-    const int64_t al_lo = lo & ~(int64_t)3, al_hi = (hi + 3) & ~(int64_t)3;
-    const int64_t cw0 = al_lo + (int64_t)cur.c * BT_W;
-    const int nw = (int)((cw0 + BT_W < al_hi ? cw0 + BT_W : al_hi) - cw0);  // staged words
-    const int rel_lo = (int)(lo - cw0), rel_hi = (int)(hi - cw0);          // the row, in words of this tile
-    const int mshift = (int)(cw0 & 15);
-    if (cw0 + BT_W >= al_hi) {  // the row's right end: V_T = 0 and nothing to carry in (core_algos.py:100)
+    const TileGeom g = bt_geom(cur, T);
+    if (g.right_end) {  // V_T = 0 and nothing to carry in (core_algos.py:100)
       carry = 0.0f;
       v_next = 0.0f;
     }
@@ -1174,7 +1231,7 @@ __global__ void __launch_bounds__(BT_T) gae_scan_bulk_kernel(int B, int T, const
     const int w0 = BT_K * tid;
     const float4 r0 = reinterpret_cast<const float4*>(S.r)[2 * tid], r1 = reinterpret_cast<const float4*>(S.r)[2 * tid + 1];
     const float4 v0 = reinterpret_cast<const float4*>(S.v)[2 * tid], v1 = reinterpret_cast<const float4*>(S.v)[2 * tid + 1];
-    const uint32_t* mwp = reinterpret_cast<const uint32_t*>(S.m + mshift + w0);  // mshift is a multiple of four, w0 of eight
+    const uint32_t* mwp = reinterpret_cast<const uint32_t*>(S.m + g.mshift + w0);  // mshift is a multiple of four, w0 of eight
     const uint2 mw = make_uint2(mwp[0], mwp[1]);
     float vn = __shfl_down_sync(FULL, v0.x, 1);
     if (lane == 31) vn = (tid == BT_T - 1) ? v_next : S.v[w0 + BT_K];
@@ -1184,8 +1241,8 @@ __global__ void __launch_bounds__(BT_T) gae_scan_bulk_kernel(int B, int T, const
     float acc = 0.0f;
 #pragma unroll
     for (int k = BT_K - 1; k >= 0; --k) {
-      const bool in = (w0 + k >= rel_lo) && (w0 + k < rel_hi);
-      const float vnext = (w0 + k + 1 < rel_hi) ? vv[k + 1] : 0.0f;  // selects, never products: words of other rows may hold anything
+      const bool in = (w0 + k >= g.rel_lo) && (w0 + k < g.rel_hi);
+      const float vnext = (w0 + k + 1 < g.rel_hi) ? vv[k + 1] : 0.0f;  // selects, never products: words of other rows may hold anything
       const float delta = in ? (rr[k] + gamma * vnext - vv[k]) : 0.0f;
       acc = delta + c * acc;
       x[k] = acc;
@@ -1212,7 +1269,7 @@ __global__ void __launch_bounds__(BT_T) gae_scan_bulk_kernel(int B, int T, const
 #pragma unroll
     for (int k = 0; k < BT_K; ++k) {
       a[k] = x[k] + cp[BT_K - k] * In;
-      const bool in = (w0 + k >= rel_lo) && (w0 + k < rel_hi);
+      const bool in = (w0 + k >= g.rel_lo) && (w0 + k < g.rel_hi);
       const unsigned mb = ((k < 4 ? mw.x : mw.y) >> (8 * (k & 3))) & 0xffu;
       if (in && mb) {
         m0 += 1.0;
@@ -1233,50 +1290,260 @@ __global__ void __launch_bounds__(BT_T) gae_scan_bulk_kernel(int B, int T, const
     carry = s_carry[0];
     v_next = s_carry[1];
     if (warp == 0) {
-      // whole 16-byte groups of the row leave by bulk store, the words at the row's ends one by one
-      const int ra0 = rel_lo > 0 ? rel_lo : 0, ra1 = rel_hi < nw ? rel_hi : nw;
-      const int g0 = (rel_lo + 3) & ~3, g1 = rel_hi & ~3;
-      const int rs0 = g0 > 0 ? g0 : 0, rs1 = g1 < nw ? g1 : nw;
-      const bool bulk = rs1 > rs0;
-      const int left_end = bulk ? rs0 : ra1;
-      if (lane == 0 && bulk) {
-        tma_store_1d(adv + cw0 + rs0, S.r + rs0, (uint32_t)(rs1 - rs0) * 4u);
-        tma_store_1d(ret + cw0 + rs0, S.v + rs0, (uint32_t)(rs1 - rs0) * 4u);
-      }
-      if (lane == 0) tma_store_commit();
-      int w = -1;
-      if (lane >= 1 && lane <= 8 && ra0 + lane - 1 < left_end) w = ra0 + lane - 1;
-      if (lane >= 9 && lane <= 11 && bulk && rs1 + lane - 9 < ra1) w = rs1 + lane - 9;
-      if (w >= 0) {
-        adv[cw0 + w] = S.r[w];
-        ret[cw0 + w] = S.v[w];
-      }
-      __syncwarp();
+      bt_store(g, S, adv, ret, lane);
       if (lane == 0) {
         tma_store_wait_read();  // the stage is free once the bulk stores have read it
         if (nxt.row < B) {
-          issue(nxt, st);
-          nxt = advance(nxt);
+          bt_issue(nxt, T, S, &full[st], rewards, values, mask);
+          nxt = bt_advance(nxt, B, T);
         }
       }
     }
   }
-  if (moments) {
-    m0 = warp_sum(m0);
-    m1 = warp_sum(m1);
-    m2 = warp_sum(m2);
-    if (lane == 0) {
-      s_mom[warp][0] = m0;
-      s_mom[warp][1] = m1;
-      s_mom[warp][2] = m2;
-    }
-    __syncthreads();
-    if (tid < 3) {
-      double acc = 0.0;
-      for (int w = 0; w < BT_NW; ++w) acc += s_mom[w][tid];
-      atomicAdd(moments + tid, acc);
+  bt_add_moments(moments, m0, m1, m2, s_mom, tid);
+}
+
+// ---- bi-level GAE as block scans (ragen_bilevel_gae's many-row path) ---------------------------------------------------------------
+// ragen/trainer/core_algos.py:44-88 read as maps on a state that travels right to left, so that every piece is an associative
+// composition and a 2304-word tile is done by 288 threads at once instead of by one lane:
+//   Z ("value of the next loss-mask token"):   X -> m_t ? V_t : X          E ("value of the next reward position"): X -> e_t ? V_t : X
+//   H (turn-level lastgaelam, :62-71):         X -> e_t ? (r_t + hg * E_in - V_t) + hg*lam * X : X
+//   L (token-level lastgaelam, :73-88):        X -> m_t ? (e_t ? (H_t + V_t) - V_t : (gamma * Z_in - V_t) + gamma*lam * X) : X
+// where Z_in / E_in are the states ENTERING position t from the right and e_t = (r_t != 0).  Each round composes a thread's 8
+// maps, suffix-scans the 288 compositions (warp shuffles, then the 9 warp totals), and re-walks the 8 words with the true
+// incoming state.  Three rounds (Z and E together, H, L), one CTA barrier each.  Equal to the sequential kernel up to fp32
+// rounding (tests: 1e-5 of the tensor's scale); ragen_bilevel_gae keeps the sequential kernel below 4096 rows and for tensors
+// the bulk copies cannot take.
+template <int NS, int BI_CTAS>
+__global__ void __launch_bounds__(BT_T, BI_CTAS) bilevel_scan_bulk_kernel(int B, int T, const float* __restrict__ rewards,
+                                                               const float* __restrict__ values, const uint8_t* __restrict__ mask,
+                                                               float gamma, float gl, float hgamma, float hgl,
+                                                               float* __restrict__ adv, float* __restrict__ ret, double* moments) {
+  extern __shared__ __align__(128) uint8_t bulk_smem[];
+  BulkStage* stage = reinterpret_cast<BulkStage*>(bulk_smem);
+  __shared__ __align__(8) uint64_t full[NS];
+  __shared__ float s_zv[BT_NW], s_ev[BT_NW], s_ha[BT_NW], s_hb[BT_NW], s_ta[BT_NW], s_tb[BT_NW];
+  __shared__ uint8_t s_zh[BT_NW], s_eh[BT_NW];
+  __shared__ float s_carry[4];
+  __shared__ double s_mom[BT_NW][3];
+  const unsigned FULL = 0xffffffffu;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) {
+    for (int s = 0; s < NS; ++s) mbar_init(&full[s], 1);
+    fence_mbar_init();
+  }
+  __syncthreads();
+  ScanTile cur = bt_first(B, T);
+  ScanTile nxt = cur;
+  if (tid == 0) {
+    for (int s = 0; s < NS && nxt.row < B; ++s) {
+      bt_issue(nxt, T, stage[s], &full[s], rewards, values, mask);
+      nxt = bt_advance(nxt, B, T);
     }
   }
+  double m0 = 0.0, m1 = 0.0, m2 = 0.0;
+  float z_c = 0.0f, e_c = 0.0f, h_c = 0.0f, t_c = 0.0f;  // the four states entering the tile from the right
+  for (int it = 0; cur.row < B; ++it, cur = bt_advance(cur, B, T)) {
+    const int st = it % NS;
+    const TileGeom g = bt_geom(cur, T);
+    if (g.right_end) z_c = e_c = h_c = t_c = 0.0f;  // no next value, both lastgaelam 0 (:60, :75; a missing next loss-mask value reads 0)
+    BulkStage& S = stage[st];
+    mbar_wait(&full[st], (uint32_t)((it / NS) & 1));
+    const int w0 = BT_K * tid;
+    // every use of a word's reward / value below sits behind a select keyed by the word's bit in mk / ek, and those bits are
+    // zero off the row: words of other rows (or stale ones past a short tile) may hold anything, NaN included
+    const float4 r0 = reinterpret_cast<const float4*>(S.r)[2 * tid], r1 = reinterpret_cast<const float4*>(S.r)[2 * tid + 1];
+    const float4 v0 = reinterpret_cast<const float4*>(S.v)[2 * tid], v1 = reinterpret_cast<const float4*>(S.v)[2 * tid + 1];
+    const float vv[BT_K] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+    unsigned mk, ek = 0;  // bit k: word k is a loss-mask token / a reward position of this row
+    {
+      const int lo_k = min(max(g.rel_lo - w0, 0), BT_K), hi_k = min(max(g.rel_hi - w0, 0), BT_K);
+      const unsigned inb = ((1u << hi_k) - 1u) & ~((1u << lo_k) - 1u);  // words of the row among the eight
+      const uint32_t* mwp = reinterpret_cast<const uint32_t*>(S.m + g.mshift + w0);
+      // one bit per non-zero byte: 0x01 per byte, then the four bits gathered by a multiply (no two partial products meet)
+      const uint32_t nlo = __vsetne4(mwp[0], 0u), nhi = __vsetne4(mwp[1], 0u);
+      mk = ((((nlo * 0x00204081u) >> 21) & 0xfu) | ((((nhi * 0x00204081u) >> 21) & 0xfu) << 4)) & inb;
+#pragma unroll
+      const float r_[BT_K] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};  // not kept: the few reward positions re-read theirs
+#pragma unroll
+      for (int k = 0; k < BT_K; ++k) ek |= (r_[k] != 0.0f) ? (1u << k) : 0u;  // reward_mask = token_level_rewards.bool() (:50)
+      ek &= inb;
+    }
+    const unsigned ew = __reduce_or_sync(FULL, ek);  // warp-uniform: which of the eight steps meet a reward position in ANY lane
+    // ---- round 1: Z and E --------------------------------------------------------------------------------------------------
+    float zv = 0.0f, ev = 0.0f;
+#pragma unroll
+    for (int k = BT_K - 1; k >= 0; --k) {  // the leftmost flagged word of the eight wins
+      zv = ((mk >> k) & 1u) ? vv[k] : zv;
+      if ((ew >> k) & 1u) ev = ((ek >> k) & 1u) ? vv[k] : ev;
+    }
+    const bool zh = mk != 0, eh = ek != 0;
+    // a select map needs no scan: the state entering a lane is the value of the nearest flagged lane to its right (ballot + one
+    // shuffle), else whatever enters the warp
+    const unsigned zbits = __ballot_sync(FULL, zh), ebits = __ballot_sync(FULL, eh);
+    const unsigned above = lane == 31 ? 0u : (0xfffffffeu << lane);
+    const unsigned zr = zbits & above, er = ebits & above;  // flagged lanes right of this one
+    const float z_from = __shfl_sync(FULL, zv, zr ? __ffs(zr) - 1 : 0), e_from = __shfl_sync(FULL, ev, er ? __ffs(er) - 1 : 0);
+    const float z_first = __shfl_sync(FULL, zv, zbits ? __ffs(zbits) - 1 : 0), e_first = __shfl_sync(FULL, ev, ebits ? __ffs(ebits) - 1 : 0);
+    if (lane == 0) {
+      s_zv[warp] = z_first; s_zh[warp] = zbits ? 1 : 0;
+      s_ev[warp] = e_first; s_eh[warp] = ebits ? 1 : 0;
+    }
+    __syncthreads();
+    float Gz = z_c, Ge = e_c;  // the states entering this WARP
+#pragma unroll
+    for (int w = BT_NW - 1; w >= 1; --w) {  // all loads up front, the same work in every warp
+      const float wz = s_zv[w], we = s_ev[w];
+      const bool hz = s_zh[w] != 0 && w > warp, he = s_eh[w] != 0 && w > warp;
+      Gz = hz ? wz : Gz;
+      Ge = he ? we : Ge;
+    }
+    const float In_z = zr ? z_from : Gz, In_e = er ? e_from : Ge;  // the states entering this thread from the right
+    const float Sz = zbits ? z_first : Gz, Se = ebits ? e_first : Ge;  // ... and leaving the warp on the left (tid 0: the tile)
+    // ---- round 2: H, the turn-level recurrence over the reward positions -----------------------------------------------------------
+    float Ah = 1.0f, Bh = 0.0f;
+    {
+      float E = In_e;
+#pragma unroll
+      for (int k = BT_K - 1; k >= 0; --k)
+        if ((ew >> k) & 1u) {  // a handful of reward positions per row: most steps are skipped by the whole warp
+          const bool e = (ek >> k) & 1u;
+          const float nb = (S.r[w0 + k] + hgamma * E - vv[k]) + hgl * Bh;
+          Bh = e ? nb : Bh;
+          Ah = e ? hgl * Ah : Ah;
+          E = e ? vv[k] : E;
+        }
+    }
+    float PA = Ah, PB = Bh;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const float a2 = __shfl_down_sync(FULL, PA, o), b2 = __shfl_down_sync(FULL, PB, o);
+      const bool on = lane + o < 32;
+      PB = on ? PB + PA * b2 : PB;
+      PA = on ? PA * a2 : PA;
+    }
+    if (lane == 0) { s_ha[warp] = PA; s_hb[warp] = PB; }
+    __syncthreads();
+    float Gh = h_c;
+#pragma unroll
+    for (int w = BT_NW - 1; w >= 1; --w) {
+      const float nh = s_hb[w] + s_ha[w] * Gh;
+      Gh = w > warp ? nh : Gh;
+    }
+    const float Sh = PB + PA * Gh;
+    float In_h = __shfl_down_sync(FULL, Sh, 1);
+    if (lane == 31) In_h = Gh;
+    float hv[BT_K];  // turn-level advantage at the thread's reward positions
+    {
+      float E = In_e, H = In_h;
+#pragma unroll
+      for (int k = BT_K - 1; k >= 0; --k) {
+        hv[k] = 0.0f;
+        if ((ew >> k) & 1u) {
+          const bool e = (ek >> k) & 1u;
+          const float nh = (S.r[w0 + k] + hgamma * E - vv[k]) + hgl * H;
+          H = e ? nh : H;
+          hv[k] = H;
+          E = e ? vv[k] : E;
+        }
+      }
+    }
+    // ---- round 3: L, the token-level recurrence over the loss-mask tokens ----------------------------------------------------------
+    float At = 1.0f, Bt = 0.0f;
+    {
+      float Z = In_z;
+#pragma unroll
+      for (int k = BT_K - 1; k >= 0; --k) {
+        const bool m = (mk >> k) & 1u;
+        float ak = gl, bk = gamma * Z - vv[k];
+        if ((ew >> k) & 1u) {  // restart from the updated reward: next value 0, lastgaelam 0 (:78-81)
+          const bool e = (ek >> k) & 1u;
+          ak = e ? 0.0f : ak;
+          bk = e ? (hv[k] + vv[k]) - vv[k] : bk;
+        }
+        Bt = m ? bk + ak * Bt : Bt;
+        At = m ? ak * At : At;
+        Z = m ? vv[k] : Z;
+      }
+    }
+    PA = At;
+    PB = Bt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const float a2 = __shfl_down_sync(FULL, PA, o), b2 = __shfl_down_sync(FULL, PB, o);
+      const bool on = lane + o < 32;
+      PB = on ? PB + PA * b2 : PB;
+      PA = on ? PA * a2 : PA;
+    }
+    if (lane == 0) { s_ta[warp] = PA; s_tb[warp] = PB; }
+    __syncthreads();
+    float Gt = t_c;
+#pragma unroll
+    for (int w = BT_NW - 1; w >= 1; --w) {
+      const float nt = s_tb[w] + s_ta[w] * Gt;
+      Gt = w > warp ? nt : Gt;
+    }
+    const float St = PB + PA * Gt;
+    float In_t = __shfl_down_sync(FULL, St, 1);
+    if (lane == 31) In_t = Gt;
+    float a[BT_K], rt[BT_K];
+    {
+      float Z = In_z, X = In_t;
+      float s1 = 0.0f, s2 = 0.0f;  // the thread's eight masked advantages summed in fp32, then added to the fp64 totals
+#pragma unroll
+      for (int k = BT_K - 1; k >= 0; --k) {
+        const bool m = (mk >> k) & 1u;
+        float ak = gl, bk = gamma * Z - vv[k];
+        if ((ew >> k) & 1u) {
+          const bool e = (ek >> k) & 1u;
+          ak = e ? 0.0f : ak;
+          bk = e ? (hv[k] + vv[k]) - vv[k] : bk;
+        }
+        X = m ? bk + ak * X : X;
+        Z = m ? vv[k] : Z;
+        const float am = m ? X : 0.0f;
+        a[k] = am;
+        rt[k] = m ? X + vv[k] : 0.0f;
+        s1 += am;
+        s2 = fmaf(am, am, s2);
+        if ((ew >> k) & 1u) {  // a reward position off the loss mask keeps the turn-level pair (:70-71)
+          const bool only_e = !m && ((ek >> k) & 1u);
+          a[k] = only_e ? hv[k] : a[k];
+          rt[k] = only_e ? hv[k] + vv[k] : rt[k];
+        }
+      }
+      m0 += (double)__popc(mk);
+      m1 += (double)s1;
+      m2 += (double)s2;
+    }
+    reinterpret_cast<float4*>(S.r)[2 * tid] = make_float4(a[0], a[1], a[2], a[3]);
+    reinterpret_cast<float4*>(S.r)[2 * tid + 1] = make_float4(a[4], a[5], a[6], a[7]);
+    reinterpret_cast<float4*>(S.v)[2 * tid] = make_float4(rt[0], rt[1], rt[2], rt[3]);
+    reinterpret_cast<float4*>(S.v)[2 * tid + 1] = make_float4(rt[4], rt[5], rt[6], rt[7]);
+    if (tid == 0) {
+      s_carry[0] = Sz;
+      s_carry[1] = Se;
+      s_carry[2] = Sh;
+      s_carry[3] = St;
+    }
+    fence_async_smem();
+    __syncthreads();
+    z_c = s_carry[0];
+    e_c = s_carry[1];
+    h_c = s_carry[2];
+    t_c = s_carry[3];
+    if (warp == 0) {
+      bt_store(g, S, adv, ret, lane);
+      if (lane == 0) {
+        tma_store_wait_read();
+        if (nxt.row < B) {
+          bt_issue(nxt, T, S, &full[st], rewards, values, mask);
+          nxt = bt_advance(nxt, B, T);
+        }
+      }
+    }
+  }
+  bt_add_moments(moments, m0, m1, m2, s_mom, tid);
 }
 
 // below this many rows the per-row kernels finish in a wave or two and win (RAGEN_TS_MIN_ROWS overrides, for probing)
@@ -1389,6 +1656,33 @@ extern "C" int ragen_bilevel_gae(ragen_ctx* ctx, int B, int T, const float* rewa
   else
     bilevel_gae_kernel<<<B, RT, 0, st>>>(B, T, rewards, values, loss_mask, (float)gamma, (float)(gamma * lam), (float)high_level_gamma,
                                          (float)(high_level_gamma * lam), adv, ret, moments);
+  RAGEN_LAUNCHED(ctx);
+  return RAGEN_OK;
+}
+
+// The bi-level estimator as block scans (bilevel_scan_bulk_kernel): same arguments and outputs as ragen_bilevel_gae, equal to it up
+// to fp32 rounding (another summation order).  Tensors the bulk copies cannot take (a base pointer off a 16-byte boundary,
+// B * T % 16 != 0) go to ragen_bilevel_gae.
+extern "C" int ragen_bilevel_gae_scan(ragen_ctx* ctx, int B, int T, const float* rewards, const float* values,
+                                      const uint8_t* loss_mask, double gamma, double lam, double high_level_gamma, float* adv,
+                                      float* ret, double* moments, void* stream) {
+  RAGEN_REQUIRE(ctx, "ctx is NULL");
+  RAGEN_BT(B, T);
+  RAGEN_REQUIRE(B == 0 || (rewards && values && loss_mask && adv && ret), "NULL pointer argument");
+  const bool aligned = (((uintptr_t)rewards | (uintptr_t)values | (uintptr_t)loss_mask | (uintptr_t)adv | (uintptr_t)ret) & 15) == 0;
+  if (B == 0 || !aligned || ((int64_t)B * T) % 16 != 0)
+    return ragen_bilevel_gae(ctx, B, T, rewards, values, loss_mask, gamma, lam, high_level_gamma, adv, ret, moments, stream);
+  DeviceGuard guard(ctx->device);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (moments) RAGEN_CUDA(cudaMemsetAsync(moments, 0, 3 * sizeof(double), st));
+  const int ns = scan_knob("RAGEN_SCAN_STAGES", 2), per_sm = scan_knob("RAGEN_BISCAN_CTAS", 3);
+  RAGEN_REQUIRE(ns == 2 || ns == 3, "RAGEN_SCAN_STAGES is 2 or 3");
+  const int grid = B < ctx->sm_count * per_sm ? B : ctx->sm_count * per_sm;
+  const size_t smem = (size_t)ns * sizeof(BulkStage);
+  auto kern = per_sm >= 4 ? bilevel_scan_bulk_kernel<2, 4> : per_sm == 2 ? bilevel_scan_bulk_kernel<2, 2> : ns == 3 ? bilevel_scan_bulk_kernel<3, 3> : bilevel_scan_bulk_kernel<2, 3>;
+  RAGEN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  kern<<<grid, BT_T, smem, st>>>(B, T, rewards, values, loss_mask, (float)gamma, (float)(gamma * lam), (float)high_level_gamma,
+                                 (float)(high_level_gamma * lam), adv, ret, moments);
   RAGEN_LAUNCHED(ctx);
   return RAGEN_OK;
 }

@@ -38,14 +38,17 @@ def gae_raw(rewards, values, mask, gamma, lam, exact=True):
     return adv, ret, mom
 
 
-def bilevel_gae_raw(rewards, values, loss_mask, gamma, lam, high_level_gamma):
+def bilevel_gae_raw(rewards, values, loss_mask, gamma, lam, high_level_gamma, exact=True):
+    """exact=True: the reference's fp32 operation order, bit for bit (ragen_bilevel_gae); exact=False: the block-scan kernel
+    (ragen_bilevel_gae_scan), equal up to rounding and several times faster from a few thousand rows on."""
     ctx = _ctx(rewards)
     r, v, m = _f32(rewards), _f32(values), _u8(loss_mask).contiguous()
     B, T = r.shape
     adv, ret = torch.empty_like(r), torch.empty_like(r)
     mom = torch.empty(3, dtype=torch.float64, device=r.device)
-    _lib.check(ctx.lib.ragen_bilevel_gae(ctx.handle, B, T, _lib.ptr(r), _lib.ptr(v), _lib.ptr(m), float(gamma), float(lam),
-                                         float(high_level_gamma), _lib.ptr(adv), _lib.ptr(ret), _lib.ptr(mom), ctx.stream()))
+    fn = ctx.lib.ragen_bilevel_gae if exact else ctx.lib.ragen_bilevel_gae_scan
+    _lib.check(fn(ctx.handle, B, T, _lib.ptr(r), _lib.ptr(v), _lib.ptr(m), float(gamma), float(lam),
+                  float(high_level_gamma), _lib.ptr(adv), _lib.ptr(ret), _lib.ptr(mom), ctx.stream()))
     return adv, ret, mom
 
 

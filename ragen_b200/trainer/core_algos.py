@@ -49,10 +49,15 @@ def compute_gae_advantage_return(token_level_rewards, values, response_mask, gam
 
 
 def compute_bi_level_gae_advantage_return(token_level_rewards, values, loss_mask, gamma, lam, high_level_gamma, device=None,
-                                          sharded=False, group=None):
+                                          sharded=False, group=None, exact=None):
+    """exact as in compute_gae_advantage_return: None takes the block-scan kernel (ragen_bilevel_gae_scan) from SCAN_MIN_ROWS
+    rows on and the reference's fp32 operation order (ragen_bilevel_gae) below."""
     home, dev = token_level_rewards.device, _dev(token_level_rewards, device)
+    if exact is None:
+        exact = token_level_rewards.shape[0] < SCAN_MIN_ROWS
     with torch.no_grad():
-        adv, ret, mom = ops.bilevel_gae_raw(token_level_rewards.to(dev), values.to(dev), loss_mask.to(dev), gamma, lam, high_level_gamma)
+        adv, ret, mom = ops.bilevel_gae_raw(token_level_rewards.to(dev), values.to(dev), loss_mask.to(dev), gamma, lam, high_level_gamma,
+                                            exact=exact)
         adv = _whiten_from(adv, mom, sharded, group)
     return adv.to(home), ret.to(home)
 

@@ -13,11 +13,16 @@ g = torch.Generator(device="cuda").manual_seed(0)
 mask = (torch.rand(B, T, device="cuda", generator=g) < 0.5).to(torch.uint8)
 values = torch.randn(B, T, device="cuda", generator=g) * mask
 rewards = torch.randn(B, T, device="cuda", generator=g)
+# bi-level: a reward at the end of each of ~5 turns per row
+r2 = rewards * (torch.rand(B, T, device="cuda", generator=g) < 5.0 / T) * mask
+r2[:, -1] = 1.0
+mask[:, -1] = 1
 adv0, _, mom0 = ops.gae_raw(rewards, values, mask, 1.0, 1.0, exact=False)
 for fn, name in [(lambda: ops.gae_raw(rewards, values, mask, 1.0, 1.0), "gae"),
                  (lambda: ops.gae_raw(rewards, values, mask, 1.0, 1.0, exact=False), "gae-scan"),
                  (lambda: ops.whiten_(adv0, mom0, check=False), "whiten"),
-                 (lambda: ops.bilevel_gae_raw(rewards, values, mask, 1.0, 1.0, 0.95), "bilevel"),
+                 (lambda: ops.bilevel_gae_raw(r2, values, mask, 1.0, 1.0, 0.95), "bilevel"),
+                 (lambda: ops.bilevel_gae_raw(r2, values, mask, 1.0, 1.0, 0.95, exact=False), "bilevel-scan"),
                  (lambda: ops.discounted_returns(rewards, mask, 1.0), "rfpp")]:
     for _ in range(3):
         fn()

@@ -287,3 +287,33 @@ def test_many_rows_bilevel_equals_the_per_row_kernel_and_the_oracle():
             pick = torch.tensor([0, 1, 7, 8, 9, 31, 32, half, B - 9, B - 8, B - 2, B - 1])
             wa, wr = A.bilevel_gae_raw(rewards[pick], values[pick], mask[pick], gamma, lam, hg)
             assert torch.equal(adv.cpu()[pick], wa) and torch.equal(ret.cpu()[pick], wr)
+
+
+@pytest.mark.parametrize("B,T", [(128, 2047), (16, 1), (16, 7), (48, 2303), (16, 2305), (32, 4097), (16, 6911), (4112, 257), (7, 33)])
+def test_bilevel_gae_as_block_scans_is_within_the_bar(B, T):
+    """ragen_bilevel_gae_scan: the four recurrences of the bi-level estimator as compositions of maps, scanned 2304 words at a time.
+    Against the sequential kernel (itself pinned to the oracle bit for bit above) on the same rows, and a sample of rows against the
+    oracle's Python loops; rewards on and off the loss mask, rows with one reward and rows with dozens, (7, 33) takes the
+    hand-over to ragen_bilevel_gae (B * T % 16 != 0)."""
+    from ragen_b200 import ops
+
+    gen = torch.Generator().manual_seed(B * 7 + T)
+    mask = (torch.rand(B, T, generator=gen) < 0.55).float()
+    rewards = (torch.randint(-3, 12, (B, T), generator=gen).float() * 0.1 + 0.05) * (torch.rand(B, T, generator=gen) < 0.02)
+    last = T - 1 - mask.flip(-1).argmax(-1)
+    rows = torch.arange(B)
+    mask[rows, last] = 1
+    rewards[rows, last] = 0.7
+    values = torch.randn(B, T, generator=gen) * mask
+    for gamma, lam, hg in [(1.0, 1.0, 0.95), (0.99, 0.95, 0.9)]:
+        want_adv, want_ret, want_mom = ops.bilevel_gae_raw(rewards.cuda(), values.cuda(), mask.cuda(), gamma, lam, hg, exact=True)
+        adv, ret, mom = ops.bilevel_gae_raw(rewards.cuda(), values.cuda(), mask.cuda(), gamma, lam, hg, exact=False)
+        close(adv, want_adv.cpu(), per_element=False)  # sums of up to T terms in another order: 1e-5 of the tensor's scale
+        close(ret, want_ret.cpu(), per_element=False)
+        off = (mask == 0) & (rewards == 0)
+        assert not adv.cpu()[off].any() and not ret.cpu()[off].any()  # nothing but zeros off the loss mask and the reward positions
+        assert float((mom.cpu() - want_mom.cpu()).abs().max()) <= 1e-5 * max(1.0, float(want_mom.abs().max()))
+        pick = torch.tensor(sorted({0, 1, B // 2, B - 2, B - 1} & set(range(B))))
+        wa, wr = A.bilevel_gae_raw(rewards[pick], values[pick], mask[pick], gamma, lam, hg)
+        close(adv.cpu()[pick], wa, per_element=False)
+        close(ret.cpu()[pick], wr, per_element=False)

@@ -18,7 +18,10 @@
 namespace {
 
 constexpr int PWARPS = 4;
-constexpr int CLEAN_CAP = 4096;  // bytes of shared memory per warp for cleaning a span
+// bytes of shared memory per warp for cleaning a span (longer spans are cleaned in the scratch blob).  Kept small on purpose: every
+// byte the parser looks at after the first vector scan comes through L1, and 12 CTAs x 4 warps x 4 KiB of stage left L1 ~30 KB for
+// 48 warps' responses (C3: 67 -> 59 us with 1 KiB)
+constexpr int CLEAN_CAP = 1024;
 using parse::MAX_ACTIONS;
 
 struct ParseParams {
@@ -215,11 +218,13 @@ __device__ __forceinline__ void parse_one(const ParseParams& p, const int64_t r,
             inside &= inside - 1;
             const int q = __shfl_sync(0xffffffffu, occ_pos, l), ql = __shfl_sync(0xffffffffu, occ_len, l);
             if (q < from) continue;  // starts inside an occurrence already removed: cannot happen (no '<' inside one)
-            for (int i = from + lane; i < q; i += 32) scr[s + w + (i - from)] = text[i];
+#pragma unroll 8
+            for (int i = from + lane; i < q; i += 32) scr[s + w + (i - from)] = text[i];  // unrolled: eight loads in flight per lane
             w += q - from;
             from = q + ql;
             if (lane == l) my_junction = w;
           }
+#pragma unroll 8
           for (int i = from + lane; i < e; i += 32) scr[s + w + (i - from)] = text[i];
           w += e - from;
           __syncwarp();

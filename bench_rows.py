@@ -341,9 +341,19 @@ def c5_rows(quick):
             ops.whiten_masked(ret, m8, mom, check=False)
         ms_p = dev_time(rfpp, reps=50, inner=INNER)
         rows.append(line(f"REINFORCE++ {tag}", "token", B * T, ms_p, 4 + 1 + 4 + 4 + 1 + 4, None, None, kernel="returns_kernel<0> + whiten_masked_kernel"))
+
+        def rfpp_scan():
+            ret, m8, mom = ops.discounted_returns(rewards, lm, 1.0, exact=False)
+            ops.whiten_masked(ret, m8, mom, check=False)
+        ms_ps = dev_time(rfpp_scan, reps=50, inner=INNER)
+        rows.append(line(f"REINFORCE++ (block scans) {tag}", "token", B * T, ms_ps, 4 + 1 + 4 + 4 + 1 + 4, None, None,
+                         kernel="returns_scan_bulk_kernel<0> + whiten_masked_kernel (within 1e-5 of the sequential order)"))
         base = torch.randn(B, device="cuda")
         ms_x = dev_time(lambda: ops.remax(rewards, lm, base), reps=50, inner=INNER)
         rows.append(line(f"ReMax {tag}", "token", B * T, ms_x, 4 + 1 + 4 + 4, None, None, kernel="returns_kernel<1>"))
+        ms_xs = dev_time(lambda: ops.remax(rewards, lm, base, exact=False), reps=50, inner=INNER)
+        rows.append(line(f"ReMax (block scans) {tag}", "token", B * T, ms_xs, 4 + 1 + 4 + 4, None, None,
+                         kernel="returns_scan_bulk_kernel<1> (within 1e-5 of the sequential order)"))
         lp = -torch.rand(B, T, device="cuda")
         rf = lp + 0.1 * torch.randn(B, T, device="cuda")
         ms_k = dev_time(lambda: ops.kl_rewards(rewards, lp, rf, lm, "low_var_kl", 0.05), reps=50, inner=INNER)

@@ -388,6 +388,15 @@ int ragen_whiten_masked(ragen_ctx* ctx, int64_t n, const float* x, const uint8_t
 int ragen_remax(ragen_ctx* ctx, int B, int T, const float* rewards, const uint8_t* mask, const float* baselines,
                 float* adv, float* ret, void* stream);
 
+/* The two estimators above as block scans (the running value of REINFORCE++ is an affine map per token, ReMax a plain suffix sum,
+ * still summed in double): equal to ragen_discounted_returns / ragen_remax up to fp32 rounding instead of bit for bit, at HBM
+ * speed for any number of rows.  Tiles travel by bulk copies (16-byte-aligned base pointers, B * T % 16 == 0); other tensors are
+ * handed to the sequential entry points. */
+int ragen_discounted_returns_scan(ragen_ctx* ctx, int B, int T, const float* rewards, const uint8_t* mask, double gamma,
+                                  float* ret, double* moments, void* stream);
+int ragen_remax_scan(ragen_ctx* ctx, int B, int T, const float* rewards, const uint8_t* mask, const float* baselines,
+                     float* adv, float* ret, void* stream);
+
 /* apply_kl_penalty (verl/verl/trainer/ppo/ray_trainer.py:145-175) with kl_penalty (verl core_algos.py:469-501):
  * kld = f(logp, ref_logp) * mask with mode 0 "kl", 1 "abs", 2 "mse", 3 "low_var_kl"; rewards_out = scores - beta*kld;
  * row_kl[b] (may be NULL) = sum_t kld / (sum_t mask + 1e-8), whose mean over rows is the controller's current_kl. */

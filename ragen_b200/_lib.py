@@ -62,6 +62,8 @@ SIGNATURES = {
     "ragen_outcome_advantage": [_P, _I, _I, _P, _P, _P, _I, _I, _D, _P, _P, _P, _P],
     "ragen_discounted_returns": [_P, _I, _I, _P, _P, _D, _P, _P, _P],
     "ragen_remax": [_P, _I, _I, _P, _P, _P, _P, _P, _P],
+    "ragen_remax_scan": [_P, _I, _I, _P, _P, _P, _P, _P, _P],
+    "ragen_discounted_returns_scan": [_P, _I, _I, _P, _P, _D, _P, _P, _P],
     "ragen_whiten_masked": [_P, _L, _P, _P, _P, _P, _P],
     "ragen_kl_rewards": [_P, _I, _I, _P, _P, _P, _P, _I, _D, _P, _P, _P],
     "ragen_text_score": [_P, _L, _I, _P, _P, _P, _P, _P, _P],

@@ -14,6 +14,8 @@
 // Rows are independent, so the recurrence latency is hidden across warps; the pass is HBM-bound (17 B per token).
 #include <stdlib.h>
 
+#include <type_traits>
+
 #include "common.cuh"
 
 namespace {
@@ -1128,13 +1130,14 @@ __device__ __forceinline__ void bt_issue(ScanTile t, int T, BulkStage& S, uint64
   const int64_t cw1 = g.cw0 + g.nw;
   const int64_t mb0 = g.cw0 & ~(int64_t)15, mb1 = (cw1 + 15) & ~(int64_t)15;  // B * T % 16 == 0: never past the tensor
   const uint32_t wbytes = (uint32_t)g.nw * 4u, mbytes = (uint32_t)(mb1 - mb0);
-  mbar_expect_tx(bar, 2u * wbytes + mbytes);
+  mbar_expect_tx(bar, (values ? 2u : 1u) * wbytes + mbytes);
   tma_load_1d(S.r, rewards + g.cw0, wbytes, bar);
-  tma_load_1d(S.v, values + g.cw0, wbytes, bar);
+  if (values) tma_load_1d(S.v, values + g.cw0, wbytes, bar);  // the returns-only estimators have no values
   tma_load_1d(S.m, mask + mb0, mbytes, bar);
 }
 // warp 0, after the barrier that follows the tile's last shared-memory write (and fence_async_smem): whole 16-byte groups of the
 // row leave by bulk store (lane 0, one committed group), the words at the row's ends one by one (lanes 1..11)
+// (S.r -> adv, S.v -> ret; ret may be NULL)
 __device__ __forceinline__ void bt_store(const TileGeom& g, BulkStage& S, float* adv, float* ret, int lane) {
   const int ra0 = g.rel_lo > 0 ? g.rel_lo : 0, ra1 = g.rel_hi < g.nw ? g.rel_hi : g.nw;
   const int g0 = (g.rel_lo + 3) & ~3, g1 = g.rel_hi & ~3;
@@ -1143,7 +1146,7 @@ __device__ __forceinline__ void bt_store(const TileGeom& g, BulkStage& S, float*
   const int left_end = bulk ? rs0 : ra1;
   if (lane == 0 && bulk) {
     tma_store_1d(adv + g.cw0 + rs0, S.r + rs0, (uint32_t)(rs1 - rs0) * 4u);
-    tma_store_1d(ret + g.cw0 + rs0, S.v + rs0, (uint32_t)(rs1 - rs0) * 4u);
+    if (ret) tma_store_1d(ret + g.cw0 + rs0, S.v + rs0, (uint32_t)(rs1 - rs0) * 4u);
   }
   if (lane == 0) tma_store_commit();
   int w = -1;
@@ -1151,7 +1154,7 @@ __device__ __forceinline__ void bt_store(const TileGeom& g, BulkStage& S, float*
   if (lane >= 9 && lane <= 11 && bulk && rs1 + lane - 9 < ra1) w = rs1 + lane - 9;
   if (w >= 0) {
     adv[g.cw0 + w] = S.r[w];
-    ret[g.cw0 + w] = S.v[w];
+    if (ret) ret[g.cw0 + w] = S.v[w];
   }
   __syncwarp();
 }
@@ -1546,6 +1549,156 @@ __global__ void __launch_bounds__(BT_T, BI_CTAS) bilevel_scan_bulk_kernel(int B,
   bt_add_moments(moments, m0, m1, m2, s_mom, tid);
 }
 
+// ---- REINFORCE++ returns and ReMax as block scans ------------------------------------------------------------------------------
+// MODE 0, compute_reinforce_plus_plus_outcome_advantage (core_algos.py:262-270): run = r_t + gamma * run; returns_t = run;
+// run *= mask_t - the state that travels right to left is X -> mask_t * (r_t + gamma * X), an affine map, and returns_t =
+// r_t + gamma * X_in.  MODE 1, compute_remax_outcome_advantage (:295-303): returns = reverse cumsum of r * mask (X -> X + r_t *
+// mask_t, summed in double like the sequential kernel), advantages = returns - baseline * mask.  Same tiles, staging and scan
+// skeleton as gae_scan_bulk_kernel; S.r carries returns (MODE 0) / advantages (MODE 1) out, S.v the returns of MODE 1.
+template <int MODE>
+__global__ void __launch_bounds__(BT_T) returns_scan_bulk_kernel(int B, int T, const float* __restrict__ rewards,
+                                                               const uint8_t* __restrict__ mask, float gamma,
+                                                               const float* __restrict__ baselines, float* __restrict__ out0,
+                                                               float* __restrict__ out1, double* moments) {
+  constexpr int NS = 2;
+  using acc_t = typename std::conditional<MODE == 1, double, float>::type;
+  extern __shared__ __align__(128) uint8_t bulk_smem[];
+  BulkStage* stage = reinterpret_cast<BulkStage*>(bulk_smem);
+  __shared__ __align__(8) uint64_t full[NS];
+  __shared__ acc_t s_a[BT_NW], s_b[BT_NW];
+  __shared__ acc_t s_carry;
+  __shared__ double s_mom[BT_NW][3];
+  const unsigned FULL = 0xffffffffu;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) {
+    for (int s = 0; s < NS; ++s) mbar_init(&full[s], 1);
+    fence_mbar_init();
+  }
+  __syncthreads();
+  ScanTile cur = bt_first(B, T);
+  ScanTile nxt = cur;
+  if (tid == 0) {
+    for (int s = 0; s < NS && nxt.row < B; ++s) {
+      bt_issue(nxt, T, stage[s], &full[s], rewards, nullptr, mask);
+      nxt = bt_advance(nxt, B, T);
+    }
+  }
+  double m0 = 0.0, m1 = 0.0, m2 = 0.0;
+  acc_t carry = 0;
+  for (int it = 0; cur.row < B; ++it, cur = bt_advance(cur, B, T)) {
+    const int st = it % NS;
+    const TileGeom g = bt_geom(cur, T);
+    if (g.right_end) carry = 0;
+    BulkStage& S = stage[st];
+    mbar_wait(&full[st], (uint32_t)((it / NS) & 1));
+    const int w0 = BT_K * tid;
+    const float4 r0 = reinterpret_cast<const float4*>(S.r)[2 * tid], r1 = reinterpret_cast<const float4*>(S.r)[2 * tid + 1];
+    const float r_[BT_K] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
+    unsigned mk, inb;
+    {
+      const int lo_k = min(max(g.rel_lo - w0, 0), BT_K), hi_k = min(max(g.rel_hi - w0, 0), BT_K);
+      inb = ((1u << hi_k) - 1u) & ~((1u << lo_k) - 1u);
+      const uint32_t* mwp = reinterpret_cast<const uint32_t*>(S.m + g.mshift + w0);
+      const uint32_t nlo = __vsetne4(mwp[0], 0u), nhi = __vsetne4(mwp[1], 0u);
+      mk = ((((nlo * 0x00204081u) >> 21) & 0xfu) | ((((nhi * 0x00204081u) >> 21) & 0xfu) << 4)) & inb;
+    }
+    float rr[BT_K];
+#pragma unroll
+    for (int k = 0; k < BT_K; ++k) rr[k] = ((inb >> k) & 1u) ? r_[k] : 0.0f;  // words of other rows may hold anything
+    // the eight maps of this thread composed: X -> Bq + Aq * X
+    acc_t Aq = 1, Bq = 0;
+#pragma unroll
+    for (int k = BT_K - 1; k >= 0; --k) {
+      const bool m = (mk >> k) & 1u;
+      if (MODE == 0) {
+        const float a = m ? gamma : 0.0f, b = m ? rr[k] : 0.0f;
+        Bq = b + a * Bq;
+        Aq = a * Aq;
+      } else {
+        Bq += m ? (acc_t)rr[k] : (acc_t)0;  // Aq stays 1
+      }
+    }
+    // (off the row a = b = 0 (MODE 0) / b = 0 (MODE 1): right of the row's end the state is zero anyway, left of its start
+    // nothing is used)
+    acc_t PA = Aq, PB = Bq;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const acc_t b2 = __shfl_down_sync(FULL, PB, o);
+      const bool on = lane + o < 32;
+      if (MODE == 0) {
+        const acc_t a2 = __shfl_down_sync(FULL, PA, o);
+        PB = on ? PB + PA * b2 : PB;
+        PA = on ? PA * a2 : PA;
+      } else {
+        PB = on ? PB + b2 : PB;
+      }
+    }
+    if (lane == 0) {
+      s_a[warp] = PA;
+      s_b[warp] = PB;
+    }
+    __syncthreads();
+    acc_t G = carry;
+#pragma unroll
+    for (int w = BT_NW - 1; w >= 1; --w) {
+      const acc_t ng = MODE == 0 ? s_b[w] + s_a[w] * G : s_b[w] + G;
+      G = w > warp ? ng : G;
+    }
+    const acc_t Sx = MODE == 0 ? PB + PA * G : PB + G;  // the state leaving this thread's first word
+    acc_t In = __shfl_down_sync(FULL, Sx, 1);
+    if (lane == 31) In = G;
+    float o0[BT_K], o1[BT_K];
+    float s1 = 0.0f, s2 = 0.0f;
+    {
+      acc_t X = In;
+#pragma unroll
+      for (int k = BT_K - 1; k >= 0; --k) {
+        const bool m = (mk >> k) & 1u;
+        if (MODE == 0) {
+          const float R = rr[k] + gamma * (float)X;  // returns_t
+          o0[k] = R;
+          o1[k] = 0.0f;
+          X = m ? R : 0.0f;  // run *= mask_t
+          const float Rm = m ? R : 0.0f;
+          s1 += Rm;
+          s2 = fmaf(Rm, Rm, s2);
+        } else {
+          X += m ? (acc_t)rr[k] : (acc_t)0;
+          const float R = (float)X;
+          o1[k] = R;
+          o0[k] = R - (m ? baselines[cur.row] : 0.0f);
+        }
+      }
+    }
+    if (MODE == 0) {
+      m0 += (double)__popc(mk);
+      m1 += (double)s1;
+      m2 += (double)s2;
+    }
+    reinterpret_cast<float4*>(S.r)[2 * tid] = make_float4(o0[0], o0[1], o0[2], o0[3]);
+    reinterpret_cast<float4*>(S.r)[2 * tid + 1] = make_float4(o0[4], o0[5], o0[6], o0[7]);
+    if (MODE == 1) {
+      reinterpret_cast<float4*>(S.v)[2 * tid] = make_float4(o1[0], o1[1], o1[2], o1[3]);
+      reinterpret_cast<float4*>(S.v)[2 * tid + 1] = make_float4(o1[4], o1[5], o1[6], o1[7]);
+    }
+    if (tid == 0) s_carry = Sx;
+    fence_async_smem();
+    __syncthreads();
+    carry = s_carry;
+    if (warp == 0) {
+      bt_store(g, S, out0, MODE == 1 ? out1 : nullptr, lane);
+      if (lane == 0) {
+        tma_store_wait_read();
+        if (nxt.row < B) {
+          bt_issue(nxt, T, S, &full[st], rewards, nullptr, mask);
+          nxt = bt_advance(nxt, B, T);
+        }
+      }
+    }
+  }
+  if (MODE == 0) bt_add_moments(moments, m0, m1, m2, s_mom, tid);
+}
+
 // below this many rows the per-row kernels finish in a wave or two and win (RAGEN_TS_MIN_ROWS overrides, for probing)
 static int ts_min_rows() {
   static const int v = [] {
@@ -1790,6 +1943,45 @@ extern "C" int ragen_remax(ragen_ctx* ctx, int B, int T, const float* rewards, c
     launch_tile_scan<TS_REMAX>(ctx, (cudaStream_t)stream, B, T, rewards, nullptr, mask, 0.0f, 0.0f, baselines, adv, ret, nullptr);
   else
     returns_kernel<1><<<B, RT, 0, (cudaStream_t)stream>>>(B, T, rewards, mask, 0.0f, baselines, adv, ret, nullptr);
+  RAGEN_LAUNCHED(ctx);
+  return RAGEN_OK;
+}
+
+// The two estimators above as block scans over bulk-staged tiles (returns_scan_bulk_kernel): same arguments and outputs, equal up
+// to fp32 rounding (another summation order; ReMax still sums in double).  Tensors the bulk copies cannot take go to the
+// sequential entry points.
+extern "C" int ragen_discounted_returns_scan(ragen_ctx* ctx, int B, int T, const float* rewards, const uint8_t* mask, double gamma,
+                                             float* ret, double* moments, void* stream) {
+  RAGEN_REQUIRE(ctx, "ctx is NULL");
+  RAGEN_BT(B, T);
+  RAGEN_REQUIRE(moments && (B == 0 || (rewards && mask && ret)), "NULL pointer argument");
+  const bool aligned = (((uintptr_t)rewards | (uintptr_t)mask | (uintptr_t)ret) & 15) == 0;
+  if (B == 0 || !aligned || ((int64_t)B * T) % 16 != 0) return ragen_discounted_returns(ctx, B, T, rewards, mask, gamma, ret, moments, stream);
+  DeviceGuard guard(ctx->device);
+  cudaStream_t st = (cudaStream_t)stream;
+  RAGEN_CUDA(cudaMemsetAsync(moments, 0, 3 * sizeof(double), st));
+  const int per_sm = scan_knob("RAGEN_RSCAN_CTAS", 4);  // 56 registers: four CTAs of 288 threads per SM
+  const int grid = B < ctx->sm_count * per_sm ? B : ctx->sm_count * per_sm;
+  const size_t smem = 2 * sizeof(BulkStage);
+  RAGEN_CUDA(cudaFuncSetAttribute(returns_scan_bulk_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  returns_scan_bulk_kernel<0><<<grid, BT_T, smem, st>>>(B, T, rewards, mask, (float)gamma, nullptr, ret, nullptr, moments);
+  RAGEN_LAUNCHED(ctx);
+  return RAGEN_OK;
+}
+
+extern "C" int ragen_remax_scan(ragen_ctx* ctx, int B, int T, const float* rewards, const uint8_t* mask, const float* baselines,
+                                float* adv, float* ret, void* stream) {
+  RAGEN_REQUIRE(ctx, "ctx is NULL");
+  RAGEN_BT(B, T);
+  RAGEN_REQUIRE(rewards && mask && baselines && adv && ret, "NULL pointer argument");
+  const bool aligned = (((uintptr_t)rewards | (uintptr_t)mask | (uintptr_t)adv | (uintptr_t)ret) & 15) == 0;
+  if (B == 0 || !aligned || ((int64_t)B * T) % 16 != 0) return ragen_remax(ctx, B, T, rewards, mask, baselines, adv, ret, stream);
+  DeviceGuard guard(ctx->device);
+  const int per_sm = scan_knob("RAGEN_RSCAN_CTAS", 4);  // 56 registers: four CTAs of 288 threads per SM
+  const int grid = B < ctx->sm_count * per_sm ? B : ctx->sm_count * per_sm;
+  const size_t smem = 2 * sizeof(BulkStage);
+  RAGEN_CUDA(cudaFuncSetAttribute(returns_scan_bulk_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  returns_scan_bulk_kernel<1><<<grid, BT_T, smem, (cudaStream_t)stream>>>(B, T, rewards, mask, 0.0f, baselines, adv, ret, nullptr);
   RAGEN_LAUNCHED(ctx);
   return RAGEN_OK;
 }

@@ -116,15 +116,16 @@ def outcome_advantage(rewards, mask, group_index, n_groups, mode, epsilon=1e-6, 
     return adv, scores, mom
 
 
-def discounted_returns(rewards, mask, gamma):
-    """REINFORCE++ returns (reset after masked-out tokens) + their masked moments."""
+def discounted_returns(rewards, mask, gamma, exact=True):
+    """REINFORCE++ returns (reset after masked-out tokens) + their masked moments.  exact=False: the block-scan kernel (equal up to
+    fp32 rounding)."""
     ctx = _ctx(rewards)
     r, m = _f32(rewards), _u8(mask).contiguous()
     B, T = r.shape
     ret = torch.empty_like(r)
     mom = torch.empty(3, dtype=torch.float64, device=r.device)
-    _lib.check(ctx.lib.ragen_discounted_returns(ctx.handle, B, T, _lib.ptr(r), _lib.ptr(m), float(gamma), _lib.ptr(ret), _lib.ptr(mom),
-                                                ctx.stream()))
+    fn = ctx.lib.ragen_discounted_returns if exact else ctx.lib.ragen_discounted_returns_scan
+    _lib.check(fn(ctx.handle, B, T, _lib.ptr(r), _lib.ptr(m), float(gamma), _lib.ptr(ret), _lib.ptr(mom), ctx.stream()))
     return ret, m, mom
 
 
@@ -143,12 +144,13 @@ def whiten_masked(x, mask_u8, moments, check=True):
     return out
 
 
-def remax(rewards, mask, baselines):
+def remax(rewards, mask, baselines, exact=True):
     ctx = _ctx(rewards)
     r, m, b = _f32(rewards), _u8(mask).contiguous(), _f32(baselines)
     B, T = r.shape
     adv, ret = torch.empty_like(r), torch.empty_like(r)
-    _lib.check(ctx.lib.ragen_remax(ctx.handle, B, T, _lib.ptr(r), _lib.ptr(m), _lib.ptr(b), _lib.ptr(adv), _lib.ptr(ret), ctx.stream()))
+    fn = ctx.lib.ragen_remax if exact else ctx.lib.ragen_remax_scan
+    _lib.check(fn(ctx.handle, B, T, _lib.ptr(r), _lib.ptr(m), _lib.ptr(b), _lib.ptr(adv), _lib.ptr(ret), ctx.stream()))
     return adv, ret
 
 

@@ -106,22 +106,27 @@ def compute_reinforce_plus_plus_baseline_outcome_advantage(token_level_rewards, 
     return adv, adv
 
 
-def compute_reinforce_plus_plus_outcome_advantage(token_level_rewards, response_mask, gamma, device=None, sharded=False, group=None):
-    """verl/verl/trainer/ppo/core_algos.py:245-278."""
+def compute_reinforce_plus_plus_outcome_advantage(token_level_rewards, response_mask, gamma, device=None, sharded=False, group=None,
+                                                  exact=None):
+    """verl/verl/trainer/ppo/core_algos.py:245-278.  exact as in compute_gae_advantage_return."""
     home, dev = token_level_rewards.device, _dev(token_level_rewards, device)
+    if exact is None:
+        exact = token_level_rewards.shape[0] < SCAN_MIN_ROWS
     with torch.no_grad():
-        ret, m, mom = ops.discounted_returns(token_level_rewards.to(dev), response_mask.to(dev), float(gamma))
+        ret, m, mom = ops.discounted_returns(token_level_rewards.to(dev), response_mask.to(dev), float(gamma), exact=exact)
         if sharded:
             ops.all_reduce_moments(mom, group)
         adv = ops.whiten_masked(ret, m, mom)
     return adv.to(home), ret.to(home)
 
 
-def compute_remax_outcome_advantage(token_level_rewards, reward_baselines, response_mask, device=None):
-    """verl/verl/trainer/ppo/core_algos.py:281-305."""
+def compute_remax_outcome_advantage(token_level_rewards, reward_baselines, response_mask, device=None, exact=None):
+    """verl/verl/trainer/ppo/core_algos.py:281-305.  exact as in compute_gae_advantage_return."""
     home, dev = token_level_rewards.device, _dev(token_level_rewards, device)
+    if exact is None:
+        exact = token_level_rewards.shape[0] < SCAN_MIN_ROWS
     with torch.no_grad():
-        adv, ret = ops.remax(token_level_rewards.to(dev), response_mask.to(dev), reward_baselines.to(dev))
+        adv, ret = ops.remax(token_level_rewards.to(dev), response_mask.to(dev), reward_baselines.to(dev), exact=exact)
     return adv.to(home), ret.to(home)
 
 

@@ -17,13 +17,17 @@ rewards = torch.randn(B, T, device="cuda", generator=g)
 r2 = rewards * (torch.rand(B, T, device="cuda", generator=g) < 5.0 / T) * mask
 r2[:, -1] = 1.0
 mask[:, -1] = 1
+base = torch.randn(B, device="cuda", generator=g)
 adv0, _, mom0 = ops.gae_raw(rewards, values, mask, 1.0, 1.0, exact=False)
 for fn, name in [(lambda: ops.gae_raw(rewards, values, mask, 1.0, 1.0), "gae"),
                  (lambda: ops.gae_raw(rewards, values, mask, 1.0, 1.0, exact=False), "gae-scan"),
                  (lambda: ops.whiten_(adv0, mom0, check=False), "whiten"),
                  (lambda: ops.bilevel_gae_raw(r2, values, mask, 1.0, 1.0, 0.95), "bilevel"),
                  (lambda: ops.bilevel_gae_raw(r2, values, mask, 1.0, 1.0, 0.95, exact=False), "bilevel-scan"),
-                 (lambda: ops.discounted_returns(rewards, mask, 1.0), "rfpp")]:
+                 (lambda: ops.discounted_returns(rewards, mask, 1.0), "rfpp"),
+                 (lambda: ops.discounted_returns(rewards, mask, 1.0, exact=False), "rfpp-scan"),
+                 (lambda: ops.remax(rewards, mask, base), "remax"),
+                 (lambda: ops.remax(rewards, mask, base, exact=False), "remax-scan")]:
     for _ in range(3):
         fn()
     torch.cuda.synchronize()

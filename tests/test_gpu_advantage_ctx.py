@@ -317,3 +317,32 @@ def test_bilevel_gae_as_block_scans_is_within_the_bar(B, T):
         wa, wr = A.bilevel_gae_raw(rewards[pick], values[pick], mask[pick], gamma, lam, hg)
         close(adv.cpu()[pick], wa, per_element=False)
         close(ret.cpu()[pick], wr, per_element=False)
+
+
+@pytest.mark.parametrize("B,T", [(128, 2047), (16, 1), (16, 7), (48, 2303), (16, 2305), (32, 4097), (4112, 257), (7, 33)])
+def test_reinforce_pp_and_remax_as_block_scans_are_within_the_bar(B, T):
+    """ragen_discounted_returns_scan / ragen_remax_scan (returns_scan_bulk_kernel) against the oracle; (7, 33) takes the hand-over
+    to the sequential entry points (B * T % 16 != 0).  Masks with holes in the middle of a row (the REINFORCE++ running value is
+    reset there) and rows that end in masked-out tokens."""
+    from ragen_b200 import ops
+
+    gen = torch.Generator().manual_seed(B * 11 + T)
+    mask = (torch.rand(B, T, generator=gen) < 0.7).float()
+    mask[: B // 2, T // 2:] = (torch.rand(B // 2, T - T // 2, generator=gen) < 0.2).float()
+    rewards = torch.randn(B, T, generator=gen) * 0.1
+    base = torch.randn(B, generator=gen)
+    for gamma in (1.0, 0.97):
+        ret, m_u8, mom = ops.discounted_returns(rewards.cuda(), mask.cuda(), gamma, exact=False)
+        want_adv, want_ret = A.rfpp(rewards, mask, gamma)
+        close(ret, want_ret, per_element=False)
+        sel = mask.bool()
+        want_mom = torch.stack([mask.double().sum(), want_ret.double()[sel].sum(), (want_ret.double()[sel] ** 2).sum()])
+        assert float((mom.cpu() - want_mom).abs().max()) <= 1e-5 * max(1.0, float(want_mom.abs().max()))
+        if int(mask.sum()) > 1:
+            close(ops.whiten_masked(ret, m_u8, mom), want_adv, per_element=False)
+    adv, ret = ops.remax(rewards.cuda(), mask.cuda(), base.cuda(), exact=False)
+    want_adv, want_ret = A.remax(rewards, base, mask)
+    close(ret, want_ret, per_element=False)
+    close(adv, want_adv, per_element=False)
+    exact_adv, exact_ret = ops.remax(rewards.cuda(), mask.cuda(), base.cuda())
+    close(exact_ret, want_ret, per_element=False)

@@ -447,34 +447,78 @@ def run_native(args):
             # flight (launch i+1 while the results of step i drain on a copy stream)
             tickets = {}
 
-            def pipelined(i):
-                tickets[i + 1] = batches[(i + 1) & 1].step_host_begin(host_actions[(i + 1) % RA], "delta")
-                batches[i & 1].step_host_end(tickets.pop(i))
+            def run_pipelined(steps, fmt):
+                def pipelined(i):
+                    tickets[i + 1] = batches[(i + 1) & 1].step_host_begin(host_actions[(i + 1) % RA], fmt)
+                    batches[i & 1].step_host_end(tickets.pop(i))
 
-            def run_pipelined(steps):
                 for w in range(4):  # both batches, both pipeline slots: every pinned / device buffer exists before the clock starts
-                    batches[w & 1].step_host_end(batches[w & 1].step_host_begin(host_actions[w % RA], "delta"))
-                    batches[w & 1].step_host_end(batches[w & 1].step_host_begin(host_actions[w % RA], "delta"))
+                    batches[w & 1].step_host_end(batches[w & 1].step_host_begin(host_actions[w % RA], fmt))
+                    batches[w & 1].step_host_end(batches[w & 1].step_host_begin(host_actions[w % RA], fmt))
                 barrier()
                 t0 = time.perf_counter()
-                tickets[0] = batches[0].step_host_begin(host_actions[0], "delta")
+                tickets[0] = batches[0].step_host_begin(host_actions[0], fmt)
                 for i in range(steps):
                     pipelined(i)
                 batches[steps & 1].step_host_end(tickets.pop(steps))  # drain the look-ahead step (not counted)
                 barrier()
                 return max_over_ranks(time.perf_counter() - t0)
 
-            # wall-clock over 20 short steps: one stray host hiccup (a pinned allocation, a collector pass) is 10x the region, so the
+            # wall-clock over 20 short steps: one stray host hiccup (a pinned allocation, a collector pass) is 10x the region, so a
             # leg runs three times and the MEDIAN is the line's number; all three are listed
-            delta_runs = sorted(run_pipelined(e2e_steps) for _ in range(3))
-            delta_s = delta_runs[1]
-            e2e = {"value": n * world * e2e_steps / delta_s, "unit": UNIT, "h2d_bytes_per_step": n * 1, "d2h_bytes_per_step": n * 4,
-                   "ms_per_step": 1e3 * delta_s / e2e_steps, "host_numa": numa,
-                   "ms_per_step_runs": [round(1e3 * t / e2e_steps, 4) for t in delta_runs],
-                   "api": "SokobanBatch.step_host_begin/_end -> ragen_sokoban_step_%s (C ABI): pinned host actions up, 4-byte step " % ("glyph3 with delta records" if glyph else "delta") +
-                          "deltas down (player cell before / after, box destination, reward code + done / effective / success bits), "
-                          "two steps in flight; decode_delta / HostMirror rebuild rewards, flags and glyph rows on the host on demand",
-                   "full_rows": e2e_rows}
+            def delta_leg(fmt, record_bytes, what):
+                runs = sorted(run_pipelined(e2e_steps, fmt) for _ in range(3))
+                return {"value": n * world * e2e_steps / runs[1], "unit": UNIT, "h2d_bytes_per_step": n * 1,
+                        "d2h_bytes_per_step": n * record_bytes, "ms_per_step": 1e3 * runs[1] / e2e_steps,
+                        "ms_per_step_runs": [round(1e3 * t / e2e_steps, 4) for t in runs], "api": what}
+
+            rooms_name = "glyph rooms" if glyph else "nibble rooms"
+            delta4 = delta_leg("delta", 4, "SokobanBatch.step_host_begin/_end -> ragen_sokoban_step_%s (C ABI): 4-byte step deltas down "
+                               "(player cell before / after, box destination, info byte), self-contained records" % ("glyph3" if glyph else "delta"))
+            e2e = delta_leg("delta1", 1, "SokobanBatch.step_host_begin/_end -> ragen_sokoban_step_delta1 (C ABI, %s): pinned host actions up, "
+                            "ONE byte per action down (reward code + done / effective / success / executed / box-moved bits), two steps in "
+                            "flight; decode_delta rebuilds rewards and flags, HostMirror (which knows the actions it sent and where every "
+                            "player stands) the rooms and glyph rows, on the host on demand" % rooms_name)
+            # the same one-byte records through SokobanBatch.host_stepper: [actions up | step | records down] captured ONCE per
+            # (batch, pinned action buffer) as a CUDA graph, replayed per step - the per-step host work drops from a dozen framework
+            # calls to a replay and a stream wait.  One stepper per rotating action slab and batch; two steps in flight.
+            eager1 = e2e
+            try:
+                steppers = {}
+                for j in range(2):
+                    for a_ in range(RA):
+                        if (a_ & 1) == j or RA == 1:
+                            steppers[(j, a_)] = batches[j].host_stepper(host_actions[a_], record_bytes=1)
+
+                def run_graph(steps):
+                    def st(i):
+                        return steppers[(i & 1, i % RA)]
+                    for w in range(4):
+                        st(w).launch()
+                        st(w).wait()
+                    barrier()
+                    t0 = time.perf_counter()
+                    st(0).launch()
+                    for i in range(steps):
+                        st(i + 1).launch()
+                        st(i).wait()
+                    st(steps).wait()  # drain the look-ahead step (not counted)
+                    barrier()
+                    return max_over_ranks(time.perf_counter() - t0)
+
+                runs = sorted(run_graph(e2e_steps) for _ in range(3))
+                e2e = {"value": n * world * e2e_steps / runs[1], "unit": UNIT, "h2d_bytes_per_step": n * 1, "d2h_bytes_per_step": n * 1,
+                       "ms_per_step": 1e3 * runs[1] / e2e_steps, "ms_per_step_runs": [round(1e3 * t / e2e_steps, 4) for t in runs],
+                       "api": "SokobanBatch.host_stepper(pinned actions, record_bytes=1).launch() / .wait() -> one CUDA graph per step: "
+                              "actions host->device, ragen_sokoban_step_delta1 (C ABI, %s), one byte per action device->host into pinned "
+                              "memory; two steps in flight; decode_delta / HostMirror rebuild rewards, flags, rooms and glyph rows on "
+                              "the host on demand" % rooms_name,
+                       "eager_delta1": eager1}
+            except Exception as ex:  # capture unavailable: the eager leg stays the line's number, and says why
+                e2e = dict(eager1, graph_leg_failed=f"{type(ex).__name__}: {ex}"[:200])
+            e2e["host_numa"] = numa
+            e2e["delta4"] = delta4
+            e2e["full_rows"] = e2e_rows
 
         if compact:
             # (3) the same step with the observations as TEXT in host memory: the three-bit rows the step wrote are rendered to

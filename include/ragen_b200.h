@@ -129,6 +129,14 @@ int ragen_sokoban_step_glyph3(ragen_ctx* ctx, int64_t n, int H, int W, int num_b
                               uint8_t* state3, int16_t* meta,
                               double* acc_reward, uint8_t* done, uint8_t* flags, uint8_t* n_executed,
                               uint8_t* delta, void* stream);
+/* The same step reporting ONE byte per action, delta1 [n][K]: byte 3 of the record above with bit 7 = "a box moved".  The consumer
+ * sent the action and mirrors the player's cell, so "moved" (bit 4) and "a box moved" say the rest: the player went one cell in
+ * the action's direction (1 up, 2 down, 3 left, 4 right: -W, +W, -1, +1) and the box, if any, one cell further.  Two bytes per
+ * env-step cross the host link (one action up, one record down).  rooms_format 3: `rooms` is state4 as in
+ * ragen_sokoban_step_delta; 4: state3 as in ragen_sokoban_step_glyph3.  Any room size the format covers (no cell index is sent). */
+int ragen_sokoban_step_delta1(ragen_ctx* ctx, int64_t n, int H, int W, int num_boxes, int max_steps,
+                              const uint8_t* actions, int K, const uint8_t* n_actions, int rooms_format, uint8_t* rooms,
+                              int16_t* meta, uint8_t* delta1, void* stream);
 int ragen_sokoban_render_packed3(ragen_ctx* ctx, int64_t n, int H, int W, const uint8_t* state,
                                  const int16_t* meta, uint8_t* obs_packed3, void* stream);
 

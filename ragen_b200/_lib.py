@@ -35,6 +35,7 @@ SIGNATURES = {
     "ragen_sokoban_adopt": [_P, _L, _I, _I, _I, _P, _P, _P, _P, _P],
     "ragen_sokoban_adopt_slots": [_P, _L, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P],
     "ragen_sokoban_step_glyph3": [_P, _L, _I, _I, _I, _I, _P, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P],
+    "ragen_sokoban_step_delta1": [_P, _L, _I, _I, _I, _I, _P, _I, _P, _I, _P, _P, _P, _P],
     "ragen_sokoban_generate": [_P, _L, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P],
     "ragen_sokoban_solve": [_P, _L, _I, _I, _P, _P, _I, _L, _P, _P, _P, _P, _P],
     "ragen_frozenlake_reset": [_P, _L, _I, _D, _P, _P, _P, _P, _P, _P, _P],

@@ -47,6 +47,7 @@ struct StepParams {
   uint8_t* n_executed;
   uint8_t* obs;
   uint8_t* delta;  // [n][K][4] or NULL: per-action delta records instead of the four result arrays (ragen_sokoban_step_delta)
+  int delta1;      // the records are ONE byte each, [n][K] (ragen_sokoban_step_delta1): the info byte alone, bit 7 = a box moved
 };
 
 __host__ __device__ inline int round16(int x) { return (x + 15) & ~15; }
@@ -439,13 +440,19 @@ __global__ void __launch_bounds__(TE, (PACK >= 3 && !RENDER_ONLY) ? 16 : 1) soko
         // [player before | player after | box destination or 0xff | reward code (0: -0.1, 1: +1, 2: -1, then +10 when won: 3 with
         // the +1, 4 without) | done << 3 | effective << 4 | success << 5 | executed << 6]
         const int code = won ? (now_on_rose ? 3 : 4) : now_on_rose ? 1 : now_on_fell ? 2 : 0;
-        drec[k] = (uint32_t)before | ((uint32_t)pos << 8) | ((uint32_t)box_to << 16) |
-                  ((uint32_t)(code | (dn << 3) | ((before != pos) << 4) | ((int)won << 5) | (1 << 6)) << 24);
+        const uint32_t info = (uint32_t)(code | (dn << 3) | ((before != pos) << 4) | ((int)won << 5) | (1 << 6));
+        if (p.delta1)  // the consumer knows the action it sent and mirrors the player: "moved" and "a box moved" say the rest
+          p.delta[g * p.K + k] = (uint8_t)(info | (box_to != 0xff ? 0x80u : 0u));
+        else
+          drec[k] = (uint32_t)before | ((uint32_t)pos << 8) | ((uint32_t)box_to << 16) | (info << 24);
       }
       if (dn) break;
     }
     if (drec)
-      for (int k = nexec; k < p.K; ++k) drec[k] = 0u;  // not executed
+      for (int k = nexec; k < p.K; ++k) {  // not executed
+        if (p.delta1) p.delta[g * p.K + k] = 0;
+        else drec[k] = 0u;
+      }
     m.player = (int16_t)pos;
     m.steps = (uint16_t)steps;
     m.on_target = (int8_t)on;
@@ -678,20 +685,21 @@ bool aligned8(const void* p) { return ((uintptr_t)p & 7) == 0; }
 namespace {
 int sokoban_step_entry(int pack, ragen_ctx* ctx, int64_t n, int H, int W, int num_boxes, int max_steps, const uint8_t* actions,
                        int K, const uint8_t* n_actions, uint8_t* state, int16_t* meta, double* acc_reward, uint8_t* done,
-                       uint8_t* flags, uint8_t* n_executed, uint8_t* obs, void* stream, uint8_t* delta = nullptr) {
+                       uint8_t* flags, uint8_t* n_executed, uint8_t* obs, void* stream, uint8_t* delta = nullptr, int delta1 = 0) {
   RAGEN_REQUIRE(ctx, "ctx is NULL");
   RAGEN_SOKOBAN_SHAPE(n, H, W);
   RAGEN_REQUIRE(K >= 1 && K <= 255, "K=%d out of range", K);
   RAGEN_REQUIRE(num_boxes >= 0 && num_boxes <= 127, "num_boxes=%d out of range", num_boxes);
   RAGEN_REQUIRE(actions && state && meta, "NULL pointer argument");
   RAGEN_REQUIRE(delta || (acc_reward && done && flags && n_executed), "NULL pointer argument");
-  RAGEN_REQUIRE(aligned16(state) && (!obs || aligned16(obs)) && aligned8(meta) && aligned8(acc_reward) && (((uintptr_t)delta & 3) == 0),
+  RAGEN_REQUIRE(aligned16(state) && (!obs || aligned16(obs)) && aligned8(meta) && aligned8(acc_reward) &&
+                    (delta1 || ((uintptr_t)delta & 3) == 0),
                 "state/obs must be 16-byte aligned, meta/acc_reward 8-byte aligned, delta 4-byte aligned");
-  RAGEN_REQUIRE(!delta || H * W <= 255, "delta records hold cell indices in one byte: H*W <= 255");
+  RAGEN_REQUIRE(!delta || delta1 || H * W <= 255, "delta records hold cell indices in one byte: H*W <= 255");
   if (n == 0) return RAGEN_OK;
   DeviceGuard guard(ctx->device);
   StepParams p{n, H, W, num_boxes, max_steps, K, actions, n_actions, state, reinterpret_cast<EnvMeta*>(meta),
-               acc_reward, done, flags, n_executed, obs, delta};
+               acc_reward, done, flags, n_executed, obs, delta, delta1};
   RAGEN_REQUIRE(pack != 4 || !obs, "glyph rooms are their own observation: obs must be NULL");
   return pack == 4   ? launch_tiles<false, 4>(ctx, p, (cudaStream_t)stream)
          : pack == 3 ? launch_tiles<false, 3>(ctx, p, (cudaStream_t)stream)
@@ -777,6 +785,15 @@ extern "C" int ragen_sokoban_step_glyph3(ragen_ctx* ctx, int64_t n, int H, int W
                                          uint8_t* n_executed, uint8_t* delta, void* stream) {
   return sokoban_step_entry(4, ctx, n, H, W, num_boxes, max_steps, actions, K, n_actions, state3, meta, acc_reward, done, flags,
                             n_executed, nullptr, stream, delta);
+}
+
+extern "C" int ragen_sokoban_step_delta1(ragen_ctx* ctx, int64_t n, int H, int W, int num_boxes, int max_steps,
+                                         const uint8_t* actions, int K, const uint8_t* n_actions, int rooms_format, uint8_t* rooms,
+                                         int16_t* meta, uint8_t* delta1, void* stream) {
+  RAGEN_REQUIRE(delta1, "delta1 is NULL");
+  RAGEN_REQUIRE(rooms_format == 3 || rooms_format == 4, "rooms_format %d (3: nibble rooms, 4: three-bit glyph rooms)", rooms_format);
+  return sokoban_step_entry(rooms_format, ctx, n, H, W, num_boxes, max_steps, actions, K, n_actions, rooms, meta, nullptr, nullptr,
+                            nullptr, nullptr, nullptr, stream, delta1, 1);
 }
 
 extern "C" int ragen_sokoban_render_packed3(ragen_ctx* ctx, int64_t n, int H, int W, const uint8_t* state,

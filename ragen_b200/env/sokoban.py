@@ -135,11 +135,12 @@ REWARD_CODES = (-0.1, -0.1 + 1, -0.1 + -1, -0.1 + 1 + 10, -0.1 + 10)  # gym_soko
 
 
 def decode_delta(delta):
-    """delta uint8 [n, K, 4] (ragen_sokoban_step_delta) -> (acc_reward f64 [n], done u8 [n], flags u8 [n], n_executed u8 [n]) as
-    the other step entry points report them: rewards summed left to right in doubles, done / flags of the last executed action."""
+    """delta uint8 [n, K, 4] (ragen_sokoban_step_delta) or [n, K] (the one-byte records of ragen_sokoban_step_delta1) ->
+    (acc_reward f64 [n], done u8 [n], flags u8 [n], n_executed u8 [n]) as the other step entry points report them: rewards summed
+    left to right in doubles, done / flags of the last executed action."""
     d = np.asarray(delta)
     n, K = d.shape[0], d.shape[1]
-    info = d[:, :, 3]
+    info = d[:, :, 3] if d.ndim == 3 else d
     executed = (info >> 6) & 1
     table = np.array(REWARD_CODES + (0.0, 0.0, 0.0), dtype=np.float64)
     acc = np.zeros(n, dtype=np.float64)
@@ -163,8 +164,12 @@ class HostMirror:
         self.state = np.ascontiguousarray(state, dtype=np.uint8).reshape(-1, H * W).copy()
         self.n = self.state.shape[0]
 
-    def apply(self, delta):
+    def apply(self, delta, actions=None):
+        """Patches the mirror from a turn's records: [n, K, 4] records carry the cells; the one-byte records [n, K] need the
+        turn's `actions` [n, K] (the mirror knows where every player stands)."""
         d = np.asarray(delta)
+        if d.ndim == 2:
+            return self._apply1(d, np.asarray(actions).reshape(d.shape))
         for k in range(d.shape[1]):
             rec = d[:, k]
             rows = np.flatnonzero((rec[:, 3] >> 4) & 1)  # the player moved (a push moves it too)
@@ -173,9 +178,42 @@ class HostMirror:
             before, after, box = rec[rows, 0].astype(np.int64), rec[rows, 1].astype(np.int64), rec[rows, 2].astype(np.int64)
             self.state[rows, before] = self.fixed[rows, before]
             self.state[rows, after] = 5
+            if getattr(self, "_player", None) is not None:
+                self._player[rows] = after
             pushed = box != 0xff
             pr, pc = rows[pushed], box[pushed]
             self.state[pr, pc] = np.where(self.fixed[pr, pc] == 2, 3, 4)
+
+    def players(self):
+        """Cell of every room's player (from the mirrored state; -1 where a room has none)."""
+        has = (self.state == 5).any(axis=1)
+        return np.where(has, (self.state == 5).argmax(axis=1), -1).astype(np.int64)
+
+    def _apply1(self, d, actions):
+        step = np.array([0, -self.W, self.W, -1, 1, 0, 0, 0], dtype=np.int64)  # config.py:12: 1 up, 2 down, 3 left, 4 right
+        player = getattr(self, "_player", None)
+        if player is None:
+            player = self._player = self.players()
+        for k in range(d.shape[1]):
+            rec = d[:, k]
+            rows = np.flatnonzero((rec >> 4) & 1)  # the player moved (a push moves it too)
+            if rows.size == 0:
+                continue
+            dlt = step[actions[rows, k] & 7]
+            before = player[rows]
+            after = before + dlt
+            self.state[rows, before] = self.fixed[rows, before]
+            self.state[rows, after] = 5
+            player[rows] = after
+            pushed = (rec[rows] >> 7) & 1 == 1
+            pr, pc = rows[pushed], after[pushed] + dlt[pushed]
+            self.state[pr, pc] = np.where(self.fixed[pr, pc] == 2, 3, 4)
+
+    def refresh(self, rows, fixed, state):
+        """Rooms that were reset: take their new fixed / state rows."""
+        self.fixed[rows], self.state[rows] = fixed, state
+        if getattr(self, "_player", None) is not None:
+            self._player = self.players()
 
     def glyphs(self, rows=None):
         """[m, H*(W+1)] glyph codes with separators: what the render entry points write."""
@@ -185,6 +223,49 @@ class HostMirror:
         out = np.full((g.shape[0], self.H, self.W + 1), 7, dtype=np.uint8)
         out[:, :, : self.W] = g
         return out.reshape(g.shape[0], -1)
+
+
+class HostStepper:
+    """SokobanBatch.host_stepper: one CUDA graph = copy the pinned actions up, step (delta records), copy the records down."""
+
+    def __init__(self, batch, h_actions, record_bytes=1):
+        assert isinstance(h_actions, torch.Tensor) and h_actions.is_pinned() and h_actions.dtype == torch.uint8
+        assert record_bytes in (1, 4)
+        self.batch = batch
+        self.actions = h_actions if h_actions.dim() == 2 else h_actions.unsqueeze(1)
+        n, K = self.actions.shape
+        assert n == batch.n
+        self.K = K
+        self.stream = torch.cuda.Stream(batch.device)
+        self._d_act = torch.empty((n, K), dtype=torch.uint8, device=batch.device)
+        shape = (n, K) if record_bytes == 1 else (n, K, 4)
+        self._h_rec = torch.empty(shape, dtype=torch.uint8, pin_memory=True)
+        self.records = self._h_rec.numpy()
+        self.record_bytes = record_bytes
+        self.stream.wait_stream(torch.cuda.current_stream(batch.device))
+        with torch.cuda.stream(self.stream):
+            # once outright, executing NO action (n_actions = 0 leaves rooms and counters as they are): the batch's record buffer
+            # and the library's state exist before the capture
+            self._body(torch.zeros(n, dtype=torch.uint8, device=batch.device))
+            self.stream.synchronize()
+            self.graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self.graph, stream=self.stream):
+                self._body(None)
+
+    def _body(self, n_actions):
+        self._d_act.copy_(self.actions, non_blocking=True)
+        rec = self.batch.step_delta(self._d_act, n_actions, record_bytes=self.record_bytes)  # the batch's own (persistent) buffer
+        self._h_rec.copy_(rec, non_blocking=True)
+
+    def launch(self):
+        with torch.cuda.stream(self.stream):
+            self.graph.replay()
+        self.batch._state_stale = True
+        self.batch.obs_stale = True
+
+    def wait(self):
+        self.stream.synchronize()
+        return self.records
 
 
 def unpack3_rooms(state3, HW, out=None):
@@ -458,15 +539,27 @@ class SokobanBatch:
                       _lib.ptr(self.flags), _lib.ptr(self.n_executed), _lib.ptr(obs), self.ctx.stream()))
         return StepOut(self.reward, self.done, self.flags, self.n_executed, obs if render else self.obs)
 
-    def step_delta(self, actions, n_actions=None):
-        """The compact step reporting DELTAS (ragen_sokoban_step_delta): returns the device tensor uint8 [n, K, 4]; nothing is
-        rendered and the result arrays are not written (decode_delta / HostMirror turn deltas into them on the host)."""
+    def step_delta(self, actions, n_actions=None, record_bytes=4):
+        """The compact step reporting DELTAS (ragen_sokoban_step_delta): returns the device tensor uint8 [n, K, 4] - or, with
+        record_bytes=1, the one-byte records [n, K] of ragen_sokoban_step_delta1; nothing is rendered and the result arrays are
+        not written (decode_delta / HostMirror turn deltas into them on the host)."""
         if not (self.compact or self.glyph3):
             raise ValueError("step_delta steps nibble or glyph rooms: construct the batch with compact=True or rooms='glyph3'")
         if actions.dim() == 1:
             actions = actions.unsqueeze(1)
         assert actions.dtype == torch.uint8 and actions.is_cuda and actions.is_contiguous() and actions.shape[0] == self.n
         K = actions.shape[1]
+        if record_bytes == 1:
+            buf = getattr(self, "_delta1", None)
+            if buf is None or buf.shape[1] != K:
+                buf = self._delta1 = torch.zeros((self.n, K), dtype=torch.uint8, device=self.device)
+            rooms = self.state3 if self.glyph3 else self.state4
+            _lib.check(self.lib.ragen_sokoban_step_delta1(
+                self.ctx.handle, self.n, self.H, self.W, self.num_boxes, self.max_steps, _lib.ptr(actions), K, _lib.ptr(n_actions),
+                4 if self.glyph3 else 3, _lib.ptr(rooms), _lib.ptr(self.meta), _lib.ptr(buf), self.ctx.stream()))
+            self._state_stale = True
+            self.obs_stale = True
+            return buf
         buf = getattr(self, "_delta", None)
         if buf is None or buf.shape[1] != K:
             buf = self._delta = torch.zeros((self.n, K, 4), dtype=torch.uint8, device=self.device)
@@ -518,8 +611,8 @@ class SokobanBatch:
     # -- pipelined host-buffer stepping: launch step i+1 while the results of step i drain ------------------------------------
     def step_host_begin(self, h_actions, fmt="delta"):
         """h_actions: PINNED uint8 host tensor [n] or [n, K].  Queues host->device copy + step on the compute stream and the
-        device->host copy of the results on a copy stream; returns a ticket for step_host_end.  fmt: "delta" (4 B per action)
-        or 3 (three-bit rows + scalars, 49 B per 10x10 env).  Up to two tickets may be open per batch."""
+        device->host copy of the results on a copy stream; returns a ticket for step_host_end.  fmt: "delta" (4 B per action),
+        "delta1" (1 B per action) or 3 (three-bit rows + scalars, 49 B per 10x10 env).  Up to two tickets may be open per batch."""
         assert isinstance(h_actions, torch.Tensor) and h_actions.is_pinned() and h_actions.dtype == torch.uint8
         h_act = h_actions if h_actions.dim() == 2 else h_actions.unsqueeze(1)
         pipe = getattr(self, "_pipe", None)
@@ -536,9 +629,11 @@ class SokobanBatch:
         d_act.copy_(h_act, non_blocking=True)
         if fmt == "delta":
             src = self.step_delta(d_act).view(-1)
+        elif fmt == "delta1":
+            src = self.step_delta(d_act, record_bytes=1).view(-1)
         else:
             if self.glyph3:
-                raise ValueError("glyph rooms: pipelined host stepping carries deltas (fmt='delta'); full rows come from step_host")
+                raise ValueError("glyph rooms: pipelined host stepping carries deltas (fmt='delta' / 'delta1'); full rows come from step_host")
             self.step(d_act, packed=3)
             src = self._slab[: self._off_sc + 11 * self.n]
         h = self._pin(("pipe", fmt, j), (src.numel(),), torch.uint8)
@@ -553,15 +648,25 @@ class SokobanBatch:
         return (fmt, h, done, h_act.shape[1])
 
     def step_host_end(self, ticket):
-        """Waits for the ticket's results.  "delta": numpy uint8 [n, K, 4]; 3: (rows, reward, done, flags, n_executed)."""
+        """Waits for the ticket's results.  "delta": numpy uint8 [n, K, 4]; "delta1": [n, K]; 3: (rows, reward, done, flags, n_executed)."""
         fmt, h, done, K = ticket
         done.synchronize()
         hn = h.numpy()
         if fmt == "delta":
             return hn.reshape(self.n, K, 4)
+        if fmt == "delta1":
+            return hn.reshape(self.n, K)
         n_, o = self.n, self._off_sc
         return (hn[: n_ * self._b3].reshape(n_, -1), hn[o: o + 8 * n_].view(np.float64), hn[o + 8 * n_: o + 9 * n_],
                 hn[o + 9 * n_: o + 10 * n_], hn[o + 10 * n_: o + 11 * n_])
+
+    def host_stepper(self, h_actions, record_bytes=1):
+        """A captured host-buffer step for callers that step the same batch many times: returns a HostStepper whose launch() replays
+        [actions host->device | step with delta records | records device->host] as ONE CUDA graph on the stepper's own stream -
+        a few microseconds of host work per step instead of a dozen framework calls - and whose wait() returns the records
+        (numpy view of pinned memory, decode_delta / HostMirror.apply take them).  h_actions: the PINNED uint8 tensor [n] or
+        [n, K] the caller fills before every launch()."""
+        return HostStepper(self, h_actions, record_bytes)
 
     def _pin(self, name, shape, dtype):
         key = (name, tuple(shape), dtype)

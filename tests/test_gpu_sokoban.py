@@ -476,30 +476,41 @@ def test_step_deltas_rebuild_rooms_rewards_and_rows_on_the_host(H, W, nb, n, K):
     o = SokobanBatchOracle(fixed, state, H, W, nb, max_steps)
     b = SokobanBatch(n, (H, W), nb, max_steps, search_depth=20, compact=True)
     twin = SokobanBatch(n, (H, W), nb, max_steps, search_depth=20, compact=True)
+    one = SokobanBatch(n, (H, W), nb, max_steps, search_depth=20, rooms="glyph3" if K % 2 else "nibbles")  # one-byte records
     b.load_rooms(fixed, state)
     twin.load_rooms(fixed, state)
+    one.load_rooms(fixed, state)
     mirror = b.host_mirror()
-    assert np.array_equal(mirror.glyphs(), o.glyphs())
+    mirror1 = one.host_mirror()
+    assert np.array_equal(mirror.glyphs(), o.glyphs()) and np.array_equal(mirror1.glyphs(), o.glyphs())
     for turn in range(50):
         acts = rng.integers(0, 5, (n, K)).astype(np.uint8)
         na = rng.integers(0, K + 1, n).astype(np.uint8) if turn % 4 == 3 else None
         d_act = torch.from_numpy(acts).cuda()
         d_na = None if na is None else torch.from_numpy(na).cuda()
         delta = b.step_delta(d_act, d_na).cpu().numpy()
+        delta1 = one.step_delta(d_act, d_na, record_bytes=1).cpu().numpy()
         full = twin.step(d_act, d_na, packed=3)
         acc, done, flags, nexec = o.step_turn(acts, na)
         mirror.apply(delta)
-        got = decode_delta(delta)
-        for g, w, f in zip(got, (acc, done, flags, nexec), (full.reward, full.done, full.flags, full.n_executed)):
-            assert np.array_equal(g, w) and np.array_equal(g, f.cpu().numpy()), turn
+        mirror1.apply(delta1, acts)
+        assert delta1.shape == (n, K) and np.array_equal(delta1 & 0x7f, delta[:, :, 3])  # the info byte; bit 7: a box moved
+        assert np.array_equal(delta1 >> 7, ((delta[:, :, 2] != 0xff) & (delta[:, :, 3] != 0)).astype(np.uint8))
+        for got in (decode_delta(delta), decode_delta(delta1)):
+            for g, w, f in zip(got, (acc, done, flags, nexec), (full.reward, full.done, full.flags, full.n_executed)):
+                assert np.array_equal(g, w) and np.array_equal(g, f.cpu().numpy()), turn
         assert np.array_equal(mirror.state, o.state) and np.array_equal(b.state.cpu().numpy(), o.state)
+        assert np.array_equal(mirror1.state, o.state) and np.array_equal(one.state.cpu().numpy(), o.state)
         assert np.array_equal(mirror.glyphs(), unpack3_glyphs(full.obs.cpu().numpy(), H, W)), turn
+        assert np.array_equal(mirror1.glyphs(), mirror.glyphs())
         if turn == 20 and H == 6:  # a partial reset: the mirror is refreshed for the slots that were reset
             slots = [1, n // 2]
             b.reset([5, 6], slots=slots)
             twin.reset([5, 6], slots=slots)
+            one.reset([5, 6], slots=slots)
             st, fx = b.state.cpu().numpy(), b.fixed.cpu().numpy()
             mirror.state[slots], mirror.fixed[slots] = st[slots], fx[slots]
+            mirror1.refresh(slots, fx[slots], st[slots])
             o = SokobanBatchOracle(fx, st, H, W, nb, max_steps)
             o.env_steps = b.env_steps.cpu().numpy().astype(np.int64)
             o.on_target = b.on_target.cpu().numpy().astype(np.int64)
@@ -512,7 +523,7 @@ def test_pipelined_host_steps_equal_the_plain_ones():
     n, H, W, nb = 5000, 10, 10, 2
     fixed, state = synthetic_rooms(n, H, W, nb, seed=3)
     rng = np.random.default_rng(4)
-    for fmt in ("delta", 3):
+    for fmt in ("delta", "delta1", 3):
         a = SokobanBatch(n, (H, W), nb, 100, compact=True)
         t = SokobanBatch(n, (H, W), nb, 100, compact=True)
         a.load_rooms(fixed, state)
@@ -524,7 +535,7 @@ def test_pipelined_host_steps_equal_the_plain_ones():
                 tickets.append(a.step_host_begin(acts[i + 1], fmt))  # step i+1 is queued before step i's results are read
             res = a.step_host_end(tickets[i])
             rows, rew, done, flags, nex = t.step_host(acts[i], packed=3)
-            if fmt == "delta":
+            if fmt in ("delta", "delta1"):
                 acc, d, f, k = decode_delta(res)
                 assert np.array_equal(acc, rew) and np.array_equal(d, done) and np.array_equal(f, flags) and np.array_equal(k, nex)
             else:
@@ -661,3 +672,34 @@ def test_compact_rooms_refuse_other_shapes():
     rc = b.lib.ragen_sokoban_step_compact(b.ctx.handle, 4, 7, 6, 1, 50, _lib.ptr(a), 1, None, _lib.ptr(z), _lib.ptr(b.meta), _lib.ptr(b.reward),
                                           _lib.ptr(b.done), _lib.ptr(b.flags), _lib.ptr(b.n_executed), None, b.ctx.stream())
     assert rc != 0
+
+
+def test_captured_host_stepper_equals_the_plain_host_steps():
+    """SokobanBatch.host_stepper: [actions up | step | records down] replayed as one CUDA graph, two steppers in flight on two
+    batches; records, rooms and counters equal step_host's on twin batches, and building a stepper leaves the rooms alone."""
+    from ragen_b200.env.sokoban import SokobanBatch, decode_delta
+
+    n, H, W, nb = 5000, 10, 10, 2
+    fixed, state = synthetic_rooms(n, H, W, nb, seed=5)
+    rng = np.random.default_rng(6)
+    for rooms, rb in (("glyph3", 1), ("nibbles", 4)):
+        pair = [SokobanBatch(n, (H, W), nb, 100, rooms=rooms) for _ in range(2)]
+        twins = [SokobanBatch(n, (H, W), nb, 100, rooms=rooms) for _ in range(2)]
+        for b in pair + twins:
+            b.load_rooms(fixed, state)
+        bufs = [torch.zeros(n, dtype=torch.uint8).pin_memory() for _ in range(2)]
+        steppers = [pair[j].host_stepper(bufs[j], record_bytes=rb) for j in range(2)]
+        assert all(torch.equal(p_.state, t_.state) for p_, t_ in zip(pair, twins))  # construction executed no action
+        acts = [rng.integers(0, 5, n).astype(np.uint8) for _ in range(8)]
+        bufs[0].numpy()[:] = acts[0]
+        steppers[0].launch()
+        for i in range(8):
+            if i + 1 < 8:  # step i+1 (the other batch) is queued before step i's records are read
+                bufs[(i + 1) & 1].numpy()[:] = acts[i + 1]
+                steppers[(i + 1) & 1].launch()
+            rec = steppers[i & 1].wait()
+            rows, rew, done, flags, nex = twins[i & 1].step_host(acts[i], packed=3)
+            acc, d, f, k = decode_delta(rec)
+            assert np.array_equal(acc, rew) and np.array_equal(d, done) and np.array_equal(f, flags) and np.array_equal(k, nex), i
+        for p_, t_ in zip(pair, twins):
+            assert torch.equal(p_.state, t_.state) and torch.equal(p_.env_steps, t_.env_steps)

@@ -484,25 +484,26 @@ def run_native(args):
             # calls to a replay and a stream wait.  One stepper per rotating action slab and batch; two steps in flight.
             eager1 = e2e
             try:
+                NBE = len(batches) if RA % len(batches) == 0 else 2  # batches stepped in turn; NBE - 1 steps are in flight behind the one awaited
                 steppers = {}
-                for j in range(2):
-                    for a_ in range(RA):
-                        if (a_ & 1) == j or RA == 1:
-                            steppers[(j, a_)] = batches[j].host_stepper(host_actions[a_], record_bytes=1)
+                for i_ in range(RA):
+                    steppers[(i_ % NBE, i_ % RA)] = batches[i_ % NBE].host_stepper(host_actions[i_ % RA], record_bytes=1)
 
                 def run_graph(steps):
                     def st(i):
-                        return steppers[(i & 1, i % RA)]
-                    for w in range(4):
+                        return steppers[(i % NBE, i % RA)]
+                    for w in range(RA):
                         st(w).launch()
                         st(w).wait()
                     barrier()
                     t0 = time.perf_counter()
-                    st(0).launch()
+                    for i in range(NBE - 1):
+                        st(i).launch()
                     for i in range(steps):
-                        st(i + 1).launch()
+                        st(i + NBE - 1).launch()
                         st(i).wait()
-                    st(steps).wait()  # drain the look-ahead step (not counted)
+                    for i in range(steps, steps + NBE - 1):
+                        st(i).wait()  # drain the look-ahead steps (not counted)
                     barrier()
                     return max_over_ranks(time.perf_counter() - t0)
 
@@ -511,8 +512,8 @@ def run_native(args):
                        "ms_per_step": 1e3 * runs[1] / e2e_steps, "ms_per_step_runs": [round(1e3 * t / e2e_steps, 4) for t in runs],
                        "api": "SokobanBatch.host_stepper(pinned actions, record_bytes=1).launch() / .wait() -> one CUDA graph per step: "
                               "actions host->device, ragen_sokoban_step_delta1 (C ABI, %s), one byte per action device->host into pinned "
-                              "memory; two steps in flight; decode_delta / HostMirror rebuild rewards, flags, rooms and glyph rows on "
-                              "the host on demand" % rooms_name,
+                              "memory; %d batches stepped in turn, %d steps in flight; decode_delta / HostMirror rebuild rewards, flags, rooms "
+                              "and glyph rows on the host on demand" % (rooms_name, NBE, NBE),
                        "eager_delta1": eager1}
             except Exception as ex:  # capture unavailable: the eager leg stays the line's number, and says why
                 e2e = dict(eager1, graph_leg_failed=f"{type(ex).__name__}: {ex}"[:200])

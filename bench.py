@@ -52,6 +52,7 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-reset", action="store_true", help="skip the batched-reset leg (room generator + solver at config 4 size)")
+    ap.add_argument("--no-chains", action="store_true", help="`value` from one chain of launches instead of one chain per resident batch")
     ap.add_argument("--no-graph", action="store_true", help="issue the launches of a step from Python instead of replaying a CUDA graph")
     ap.add_argument("--launches-per-step", type=int, default=128,
                     help="back-to-back step launches (alternating batches) that make ONE bench step; env-steps per step = envs x this")
@@ -347,6 +348,8 @@ def run_native(args):
     # Several batches of n envs each, stepped in rotation: ONE batch's lines (58 MB with glyph rooms, 108 MB with nibble rooms) would
     # fit the 126 MB L2, so between two touches of a line the other batches' lines (>= 1.6 x L2 in all) go through it.
     NBATCH = resident_batches(n, args.obs, args.rooms)
+    if os.environ.get("RAGEN_BENCH_BATCHES"):  # probing: more batches in rotation (an even divisor of --launches-per-step and of 8)
+        NBATCH = int(os.environ["RAGEN_BENCH_BATCHES"])
     batches = []
     for j in range(NBATCH):
         if j:
@@ -380,7 +383,7 @@ def run_native(args):
 
     one_step(0)  # module load, cudaFuncSetAttribute: before any capture
     torch.cuda.synchronize()
-    launch_mode, graph = "loop", None
+    launch_mode, graph, chains = "loop", None, None
     if not args.no_graph and R % NBATCH == 0 and R % RA == 0:
         try:
             side = torch.cuda.Stream(dev)
@@ -392,8 +395,22 @@ def run_native(args):
             with torch.cuda.graph(graph, stream=side):
                 one_step(0)
             launch_mode = "cuda_graph"
+            if not args.no_chains:
+                # the resident batches are independent jobs: each batch's launches form one chain (its own stream inside the
+                # capture), the chains meet again at the end of the step.  Launches of different batches overlap where one kernel
+                # drains and the next ramps up; launches of the same batch stay in order.
+                chains = torch.cuda.CUDAGraph()
+                lanes = [torch.cuda.Stream(dev) for _ in range(NBATCH)]
+                with torch.cuda.graph(chains, stream=side):
+                    for b_i, lane_s in enumerate(lanes):
+                        lane_s.wait_stream(side)
+                        with torch.cuda.stream(lane_s):
+                            for i in range(b_i, R, NBATCH):
+                                batches[i % NBATCH].step(actions[i % RA], packed=packed)
+                    for lane_s in lanes:
+                        side.wait_stream(lane_s)
         except Exception as e:  # the plain loop is the same GPU work; say which one ran
-            graph, launch_mode = None, f"loop (graph capture failed: {type(e).__name__})"
+            graph, chains, launch_mode = None, None, f"loop (graph capture failed: {type(e).__name__})"
             torch.cuda.synchronize()
 
     def run_step(i):
@@ -418,6 +435,22 @@ def run_native(args):
     # region divided by the launches; an event pair around every launch would itself cost ~2 us per launch
     kern_ms = total_ms / max(1, launches)
     total_ms = max_over_ranks(total_ms)
+    serial = None
+    if chains is not None:
+        # `value`: the same launches with the NBATCH batches as independent chains.  The region above (one launch after the other)
+        # stays the source of roofline.kernel_ms / achieved / frac - a launch's own duration, what ncu's launch list can be held
+        # against - and is reported as `serial_chain`
+        serial = {"value": n * world * launches / (total_ms * 1e-3), "unit": UNIT, "ms_per_step": total_ms / args.steps}
+        for i in range(max(args.warmup, 3)):
+            chains.replay()
+        barrier()
+        t_begin.record()
+        for i in range(args.steps):
+            chains.replay()
+        t_end.record()
+        barrier()
+        total_ms = max_over_ranks(t_begin.elapsed_time(t_end))
+        launch_mode = f"cuda_graph, {NBATCH} per-batch chains (serial_chain / roofline: one chain)"
 
     # ---- end to end with host buffers ----------------------------------------------------------------
     e2e = None
@@ -581,12 +614,18 @@ def run_native(args):
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
                 "config": workload_config(world, n, args.obs, args.rooms, R), "launch_mode": launch_mode,
-                "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
+                "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "serial_chain": serial,
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                              "traffic": traffic, "traffic_source": traffic_src, "kernel": kname, "kernel_ms": kern_ms,
                              "bytes_per_env_step": moved, "peak_source": peak_src,
                              "frac_survey_431B": BYTES_PER_STEP * n / (kern_ms * 1e-3) / 1e9 / peak,
-                             "note": "achieved / frac count the bytes this kernel has to move per env-step (glyph rooms: room in and out 76 - the room is the "
+                             "achieved_with_overlap": moved * n * launches / (total_ms * 1e-3) / 1e9 / world,
+                             "frac_with_overlap": moved * n * launches / (total_ms * 1e-3) / 1e9 / world / peak,
+                             "note": "kernel_ms / achieved / frac: launches one after the other (serial_chain) - a launch's own duration; "
+                                     "achieved_with_overlap / frac_with_overlap: the bytes of `value`'s region, where launches of independent "
+                                     "batches overlap at their ends (above 1.0 of the torch copy_ figure the peak was measured with; the same "
+                                     "with 8 batches = 464 MB in rotation, so not L2).  "
+                                     "achieved / frac count the bytes this kernel has to move per env-step (glyph rooms: room in and out 76 - the room is the "
                                      "observation - record r+w 16, action 1, results 11 = 104; nibble rooms: 100 + 16 + 1 + 11 + three-bit rows 38 = 166; 266 / 283 / "
                                      "338 B with byte rooms and three-bit / nibble / byte rows).  frac_survey_431B applies SURVEY.md 8(d)'s figure, "
                                      "which charges a 100 B room_fixed read and 110 B of glyph bytes this kernel does not move: it is "

@@ -32,3 +32,6 @@ print(s.getvalue()[:9000])
 s = io.StringIO()
 pstats.Stats(pr, stream=s).sort_stats("tottime").print_stats(25)
 print(s.getvalue()[:6000])
+s = io.StringIO()
+pstats.Stats(pr, stream=s).print_callers("inner|fromnumeric.py.*sum|tolist")
+print(s.getvalue()[:5000])

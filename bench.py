@@ -619,8 +619,8 @@ def run_native(args):
                              "traffic": traffic, "traffic_source": traffic_src, "kernel": kname, "kernel_ms": kern_ms,
                              "bytes_per_env_step": moved, "peak_source": peak_src,
                              "frac_survey_431B": BYTES_PER_STEP * n / (kern_ms * 1e-3) / 1e9 / peak,
-                             "achieved_with_overlap": moved * n * launches / (total_ms * 1e-3) / 1e9 / world,
-                             "frac_with_overlap": moved * n * launches / (total_ms * 1e-3) / 1e9 / world / peak,
+                             "achieved_with_overlap": moved * n * launches / (total_ms * 1e-3) / 1e9,  # per GPU: n and launches are a rank's
+                             "frac_with_overlap": moved * n * launches / (total_ms * 1e-3) / 1e9 / peak,
                              "note": "kernel_ms / achieved / frac: launches one after the other (serial_chain) - a launch's own duration; "
                                      "achieved_with_overlap / frac_with_overlap: the bytes of `value`'s region, where launches of independent "
                                      "batches overlap at their ends (above 1.0 of the torch copy_ figure the peak was measured with; the same "

@@ -17,6 +17,7 @@
 #include <type_traits>
 
 #include "common.cuh"
+#include "scan_tiles.cuh"
 
 namespace {
 
@@ -1070,10 +1071,12 @@ __global__ void __launch_bounds__(BS_T, 4) gae_scan_kernel(int B, int T, const f
 // at the same flat index.  Results leave by bulk stores too - whole 16-byte groups inside the row - and the up to three words at
 // either end of a row by ordinary stores.  288 threads x 8 words = 2304 words per tile: a row of T = 2047 fits one tile whatever
 // its alignment.  Needs 16-byte-aligned base pointers and B * T % 16 == 0; everything else takes the kernel above.
-constexpr int BT_T = 288;            // threads (9 warps)
-constexpr int BT_K = 8;              // words per thread
-constexpr int BT_W = BT_T * BT_K;    // words per tile
-constexpr int BT_NW = BT_T / 32;     // warps
+using scan_tiles::BT_K;
+using scan_tiles::BT_NW;
+using scan_tiles::BT_T;
+using scan_tiles::BT_W;
+using scan_tiles::ScanTile;
+using scan_tiles::TileGeom;
 
 struct __align__(128) BulkStage {
   float r[BT_W];           // rewards in, advantages out
@@ -1081,54 +1084,25 @@ struct __align__(128) BulkStage {
   uint8_t m[BT_W + 48];    // mask bytes of the tile's words, from the 16-byte boundary at or below the tile's first word
 };
 
-struct ScanTile {  // which (row, chunk) a CTA works on; chunks of a row run right to left
-  int row, c;
-};
-
-struct TileGeom {
-  int64_t cw0;         // first flat word of the tile (a multiple of four)
-  int nw;              // staged words (a multiple of four)
-  int rel_lo, rel_hi;  // the row, in words of this tile: word w of the tile belongs to the row iff rel_lo <= w < rel_hi
-  int mshift;          // the tile's first mask byte sits at S.m[mshift] (0, 4, 8 or 12)
-  bool right_end;      // the tile holds the row's last token
-};
-
-// the flat word index of a row's first token is 64-bit; everything relative to the tile fits an int (|.| <= T + BT_W)
-__device__ __forceinline__ int bt_row_chunks(int row, int T) {
-  const int off = (int)(((int64_t)row * T) & 3);  // words between the 16-byte boundary below the row and its first token
-  return (((off + T + 3) & ~3) + BT_W - 1) / BT_W;
-}
+// tiles of a CTA: rows in grid-stride order, the chunks of a row right to left (geometry: scan_tiles.cuh)
 __device__ __forceinline__ ScanTile bt_first(int B, int T) {
   ScanTile t{(int)blockIdx.x, 0};
-  if (t.row < B) t.c = bt_row_chunks(t.row, T) - 1;
+  if (t.row < B) t.c = scan_tiles::row_chunks(t.row, T) - 1;
   return t;
 }
 __device__ __forceinline__ ScanTile bt_advance(ScanTile t, int B, int T) {
   if (t.c > 0) return ScanTile{t.row, t.c - 1};
   t.row += gridDim.x;
-  t.c = t.row < B ? bt_row_chunks(t.row, T) - 1 : 0;
+  t.c = t.row < B ? scan_tiles::row_chunks(t.row, T) - 1 : 0;
   return t;
 }
-__device__ __forceinline__ TileGeom bt_geom(ScanTile t, int T) {
-  const int64_t lo = (int64_t)t.row * T;
-  const int off = (int)(lo & 3);
-  const int span = (off + T + 3) & ~3;  // aligned words that cover the row
-  const int c0 = t.c * BT_W;            // the tile's first word, counted from the row's aligned start
-  TileGeom g;
-  g.cw0 = (lo - off) + c0;
-  g.right_end = c0 + BT_W >= span;
-  g.nw = g.right_end ? span - c0 : BT_W;
-  g.rel_lo = off - c0;
-  g.rel_hi = g.rel_lo + T;
-  g.mshift = (int)(g.cw0 & 15);
-  return g;
-}
+__device__ __forceinline__ TileGeom bt_geom(ScanTile t, int T) { return scan_tiles::geom(t, T); }
 // one thread: arm the stage's barrier and queue the three bulk loads of tile t
 __device__ __forceinline__ void bt_issue(ScanTile t, int T, BulkStage& S, uint64_t* bar, const float* rewards, const float* values,
                                          const uint8_t* mask) {
   const TileGeom g = bt_geom(t, T);
-  const int64_t cw1 = g.cw0 + g.nw;
-  const int64_t mb0 = g.cw0 & ~(int64_t)15, mb1 = (cw1 + 15) & ~(int64_t)15;  // B * T % 16 == 0: never past the tensor
+  int64_t mb0, mb1;
+  scan_tiles::mask_window(g, mb0, mb1);  // B * T % 16 == 0: never past the tensor
   const uint32_t wbytes = (uint32_t)g.nw * 4u, mbytes = (uint32_t)(mb1 - mb0);
   mbar_expect_tx(bar, (values ? 2u : 1u) * wbytes + mbytes);
   tma_load_1d(S.r, rewards + g.cw0, wbytes, bar);
@@ -1139,11 +1113,9 @@ __device__ __forceinline__ void bt_issue(ScanTile t, int T, BulkStage& S, uint64
 // row leave by bulk store (lane 0, one committed group), the words at the row's ends one by one (lanes 1..11)
 // (S.r -> adv, S.v -> ret; ret may be NULL)
 __device__ __forceinline__ void bt_store(const TileGeom& g, BulkStage& S, float* adv, float* ret, int lane) {
-  const int ra0 = g.rel_lo > 0 ? g.rel_lo : 0, ra1 = g.rel_hi < g.nw ? g.rel_hi : g.nw;
-  const int g0 = (g.rel_lo + 3) & ~3, g1 = g.rel_hi & ~3;
-  const int rs0 = g0 > 0 ? g0 : 0, rs1 = g1 < g.nw ? g1 : g.nw;
-  const bool bulk = rs1 > rs0;
-  const int left_end = bulk ? rs0 : ra1;
+  const scan_tiles::StorePlan sp = scan_tiles::store_plan(g);
+  const int ra0 = sp.ra0, ra1 = sp.ra1, rs0 = sp.rs0, rs1 = sp.rs1, left_end = sp.left_end;
+  const bool bulk = sp.bulk;
   if (lane == 0 && bulk) {
     tma_store_1d(adv + g.cw0 + rs0, S.r + rs0, (uint32_t)(rs1 - rs0) * 4u);
     if (ret) tma_store_1d(ret + g.cw0 + rs0, S.v + rs0, (uint32_t)(rs1 - rs0) * 4u);
@@ -1366,7 +1338,6 @@ __global__ void __launch_bounds__(BT_T, BI_CTAS) bilevel_scan_bulk_kernel(int B,
       // one bit per non-zero byte: 0x01 per byte, then the four bits gathered by a multiply (no two partial products meet)
       const uint32_t nlo = __vsetne4(mwp[0], 0u), nhi = __vsetne4(mwp[1], 0u);
       mk = ((((nlo * 0x00204081u) >> 21) & 0xfu) | ((((nhi * 0x00204081u) >> 21) & 0xfu) << 4)) & inb;
-#pragma unroll
       const float r_[BT_K] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};  // not kept: the few reward positions re-read theirs
 #pragma unroll
       for (int k = 0; k < BT_K; ++k) ek |= (r_[k] != 0.0f) ? (1u << k) : 0u;  // reward_mask = token_level_rewards.bool() (:50)
@@ -1403,45 +1374,51 @@ __global__ void __launch_bounds__(BT_T, BI_CTAS) bilevel_scan_bulk_kernel(int B,
     }
     const float In_z = zr ? z_from : Gz, In_e = er ? e_from : Ge;  // the states entering this thread from the right
     const float Sz = zbits ? z_first : Gz, Se = ebits ? e_first : Ge;  // ... and leaving the warp on the left (tid 0: the tile)
+    // A warp whose 256 words hold no reward position (three warps in four at a handful of rewards per row) takes the short way
+    // through both rounds: its H maps are the identity and its L walks need no reward tests.  any_e is warp-uniform; the CTA
+    // barriers stay outside the branches.
+    const bool any_e = ew != 0;
     // ---- round 2: H, the turn-level recurrence over the reward positions -----------------------------------------------------------
-    float Ah = 1.0f, Bh = 0.0f;
-    {
+    float PA = 1.0f, PB = 0.0f;
+    if (any_e) {
       float E = In_e;
 #pragma unroll
       for (int k = BT_K - 1; k >= 0; --k)
         if ((ew >> k) & 1u) {  // a handful of reward positions per row: most steps are skipped by the whole warp
           const bool e = (ek >> k) & 1u;
-          const float nb = (S.r[w0 + k] + hgamma * E - vv[k]) + hgl * Bh;
-          Bh = e ? nb : Bh;
-          Ah = e ? hgl * Ah : Ah;
+          const float nb = (S.r[w0 + k] + hgamma * E - vv[k]) + hgl * PB;
+          PB = e ? nb : PB;
+          PA = e ? hgl * PA : PA;
           E = e ? vv[k] : E;
         }
-    }
-    float PA = Ah, PB = Bh;
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const float a2 = __shfl_down_sync(FULL, PA, o), b2 = __shfl_down_sync(FULL, PB, o);
-      const bool on = lane + o < 32;
-      PB = on ? PB + PA * b2 : PB;
-      PA = on ? PA * a2 : PA;
+      for (int o = 1; o < 32; o <<= 1) {
+        const float a2 = __shfl_down_sync(FULL, PA, o), b2 = __shfl_down_sync(FULL, PB, o);
+        const bool on = lane + o < 32;
+        PB = on ? PB + PA * b2 : PB;
+        PA = on ? PA * a2 : PA;
+      }
     }
     if (lane == 0) { s_ha[warp] = PA; s_hb[warp] = PB; }
     __syncthreads();
     float Gh = h_c;
+    if (any_e || warp == 0) {  // warp 0 always: its first thread carries the state out of the tile
 #pragma unroll
-    for (int w = BT_NW - 1; w >= 1; --w) {
-      const float nh = s_hb[w] + s_ha[w] * Gh;
-      Gh = w > warp ? nh : Gh;
+      for (int w = BT_NW - 1; w >= 1; --w) {
+        const float nh = s_hb[w] + s_ha[w] * Gh;
+        Gh = w > warp ? nh : Gh;
+      }
     }
     const float Sh = PB + PA * Gh;
-    float In_h = __shfl_down_sync(FULL, Sh, 1);
-    if (lane == 31) In_h = Gh;
     float hv[BT_K];  // turn-level advantage at the thread's reward positions
-    {
+#pragma unroll
+    for (int k = 0; k < BT_K; ++k) hv[k] = 0.0f;
+    if (any_e) {
+      float In_h = __shfl_down_sync(FULL, Sh, 1);
+      if (lane == 31) In_h = Gh;
       float E = In_e, H = In_h;
 #pragma unroll
-      for (int k = BT_K - 1; k >= 0; --k) {
-        hv[k] = 0.0f;
+      for (int k = BT_K - 1; k >= 0; --k)
         if ((ew >> k) & 1u) {
           const bool e = (ek >> k) & 1u;
           const float nh = (S.r[w0 + k] + hgamma * E - vv[k]) + hgl * H;
@@ -1449,28 +1426,36 @@ __global__ void __launch_bounds__(BT_T, BI_CTAS) bilevel_scan_bulk_kernel(int B,
           hv[k] = H;
           E = e ? vv[k] : E;
         }
-      }
     }
     // ---- round 3: L, the token-level recurrence over the loss-mask tokens ----------------------------------------------------------
-    float At = 1.0f, Bt = 0.0f;
-    {
-      float Z = In_z;
-#pragma unroll
-      for (int k = BT_K - 1; k >= 0; --k) {
-        const bool m = (mk >> k) & 1u;
-        float ak = gl, bk = gamma * Z - vv[k];
+    // one step of the walk: the map of word k applied to (A, B) (compose) or to X (re-walk)
+    auto step_map = [&](auto has_e, int k, float Z, float& ak, float& bk) {
+      ak = gl;
+      bk = gamma * Z - vv[k];
+      if constexpr (decltype(has_e)::value) {
         if ((ew >> k) & 1u) {  // restart from the updated reward: next value 0, lastgaelam 0 (:78-81)
           const bool e = (ek >> k) & 1u;
           ak = e ? 0.0f : ak;
           bk = e ? (hv[k] + vv[k]) - vv[k] : bk;
         }
+      }
+    };
+    auto compose3 = [&](auto has_e, float& At, float& Bt) {
+      float Z = In_z;
+#pragma unroll
+      for (int k = BT_K - 1; k >= 0; --k) {
+        const bool m = (mk >> k) & 1u;
+        float ak, bk;
+        step_map(has_e, k, Z, ak, bk);
         Bt = m ? bk + ak * Bt : Bt;
         At = m ? ak * At : At;
         Z = m ? vv[k] : Z;
       }
-    }
-    PA = At;
-    PB = Bt;
+    };
+    PA = 1.0f;
+    PB = 0.0f;
+    if (any_e) compose3(std::true_type{}, PA, PB);
+    else compose3(std::false_type{}, PA, PB);
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
       const float a2 = __shfl_down_sync(FULL, PA, o), b2 = __shfl_down_sync(FULL, PB, o);
@@ -1490,18 +1475,14 @@ __global__ void __launch_bounds__(BT_T, BI_CTAS) bilevel_scan_bulk_kernel(int B,
     float In_t = __shfl_down_sync(FULL, St, 1);
     if (lane == 31) In_t = Gt;
     float a[BT_K], rt[BT_K];
-    {
+    float s1 = 0.0f, s2 = 0.0f;  // the thread's eight masked advantages summed in fp32, then added to the fp64 totals
+    auto rewalk3 = [&](auto has_e) {
       float Z = In_z, X = In_t;
-      float s1 = 0.0f, s2 = 0.0f;  // the thread's eight masked advantages summed in fp32, then added to the fp64 totals
 #pragma unroll
       for (int k = BT_K - 1; k >= 0; --k) {
         const bool m = (mk >> k) & 1u;
-        float ak = gl, bk = gamma * Z - vv[k];
-        if ((ew >> k) & 1u) {
-          const bool e = (ek >> k) & 1u;
-          ak = e ? 0.0f : ak;
-          bk = e ? (hv[k] + vv[k]) - vv[k] : bk;
-        }
+        float ak, bk;
+        step_map(has_e, k, Z, ak, bk);
         X = m ? bk + ak * X : X;
         Z = m ? vv[k] : Z;
         const float am = m ? X : 0.0f;
@@ -1509,16 +1490,20 @@ __global__ void __launch_bounds__(BT_T, BI_CTAS) bilevel_scan_bulk_kernel(int B,
         rt[k] = m ? X + vv[k] : 0.0f;
         s1 += am;
         s2 = fmaf(am, am, s2);
-        if ((ew >> k) & 1u) {  // a reward position off the loss mask keeps the turn-level pair (:70-71)
-          const bool only_e = !m && ((ek >> k) & 1u);
-          a[k] = only_e ? hv[k] : a[k];
-          rt[k] = only_e ? hv[k] + vv[k] : rt[k];
+        if constexpr (decltype(has_e)::value) {
+          if ((ew >> k) & 1u) {  // a reward position off the loss mask keeps the turn-level pair (:70-71)
+            const bool only_e = !m && ((ek >> k) & 1u);
+            a[k] = only_e ? hv[k] : a[k];
+            rt[k] = only_e ? hv[k] + vv[k] : rt[k];
+          }
         }
       }
-      m0 += (double)__popc(mk);
-      m1 += (double)s1;
-      m2 += (double)s2;
-    }
+    };
+    if (any_e) rewalk3(std::true_type{});
+    else rewalk3(std::false_type{});
+    m0 += (double)__popc(mk);
+    m1 += (double)s1;
+    m2 += (double)s2;
     reinterpret_cast<float4*>(S.r)[2 * tid] = make_float4(a[0], a[1], a[2], a[3]);
     reinterpret_cast<float4*>(S.r)[2 * tid + 1] = make_float4(a[4], a[5], a[6], a[7]);
     reinterpret_cast<float4*>(S.v)[2 * tid] = make_float4(rt[0], rt[1], rt[2], rt[3]);

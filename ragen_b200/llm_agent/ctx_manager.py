@@ -412,7 +412,8 @@ class ContextManager:
         }
         if messages_list is None:
             # the managers keep mutating these dicts (es_manager.py:212-228): the messages are those of THIS call
-            snapshot = [{"env_id": eo["env_id"], "history": [dict(h) for h in eo["history"]]} for eo in env_outputs]
+            # (only the LAST entry of a history is ever updated in place; the finished ones are shared, the list itself is copied)
+            snapshot = [{"env_id": eo["env_id"], "history": eo["history"][:-1] + [dict(eo["history"][-1])]} for eo in env_outputs]
             non_tensor = LazyBatch(non_tensor, "messages_list", lambda: np.array(
                 [self._messages_of(eo, prepare_for_update) for eo in snapshot], dtype=object))
         else:

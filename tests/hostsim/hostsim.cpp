@@ -11,6 +11,7 @@
 #include "../../ragen_b200/csrc/sokoban_solve_logic.cuh"
 #include <stdlib.h>
 #include "../../ragen_b200/csrc/toy_logic.cuh"
+#include "../../ragen_b200/csrc/scan_tiles.cuh"
 
 extern "C" {
 
@@ -213,3 +214,44 @@ int hs_sokoban_solve(const uint8_t* fixed, const uint8_t* state, int H, int W, i
 }
 
 }  // extern "C"
+
+// Tiles of the bulk-staged advantage scans (scan_tiles.cuh) over a [B, T] tensor with B * T % 16 == 0: cover[w] counts how often
+// flat word w is written by a tile's store plan (bulk range or edge words); returns the number of broken invariants.
+extern "C" int hs_scan_tiles(int B, int T, int32_t* cover, int32_t* n_tiles) {
+  using namespace scan_tiles;
+  const int64_t total = (int64_t)B * T;
+  int bad = 0, tiles = 0;
+  for (int row = 0; row < B; ++row) {
+    const int nc = row_chunks(row, T);
+    const int64_t lo = (int64_t)row * T, hi = lo + T;
+    int64_t expect_next = -1;  // chunks run right to left and are contiguous
+    for (int c = nc - 1; c >= 0; --c) {
+      const TileGeom g = geom(ScanTile{row, c}, T);
+      ++tiles;
+      if (g.cw0 % 4 != 0 || g.nw % 4 != 0 || g.nw <= 0 || g.nw > BT_W) ++bad;
+      if (g.cw0 < 0 || g.cw0 + g.nw > total) ++bad;                       // staged words inside the tensor
+      if (g.cw0 + g.rel_lo != lo || g.cw0 + g.rel_hi != hi) ++bad;         // the row, seen from the tile
+      if (g.right_end != (c == nc - 1)) ++bad;
+      if (expect_next >= 0 && g.cw0 + g.nw != expect_next) ++bad;
+      expect_next = g.cw0;
+      if (g.mshift != (int)(g.cw0 % 16) || g.mshift % 4 != 0) ++bad;
+      int64_t mb0, mb1;
+      mask_window(g, mb0, mb1);
+      if (mb0 % 16 != 0 || mb1 % 16 != 0 || mb0 < 0 || mb1 > total || mb0 > g.cw0 || mb1 < g.cw0 + g.nw || mb1 - mb0 > BT_W + 48) ++bad;
+      const StorePlan p = store_plan(g);
+      if (p.bulk) {
+        if ((g.cw0 + p.rs0) % 4 != 0 || (p.rs1 - p.rs0) % 4 != 0) ++bad;   // 16-byte aligned source and destination, whole groups
+        if (g.cw0 + p.rs0 < lo || g.cw0 + p.rs1 > hi) ++bad;               // never a word of another row
+        for (int w = p.rs0; w < p.rs1; ++w) ++cover[g.cw0 + w];
+        if (p.rs0 - p.ra0 > 3 || p.ra1 - p.rs1 > 3) ++bad;                 // at most three edge words on either side
+        for (int w = p.rs1; w < p.ra1; ++w) ++cover[g.cw0 + w];
+      } else if (p.ra1 - p.ra0 > 8) {
+        ++bad;                                                             // eight lanes store the words of a tile without a whole group
+      }
+      for (int w = p.ra0; w < p.left_end; ++w) ++cover[g.cw0 + w];
+    }
+    if (expect_next > lo) ++bad;  // the leftmost tile starts at or below the row's first word
+  }
+  *n_tiles = tiles;
+  return bad;
+}

@@ -21,7 +21,7 @@ c = ctypes
 @pytest.fixture(scope="session")
 def hs():
     src = os.path.join(HS_DIR, "hostsim.cpp")
-    deps = [src] + [os.path.join(ROOT, "ragen_b200", "csrc", f) for f in ("np_random.cuh", "parse_logic.cuh", "score_logic.cuh", "toy_logic.cuh", "mt19937.cuh", "sokoban_gen_logic.cuh")]
+    deps = [src] + [os.path.join(ROOT, "ragen_b200", "csrc", f) for f in ("np_random.cuh", "parse_logic.cuh", "score_logic.cuh", "toy_logic.cuh", "mt19937.cuh", "sokoban_gen_logic.cuh", "scan_tiles.cuh")]
     if not os.path.exists(HS_SO) or any(os.path.getmtime(d) > os.path.getmtime(HS_SO) for d in deps):
         subprocess.run(["g++", "-std=c++17", "-O2", "-shared", "-fPIC", "-o", HS_SO, src], check=True)
     lib = c.CDLL(HS_SO)
@@ -38,6 +38,8 @@ def hs():
     lib.hs_text_score.restype = c.c_int
     lib.hs_text_score.argtypes = [c.c_int, c.c_char_p, c.c_int, c.c_char_p, c.c_int]
     lib.hs_mt.argtypes = [c.c_uint64, c.c_uint32, c.c_int, c.c_void_p, c.c_void_p, c.c_void_p]
+    lib.hs_scan_tiles.restype = c.c_int
+    lib.hs_scan_tiles.argtypes = [c.c_int, c.c_int, c.c_void_p, c.c_void_p]
     lib.hs_sokoban_generate.argtypes = [c.c_int] * 5 + [c.c_uint64, c.c_int, c.c_void_p, c.c_void_p, c.c_void_p]
     return lib
 
@@ -417,3 +419,18 @@ def test_text_scores_flag_what_they_cannot_decide(hs):
     assert hs_score(hs, "exact_match", "\u00c9cole", "\u00e9cole")[2]            # Unicode case folding
     assert hs_score(hs, "numeric", "0.1000000000000000000001", "0.1")[2]          # > 15 significant digits
     assert not hs_score(hs, "numeric", "0.100", "0.1")[2]
+
+
+@pytest.mark.parametrize("B,T", [(128, 2047), (16, 1), (16, 3), (16, 5), (16, 7), (48, 2303), (16, 2304), (16, 2305), (32, 4097), (16, 6911),
+                                 (4112, 257), (8192, 2047), (64, 3000), (16, 4609), (80, 4607)])
+def test_scan_tiles_cover_every_token_once(hs, B, T):
+    """scan_tiles.cuh (the tile geometry of the bulk-staged advantage scans): over a [B, T] tensor with B * T % 16 == 0 the store
+    plans of all tiles write every word exactly once, bulk ranges are whole 16-byte groups inside their row, at most three edge
+    words per side, staged words and mask windows stay inside the tensor, the chunks of a row are contiguous."""
+    assert (B * T) % 16 == 0
+    cover = np.zeros(B * T, np.int32)
+    n_tiles = np.zeros(1, np.int32)
+    bad = hs.hs_scan_tiles(B, T, P(cover), P(n_tiles))
+    assert bad == 0
+    assert cover.min() == 1 and cover.max() == 1
+    assert int(n_tiles[0]) >= B * -(-T // 2304)

@@ -18,6 +18,8 @@
 // and saves H*W bytes of HBM traffic per env-step.
 //
 // HBM-bound by design: nothing here is a contraction, tensor cores are not used.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace {
@@ -298,6 +300,10 @@ __global__ void __launch_bounds__(TE, (PACK >= 3 && !RENDER_ONLY) ? 16 : 1) soko
   const int B3 = ((HW * 3 + 15) / 16) * 2;  // bytes of a three-bit row stream
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ __align__(8) uint64_t bar;
+  // the next kernel of the stream may be scheduled as soon as every CTA of this one has started; this one touches global memory
+  // only after the kernel before it has completed (launch_tiles)
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
 
   uint8_t* s_state = smem;
   uint8_t* s_obs = s_state + round16(STATE3 ? TE * B3 : STATE4 ? (TE * HW) >> 1 : TE * HW) + 16;  // +16: the render window may read one word past the tile
@@ -651,6 +657,19 @@ size_t tile_smem(int H, int W, int pack) {
   return (size_t)round16(pack == 3 ? TE * H * W / 2 : TE * H * W) + 16 + round16(glyph_bytes) + 16;
 }
 
+// Programmatic dependent launch: the tile kernels begin with griddepcontrol.launch_dependents + griddepcontrol.wait, and are
+// launched with programmaticStreamSerializationAllowed - the CTAs of a step are scheduled into the SM slots the previous kernel
+// of the stream vacates while it drains and sit at the wait until that kernel has completed and flushed (stream order as
+// before: nothing is read or written ahead of the wait), so the launch gap and the prologue of a launch run under the tail of
+// the one before.  RAGEN_PDL=0 launches the plain way.
+static bool pdl_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("RAGEN_PDL");
+    return !(e && e[0] == '0');
+  }();
+  return on;
+}
+
 template <bool RENDER_ONLY, int PACK>
 int launch_tiles(ragen_ctx* ctx, const StepParams& p, cudaStream_t stream) {
   RAGEN_REQUIRE(PACK != 1 || ((p.H * (p.W + 1)) & 1) == 0, "packed glyph rows need an even H*(W+1), got %dx%d", p.H, p.W);
@@ -663,7 +682,17 @@ int launch_tiles(ragen_ctx* ctx, const StepParams& p, cudaStream_t stream) {
   do {                                                                                              \
     auto kern = sokoban_tile_kernel<CH, CW, RENDER_ONLY, PACK>;                                            \
     RAGEN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
-    kern<<<grid, TE, smem, stream>>>(p);                                                            \
+    cudaLaunchConfig_t cfg = {};                                                                    \
+    cfg.gridDim = dim3(grid);                                                                       \
+    cfg.blockDim = dim3(TE);                                                                        \
+    cfg.dynamicSmemBytes = smem;                                                                    \
+    cfg.stream = stream;                                                                            \
+    cudaLaunchAttribute attr[1];                                                                    \
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;                                \
+    attr[0].val.programmaticStreamSerializationAllowed = 1;                                         \
+    cfg.attrs = attr;                                                                               \
+    cfg.numAttrs = pdl_enabled() ? 1 : 0;                                                           \
+    RAGEN_CUDA(cudaLaunchKernelEx(&cfg, kern, p));                                                  \
   } while (0)
   if (p.H == 6 && p.W == 6) RAGEN_TILE_LAUNCH(6, 6);
   else if (p.H == 8 && p.W == 8) RAGEN_TILE_LAUNCH(8, 8);

@@ -368,8 +368,22 @@ __global__ void __launch_bounds__(RT) grpo_scores_kernel(int B, int T, const flo
   const int row = blockIdx.x;
   const size_t base = (size_t)row * T;
   double s = 0.0;
-#pragma unroll 4
-  for (int t = threadIdx.x; t < T; t += RT) s += (double)__ldg(rewards + base + t);
+  // a row of an odd T starts anywhere: up to three tokens one by one until the address is 16-byte aligned, then 128-bit loads
+  const float* p = rewards + base;
+  const bool vec = (reinterpret_cast<uintptr_t>(rewards) & 15) == 0;
+  const int head = vec ? min((int)((4 - (base & 3)) & 3), T) : T;
+  for (int t = threadIdx.x; t < head; t += RT) s += (double)__ldg(p + t);
+  const int nv = (T - head) >> 2;
+  const float4* p4 = reinterpret_cast<const float4*>(p + head);
+#pragma unroll 2
+  for (int i = threadIdx.x; i < nv; i += RT) {
+    const float4 x = __ldg(p4 + i);
+    s += (double)x.x;
+    s += (double)x.y;
+    s += (double)x.z;
+    s += (double)x.w;
+  }
+  for (int t = head + 4 * nv + threadIdx.x; t < T; t += RT) s += (double)__ldg(p + t);
   s = block_sum(s);
   if (threadIdx.x == 0) {
     const float sf = (float)s;
@@ -416,8 +430,26 @@ __global__ void __launch_bounds__(RT) outcome_apply_kernel(int B, int T, const f
   const size_t base = (size_t)row * T;
   const float off = __fmul_rn(val, 0.0f);
   int on = 0;
-#pragma unroll 4
-  for (int t = threadIdx.x; t < T; t += RT) {
+  // token index and flat index agree for the mask bytes and the output words: the same up-to-three head tokens bring both to
+  // their alignment (4 bytes of mask, 16 bytes of output), then one mask word and one 128-bit store per four tokens
+  const bool vec = (reinterpret_cast<uintptr_t>(adv) & 15) == 0 && (reinterpret_cast<uintptr_t>(mask) & 3) == 0;
+  const int head = vec ? min((int)((4 - (base & 3)) & 3), T) : T;
+  for (int t = threadIdx.x; t < head; t += RT) {
+    const bool m = mask[base + t] != 0;
+    adv[base + t] = m ? val : off;
+    on += m;
+  }
+  const int nv = (T - head) >> 2;
+  const uint32_t* m4 = reinterpret_cast<const uint32_t*>(mask + base + head);
+  float4* a4 = reinterpret_cast<float4*>(adv + base + head);
+#pragma unroll 2
+  for (int i = threadIdx.x; i < nv; i += RT) {
+    const uint32_t mw = __ldg(m4 + i);
+    const bool b0 = (mw & 0xffu) != 0, b1 = (mw & 0xff00u) != 0, b2 = (mw & 0xff0000u) != 0, b3 = (mw & 0xff000000u) != 0;
+    a4[i] = make_float4(b0 ? val : off, b1 ? val : off, b2 ? val : off, b3 ? val : off);
+    on += (int)b0 + (int)b1 + (int)b2 + (int)b3;
+  }
+  for (int t = head + 4 * nv + threadIdx.x; t < T; t += RT) {
     const bool m = mask[base + t] != 0;
     adv[base + t] = m ? val : off;
     on += m;

@@ -47,7 +47,43 @@ def dev_time(fn, reps=20, warm=3, inner=1):
         b.record()
         torch.cuda.synchronize()
         ts.append(a.elapsed_time(b) / inner)
+    global _LAST_GRAPH_MS
+    _LAST_GRAPH_MS = graph_time(fn, reps, inner) if inner > 1 else None
     return float(np.median(ts))
+
+
+_LAST_GRAPH_MS = None
+
+
+def graph_time(fn, reps, inner):
+    """The same back-to-back calls captured once as a CUDA graph and replayed: GPU time only.  An op of two 15 us kernels issued from
+    Python is bound by its ~45 us of host work; the replay shows what the kernels take.  None when the op cannot be captured."""
+    try:
+        cur = torch.cuda.current_stream()
+        side = torch.cuda.Stream()
+        side.wait_stream(cur)
+        with torch.cuda.stream(side):
+            fn()
+        cur.wait_stream(side)
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=side):
+            for _ in range(inner):
+                fn()
+        g.replay()
+        torch.cuda.synchronize()
+        ts = []
+        for _ in range(reps):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            g.replay()
+            b.record()
+            torch.cuda.synchronize()
+            ts.append(a.elapsed_time(b) / inner)
+        return float(np.median(ts))
+    except Exception:
+        torch.cuda.synchronize()
+        return None
 
 
 def cpu_time(fn, budget_s=5.0, min_reps=1):
@@ -66,6 +102,12 @@ def line(row, unit, units, ms, bytes_per_unit, cpu_units_per_s=None, cpu_sample=
     out = {"row": row, "unit": unit, "units_per_launch": units, "ms": ms, "units_per_s": units / (ms * 1e-3),
            "bytes_per_unit": bytes_per_unit, "achieved_gbs": ach, "peak_gbs": peak_gbs(), "frac": ach / peak_gbs() if ach else None,
            "cpu_port_units_per_s": cpu_units_per_s, "cpu_sample": cpu_sample}
+    global _LAST_GRAPH_MS
+    if _LAST_GRAPH_MS is not None:  # the row's last timed op, replayed from a CUDA graph (GPU time without the host's share)
+        out["ms_graph"] = _LAST_GRAPH_MS
+        if bytes_per_unit:
+            out["frac_graph"] = bytes_per_unit * units / (_LAST_GRAPH_MS * 1e-3) / 1e9 / peak_gbs()
+        _LAST_GRAPH_MS = None
     out.update(extra)
     print(json.dumps(out), flush=True)
     return out

@@ -581,9 +581,8 @@ __global__ void __launch_bounds__(RT) kl_rewards_kernel(int B, int T, const floa
   const int row = blockIdx.x;
   const size_t base = (size_t)row * T;
   double ksum = 0.0, msum = 0.0;
-#pragma unroll 4
-  for (int t = threadIdx.x; t < T; t += RT) {
-    const float a = __ldg(logp + base + t), b = __ldg(ref + base + t);
+  // one token: the penalty term (masked), the token-level reward, the two row sums
+  auto token = [&](float a, float b, float sc, bool m) -> float {
     float k;
     if (mode == 0) {
       k = __fsub_rn(a, b);
@@ -597,12 +596,36 @@ __global__ void __launch_bounds__(RT) kl_rewards_kernel(int B, int T, const floa
       k = __fsub_rn(__fsub_rn(expf(d), d), 1.0f);
       k = fminf(fmaxf(k, -10.0f), 10.0f);
     }
-    const bool m = mask[base + t] != 0;
     k = m ? k : __fmul_rn(k, 0.0f);
-    out[base + t] = __fsub_rn(__ldg(scores + base + t), __fmul_rn(beta, k));
     ksum += (double)k;
     msum += m ? 1.0 : 0.0;
+    return __fsub_rn(sc, __fmul_rn(beta, k));
+  };
+  auto scalar = [&](int t) { out[base + t] = token(__ldg(logp + base + t), __ldg(ref + base + t), __ldg(scores + base + t), mask[base + t] != 0); };
+  // up to three head tokens bring all five arrays to their alignment at once (token index = flat index), then 128-bit accesses
+  const bool vec = ((reinterpret_cast<uintptr_t>(scores) | reinterpret_cast<uintptr_t>(logp) | reinterpret_cast<uintptr_t>(ref) |
+                     reinterpret_cast<uintptr_t>(out)) & 15) == 0 && (reinterpret_cast<uintptr_t>(mask) & 3) == 0;
+  const int head = vec ? min((int)((4 - (base & 3)) & 3), T) : T;
+  for (int t = threadIdx.x; t < head; t += RT) scalar(t);
+  const int nv = (T - head) >> 2;
+  const size_t vb = base + head;
+  const float4* a4 = reinterpret_cast<const float4*>(logp + vb);
+  const float4* b4 = reinterpret_cast<const float4*>(ref + vb);
+  const float4* s4 = reinterpret_cast<const float4*>(scores + vb);
+  const uint32_t* m4 = reinterpret_cast<const uint32_t*>(mask + vb);
+  float4* o4 = reinterpret_cast<float4*>(out + vb);
+#pragma unroll 2
+  for (int i = threadIdx.x; i < nv; i += RT) {
+    const float4 a = __ldg(a4 + i), b = __ldg(b4 + i), sc = __ldg(s4 + i);
+    const uint32_t mw = __ldg(m4 + i);
+    float4 o;
+    o.x = token(a.x, b.x, sc.x, (mw & 0xffu) != 0);
+    o.y = token(a.y, b.y, sc.y, (mw & 0xff00u) != 0);
+    o.z = token(a.z, b.z, sc.z, (mw & 0xff0000u) != 0);
+    o.w = token(a.w, b.w, sc.w, (mw & 0xff000000u) != 0);
+    o4[i] = o;
   }
+  for (int t = head + 4 * nv + threadIdx.x; t < T; t += RT) scalar(t);
   ksum = block_sum(ksum);
   msum = block_sum(msum);
   if (threadIdx.x == 0 && row_kl) row_kl[row] = (float)ksum / ((float)msum + 1e-8f);

@@ -362,30 +362,35 @@ __global__ void moments_kernel(int64_t n, const float* __restrict__ x, const uin
 
 // Outcome estimators, step 1: scores[b] = sum_t rewards[b][t] (fp64 accumulation, rounded once); per-group
 // {count, sum, sum of squares} (core_algos.py:139-149).  One CTA per row.
+// TPR threads per row: RT (one CTA per row - few rows, all SMs busy) or 32 (one warp per row, eight rows per CTA - thousands of
+// rows: a CTA per 8 KB row spends as long being scheduled and reducing across warps as streaming its row)
+template <int TPR>
 __global__ void __launch_bounds__(RT) grpo_scores_kernel(int B, int T, const float* __restrict__ rewards,
                                                          const int32_t* __restrict__ group, int n_groups,
                                                          float* __restrict__ scores, double* gstats) {
-  const int row = blockIdx.x;
+  const int row = blockIdx.x * (RT / TPR) + threadIdx.x / TPR;
+  const int tr = threadIdx.x % TPR;
+  if (TPR != RT && row >= B) return;  // whole warps (no CTA barrier on this path)
   const size_t base = (size_t)row * T;
   double s = 0.0;
   // a row of an odd T starts anywhere: up to three tokens one by one until the address is 16-byte aligned, then 128-bit loads
   const float* p = rewards + base;
   const bool vec = (reinterpret_cast<uintptr_t>(rewards) & 15) == 0;
   const int head = vec ? min((int)((4 - (base & 3)) & 3), T) : T;
-  for (int t = threadIdx.x; t < head; t += RT) s += (double)__ldg(p + t);
+  for (int t = tr; t < head; t += TPR) s += (double)__ldg(p + t);
   const int nv = (T - head) >> 2;
   const float4* p4 = reinterpret_cast<const float4*>(p + head);
-#pragma unroll 2
-  for (int i = threadIdx.x; i < nv; i += RT) {
+#pragma unroll 4
+  for (int i = tr; i < nv; i += TPR) {
     const float4 x = __ldg(p4 + i);
     s += (double)x.x;
     s += (double)x.y;
     s += (double)x.z;
     s += (double)x.w;
   }
-  for (int t = head + 4 * nv + threadIdx.x; t < T; t += RT) s += (double)__ldg(p + t);
-  s = block_sum(s);
-  if (threadIdx.x == 0) {
+  for (int t = head + 4 * nv + tr; t < T; t += TPR) s += (double)__ldg(p + t);
+  s = TPR == RT ? block_sum(s) : warp_sum(s);
+  if (tr == 0) {
     const float sf = (float)s;
     scores[row] = sf;
     const int g = group ? group[row] : -1;
@@ -401,11 +406,15 @@ __global__ void __launch_bounds__(RT) grpo_scores_kernel(int B, int T, const flo
 // (core_algos.py:150-165); 2: RLOO, score*n/(n-1) - mean*n/(n-1) for groups of n > 1 (:205-242); 3: REINFORCE++-baseline,
 // score - mean, to be whitened by the caller from `moments` (:168-202).  Groups of one use mean 0 (and std 1).  The value is
 // broadcast over the row and multiplied by the mask.
+template <int TPR>
 __global__ void __launch_bounds__(RT) outcome_apply_kernel(int B, int T, const float* __restrict__ scores,
                                                            const int32_t* __restrict__ group, int n_groups,
                                                            const double* __restrict__ gstats, const uint8_t* __restrict__ mask,
                                                            float eps, int mode, float* __restrict__ adv, double* moments) {
-  const int row = blockIdx.x;
+  const int row_raw = blockIdx.x * (RT / TPR) + threadIdx.x / TPR;
+  const int tr = threadIdx.x % TPR;
+  const bool live = row_raw < B;  // a warp past the last row writes nothing but stays for the CTA-wide moments
+  const int row = live ? row_raw : B - 1;
   const int g = group[row];
   float mean = 0.0f, sd = 1.0f, cnt = 1.0f;
   if (g >= 0 && g < n_groups) {
@@ -433,28 +442,46 @@ __global__ void __launch_bounds__(RT) outcome_apply_kernel(int B, int T, const f
   // token index and flat index agree for the mask bytes and the output words: the same up-to-three head tokens bring both to
   // their alignment (4 bytes of mask, 16 bytes of output), then one mask word and one 128-bit store per four tokens
   const bool vec = (reinterpret_cast<uintptr_t>(adv) & 15) == 0 && (reinterpret_cast<uintptr_t>(mask) & 3) == 0;
-  const int head = vec ? min((int)((4 - (base & 3)) & 3), T) : T;
-  for (int t = threadIdx.x; t < head; t += RT) {
+  const int Tl = live ? T : 0;
+  const int head = vec ? min((int)((4 - (base & 3)) & 3), Tl) : Tl;
+  for (int t = tr; t < head; t += TPR) {
     const bool m = mask[base + t] != 0;
     adv[base + t] = m ? val : off;
     on += m;
   }
-  const int nv = (T - head) >> 2;
+  const int nv = (Tl - head) >> 2;
   const uint32_t* m4 = reinterpret_cast<const uint32_t*>(mask + base + head);
   float4* a4 = reinterpret_cast<float4*>(adv + base + head);
-#pragma unroll 2
-  for (int i = threadIdx.x; i < nv; i += RT) {
+#pragma unroll 4
+  for (int i = tr; i < nv; i += TPR) {
     const uint32_t mw = __ldg(m4 + i);
     const bool b0 = (mw & 0xffu) != 0, b1 = (mw & 0xff00u) != 0, b2 = (mw & 0xff0000u) != 0, b3 = (mw & 0xff000000u) != 0;
     a4[i] = make_float4(b0 ? val : off, b1 ? val : off, b2 ? val : off, b3 ? val : off);
     on += (int)b0 + (int)b1 + (int)b2 + (int)b3;
   }
-  for (int t = head + 4 * nv + threadIdx.x; t < T; t += RT) {
+  for (int t = head + 4 * nv + tr; t < Tl; t += TPR) {
     const bool m = mask[base + t] != 0;
     adv[base + t] = m ? val : off;
     on += m;
   }
   if (moments) add_moments(moments, (double)on, (double)on * (double)val, (double)on * (double)val * (double)val);
+}
+
+// from this many rows on a warp per row (eight rows per CTA) beats a CTA per row
+constexpr int WARP_ROWS_MIN = 1024;
+static void launch_row_sums(cudaStream_t st, int B, int T, const float* rewards, const int32_t* group, int n_groups, float* scores,
+                            double* gstats) {
+  if (B >= WARP_ROWS_MIN)
+    grpo_scores_kernel<32><<<(B + RT / 32 - 1) / (RT / 32), RT, 0, st>>>(B, T, rewards, group, n_groups, scores, gstats);
+  else
+    grpo_scores_kernel<RT><<<B, RT, 0, st>>>(B, T, rewards, group, n_groups, scores, gstats);
+}
+static void launch_outcome_apply(cudaStream_t st, int B, int T, const float* scores, const int32_t* group, int n_groups,
+                                 const double* gstats, const uint8_t* mask, float eps, int mode, float* adv, double* moments) {
+  if (B >= WARP_ROWS_MIN)
+    outcome_apply_kernel<32><<<(B + RT / 32 - 1) / (RT / 32), RT, 0, st>>>(B, T, scores, group, n_groups, gstats, mask, eps, mode, adv, moments);
+  else
+    outcome_apply_kernel<RT><<<B, RT, 0, st>>>(B, T, scores, group, n_groups, gstats, mask, eps, mode, adv, moments);
 }
 
 // REINFORCE++ (core_algos.py:245-278): running = r_t + gamma * running, returns_t = running, running *= mask_t, right to
@@ -1925,10 +1952,9 @@ extern "C" int ragen_grpo_outcome(ragen_ctx* ctx, int B, int T, const float* rew
   double* gstats = (double*)ragen_scratch(ctx, bytes);
   if (!gstats) return RAGEN_ENOMEM;
   RAGEN_CUDA(cudaMemsetAsync(gstats, 0, bytes, st));
-  grpo_scores_kernel<<<B, RT, 0, st>>>(B, T, rewards, group, n_groups, scores, gstats);
+  launch_row_sums(st, B, T, rewards, group, n_groups, scores, gstats);
   RAGEN_LAUNCHED(ctx);
-  outcome_apply_kernel<<<B, RT, 0, st>>>(B, T, scores, group, n_groups, gstats, mask, (float)epsilon, norm_by_std ? 1 : 0, adv,
-                                         nullptr);
+  launch_outcome_apply(st, B, T, scores, group, n_groups, gstats, mask, (float)epsilon, norm_by_std ? 1 : 0, adv, nullptr);
   RAGEN_LAUNCHED(ctx);
   return RAGEN_OK;
 }
@@ -1947,10 +1973,9 @@ extern "C" int ragen_outcome_advantage(ragen_ctx* ctx, int B, int T, const float
   double* gstats = (double*)ragen_scratch(ctx, bytes);
   if (!gstats) return RAGEN_ENOMEM;
   RAGEN_CUDA(cudaMemsetAsync(gstats, 0, bytes, st));
-  grpo_scores_kernel<<<B, RT, 0, st>>>(B, T, rewards, group, n_groups, scores, gstats);
+  launch_row_sums(st, B, T, rewards, group, n_groups, scores, gstats);
   RAGEN_LAUNCHED(ctx);
-  outcome_apply_kernel<<<B, RT, 0, st>>>(B, T, scores, group, n_groups, gstats, mask, (float)epsilon,
-                                                                  mode, adv, moments);
+  launch_outcome_apply(st, B, T, scores, group, n_groups, gstats, mask, (float)epsilon, mode, adv, moments);
   RAGEN_LAUNCHED(ctx);
   return RAGEN_OK;
 }
@@ -2061,7 +2086,7 @@ extern "C" int ragen_group_filter_stats(ragen_ctx* ctx, int n_groups, int group_
   if (n_groups == 0) return RAGEN_OK;
   DeviceGuard guard(ctx->device);
   cudaStream_t st = (cudaStream_t)stream;
-  grpo_scores_kernel<<<n_groups * group_size, RT, 0, st>>>(n_groups * group_size, T, scores, nullptr, 0, row_sum, nullptr);
+  launch_row_sums(st, n_groups * group_size, T, scores, nullptr, 0, row_sum, nullptr);
   RAGEN_LAUNCHED(ctx);
   group_stats_kernel<<<(n_groups + 127) / 128, 128, 0, st>>>(n_groups, group_size, row_sum, gstd, gmax, gmean);
   RAGEN_LAUNCHED(ctx);

@@ -346,3 +346,31 @@ def test_reinforce_pp_and_remax_as_block_scans_are_within_the_bar(B, T):
     close(adv, want_adv, per_element=False)
     exact_adv, exact_ret = ops.remax(rewards.cuda(), mask.cuda(), base.cuda())
     close(exact_ret, want_ret, per_element=False)
+
+
+@pytest.mark.parametrize("B,T,gsz", [(1030, 301, 10), (2048, 2047, 16)])
+def test_outcome_estimators_with_a_warp_per_row(B, T, gsz):
+    """From 1024 rows on the row sums and the broadcast run with a warp per row (eight rows per CTA; the last CTA of 1030 rows is
+    ragged): GRPO with and without std, RLOO, REINFORCE++-baseline (whitened) and the StarPO-S filter statistics vs the oracle."""
+    from ragen_b200 import ops
+
+    gen = torch.Generator().manual_seed(B + T)
+    rewards = torch.zeros(B, T)
+    rewards[torch.arange(B), torch.randint(0, T, (B,), generator=gen)] = torch.randn(B, generator=gen)
+    mask = (torch.rand(B, T, generator=gen) > 0.4).float()
+    index = [i // gsz for i in range(B)]
+    ng = index[-1] + 1
+    gi = dev(index, torch.int32)
+    for by_std in (True, False):
+        adv, scores = ops.grpo_outcome(rewards.cuda(), mask.cuda(), gi, ng, 1e-6, by_std)
+        want, _ = A.grpo_outcome(rewards, mask, index, norm_by_std=by_std)
+        close(adv, want)
+        close(scores, rewards.sum(-1))
+    adv, _, _ = ops.outcome_advantage(rewards.cuda(), mask.cuda(), gi, ng, "rloo")
+    close(adv, A.rloo(rewards, mask, index))
+    adv, _, mom = ops.outcome_advantage(rewards.cuda(), mask.cuda(), gi, ng, "rfpp_baseline", want_moments=True)
+    close(ops.whiten_(adv, mom), A.rfpp_baseline(rewards, mask, index), per_element=False)  # masked_whiten of the tiled scores (:200)
+    if B % gsz == 0:
+        row, std, mx, mean = ops.group_filter_stats(rewards.cuda(), ng, gsz)
+        wstd, wmx, wmean = A.group_filter_stats(rewards, ng, gsz)
+        close(std, wstd); close(mx, wmx); close(mean, wmean); close(row, rewards.sum(-1))
